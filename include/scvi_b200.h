@@ -1,0 +1,214 @@
+/*
+ * scvi_b200.h -- C ABI of the B200-native SCVI VAE minibatch training hot path.
+ *
+ * The reference (scverse/scvi-tools v1.5.0.post1) is pure Python/PyTorch and has NO FFI for
+ * this path; its boundary is the Python class surface.  This header is
+ * the ABI a maintainer binds UNDER that surface (ctypes stub in INTEGRATION.md): each entry
+ * point names the reference code it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer unless the name ends in `_host`; row-major; fp32
+ *    values, int64 row / category indices (the reference's dtypes: src/scvi/data/_utils.py:37-47)
+ *  - `stream` is a `cudaStream_t` passed as `void*` (NULL = legacy default stream)
+ *  - every function returns 0 on success, a negative SCVI_E* code otherwise; it never
+ *    throws, never exits, never synchronises the device; `scvi_last_error_string()` holds the
+ *    message of the calling thread's last failure
+ *  - the library allocates nothing persistent: all buffers (workspaces too) are caller-owned
+ *  - "BN tile" = SCVI_BN_TILE consecutive rows; kernels that produce a pre-BatchNorm
+ *    activation also emit per-tile column statistics (mean, M2) merged later by
+ *    scvi_bn_finalize (Chan's parallel variance; deterministic)
+ */
+#ifndef SCVI_B200_H
+#define SCVI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCVI_OK 0
+#define SCVI_EINVAL (-1)   /* bad argument (shape, alignment, NULL) */
+#define SCVI_ECUDA (-2)    /* CUDA runtime error at launch */
+#define SCVI_EUNSUPPORTED (-3) /* configuration outside what the kernels implement */
+
+#define SCVI_BN_TILE 64
+
+/* likelihood selector: reference `gene_likelihood` (src/scvi/module/_vae.py:520-528) */
+#define SCVI_LIK_NB 0
+#define SCVI_LIK_ZINB 1
+
+/* scvi_linear_fwd / _bwd flags */
+#define SCVI_LIN_LOG1P 1   /* input is log1p(x)   (src/scvi/module/_vae.py:373-374) */
+#define SCVI_LIN_LIBRARY 2 /* also emit library = log(sum_g x)  (src/scvi/module/_vae.py:371-372) */
+
+/* GEMM arithmetic of the fused decoder kernels */
+#define SCVI_PREC_FP32 0   /* FFMA, fp32 everywhere: the parity path */
+#define SCVI_PREC_TC 1     /* tcgen05 tensor-core path (when built) */
+
+int scvi_b200_abi_version(void);
+const char* scvi_last_error_string(void);
+
+/* ---- a1: minibatch row gather --------------------------------------------------------
+ * replaces AnnTorchDataset.__getitem__ (src/scvi/data/_anntorchdataset.py:115-169,
+ * `data[indexes].astype(float32)`) + the Lightning host->device copy, and
+ * _DeviceBackedDataset.__getitem__ (src/scvi/dataloaders/_data_splitting.py:589-732).
+ * out[b, :] = X[idx[b], :] bit-exactly.  idx values must lie in [0, n_rows). */
+int scvi_gather_rows(const float* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx,
+                     int64_t B, float* out, int64_t ldo, void* stream);
+/* out[b] = src[idx[b]] for the int64 `batch` / `labels` columns (shape (B,1) in the reference) */
+int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int64_t B, int64_t* out,
+                    void* stream);
+/* same gather from a uint16-compressed resident matrix (counts < 65536), densified to fp32 */
+int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t ldx,
+                         const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
+
+/* ---- a7/a8: standalone likelihood kernels ("NB-loss kernel") --------------------------
+ * replace log_nb_positive / log_zinb_positive
+ * (src/scvi/distributions/_negative_binomial.py:99-135, :36-96) as called by
+ * NegativeBinomial.log_prob (:445-459) / ZeroInflatedNegativeBinomial.log_prob (:573-586).
+ * x, mu, pi, out are [B,G] with row strides ld*; theta is [G] (theta_ld = 0) or [B,G].
+ * eps is the reference's 1e-8.  `bad_support` (nullable, int32[1]) is set to 1 if any x is
+ * negative or non-integer -- the lazily raised counterpart of _validate_sample (:575-582). */
+int scvi_nb_logprob_fwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu, const float* theta,
+                        int64_t theta_ld, int64_t B, int64_t G, float eps, float* out, int64_t ldo,
+                        int32_t* bad_support, void* stream);
+int scvi_zinb_logprob_fwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu,
+                          const float* theta, int64_t theta_ld, const float* pi, int64_t ldpi,
+                          int64_t B, int64_t G, float eps, float* out, int64_t ldo,
+                          int32_t* bad_support, void* stream);
+/* backward: gout is d(loss)/d(out) [B,G]; writes dmu, (dpi) [B,G] and dtheta either [B,G]
+ * (theta_ld != 0) or per-row-tile partials [ceil(B/SCVI_BN_TILE), G] to be summed by
+ * scvi_colsum_partials (theta_ld == 0).  Any of dmu/dtheta/dpi may be NULL (skipped). */
+int scvi_nb_logprob_bwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu, const float* theta,
+                        int64_t theta_ld, const float* gout, int64_t ldg, int64_t B, int64_t G,
+                        float eps, float* dmu, float* dtheta, void* stream);
+int scvi_zinb_logprob_bwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu,
+                          const float* theta, int64_t theta_ld, const float* pi, int64_t ldpi,
+                          const float* gout, int64_t ldg, int64_t B, int64_t G, float eps, float* dmu,
+                          float* dtheta, float* dpi, void* stream);
+/* out[n] = sum_t partials[t, n] in fixed order (deterministic) */
+int scvi_colsum_partials(const float* partials, int64_t n_tiles, int64_t N, float* out, int accumulate,
+                         void* stream);
+
+/* ---- a2/a3: FCLayers linear layer with covariate injection ----------------------------
+ * replaces, per layer, `torch.cat((x, one_hot(cat)...))` + nn.Linear
+ * (src/scvi/nn/_base_components.py:148-188,198-215) and for the encoder input the pre-ops
+ * `library = log(x.sum(1))`, `x_ = log1p(x)` (src/scvi/module/_vae.py:370-374).
+ *   y[b, n] = sum_k f(x[r(b), k]) * W[n, k] + sum_c W[n, cov_cols[b, c]] + bias[n]
+ * with r(b) = row_idx ? row_idx[b] : b (reads straight from the resident count matrix),
+ * f = log1p when SCVI_LIN_LOG1P.  The one-hot concat becomes a weight-column gather:
+ * cov_cols[b, c] is the absolute column of W (>= K) selected by covariate c of cell b.
+ * bn_partials (nullable) [ceil(B/SCVI_BN_TILE), 2, N] receives per-tile (mean, M2) of y. */
+int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+                    const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols,
+                    int n_cov, int flags, float* y, int64_t ldy, float* library, float* bn_partials,
+                    void* stream);
+/* backward of the above.  dW [N, ldw] (all K + covariate columns are written: covariate
+ * columns receive the per-category column sums of dy -- the one-hot GEMM as a segmented
+ * sum), db [N] (nullable), dx [B,K] (nullable; not available with SCVI_LIN_LOG1P).
+ * `ws` is a caller-owned workspace of scvi_linear_bwd_ws_bytes() bytes (split-B partial
+ * slabs reduced in fixed order: deterministic, no atomics).  n_w_cols = total columns of W. */
+int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols);
+int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+                    const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov,
+                    int flags, const float* dy, int64_t lddy, float* dW, float* db, float* dx,
+                    int64_t lddx, void* ws, void* stream);
+
+/* ---- a3: BatchNorm1d(momentum .01, eps 1e-3) + ReLU + Dropout --------------------------
+ * replaces nn.BatchNorm1d / nn.ReLU / nn.Dropout of FCLayers._build_layer
+ * (src/scvi/nn/_base_components.py:102-115).
+ * scvi_bn_finalize: training != 0: merge tile partials -> batch mean, rstd = 1/sqrt(var_b+eps),
+ *   and running <- (1-momentum)*running + momentum*{mean, unbiased var} (nullable buffers);
+ *   training == 0: mean = running_mean, rstd = 1/sqrt(running_var+eps). */
+int scvi_bn_finalize(const float* bn_partials, int64_t B, int64_t N, int training, float eps, float momentum,
+                     float* running_mean, float* running_var, float* mean, float* rstd, void* stream);
+/* standalone tile statistics for a [B,N] activation produced elsewhere */
+int scvi_bn_partials(const float* y, int64_t ldy, int64_t B, int64_t N, float* bn_partials, void* stream);
+/* a = keep * drop_scale * act(gamma * (y - mean) * rstd + beta); mean/rstd/gamma/beta NULL => no
+ * norm; relu = 0 => no activation; drop_mask (uint8 keep-mask, nullable) => no dropout. */
+int scvi_bn_act_drop_fwd(const float* y, int64_t ldy, int64_t B, int64_t N, const float* mean,
+                         const float* rstd, const float* gamma, const float* beta, int relu,
+                         const uint8_t* drop_mask, float drop_scale, float* a, int64_t lda, void* stream);
+/* full backward (through the batch statistics when training != 0).  `ws` holds
+ * scvi_bn_bwd_ws_bytes() bytes.  dgamma/dbeta nullable. */
+int64_t scvi_bn_bwd_ws_bytes(int64_t B, int64_t N);
+int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t ldy, int64_t B, int64_t N,
+                         const float* mean, const float* rstd, const float* gamma, const float* beta,
+                         int relu, const uint8_t* drop_mask, float drop_scale, int training, float* dy,
+                         int64_t lddy, float* dgamma, float* dbeta, void* ws, void* stream);
+
+/* ---- a4/a9: latent heads, reparameterisation, Normal KL -------------------------------
+ * replaces Encoder.forward's heads (src/scvi/nn/_base_components.py:311-317):
+ *   q_m = a Wm^T + bm;  q_v = exp(a Wv^T + bv) + var_eps;  z = q_m + sqrt(q_v) * noise
+ * and kl_divergence(Normal(q_m, sqrt(q_v)), Normal(0,1)).sum(-1) (src/scvi/module/_vae.py:563-565).
+ * L <= 32. */
+int scvi_latent_fwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L, const float* Wm,
+                    const float* bm, const float* Wv, const float* bv, const float* noise, float var_eps,
+                    float* q_m, float* q_v, float* z, float* kl, void* stream);
+/* upstream grads g_* nullable ([B,L] for q_m/q_v/z, [B] for kl).  Writes da [B,H], dWm/dWv [L,H],
+ * dbm/dbv [L].  ws: scvi_latent_bwd_ws_bytes(). */
+int64_t scvi_latent_bwd_ws_bytes(int64_t B, int64_t H, int64_t L);
+int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L, const float* Wm,
+                    const float* Wv, const float* noise, float var_eps, const float* q_m,
+                    const float* q_v, const float* g_qm, const float* g_qv, const float* g_z,
+                    const float* g_kl, float* da, int64_t ldda, float* dWm, float* dbm, float* dWv,
+                    float* dbv, void* ws, void* stream);
+
+/* ---- a5/a6/a7/a8/a9: fused decoder heads + softmax + library scaling + NB/ZINB NLL ----
+ * replaces DecoderSCVI.forward's heads (src/scvi/nn/_base_components.py:436-441:
+ * px_scale = softmax(Linear(h)), px_dropout = Linear(h), px_rate = exp(library) * px_scale),
+ * `px_r = exp(self.px_r)` (src/scvi/module/_vae.py:516-518), the distribution's log_prob
+ * (log_zinb_positive / log_nb_positive) and `-log_prob(x).sum(-1)` (_vae.py:571).
+ * The [B,G] tensors px_scale / px_rate / px_dropout / log_prob are never written to HBM.
+ *   h [B,H]; Ws, Wp [G,H] (scale / dropout heads; Wp, bp NULL for NB); px_r [G];
+ *   x rows via row_idx as in scvi_linear_fwd; library [B].
+ * Outputs: reconst [B]; row_stats [B,4] = (row max of scale logits, sum exp(logit-max),
+ *   exp(library)/sumexp, S = sum_g mu * d(reconst)/d(mu)) consumed by the backward. */
+int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
+                         const float* bs, const float* Wp, const float* bp, const float* px_r,
+                         const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
+                         int likelihood, int precision, float* reconst, float* row_stats, void* stream);
+/* g_reconst [B] = d(loss)/d(reconst).  Writes dh [B,H], dWs/dWp [G,H], dbs/dbp [G], dpx_r [G].
+ * ws: scvi_decoder_nll_bwd_ws_bytes(). */
+int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
+int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
+                         const float* bs, const float* Wp, const float* bp, const float* px_r,
+                         const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
+                         const float* row_stats, const float* g_reconst, int likelihood, int precision,
+                         float* dh, int64_t lddh, float* dWs, float* dbs, float* dWp, float* dbp,
+                         float* dpx_r, void* ws, void* stream);
+/* materialising variant for inference-time getters (px.scale / px.mu / px.zi_logits):
+ * any of the three outputs may be NULL. */
+int scvi_decoder_params_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
+                            const float* bs, const float* Wp, const float* bp, const float* library,
+                            float* px_scale, float* px_rate, float* px_dropout, int64_t ldo, void* stream);
+
+/* ---- a12: multi-tensor Adam over one flat arena ---------------------------------------
+ * replaces torch.optim.Adam(lr=1e-3, eps=0.01, weight_decay=1e-6) built by
+ * TrainingPlan.configure_optimizers (src/scvi/train/_trainingplans.py:475-482,497-519):
+ * coupled L2, bias correction, same op order as torch's single-tensor path.
+ * `step` is the 1-based step count; grad_scale multiplies g first (1/world for the DDP mean). */
+int scvi_adam_step(float* p, const float* g, float* m, float* v, int64_t n, int64_t step, float lr,
+                   float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                   void* stream);
+/* CUDA-graph friendly variant: the 1-based step is `*step_counter + 1` read on the device; the
+ * counter is incremented after the update, so a captured graph replays with the right bias
+ * correction every time. */
+int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, int64_t* step_counter,
+                         float lr, float beta1, float beta2, float eps, float weight_decay,
+                         float grad_scale, void* stream);
+/* loss pieces of VAE.loss (src/scvi/module/_vae.py:573-580):
+ * out[0] = mean_b(reconst + kl_weight * kl), out[1] = sum reconst, out[2] = sum kl.
+ * kl_weight_dev (nullable, device float[1]) overrides `kl_weight` (graph replay: the KL warm-up
+ * weight of src/scvi/train/_trainingplans.py:521-532 changes per epoch without re-capture). */
+int scvi_elbo_reduce(const float* reconst, const float* kl, int64_t B, float kl_weight,
+                     const float* kl_weight_dev, float* out3, void* stream);
+/* backward seeds of that mean: g_reconst[b] = scale / B, g_kl[b] = scale * kl_weight / B */
+int scvi_elbo_seed(int64_t B, float kl_weight, const float* kl_weight_dev, float scale, float* g_reconst,
+                   float* g_kl, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCVI_B200_H */

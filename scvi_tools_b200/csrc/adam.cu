@@ -1,0 +1,152 @@
+// Multi-tensor Adam over one flat fp32 arena + ELBO reduction / seeding.
+// Replaces torch.optim.Adam(lr=1e-3, eps=0.01, weight_decay=1e-6) as configured by
+// TrainingPlan.configure_optimizers (reference src/scvi/train/_trainingplans.py:475-482,497-519)
+// -- coupled L2, bias correction, op order of torch's single-tensor path -- and the
+// mean over the minibatch in VAE.loss (src/scvi/module/_vae.py:573-580).
+// HBM-bound: 28 bytes per parameter (read p, g, m, v; write p, m, v).
+#include "common.cuh"
+
+namespace scvi {
+
+__device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, float grad_scale, float wd,
+                                          float beta1, float beta2, float step_size, float bc2_sqrt, float eps) {
+  g = g * grad_scale;
+  g = fmaf(wd, p, g);                          // grad.add(param, alpha=weight_decay)
+  m = m + (g - m) * (1.f - beta1);             // exp_avg.lerp_(grad, 1 - beta1)
+  v = v * beta2 + (1.f - beta2) * g * g;       // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1-beta2)
+  const float denom = sqrtf(v) / bc2_sqrt + eps;
+  p = p - step_size * (m / denom);             // param.addcdiv_(exp_avg, denom, value=-step_size)
+}
+
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, int64_t n, const int64_t* __restrict__ step_counter,
+                            int64_t step_host, float lr, float beta1, float beta2, float eps, float wd,
+                            float grad_scale) {
+  const int64_t step = step_counter ? (*step_counter + 1) : step_host;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  const float step_size = (float)((double)lr / bc1);
+  const float bc2_sqrt = (float)sqrt(bc2);
+  const int64_t n4 = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+    float4 pp = reinterpret_cast<float4*>(p)[i];
+    const float4 gg = reinterpret_cast<const float4*>(g)[i];
+    float4 mm = reinterpret_cast<float4*>(m)[i];
+    float4 vv = reinterpret_cast<float4*>(v)[i];
+    adam_elem(pp.x, gg.x, mm.x, vv.x, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_elem(pp.y, gg.y, mm.y, vv.y, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_elem(pp.z, gg.z, mm.z, vv.z, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_elem(pp.w, gg.w, mm.w, vv.w, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    reinterpret_cast<float4*>(p)[i] = pp;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+  }
+  for (int64_t i = 4 * n4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    adam_elem(p[i], g[i], m[i], v[i], grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+}
+
+__global__ void counter_inc_kernel(int64_t* c) { *c += 1; }
+
+// out[0] = mean(reconst + klw * kl), out[1] = sum reconst, out[2] = sum kl  (single block, fixed order)
+__global__ void elbo_reduce_kernel(const float* __restrict__ reconst, const float* __restrict__ kl, int64_t B,
+                                   float klw_host, const float* __restrict__ klw_dev, float* __restrict__ out) {
+  __shared__ float sh[3][32];
+  const float klw = klw_dev ? *klw_dev : klw_host;
+  float a = 0.f, r = 0.f, k = 0.f;
+  for (int64_t i = threadIdx.x; i < B; i += blockDim.x) {
+    const float rv = reconst[i], kv = kl[i];
+    a += rv + klw * kv;
+    r += rv;
+    k += kv;
+  }
+  a = warp_sum(a);
+  r = warp_sum(r);
+  k = warp_sum(k);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) {
+    sh[0][w] = a;
+    sh[1][w] = r;
+    sh[2][w] = k;
+  }
+  __syncthreads();
+  if (w == 0) {
+    const int nw = blockDim.x >> 5;
+    a = lane < nw ? sh[0][lane] : 0.f;
+    r = lane < nw ? sh[1][lane] : 0.f;
+    k = lane < nw ? sh[2][lane] : 0.f;
+    a = warp_sum(a);
+    r = warp_sum(r);
+    k = warp_sum(k);
+    if (lane == 0) {
+      out[0] = a / (float)B;
+      out[1] = r;
+      out[2] = k;
+    }
+  }
+}
+
+__global__ void elbo_seed_kernel(int64_t B, float klw_host, const float* __restrict__ klw_dev, float scale,
+                                 float* __restrict__ g_reconst, float* __restrict__ g_kl) {
+  const float klw = klw_dev ? *klw_dev : klw_host;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < B) {
+    const float s = scale / (float)B;
+    g_reconst[i] = s;
+    g_kl[i] = s * klw;
+  }
+}
+
+static int adam_launch(float* p, const float* g, float* m, float* v, int64_t n, int64_t* counter, int64_t step,
+                       float lr, float beta1, float beta2, float eps, float wd, float grad_scale, void* stream,
+                       const char* name) {
+  SCVI_REQUIRE(p && g && m && v && n >= 0, "%s: bad argument", name);
+  SCVI_REQUIRE(((uintptr_t)p % 16 == 0) && ((uintptr_t)g % 16 == 0) && ((uintptr_t)m % 16 == 0) &&
+                   ((uintptr_t)v % 16 == 0),
+               "%s: arenas must be 16-byte aligned", name);
+  SCVI_REQUIRE(counter || step >= 1, "%s: step must be >= 1", name);
+  if (n == 0) return SCVI_OK;
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(cdiv(n, 4), 256), 148 * 8);
+  adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, counter, step, lr, beta1, beta2, eps, wd, grad_scale);
+  SCVI_LAUNCH_CHECK(name);
+  if (counter) {
+    counter_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter);
+    SCVI_LAUNCH_CHECK(name);
+  }
+  return SCVI_OK;
+}
+
+}  // namespace scvi
+
+extern "C" {
+
+int scvi_adam_step(float* p, const float* g, float* m, float* v, int64_t n, int64_t step, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, float grad_scale, void* stream) {
+  return scvi::adam_launch(p, g, m, v, n, nullptr, step, lr, beta1, beta2, eps, weight_decay, grad_scale, stream, "scvi_adam_step");
+}
+
+int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, int64_t* step_counter, float lr,
+                         float beta1, float beta2, float eps, float weight_decay, float grad_scale, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(step_counter, "scvi_adam_step_graph: NULL step counter");
+  return adam_launch(p, g, m, v, n, step_counter, 0, lr, beta1, beta2, eps, weight_decay, grad_scale, stream, "scvi_adam_step_graph");
+}
+
+int scvi_elbo_reduce(const float* reconst, const float* kl, int64_t B, float kl_weight, const float* kl_weight_dev,
+                     float* out3, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(reconst && kl && out3 && B > 0, "scvi_elbo_reduce: bad argument");
+  elbo_reduce_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(reconst, kl, B, kl_weight, kl_weight_dev, out3);
+  SCVI_LAUNCH_CHECK("scvi_elbo_reduce");
+  return SCVI_OK;
+}
+
+int scvi_elbo_seed(int64_t B, float kl_weight, const float* kl_weight_dev, float scale, float* g_reconst, float* g_kl,
+                   void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(g_reconst && g_kl && B > 0, "scvi_elbo_seed: bad argument");
+  elbo_seed_kernel<<<(unsigned)cdiv(B, 256), 256, 0, (cudaStream_t)stream>>>(B, kl_weight, kl_weight_dev, scale, g_reconst, g_kl);
+  SCVI_LAUNCH_CHECK("scvi_elbo_seed");
+  return SCVI_OK;
+}
+}

@@ -1,0 +1,223 @@
+// BatchNorm1d(momentum 0.01, eps 1e-3) + ReLU + Dropout of FCLayers._build_layer
+// (reference src/scvi/nn/_base_components.py:102-115), forward and full backward.
+// Statistics are computed as per-tile (mean, M2) partials merged with Chan's parallel
+// variance formula: deterministic, two-pass accuracy inside a tile, no atomics.
+#include "common.cuh"
+
+namespace scvi {
+
+// ---- statistics ------------------------------------------------------------------------
+__global__ void bn_partials_kernel(const float* __restrict__ y, int64_t ldy, int64_t B, int64_t N,
+                                   float* __restrict__ part) {
+  // 64 threads = 64 columns; one block per (row tile, 64-column group)
+  const int64_t n = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
+  const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
+  if (n >= N) return;
+  float s = 0.f;
+  for (int r = 0; r < cnt; ++r) s += y[(r0 + r) * ldy + n];
+  const float mean = s / (float)cnt;
+  float m2 = 0.f;
+  for (int r = 0; r < cnt; ++r) {
+    const float d = y[(r0 + r) * ldy + n] - mean;
+    m2 = fmaf(d, d, m2);
+  }
+  part[((int64_t)blockIdx.x * 2 + 0) * N + n] = mean;
+  part[((int64_t)blockIdx.x * 2 + 1) * N + n] = m2;
+}
+
+__global__ void bn_finalize_kernel(const float* __restrict__ part, int64_t B, int64_t N, int training, float eps,
+                                   float momentum, float* __restrict__ run_mean, float* __restrict__ run_var,
+                                   float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  if (!training) {
+    mean_out[n] = run_mean[n];
+    rstd_out[n] = 1.f / sqrtf(run_var[n] + eps);
+    return;
+  }
+  const int64_t T = (B + SCVI_BN_TILE - 1) / SCVI_BN_TILE;
+  float cnt = 0.f, mean = 0.f, m2 = 0.f;
+  for (int64_t t = 0; t < T; ++t) {
+    const float cb = (float)min((int64_t)SCVI_BN_TILE, B - t * SCVI_BN_TILE);
+    const float mb = part[(t * 2 + 0) * N + n];
+    const float m2b = part[(t * 2 + 1) * N + n];
+    const float tot = cnt + cb;
+    const float delta = mb - mean;
+    mean += delta * (cb / tot);
+    m2 += m2b + delta * delta * (cnt * cb / tot);
+    cnt = tot;
+  }
+  const float var_b = m2 / cnt;
+  mean_out[n] = mean;
+  rstd_out[n] = 1.f / sqrtf(var_b + eps);
+  if (run_mean) run_mean[n] = (1.f - momentum) * run_mean[n] + momentum * mean;
+  if (run_var) run_var[n] = (1.f - momentum) * run_var[n] + momentum * (m2 / fmaxf(cnt - 1.f, 1.f));
+}
+
+// ---- forward apply -----------------------------------------------------------------------
+__global__ void bn_act_drop_fwd_kernel(const float* __restrict__ y, int64_t ldy, int64_t B, int64_t N,
+                                       const float* __restrict__ mean, const float* __restrict__ rstd,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta, int relu,
+                                       const uint8_t* __restrict__ mask, float drop_scale, float* __restrict__ a,
+                                       int64_t lda) {
+  const int64_t total = B * N;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = e / N, n = e % N;
+    float v = y[b * ldy + n];
+    if (mean) {
+      const float g = gamma ? gamma[n] : 1.f;
+      v = (v - mean[n]) * (rstd[n] * g) + (beta ? beta[n] : 0.f);
+    }
+    if (relu) v = fmaxf(v, 0.f);
+    if (mask) v = mask[e] ? v * drop_scale : 0.f;
+    a[b * lda + n] = v;
+  }
+}
+
+// ---- backward ------------------------------------------------------------------------------
+// du = da * keep*scale * 1[u>0];  partial column sums of du and du*xhat per row tile
+__global__ void bn_bwd_reduce_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y,
+                                     int64_t ldy, int64_t B, int64_t N, const float* __restrict__ mean,
+                                     const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                     const float* __restrict__ beta, int relu, const uint8_t* __restrict__ mask,
+                                     float drop_scale, float* __restrict__ part /*[T][2][N]*/) {
+  const int64_t n = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
+  const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
+  if (n >= N) return;
+  const float mu = mean[n], rs = rstd[n];
+  const float g = gamma ? gamma[n] : 1.f, bt = beta ? beta[n] : 0.f;
+  float s1 = 0.f, s2 = 0.f;
+  for (int r = 0; r < cnt; ++r) {
+    const int64_t b = r0 + r;
+    const float xhat = (y[b * ldy + n] - mu) * rs;
+    const float u = xhat * g + bt;
+    float d = da[b * ldda + n];
+    if (mask) d = mask[b * N + n] ? d * drop_scale : 0.f;
+    if (relu && !(u > 0.f)) d = 0.f;
+    s1 += d;
+    s2 = fmaf(d, xhat, s2);
+  }
+  part[((int64_t)blockIdx.x * 2 + 0) * N + n] = s1;
+  part[((int64_t)blockIdx.x * 2 + 1) * N + n] = s2;
+}
+
+__global__ void bn_bwd_sums_kernel(const float* __restrict__ part, int64_t T, int64_t N, float* __restrict__ sums,
+                                   float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float s1 = 0.f, s2 = 0.f;
+  for (int64_t t = 0; t < T; ++t) {
+    s1 += part[(t * 2 + 0) * N + n];
+    s2 += part[(t * 2 + 1) * N + n];
+  }
+  sums[n] = s1;
+  sums[N + n] = s2;
+  if (dbeta) dbeta[n] = s1;
+  if (dgamma) dgamma[n] = s2;
+}
+
+__global__ void bn_bwd_apply_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y,
+                                    int64_t ldy, int64_t B, int64_t N, const float* __restrict__ mean,
+                                    const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                    const float* __restrict__ beta, int relu, const uint8_t* __restrict__ mask,
+                                    float drop_scale, int training, const float* __restrict__ sums,
+                                    float* __restrict__ dy, int64_t lddy) {
+  const int64_t total = B * N;
+  const float invB = 1.f / (float)B;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+       e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = e / N, n = e % N;
+    float d = da[b * ldda + n];
+    if (mask) d = mask[e] ? d * drop_scale : 0.f;
+    if (!mean) {
+      if (relu && !(y[b * ldy + n] > 0.f)) d = 0.f;
+      dy[b * lddy + n] = d;
+      continue;
+    }
+    const float g = gamma ? gamma[n] : 1.f;
+    const float xhat = (y[b * ldy + n] - mean[n]) * rstd[n];
+    const float u = xhat * g + (beta ? beta[n] : 0.f);
+    if (relu && !(u > 0.f)) d = 0.f;
+    float r;
+    if (training)
+      r = rstd[n] * g * (d - sums[n] * invB - xhat * (sums[N + n] * invB));
+    else
+      r = rstd[n] * g * d;
+    dy[b * lddy + n] = r;
+  }
+}
+
+}  // namespace scvi
+
+extern "C" {
+
+int scvi_bn_partials(const float* y, int64_t ldy, int64_t B, int64_t N, float* bn_partials, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(y && bn_partials && B > 0 && N > 0 && ldy >= N, "scvi_bn_partials: bad argument");
+  dim3 grid((unsigned)cdiv(B, SCVI_BN_TILE), (unsigned)cdiv(N, 64));
+  bn_partials_kernel<<<grid, 64, 0, (cudaStream_t)stream>>>(y, ldy, B, N, bn_partials);
+  SCVI_LAUNCH_CHECK("scvi_bn_partials");
+  return SCVI_OK;
+}
+
+int scvi_bn_finalize(const float* bn_partials, int64_t B, int64_t N, int training, float eps, float momentum,
+                     float* running_mean, float* running_var, float* mean, float* rstd, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(mean && rstd && B > 0 && N > 0, "scvi_bn_finalize: bad argument");
+  SCVI_REQUIRE(training ? (bn_partials != nullptr) : (running_mean && running_var),
+               "scvi_bn_finalize: missing partials (training) or running buffers (eval)");
+  bn_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(
+      bn_partials, B, N, training, eps, momentum, running_mean, running_var, mean, rstd);
+  SCVI_LAUNCH_CHECK("scvi_bn_finalize");
+  return SCVI_OK;
+}
+
+int scvi_bn_act_drop_fwd(const float* y, int64_t ldy, int64_t B, int64_t N, const float* mean, const float* rstd,
+                         const float* gamma, const float* beta, int relu, const uint8_t* drop_mask,
+                         float drop_scale, float* a, int64_t lda, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(y && a && B >= 0 && N > 0 && ldy >= N && lda >= N, "scvi_bn_act_drop_fwd: bad argument");
+  SCVI_REQUIRE((mean == nullptr) == (rstd == nullptr), "scvi_bn_act_drop_fwd: mean and rstd go together");
+  if (B == 0) return SCVI_OK;
+  const int64_t total = B * N;
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(total, 256), 148 * 8);
+  bn_act_drop_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(y, ldy, B, N, mean, rstd, gamma, beta, relu,
+                                                                   drop_mask, drop_scale, a, lda);
+  SCVI_LAUNCH_CHECK("scvi_bn_act_drop_fwd");
+  return SCVI_OK;
+}
+
+int64_t scvi_bn_bwd_ws_bytes(int64_t B, int64_t N) {
+  return 4 * (scvi::cdiv(B, SCVI_BN_TILE) * 2 * N + 2 * N) + 256;
+}
+
+int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t ldy, int64_t B, int64_t N,
+                         const float* mean, const float* rstd, const float* gamma, const float* beta, int relu,
+                         const uint8_t* drop_mask, float drop_scale, int training, float* dy, int64_t lddy,
+                         float* dgamma, float* dbeta, void* ws, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(da && y && dy && ws && B > 0 && N > 0, "scvi_bn_act_drop_bwd: bad argument");
+  SCVI_REQUIRE((mean == nullptr) == (rstd == nullptr), "scvi_bn_act_drop_bwd: mean and rstd go together");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t T = cdiv(B, SCVI_BN_TILE);
+  float* part = (float*)ws;
+  float* sums = part + T * 2 * N;
+  if (mean) {
+    dim3 grid((unsigned)T, (unsigned)cdiv(N, 64));
+    bn_bwd_reduce_kernel<<<grid, 64, 0, st>>>(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask,
+                                              drop_scale, part);
+    SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(reduce)");
+    bn_bwd_sums_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, T, N, sums, dgamma, dbeta);
+    SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(sums)");
+  }
+  const int64_t total = B * N;
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(total, 256), 148 * 8);
+  bn_bwd_apply_kernel<<<blocks, 256, 0, st>>>(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask,
+                                              drop_scale, training, sums, dy, lddy);
+  SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(apply)");
+  return SCVI_OK;
+}
+}

@@ -1,0 +1,193 @@
+// Latent heads of Encoder.forward + reparameterisation + Normal KL, forward and backward.
+// Replaces (reference src/scvi/nn/_base_components.py:311-317)
+//   q_m = mean_encoder(q); q_v = exp(var_encoder(q)) + var_eps; z = Normal(q_m, sqrt(q_v)).rsample()
+// and kl_divergence(qz, Normal(0,1)).sum(-1) (src/scvi/module/_vae.py:563-565), where torch's
+// kl_normal_normal gives 0.5 * (s^2 + q_m^2 - 1 - log(s^2)) with s = sqrt(q_v).
+#include "common.cuh"
+
+namespace scvi {
+
+constexpr int LAT_WARPS = 4;
+
+// one warp per row; weights staged in smem as Wt[k][2L] (k-major => lane j reads Wt[k][j])
+__global__ void __launch_bounds__(LAT_WARPS * 32)
+    latent_fwd_kernel(const float* __restrict__ a, int64_t lda, int64_t B, int H, int L,
+                      const float* __restrict__ Wm, const float* __restrict__ bm, const float* __restrict__ Wv,
+                      const float* __restrict__ bv, const float* __restrict__ noise, float var_eps,
+                      float* __restrict__ q_m, float* __restrict__ q_v, float* __restrict__ z,
+                      float* __restrict__ kl) {
+  extern __shared__ float sm[];
+  const int L2 = 2 * L;
+  float* Wt = sm;                          // [H][L2]
+  float* arow = Wt + (size_t)H * L2;       // [LAT_WARPS][H]
+  float* res = arow + LAT_WARPS * H;       // [LAT_WARPS][L2]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int e = tid; e < H * L2; e += blockDim.x) {
+    const int k = e / L2, j = e % L2;
+    Wt[e] = (j < L) ? Wm[j * H + k] : Wv[(j - L) * H + k];
+  }
+  __syncthreads();
+  for (int64_t r = (int64_t)blockIdx.x * LAT_WARPS + warp; r < B; r += (int64_t)gridDim.x * LAT_WARPS) {
+    for (int k = lane; k < H; k += 32) arow[warp * H + k] = a[r * lda + k];
+    __syncwarp();
+    for (int j = lane; j < L2; j += 32) {
+      float s = (j < L) ? bm[j] : bv[j - L];
+      const float* ar = arow + warp * H;
+      for (int k = 0; k < H; ++k) s = fmaf(ar[k], Wt[k * L2 + j], s);
+      res[warp * L2 + j] = s;
+    }
+    __syncwarp();
+    float klp = 0.f;
+    for (int l = lane; l < L; l += 32) {
+      const float m = res[warp * L2 + l];
+      const float v = expf(res[warp * L2 + L + l]) + var_eps;
+      const float s = sqrtf(v);
+      const float s2 = s * s;
+      q_m[r * L + l] = m;
+      q_v[r * L + l] = v;
+      z[r * L + l] = fmaf(s, noise[r * L + l], m);
+      klp += 0.5f * (s2 + m * m - 1.f - logf(s2));
+    }
+    klp = warp_sum(klp);
+    if (lane == 0) kl[r] = klp;
+    __syncwarp();
+  }
+}
+
+constexpr int LATB_ROWS = 64;
+constexpr int LATB_THREADS = 128;
+
+__global__ void __launch_bounds__(LATB_THREADS)
+    latent_bwd_kernel(const float* __restrict__ a, int64_t lda, int64_t B, int H, int L,
+                      const float* __restrict__ Wm, const float* __restrict__ Wv, const float* __restrict__ noise,
+                      float var_eps, const float* __restrict__ q_m, const float* __restrict__ q_v,
+                      const float* __restrict__ g_qm, const float* __restrict__ g_qv, const float* __restrict__ g_z,
+                      const float* __restrict__ g_kl, float* __restrict__ da, int64_t ldda,
+                      float* __restrict__ partW /*[ctas][2L][H]*/, float* __restrict__ partb /*[ctas][2L]*/) {
+  extern __shared__ float sm[];
+  const int L2 = 2 * L;
+  float* Wn = sm;                            // [L2][H]   rows 0..L-1 = Wm, L..2L-1 = Wv
+  float* as = Wn + (size_t)L2 * H;           // [LATB_ROWS][H]
+  float* dq = as + (size_t)LATB_ROWS * H;    // [LATB_ROWS][L2]  (dq_m | dt)
+  const int tid = threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.x * LATB_ROWS;
+  const int cnt = (int)min((int64_t)LATB_ROWS, B - r0);
+  for (int e = tid; e < L2 * H; e += blockDim.x) Wn[e] = (e < L * H) ? Wm[e] : Wv[e - L * H];
+  for (int e = tid; e < LATB_ROWS * H; e += blockDim.x) {
+    const int r = e / H, k = e % H;
+    as[e] = (r < cnt) ? a[(r0 + r) * lda + k] : 0.f;
+  }
+  for (int e = tid; e < LATB_ROWS * L; e += blockDim.x) {
+    const int r = e / L, l = e % L;
+    float dm = 0.f, dt = 0.f;
+    if (r < cnt) {
+      const int64_t i = (r0 + r) * L + l;
+      const float m = q_m[i], v = q_v[i];
+      const float gk = g_kl ? g_kl[r0 + r] : 0.f;
+      const float gz = g_z ? g_z[i] : 0.f;
+      dm = (g_qm ? g_qm[i] : 0.f) + gz + gk * m;
+      const float s = sqrtf(v);
+      float dv = (g_qv ? g_qv[i] : 0.f) + gz * noise[i] / (2.f * s) + gk * 0.5f * (1.f - 1.f / v);
+      dt = dv * (v - var_eps);  // d exp(t) = exp(t) = q_v - var_eps
+    }
+    dq[r * L2 + l] = dm;
+    dq[r * L2 + L + l] = dt;
+  }
+  __syncthreads();
+  for (int k = tid; k < H; k += blockDim.x) {
+    // da[r][k] = sum_j dq[r][j] * Wn[j][k]
+    for (int r = 0; r < cnt; ++r) {
+      float s = 0.f;
+      for (int j = 0; j < L2; ++j) s = fmaf(dq[r * L2 + j], Wn[j * H + k], s);
+      da[(r0 + r) * ldda + k] = s;
+    }
+    // dW[j][k] partial = sum_r dq[r][j] * a[r][k]
+    for (int j = 0; j < L2; ++j) {
+      float s = 0.f;
+      for (int r = 0; r < cnt; ++r) s = fmaf(dq[r * L2 + j], as[r * H + k], s);
+      partW[((int64_t)blockIdx.x * L2 + j) * H + k] = s;
+    }
+  }
+  for (int j = tid; j < L2; j += blockDim.x) {
+    float s = 0.f;
+    for (int r = 0; r < cnt; ++r) s += dq[r * L2 + j];
+    partb[(int64_t)blockIdx.x * L2 + j] = s;
+  }
+}
+
+__global__ void latent_bwd_reduce_kernel(const float* __restrict__ partW, const float* __restrict__ partb,
+                                         int64_t ctas, int H, int L, float* __restrict__ dWm,
+                                         float* __restrict__ dbm, float* __restrict__ dWv, float* __restrict__ dbv) {
+  const int L2 = 2 * L;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < (int64_t)L2 * H) {
+    float s = 0.f;
+    for (int64_t c = 0; c < ctas; ++c) s += partW[c * L2 * H + e];
+    if (e < (int64_t)L * H) {
+      if (dWm) dWm[e] = s;
+    } else if (dWv) {
+      dWv[e - (int64_t)L * H] = s;
+    }
+  }
+  if (e < L2) {
+    float s = 0.f;
+    for (int64_t c = 0; c < ctas; ++c) s += partb[c * L2 + e];
+    if (e < L) {
+      if (dbm) dbm[e] = s;
+    } else if (dbv) {
+      dbv[e - L] = s;
+    }
+  }
+}
+
+}  // namespace scvi
+
+extern "C" {
+
+int scvi_latent_fwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L, const float* Wm, const float* bm,
+                    const float* Wv, const float* bv, const float* noise, float var_eps, float* q_m, float* q_v,
+                    float* z, float* kl, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(a && Wm && bm && Wv && bv && noise && q_m && q_v && z && kl, "scvi_latent_fwd: NULL pointer");
+  SCVI_REQUIRE(B >= 0 && H > 0 && L > 0 && L <= 32 && lda >= H, "scvi_latent_fwd: bad shape (L <= 32)");
+  if (B == 0) return SCVI_OK;
+  const size_t smem = sizeof(float) * ((size_t)H * 2 * L + LAT_WARPS * H + LAT_WARPS * 2 * L);
+  SCVI_REQUIRE(smem <= 48 * 1024, "scvi_latent_fwd: H*L too large for shared memory");
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(B, LAT_WARPS), 148 * 4);
+  latent_fwd_kernel<<<blocks, LAT_WARPS * 32, smem, (cudaStream_t)stream>>>(a, lda, B, (int)H, (int)L, Wm, bm, Wv, bv, noise, var_eps, q_m, q_v, z, kl);
+  SCVI_LAUNCH_CHECK("scvi_latent_fwd");
+  return SCVI_OK;
+}
+
+int64_t scvi_latent_bwd_ws_bytes(int64_t B, int64_t H, int64_t L) {
+  const int64_t ctas = scvi::cdiv(B, scvi::LATB_ROWS);
+  return 4 * (ctas * 2 * L * H + ctas * 2 * L) + 256;
+}
+
+int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L, const float* Wm, const float* Wv,
+                    const float* noise, float var_eps, const float* q_m, const float* q_v, const float* g_qm,
+                    const float* g_qv, const float* g_z, const float* g_kl, float* da, int64_t ldda, float* dWm,
+                    float* dbm, float* dWv, float* dbv, void* ws, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(a && Wm && Wv && noise && q_m && q_v && da && ws, "scvi_latent_bwd: NULL pointer");
+  SCVI_REQUIRE(B > 0 && H > 0 && L > 0 && L <= 32 && lda >= H && ldda >= H, "scvi_latent_bwd: bad shape");
+  const size_t smem = sizeof(float) * ((size_t)2 * L * H + (size_t)LATB_ROWS * H + (size_t)LATB_ROWS * 2 * L);
+  static bool attr_set = false;
+  if (smem > 48 * 1024) {
+    SCVI_REQUIRE(smem <= 200 * 1024, "scvi_latent_bwd: H*L too large for shared memory");
+    if (!attr_set) {
+      cudaFuncSetAttribute(latent_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      attr_set = true;
+    }
+  }
+  const int64_t ctas = cdiv(B, LATB_ROWS);
+  float* partW = (float*)ws;
+  float* partb = partW + ctas * 2 * L * H;
+  cudaStream_t st = (cudaStream_t)stream;
+  latent_bwd_kernel<<<(unsigned)ctas, LATB_THREADS, smem, st>>>(a, lda, B, (int)H, (int)L, Wm, Wv, noise, var_eps, q_m, q_v, g_qm, g_qv, g_z, g_kl, da, ldda, partW, partb);
+  SCVI_LAUNCH_CHECK("scvi_latent_bwd");
+  latent_bwd_reduce_kernel<<<(unsigned)cdiv(2 * L * H, 256), 256, 0, st>>>(partW, partb, ctas, (int)H, (int)L, dWm, dbm, dWv, dbv);
+  SCVI_LAUNCH_CHECK("scvi_latent_bwd(reduce)");
+  return SCVI_OK;
+}
+}

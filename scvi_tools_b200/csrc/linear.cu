@@ -1,0 +1,454 @@
+// FCLayers linear layer: y = f(x) W[:, :K]^T + sum_c W[:, cov_col_c] + b, fp32 FFMA tiles.
+// Replaces `torch.cat((x, one_hot(cat)))` + nn.Linear of FCLayers
+// (reference src/scvi/nn/_base_components.py:148-188,198-215) and the encoder pre-ops
+// log1p / library (src/scvi/module/_vae.py:370-374).  The one-hot concat is a weight-column
+// gather in forward and a segmented column sum in backward.
+#include "common.cuh"
+
+namespace scvi {
+
+constexpr int LT = 64;        // output tile edge (rows and cols)
+constexpr int LK = 32;        // reduction chunk
+constexpr int LPAD = LK + 4;  // smem row stride (floats): conflict-free float4 reads for strided rows
+constexpr int LTHREADS = 256;
+
+// ---------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------
+template <bool VEC>
+__global__ void __launch_bounds__(LTHREADS)
+    linear_fwd_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+                      int64_t K, int64_t N, const float* __restrict__ W, int64_t ldw,
+                      const float* __restrict__ bias, const int32_t* __restrict__ cov_cols, int n_cov,
+                      int flags, float* __restrict__ y, int64_t ldy, float* __restrict__ library,
+                      float* __restrict__ bn_partials) {
+  __shared__ __align__(16) float smem[2 * LT * LPAD + LT];
+  float* xs = smem;              // [LT][LPAD]
+  float* ws = smem + LT * LPAD;  // [LT][LPAD]
+  __shared__ int64_t rows[LT];
+
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t r0 = (int64_t)blockIdx.x * LT;
+  const int64_t n0 = (int64_t)blockIdx.y * LT;
+  const bool log1p_in = flags & SCVI_LIN_LOG1P;
+  const bool want_lib = (flags & SCVI_LIN_LIBRARY) && blockIdx.y == 0 && library != nullptr;
+
+  if (tid < LT) {
+    const int64_t r = r0 + tid;
+    rows[tid] = (r < B) ? (row_idx ? row_idx[r] : r) : -1;
+  }
+  __syncthreads();
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  float lib_part[2] = {0.f, 0.f};
+
+  for (int64_t k0 = 0; k0 < K; k0 += LK) {
+    if (VEC) {
+      // 64 rows x 8 float4 per operand; thread -> (row = tid/8 + 32*it, kq = tid%8)
+      const int kq = tid & 7;
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        const int rr = (tid >> 3) + 32 * it;
+        const int64_t k = k0 + 4 * kq;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t src = rows[rr];
+        if (src >= 0 && k < K) v = ld_stream4(x + src * ldx + k);
+        lib_part[it] += (v.x + v.y) + (v.z + v.w);
+        if (log1p_in) v = make_float4(log1pf(v.x), log1pf(v.y), log1pf(v.z), log1pf(v.w));
+        *reinterpret_cast<float4*>(&xs[rr * LPAD + 4 * kq]) = v;
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t n = n0 + rr;
+        if (n < N && k < K) w = *reinterpret_cast<const float4*>(W + n * ldw + k);
+        *reinterpret_cast<float4*>(&ws[rr * LPAD + 4 * kq]) = w;
+      }
+    } else {
+      // scalar path: thread -> (row = tid/32 + 8*it, k = tid%32)
+      const int kk = tid & 31;
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rr = (tid >> 5) + 8 * it;
+        const int64_t k = k0 + kk;
+        float v = 0.f;
+        const int64_t src = rows[rr];
+        if (src >= 0 && k < K) v = x[src * ldx + k];
+        const float raw = v;
+        if (log1p_in) v = log1pf(v);
+        xs[rr * LPAD + kk] = v;
+        const int64_t n = n0 + rr;
+        ws[rr * LPAD + kk] = (n < N && k < K) ? W[n * ldw + k] : 0.f;
+        if (want_lib) {
+          // warp-level row sum of this chunk (all 32 lanes of the warp share row rr)
+          float s = warp_sum(raw);
+          if (kk == 0) smem[2 * LT * LPAD + rr] = (k0 == 0 ? 0.f : smem[2 * LT * LPAD + rr]) + s;
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < LK; k += 4) {
+      float4 a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(&xs[(ty + 16 * i) * LPAD + k]);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4*>(&ws[(tx + 16 * j) * LPAD + k]);
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+          acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+          acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+          acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+        }
+    }
+    __syncthreads();
+  }
+
+  // library = log(sum_g x)   (reference _vae.py:372)
+  if (want_lib) {
+    if (VEC) {
+#pragma unroll
+      for (int it = 0; it < 2; ++it) {
+        float s = lib_part[it];
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        s += __shfl_xor_sync(0xffffffffu, s, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 4);
+        const int rr = (tid >> 3) + 32 * it;
+        if ((tid & 7) == 0 && r0 + rr < B) library[r0 + rr] = logf(s);
+      }
+    } else {
+      if (tid < LT && r0 + tid < B) library[r0 + tid] = logf(smem[2 * LT * LPAD + tid]);
+    }
+  }
+
+  // epilogue: bias + covariate columns (the one-hot GEMM as a column gather)
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t r = r0 + ty + 16 * i;
+    if (r >= B) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t n = n0 + tx + 16 * j;
+      if (n >= N) continue;
+      float v = acc[i][j];
+      for (int c = 0; c < n_cov; ++c) v += W[n * ldw + cov_cols[r * n_cov + c]];
+      if (bias) v += bias[n];
+      acc[i][j] = v;
+      y[r * ldy + n] = v;
+    }
+  }
+
+  // per-tile BatchNorm statistics (mean, M2) over the valid rows of this tile
+  if (bn_partials != nullptr) {
+    float* ts = smem;  // [LT][LT+1] staging, reuses xs/ws (>= 64*65 floats)
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ts[(ty + 16 * i) * (LT + 1) + tx + 16 * j] = acc[i][j];
+    __syncthreads();
+    if (tid < LT) {
+      const int64_t n = n0 + tid;
+      const int cnt = (int)min((int64_t)LT, B - r0);
+      if (n < N) {
+        float s = 0.f;
+        for (int r = 0; r < cnt; ++r) s += ts[r * (LT + 1) + tid];
+        const float mean = s / (float)cnt;
+        float m2 = 0.f;
+        for (int r = 0; r < cnt; ++r) {
+          const float d = ts[r * (LT + 1) + tid] - mean;
+          m2 = fmaf(d, d, m2);
+        }
+        bn_partials[((int64_t)blockIdx.x * 2 + 0) * N + n] = mean;
+        bn_partials[((int64_t)blockIdx.x * 2 + 1) * N + n] = m2;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// backward: dW[n, k] = sum_b dy[b, n] * f(x[b, k]), split over B, partial slabs
+// ---------------------------------------------------------------------------------------
+constexpr int BB = 32;  // rows per reduction chunk
+
+template <bool VEC>
+__global__ void __launch_bounds__(LTHREADS)
+    linear_dw_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+                     int64_t K, int64_t N, const float* __restrict__ dy, int64_t lddy, int log1p_in,
+                     int64_t rows_per_split, float* __restrict__ out, int64_t ldo, int64_t slab_stride) {
+  __shared__ __align__(16) float dys[BB][LT];  // [b][n]
+  __shared__ __align__(16) float xs[BB][LT];   // [b][k]
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t k0 = (int64_t)blockIdx.x * LT;
+  const int64_t n0 = (int64_t)blockIdx.y * LT;
+  const int64_t b_begin = (int64_t)blockIdx.z * rows_per_split;
+  const int64_t b_end = min(B, b_begin + rows_per_split);
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int64_t b0 = b_begin; b0 < b_end; b0 += BB) {
+    // 32 rows x 64 cols per operand = 512 float4 -> 2 per thread
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int e = tid + LTHREADS * it;  // 0..511
+      const int rr = e >> 4;              // 0..31
+      const int c4 = (e & 15) * 4;
+      const int64_t b = b0 + rr;
+      const bool rv = b < b_end;
+      float4 d = make_float4(0.f, 0.f, 0.f, 0.f), v = d;
+      if (rv) {
+        const int64_t src = row_idx ? row_idx[b] : b;
+        if (VEC) {
+          if (n0 + c4 < N) d = *reinterpret_cast<const float4*>(dy + b * lddy + n0 + c4);
+          if (k0 + c4 < K) v = ld_stream4(x + src * ldx + k0 + c4);
+        } else {
+          float* dp = &d.x;
+          float* vp = &v.x;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (n0 + c4 + q < N) dp[q] = dy[b * lddy + n0 + c4 + q];
+            if (k0 + c4 + q < K) vp[q] = x[src * ldx + k0 + c4 + q];
+          }
+        }
+        if (log1p_in) v = make_float4(log1pf(v.x), log1pf(v.y), log1pf(v.z), log1pf(v.w));
+      }
+      *reinterpret_cast<float4*>(&dys[rr][c4]) = d;
+      *reinterpret_cast<float4*>(&xs[rr][c4]) = v;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int r = 0; r < BB; ++r) {
+      const float4 a = *reinterpret_cast<const float4*>(&dys[r][4 * ty]);
+      const float4 b = *reinterpret_cast<const float4*>(&xs[r][4 * tx]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  float* o = out + (int64_t)blockIdx.z * slab_stride;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t n = n0 + 4 * ty + i;
+    if (n >= N) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t k = k0 + 4 * tx + j;
+      if (k < K) o[n * ldo + k] = acc[i][j];
+    }
+  }
+}
+
+// covariate columns + bias: per row-chunk partial of
+//   extra[c, n] = sum_{b : some cov_cols[b,.] == K + c} dy[b, n],   extra[n_extra, n] = sum_b dy[b, n]
+// one thread per output column n (no conflicts), rows in chunks of COV_ROWS.
+constexpr int COV_ROWS = 256;
+__global__ void linear_dcov_kernel(const float* __restrict__ dy, int64_t lddy, int64_t B, int64_t K, int64_t N,
+                                   const int32_t* __restrict__ cov_cols, int n_cov, int n_extra,
+                                   float* __restrict__ part /*[chunks][n_extra+1][N]*/) {
+  extern __shared__ float accs[];  // [(n_extra+1)][blockDim.x]
+  const int n_local = threadIdx.x;
+  const int64_t n = (int64_t)blockIdx.y * blockDim.x + n_local;
+  for (int c = 0; c <= n_extra; ++c) accs[c * blockDim.x + n_local] = 0.f;
+  const int64_t b0 = (int64_t)blockIdx.x * COV_ROWS;
+  const int64_t b1 = min(B, b0 + COV_ROWS);
+  if (n < N) {
+    for (int64_t b = b0; b < b1; ++b) {
+      const float d = dy[b * lddy + n];
+      accs[n_extra * blockDim.x + n_local] += d;
+      for (int c = 0; c < n_cov; ++c) {
+        const int col = cov_cols[b * n_cov + c] - (int)K;
+        accs[col * blockDim.x + n_local] += d;
+      }
+    }
+    for (int c = 0; c <= n_extra; ++c)
+      part[((int64_t)blockIdx.x * (n_extra + 1) + c) * N + n] = accs[c * blockDim.x + n_local];
+  }
+}
+
+// dW[n, k] = sum_s slab[s][n][k]  (fixed order); extra columns / bias from the dcov partials
+__global__ void linear_bwd_reduce_kernel(const float* __restrict__ slabs, int64_t S, int64_t slab_stride,
+                                         int64_t N, int64_t K, int64_t ldw, float* __restrict__ dW) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= N * K) return;
+  const int64_t n = e / K, k = e % K;
+  float s = 0.f;
+  for (int64_t t = 0; t < S; ++t) s += slabs[t * slab_stride + n * K + k];
+  dW[n * ldw + k] = s;
+}
+__global__ void linear_dcov_reduce_kernel(const float* __restrict__ part, int64_t chunks, int n_extra, int64_t N,
+                                          int64_t K, int64_t ldw, float* __restrict__ dW, float* __restrict__ db) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)(n_extra + 1) * N) return;
+  const int c = (int)(e / N);
+  const int64_t n = e % N;
+  float s = 0.f;
+  for (int64_t t = 0; t < chunks; ++t) s += part[(t * (n_extra + 1) + c) * N + n];
+  if (c < n_extra) {
+    if (dW) dW[n * ldw + K + c] = s;
+  } else if (db) {
+    db[n] = s;
+  }
+}
+
+// dx[b, k] = sum_n dy[b, n] * W[n, k]   (k < K)
+__global__ void __launch_bounds__(LTHREADS)
+    linear_dx_kernel(const float* __restrict__ dy, int64_t lddy, int64_t B, int64_t K, int64_t N,
+                     const float* __restrict__ W, int64_t ldw, float* __restrict__ dx, int64_t lddx) {
+  __shared__ float dys[LT][LK + 1];  // [b][n]
+  __shared__ float wsm[LK][LT + 1];  // [n][k]
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t r0 = (int64_t)blockIdx.x * LT;
+  const int64_t k0 = (int64_t)blockIdx.y * LT;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (int64_t nn0 = 0; nn0 < N; nn0 += LK) {
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int e = tid + LTHREADS * it;  // 0..2047
+      {  // dy tile: [64 b][32 n]
+        const int rr = e >> 5, nn = e & 31;
+        const int64_t b = r0 + rr, n = nn0 + nn;
+        dys[rr][nn] = (b < B && n < N) ? dy[b * lddy + n] : 0.f;
+      }
+      {  // W tile: [32 n][64 k]
+        const int nn = e >> 6, kk = e & 63;
+        const int64_t n = nn0 + nn, k = k0 + kk;
+        wsm[nn][kk] = (n < N && k < K) ? W[n * ldw + k] : 0.f;
+      }
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int nn = 0; nn < LK; ++nn) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = dys[ty + 16 * i][nn];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = wsm[nn][tx + 16 * j];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t b = r0 + ty + 16 * i;
+    if (b >= B) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t k = k0 + tx + 16 * j;
+      if (k < K) dx[b * lddx + k] = acc[i][j];
+    }
+  }
+}
+
+static int64_t dw_splits(int64_t B, int64_t K, int64_t N) {
+  const int64_t tiles = cdiv(K, LT) * cdiv(N, LT);
+  int64_t s = cdiv(4 * 148, tiles);                  // aim for ~4 CTAs per SM
+  s = std::min<int64_t>(s, cdiv(B, 4 * BB));         // at least 128 rows per split
+  return std::max<int64_t>(1, std::min<int64_t>(s, 64));
+}
+
+}  // namespace scvi
+
+extern "C" {
+
+int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+                    const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols, int n_cov, int flags,
+                    float* y, int64_t ldy, float* library, float* bn_partials, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(x && W && y, "scvi_linear_fwd: NULL pointer");
+  SCVI_REQUIRE(B >= 0 && K > 0 && N > 0 && ldx >= K && ldw >= K && ldy >= N, "scvi_linear_fwd: bad shape");
+  SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_fwd: n_cov > 0 but cov_cols is NULL");
+  SCVI_REQUIRE(!(flags & SCVI_LIN_LIBRARY) || library, "scvi_linear_fwd: SCVI_LIN_LIBRARY needs `library`");
+  if (B == 0) return SCVI_OK;
+  const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && (ldw % 4 == 0) && ((uintptr_t)x % 16 == 0) &&
+                   ((uintptr_t)W % 16 == 0);
+  dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(N, LT));
+  if (vec)
+    linear_fwd_kernel<true><<<grid, LTHREADS, 0, (cudaStream_t)stream>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials);
+  else
+    linear_fwd_kernel<false><<<grid, LTHREADS, 0, (cudaStream_t)stream>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials);
+  SCVI_LAUNCH_CHECK("scvi_linear_fwd");
+  return SCVI_OK;
+}
+
+int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols) {
+  using namespace scvi;
+  const int64_t S = dw_splits(B, K, N);
+  const int64_t n_extra = n_w_cols - K;
+  return 4 * (S * N * K + cdiv(B, COV_ROWS) * (n_extra + 1) * N) + 256;
+}
+
+int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+                    const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov, int flags,
+                    const float* dy, int64_t lddy, float* dW, float* db, float* dx, int64_t lddx, void* ws,
+                    void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(x && dy && ws, "scvi_linear_bwd: NULL pointer");
+  SCVI_REQUIRE(B > 0 && K > 0 && N > 0 && ldx >= K && lddy >= N && n_w_cols >= K && ldw >= n_w_cols,
+               "scvi_linear_bwd: bad shape");
+  SCVI_REQUIRE(!(dx && (flags & SCVI_LIN_LOG1P)), "scvi_linear_bwd: dx is not available with SCVI_LIN_LOG1P");
+  SCVI_REQUIRE(!dx || (W && lddx >= K), "scvi_linear_bwd: dx needs W");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int n_extra = (int)(n_w_cols - K);
+  float* slabs = (float*)ws;
+  const int64_t S = dw_splits(B, K, N);
+  if (dW) {
+    const bool vec = (K % 4 == 0) && (N % 4 == 0) && (ldx % 4 == 0) && (lddy % 4 == 0) &&
+                     ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0);
+    const int64_t rps = cdiv(cdiv(B, S), BB) * BB;
+    dim3 grid((unsigned)cdiv(K, LT), (unsigned)cdiv(N, LT), (unsigned)S);
+    float* out = (S == 1) ? dW : slabs;
+    const int64_t ldo = (S == 1) ? ldw : K;
+    if (vec)
+      linear_dw_kernel<true><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * K);
+    else
+      linear_dw_kernel<false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * K);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dW)");
+    if (S > 1) {
+      linear_bwd_reduce_kernel<<<(unsigned)cdiv(N * K, 256), 256, 0, st>>>(slabs, S, N * K, N, K, ldw, dW);
+      SCVI_LAUNCH_CHECK("scvi_linear_bwd(reduce)");
+    }
+  }
+  if ((dW && n_extra > 0) || db) {
+    SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_bwd: cov_cols is NULL");
+    float* part = slabs + S * N * K;
+    const int64_t chunks = cdiv(B, COV_ROWS);
+    const int bt = 128;
+    const size_t sm = (size_t)(n_extra + 1) * bt * sizeof(float);
+    SCVI_REQUIRE(sm <= 48 * 1024, "scvi_linear_bwd: too many covariate columns (%d)", n_extra);
+    dim3 grid((unsigned)chunks, (unsigned)cdiv(N, bt));
+    linear_dcov_kernel<<<grid, bt, sm, st>>>(dy, lddy, B, K, N, cov_cols, n_cov, n_extra, part);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dcov)");
+    linear_dcov_reduce_kernel<<<(unsigned)cdiv((int64_t)(n_extra + 1) * N, 256), 256, 0, st>>>(
+        part, chunks, n_extra, N, K, ldw, dW, db);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dcov reduce)");
+  }
+  if (dx) {
+    dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(K, LT));
+    linear_dx_kernel<<<grid, LTHREADS, 0, st>>>(dy, lddy, B, K, N, W, ldw, dx, lddx);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dx)");
+  }
+  return SCVI_OK;
+}
+}
