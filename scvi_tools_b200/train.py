@@ -1,0 +1,370 @@
+"""Fused SCVI training plan: the whole minibatch step as one fixed sequence of C-ABI kernels.
+
+Stands in for `TrainingPlan.training_step` + Lightning's `loss.backward()` + `Adam.step()`
+(reference src/scvi/train/_trainingplans.py:427-454,475-532): KL warm-up weight `epoch/400`
+(:31-72), `torch.optim.Adam(lr=1e-3, eps=0.01, weight_decay=1e-6)` over the parameters that
+receive gradient, mean-reduced loss.  No autograd graph is built: forward and backward are
+the explicit kernel sequence of DESIGN.md section 3, reading minibatch rows straight from the
+HBM-resident count matrix (`row_idx`), writing gradients into one flat arena that a single
+multi-tensor Adam launch consumes.  The sequence is captured once in a CUDA graph.
+
+Supported configuration = the reference default SCVI module: n_layers=1, one-hot batch
+covariate, observed library, dispersion="gene", gene_likelihood in {"zinb","nb"},
+BatchNorm in encoder and decoder, no LayerNorm.  Anything else: use the autograd path
+(`VAE.forward` + torch optimizer), which runs on the same kernels.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import call, query
+from .data import DeviceResidentCounts, epoch_indices
+from .ops import BN_EPS, BN_MOMENTUM
+
+
+def compute_kl_weight(epoch, step, n_epochs_kl_warmup=400, n_steps_kl_warmup=None, max_kl_weight=1.0,
+                      min_kl_weight=0.0):
+    """KL warm-up schedule (reference src/scvi/train/_trainingplans.py:31-72)."""
+    if min_kl_weight > max_kl_weight:
+        raise ValueError(f"min_kl_weight={min_kl_weight} is larger than max_kl_weight={max_kl_weight}.")
+    slope = max_kl_weight - min_kl_weight
+    if n_epochs_kl_warmup:
+        if epoch < n_epochs_kl_warmup:
+            return slope * (epoch / n_epochs_kl_warmup) + min_kl_weight
+    elif n_steps_kl_warmup:
+        if step < n_steps_kl_warmup:
+            return slope * (step / n_steps_kl_warmup) + min_kl_weight
+    return max_kl_weight
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+ENC = "z_encoder.encoder.fc_layers.Layer 0."
+DEC = "decoder.px_decoder.fc_layers.Layer 0."
+# arena order: decoder-head gradients first (they are ready first in backward and are 2/3 of the
+# bytes), so the data-parallel allreduce of that chunk overlaps the rest of backward
+ARENA_ORDER = [
+    "px_r",
+    "decoder.px_scale_decoder.0.weight", "decoder.px_scale_decoder.0.bias",
+    "decoder.px_dropout_decoder.weight", "decoder.px_dropout_decoder.bias",
+    DEC + "0.weight", DEC + "0.bias", DEC + "1.weight", DEC + "1.bias",
+    "z_encoder.mean_encoder.weight", "z_encoder.mean_encoder.bias",
+    "z_encoder.var_encoder.weight", "z_encoder.var_encoder.bias",
+    ENC + "0.weight", ENC + "0.bias", ENC + "1.weight", ENC + "1.bias",
+]
+N_HEAD_TENSORS = 5
+
+
+class FusedTrainingPlan:
+    """One object = module + optimizer state + preallocated step buffers for a fixed batch size."""
+
+    def __init__(self, module, data: DeviceResidentCounts, batch_size: int = 128, lr: float = 1e-3,
+                 eps: float = 0.01, weight_decay: float = 1e-6, betas=(0.9, 0.999),
+                 n_epochs_kl_warmup: int | None = 400, n_steps_kl_warmup: int | None = None,
+                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, seed: int = 0,
+                 use_cuda_graph: bool = True, process_group=None):
+        m = module
+        self._check_supported(m)
+        self.module, self.data = m, data
+        self.B = int(batch_size)
+        self.lr, self.eps, self.wd, self.betas = lr, eps, weight_decay, betas
+        self.n_epochs_kl_warmup, self.n_steps_kl_warmup = n_epochs_kl_warmup, n_steps_kl_warmup
+        self.max_kl_weight, self.min_kl_weight = max_kl_weight, min_kl_weight
+        self.seed = seed
+        self.use_cuda_graph = use_cuda_graph
+        self.pg = process_group
+        self.world = 1 if process_group is None else torch.distributed.get_world_size(process_group)
+        self.rank = 0 if process_group is None else torch.distributed.get_rank(process_group)
+        self.zinb = m.gene_likelihood == "zinb"
+        self.dev = data.X.device
+        self.G, self.H, self.L, self.nb = m.n_input, m.n_hidden, m.n_latent, m.n_batch
+        self.current_epoch = 0
+        self.global_step = 0
+        self.kernel_launches_per_step = 0
+        self._build_arena()
+        self._alloc_step_buffers()
+        self._graphs = None
+
+    @staticmethod
+    def _check_supported(m):
+        ok = (
+            m.n_layers == 1 and m.dispersion == "gene" and m.use_observed_lib_size and m.log_variational
+            and not m.encode_covariates and m.latent_distribution == "normal" and not m.use_size_factor_key
+            and m.n_hidden in (64, 128, 256) and m.n_latent <= 32
+            and m.z_encoder.encoder.use_batch_norm and m.decoder.px_decoder.use_batch_norm
+            and not m.z_encoder.encoder.use_layer_norm and not m.decoder.px_decoder.use_layer_norm
+            and len(m.decoder.px_decoder.n_cat_list) == 1 and m.decoder.px_decoder.n_cont == 0
+        )
+        if not ok:
+            raise NotImplementedError(
+                "FusedTrainingPlan covers the default SCVI module configuration; use VAE.forward + a torch "
+                "optimizer (same kernels through autograd) for other options"
+            )
+
+    # ------------------------------------------------------------------ arena
+    def _build_arena(self):
+        named = dict(self.module.named_parameters())
+        keys = [k for k in ARENA_ORDER if not (("px_dropout" in k) and not self.zinb)]
+        self.keys = keys
+        offs, off = {}, 0
+        for k in keys:
+            offs[k] = off
+            off += (named[k].numel() + 3) // 4 * 4  # keep every slice 16-byte aligned
+        self.n_arena = off
+        self.n_head = offs[keys[N_HEAD_TENSORS if self.zinb else 3]]
+        dev = self.dev
+        self.p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.g = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.m = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.v = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.P, self.Gd = {}, {}
+        for k in keys:
+            prm = named[k]
+            n = prm.numel()
+            view = self.p[offs[k] : offs[k] + n].view(prm.shape)
+            view.copy_(prm.data.to(dev))
+            prm.data = view  # the module's parameter now lives in the arena
+            self.P[k] = view
+            self.Gd[k] = self.g[offs[k] : offs[k] + n].view(prm.shape)
+        self.step_counter = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.klw = torch.zeros(1, dtype=torch.float32, device=dev)
+        # make sure the BN buffers are on the device
+        self.module.to(dev)
+        sd = dict(self.module.named_buffers())
+        self.bn1_rm, self.bn1_rv = sd[ENC + "1.running_mean"], sd[ENC + "1.running_var"]
+        self.bn2_rm, self.bn2_rv = sd[DEC + "1.running_mean"], sd[DEC + "1.running_var"]
+        self.bn1_nbt, self.bn2_nbt = sd[ENC + "1.num_batches_tracked"], sd[DEC + "1.num_batches_tracked"]
+
+    # ------------------------------------------------------------------ buffers
+    def _alloc_step_buffers(self):
+        B, G, H, L, dev = self.B, self.G, self.H, self.L, self.dev
+        f = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)  # noqa: E731
+        T = (B + _lib.BN_TILE - 1) // _lib.BN_TILE
+        self.idx = torch.zeros(B, dtype=torch.int64, device=dev)
+        self.cov_cols = torch.zeros(B, 1, dtype=torch.int32, device=dev)
+        self.batch_cols = (self.data.batch + L).to(torch.int32)  # one-hot column of Wd per cell
+        self.y1, self.a1, self.dy1, self.da1 = f(B, H), f(B, H), f(B, H), f(B, H)
+        self.y2, self.h, self.dy2, self.dh = f(B, H), f(B, H), f(B, H), f(B, H)
+        self.part1, self.part2 = f(T, 2, H), f(T, 2, H)
+        self.mean1, self.rstd1, self.mean2, self.rstd2 = f(H), f(H), f(H), f(H)
+        self.library = f(B)
+        self.maskb = torch.ones(B, H, dtype=torch.bool, device=dev)
+        self.mask = self.maskb.view(torch.uint8)  # keep-mask, 1 byte per element
+        self.u = f(B, H)
+        self.B_cur = B
+        self.noise = f(B, L)
+        self.q_m, self.q_v, self.z, self.dz = f(B, L), f(B, L), f(B, L), f(B, L)
+        self.kl, self.reconst, self.stats = f(B), f(B), f(B, 4)
+        self.g_rec, self.g_kl = f(B), f(B)
+        self.out3 = torch.zeros(3, dtype=torch.float32, device=dev)
+        enc = self.module.z_encoder.encoder.fc_layers[0]
+        self.p_drop = float(enc[4].p) if enc[4] is not None else 0.0
+        lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
+        nbytes = max(
+            query("scvi_linear_bwd_ws_bytes", B, G, H, G),
+            query("scvi_linear_bwd_ws_bytes", B, L, H, L + max(self.nb, 0)),
+            query("scvi_bn_bwd_ws_bytes", B, H),
+            query("scvi_latent_bwd_ws_bytes", B, H, L),
+            query("scvi_decoder_nll_bwd_ws_bytes", B, H, G, lik),
+        )
+        self.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+
+    # ------------------------------------------------------------------ the step
+    def _forward_backward(self, st):
+        """Kernel sequence of one minibatch: forward, ELBO, backward into the gradient arena.
+        Rows are read from the resident matrix through `self.idx`.  `st` = cudaStream_t."""
+        B, G, H, L = self.B_cur, self.G, self.H, self.L
+        P, Gd, X = self.P, self.Gd, self.data.X
+        if X.dtype != torch.float32:
+            raise NotImplementedError("fused training reads fp32 resident counts (uint16 residency: gather path)")
+        ldx = X.stride(0)
+        lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
+        prec = self.module.precision
+        n = 0
+        # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
+        call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
+             None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY, _p(self.y1), H, _p(self.library), _p(self.part1), st)
+        call("scvi_bn_finalize", _p(self.part1), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn1_rm), _p(self.bn1_rv),
+             _p(self.mean1), _p(self.rstd1), st)
+        drop = self.p_drop > 0
+        call("scvi_bn_act_drop_fwd", _p(self.y1), H, B, H, _p(self.mean1), _p(self.rstd1), _p(P[ENC + "1.weight"]),
+             _p(P[ENC + "1.bias"]), 1, _p(self.mask) if drop else None, 1.0 / (1.0 - self.p_drop) if drop else 1.0,
+             _p(self.a1), H, st)
+        # ---- latent heads + rsample + KL
+        call("scvi_latent_fwd", _p(self.a1), H, B, H, L, _p(P["z_encoder.mean_encoder.weight"]),
+             _p(P["z_encoder.mean_encoder.bias"]), _p(P["z_encoder.var_encoder.weight"]),
+             _p(P["z_encoder.var_encoder.bias"]), _p(self.noise), self.module.z_encoder.var_eps, _p(self.q_m),
+             _p(self.q_v), _p(self.z), _p(self.kl), st)
+        # ---- decoder layer 0 with the batch covariate as a weight-column gather
+        inj = self.nb > 1
+        ncols = L + (self.nb if inj else 0)
+        call("scvi_linear_fwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, _p(P[DEC + "0.bias"]),
+             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.y2), H, None, _p(self.part2), st)
+        call("scvi_bn_finalize", _p(self.part2), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn2_rm), _p(self.bn2_rv),
+             _p(self.mean2), _p(self.rstd2), st)
+        call("scvi_bn_act_drop_fwd", _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
+             _p(P[DEC + "1.bias"]), 1, None, 1.0, _p(self.h), H, st)
+        # ---- fused heads + softmax + likelihood
+        Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
+        Wp = P.get("decoder.px_dropout_decoder.weight")
+        bp = P.get("decoder.px_dropout_decoder.bias")
+        call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
+             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), st)
+        call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
+        call("scvi_elbo_seed", B, 0.0, _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), st)
+        n += 10
+        # ---- backward
+        call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
+             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, _p(self.dh), H,
+             _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
+             _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
+             _p(Gd["px_r"]), _p(self.ws), st)
+        n += 3
+        self._after_head_grads(st)
+        call("scvi_bn_act_drop_bwd", _p(self.dh), H, _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2),
+             _p(P[DEC + "1.weight"]), _p(P[DEC + "1.bias"]), 1, None, 1.0, 1, _p(self.dy2), H, _p(Gd[DEC + "1.weight"]),
+             _p(Gd[DEC + "1.bias"]), _p(self.ws), st)
+        call("scvi_linear_bwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, ncols,
+             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.dy2), H, _p(Gd[DEC + "0.weight"]),
+             _p(Gd[DEC + "0.bias"]), _p(self.dz), L, _p(self.ws), st)
+        call("scvi_latent_bwd", _p(self.a1), H, B, H, L, _p(P["z_encoder.mean_encoder.weight"]),
+             _p(P["z_encoder.var_encoder.weight"]), _p(self.noise), self.module.z_encoder.var_eps, _p(self.q_m),
+             _p(self.q_v), None, None, _p(self.dz), _p(self.g_kl), _p(self.da1), H,
+             _p(Gd["z_encoder.mean_encoder.weight"]), _p(Gd["z_encoder.mean_encoder.bias"]),
+             _p(Gd["z_encoder.var_encoder.weight"]), _p(Gd["z_encoder.var_encoder.bias"]), _p(self.ws), st)
+        call("scvi_bn_act_drop_bwd", _p(self.da1), H, _p(self.y1), H, B, H, _p(self.mean1), _p(self.rstd1),
+             _p(P[ENC + "1.weight"]), _p(P[ENC + "1.bias"]), 1, _p(self.mask) if drop else None,
+             1.0 / (1.0 - self.p_drop) if drop else 1.0, 1, _p(self.dy1), H, _p(Gd[ENC + "1.weight"]),
+             _p(Gd[ENC + "1.bias"]), _p(self.ws), st)
+        call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
+             _lib.LIN_LOG1P, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0, _p(self.ws), st)
+        n += 3 + 6 + 2 + 3 + 4
+        self.kernel_launches_per_step = n + 2  # + adam, counter
+
+    def _after_head_grads(self, st):
+        """Hook between the decoder-head backward and the rest (data-parallel overlap point)."""
+
+    def _adam(self, st):
+        call("scvi_adam_step_graph", _p(self.p), _p(self.g), _p(self.m), _p(self.v), self.n_arena,
+             _p(self.step_counter), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1.0 / self.world, st)
+
+    # ------------------------------------------------------------------ driving the step
+    def _draw_rng(self):
+        """Dropout keep-mask and reparameterisation noise from torch's CUDA generator (graph-safe)."""
+        if self.p_drop > 0:
+            self.u.uniform_()
+            torch.ge(self.u, self.p_drop, out=self.maskb)
+        self.noise.normal_()
+
+    def _whole_step(self, feed_rng: bool = True):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        if feed_rng:
+            self._draw_rng()
+        if self.nb > 1:
+            torch.index_select(self.batch_cols, 0, self.idx[: self.B_cur], out=self.cov_cols.view(-1)[: self.B_cur])
+        self._forward_backward(st)
+        if self.world > 1:
+            torch.distributed.all_reduce(self.g, group=self.pg)  # sum; Adam applies 1/world
+        self._adam(st)
+
+    def _capture(self):
+        """Capture the full-batch step once.  With data parallelism the graph is cut at the gradient
+        allreduce (fwd+bwd graph -> NCCL -> Adam graph)."""
+        self.B_cur = self.B
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):  # warm-up outside capture (lazy module loading, cudaFuncSetAttribute)
+            snap = (self.p.clone(), self.m.clone(), self.v.clone(), self.step_counter.clone(),
+                    self.bn1_rm.clone(), self.bn1_rv.clone(), self.bn2_rm.clone(), self.bn2_rv.clone())
+            self._whole_step()
+            for dst, src in zip((self.p, self.m, self.v, self.step_counter, self.bn1_rm, self.bn1_rv, self.bn2_rm,
+                                 self.bn2_rv), snap, strict=True):
+                dst.copy_(src)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        if self.world == 1:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._whole_step()
+            self._graphs = (g,)
+        else:
+            g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g1):
+                st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+                self._draw_rng()
+                if self.nb > 1:
+                    torch.index_select(self.batch_cols, 0, self.idx, out=self.cov_cols.view(-1))
+                self._forward_backward(st)
+            with torch.cuda.graph(g2):
+                self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream))
+            self._graphs = (g1, g2)
+
+    def set_epoch(self, epoch: int):
+        self.current_epoch = epoch
+        klw = compute_kl_weight(epoch, self.global_step, self.n_epochs_kl_warmup, self.n_steps_kl_warmup,
+                                self.max_kl_weight, self.min_kl_weight)
+        self.klw.fill_(float(klw))
+
+    def training_step(self, idx: torch.Tensor, drop_mask=None, noise=None):
+        """One optimisation step on the cells `idx` (device int64).  Returns the device tensor
+        `out3` = (loss, sum reconst, sum kl) without synchronising.  Explicit `drop_mask` /
+        `noise` (parity tests) force the eager path."""
+        n = idx.numel()
+        self.idx[:n].copy_(idx, non_blocking=True)
+        fed = drop_mask is not None or noise is not None
+        if fed or n != self.B or not self.use_cuda_graph:
+            self.B_cur = n
+            if drop_mask is not None:
+                self.mask[:n].copy_(drop_mask.to(self.dev, dtype=torch.uint8))
+            if noise is not None:
+                self.noise[:n].copy_(noise.to(self.dev))
+            self._whole_step(feed_rng=not fed)
+            self.B_cur = self.B
+        else:
+            if self._graphs is None:
+                self._capture()
+            if self.world == 1:
+                self._graphs[0].replay()
+            else:
+                self._graphs[0].replay()
+                torch.distributed.all_reduce(self.g, group=self.pg)
+                self._graphs[1].replay()
+        self.bn1_nbt.add_(1)
+        self.bn2_nbt.add_(1)
+        self.global_step += 1
+        return self.out3
+
+    def fit(self, max_epochs: int, shuffle: bool = True, drop_last: bool = False, log_every_epoch: bool = True):
+        """Train for `max_epochs` over this rank's shard; returns the per-epoch history
+        (train loss, ELBO pieces per cell) -- the numbers `TrainingPlan` logs."""
+        history = []
+        for epoch in range(self.current_epoch, self.current_epoch + max_epochs):
+            self.set_epoch(epoch)
+            order = epoch_indices(self.data.n_obs, self.rank, self.world, epoch, self.seed, shuffle).to(self.dev)
+            acc = torch.zeros(3, dtype=torch.float64, device=self.dev)
+            n_cells = 0
+            for s in range(0, order.numel(), self.B):
+                chunk = order[s : s + self.B]
+                if chunk.numel() < self.B and (drop_last or chunk.numel() < 2):
+                    break
+                out = self.training_step(chunk)
+                acc[0] += out[0].double() * chunk.numel()
+                acc[1:] += out[1:].double()
+                n_cells += chunk.numel()
+            if self.world > 1:  # BN running buffers follow rank 0 (DDP broadcast_buffers semantics)
+                for b in (self.bn1_rm, self.bn1_rv, self.bn2_rm, self.bn2_rv):
+                    torch.distributed.broadcast(b, src=0, group=self.pg)
+            if log_every_epoch:
+                a = acc.cpu()
+                history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
+                                "reconstruction_loss": float(a[1]) / max(n_cells, 1),
+                                "kl_local": float(a[2]) / max(n_cells, 1), "n_cells": n_cells,
+                                "kl_weight": float(self.klw.item())})
+        self.current_epoch += max_epochs
+        return history
