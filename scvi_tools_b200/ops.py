@@ -58,6 +58,8 @@ def gather_rows(X: torch.Tensor, idx: torch.Tensor, out: torch.Tensor | None = N
     B, G = idx.numel(), X.shape[1]
     if out is None:
         out = torch.empty(B, G, dtype=torch.float32, device=X.device)
+    if B == 0:
+        return out
     if X.dtype == torch.float32:
         X = _rowmajor(X, "X")
         call("scvi_gather_rows", _ptr(X), X.shape[0], G, X.stride(0), _ptr(idx), B, _ptr(out), out.stride(0), _stream())
@@ -73,6 +75,8 @@ def gather_i64(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     src = _check(src, "src", torch.int64).contiguous().view(-1)
     idx = _check(idx, "idx", torch.int64).contiguous()
     out = torch.empty(idx.numel(), dtype=torch.int64, device=src.device)
+    if idx.numel() == 0:
+        return out
     call("scvi_gather_i64", _ptr(src), src.numel(), _ptr(idx), idx.numel(), _ptr(out), _stream())
     return out
 

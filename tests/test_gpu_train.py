@@ -46,7 +46,8 @@ def test_two_adam_steps_match_reference_trajectory(name):
         # Adam with eps=0.01 moves each weight by <= lr per step: compare the *update*, not only the value
         upd_ref = out[f"param_after{n}::" + k] - P[k].numpy()
         upd = sd[k].cpu().numpy() - P[k].numpy()
-        assert np.linalg.norm(upd - upd_ref) <= 2e-3 * np.linalg.norm(upd_ref) + 1e-9, k
+        # floor: 1e-6 per element = 0.1% of lr (biases feeding a BatchNorm have pure-noise gradients)
+        assert np.linalg.norm(upd - upd_ref) <= 2e-3 * np.linalg.norm(upd_ref) + 1e-6 * np.sqrt(upd.size), k
         assert rel_err(sd[k].cpu(), out[f"param_after{n}::" + k]) < 1e-5, k
     assert int(sd["z_encoder.encoder.fc_layers.Layer 0.1.num_batches_tracked"]) == n
 
