@@ -244,7 +244,8 @@ def time_kernels(plan, a, reps=10):
 
     def k_dec_fwd():
         call("scvi_decoder_nll_fwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),
-             X.stride(0), _p(plan.idx), _p(plan.library), lik, plan.module.precision, _p(plan.reconst), _p(plan.stats), st)
+             X.stride(0), _p(plan.idx), _p(plan.library), lik, plan.module.precision, _p(plan.reconst), _p(plan.stats),
+             _p(plan.ws_fwd), st)
 
     def k_dec_bwd():
         call("scvi_decoder_nll_bwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),

@@ -164,11 +164,16 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
  *   h [B,H]; Ws, Wp [G,H] (scale / dropout heads; Wp, bp NULL for NB); px_r [G];
  *   x rows via row_idx as in scvi_linear_fwd; library [B].
  * Outputs: reconst [B]; row_stats [B,4] = (row max of scale logits, sum exp(logit-max),
- *   exp(library)/sumexp, S = sum_g mu * d(reconst)/d(mu)) consumed by the backward. */
+ *   exp(library)/sumexp, S = sum_g mu * d(reconst)/d(mu)) consumed by the backward.
+ * precision SCVI_PREC_FP32: FFMA tiles, ws may be NULL.  SCVI_PREC_TC: tcgen05 tensor cores with an
+ *   error-compensated fp16 split (fp32-level accuracy; needs H == 128) and a 256-byte aligned
+ *   workspace of scvi_decoder_nll_fwd_ws_bytes() bytes. */
+int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, int precision);
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r,
                          const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
-                         int likelihood, int precision, float* reconst, float* row_stats, void* stream);
+                         int likelihood, int precision, float* reconst, float* row_stats, void* ws,
+                         void* stream);
 /* g_reconst [B] = d(loss)/d(reconst).  Writes dh [B,H], dWs/dWp [G,H], dbs/dbp [G], dpx_r [G].
  * ws: scvi_decoder_nll_bwd_ws_bytes(). */
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);

@@ -11,48 +11,12 @@
 //   backward : A (CTA = 64 rows, all genes)  -> dh = ds Ws + dp Wp        (no atomics)
 //              B (CTA = 64 genes, row split) -> dWs, dWp, dbs, dbp, dpx_r (partial slabs,
 //              reduced in fixed order)
-#include "likelihood.cuh"
+#include "decoder_math.cuh"
 
 namespace scvi {
 
 constexpr int DT = 64;         // tile edge: rows per CTA (fwd / bwd A), genes per tile
 constexpr int DTHREADS = 256;  // 16 x 16 threads, 4 x 4 strided micro-tile each
-
-struct RowC {  // per-row constants
-  float m, invl, c, S, u;
-};
-
-// ll and d(ll)/d(mu) of one element, sharing sub-expressions
-template <bool ZINB>
-__device__ __forceinline__ void elem_fwd(float x, float mu, float pi, const GeneConst& gc, float eps, float& ll,
-                                         float& dmu) {
-  const float T = gc.theta + mu + eps;
-  const float rT = 1.f / T;
-  const float d_log = gc.log_theta - logf(T);
-  if (ZINB) {
-    const float sp = softplus_t(-pi);
-    const float a = -pi + gc.theta * d_log;
-    if (x < eps) {
-      ll = softplus_t(a) - sp;
-      dmu = sigmoid_t(a) * (-gc.theta * rT);
-    } else if (x > eps) {
-      const float me = mu + eps;
-      ll = -sp + a + x * (logf(me) - logf(T)) + lgammaf(x + gc.theta) - gc.lg_theta - lgammaf(x + 1.f);
-      dmu = -gc.theta * rT + x * (1.f / me - rT);
-    } else {
-      ll = 0.f;
-      dmu = 0.f;
-    }
-  } else {
-    const float me = mu + eps;
-    ll = gc.theta * d_log;
-    dmu = -gc.theta * rT;
-    if (x != 0.f) {  // x == 0: the remaining terms are exactly 0 in the reference too
-      ll += x * (logf(me) - logf(T)) + lgammaf(x + gc.theta) - gc.lg_theta - lgammaf(x + 1.f);
-      dmu += x * (1.f / me - rT);
-    }
-  }
-}
 
 // 64x64 logits tile: acc[i][j] += sum_k hs[ty+16i][k] * ws[tx+16j][k]
 template <bool TWO>
@@ -235,23 +199,6 @@ __global__ void __launch_bounds__(DTHREADS)
       *reinterpret_cast<float4*>(row_stats + (r0 + rr) * 4) = st;
     }
   }
-}
-
-// per-element backward: ds, dp (already multiplied by the upstream u) and u * theta * d(reconst)/d(theta)
-template <bool ZINB>
-__device__ __forceinline__ void elem_bwd(float x, float s, float pi, const RowC& rc, const GeneConst& gc, float eps,
-                                         float& ds, float& dp, float& dr) {
-  const float e = expf(s - rc.m);
-  const float mu = e * rc.c;
-  float dmu, dth, dpi = 0.f;
-  if (ZINB)
-    zinb_ll_grad(x, mu, pi, gc, eps, dmu, dth, dpi);
-  else
-    nb_ll_grad(x, mu, gc, eps, dmu, dth);
-  // reconst = -sum ll:  d/ds = mu * g - softmax * S,  g = -dmu,  softmax = e * invl
-  ds = rc.u * (-mu * dmu - e * rc.invl * rc.S);
-  dp = -rc.u * dpi;
-  dr = -rc.u * gc.theta * dth;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -686,12 +633,25 @@ static int set_smem(K kernel, size_t bytes, const char* name) {
 
 }  // namespace scvi
 
+namespace scvi {
+int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
+int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
+                       const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                       const int64_t* row_idx, const float* library, int likelihood, float* reconst,
+                       float* row_stats, void* ws, cudaStream_t st);
+}  // namespace scvi
+
 extern "C" {
+
+int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, int precision) {
+  if (precision == SCVI_PREC_TC) return scvi::tc_decoder_fwd_ws_bytes(B, H, G, likelihood);
+  return 0;
+}
 
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r, const float* x,
                          int64_t ldx, const int64_t* row_idx, const float* library, int likelihood, int precision,
-                         float* reconst, float* row_stats, void* stream) {
+                         float* reconst, float* row_stats, void* ws, void* stream) {
   using namespace scvi;
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "scvi_decoder_nll_fwd: unknown likelihood %d", likelihood);
@@ -702,11 +662,14 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   SCVI_REQUIRE(((uintptr_t)h % 16 == 0) && ((uintptr_t)Ws % 16 == 0) && (!zinb || (uintptr_t)Wp % 16 == 0) &&
                    ((uintptr_t)row_stats % 16 == 0),
                "scvi_decoder_nll_fwd: h / Ws / Wp / row_stats must be 16-byte aligned");
+  if (B == 0) return SCVI_OK;
+  if (precision == SCVI_PREC_TC)
+    return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, likelihood, reconst,
+                              row_stats, ws, (cudaStream_t)stream);
   if (precision != SCVI_PREC_FP32) {
-    set_error("scvi_decoder_nll_fwd: precision %d not built", precision);
+    set_error("scvi_decoder_nll_fwd: unknown precision %d", precision);
     return SCVI_EUNSUPPORTED;
   }
-  if (B == 0) return SCVI_OK;
   const size_t smem = sizeof(float) * ((size_t)DT * (H + 4) * (zinb ? 3 : 2) + DT * 5);
   SCVI_REQUIRE(smem <= 220 * 1024, "scvi_decoder_nll_fwd: n_hidden %lld too large", (long long)H);
   cudaStream_t st = (cudaStream_t)stream;
@@ -765,8 +728,8 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
     return SCVI_EUNSUPPORTED;
   }
   SCVI_REQUIRE(!dh || (lddh >= H && lddh % 4 == 0 && (uintptr_t)dh % 16 == 0), "%s: dh must be 16-byte aligned", name);
-  if (precision != SCVI_PREC_FP32) {
-    set_error("%s: precision %d not built", name, precision);
+  if (precision != SCVI_PREC_FP32 && precision != SCVI_PREC_TC) {
+    set_error("%s: unknown precision %d", name, precision);
     return SCVI_EUNSUPPORTED;
   }
   (void)library;

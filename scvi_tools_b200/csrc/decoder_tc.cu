@@ -1,0 +1,435 @@
+// tcgen05 / TMEM variant of the fused decoder heads + softmax + NB/ZINB likelihood (SCVI_PREC_TC).
+//
+// GEMM: logits[128 rows, 128 genes] = h[128, H=128] * W_tile[128 genes, 128]^T on the 5th-gen tensor
+// cores (tcgen05.mma kind::f16, fp32 accumulators in TMEM).  fp32 parity is kept with an
+// error-compensated fp16 split: v = hi + lo (2 x 11-bit significands), D = hi*hi + hi*lo + lo*hi
+// (3 MMAs per K-step, error ~2^-22).  Operands are pre-scaled by powers of two (h x 4, W x 256) so the
+// `lo` parts stay in fp16's normal range; the accumulator is rescaled by 2^-10 in the epilogue.
+//
+// Pipeline per CTA (128 rows x a contiguous range of 128-gene tiles), warp-specialised:
+//   warp 0     : producer   -- 1-D bulk async copies (TMA engine) of pre-packed W tiles, 2-stage ring
+//   warp 1     : MMA issuer -- one elected lane issues 24 tcgen05.mma per head tile, commits to mbarriers
+//   warp 2     : TMEM allocator
+//   warps 4-11 : epilogue   -- tcgen05.ld 16 columns at a time, per-element likelihood, row reductions
+// TMEM holds 2 buffers x (1|2 heads) x 128 fp32 columns so the MMAs of tile j+1 overlap the epilogue of j.
+#include "decoder_math.cuh"
+#include "tc.cuh"
+
+namespace scvi {
+
+constexpr int TC_M = 128;          // rows per CTA (UMMA M)
+constexpr int TC_N = 128;          // genes per tile (UMMA N)
+constexpr int TC_H = 128;          // n_hidden (K)
+constexpr int TC_KC = TC_H / 8;    // 16-byte k-chunks per row (8 halves each)
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 32 * (4 + TC_EPI_WARPS);
+constexpr float TC_SCALE_H = 4.f, TC_SCALE_W = 256.f, TC_RESCALE = 1.f / (4.f * 256.f);
+constexpr uint32_t TC_OPER_BYTES = TC_M * TC_H * 2;        // one fp16 operand block (hi or lo): 32 KB
+constexpr uint32_t TC_STAGE_BYTES = 2 * TC_OPER_BYTES;     // hi + lo of one head tile: 64 KB
+constexpr int TC_GC = 8;                                   // floats per gene in the constant table
+
+// ---------------------------------------------------------------------------------------
+// pack: W fp32 [G, H] -> per (gene tile, head) contiguous {hi block, lo block} in the UMMA K-major
+// no-swizzle layout addr(r, kc) = kc * (128 * 16 B) + r * 16 B; plus the per-gene constant table.
+// ---------------------------------------------------------------------------------------
+__global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* __restrict__ bs,
+                                     const float* __restrict__ Wp, const float* __restrict__ bp,
+                                     const float* __restrict__ px_r, int64_t G, int nheads, float eps,
+                                     __half* __restrict__ packed, float* __restrict__ gconst) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nT = (G + TC_N - 1) / TC_N;
+  const int64_t items = nT * nheads * TC_KC * TC_N;
+  if (e < items) {
+    const int r = (int)(e % TC_N);
+    const int kc = (int)((e / TC_N) % TC_KC);
+    const int head = (int)((e / (TC_N * TC_KC)) % nheads);
+    const int64_t t = e / ((int64_t)TC_N * TC_KC * nheads);
+    const int64_t g = t * TC_N + r;
+    const float* W = head == 0 ? Ws : Wp;
+    __half hi[8], lo[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      float v = (g < G) ? W[g * TC_H + 8 * kc + q] * TC_SCALE_W : 0.f;
+      v = fminf(fmaxf(v, -60000.f), 60000.f);
+      tc::split_f16(v, hi[q], lo[q]);
+    }
+    __half* base = packed + ((t * nheads + head) * 2) * (int64_t)(TC_M * TC_H);
+    *reinterpret_cast<uint4*>(base + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(hi);
+    *reinterpret_cast<uint4*>(base + (int64_t)TC_M * TC_H + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(lo);
+  }
+  if (e < nT * TC_N) {
+    const bool ok = e < G;
+    const GeneConst gc = make_gene_const(ok ? expf(px_r[e]) : 1.f, eps);
+    float* o = gconst + e * TC_GC;
+    o[0] = gc.theta;
+    o[1] = gc.log_theta;
+    o[2] = gc.lg_theta;
+    o[3] = ok ? bs[e] : 0.f;
+    o[4] = (ok && nheads == 2) ? bp[e] : 0.f;
+    o[5] = o[6] = o[7] = 0.f;
+  }
+}
+
+// h tile: fp32 [rows, H] -> scaled fp16 hi / lo blocks in shared memory (same layout as the packed W)
+__device__ __forceinline__ void tc_stage_h(const float* __restrict__ h, int64_t ldh, int valid, __half* s_hi,
+                                           __half* s_lo, int tid, int nthreads) {
+  for (int e = tid; e < TC_M * TC_KC; e += nthreads) {
+    const int r = e % TC_M, kc = e / TC_M;
+    __half hi[8], lo[8];
+    if (r < valid) {
+      const float4 a = *reinterpret_cast<const float4*>(h + (int64_t)r * ldh + 8 * kc);
+      const float4 b = *reinterpret_cast<const float4*>(h + (int64_t)r * ldh + 8 * kc + 4);
+      const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int q = 0; q < 8; ++q) tc::split_f16(fminf(fmaxf(v[q] * TC_SCALE_H, -60000.f), 60000.f), hi[q], lo[q]);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) hi[q] = lo[q] = __float2half_rn(0.f);
+    }
+    *reinterpret_cast<uint4*>(s_hi + kc * TC_M * 8 + r * 8) = *reinterpret_cast<uint4*>(hi);
+    *reinterpret_cast<uint4*>(s_lo + kc * TC_M * 8 + r * 8) = *reinterpret_cast<uint4*>(lo);
+  }
+}
+
+struct TcSmem {
+  // dynamic smem carve-up (byte offsets from a 1024-aligned base)
+  static constexpr uint32_t H_HI = 0;
+  static constexpr uint32_t H_LO = TC_OPER_BYTES;
+  static constexpr uint32_t STAGE0 = 2 * TC_OPER_BYTES;
+  static constexpr uint32_t BARS = STAGE0 + 2 * TC_STAGE_BYTES;  // 8 mbarriers
+  static constexpr uint32_t TMEM_PTR = BARS + 8 * 8;
+  static constexpr uint32_t RED = TMEM_PTR + 16;                 // [2 halves][128 rows][2] floats
+  static constexpr uint32_t TOTAL = RED + 2 * TC_M * 2 * 4;
+};
+
+// issue the 3 x 8 MMAs of one head tile: D = Ahi*Bhi + Ahi*Blo + Alo*Bhi over K = 128
+__device__ __forceinline__ void tc_issue_head(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi,
+                                              uint32_t b_lo) {
+  constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_N);
+  constexpr uint32_t LBO = TC_M * 16, SBO = 128, KSTEP = 2 * LBO;  // one MMA consumes K = 16 = 2 k-chunks
+#pragma unroll
+  for (int ks = 0; ks < TC_H / 16; ++ks) {
+    const uint64_t ah = tc::smem_desc_kmajor(a_hi + ks * KSTEP, LBO, SBO);
+    const uint64_t al = tc::smem_desc_kmajor(a_lo + ks * KSTEP, LBO, SBO);
+    const uint64_t bh = tc::smem_desc_kmajor(b_hi + ks * KSTEP, LBO, SBO);
+    const uint64_t bl = tc::smem_desc_kmajor(b_lo + ks * KSTEP, LBO, SBO);
+    tc::mma_f16_ss(d_tmem, ah, bh, idesc, ks > 0);
+    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1);
+    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// forward.  MODE 0: per-(split,row) online (max, sum-exp) of the scale logits.
+//           MODE 1: per-(split,row) partial (-sum ll, S) given the merged (max, sum-exp).
+// grid = (row tiles, gene splits); CTA handles gene tiles [t0, t1).
+// ---------------------------------------------------------------------------------------
+template <int MODE, bool ZINB>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+    tc_decoder_fwd_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, int64_t G,
+                          const __half* __restrict__ packed, const float* __restrict__ gconst,
+                          const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx,
+                          const float* __restrict__ library, int tiles_per_split, int nsplit, float eps, int xvec,
+                          float* __restrict__ lse_part /*[nsplit][B][2]*/,
+                          float* __restrict__ out_part /*[nsplit][B][2]*/) {
+  constexpr int NHEADS_PACK = ZINB ? 2 : 1;               // heads present in `packed`
+  constexpr int NHEADS = (MODE == 1 && ZINB) ? 2 : 1;     // heads this kernel multiplies
+  constexpr uint32_t TMEM_COLS = 2 * NHEADS * TC_N;       // 2 buffers
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
+  __half* s_hhi = reinterpret_cast<__half*>(smem + TcSmem::H_HI);
+  __half* s_hlo = reinterpret_cast<__half*>(smem + TcSmem::H_LO);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TcSmem::BARS);
+  uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + TcSmem::TMEM_PTR);
+  float* s_red = reinterpret_cast<float*>(smem + TcSmem::RED);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = (int64_t)blockIdx.x * TC_M;
+  const int valid = (int)min((int64_t)TC_M, B - r0);
+  const int nT = (int)((G + TC_N - 1) / TC_N);
+  const int t0 = blockIdx.y * tiles_per_split;
+  const int t1 = min(nT, t0 + tiles_per_split);
+  const int ntiles = max(0, t1 - t0);
+
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&full[i], 1);
+      tc::mbar_init(&empty[i], 1);
+      tc::mbar_init(&tfull[i], 1);
+      tc::mbar_init(&tempty[i], TC_EPI_WARPS);
+    }
+    tc::fence_mbar_init();
+  }
+  if (warp == 2) tc::tmem_alloc(s_tmem, TMEM_COLS);
+  tc_stage_h(h + r0 * ldh, ldh, valid, s_hhi, s_hlo, tid, TC_THREADS);
+  tc::fence_proxy_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    // ===== producer: one head tile (hi+lo, 64 KB) per stage
+    if (lane == 0) {
+      int it = 0;
+      for (int t = t0; t < t1; ++t)
+        for (int hd = 0; hd < NHEADS; ++hd, ++it) {
+          const int s = it & 1;
+          tc::mbar_wait(&empty[s], ((it >> 1) & 1) ^ 1);
+          tc::mbar_arrive_expect_tx(&full[s], TC_STAGE_BYTES);
+          const __half* src = packed + ((int64_t)(t * NHEADS_PACK + hd) * 2) * (TC_M * TC_H);
+          uint8_t* dst = smem + TcSmem::STAGE0 + s * TC_STAGE_BYTES;
+          tc::bulk_g2s(dst, src, TC_OPER_BYTES, &full[s]);
+          tc::bulk_g2s(dst + TC_OPER_BYTES, src + TC_M * TC_H, TC_OPER_BYTES, &full[s]);
+        }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer
+    if (lane == 0) {
+      const uint32_t a_hi = tc::smem_u32(s_hhi), a_lo = tc::smem_u32(s_hlo);
+      int it = 0;
+      for (int j = 0; j < ntiles; ++j) {
+        const int buf = j & 1;
+        tc::mbar_wait(&tempty[buf], ((j >> 1) & 1) ^ 1);
+        tc::fence_after_sync();
+        for (int hd = 0; hd < NHEADS; ++hd, ++it) {
+          const int s = it & 1;
+          tc::mbar_wait(&full[s], (it >> 1) & 1);
+          tc::fence_after_sync();
+          const uint32_t b_hi = tc::smem_u32(smem + TcSmem::STAGE0 + s * TC_STAGE_BYTES);
+          tc_issue_head(tmem_base + (buf * NHEADS + hd) * TC_N, a_hi, a_lo, b_hi, b_hi + TC_OPER_BYTES);
+          tc::mma_commit(&empty[s]);  // stage reusable once these MMAs have read it
+        }
+        tc::mma_commit(&tfull[buf]);  // accumulators of tile j complete
+      }
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column half)
+    const int q = warp & 3, half = (warp - 4) >> 2;
+    const int r = 32 * q + lane;
+    const bool rvalid = r < valid;
+    const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
+    const float* xrow = x + grow * ldx;
+    float m_run = -INFINITY, l_run = 0.f, nll = 0.f, S = 0.f;
+    RowC rc;
+    rc.m = 0.f; rc.invl = 0.f; rc.c = 0.f; rc.S = 0.f; rc.u = 0.f;
+    if (MODE == 1) {
+      // merge the per-split (max, sum-exp) partials of this row
+      float m = -INFINITY, l = 0.f;
+      if (rvalid) {
+        for (int sp = 0; sp < nsplit; ++sp) {
+          const float2 ml = *reinterpret_cast<const float2*>(lse_part + ((int64_t)sp * B + r0 + r) * 2);
+          if (ml.x == -INFINITY) continue;
+          const float mn = fmaxf(m, ml.x);
+          l = (m == -INFINITY ? 0.f : l * expf(m - mn)) + ml.y * expf(ml.x - mn);
+          m = mn;
+        }
+        rc.m = m;
+        rc.invl = 1.f / l;
+        rc.c = expf(library[r0 + r]) / l;
+      }
+    }
+    const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
+    for (int j = 0; j < ntiles; ++j) {
+      const int buf = j & 1;
+      const int64_t g0 = (int64_t)(t0 + j) * TC_N;
+      tc::mbar_wait(&tfull[buf], (j >> 1) & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        const int col0 = 64 * half + 16 * c;
+        float sv[16], pv[16];
+        tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 0) * TC_N + col0, sv);
+        if (NHEADS == 2) tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 1) * TC_N + col0, pv);
+        tc::tmem_ld_wait();
+        const int64_t gb = g0 + col0;
+        if (MODE == 0) {
+          float tm = -INFINITY;
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            sv[i] = fmaf(sv[i], TC_RESCALE, gconst[(gb + i) * TC_GC + 3]);
+            if (gb + i < G) tm = fmaxf(tm, sv[i]);
+          }
+          if (tm > m_run) {
+            l_run *= expf(m_run - tm);
+            m_run = tm;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (gb + i < G) l_run += expf(sv[i] - m_run);
+        } else if (rvalid) {
+          float xq[16];
+          if (xvec) {  // 4 x 16-byte streaming loads (row start and G are multiples of 4 floats)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (gb + 4 * k < G) t4 = ld_stream4(xrow + gb + 4 * k);
+              xq[4 * k] = t4.x; xq[4 * k + 1] = t4.y; xq[4 * k + 2] = t4.z; xq[4 * k + 3] = t4.w;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) xq[i] = (gb + i < G) ? __ldg(xrow + gb + i) : 0.f;
+          }
+#pragma unroll 4
+          for (int i = 0; i < 16; ++i) {
+            if (gb + i >= G) break;
+            const float4 k0 = *reinterpret_cast<const float4*>(gconst + (gb + i) * TC_GC);
+            const float bpv = gconst[(gb + i) * TC_GC + 4];
+            GeneConst gc;
+            gc.theta = k0.x;
+            gc.log_theta = k0.y;
+            gc.lg_theta = k0.z;
+            const float s = fmaf(sv[i], TC_RESCALE, k0.w);
+            const float pi = NHEADS == 2 ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
+            const float xv = xq[i];
+            const float mu = expf(s - rc.m) * rc.c;
+            float ll, dmu;
+            elem_fwd<ZINB>(xv, mu, pi, gc, eps, ll, dmu);
+            nll -= ll;
+            S -= mu * dmu;
+          }
+        }
+      }
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty[buf]);
+    }
+    // combine the two column halves of each row and write this split's partial
+    float a0 = MODE == 0 ? m_run : nll, a1 = MODE == 0 ? l_run : S;
+    if (half == 1) {
+      s_red[r * 2 + 0] = a0;
+      s_red[r * 2 + 1] = a1;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
+    if (half == 0 && rvalid) {
+      const float b0 = s_red[r * 2 + 0], b1 = s_red[r * 2 + 1];
+      float2 o;
+      if (MODE == 0) {
+        const float mn = fmaxf(a0, b0);
+        o.x = mn;
+        o.y = (a0 == -INFINITY ? 0.f : a1 * expf(a0 - mn)) + (b0 == -INFINITY ? 0.f : b1 * expf(b0 - mn));
+        *reinterpret_cast<float2*>(lse_part + ((int64_t)blockIdx.y * B + r0 + r) * 2) = o;
+      } else {
+        o.x = a0 + b0;
+        o.y = a1 + b1;
+        *reinterpret_cast<float2*>(out_part + ((int64_t)blockIdx.y * B + r0 + r) * 2) = o;
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// reconst[b] = sum_split nll; row_stats[b] = (max, sumexp, exp(library)/sumexp, sum_split S)
+__global__ void tc_rowstats_combine_kernel(const float* __restrict__ lse_part, const float* __restrict__ out_part,
+                                           const float* __restrict__ library, int64_t B, int nsplit,
+                                           float* __restrict__ reconst, float* __restrict__ row_stats) {
+  const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float m = -INFINITY, l = 0.f, nll = 0.f, S = 0.f;
+  for (int sp = 0; sp < nsplit; ++sp) {
+    const float2 ml = *reinterpret_cast<const float2*>(lse_part + ((int64_t)sp * B + b) * 2);
+    const float2 o = *reinterpret_cast<const float2*>(out_part + ((int64_t)sp * B + b) * 2);
+    nll += o.x;
+    S += o.y;
+    if (ml.x == -INFINITY) continue;
+    const float mn = fmaxf(m, ml.x);
+    l = (m == -INFINITY ? 0.f : l * expf(m - mn)) + ml.y * expf(ml.x - mn);
+    m = mn;
+  }
+  reconst[b] = nll;
+  *reinterpret_cast<float4*>(row_stats + b * 4) = make_float4(m, l, expf(library[b]) / l, S);
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+struct TcPlan {
+  int64_t nT, rowtiles;
+  int nsplit, tiles_per_split;
+  size_t off_packed, off_gconst, off_lse, off_out, total;
+};
+
+static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
+  TcPlan p;
+  p.nT = cdiv(G, TC_N);
+  p.rowtiles = cdiv(B, TC_M);
+  int64_t ns = std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles));
+  ns = std::min<int64_t>(ns, p.nT);
+  p.tiles_per_split = (int)cdiv(p.nT, ns);
+  p.nsplit = (int)cdiv(p.nT, p.tiles_per_split);
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  p.off_packed = 0;
+  p.off_gconst = al(p.off_packed + (size_t)p.nT * nheads * 2 * TC_M * TC_H * sizeof(__half));
+  p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * TC_GC * sizeof(float));
+  p.off_out = al(p.off_lse + (size_t)p.nsplit * B * 2 * sizeof(float));
+  p.total = al(p.off_out + (size_t)p.nsplit * B * 2 * sizeof(float));
+  return p;
+}
+
+int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood) {
+  (void)H;
+  return (int64_t)tc_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
+}
+
+template <int MODE, bool ZINB>
+static int tc_launch_fwd(const TcPlan& p, const float* h, int64_t ldh, int64_t B, int64_t G, const __half* packed,
+                         const float* gconst, const float* x, int64_t ldx, const int64_t* row_idx,
+                         const float* library, int xvec, float* lse, float* outp, cudaStream_t st) {
+  auto k = tc_decoder_fwd_kernel<MODE, ZINB>;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcSmem::TOTAL + 1024);
+    if (e != cudaSuccess) {
+      set_error("tc_decoder_fwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
+      return SCVI_ECUDA;
+    }
+    attr = true;
+  }
+  dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
+  k<<<grid, TC_THREADS, TcSmem::TOTAL + 1024, st>>>(h, ldh, B, G, packed, gconst, x, ldx, row_idx, library,
+                                                     p.tiles_per_split, p.nsplit, 1e-8f, xvec, lse, outp);
+  return SCVI_OK;
+}
+
+int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
+                       const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                       const int64_t* row_idx, const float* library, int likelihood, float* reconst,
+                       float* row_stats, void* ws, cudaStream_t st) {
+  const bool zinb = likelihood == SCVI_LIK_ZINB;
+  if (H != TC_H) {
+    set_error("scvi_decoder_nll_fwd(SCVI_PREC_TC): n_hidden must be %d (got %lld)", TC_H, (long long)H);
+    return SCVI_EUNSUPPORTED;
+  }
+  SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_fwd(SCVI_PREC_TC): ws must be 256-byte aligned");
+  SCVI_REQUIRE(ldh % 4 == 0 && ((uintptr_t)h % 16 == 0), "scvi_decoder_nll_fwd(SCVI_PREC_TC): h must be 16-byte aligned");
+  const int nheads = zinb ? 2 : 1;
+  const TcPlan p = tc_plan(B, G, nheads);
+  uint8_t* w8 = (uint8_t*)ws;
+  __half* packed = (__half*)(w8 + p.off_packed);
+  float* gconst = (float*)(w8 + p.off_gconst);
+  float* lse = (float*)(w8 + p.off_lse);
+  float* outp = (float*)(w8 + p.off_out);
+  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
+  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, gconst);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
+  const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);
+  int rc;
+  if (zinb) {
+    if ((rc = tc_launch_fwd<0, true>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;
+    SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");
+    if ((rc = tc_launch_fwd<1, true>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;
+  } else {
+    if ((rc = tc_launch_fwd<0, false>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;
+    SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");
+    if ((rc = tc_launch_fwd<1, false>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;
+  }
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc nll)");
+  tc_rowstats_combine_kernel<<<(unsigned)cdiv(B, 256), 256, 0, st>>>(lse, outp, library, B, p.nsplit, reconst, row_stats);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc combine)");
+  return SCVI_OK;
+}
+
+}  // namespace scvi

@@ -328,9 +328,11 @@ class DecoderNLL(torch.autograd.Function):
         dev = h.device
         reconst = torch.empty(B, dtype=torch.float32, device=dev)
         stats = torch.empty(B, 4, dtype=torch.float32, device=dev)
+        nws = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, likelihood, precision)
+        ws = _ws(nws, dev) if nws > 0 else None
         call("scvi_decoder_nll_fwd", _ptr(h), h.stride(0), B, H, G, _ptr(Ws), _ptr(bs), _ptr(Wp) if zinb else None,
              _ptr(bp) if zinb else None, _ptr(px_r), _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), likelihood,
-             precision, _ptr(reconst), _ptr(stats), _stream())
+             precision, _ptr(reconst), _ptr(stats), _ptr(ws), _stream())
         ctx.save_for_backward(h, Ws, bs, Wp if zinb else None, bp if zinb else None, px_r, x, library, stats, row_idx)
         ctx.meta = (likelihood, precision)
         return reconst

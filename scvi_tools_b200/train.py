@@ -174,6 +174,8 @@ class FusedTrainingPlan:
             query("scvi_decoder_nll_bwd_ws_bytes", B, H, G, lik),
         )
         self.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik, self.module.precision)
+        self.ws_fwd = torch.empty(int(nf), dtype=torch.uint8, device=dev) if nf > 0 else None
 
     # ------------------------------------------------------------------ the step
     def _forward_backward(self, st):
@@ -215,7 +217,7 @@ class FusedTrainingPlan:
         Wp = P.get("decoder.px_dropout_decoder.weight")
         bp = P.get("decoder.px_dropout_decoder.bias")
         call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), st)
+             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), _p(self.ws_fwd), st)
         call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         call("scvi_elbo_seed", B, 0.0, _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), st)
         n += 10
