@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--cells", type=int, default=N_CELLS)
     ap.add_argument("--genes", type=int, default=N_GENES)
     ap.add_argument("--likelihood", default="zinb", choices=["zinb", "nb"])
+    ap.add_argument("--precision", default="tc", choices=["tc", "fp32"],
+                    help="GEMM arithmetic of the fused decoder kernels: tc = tcgen05 error-compensated fp16 split "
+                         "(fp32-grade accuracy, parity-tested), fp32 = FFMA")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -317,7 +320,8 @@ def run_b200_arm(a):
     batch = (torch.arange(a.cells, device=dev) * N_BATCH // a.cells)
     data = DeviceResidentCounts(X, batch=batch, device=dev)
     torch.manual_seed(0)
-    m = S.VAE(n_input=a.genes, n_batch=N_BATCH, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT).train()
+    m = S.VAE(n_input=a.genes, n_batch=N_BATCH, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT,
+              precision=1 if a.precision == "tc" else 0).train()
     plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True)
     plan.set_epoch(0)
     order = torch.randperm(a.cells, device=dev)
@@ -437,7 +441,8 @@ def run_b200_arm(a):
                        "global_batch": B * world,
                        "cache": "inputs larger than L2: rows gathered at random from the HBM-resident count matrix "
                                 f"({a.cells * a.genes * 4 / 1e9:.1f} GB)",
-                       "precision": "fp32 FFMA GEMMs (parity path)", "cuda_graph": True},
+                       "precision": ("tcgen05 fp16 hi/lo split GEMMs, fp32 accumulate (fp32-grade, parity-tested)"
+                                     if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True},
             "clocks": clocks, "e2e": e2e, "gpu_launches": plan.kernel_launches_per_step * K,
             "roofline": roof, "kernels": kern, "cpu_baseline": cpu, "final_loss": loss_end,
         }

@@ -14,7 +14,7 @@ PREC_TC = 1
 def _run(G, B, nb, lik, precision, seed):
     import scvi_tools_b200 as S
 
-    X, batch = O.synthetic_iid(max(B, nb * 40), G, nb, seed=seed)
+    X, batch = O.synthetic_iid(max(B, nb * 40) + nb, G, nb, seed=seed)  # synthetic_iid rounds down to a multiple of nb
     torch.manual_seed(seed)
     m = S.VAE(n_input=G, n_batch=nb, gene_likelihood=lik, precision=precision)
     P = {k: v.detach().clone() for k, v in m.state_dict().items()}
@@ -77,5 +77,6 @@ def test_tc_large_batch_matches_ffma_path():
     a = lo_tc.reconstruction_loss["reconstruction_loss"].detach().cpu()
     b = lo_32.reconstruction_loss["reconstruction_loss"].detach().cpu()
     assert max_rel(a, b) < 5e-6
+    gs = max(float(v.abs().max()) for v in g_32.values())
     for k in g_32:
-        assert float((g_tc[k] - g_32[k]).norm()) <= 1e-4 * float(g_32[k].norm()) + 1e-7, k
+        assert grad_close(g_tc[k], g_32[k], 1e-4, gs), k
