@@ -13,32 +13,28 @@
 //   warps 4-11 : epilogue   -- tcgen05.ld 16 columns at a time, per-element likelihood, row reductions
 // TMEM holds 2 buffers x (1|2 heads) x 128 fp32 columns so the MMAs of tile j+1 overlap the epilogue of j.
 #include "decoder_math.cuh"
-#include "tc.cuh"
+#include "tc_layout.cuh"
 
 namespace scvi {
 
-constexpr int TC_M = 128;          // rows per CTA (UMMA M)
-constexpr int TC_N = 128;          // genes per tile (UMMA N)
-constexpr int TC_H = 128;          // n_hidden (K)
-constexpr int TC_KC = TC_H / 8;    // 16-byte k-chunks per row (8 halves each)
 constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_THREADS = 32 * (4 + TC_EPI_WARPS);
-constexpr float TC_SCALE_H = 4.f, TC_SCALE_W = 256.f, TC_RESCALE = 1.f / (4.f * 256.f);
-constexpr uint32_t TC_OPER_BYTES = TC_M * TC_H * 2;        // one fp16 operand block (hi or lo): 32 KB
-constexpr uint32_t TC_STAGE_BYTES = 2 * TC_OPER_BYTES;     // hi + lo of one head tile: 64 KB
-constexpr int TC_GC = 8;                                   // floats per gene in the constant table
 
 // ---------------------------------------------------------------------------------------
-// pack: W fp32 [G, H] -> per (gene tile, head) contiguous {hi block, lo block} in the UMMA K-major
-// no-swizzle layout addr(r, kc) = kc * (128 * 16 B) + r * 16 B; plus the per-gene constant table.
+// pack: W fp32 [G, H] -> fp16 hi / lo blocks in the UMMA no-swizzle layout (tc_layout.cuh), twice:
+//   packed128: per (128-gene tile, head) {hi block, lo block} of 128 x 128   (LSE / NLL-only / dW kernels)
+//   packed32 : per 32-gene tile {Ws hi, Ws lo, (Wp hi, Wp lo), gene constants}  (fused NLL + dh kernel)
+// plus the per-gene constant table gconst [nT128 * 128][TC_GC].
 // ---------------------------------------------------------------------------------------
 __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* __restrict__ bs,
                                      const float* __restrict__ Wp, const float* __restrict__ bp,
                                      const float* __restrict__ px_r, int64_t G, int nheads, float eps,
-                                     __half* __restrict__ packed, float* __restrict__ gconst) {
+                                     __half* __restrict__ packed, uint8_t* __restrict__ packed32,
+                                     float* __restrict__ gconst) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t nT = (G + TC_N - 1) / TC_N;
   const int64_t items = nT * nheads * TC_KC * TC_N;
+  const uint32_t st32 = tc_w32_stage_bytes(nheads);
   if (e < items) {
     const int r = (int)(e % TC_N);
     const int kc = (int)((e / TC_N) % TC_KC);
@@ -53,20 +49,40 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
       v = fminf(fmaxf(v, -60000.f), 60000.f);
       tc::split_f16(v, hi[q], lo[q]);
     }
-    __half* base = packed + ((t * nheads + head) * 2) * (int64_t)(TC_M * TC_H);
-    *reinterpret_cast<uint4*>(base + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(hi);
-    *reinterpret_cast<uint4*>(base + (int64_t)TC_M * TC_H + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(lo);
+    if (packed) {
+      __half* base = packed + ((t * nheads + head) * 2) * (int64_t)(TC_M * TC_H);
+      *reinterpret_cast<uint4*>(base + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(hi);
+      *reinterpret_cast<uint4*>(base + (int64_t)TC_M * TC_H + (int64_t)kc * TC_N * 8 + r * 8) = *reinterpret_cast<uint4*>(lo);
+    }
+    if (packed32) {
+      const int64_t t32 = g / TC_NT;
+      const int r32 = (int)(g % TC_NT);
+      uint8_t* base = packed32 + t32 * st32 + (size_t)head * 2 * TC_BLK32;
+      *reinterpret_cast<uint4*>(base + (size_t)kc * TC_NT * 16 + r32 * 16) = *reinterpret_cast<uint4*>(hi);
+      *reinterpret_cast<uint4*>(base + TC_BLK32 + (size_t)kc * TC_NT * 16 + r32 * 16) = *reinterpret_cast<uint4*>(lo);
+    }
   }
   if (e < nT * TC_N) {
     const bool ok = e < G;
-    const GeneConst gc = make_gene_const(ok ? expf(px_r[e]) : 1.f, eps);
-    float* o = gconst + e * TC_GC;
-    o[0] = gc.theta;
-    o[1] = gc.log_theta;
-    o[2] = gc.lg_theta;
+    const float theta = ok ? expf(px_r[e]) : 1.f;
+    float o[TC_GC];
+    o[0] = theta;
+    o[1] = logf(theta + eps);
+    o[2] = lgammaf(theta);
     o[3] = ok ? bs[e] : 0.f;
     o[4] = (ok && nheads == 2) ? bp[e] : 0.f;
-    o[5] = o[6] = o[7] = 0.f;
+    o[5] = 1.f / (theta + eps);
+    o[6] = digamma_pos(theta);
+    o[7] = 0.f;
+    if (gconst) {
+#pragma unroll
+      for (int q = 0; q < TC_GC; ++q) gconst[e * TC_GC + q] = o[q];
+    }
+    if (packed32) {
+      float* gc32 = reinterpret_cast<float*>(packed32 + (e / TC_NT) * st32 + (size_t)nheads * 2 * TC_BLK32) + (e % TC_NT) * TC_GC;
+#pragma unroll
+      for (int q = 0; q < TC_GC; ++q) gc32[q] = o[q];
+    }
   }
 }
 
@@ -99,7 +115,8 @@ struct TcSmem {
   static constexpr uint32_t BARS = STAGE0 + 2 * TC_STAGE_BYTES;  // 8 mbarriers
   static constexpr uint32_t TMEM_PTR = BARS + 8 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;                 // [2 halves][128 rows][2] floats
-  static constexpr uint32_t TOTAL = RED + 2 * TC_M * 2 * 4;
+  static constexpr uint32_t LGX1 = RED + 2 * TC_M * 2 * 4;       // lgamma(x+1) table
+  static constexpr uint32_t TOTAL = LGX1 + fm::LGX1_TABLE * 4;
 };
 
 // issue the 3 x 8 MMAs of one head tile: D = Ahi*Bhi + Ahi*Blo + Alo*Bhi over K = 128
@@ -143,6 +160,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   uint64_t *full = bars, *empty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + TcSmem::TMEM_PTR);
   float* s_red = reinterpret_cast<float*>(smem + TcSmem::RED);
+  float* s_lgx1 = reinterpret_cast<float*>(smem + TcSmem::LGX1);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t r0 = (int64_t)blockIdx.x * TC_M;
@@ -162,6 +180,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     tc::fence_mbar_init();
   }
   if (warp == 2) tc::tmem_alloc(s_tmem, TMEM_COLS);
+  if (MODE == 1)
+    for (int i = tid; i < fm::LGX1_TABLE; i += TC_THREADS) s_lgx1[i] = lgammaf((float)i + 1.f);
   tc_stage_h(h + r0 * ldh, ldh, valid, s_hhi, s_hlo, tid, TC_THREADS);
   tc::fence_proxy_async_smem();
   tc::fence_before_sync();
@@ -214,6 +234,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     float m_run = -INFINITY, l_run = 0.f, nll = 0.f, S = 0.f;
     RowC rc;
     rc.m = 0.f; rc.invl = 0.f; rc.c = 0.f; rc.S = 0.f; rc.u = 0.f;
+    float krow = 0.f;
     if (MODE == 1) {
       // merge the per-split (max, sum-exp) partials of this row
       float m = -INFINITY, l = 0.f;
@@ -228,6 +249,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         rc.m = m;
         rc.invl = 1.f / l;
         rc.c = expf(library[r0 + r]) / l;
+        krow = (library[r0 + r] - m) * fm::LOG2E - log2f(l);
       }
     }
     const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
@@ -274,20 +296,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 #pragma unroll 4
           for (int i = 0; i < 16; ++i) {
             if (gb + i >= G) break;
-            const float4 k0 = *reinterpret_cast<const float4*>(gconst + (gb + i) * TC_GC);
-            const float bpv = gconst[(gb + i) * TC_GC + 4];
-            GeneConst gc;
-            gc.theta = k0.x;
-            gc.log_theta = k0.y;
-            gc.lg_theta = k0.z;
-            const float s = fmaf(sv[i], TC_RESCALE, k0.w);
-            const float pi = NHEADS == 2 ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
-            const float xv = xq[i];
-            const float mu = expf(s - rc.m) * rc.c;
-            float ll, dmu;
-            elem_fwd<ZINB>(xv, mu, pi, gc, eps, ll, dmu);
+            const float* gcp = gconst + (gb + i) * TC_GC;
+            const fm::GeneK gk = load_gene_k(gcp);
+            const float s = fmaf(sv[i], TC_RESCALE, gcp[3]);
+            const float pi = NHEADS == 2 ? fmaf(pv[i], TC_RESCALE, gcp[4]) : 0.f;
+            float ll, g1, dpi, mu;
+            fm::elem_fwd<ZINB>(xq[i], s, pi, krow, gk, eps, s_lgx1, ll, g1, dpi, mu);
             nll -= ll;
-            S -= mu * dmu;
+            S += g1;
           }
         }
       }
@@ -413,7 +429,7 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
   float* lse = (float*)(w8 + p.off_lse);
   float* outp = (float*)(w8 + p.off_out);
   const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
-  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, gconst);
+  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
   const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);
   int rc;

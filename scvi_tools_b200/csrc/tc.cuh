@@ -94,6 +94,14 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
+  uint32_t r[8];
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr));
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ------------------------------------------------------------------------------
@@ -108,13 +116,35 @@ __device__ __forceinline__ uint64_t smem_desc_kmajor(uint32_t smem_addr, uint32_
   d |= (uint64_t)1 << 46;  // descriptor version 1 (Blackwell)
   return d;                // base_offset 0, lbo_mode 0, layout_type 0 = SWIZZLE_NONE
 }
-// instruction descriptor, kind::f16: F16 x F16 -> F32, both operands K-major, M x N tile
-__host__ __device__ constexpr uint32_t idesc_f16_f32(int M, int N) {
+// MN-major operand, no swizzle: element (mn index i, reduction index k) at
+//   base + (k % 8) * 16 + (k / 8) * LBO + (i / 8) * SBO + (i % 8) * 2     (fp16)
+// i.e. 8 reduction rows x 16 B (8 contiguous MN elements) core matrices.  The same descriptor encoding as
+// the K-major one; the major-ness is selected by the instruction descriptor.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return smem_desc_kmajor(smem_addr, lbo_bytes, sbo_bytes);
+}
+// instruction descriptor, kind::f16: F16 x F16 -> F32, M x N tile; a_mn / b_mn = 1 selects an MN-major operand
+__host__ __device__ constexpr uint32_t idesc_f16_f32(int M, int N, int a_mn = 0, int b_mn = 0) {
   return (1u << 4)                      // c_format = F32
          | (0u << 7) | (0u << 10)       // a_format = b_format = F16
-         | (0u << 15) | (0u << 16)      // a_major = b_major = K
+         | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16)
          | ((uint32_t)(N >> 3) << 17)   // n_dim
          | ((uint32_t)(M >> 4) << 24);  // m_dim
+}
+// exact power of two 2^e as a float (|e| <= 126)
+__device__ __forceinline__ float pow2i(int e) { return __int_as_float((127 + e) << 23); }
+// 8 floats (already scaled into fp16 range) -> one 16-byte chunk of fp16 `hi` and one of `lo` residuals
+__device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo) {
+  __half2 h[4], l[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const __half2 hh = __floats2half2_rn(v[2 * q], v[2 * q + 1]);
+    const float2 back = __half22float2(hh);
+    h[q] = hh;
+    l[q] = __floats2half2_rn(v[2 * q] - back.x, v[2 * q + 1] - back.y);
+  }
+  hi = *reinterpret_cast<uint4*>(h);
+  lo = *reinterpret_cast<uint4*>(l);
 }
 
 // ---- fp16 hi/lo split: v ~= hi + lo with |err| <= 2^-22 |v| for |v| in fp16 normal range ---------
