@@ -248,12 +248,12 @@ def time_kernels(plan, a, reps=10):
     def k_dec_fwd():
         call("scvi_decoder_nll_fwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),
              X.stride(0), _p(plan.idx), _p(plan.library), lik, plan.module.precision, _p(plan.reconst), _p(plan.stats),
-             _p(plan.ws_fwd), st)
+             _p(plan.g_rec), _p(plan.dh), H, _p(plan.ws_fwd), st)
 
     def k_dec_bwd():
         call("scvi_decoder_nll_bwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),
              X.stride(0), _p(plan.idx), _p(plan.library), _p(plan.stats), _p(plan.g_rec), lik, plan.module.precision,
-             _p(plan.dh), H, _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
+             None, H, _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
              _p(Gd["px_r"]), _p(plan.ws), st)
 

@@ -46,7 +46,7 @@ extern "C" {
 #define SCVI_PREC_FP32 0   /* FFMA, fp32 everywhere: the parity path */
 #define SCVI_PREC_TC 1     /* tcgen05 tensor-core path (when built) */
 
-int scvi_b200_abi_version(void);
+int scvi_b200_abi_version(void); /* 2 */
 const char* scvi_last_error_string(void);
 
 /* ---- a1: minibatch row gather --------------------------------------------------------
@@ -165,6 +165,11 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
  *   x rows via row_idx as in scvi_linear_fwd; library [B].
  * Outputs: reconst [B]; row_stats [B,4] = (row max of scale logits, sum exp(logit-max),
  *   exp(library)/sumexp, S = sum_g mu * d(reconst)/d(mu)) consumed by the backward.
+ * Training fusion: when `dh` [B,H] is non-NULL the forward also emits
+ *   dh[b,:] = g_reconst[b] * d(reconst[b])/d(h[b,:])   (g_reconst NULL = all ones),
+ * computed in the same pass as the likelihood (the per-element derivatives share every
+ * sub-expression with the log-probability), so the backward only has to produce the weight
+ * gradients (call scvi_decoder_nll_bwd with dh = NULL).
  * precision SCVI_PREC_FP32: FFMA tiles, ws may be NULL.  SCVI_PREC_TC: tcgen05 tensor cores with an
  *   error-compensated fp16 split (fp32-level accuracy; needs H == 128) and a 256-byte aligned
  *   workspace of scvi_decoder_nll_fwd_ws_bytes() bytes. */
@@ -172,8 +177,8 @@ int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likel
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r,
                          const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
-                         int likelihood, int precision, float* reconst, float* row_stats, void* ws,
-                         void* stream);
+                         int likelihood, int precision, float* reconst, float* row_stats,
+                         const float* g_reconst, float* dh, int64_t lddh, void* ws, void* stream);
 /* g_reconst [B] = d(loss)/d(reconst).  Writes dh [B,H], dWs/dWp [G,H], dbs/dbp [G], dpx_r [G].
  * ws: scvi_decoder_nll_bwd_ws_bytes(). */
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);

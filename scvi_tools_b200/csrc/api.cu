@@ -15,6 +15,6 @@ void set_error(const char* fmt, ...) {
 }  // namespace scvi
 
 extern "C" {
-int scvi_b200_abi_version(void) { return 1; }
+int scvi_b200_abi_version(void) { return 2; }
 const char* scvi_last_error_string(void) { return scvi::g_err; }
 }

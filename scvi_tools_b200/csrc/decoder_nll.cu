@@ -241,7 +241,7 @@ __global__ void __launch_bounds__(DTHREADS)
       rc[i].invl = 1.f / st.y;
       rc[i].c = st.z;
       rc[i].S = st.w;
-      rc[i].u = g_reconst[r0 + rr];
+      rc[i].u = g_reconst ? g_reconst[r0 + rr] : 1.f;
     } else {
       rc[i].m = 0.f; rc[i].invl = 0.f; rc[i].c = 0.f; rc[i].S = 0.f; rc[i].u = 0.f;
     }
@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(DTHREADS)
       rcs[tid * 5 + 1] = 1.f / st.y;
       rcs[tid * 5 + 2] = st.z;
       rcs[tid * 5 + 3] = st.w;
-      rcs[tid * 5 + 4] = ok ? g_reconst[rb + tid] : 0.f;
+      rcs[tid * 5 + 4] = ok ? (g_reconst ? g_reconst[rb + tid] : 1.f) : 0.f;
     }
     __syncthreads();
     tile_gemm<ZINB>(hs, ws, wp, H, ldh, tx, ty, as, ap);
@@ -638,7 +638,7 @@ int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood)
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
                        const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
-                       float* row_stats, void* ws, cudaStream_t st);
+                       float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws, cudaStream_t st);
 }  // namespace scvi
 
 extern "C" {
@@ -651,7 +651,8 @@ int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likel
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r, const float* x,
                          int64_t ldx, const int64_t* row_idx, const float* library, int likelihood, int precision,
-                         float* reconst, float* row_stats, void* ws, void* stream) {
+                         float* reconst, float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
+                         void* stream) {
   using namespace scvi;
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "scvi_decoder_nll_fwd: unknown likelihood %d", likelihood);
@@ -665,7 +666,7 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   if (B == 0) return SCVI_OK;
   if (precision == SCVI_PREC_TC)
     return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, likelihood, reconst,
-                              row_stats, ws, (cudaStream_t)stream);
+                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream);
   if (precision != SCVI_PREC_FP32) {
     set_error("scvi_decoder_nll_fwd: unknown precision %d", precision);
     return SCVI_EUNSUPPORTED;
@@ -683,6 +684,10 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
     decoder_nll_fwd_kernel<false><<<grid, DTHREADS, smem, st>>>(h, ldh, B, (int)H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, 1e-8f, reconst, row_stats);
   }
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd");
+  if (dh)  // FFMA path: the dh kernel of the backward, run right after the forward
+    return scvi_decoder_nll_bwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, row_stats, g_reconst,
+                                likelihood, precision, dh, lddh, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                stream);
   return SCVI_OK;
 }
 
@@ -720,7 +725,8 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   const char* name = "scvi_decoder_nll_bwd";
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "%s: unknown likelihood %d", name, likelihood);
-  SCVI_REQUIRE(h && Ws && bs && px_r && x && row_stats && g_reconst && ws && (!zinb || (Wp && bp)),
+  const bool want_dw = dWs || dWp || dbs || dbp || dpx_r;
+  SCVI_REQUIRE(h && Ws && bs && px_r && x && row_stats && (ws || !want_dw) && (!zinb || (Wp && bp)),
                "%s: NULL pointer", name);
   SCVI_REQUIRE(B > 0 && G > 0 && ldh >= H && ldh % 4 == 0 && ldx >= G, "%s: bad shape", name);
   if (!(H == 64 || H == 128 || H == 256)) {

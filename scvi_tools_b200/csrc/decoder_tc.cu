@@ -364,8 +364,9 @@ __global__ void tc_rowstats_combine_kernel(const float* __restrict__ lse_part, c
 // ---------------------------------------------------------------------------------------
 struct TcPlan {
   int64_t nT, rowtiles;
-  int nsplit, tiles_per_split;
-  size_t off_packed, off_gconst, off_lse, off_out, total;
+  int nsplit, tiles_per_split;    // LSE / NLL-only kernels: 128-gene tiles
+  int nsplit2, tiles_per_split2;  // fused NLL + dh kernel: 32-gene tiles
+  size_t off_packed, off_gconst, off_lse, off_out, off_packed32, off_dh, total;
 };
 
 static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
@@ -380,8 +381,15 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
   p.off_packed = 0;
   p.off_gconst = al(p.off_packed + (size_t)p.nT * nheads * 2 * TC_M * TC_H * sizeof(__half));
   p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * TC_GC * sizeof(float));
+  const int64_t nT32 = cdiv(G, TC_NT);
+  int64_t ns2 = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), nT32);
+  p.tiles_per_split2 = (int)cdiv(nT32, ns2);
+  p.nsplit2 = (int)cdiv(nT32, p.tiles_per_split2);
+  const int nsmax = std::max(p.nsplit, p.nsplit2);
   p.off_out = al(p.off_lse + (size_t)p.nsplit * B * 2 * sizeof(float));
-  p.total = al(p.off_out + (size_t)p.nsplit * B * 2 * sizeof(float));
+  p.off_packed32 = al(p.off_out + (size_t)nsmax * B * 2 * sizeof(float));
+  p.off_dh = al(p.off_packed32 + (size_t)p.nT * 4 * tc_w32_stage_bytes(nheads));
+  p.total = al(p.off_dh + (size_t)p.nsplit2 * 2 * B * TC_H * sizeof(float));
   return p;
 }
 
@@ -410,10 +418,17 @@ static int tc_launch_fwd(const TcPlan& p, const float* h, int64_t ldh, int64_t B
   return SCVI_OK;
 }
 
+int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
+                     const float* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
+                     int nsplit_lse, int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part,
+                     const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
+                     cudaStream_t st);
+
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
                        const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
-                       float* row_stats, void* ws, cudaStream_t st) {
+                       float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
+                       cudaStream_t st) {
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   if (H != TC_H) {
     set_error("scvi_decoder_nll_fwd(SCVI_PREC_TC): n_hidden must be %d (got %lld)", TC_H, (long long)H);
@@ -429,10 +444,21 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
   float* lse = (float*)(w8 + p.off_lse);
   float* outp = (float*)(w8 + p.off_out);
   const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
-  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
+  uint8_t* packed32 = dh ? w8 + p.off_packed32 : nullptr;
+  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, packed32, gconst);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
   const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);
   int rc;
+  if (dh) {  // training: LSE pass, then the fused NLL + dh kernel
+    SCVI_REQUIRE(lddh >= TC_H && lddh % 4 == 0 && ((uintptr_t)dh % 16 == 0), "scvi_decoder_nll_fwd(SCVI_PREC_TC): dh must be 16-byte aligned");
+    if (zinb) rc = tc_launch_fwd<0, true>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st);
+    else rc = tc_launch_fwd<0, false>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st);
+    if (rc) return rc;
+    SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");
+    return tc_launch_nll_dh(zinb, h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, p.nsplit, p.nsplit2,
+                            p.tiles_per_split2, xvec, outp, (float*)(w8 + p.off_dh), g_reconst, reconst, row_stats, dh,
+                            lddh, st);
+  }
   if (zinb) {
     if ((rc = tc_launch_fwd<0, true>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");

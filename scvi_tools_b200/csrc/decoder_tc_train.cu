@@ -1,0 +1,413 @@
+// tcgen05 / TMEM training kernels of the fused decoder (SCVI_PREC_TC):
+//
+//   K2  tc_nll_dh_kernel   (CTA = 128 rows x a range of 32-gene tiles, "rows-owned")
+//       logits GEMM -> per-element NB/ZINB likelihood AND its per-element derivatives in one pass ->
+//       reconst partials, S = sum_g g1, and dh through three more tensor-core GEMMs whose A operands
+//       (g1, softmax p, -dpi) are staged by the epilogue warps as fp16 hi/lo blocks:
+//           dh_a = g1 * Ws + (-dpi) * Wp          dh_b = p * Ws          dh = u * (dh_a - S * dh_b)
+//       (the softmax backward term needs the full-row S, hence the second accumulator).
+//   K3  tc_dw_kernel       (CTA = 128 genes x a range of 32-row tiles, "genes-owned", transposed tile)
+//       logits^T GEMM -> per-element derivatives -> ds^T, dp^T staged -> dWs, dWp accumulate in TMEM
+//       over all the CTA's rows; column sums dbs, dbp, dpx_r in registers.  Partial slabs per row split,
+//       reduced in fixed order (deterministic, no atomics).
+//
+// Replaces autograd's backward of DecoderSCVI.forward's heads + log_prob (reference
+// src/scvi/nn/_base_components.py:436-441, src/scvi/distributions/_negative_binomial.py:36-135).
+// Warp roles: warp 0 = bulk-copy producer, warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
+// warps 4..19 = epilogue (thread = one TMEM lane x 8 columns).
+#include "decoder_math.cuh"
+#include "tc_layout.cuh"
+
+namespace scvi {
+
+constexpr int TT_EPI_WARPS = 16;
+constexpr int TT_THREADS = 32 * (4 + TT_EPI_WARPS);
+constexpr uint32_t TT_ABLK = TC_M * TC_NT * 2;  // staged A block: 128 x 32 fp16 = 8 KB
+
+// fp32 [rows, H] -> scaled fp16 hi / lo blocks (128-row block layout) in shared memory
+__device__ __forceinline__ void tt_stage_h(const float* __restrict__ h, int64_t ldh, int valid, uint8_t* s_hi,
+                                           uint8_t* s_lo, int tid, int nthreads) {
+  for (int e = tid; e < TC_M * TC_KC; e += nthreads) {
+    const int r = e % TC_M, kc = e / TC_M;
+    float v[8];
+    if (r < valid) {
+      const float4 a = *reinterpret_cast<const float4*>(h + (int64_t)r * ldh + 8 * kc);
+      const float4 b = *reinterpret_cast<const float4*>(h + (int64_t)r * ldh + 8 * kc + 4);
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = fminf(fmaxf(v[q] * TC_SCALE_H, -60000.f), 60000.f);
+    } else {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = 0.f;
+    }
+    uint4 hi, lo;
+    tc::split8(v, hi, lo);
+    *reinterpret_cast<uint4*>(s_hi + kc * TC_M * 16 + r * 16) = hi;
+    *reinterpret_cast<uint4*>(s_lo + kc * TC_M * 16 + r * 16) = lo;
+  }
+}
+
+// 3-MMA error-compensated product over `ksteps` K-steps of 16: D (+)= A * B with A, B as hi/lo blocks.
+// a_step / b_step = byte advance of the operand start address per K-step.
+__device__ __forceinline__ void tt_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t a_lbo, uint32_t a_sbo,
+                                        uint32_t a_step, uint32_t b_hi, uint32_t b_lo, uint32_t b_lbo, uint32_t b_sbo,
+                                        uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate) {
+  for (int ks = 0; ks < ksteps; ++ks) {
+    const uint64_t ah = tc::smem_desc(a_hi + ks * a_step, a_lbo, a_sbo);
+    const uint64_t al = tc::smem_desc(a_lo + ks * a_step, a_lbo, a_sbo);
+    const uint64_t bh = tc::smem_desc(b_hi + ks * b_step, b_lbo, b_sbo);
+    const uint64_t bl = tc::smem_desc(b_lo + ks * b_step, b_lbo, b_sbo);
+    tc::mma_f16_ss(d_tmem, ah, bh, idesc, (accumulate || ks > 0) ? 1u : 0u);
+    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1u);
+    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1u);
+  }
+}
+
+// =======================================================================================
+// K2: fused NLL + dh
+// =======================================================================================
+template <bool ZINB>
+struct K2Smem {
+  static constexpr int NH = ZINB ? 2 : 1;
+  static constexpr uint32_t WSTAGE = tc_w32_stage_bytes(NH);
+  static constexpr int NSTG = ZINB ? 3 : 2;  // staged operands: g1, p, (dp)
+  static constexpr uint32_t H_HI = 0;
+  static constexpr uint32_t H_LO = TC_OPER_BYTES;
+  static constexpr uint32_t W0 = 2 * TC_OPER_BYTES;
+  static constexpr uint32_t STG = W0 + 2 * WSTAGE;
+  static constexpr uint32_t BARS = STG + NSTG * 2 * TT_ABLK;  // 11 mbarriers
+  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr uint32_t LGX1 = TMEM_PTR + 16;
+  static constexpr uint32_t RED = LGX1 + fm::LGX1_TABLE * 4;  // [4 col groups][128 rows][2]
+  static constexpr uint32_t TOTAL = RED + 4 * TC_M * 2 * 4;
+};
+
+template <bool ZINB>
+__global__ void __launch_bounds__(TT_THREADS, 1)
+    tc_nll_dh_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, int64_t G,
+                     const uint8_t* __restrict__ packed32, const float* __restrict__ x, int64_t ldx,
+                     const int64_t* __restrict__ row_idx, const float* __restrict__ library,
+                     const float* __restrict__ lse_part /*[nsplit_lse][B][2]*/, int nsplit_lse, int tiles_per_split,
+                     float eps, int xvec, float* __restrict__ out_part /*[nsplit][B][2] = (nll, S)*/,
+                     float* __restrict__ dh_part /*[nsplit][2][B][H]*/) {
+  using L = K2Smem<ZINB>;
+  constexpr int NH = L::NH;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *wfull = bars, *wempty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
+  uint64_t *sfull = bars + 8, *sempty = bars + 9, *accfull = bars + 10;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+  float* s_lgx1 = reinterpret_cast<float*>(smem + L::LGX1);
+  float* s_red = reinterpret_cast<float*>(smem + L::RED);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = (int64_t)blockIdx.x * TC_M;
+  const int valid = (int)min((int64_t)TC_M, B - r0);
+  const int nT = (int)((G + TC_NT - 1) / TC_NT);
+  const int t0 = blockIdx.y * tiles_per_split;
+  const int t1 = min(nT, t0 + tiles_per_split);
+  const int ntiles = max(0, t1 - t0);
+
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&wfull[i], 1);
+      tc::mbar_init(&wempty[i], 1);
+      tc::mbar_init(&tfull[i], 1);
+      tc::mbar_init(&tempty[i], TT_EPI_WARPS);
+    }
+    tc::mbar_init(sfull, TT_EPI_WARPS);
+    tc::mbar_init(sempty, 1);
+    tc::mbar_init(accfull, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 2) tc::tmem_alloc(s_tmem, 512);
+  for (int i = tid; i < fm::LGX1_TABLE; i += TT_THREADS) s_lgx1[i] = lgammaf((float)i + 1.f);
+  tt_stage_h(h + r0 * ldh, ldh, valid, smem + L::H_HI, smem + L::H_LO, tid, TT_THREADS);
+  tc::fence_proxy_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *s_tmem;
+  // TMEM columns: logits [buf][head] 32 each at 0..127; acc1 (g1*Ws) 128; acc2 (p*Ws) 256; acc3 (dp*Wp) 384
+  const uint32_t ACC1 = tmem_base + 128, ACC2 = tmem_base + 256, ACC3 = tmem_base + 384;
+
+  if (warp == 0) {
+    // ===== producer: one 32-gene tile {Ws hi/lo, (Wp hi/lo), gene constants} per stage, one bulk copy
+    if (lane == 0) {
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j & 1;
+        tc::mbar_wait(&wempty[s], ((j >> 1) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&wfull[s], L::WSTAGE);
+        tc::bulk_g2s(smem + L::W0 + s * L::WSTAGE, packed32 + (size_t)(t0 + j) * L::WSTAGE, L::WSTAGE, &wfull[s]);
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idescL = tc::idesc_f16_f32(TC_M, TC_NT, 0, 0);  // logits: 128 x 32, both K-major
+      constexpr uint32_t idescO = tc::idesc_f16_f32(TC_M, TC_H, 0, 1);   // dh: 128 x 128, B MN-major
+      const uint32_t a_hi = tc::smem_u32(smem + L::H_HI), a_lo = tc::smem_u32(smem + L::H_LO);
+      const uint32_t stg = tc::smem_u32(smem + L::STG);
+      auto issue_logits = [&](int j) {
+        const int s = j & 1;
+        tc::mbar_wait(&wfull[s], (j >> 1) & 1);
+        tc::mbar_wait(&tempty[s], ((j >> 1) & 1) ^ 1);
+        tc::fence_after_sync();
+        const uint32_t w = tc::smem_u32(smem + L::W0 + s * L::WSTAGE);
+#pragma unroll
+        for (int hd = 0; hd < NH; ++hd)
+          tt_mma3(tmem_base + (s * 2 + hd) * TC_NT, a_hi, a_lo, TC_M * 16, 128, 2 * TC_M * 16,
+                  w + hd * 2 * TC_BLK32, w + hd * 2 * TC_BLK32 + TC_BLK32, TC_NT * 16, 128, 2 * TC_NT * 16, TC_H / 16,
+                  idescL, false);
+        tc::mma_commit(&tfull[s]);
+      };
+      issue_logits(0);
+      for (int j = 0; j < ntiles; ++j) {
+        if (j + 1 < ntiles) issue_logits(j + 1);
+        const int s = j & 1;
+        tc::mbar_wait(sfull, j & 1);
+        tc::fence_after_sync();
+        const uint32_t w = tc::smem_u32(smem + L::W0 + s * L::WSTAGE);
+        // staged A blocks (K-major, 128 rows x 32 genes): LBO = 128*16, SBO = 128, K-step = 2 chunks
+        // W blocks as MN-major B (N = hidden, K = genes): LBO = 128 (next 8 genes), SBO = 32*16, K-step = 256 B
+        tt_mma3(ACC1, stg + 0 * TT_ABLK, stg + 1 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + TC_BLK32, 128,
+                TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
+        tt_mma3(ACC2, stg + 2 * TT_ABLK, stg + 3 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + TC_BLK32, 128,
+                TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
+        if (ZINB)
+          tt_mma3(ACC3, stg + 4 * TT_ABLK, stg + 5 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w + 2 * TC_BLK32,
+                  w + 3 * TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
+        tc::mma_commit(sempty);      // staging buffers reusable
+        tc::mma_commit(&wempty[s]);  // weight stage reusable
+      }
+      tc::mma_commit(accfull);
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column group cg of 8 genes)
+    const int q = warp & 3, cg = (warp - 4) >> 2;
+    const int r = 32 * q + lane;
+    const bool rvalid = r < valid;
+    const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
+    const float* xrow = x + grow * ldx;
+    float krow = 0.f, elib_inv = 0.f, s1 = 1.f, inv_s1 = 1.f;
+    if (rvalid) {
+      float m = -INFINITY, l = 0.f;
+      for (int sp = 0; sp < nsplit_lse; ++sp) {
+        const float2 ml = *reinterpret_cast<const float2*>(lse_part + ((int64_t)sp * B + r0 + r) * 2);
+        if (ml.x == -INFINITY) continue;
+        const float mn = fmaxf(m, ml.x);
+        l = (m == -INFINITY ? 0.f : l * expf(m - mn)) + ml.y * expf(ml.x - mn);
+        m = mn;
+      }
+      const float lib = library[r0 + r];
+      krow = (lib - m) * fm::LOG2E - log2f(l);
+      elib_inv = expf(-lib);
+      // |g1| <= exp(library) (sum of the row's counts): scale so the bound maps to 2^14
+      int e = (int)ceilf(lib * fm::LOG2E);
+      e = max(-100, min(100, e));
+      s1 = tc::pow2i(14 - e);
+      inv_s1 = tc::pow2i(e - 14);
+    }
+    const float sP = tc::pow2i(TC_P_SCALE_LOG2), sD = tc::pow2i(TC_DP_SCALE_LOG2);
+    const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
+    uint8_t* stg = smem + L::STG;
+    float nll = 0.f, S = 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j & 1;
+      const int64_t gb = (int64_t)(t0 + j) * TC_NT + 8 * cg;
+      // x for this thread's 8 genes (issued before the wait so the loads overlap it)
+      float xq[8];
+      if (rvalid && xvec) {
+        float4 t4 = (gb < G) ? ld_stream4(xrow + gb) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 u4 = (gb + 4 < G) ? ld_stream4(xrow + gb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        xq[0] = t4.x; xq[1] = t4.y; xq[2] = t4.z; xq[3] = t4.w; xq[4] = u4.x; xq[5] = u4.y; xq[6] = u4.z; xq[7] = u4.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) xq[i] = (rvalid && gb + i < G) ? __ldg(xrow + gb + i) : 0.f;
+      }
+      tc::mbar_wait(&tfull[s], (j >> 1) & 1);
+      tc::mbar_wait(&wfull[s], (j >> 1) & 1);  // acquire the bulk-copied gene constants
+      tc::fence_after_sync();
+      float sv[8], pv[8];
+      tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 0) * TC_NT + 8 * cg, sv);
+      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 1) * TC_NT + 8 * cg, pv);
+      tc::tmem_ld_wait();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty[s]);  // logits buffer drained
+      const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
+      float a1[8], a2[8], a3[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 k0 = *reinterpret_cast<const float4*>(gc + i * TC_GC);
+        const float4 k1 = *reinterpret_cast<const float4*>(gc + i * TC_GC + 4);
+        fm::GeneK gk;
+        gk.theta = k0.x; gk.log_theta = k0.y; gk.lg_theta = k0.z; gk.rth = k1.y; gk.dg_theta = k1.z;
+        const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
+        const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
+        float ll, g1, dpi, mu;
+        fm::elem_fwd<ZINB>(xq[i], sl, pl, krow, gk, eps, s_lgx1, ll, g1, dpi, mu);
+        const bool ok = rvalid && (gb + i < G);
+        nll -= ok ? ll : 0.f;
+        S += ok ? g1 : 0.f;
+        a1[i] = ok ? g1 * s1 : 0.f;
+        a2[i] = ok ? mu * elib_inv * sP : 0.f;
+        a3[i] = ok ? -dpi * sD : 0.f;
+      }
+      uint4 hi1, lo1, hi2, lo2, hi3, lo3;
+      tc::split8(a1, hi1, lo1);
+      tc::split8(a2, hi2, lo2);
+      if (ZINB) tc::split8(a3, hi3, lo3);
+      tc::mbar_wait(sempty, (j & 1) ^ 1);  // output MMAs of the previous tile have read the staging buffers
+      const uint32_t off = cg * (TC_M * 16) + r * 16;
+      *reinterpret_cast<uint4*>(stg + 0 * TT_ABLK + off) = hi1;
+      *reinterpret_cast<uint4*>(stg + 1 * TT_ABLK + off) = lo1;
+      *reinterpret_cast<uint4*>(stg + 2 * TT_ABLK + off) = hi2;
+      *reinterpret_cast<uint4*>(stg + 3 * TT_ABLK + off) = lo2;
+      if (ZINB) {
+        *reinterpret_cast<uint4*>(stg + 4 * TT_ABLK + off) = hi3;
+        *reinterpret_cast<uint4*>(stg + 5 * TT_ABLK + off) = lo3;
+      }
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(sfull);
+    }
+    // per-row partials of this gene split: combine the 4 column groups
+    s_red[(cg * TC_M + r) * 2 + 0] = nll;
+    s_red[(cg * TC_M + r) * 2 + 1] = S;
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * TT_EPI_WARPS) : "memory");
+    if (cg == 0 && rvalid) {
+      float2 o = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        o.x += s_red[(c * TC_M + r) * 2 + 0];
+        o.y += s_red[(c * TC_M + r) * 2 + 1];
+      }
+      *reinterpret_cast<float2*>(out_part + ((int64_t)blockIdx.y * B + r0 + r) * 2) = o;
+    }
+    // dh partials: thread (r, cg) owns hidden columns 32*cg .. 32*cg+31
+    if (ntiles > 0) {
+      tc::mbar_wait(accfull, 0);
+      tc::fence_after_sync();
+    }
+    float* da = dh_part + (((int64_t)blockIdx.y * 2 + 0) * B + r0 + r) * TC_H + 32 * cg;
+    float* db = dh_part + (((int64_t)blockIdx.y * 2 + 1) * B + r0 + r) * TC_H + 32 * cg;
+    const float k1 = inv_s1 * (1.f / TC_SCALE_W), k2 = tc::pow2i(-TC_P_SCALE_LOG2) * (1.f / TC_SCALE_W),
+                k3 = tc::pow2i(-TC_DP_SCALE_LOG2) * (1.f / TC_SCALE_W);
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      float v1[8], v2[8], v3[8];
+      if (ntiles > 0) {
+        tc::tmem_ld8(ACC1 + lane_sel + 32 * cg + 8 * c, v1);
+        tc::tmem_ld8(ACC2 + lane_sel + 32 * cg + 8 * c, v2);
+        if (ZINB) tc::tmem_ld8(ACC3 + lane_sel + 32 * cg + 8 * c, v3);
+        tc::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v1[i] = v2[i] = v3[i] = 0.f;
+      }
+      if (rvalid) {
+        float oa[8], ob[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          oa[i] = v1[i] * k1 + (ZINB ? v3[i] * k3 : 0.f);
+          ob[i] = v2[i] * k2;
+        }
+        *reinterpret_cast<float4*>(da + 8 * c) = make_float4(oa[0], oa[1], oa[2], oa[3]);
+        *reinterpret_cast<float4*>(da + 8 * c + 4) = make_float4(oa[4], oa[5], oa[6], oa[7]);
+        *reinterpret_cast<float4*>(db + 8 * c) = make_float4(ob[0], ob[1], ob[2], ob[3]);
+        *reinterpret_cast<float4*>(db + 8 * c + 4) = make_float4(ob[4], ob[5], ob[6], ob[7]);
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, 512);
+}
+
+// reconst[b] = sum_split nll; row_stats[b] = (max, sumexp, exp(library)/sumexp, S);
+// dh[b, :] = u_b * (sum_split dh_a - S * sum_split dh_b)        (u_b = g_reconst[b], or 1)
+__global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int nsplit_lse,
+                                        const float* __restrict__ out_part, const float* __restrict__ dh_part,
+                                        int nsplit, const float* __restrict__ library,
+                                        const float* __restrict__ g_reconst, int64_t B, float* __restrict__ reconst,
+                                        float* __restrict__ row_stats, float* __restrict__ dh, int64_t lddh) {
+  // 32 threads per row (one float4 of dh each), 8 rows per block
+  const int64_t b = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (b >= B) return;
+  float m = -INFINITY, l = 0.f;
+  for (int sp = 0; sp < nsplit_lse; ++sp) {
+    const float2 ml = *reinterpret_cast<const float2*>(lse_part + ((int64_t)sp * B + b) * 2);
+    if (ml.x == -INFINITY) continue;
+    const float mn = fmaxf(m, ml.x);
+    l = (m == -INFINITY ? 0.f : l * expf(m - mn)) + ml.y * expf(ml.x - mn);
+    m = mn;
+  }
+  float nll = 0.f, S = 0.f;
+  for (int sp = 0; sp < nsplit; ++sp) {
+    const float2 o = *reinterpret_cast<const float2*>(out_part + ((int64_t)sp * B + b) * 2);
+    nll += o.x;
+    S += o.y;
+  }
+  if (lane == 0) {
+    reconst[b] = nll;
+    *reinterpret_cast<float4*>(row_stats + b * 4) = make_float4(m, l, expf(library[b]) / l, S);
+  }
+  if (dh) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+    for (int sp = 0; sp < nsplit; ++sp) {
+      const float4 va = *reinterpret_cast<const float4*>(dh_part + (((int64_t)sp * 2 + 0) * B + b) * TC_H + 4 * lane);
+      const float4 vb = *reinterpret_cast<const float4*>(dh_part + (((int64_t)sp * 2 + 1) * B + b) * TC_H + 4 * lane);
+      a.x += va.x; a.y += va.y; a.z += va.z; a.w += va.w;
+      c.x += vb.x; c.y += vb.y; c.z += vb.z; c.w += vb.w;
+    }
+    const float u = g_reconst ? g_reconst[b] : 1.f;
+    *reinterpret_cast<float4*>(dh + b * lddh + 4 * lane) =
+        make_float4(u * (a.x - S * c.x), u * (a.y - S * c.y), u * (a.z - S * c.z), u * (a.w - S * c.w));
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// host: K2 launcher (called by tc_decoder_nll_fwd in decoder_tc.cu when dh is requested)
+// ---------------------------------------------------------------------------------------
+template <bool ZINB>
+static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32, const float* x,
+                        int64_t ldx, const int64_t* row_idx, const float* library, const float* lse, int nsplit_lse,
+                        int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, cudaStream_t st) {
+  auto k = tc_nll_dh_kernel<ZINB>;
+  constexpr int smem = (int)K2Smem<ZINB>::TOTAL + 128;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("tc_nll_dh: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+      return SCVI_ECUDA;
+    }
+    attr = true;
+  }
+  dim3 grid((unsigned)cdiv(B, TC_M), (unsigned)nsplit);
+  k<<<grid, TT_THREADS, smem, st>>>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, tiles_per_split,
+                                    1e-8f, xvec, out_part, dh_part);
+  return SCVI_OK;
+}
+
+int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
+                     const float* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
+                     int nsplit_lse, int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part,
+                     const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
+                     cudaStream_t st) {
+  int rc = zinb ? tt_launch_k2<true>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit,
+                                     tiles_per_split, xvec, out_part, dh_part, st)
+                : tt_launch_k2<false>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit,
+                                      tiles_per_split, xvec, out_part, dh_part, st);
+  if (rc) return rc;
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc nll+dh)");
+  tc_train_combine_kernel<<<(unsigned)cdiv(B, 8), 256, 0, st>>>(lse, nsplit_lse, out_part, dh_part, nsplit, library,
+                                                               g_reconst, B, reconst, row_stats, dh, lddh);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc combine)");
+  return SCVI_OK;
+}
+
+}  // namespace scvi

@@ -328,25 +328,31 @@ class DecoderNLL(torch.autograd.Function):
         dev = h.device
         reconst = torch.empty(B, dtype=torch.float32, device=dev)
         stats = torch.empty(B, 4, dtype=torch.float32, device=dev)
+        # training fusion: d(reconst)/d(h) comes out of the same pass as the likelihood
+        dh_unit = torch.empty(B, H, dtype=torch.float32, device=dev) if (ctx.needs_input_grad[0] and B > 0) else None
         nws = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, likelihood, precision)
         ws = _ws(nws, dev) if nws > 0 else None
         call("scvi_decoder_nll_fwd", _ptr(h), h.stride(0), B, H, G, _ptr(Ws), _ptr(bs), _ptr(Wp) if zinb else None,
              _ptr(bp) if zinb else None, _ptr(px_r), _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), likelihood,
-             precision, _ptr(reconst), _ptr(stats), _ptr(ws), _stream())
-        ctx.save_for_backward(h, Ws, bs, Wp if zinb else None, bp if zinb else None, px_r, x, library, stats, row_idx)
+             precision, _ptr(reconst), _ptr(stats), None, _ptr(dh_unit), H, _ptr(ws), _stream())
+        ctx.save_for_backward(h, Ws, bs, Wp if zinb else None, bp if zinb else None, px_r, x, library, stats, row_idx,
+                              dh_unit)
         ctx.meta = (likelihood, precision)
         return reconst
 
     @staticmethod
     def backward(ctx, g):
-        h, Ws, bs, Wp, bp, px_r, x, library, stats, row_idx = ctx.saved_tensors
+        h, Ws, bs, Wp, bp, px_r, x, library, stats, row_idx, dh_unit = ctx.saved_tensors
         likelihood, precision = ctx.meta
         zinb = likelihood == _lib.LIK_ZINB
         B, H = h.shape
         G = Ws.shape[0]
         dev = h.device
         g = g.contiguous().float()
-        dh = torch.empty(B, H, dtype=torch.float32, device=dev) if ctx.needs_input_grad[0] else None
+        dh = None
+        if ctx.needs_input_grad[0]:
+            dh = dh_unit * g.unsqueeze(1) if dh_unit is not None else torch.empty(B, H, dtype=torch.float32, device=dev)
+        dh_k = None if dh_unit is not None else dh  # already produced by the forward
         dWs = torch.empty_like(Ws)
         dbs = torch.empty(G, dtype=torch.float32, device=dev)
         dWp = torch.empty_like(Wp) if zinb else None
@@ -354,7 +360,7 @@ class DecoderNLL(torch.autograd.Function):
         dr = torch.empty(G, dtype=torch.float32, device=dev)
         ws = _ws(query("scvi_decoder_nll_bwd_ws_bytes", B, H, G, likelihood), dev)
         call("scvi_decoder_nll_bwd", _ptr(h), h.stride(0), B, H, G, _ptr(Ws), _ptr(bs), _ptr(Wp), _ptr(bp), _ptr(px_r),
-             _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), _ptr(stats), _ptr(g), likelihood, precision, _ptr(dh),
+             _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), _ptr(stats), _ptr(g), likelihood, precision, _ptr(dh_k),
              H, _ptr(dWs), _ptr(dbs), _ptr(dWp), _ptr(dbp), _ptr(dr), _ptr(ws), _stream())
         return dh, dWs, dbs, dWp, dbp, dr, None, None, None, None, None
 

@@ -216,14 +216,17 @@ class FusedTrainingPlan:
         Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
         Wp = P.get("decoder.px_dropout_decoder.weight")
         bp = P.get("decoder.px_dropout_decoder.bias")
-        call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), _p(self.ws_fwd), st)
-        call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
+        # the ELBO is a mean over the minibatch, so d(loss)/d(reconst) = 1/B is known before the forward:
+        # the fused kernel emits dh together with the likelihood
         call("scvi_elbo_seed", B, 0.0, _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), st)
+        call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
+             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), _p(self.g_rec), _p(self.dh), H,
+             _p(self.ws_fwd), st)
+        call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         n += 10
         # ---- backward
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, _p(self.dh), H,
+             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, None, H,
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
              _p(Gd["px_r"]), _p(self.ws), st)

@@ -75,7 +75,7 @@ def test_plan_gradients_equal_autograd_path():
 
     plan._forward_backward(ctypes.c_void_p(st))
     for k in plan.keys:
-        assert rel_err(plan.Gd[k].cpu(), auto[k].cpu()) < 1e-6 or float(auto[k].abs().max()) < 1e-5, k
+        assert rel_err(plan.Gd[k].cpu(), auto[k].cpu()) < 1e-5 or float(auto[k].abs().max()) < 1e-5, k
 
 
 def test_graph_training_learns_and_is_finite():
