@@ -639,6 +639,11 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
                        const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
                        float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws, cudaStream_t st);
+int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood);
+int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
+                          const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                          const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
+                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, cudaStream_t st);
 }  // namespace scvi
 
 extern "C" {
@@ -694,7 +699,8 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood) {
   const int64_t S = scvi::dw_row_splits(B, G);
   const int64_t nheads = likelihood == SCVI_LIK_ZINB ? 2 : 1;
-  return 4 * (S * nheads * G * H + S * 3 * G) + 256;
+  const int64_t ffma = 4 * (S * nheads * G * H + S * 3 * G) + 256;
+  return H == 128 ? std::max<int64_t>(ffma, scvi::tc_decoder_bwd_ws_bytes(B, G, likelihood)) : ffma;
 }
 
 #define SCVI_DISPATCH_NH4(KERNEL, ZINB, NH4, ...)                                  \
@@ -747,7 +753,10 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
     SCVI_DISPATCH(decoder_nll_bwd_dh_kernel, h, ldh, B, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, row_stats, g_reconst, 1e-8f, dh, lddh);
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(dh)");
   }
-  if (dWs || dWp || dbs || dbp || dpx_r) {
+  if (want_dw && precision == SCVI_PREC_TC && H == 128)
+    return tc_decoder_nll_bwd_dw(h, ldh, B, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, row_stats, g_reconst, likelihood,
+                                 dWs, dbs, dWp, dbp, dpx_r, ws, st);
+  if (want_dw) {
     const int64_t S = dw_row_splits(B, G);
     const int nheads = zinb ? 2 : 1;
     float* slabW = (float*)ws;

@@ -411,3 +411,398 @@ int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t 
 }
 
 }  // namespace scvi
+
+// =======================================================================================
+// K3: dWs, dWp, dbs, dbp, dpx_r  (genes-owned, transposed tiles: TMEM lane = gene, column = row)
+// =======================================================================================
+namespace scvi {
+
+// h fp32 [B, H] -> per 32-row tile {h hi block, h lo block, row constants}; also the global bounds that
+// fix the staged-operand scales of K3: scal[0] = max_b 3 u_b exp(library_b) >= |ds|, scal[1] = max_b |u_b|.
+__global__ void __launch_bounds__(512)
+    tc_pack_h32_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, const float* __restrict__ row_stats,
+                       const float* __restrict__ g_reconst, const int64_t* __restrict__ row_idx,
+                       uint8_t* __restrict__ hpack, unsigned int* __restrict__ scal) {
+  const int64_t t = blockIdx.x;
+  const int r = threadIdx.x & 31, kc = threadIdx.x >> 5;
+  const int64_t b = t * TC_NT + r;
+  uint8_t* base = hpack + t * TC_H32_STAGE_BYTES;
+  float v[8];
+  if (b < B) {
+    const float4 a = *reinterpret_cast<const float4*>(h + b * ldh + 8 * kc);
+    const float4 c = *reinterpret_cast<const float4*>(h + b * ldh + 8 * kc + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = fminf(fmaxf(v[q] * TC_SCALE_H, -60000.f), 60000.f);
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = 0.f;
+  }
+  uint4 hi, lo;
+  tc::split8(v, hi, lo);
+  *reinterpret_cast<uint4*>(base + kc * TC_NT * 16 + r * 16) = hi;
+  *reinterpret_cast<uint4*>(base + TC_BLK32 + kc * TC_NT * 16 + r * 16) = lo;
+  if (kc == 0) {
+    float* rc = reinterpret_cast<float*>(base + 2 * TC_BLK32) + r * TC_ROWC;
+    float krow = 0.f, u = 0.f, uSe = 0.f, ok = 0.f;
+    int64_t rid = 0;
+    if (b < B) {
+      const float4 st = *reinterpret_cast<const float4*>(row_stats + b * 4);  // (max, sumexp, exp(lib)/sumexp, S)
+      u = g_reconst ? g_reconst[b] : 1.f;
+      krow = -st.x * fm::LOG2E + log2f(st.z);
+      const float L = st.z * st.y;  // exp(library)
+      uSe = u * st.w / L;
+      ok = 1.f;
+      rid = row_idx ? row_idx[b] : b;
+      atomicMax(&scal[0], __float_as_uint(3.f * fabsf(u) * L));
+      atomicMax(&scal[1], __float_as_uint(fabsf(u)));
+    }
+    rc[0] = krow; rc[1] = u; rc[2] = uSe; rc[3] = ok;
+    rc[4] = __uint_as_float((uint32_t)(rid & 0xffffffffu));
+    rc[5] = __uint_as_float((uint32_t)((uint64_t)rid >> 32));
+    rc[6] = 0.f; rc[7] = 0.f;
+  }
+}
+
+template <bool ZINB>
+struct K3Smem {
+  static constexpr int NH = ZINB ? 2 : 1;
+  static constexpr uint32_t W = 0;                              // [head][hi, lo] 32 KB blocks
+  static constexpr uint32_t HST = NH * 2 * TC_OPER_BYTES;       // 2 stages of {h hi, h lo, row constants}
+  static constexpr uint32_t STG = HST + 2 * TC_H32_STAGE_BYTES; // [head][hi, lo] staged ds^T / dp^T
+  static constexpr uint32_t BARS = STG + NH * 2 * TT_ABLK;
+  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr uint32_t RED = TMEM_PTR + 16;                // [3][4 row groups][128 genes]
+  static constexpr uint32_t TOTAL = RED + 3 * 4 * TC_M * 4;
+};
+
+template <bool ZINB>
+__global__ void __launch_bounds__(TT_THREADS, 1)
+    tc_dw_kernel(int64_t B, int64_t G, const uint8_t* __restrict__ packed128, const float* __restrict__ gconst,
+                 const uint8_t* __restrict__ hpack, const float* __restrict__ scal, const float* __restrict__ x,
+                 int64_t ldx, int tiles_per_split, float eps, float* __restrict__ slabW /*[splits][NH][G][H]*/,
+                 float* __restrict__ slabv /*[splits][3][G]*/) {
+  using L = K3Smem<ZINB>;
+  constexpr int NH = L::NH;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *hfull = bars, *hempty = bars + 2, *tfull = bars + 4, *tempty = bars + 6;
+  uint64_t *sfull = bars + 8, *sempty = bars + 9, *accfull = bars + 10, *wfull = bars + 11;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+  float* s_red = reinterpret_cast<float*>(smem + L::RED);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t g0 = (int64_t)blockIdx.x * TC_M;
+  const int nR = (int)((B + TC_NT - 1) / TC_NT);
+  const int rt0 = blockIdx.y * tiles_per_split;
+  const int rt1 = min(nR, rt0 + tiles_per_split);
+  const int ntiles = max(0, rt1 - rt0);
+
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&hfull[i], 1);
+      tc::mbar_init(&hempty[i], 1);
+      tc::mbar_init(&tfull[i], 1);
+      tc::mbar_init(&tempty[i], TT_EPI_WARPS);
+    }
+    tc::mbar_init(sfull, TT_EPI_WARPS);
+    tc::mbar_init(sempty, 1);
+    tc::mbar_init(accfull, 1);
+    tc::mbar_init(wfull, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 2) tc::tmem_alloc(s_tmem, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *s_tmem;
+  // TMEM columns: logits^T [buf][head] 32 each at 0..127; dWs accumulator at 128, dWp at 256
+
+  if (warp == 0) {
+    if (lane == 0 && ntiles > 0) {
+      // resident weight tile of this CTA's 128 genes: NH x {hi, lo} blocks, contiguous in packed128
+      tc::mbar_arrive_expect_tx(wfull, NH * 2 * TC_OPER_BYTES);
+      const uint8_t* src = packed128 + (size_t)blockIdx.x * NH * 2 * TC_OPER_BYTES;
+      for (int i = 0; i < NH * 2; ++i)
+        tc::bulk_g2s(smem + L::W + i * TC_OPER_BYTES, src + (size_t)i * TC_OPER_BYTES, TC_OPER_BYTES, wfull);
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j & 1;
+        tc::mbar_wait(&hempty[s], ((j >> 1) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&hfull[s], TC_H32_STAGE_BYTES);
+        tc::bulk_g2s(smem + L::HST + s * TC_H32_STAGE_BYTES, hpack + (size_t)(rt0 + j) * TC_H32_STAGE_BYTES,
+                     TC_H32_STAGE_BYTES, &hfull[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idescL = tc::idesc_f16_f32(TC_M, TC_NT, 0, 0);  // logits^T: 128 genes x 32 rows
+      constexpr uint32_t idescO = tc::idesc_f16_f32(TC_M, TC_H, 0, 1);   // dW: 128 genes x 128 hidden, B MN-major
+      const uint32_t wbase = tc::smem_u32(smem + L::W);
+      const uint32_t stg = tc::smem_u32(smem + L::STG);
+      tc::mbar_wait(wfull, 0);
+      auto issue_logits = [&](int j) {
+        const int s = j & 1;
+        tc::mbar_wait(&hfull[s], (j >> 1) & 1);
+        tc::mbar_wait(&tempty[s], ((j >> 1) & 1) ^ 1);
+        tc::fence_after_sync();
+        const uint32_t hb = tc::smem_u32(smem + L::HST + s * TC_H32_STAGE_BYTES);
+#pragma unroll
+        for (int hd = 0; hd < NH; ++hd)
+          tt_mma3(tmem_base + (s * 2 + hd) * TC_NT, wbase + hd * 2 * TC_OPER_BYTES,
+                  wbase + hd * 2 * TC_OPER_BYTES + TC_OPER_BYTES, TC_M * 16, 128, 2 * TC_M * 16, hb, hb + TC_BLK32,
+                  TC_NT * 16, 128, 2 * TC_NT * 16, TC_H / 16, idescL, false);
+        tc::mma_commit(&tfull[s]);
+      };
+      issue_logits(0);
+      for (int j = 0; j < ntiles; ++j) {
+        if (j + 1 < ntiles) issue_logits(j + 1);
+        const int s = j & 1;
+        tc::mbar_wait(sfull, j & 1);
+        tc::fence_after_sync();
+        const uint32_t hb = tc::smem_u32(smem + L::HST + s * TC_H32_STAGE_BYTES);
+        // A = staged ds^T (K-major: 128 genes x 32 rows); B = h tile as MN-major (N = hidden, K = rows)
+#pragma unroll
+        for (int hd = 0; hd < NH; ++hd)
+          tt_mma3(tmem_base + 128 + hd * TC_H, stg + (hd * 2) * TT_ABLK, stg + (hd * 2 + 1) * TT_ABLK, TC_M * 16, 128,
+                  2 * TC_M * 16, hb, hb + TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
+        tc::mma_commit(sempty);
+        tc::mma_commit(&hempty[s]);
+      }
+      tc::mma_commit(accfull);
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: thread = (gene lane gl, row group rg of 8 rows)
+    const int q = warp & 3, rg = (warp - 4) >> 2;
+    const int gl = 32 * q + lane;
+    const int64_t g = g0 + gl;
+    const bool gvalid = g < G;
+    const float* gcp = gconst + g * TC_GC;  // the table is padded to whole 128-gene tiles
+    const fm::GeneK gk = load_gene_k(gcp);
+    const float bsv = gcp[3], bpv = gcp[4];
+    // staged-operand scales from the global bounds (powers of two)
+    const float bound_ds = fmaxf(scal[0], 1e-30f), bound_dp = fmaxf(scal[1], 1e-30f);
+    const int e_ds = max(-100, min(100, (int)ceilf(log2f(bound_ds)))), e_dp = max(-100, min(100, (int)ceilf(log2f(bound_dp))));
+    const float sc_ds = tc::pow2i(14 - e_ds), sc_dp = tc::pow2i(TC_DP_SCALE_LOG2 - e_dp);
+    const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
+    uint8_t* stg = smem + L::STG;
+    float cs = 0.f, cp = 0.f, cr = 0.f;
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j & 1;
+      tc::mbar_wait(&hfull[s], (j >> 1) & 1);  // acquire the row constants of this tile
+      const float* rowc = reinterpret_cast<const float*>(smem + L::HST + s * TC_H32_STAGE_BYTES + 2 * TC_BLK32) + 8 * rg * TC_ROWC;
+      float xq[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float2 id = *reinterpret_cast<const float2*>(rowc + i * TC_ROWC + 4);
+        const int64_t rid = (int64_t)(((uint64_t)__float_as_uint(id.y) << 32) | (uint64_t)__float_as_uint(id.x));
+        xq[i] = gvalid ? ld_stream(x + rid * ldx + g) : 0.f;  // padded rows carry row id 0
+      }
+      tc::mbar_wait(&tfull[s], (j >> 1) & 1);
+      tc::fence_after_sync();
+      float sv[8], pv[8];
+      tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 0) * TC_NT + 8 * rg, sv);
+      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 1) * TC_NT + 8 * rg, pv);
+      tc::tmem_ld_wait();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty[s]);
+      float a1[8], a2[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float4 rc = *reinterpret_cast<const float4*>(rowc + i * TC_ROWC);  // krow, u, u*S*exp(-lib), valid
+        const float sl = fmaf(sv[i], TC_RESCALE, bsv);
+        const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
+        float g1, dpi, dth, mu;
+        fm::elem_bwd<ZINB>(xq[i], sl, pl, rc.x, gk, eps, g1, dpi, dth, mu);
+        const bool ok = gvalid && rc.w != 0.f;
+        const float ds = ok ? rc.y * g1 - mu * rc.z : 0.f;
+        const float dp = ok ? -rc.y * dpi : 0.f;
+        cs += ds;
+        cp += dp;
+        cr += ok ? -rc.y * gk.theta * dth : 0.f;
+        a1[i] = ds * sc_ds;
+        a2[i] = dp * sc_dp;
+      }
+      uint4 hi1, lo1, hi2, lo2;
+      tc::split8(a1, hi1, lo1);
+      if (ZINB) tc::split8(a2, hi2, lo2);
+      tc::mbar_wait(sempty, (j & 1) ^ 1);
+      const uint32_t off = rg * (TC_M * 16) + gl * 16;
+      *reinterpret_cast<uint4*>(stg + 0 * TT_ABLK + off) = hi1;
+      *reinterpret_cast<uint4*>(stg + 1 * TT_ABLK + off) = lo1;
+      if (ZINB) {
+        *reinterpret_cast<uint4*>(stg + 2 * TT_ABLK + off) = hi2;
+        *reinterpret_cast<uint4*>(stg + 3 * TT_ABLK + off) = lo2;
+      }
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(sfull);
+    }
+    // column sums: combine the 4 row groups of each gene
+    s_red[(0 * 4 + rg) * TC_M + gl] = cs;
+    s_red[(1 * 4 + rg) * TC_M + gl] = cp;
+    s_red[(2 * 4 + rg) * TC_M + gl] = cr;
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * TT_EPI_WARPS) : "memory");
+    if (rg < 3 && gvalid) {  // row group rg finalises quantity rg (dbs, dbp, dpx_r)
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) sum += s_red[(rg * 4 + c) * TC_M + gl];
+      slabv[((int64_t)blockIdx.y * 3 + rg) * G + g] = sum;
+    }
+    if (ntiles > 0) {
+      tc::mbar_wait(accfull, 0);
+      tc::fence_after_sync();
+    }
+    const float k1 = 1.f / (sc_ds * TC_SCALE_H), k2 = 1.f / (sc_dp * TC_SCALE_H);
+#pragma unroll 1
+    for (int hd = 0; hd < NH; ++hd) {
+      float* o = slabW + (((int64_t)blockIdx.y * NH + hd) * G + g) * TC_H + 32 * rg;
+      const float kk = hd == 0 ? k1 : k2;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        float v[8];
+        if (ntiles > 0) {
+          tc::tmem_ld8(tmem_base + lane_sel + 128 + hd * TC_H + 32 * rg + 8 * c, v);
+          tc::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = 0.f;
+        }
+        if (gvalid) {
+          *reinterpret_cast<float4*>(o + 8 * c) = make_float4(v[0] * kk, v[1] * kk, v[2] * kk, v[3] * kk);
+          *reinterpret_cast<float4*>(o + 8 * c + 4) = make_float4(v[4] * kk, v[5] * kk, v[6] * kk, v[7] * kk);
+        }
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, 512);
+}
+
+// sum the row-split slabs in fixed order (deterministic)
+static __global__ void tt_bwd_reduce_kernel(const float* __restrict__ slabW, const float* __restrict__ slabv,
+                                            int64_t splits, int nheads, int64_t GH, int64_t G,
+                                            float* __restrict__ dWs, float* __restrict__ dWp, float* __restrict__ dbs,
+                                            float* __restrict__ dbp, float* __restrict__ dpx_r) {
+  const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (e < GH) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f), p = s;
+    for (int64_t t = 0; t < splits; ++t) {
+      const float4 a = *reinterpret_cast<const float4*>(slabW + (t * nheads + 0) * GH + e);
+      s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+      if (nheads == 2) {
+        const float4 b = *reinterpret_cast<const float4*>(slabW + (t * nheads + 1) * GH + e);
+        p.x += b.x; p.y += b.y; p.z += b.z; p.w += b.w;
+      }
+    }
+    if (dWs) *reinterpret_cast<float4*>(dWs + e) = s;
+    if (nheads == 2 && dWp) *reinterpret_cast<float4*>(dWp + e) = p;
+  }
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < G) {
+    float a = 0.f, b = 0.f, c = 0.f;
+    for (int64_t t = 0; t < splits; ++t) {
+      a += slabv[(t * 3 + 0) * G + g];
+      b += slabv[(t * 3 + 1) * G + g];
+      c += slabv[(t * 3 + 2) * G + g];
+    }
+    if (dbs) dbs[g] = a;
+    if (nheads == 2 && dbp) dbp[g] = b;
+    if (dpx_r) dpx_r[g] = c;
+  }
+}
+
+__global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* __restrict__ bs,
+                                     const float* __restrict__ Wp, const float* __restrict__ bp,
+                                     const float* __restrict__ px_r, int64_t G, int nheads, float eps,
+                                     __half* __restrict__ packed, uint8_t* __restrict__ packed32,
+                                     float* __restrict__ gconst);
+
+struct TtBwdPlan {
+  int64_t nT, nR;
+  int splits, tiles_per_split;
+  size_t off_packed, off_gconst, off_hpack, off_scal, off_slabW, off_slabv, total;
+};
+
+static TtBwdPlan tt_bwd_plan(int64_t B, int64_t G, int nheads) {
+  TtBwdPlan p;
+  p.nT = cdiv(G, TC_M);
+  p.nR = cdiv(B, TC_NT);
+  int64_t s = std::min<int64_t>(std::max<int64_t>(1, 148 / p.nT), p.nR);
+  p.tiles_per_split = (int)cdiv(p.nR, s);
+  p.splits = (int)cdiv(p.nR, p.tiles_per_split);
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  p.off_packed = 0;
+  p.off_gconst = al((size_t)p.nT * nheads * 2 * TC_OPER_BYTES);
+  p.off_hpack = al(p.off_gconst + (size_t)p.nT * TC_M * TC_GC * sizeof(float));
+  p.off_scal = al(p.off_hpack + (size_t)p.nR * TC_H32_STAGE_BYTES);
+  p.off_slabW = al(p.off_scal + 256);
+  p.off_slabv = al(p.off_slabW + (size_t)p.splits * nheads * G * TC_H * sizeof(float));
+  p.total = al(p.off_slabv + (size_t)p.splits * 3 * G * sizeof(float));
+  return p;
+}
+
+int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood) {
+  return (int64_t)tt_bwd_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
+}
+
+template <bool ZINB>
+static int tt_launch_k3(const TtBwdPlan& p, int64_t B, int64_t G, const uint8_t* packed, const float* gconst,
+                        const uint8_t* hpack, const float* scal, const float* x, int64_t ldx, float* slabW,
+                        float* slabv, cudaStream_t st) {
+  auto k = tc_dw_kernel<ZINB>;
+  constexpr int smem = (int)K3Smem<ZINB>::TOTAL + 128;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) {
+      set_error("tc_dw: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+      return SCVI_ECUDA;
+    }
+    attr = true;
+  }
+  dim3 grid((unsigned)p.nT, (unsigned)p.splits);
+  k<<<grid, TT_THREADS, smem, st>>>(B, G, packed, gconst, hpack, scal, x, ldx, p.tiles_per_split, 1e-8f, slabW, slabv);
+  return SCVI_OK;
+}
+
+// weight-gradient half of the decoder backward on the tensor cores (H == 128)
+int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
+                          const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                          const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
+                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, cudaStream_t st) {
+  const bool zinb = likelihood == SCVI_LIK_ZINB;
+  const int nheads = zinb ? 2 : 1;
+  SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): ws must be 256-byte aligned");
+  SCVI_REQUIRE(ldh % 4 == 0 && ((uintptr_t)h % 16 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): h must be 16-byte aligned");
+  const TtBwdPlan p = tt_bwd_plan(B, G, nheads);
+  uint8_t* w8 = (uint8_t*)ws;
+  __half* packed = (__half*)(w8 + p.off_packed);
+  float* gconst = (float*)(w8 + p.off_gconst);
+  uint8_t* hpack = w8 + p.off_hpack;
+  unsigned int* scal = (unsigned int*)(w8 + p.off_scal);
+  float* slabW = (float*)(w8 + p.off_slabW);
+  float* slabv = (float*)(w8 + p.off_slabv);
+  cudaError_t ce = cudaMemsetAsync(scal, 0, 8, st);
+  if (ce != cudaSuccess) {
+    set_error("scvi_decoder_nll_bwd: cudaMemsetAsync failed: %s", cudaGetErrorString(ce));
+    return SCVI_ECUDA;
+  }
+  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
+  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack W)");
+  tc_pack_h32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(h, ldh, B, row_stats, g_reconst, row_idx, hpack, scal);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack h)");
+  int rc = zinb ? tt_launch_k3<true>(p, B, G, (const uint8_t*)packed, gconst, hpack, (const float*)scal, x, ldx, slabW, slabv, st)
+                : tt_launch_k3<false>(p, B, G, (const uint8_t*)packed, gconst, hpack, (const float*)scal, x, ldx, slabW, slabv, st);
+  if (rc) return rc;
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc dW)");
+  const int64_t GH = G * TC_H;
+  tt_bwd_reduce_kernel<<<(unsigned)cdiv(std::max<int64_t>(GH / 4, G), 256), 256, 0, st>>>(slabW, slabv, p.splits, nheads, GH, G, dWs, dWp, dbs, dbp, dpx_r);
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc reduce)");
+  return SCVI_OK;
+}
+
+}  // namespace scvi
