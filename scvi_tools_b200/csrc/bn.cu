@@ -26,26 +26,49 @@ __global__ void bn_partials_kernel(const float* __restrict__ y, int64_t ldy, int
   part[((int64_t)blockIdx.x * 2 + 1) * N + n] = m2;
 }
 
-__global__ void bn_finalize_kernel(const float* __restrict__ part, int64_t B, int64_t N, int training, float eps,
-                                   float momentum, float* __restrict__ run_mean, float* __restrict__ run_var,
-                                   float* __restrict__ mean_out, float* __restrict__ rstd_out) {
-  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
+// 32 column lanes x 32 tile groups per block: each thread merges its tiles serially (Chan), thread row 0
+// then merges the 32 group results in fixed order.
+__global__ void __launch_bounds__(1024)
+    bn_finalize_kernel(const float* __restrict__ part, int64_t B, int64_t N, int training, float eps,
+                       float momentum, float* __restrict__ run_mean, float* __restrict__ run_var,
+                       float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  __shared__ float s_cnt[32][33], s_mean[32][33], s_m2[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int64_t n = (int64_t)blockIdx.x * 32 + tx;
   if (!training) {
-    mean_out[n] = run_mean[n];
-    rstd_out[n] = 1.f / sqrtf(run_var[n] + eps);
+    if (ty == 0 && n < N) {
+      mean_out[n] = run_mean[n];
+      rstd_out[n] = 1.f / sqrtf(run_var[n] + eps);
+    }
     return;
   }
   const int64_t T = (B + SCVI_BN_TILE - 1) / SCVI_BN_TILE;
   float cnt = 0.f, mean = 0.f, m2 = 0.f;
-  for (int64_t t = 0; t < T; ++t) {
-    const float cb = (float)min((int64_t)SCVI_BN_TILE, B - t * SCVI_BN_TILE);
-    const float mb = part[(t * 2 + 0) * N + n];
-    const float m2b = part[(t * 2 + 1) * N + n];
+  if (n < N) {
+    for (int64_t t = ty; t < T; t += 32) {
+      const float cb = (float)min((int64_t)SCVI_BN_TILE, B - t * SCVI_BN_TILE);
+      const float mb = part[(t * 2 + 0) * N + n];
+      const float m2b = part[(t * 2 + 1) * N + n];
+      const float tot = cnt + cb;
+      const float delta = mb - mean;
+      mean += delta * (cb / tot);
+      m2 += m2b + delta * delta * (cnt * cb / tot);
+      cnt = tot;
+    }
+  }
+  s_cnt[ty][tx] = cnt;
+  s_mean[ty][tx] = mean;
+  s_m2[ty][tx] = m2;
+  __syncthreads();
+  if (ty != 0 || n >= N) return;
+  cnt = 0.f; mean = 0.f; m2 = 0.f;
+  for (int g = 0; g < 32; ++g) {
+    const float cb = s_cnt[g][tx];
+    if (cb == 0.f) continue;
     const float tot = cnt + cb;
-    const float delta = mb - mean;
+    const float delta = s_mean[g][tx] - mean;
     mean += delta * (cb / tot);
-    m2 += m2b + delta * delta * (cnt * cb / tot);
+    m2 += s_m2[g][tx] + delta * delta * (cnt * cb / tot);
     cnt = tot;
   }
   const float var_b = m2 / cnt;
@@ -104,21 +127,6 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ da, int64_t ldda,
   part[((int64_t)blockIdx.x * 2 + 1) * N + n] = s2;
 }
 
-__global__ void bn_bwd_sums_kernel(const float* __restrict__ part, int64_t T, int64_t N, float* __restrict__ sums,
-                                   float* __restrict__ dgamma, float* __restrict__ dbeta) {
-  const int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= N) return;
-  float s1 = 0.f, s2 = 0.f;
-  for (int64_t t = 0; t < T; ++t) {
-    s1 += part[(t * 2 + 0) * N + n];
-    s2 += part[(t * 2 + 1) * N + n];
-  }
-  sums[n] = s1;
-  sums[N + n] = s2;
-  if (dbeta) dbeta[n] = s1;
-  if (dgamma) dgamma[n] = s2;
-}
-
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y,
                                     int64_t ldy, int64_t B, int64_t N, const float* __restrict__ mean,
                                     const float* __restrict__ rstd, const float* __restrict__ gamma,
@@ -169,7 +177,7 @@ int scvi_bn_finalize(const float* bn_partials, int64_t B, int64_t N, int trainin
   SCVI_REQUIRE(mean && rstd && B > 0 && N > 0, "scvi_bn_finalize: bad argument");
   SCVI_REQUIRE(training ? (bn_partials != nullptr) : (running_mean && running_var),
                "scvi_bn_finalize: missing partials (training) or running buffers (eval)");
-  bn_finalize_kernel<<<(unsigned)cdiv(N, 128), 128, 0, (cudaStream_t)stream>>>(
+  bn_finalize_kernel<<<(unsigned)cdiv(N, 32), 1024, 0, (cudaStream_t)stream>>>(
       bn_partials, B, N, training, eps, momentum, running_mean, running_var, mean, rstd);
   SCVI_LAUNCH_CHECK("scvi_bn_finalize");
   return SCVI_OK;
@@ -210,8 +218,14 @@ int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t 
     bn_bwd_reduce_kernel<<<grid, 64, 0, st>>>(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask,
                                               drop_scale, part);
     SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(reduce)");
-    bn_bwd_sums_kernel<<<(unsigned)cdiv(N, 128), 128, 0, st>>>(part, T, N, sums, dgamma, dbeta);
-    SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(sums)");
+    // sums[0..N) = sum_t du, sums[N..2N) = sum_t du * xhat; the same rows are dbeta / dgamma
+    ColsumSegs segs{};
+    segs.n = 3;
+    segs.dst[0] = sums; segs.begin[0] = 0; segs.end[0] = 2 * N;
+    segs.dst[1] = dbeta; segs.begin[1] = 0; segs.end[1] = N;
+    segs.dst[2] = dgamma; segs.begin[2] = N; segs.end[2] = 2 * N;
+    int rc = launch_colsum(part, T, 2 * N, 2 * N, segs, st, "scvi_bn_act_drop_bwd(sums)");
+    if (rc) return rc;
   }
   const int64_t total = B * N;
   const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(total, 256), 148 * 8);

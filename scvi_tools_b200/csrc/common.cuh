@@ -29,6 +29,22 @@ void set_error(const char* fmt, ...);
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// out[e] = sum_t part[t * stride + e], e < n, in a fixed order (deterministic): 32 column lanes x 32
+// tile groups per block, serial inside a group, then a fixed-order merge of the 32 group sums.
+// The result row is scattered to up to 4 destination segments: dst[i][e - begin[i]] for begin[i] <= e < end[i].
+struct ColsumSegs {
+  float* dst[4];
+  int64_t begin[4], end[4];
+  int n;
+};
+int launch_colsum(const float* part, int64_t T, int64_t stride, int64_t n, const ColsumSegs& segs, cudaStream_t st,
+                  const char* name);
+static inline ColsumSegs colsum_seg1(float* dst, int64_t n) {
+  ColsumSegs s{};
+  s.dst[0] = dst; s.begin[0] = 0; s.end[0] = n; s.n = 1;
+  return s;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(LAT_WARPS * 32)
   }
 }
 
-constexpr int LATB_ROWS = 64;
+constexpr int LATB_ROWS = 16;
 constexpr int LATB_THREADS = 128;
 
 __global__ void __launch_bounds__(LATB_THREADS)
@@ -115,31 +115,6 @@ __global__ void __launch_bounds__(LATB_THREADS)
   }
 }
 
-__global__ void latent_bwd_reduce_kernel(const float* __restrict__ partW, const float* __restrict__ partb,
-                                         int64_t ctas, int H, int L, float* __restrict__ dWm,
-                                         float* __restrict__ dbm, float* __restrict__ dWv, float* __restrict__ dbv) {
-  const int L2 = 2 * L;
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < (int64_t)L2 * H) {
-    float s = 0.f;
-    for (int64_t c = 0; c < ctas; ++c) s += partW[c * L2 * H + e];
-    if (e < (int64_t)L * H) {
-      if (dWm) dWm[e] = s;
-    } else if (dWv) {
-      dWv[e - (int64_t)L * H] = s;
-    }
-  }
-  if (e < L2) {
-    float s = 0.f;
-    for (int64_t c = 0; c < ctas; ++c) s += partb[c * L2 + e];
-    if (e < L) {
-      if (dbm) dbm[e] = s;
-    } else if (dbv) {
-      dbv[e - L] = s;
-    }
-  }
-}
-
 }  // namespace scvi
 
 extern "C" {
@@ -186,8 +161,18 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   cudaStream_t st = (cudaStream_t)stream;
   latent_bwd_kernel<<<(unsigned)ctas, LATB_THREADS, smem, st>>>(a, lda, B, (int)H, (int)L, Wm, Wv, noise, var_eps, q_m, q_v, g_qm, g_qv, g_z, g_kl, da, ldda, partW, partb);
   SCVI_LAUNCH_CHECK("scvi_latent_bwd");
-  latent_bwd_reduce_kernel<<<(unsigned)cdiv(2 * L * H, 256), 256, 0, st>>>(partW, partb, ctas, (int)H, (int)L, dWm, dbm, dWv, dbv);
-  SCVI_LAUNCH_CHECK("scvi_latent_bwd(reduce)");
+  {
+    ColsumSegs segs{};
+    segs.n = 2;
+    segs.dst[0] = dWm; segs.begin[0] = 0; segs.end[0] = L * H;
+    segs.dst[1] = dWv; segs.begin[1] = L * H; segs.end[1] = 2 * L * H;
+    int rc = launch_colsum(partW, ctas, 2 * L * H, 2 * L * H, segs, st, "scvi_latent_bwd(reduce W)");
+    if (rc) return rc;
+    segs.dst[0] = dbm; segs.end[0] = L;
+    segs.dst[1] = dbv; segs.begin[1] = L; segs.end[1] = 2 * L;
+    rc = launch_colsum(partb, ctas, 2 * L, 2 * L, segs, st, "scvi_latent_bwd(reduce b)");
+    if (rc) return rc;
+  }
   return SCVI_OK;
 }
 }

@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(LTHREADS)
 // covariate columns + bias: per row-chunk partial of
 //   extra[c, n] = sum_{b : some cov_cols[b,.] == K + c} dy[b, n],   extra[n_extra, n] = sum_b dy[b, n]
 // one thread per output column n (no conflicts), rows in chunks of COV_ROWS.
-constexpr int COV_ROWS = 256;
+constexpr int COV_ROWS = 32;
 __global__ void linear_dcov_kernel(const float* __restrict__ dy, int64_t lddy, int64_t B, int64_t K, int64_t N,
                                    const int32_t* __restrict__ cov_cols, int n_cov, int n_extra,
                                    float* __restrict__ part /*[chunks][n_extra+1][N]*/) {
@@ -279,29 +279,25 @@ __global__ void linear_dcov_kernel(const float* __restrict__ dy, int64_t lddy, i
   }
 }
 
-// dW[n, k] = sum_s slab[s][n][k]  (fixed order); extra columns / bias from the dcov partials
-__global__ void linear_bwd_reduce_kernel(const float* __restrict__ slabs, int64_t S, int64_t slab_stride,
-                                         int64_t N, int64_t K, int64_t ldw, float* __restrict__ dW) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= N * K) return;
-  const int64_t n = e / K, k = e % K;
-  float s = 0.f;
-  for (int64_t t = 0; t < S; ++t) s += slabs[t * slab_stride + n * K + k];
-  dW[n * ldw + k] = s;
-}
-__global__ void linear_dcov_reduce_kernel(const float* __restrict__ part, int64_t chunks, int n_extra, int64_t N,
-                                          int64_t K, int64_t ldw, float* __restrict__ dW, float* __restrict__ db) {
+// covariate columns / bias from the (column-summed) dcov partials: row [c][n] -> dW[n, K + c] or db[n]
+__global__ void linear_dcov_scatter_kernel(const float* __restrict__ tot, int n_extra, int64_t N, int64_t K,
+                                           int64_t ldw, float* __restrict__ dW, float* __restrict__ db) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= (int64_t)(n_extra + 1) * N) return;
   const int c = (int)(e / N);
   const int64_t n = e % N;
-  float s = 0.f;
-  for (int64_t t = 0; t < chunks; ++t) s += part[(t * (n_extra + 1) + c) * N + n];
   if (c < n_extra) {
-    if (dW) dW[n * ldw + K + c] = s;
+    if (dW) dW[n * ldw + K + c] = tot[e];
   } else if (db) {
-    db[n] = s;
+    db[n] = tot[e];
   }
+}
+// dW[n, k] (row stride ldw) = tot[n * K + k]
+__global__ void linear_dw_scatter_kernel(const float* __restrict__ tot, int64_t N, int64_t K, int64_t ldw,
+                                         float* __restrict__ dW) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= N * K) return;
+  dW[(e / K) * ldw + e % K] = tot[e];
 }
 
 // dx[b, k] = sum_n dy[b, n] * W[n, k]   (k < K)
@@ -396,7 +392,7 @@ int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_co
   using namespace scvi;
   const int64_t S = dw_splits(B, K, N);
   const int64_t n_extra = n_w_cols - K;
-  return 4 * (S * N * K + cdiv(B, COV_ROWS) * (n_extra + 1) * N) + 256;
+  return 4 * (S * N * K + N * K + (cdiv(B, COV_ROWS) + 1) * (n_extra + 1) * N) + 256;
 }
 
 int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
@@ -426,13 +422,21 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
       linear_dw_kernel<false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * K);
     SCVI_LAUNCH_CHECK("scvi_linear_bwd(dW)");
     if (S > 1) {
-      linear_bwd_reduce_kernel<<<(unsigned)cdiv(N * K, 256), 256, 0, st>>>(slabs, S, N * K, N, K, ldw, dW);
-      SCVI_LAUNCH_CHECK("scvi_linear_bwd(reduce)");
+      if (ldw == K) {
+        int rc = launch_colsum(slabs, S, N * K, N * K, colsum_seg1(dW, N * K), st, "scvi_linear_bwd(reduce)");
+        if (rc) return rc;
+      } else {
+        float* tot = slabs + S * N * K;
+        int rc = launch_colsum(slabs, S, N * K, N * K, colsum_seg1(tot, N * K), st, "scvi_linear_bwd(reduce)");
+        if (rc) return rc;
+        linear_dw_scatter_kernel<<<(unsigned)cdiv(N * K, 256), 256, 0, st>>>(tot, N, K, ldw, dW);
+        SCVI_LAUNCH_CHECK("scvi_linear_bwd(scatter)");
+      }
     }
   }
   if ((dW && n_extra > 0) || db) {
     SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_bwd: cov_cols is NULL");
-    float* part = slabs + S * N * K;
+    float* part = slabs + S * N * K + N * K;
     const int64_t chunks = cdiv(B, COV_ROWS);
     const int bt = 128;
     const size_t sm = (size_t)(n_extra + 1) * bt * sizeof(float);
@@ -440,9 +444,12 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
     dim3 grid((unsigned)chunks, (unsigned)cdiv(N, bt));
     linear_dcov_kernel<<<grid, bt, sm, st>>>(dy, lddy, B, K, N, cov_cols, n_cov, n_extra, part);
     SCVI_LAUNCH_CHECK("scvi_linear_bwd(dcov)");
-    linear_dcov_reduce_kernel<<<(unsigned)cdiv((int64_t)(n_extra + 1) * N, 256), 256, 0, st>>>(
-        part, chunks, n_extra, N, K, ldw, dW, db);
-    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dcov reduce)");
+    const int64_t ne = (int64_t)(n_extra + 1) * N;
+    float* tot = part + chunks * ne;
+    int rc = launch_colsum(part, chunks, ne, ne, colsum_seg1(tot, ne), st, "scvi_linear_bwd(dcov reduce)");
+    if (rc) return rc;
+    linear_dcov_scatter_kernel<<<(unsigned)cdiv(ne, 256), 256, 0, st>>>(tot, n_extra, N, K, ldw, dW, db);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dcov scatter)");
   }
   if (dx) {
     dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(K, LT));
