@@ -259,12 +259,13 @@ def time_kernels(plan, a, reps=10):
 
     def k_enc_fwd():
         call("scvi_linear_fwd", _p(X), X.stride(0), _p(plan.idx), B, G, H, _p(P[ENC + "0.weight"]), G,
-             _p(P[ENC + "0.bias"]), None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY, _p(plan.y1), H, _p(plan.library),
-             _p(plan.part1), st)
+             _p(P[ENC + "0.bias"]), None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | plan.enc_tc, _p(plan.y1), H,
+             _p(plan.library), _p(plan.part1), _p(plan.ws_enc), st)
 
     def k_enc_bwd():
         call("scvi_linear_bwd", _p(X), X.stride(0), _p(plan.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
-             _lib.LIN_LOG1P, _p(plan.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0, _p(plan.ws), st)
+             _lib.LIN_LOG1P | plan.enc_tc, _p(plan.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0,
+             _p(plan.ws), st)
 
     def k_gather():
         call("scvi_gather_rows", _p(X), X.shape[0], G, X.stride(0), _p(plan.idx), B, _p(out), G, st)

@@ -41,6 +41,8 @@ extern "C" {
 /* scvi_linear_fwd / _bwd flags */
 #define SCVI_LIN_LOG1P 1   /* input is log1p(x)   (src/scvi/module/_vae.py:373-374) */
 #define SCVI_LIN_LIBRARY 2 /* also emit library = log(sum_g x)  (src/scvi/module/_vae.py:371-372) */
+#define SCVI_LIN_TC 4      /* tcgen05 tensor-core path (error-compensated fp16 split, fp32-grade): needs
+                              N == 128, SCVI_LIN_LOG1P, no covariates, and a workspace */
 
 /* GEMM arithmetic of the fused decoder kernels */
 #define SCVI_PREC_FP32 0   /* FFMA, fp32 everywhere: the parity path */
@@ -100,10 +102,11 @@ int scvi_colsum_partials(const float* partials, int64_t n_tiles, int64_t N, floa
  * f = log1p when SCVI_LIN_LOG1P.  The one-hot concat becomes a weight-column gather:
  * cov_cols[b, c] is the absolute column of W (>= K) selected by covariate c of cell b.
  * bn_partials (nullable) [ceil(B/SCVI_BN_TILE), 2, N] receives per-tile (mean, M2) of y. */
+int64_t scvi_linear_fwd_ws_bytes(int64_t B, int64_t K, int64_t N, int flags); /* 0 unless SCVI_LIN_TC */
 int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols,
                     int n_cov, int flags, float* y, int64_t ldy, float* library, float* bn_partials,
-                    void* stream);
+                    void* ws, void* stream);
 /* backward of the above.  dW [N, ldw] (all K + covariate columns are written: covariate
  * columns receive the per-category column sums of dy -- the one-hot GEMM as a segmented
  * sum), db [N] (nullable), dx [B,K] (nullable; not available with SCVI_LIN_LOG1P).

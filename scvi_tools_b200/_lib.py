@@ -30,7 +30,8 @@ SIGNATURES = {
     "scvi_nb_logprob_bwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, P, P]),
     "scvi_zinb_logprob_bwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, P, P, P]),
     "scvi_colsum_partials": (C.c_int, [P, I64, I64, P, I32, P]),
-    "scvi_linear_fwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, P, P, I32, I32, P, I64, P, P, P]),
+    "scvi_linear_fwd_ws_bytes": (I64, [I64, I64, I64, I32]),
+    "scvi_linear_fwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, P, P, I32, I32, P, I64, P, P, P, P]),
     "scvi_linear_bwd_ws_bytes": (I64, [I64, I64, I64, I64]),
     "scvi_linear_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, I64, P, I32, I32, P, I64, P, P, P, I64, P, P]),
     "scvi_bn_finalize": (C.c_int, [P, I64, I64, I32, F32, F32, P, P, P, P, P]),
@@ -93,5 +94,5 @@ def query(name: str, *args) -> int:
 # constants of include/scvi_b200.h
 BN_TILE = 64
 LIK_NB, LIK_ZINB = 0, 1
-LIN_LOG1P, LIN_LIBRARY = 1, 2
+LIN_LOG1P, LIN_LIBRARY, LIN_TC = 1, 2, 4
 PREC_FP32, PREC_TC = 0, 1

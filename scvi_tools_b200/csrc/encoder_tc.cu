@@ -1,0 +1,540 @@
+// tcgen05 / TMEM kernels of the encoder input layer (SCVI_LIN_TC):
+//
+//   E1  tc_enc_fwd_kernel   y[B,128] = log1p(x) We^T   (CTA = 128 rows x a range of 32-gene K-tiles)
+//       16 converter warps read the minibatch rows straight from the resident count matrix, apply log1p,
+//       split to fp16 hi/lo and stage the A operand in shared memory; We K-tiles arrive pre-packed by bulk
+//       copy; the accumulator stays in TMEM over the whole K loop.  Row sums (library) on the side.
+//   E2  tc_enc_dw_kernel    dWe[128,G] = dy^T log1p(x)  (CTA = 128 genes x a range of 32-row K-tiles)
+//       the same converter pattern stages log1p(x)^T as an MN-major B operand; dy tiles arrive pre-packed
+//       and are used as an MN-major A operand.
+//
+// Replace nn.Linear of the encoder's FCLayers layer 0 and the pre-ops log1p / library
+// (reference src/scvi/nn/_base_components.py:148-188, src/scvi/module/_vae.py:370-374) and their autograd
+// backward.  fp32-grade accuracy through the 3-MMA fp16 split (tc_layout.cuh).
+#include "tc_layout.cuh"
+
+namespace scvi {
+
+constexpr int EN_CONV_WARPS = 16;
+constexpr int EN_THREADS = 32 * (4 + EN_CONV_WARPS);
+constexpr int EN_NS = 4;                          // pipeline stages
+constexpr uint32_t EN_BLK = TC_M * TC_NT * 2;     // 128 x 32 fp16 block = 8 KB
+constexpr int EN_X_SCALE_LOG2 = 11;               // log1p(x) <= 16 -> < 2^15
+
+__device__ __forceinline__ void en_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t a_lbo, uint32_t a_sbo,
+                                        uint32_t a_step, uint32_t b_hi, uint32_t b_lo, uint32_t b_lbo, uint32_t b_sbo,
+                                        uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate) {
+  for (int ks = 0; ks < ksteps; ++ks) {
+    const uint64_t ah = tc::smem_desc(a_hi + ks * a_step, a_lbo, a_sbo);
+    const uint64_t al = tc::smem_desc(a_lo + ks * a_step, a_lbo, a_sbo);
+    const uint64_t bh = tc::smem_desc(b_hi + ks * b_step, b_lbo, b_sbo);
+    const uint64_t bl = tc::smem_desc(b_lo + ks * b_step, b_lbo, b_sbo);
+    tc::mma_f16_ss(d_tmem, ah, bh, idesc, (accumulate || ks > 0) ? 1u : 0u);
+    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1u);
+    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1u);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// pack We fp32 [128, ldw] -> per 32-gene K-tile {hi, lo} blocks, addr(n, kc) = kc * 2048 + n * 16
+// ---------------------------------------------------------------------------------------
+__global__ void tc_pack_we_kernel(const float* __restrict__ W, int64_t ldw, int64_t K, uint8_t* __restrict__ out) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t nKT = (K + TC_NT - 1) / TC_NT;
+  if (e >= nKT * 4 * TC_M) return;
+  const int n = (int)(e % TC_M);
+  const int kc = (int)((e / TC_M) % 4);
+  const int64_t t = e / (4 * TC_M);
+  float v[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const int64_t k = t * TC_NT + 8 * kc + q;
+    v[q] = (k < K) ? fminf(fmaxf(W[n * ldw + k] * TC_SCALE_W, -60000.f), 60000.f) : 0.f;
+  }
+  uint4 hi, lo;
+  tc::split8(v, hi, lo);
+  uint8_t* base = out + t * 2 * EN_BLK;
+  *reinterpret_cast<uint4*>(base + kc * (TC_M * 16) + n * 16) = hi;
+  *reinterpret_cast<uint4*>(base + EN_BLK + kc * (TC_M * 16) + n * 16) = lo;
+}
+
+struct EnSmem {
+  static constexpr uint32_t A = 0;                       // EN_NS x {hi, lo}
+  static constexpr uint32_t W = EN_NS * 2 * EN_BLK;      // EN_NS x {hi, lo}
+  static constexpr uint32_t BARS = 2 * EN_NS * 2 * EN_BLK;
+  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr uint32_t RED = TMEM_PTR + 16;         // [4][128] row-sum partials
+  static constexpr uint32_t TOTAL = RED + 4 * TC_M * 4;
+};
+
+// load 8 consecutive counts of one row (zero beyond G)
+__device__ __forceinline__ void en_load8(const float* __restrict__ xrow, int64_t gb, int64_t G, bool rvalid, int xvec,
+                                         float (&v)[8]) {
+  if (rvalid && xvec) {
+    const float4 a = (gb < G) ? ld_stream4(xrow + gb) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 b = (gb + 4 < G) ? ld_stream4(xrow + gb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = (rvalid && gb + i < G) ? __ldg(xrow + gb + i) : 0.f;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// E1: forward
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(EN_THREADS, 1)
+    tc_enc_fwd_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+                      int64_t G, const uint8_t* __restrict__ wpack, int tiles_per_split, int log1p_in, int xvec,
+                      float* __restrict__ ypart /*[nsplit][B][128]*/, float* __restrict__ rowsum_part /*[nsplit][B]*/) {
+  using L = EnSmem;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *wfull = bars, *afull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+  float* s_red = reinterpret_cast<float*>(smem + L::RED);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = (int64_t)blockIdx.x * TC_M;
+  const int valid = (int)min((int64_t)TC_M, B - r0);
+  const int nKT = (int)((G + TC_NT - 1) / TC_NT);
+  const int t0 = blockIdx.y * tiles_per_split;
+  const int ntiles = max(0, min(nKT, t0 + tiles_per_split) - t0);
+
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < EN_NS; ++i) {
+      tc::mbar_init(&wfull[i], 1);
+      tc::mbar_init(&afull[i], EN_CONV_WARPS);
+      tc::mbar_init(&empty[i], 1);
+    }
+    tc::mbar_init(accfull, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 2) tc::tmem_alloc(s_tmem, 128);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j % EN_NS;
+        tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&wfull[s], 2 * EN_BLK);
+        tc::bulk_g2s(smem + L::W + s * 2 * EN_BLK, wpack + (size_t)(t0 + j) * 2 * EN_BLK, 2 * EN_BLK, &wfull[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_H, 0, 0);
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j % EN_NS;
+        tc::mbar_wait(&wfull[s], (j / EN_NS) & 1);
+        tc::mbar_wait(&afull[s], (j / EN_NS) & 1);
+        tc::fence_after_sync();
+        const uint32_t a = tc::smem_u32(smem + L::A + s * 2 * EN_BLK), w = tc::smem_u32(smem + L::W + s * 2 * EN_BLK);
+        en_mma3(tmem_base, a, a + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16,
+                TC_NT / 16, idesc, j > 0);
+        tc::mma_commit(&empty[s]);
+      }
+      tc::mma_commit(accfull);
+    }
+  } else if (warp >= 4) {
+    // ===== converters: thread = (row r, chunk cg of 8 genes inside the 32-gene K-tile)
+    const int q = warp & 3, cg = (warp - 4) >> 2;
+    const int r = 32 * q + lane;
+    const bool rvalid = r < valid;
+    const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
+    const float* xrow = x + grow * ldx;
+    const float sX = tc::pow2i(EN_X_SCALE_LOG2);
+    float rowsum = 0.f;
+    float xn[8];
+    if (ntiles > 0) en_load8(xrow, (int64_t)t0 * TC_NT + 8 * cg, G, rvalid, xvec, xn);
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j % EN_NS;
+      float xc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xc[i] = xn[i];
+      if (j + 1 < ntiles) en_load8(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xn);
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        rowsum += xc[i];
+        v[i] = (log1p_in ? fm::flog(1.f + xc[i]) : xc[i]) * sX;
+        v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
+      }
+      uint4 hi, lo;
+      tc::split8(v, hi, lo);
+      tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+      uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
+      *reinterpret_cast<uint4*>(a) = hi;
+      *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&afull[s]);
+    }
+    s_red[cg * TC_M + r] = rowsum;
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * EN_CONV_WARPS) : "memory");
+    if (cg == 0 && rvalid)
+      rowsum_part[(int64_t)blockIdx.y * B + r0 + r] = (s_red[r] + s_red[TC_M + r]) + (s_red[2 * TC_M + r] + s_red[3 * TC_M + r]);
+    if (ntiles > 0) {
+      tc::mbar_wait(accfull, 0);
+      tc::fence_after_sync();
+    }
+    const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
+    const float k = tc::pow2i(-EN_X_SCALE_LOG2) * (1.f / TC_SCALE_W);
+    float* o = ypart + ((int64_t)blockIdx.y * B + r0 + r) * TC_H + 32 * cg;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      float v[8];
+      if (ntiles > 0) {
+        tc::tmem_ld8(tmem_base + lane_sel + 32 * cg + 8 * c, v);
+        tc::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      }
+      if (rvalid) {
+        *reinterpret_cast<float4*>(o + 8 * c) = make_float4(v[0] * k, v[1] * k, v[2] * k, v[3] * k);
+        *reinterpret_cast<float4*>(o + 8 * c + 4) = make_float4(v[4] * k, v[5] * k, v[6] * k, v[7] * k);
+      }
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, 128);
+}
+
+// y = sum_split ypart + bias; library = log(sum_split rowsum); per-64-row-tile BatchNorm statistics.
+// block = one BN tile (64 rows) x 128 columns, 256 threads: thread (col, half) owns 32 rows of one column.
+__global__ void __launch_bounds__(256)
+    tc_enc_fwd_combine_kernel(const float* __restrict__ ypart, const float* __restrict__ rowsum_part, int nsplit,
+                              int64_t B, const float* __restrict__ bias, float* __restrict__ y, int64_t ldy,
+                              float* __restrict__ library, float* __restrict__ bn_partials) {
+  __shared__ float s_sum[2][TC_H], s_m2[2][TC_H];
+  const int col = threadIdx.x & 127, half = threadIdx.x >> 7;
+  const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
+  const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
+  const float bv = bias ? bias[col] : 0.f;
+  float vals[32];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    const int rr = half * 32 + i;
+    float v = 0.f;
+    if (rr < cnt) {
+      v = bv;
+      for (int sp = 0; sp < nsplit; ++sp) v += ypart[((int64_t)sp * B + r0 + rr) * TC_H + col];
+      y[(r0 + rr) * ldy + col] = v;
+      s += v;
+    }
+    vals[i] = v;
+  }
+  s_sum[half][col] = s;
+  __syncthreads();
+  const float mean = (s_sum[0][col] + s_sum[1][col]) / (float)cnt;
+  float m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i)
+    if (half * 32 + i < cnt) {
+      const float d = vals[i] - mean;
+      m2 = fmaf(d, d, m2);
+    }
+  s_m2[half][col] = m2;
+  __syncthreads();
+  if (half == 0 && bn_partials) {
+    bn_partials[((int64_t)blockIdx.x * 2 + 0) * TC_H + col] = mean;
+    bn_partials[((int64_t)blockIdx.x * 2 + 1) * TC_H + col] = s_m2[0][col] + s_m2[1][col];
+  }
+  if (library && threadIdx.x < cnt) {
+    float t = 0.f;
+    for (int sp = 0; sp < nsplit; ++sp) t += rowsum_part[(int64_t)sp * B + r0 + threadIdx.x];
+    library[r0 + threadIdx.x] = logf(t);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// E2: dWe = dy^T log1p(x)
+// ---------------------------------------------------------------------------------------
+// max |src| over n floats -> *out (as uint bits; out must be zeroed)
+__global__ void tc_absmax_kernel(const float* __restrict__ src, int64_t ld, int64_t B, int N, unsigned int* out) {
+  float m = 0.f;
+  const int64_t total = B * N;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(src[(e / N) * ld + e % N]));
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));
+}
+
+// dy fp32 [B, 128] -> per 32-row tile {hi, lo} blocks, addr(r, kc) = kc * 512 + r * 16, scaled by
+// 2^(14 - ceil(log2(absmax)))
+__global__ void __launch_bounds__(512)
+    tc_pack_rows32_kernel(const float* __restrict__ src, int64_t ld, int64_t B, const float* __restrict__ absmax,
+                          uint8_t* __restrict__ out) {
+  const int64_t t = blockIdx.x;
+  const int r = threadIdx.x & 31, kc = threadIdx.x >> 5;
+  const int64_t b = t * TC_NT + r;
+  const int e = max(-100, min(100, (int)ceilf(log2f(fmaxf(*absmax, 1e-30f)))));
+  const float sc = tc::pow2i(14 - e);
+  float v[8];
+  if (b < B) {
+    const float4 a = *reinterpret_cast<const float4*>(src + b * ld + 8 * kc);
+    const float4 c = *reinterpret_cast<const float4*>(src + b * ld + 8 * kc + 4);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = c.x; v[5] = c.y; v[6] = c.z; v[7] = c.w;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] *= sc;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) v[q] = 0.f;
+  }
+  uint4 hi, lo;
+  tc::split8(v, hi, lo);
+  uint8_t* base = out + t * 2 * TC_BLK32;
+  *reinterpret_cast<uint4*>(base + kc * TC_NT * 16 + r * 16) = hi;
+  *reinterpret_cast<uint4*>(base + TC_BLK32 + kc * TC_NT * 16 + r * 16) = lo;
+}
+
+__global__ void __launch_bounds__(EN_THREADS, 1)
+    tc_enc_dw_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+                     int64_t G, const uint8_t* __restrict__ dypack, const float* __restrict__ absmax,
+                     int tiles_per_split, int log1p_in, int xvec, float* __restrict__ slab /*[nsplit][128][G]*/) {
+  using L = EnSmem;  // A region = dy tiles (bulk copied), W region = converted log1p(x)^T tiles
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *dfull = bars, *xfull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
+  uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t g0 = (int64_t)blockIdx.x * TC_M;
+  const int nR = (int)((B + TC_NT - 1) / TC_NT);
+  const int rt0 = blockIdx.y * tiles_per_split;
+  const int ntiles = max(0, min(nR, rt0 + tiles_per_split) - rt0);
+
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < EN_NS; ++i) {
+      tc::mbar_init(&dfull[i], 1);
+      tc::mbar_init(&xfull[i], EN_CONV_WARPS);
+      tc::mbar_init(&empty[i], 1);
+    }
+    tc::mbar_init(accfull, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 2) tc::tmem_alloc(s_tmem, 128);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem_base = *s_tmem;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j % EN_NS;
+        tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&dfull[s], 2 * TC_BLK32);
+        tc::bulk_g2s(smem + L::A + s * 2 * EN_BLK, dypack + (size_t)(rt0 + j) * 2 * TC_BLK32, 2 * TC_BLK32, &dfull[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && ntiles > 0) {
+      // D[128 hidden, 128 genes] += dy^T (MN-major A) * log1p(x)^T (MN-major B); K = 32 rows per tile
+      constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_M, 1, 1);
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j % EN_NS;
+        tc::mbar_wait(&dfull[s], (j / EN_NS) & 1);
+        tc::mbar_wait(&xfull[s], (j / EN_NS) & 1);
+        tc::fence_after_sync();
+        const uint32_t a = tc::smem_u32(smem + L::A + s * 2 * EN_BLK), b = tc::smem_u32(smem + L::W + s * 2 * EN_BLK);
+        en_mma3(tmem_base, a, a + TC_BLK32, 128, TC_NT * 16, 256, b, b + TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16,
+                idesc, j > 0);
+        tc::mma_commit(&empty[s]);
+      }
+      tc::mma_commit(accfull);
+    }
+  } else if (warp >= 4) {
+    // ===== converters: thread = (row r of the 32-row tile = lane, chunk gc of 8 genes = warp - 4)
+    const int gc = warp - 4;
+    const int64_t gb = g0 + 8 * gc;
+    const float sX = tc::pow2i(EN_X_SCALE_LOG2);
+    auto row_id = [&](int j) -> int64_t {  // -1 = padded row
+      const int64_t b = (int64_t)(rt0 + j) * TC_NT + lane;
+      return (j < ntiles && b < B) ? (row_idx ? row_idx[b] : b) : -1;
+    };
+    float xn[8];
+    int64_t rid1 = row_id(1);        // row of tile j + 1 (register-prefetched next)
+    if (ntiles > 0) {
+      const int64_t rid0 = row_id(0);
+      en_load8(x + (rid0 < 0 ? 0 : rid0) * ldx, gb, G, rid0 >= 0, xvec, xn);
+    }
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j % EN_NS;
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = xn[i];
+      if (j + 1 < ntiles) en_load8(x + (rid1 < 0 ? 0 : rid1) * ldx, gb, G, rid1 >= 0, xvec, xn);
+      rid1 = row_id(j + 2);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        v[i] = (log1p_in ? fm::flog(1.f + v[i]) : v[i]) * sX;
+        v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
+      }
+      uint4 hi, lo;
+      tc::split8(v, hi, lo);
+      tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+      uint8_t* o = smem + L::W + s * 2 * EN_BLK + gc * (TC_NT * 16) + lane * 16;
+      *reinterpret_cast<uint4*>(o) = hi;
+      *reinterpret_cast<uint4*>(o + TC_BLK32) = lo;
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&xfull[s]);
+    }
+    if (ntiles > 0) {
+      tc::mbar_wait(accfull, 0);
+      tc::fence_after_sync();
+    }
+    // epilogue: thread = (hidden n = 32 * (warp % 4) + lane, gene group cg of 32 genes)
+    const int q = warp & 3, cg = (warp - 4) >> 2;
+    const int n = 32 * q + lane;
+    const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
+    const int e = max(-100, min(100, (int)ceilf(log2f(fmaxf(*absmax, 1e-30f)))));
+    const float k = tc::pow2i(e - 14) * tc::pow2i(-EN_X_SCALE_LOG2);
+    float* o = slab + ((int64_t)blockIdx.y * TC_M + n) * G + g0 + 32 * cg;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      float v[8];
+      if (ntiles > 0) {
+        tc::tmem_ld8(tmem_base + lane_sel + 32 * cg + 8 * c, v);
+        tc::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (g0 + 32 * cg + 8 * c + i < G) o[8 * c + i] = v[i] * k;
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, 128);
+}
+
+// ---------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------
+struct EnFwdPlan {
+  int64_t nKT, rowtiles;
+  int nsplit, tiles_per_split;
+  size_t off_w, off_y, off_rs, total;
+};
+static EnFwdPlan en_fwd_plan(int64_t B, int64_t K) {
+  EnFwdPlan p;
+  p.nKT = cdiv(K, TC_NT);
+  p.rowtiles = cdiv(B, TC_M);
+  int64_t ns = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), std::max<int64_t>(1, p.nKT / 4));
+  p.tiles_per_split = (int)cdiv(p.nKT, ns);
+  p.nsplit = (int)cdiv(p.nKT, p.tiles_per_split);
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  p.off_w = 0;
+  p.off_y = al((size_t)p.nKT * 2 * EN_BLK);
+  p.off_rs = al(p.off_y + (size_t)p.nsplit * B * TC_H * sizeof(float));
+  p.total = al(p.off_rs + (size_t)p.nsplit * B * sizeof(float));
+  return p;
+}
+int64_t tc_enc_fwd_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_fwd_plan(B, K).total; }
+
+static int en_set_smem(const void* fn, const char* name) {
+  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EnSmem::TOTAL + 128);
+  if (e != cudaSuccess) {
+    set_error("%s: cannot reserve shared memory: %s", name, cudaGetErrorString(e));
+    return SCVI_ECUDA;
+  }
+  return SCVI_OK;
+}
+
+int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
+               const float* bias, int flags, float* y, int64_t ldy, float* library, float* bn_partials, void* ws,
+               cudaStream_t st) {
+  SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_linear_fwd(SCVI_LIN_TC): ws must be 256-byte aligned");
+  const EnFwdPlan p = en_fwd_plan(B, K);
+  uint8_t* w8 = (uint8_t*)ws;
+  uint8_t* wpack = w8 + p.off_w;
+  float* ypart = (float*)(w8 + p.off_y);
+  float* rs = (float*)(w8 + p.off_rs);
+  tc_pack_we_kernel<<<(unsigned)cdiv(p.nKT * 4 * TC_M, 256), 256, 0, st>>>(W, ldw, K, wpack);
+  SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc pack)");
+  static bool attr = false;
+  if (!attr) {
+    int rc = en_set_smem((const void*)tc_enc_fwd_kernel, "scvi_linear_fwd");
+    if (rc) return rc;
+    attr = true;
+  }
+  const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
+  dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
+  tc_enc_fwd_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
+                                                                 (flags & SCVI_LIN_LOG1P) ? 1 : 0, xvec, ypart, rs);
+  SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc)");
+  tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 256, 0, st>>>(
+      ypart, rs, p.nsplit, B, bias, y, ldy, (flags & SCVI_LIN_LIBRARY) ? library : nullptr, bn_partials);
+  SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc combine)");
+  return SCVI_OK;
+}
+
+struct EnDwPlan {
+  int64_t nT, nR;
+  int nsplit, tiles_per_split;
+  size_t off_dy, off_scal, off_slab, total;
+};
+static EnDwPlan en_dw_plan(int64_t B, int64_t K) {
+  EnDwPlan p;
+  p.nT = cdiv(K, TC_M);
+  p.nR = cdiv(B, TC_NT);
+  int64_t ns = std::min<int64_t>(std::max<int64_t>(1, 148 / p.nT), std::max<int64_t>(1, p.nR / 4));
+  p.tiles_per_split = (int)cdiv(p.nR, ns);
+  p.nsplit = (int)cdiv(p.nR, p.tiles_per_split);
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  p.off_dy = 0;
+  p.off_scal = al((size_t)p.nR * 2 * TC_BLK32);
+  p.off_slab = al(p.off_scal + 256);
+  p.total = al(p.off_slab + (size_t)p.nsplit * TC_M * K * sizeof(float));
+  return p;
+}
+int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_dw_plan(B, K).total; }
+
+// dW[128, K] (row stride ldw == K) = dy^T f(x)
+int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
+              int flags, float* dW, void* ws, cudaStream_t st) {
+  SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_linear_bwd(SCVI_LIN_TC): ws must be 256-byte aligned");
+  SCVI_REQUIRE(lddy % 4 == 0 && ((uintptr_t)dy % 16 == 0), "scvi_linear_bwd(SCVI_LIN_TC): dy must be 16-byte aligned");
+  const EnDwPlan p = en_dw_plan(B, K);
+  uint8_t* w8 = (uint8_t*)ws;
+  uint8_t* dypack = w8 + p.off_dy;
+  unsigned int* scal = (unsigned int*)(w8 + p.off_scal);
+  float* slab = (float*)(w8 + p.off_slab);
+  cudaError_t ce = cudaMemsetAsync(scal, 0, 4, st);
+  if (ce != cudaSuccess) {
+    set_error("scvi_linear_bwd: cudaMemsetAsync failed: %s", cudaGetErrorString(ce));
+    return SCVI_ECUDA;
+  }
+  tc_absmax_kernel<<<148, 256, 0, st>>>(dy, lddy, B, TC_H, scal);
+  SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc absmax)");
+  tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, (const float*)scal, dypack);
+  SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc pack)");
+  static bool attr = false;
+  if (!attr) {
+    int rc = en_set_smem((const void*)tc_enc_dw_kernel, "scvi_linear_bwd");
+    if (rc) return rc;
+    attr = true;
+  }
+  const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
+  dim3 grid((unsigned)p.nT, (unsigned)p.nsplit);
+  tc_enc_dw_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, (const float*)scal,
+                                                                p.tiles_per_split, (flags & SCVI_LIN_LOG1P) ? 1 : 0,
+                                                                xvec, slab);
+  SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc dW)");
+  return launch_colsum(slab, p.nsplit, TC_M * K, TC_M * K, colsum_seg1(dW, TC_M * K), st, "scvi_linear_bwd(tc reduce)");
+}
+
+}  // namespace scvi

@@ -364,19 +364,37 @@ static int64_t dw_splits(int64_t B, int64_t K, int64_t N) {
   return std::max<int64_t>(1, std::min<int64_t>(s, 64));
 }
 
+int64_t tc_enc_fwd_ws_bytes(int64_t B, int64_t K);
+int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
+               const float* bias, int flags, float* y, int64_t ldy, float* library, float* bn_partials, void* ws,
+               cudaStream_t st);
+int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K);
+int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
+              int flags, float* dW, void* ws, cudaStream_t st);
 }  // namespace scvi
 
 extern "C" {
 
+int64_t scvi_linear_fwd_ws_bytes(int64_t B, int64_t K, int64_t N, int flags) {
+  return ((flags & SCVI_LIN_TC) && N == 128) ? scvi::tc_enc_fwd_ws_bytes(B, K) : 0;
+}
+
 int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols, int n_cov, int flags,
-                    float* y, int64_t ldy, float* library, float* bn_partials, void* stream) {
+                    float* y, int64_t ldy, float* library, float* bn_partials, void* ws, void* stream) {
   using namespace scvi;
   SCVI_REQUIRE(x && W && y, "scvi_linear_fwd: NULL pointer");
   SCVI_REQUIRE(B >= 0 && K > 0 && N > 0 && ldx >= K && ldw >= K && ldy >= N, "scvi_linear_fwd: bad shape");
   SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_fwd: n_cov > 0 but cov_cols is NULL");
   SCVI_REQUIRE(!(flags & SCVI_LIN_LIBRARY) || library, "scvi_linear_fwd: SCVI_LIN_LIBRARY needs `library`");
   if (B == 0) return SCVI_OK;
+  if (flags & SCVI_LIN_TC) {
+    if (N != 128 || n_cov != 0 || !(flags & SCVI_LIN_LOG1P) || ldy % 4 != 0) {
+      set_error("scvi_linear_fwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, ldy %% 4 == 0");
+      return SCVI_EUNSUPPORTED;
+    }
+    return tc_enc_fwd(x, ldx, row_idx, B, K, W, ldw, bias, flags, y, ldy, library, bn_partials, ws, (cudaStream_t)stream);
+  }
   const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && (ldw % 4 == 0) && ((uintptr_t)x % 16 == 0) &&
                    ((uintptr_t)W % 16 == 0);
   dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(N, LT));
@@ -392,7 +410,9 @@ int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_co
   using namespace scvi;
   const int64_t S = dw_splits(B, K, N);
   const int64_t n_extra = n_w_cols - K;
-  return 4 * (S * N * K + N * K + (cdiv(B, COV_ROWS) + 1) * (n_extra + 1) * N) + 256;
+  const int64_t cov = 4 * (cdiv(B, COV_ROWS) + 1) * (n_extra + 1) * N + 256;
+  const int64_t ffma = 4 * (S * N * K + N * K) + cov;
+  return N == 128 ? std::max<int64_t>(ffma, tc_enc_dw_ws_bytes(B, K) + cov) : ffma;
 }
 
 int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
@@ -409,7 +429,16 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
   const int n_extra = (int)(n_w_cols - K);
   float* slabs = (float*)ws;
   const int64_t S = dw_splits(B, K, N);
-  if (dW) {
+  const bool tc = (flags & SCVI_LIN_TC) != 0;
+  if (tc && (N != 128 || n_extra != 0 || ldw != K || !(flags & SCVI_LIN_LOG1P))) {
+    set_error("scvi_linear_bwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, contiguous dW");
+    return SCVI_EUNSUPPORTED;
+  }
+  float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * K + N * K;
+  if (dW && tc) {
+    int rc = tc_enc_dw(x, ldx, row_idx, B, K, dy, lddy, flags, dW, ws, st);
+    if (rc) return rc;
+  } else if (dW) {
     const bool vec = (K % 4 == 0) && (N % 4 == 0) && (ldx % 4 == 0) && (lddy % 4 == 0) &&
                      ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0);
     const int64_t rps = cdiv(cdiv(B, S), BB) * BB;
@@ -436,7 +465,6 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
   }
   if ((dW && n_extra > 0) || db) {
     SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_bwd: cov_cols is NULL");
-    float* part = slabs + S * N * K + N * K;
     const int64_t chunks = cdiv(B, COV_ROWS);
     const int bt = 128;
     const size_t sm = (size_t)(n_extra + 1) * bt * sizeof(float);

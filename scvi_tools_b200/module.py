@@ -278,6 +278,7 @@ class VAE(nn.Module):
             dropout_rate=dropout_rate, distribution=latent_distribution, inject_covariates=deeply_inject_covariates,
             use_batch_norm=bn_enc, use_layer_norm=ln_enc, var_activation=var_activation, return_dist=True, **enc_kw,
         )
+        self.z_encoder.encoder.tc_linear = precision == _lib.PREC_TC  # tcgen05 input layer (needs n_hidden == 128)
         # library encoder: present (and in the state_dict) even when the library is observed (_vae.py:255-268)
         self.l_encoder = Encoder(
             n_input_encoder, 1, n_layers=1, n_cat_list=encoder_cat_list, n_hidden=n_hidden, dropout_rate=dropout_rate,

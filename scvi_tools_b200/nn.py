@@ -204,6 +204,9 @@ class FCLayers(nn.Module):
                         off += n_cat
                 cov_cols = torch.cat(cols, dim=1).contiguous()
             flags = _first_flags if i == 0 else 0
+            if (getattr(self, "tc_linear", False) and (flags & _lib.LIN_LOG1P) and lin.out_features == 128
+                    and cov_cols is None and x.dim() == 2):
+                flags |= _lib.LIN_TC  # tcgen05 path of the encoder input layer
             training_bn = bn is not None and self.training
             y, part, lib = ops.FusedLinear.apply(
                 x, lin.weight, lin.bias, cov_cols, n_dense, flags, _row_idx if i == 0 else None, training_bn

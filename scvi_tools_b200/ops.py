@@ -175,8 +175,10 @@ class FusedLinear(torch.autograd.Function):
         T = (B + _lib.BN_TILE - 1) // _lib.BN_TILE
         part = torch.empty(T, 2, N, dtype=torch.float32, device=dev) if want_bn else None
         lib = torch.empty(B, dtype=torch.float32, device=dev) if (flags & _lib.LIN_LIBRARY) else None
+        nws = query("scvi_linear_fwd_ws_bytes", B, n_in, N, flags)
+        ws = _ws(nws, dev) if nws > 0 else None
         call("scvi_linear_fwd", _ptr(x), x.stride(0), _ptr(row_idx), B, n_in, N, _ptr(W), W.stride(0), _ptr(bias),
-             _ptr(cov_cols), n_cov, flags, _ptr(y), N, _ptr(lib), _ptr(part), _stream())
+             _ptr(cov_cols), n_cov, flags, _ptr(y), N, _ptr(lib), _ptr(part), _ptr(ws), _stream())
         ctx.save_for_backward(x, W, cov_cols, row_idx)
         ctx.meta = (n_in, flags, bias is not None)
         outs = (y, part if want_bn else y.new_empty(0), lib.view(B, 1) if lib is not None else y.new_empty(0))

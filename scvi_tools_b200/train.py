@@ -176,6 +176,9 @@ class FusedTrainingPlan:
         self.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
         nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik, self.module.precision)
         self.ws_fwd = torch.empty(int(nf), dtype=torch.uint8, device=dev) if nf > 0 else None
+        self.enc_tc = _lib.LIN_TC if (self.module.precision == _lib.PREC_TC and H == 128) else 0
+        ne = query("scvi_linear_fwd_ws_bytes", B, G, H, _lib.LIN_LOG1P | self.enc_tc)
+        self.ws_enc = torch.empty(int(ne), dtype=torch.uint8, device=dev) if ne > 0 else None
 
     # ------------------------------------------------------------------ the step
     def _forward_backward(self, st):
@@ -191,7 +194,8 @@ class FusedTrainingPlan:
         n = 0
         # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
-             None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY, _p(self.y1), H, _p(self.library), _p(self.part1), st)
+             None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc, _p(self.y1), H, _p(self.library), _p(self.part1),
+             _p(self.ws_enc), st)
         call("scvi_bn_finalize", _p(self.part1), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn1_rm), _p(self.bn1_rv),
              _p(self.mean1), _p(self.rstd1), st)
         drop = self.p_drop > 0
@@ -207,7 +211,7 @@ class FusedTrainingPlan:
         inj = self.nb > 1
         ncols = L + (self.nb if inj else 0)
         call("scvi_linear_fwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, _p(P[DEC + "0.bias"]),
-             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.y2), H, None, _p(self.part2), st)
+             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.y2), H, None, _p(self.part2), None, st)
         call("scvi_bn_finalize", _p(self.part2), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn2_rm), _p(self.bn2_rv),
              _p(self.mean2), _p(self.rstd2), st)
         call("scvi_bn_act_drop_fwd", _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
@@ -248,7 +252,8 @@ class FusedTrainingPlan:
              1.0 / (1.0 - self.p_drop) if drop else 1.0, 1, _p(self.dy1), H, _p(Gd[ENC + "1.weight"]),
              _p(Gd[ENC + "1.bias"]), _p(self.ws), st)
         call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
-             _lib.LIN_LOG1P, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0, _p(self.ws), st)
+             _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0,
+             _p(self.ws), st)
         n += 3 + 6 + 2 + 3 + 4
         self.kernel_launches_per_step = n + 2  # + adam, counter
 
