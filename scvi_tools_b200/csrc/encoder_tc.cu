@@ -38,9 +38,9 @@ __device__ __forceinline__ void en_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t
 // ---------------------------------------------------------------------------------------
 // pack We fp32 [128, ldw] -> per 32-gene K-tile {hi, lo} blocks, addr(n, kc) = kc * 2048 + n * 16
 // ---------------------------------------------------------------------------------------
-__global__ void tc_pack_we_kernel(const float* __restrict__ W, int64_t ldw, int64_t K, uint8_t* __restrict__ out) {
+__global__ void tc_pack_we_kernel(const float* __restrict__ W, int64_t ldw, int64_t K, int64_t nKT,
+                                  uint8_t* __restrict__ out) {
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t nKT = (K + TC_NT - 1) / TC_NT;
   if (e >= nKT * 4 * TC_M) return;
   const int n = (int)(e % TC_M);
   const int kc = (int)((e / TC_M) % 4);
@@ -58,14 +58,22 @@ __global__ void tc_pack_we_kernel(const float* __restrict__ W, int64_t ldw, int6
   *reinterpret_cast<uint4*>(base + EN_BLK + kc * (TC_M * 16) + n * 16) = lo;
 }
 
+// raw fp32 count tiles, gathered row by row with 1-D bulk copies (TMA engine): rows padded by 16 B so the
+// converters' 16-byte shared loads are bank-conflict free
+constexpr uint32_t EN_RAW1_ROW = TC_NT * 4 + 16;          // E1: 128 rows x 32 genes
+constexpr uint32_t EN_RAW1 = TC_M * EN_RAW1_ROW;          // 18 KB
+constexpr uint32_t EN_RAW2_ROW = TC_M * 4 + 16;           // E2: 32 rows x 128 genes
+constexpr uint32_t EN_RAW2 = TC_NT * EN_RAW2_ROW;         // 16.5 KB
 struct EnSmem {
   static constexpr uint32_t A = 0;                       // EN_NS x {hi, lo}
   static constexpr uint32_t W = EN_NS * 2 * EN_BLK;      // EN_NS x {hi, lo}
-  static constexpr uint32_t BARS = 2 * EN_NS * 2 * EN_BLK;
-  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr uint32_t RAW = 2 * EN_NS * 2 * EN_BLK; // EN_NS raw tiles
+  static constexpr uint32_t BARS = RAW + EN_NS * EN_RAW1;
+  static constexpr uint32_t TMEM_PTR = BARS + 32 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;         // [4][128] row-sum partials
   static constexpr uint32_t TOTAL = RED + 4 * TC_M * 4;
 };
+static_assert(EN_RAW2 <= EN_RAW1, "raw stage size");
 
 // load 8 consecutive counts of one row (zero beyond G)
 __device__ __forceinline__ void en_load8(const float* __restrict__ xrow, int64_t gb, int64_t G, bool rvalid, int xvec,
@@ -83,30 +91,48 @@ __device__ __forceinline__ void en_load8(const float* __restrict__ xrow, int64_t
 // ---------------------------------------------------------------------------------------
 // E1: forward
 // ---------------------------------------------------------------------------------------
+// E1 shared memory: 2 stages of {A hi, A lo} and {We hi, We lo} (32-gene K-tiles) + 2 raw chunks of
+// 128 rows x 128 genes fp32 (one 512-byte bulk copy per row: the TMA engine is issue-bound on tiny copies)
+struct En1Smem {
+  static constexpr int NS = 2;
+  static constexpr uint32_t A = 0;
+  static constexpr uint32_t W = NS * 2 * EN_BLK;
+  static constexpr uint32_t RAW = 2 * NS * 2 * EN_BLK;
+  static constexpr uint32_t RAW_ROW = TC_M * 4 + 16;
+  static constexpr uint32_t RAW_BYTES = TC_M * RAW_ROW;  // 66 KB
+  static constexpr uint32_t BARS = RAW + 2 * RAW_BYTES;
+  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr uint32_t RED = TMEM_PTR + 16;
+  static constexpr uint32_t TOTAL = RED + 4 * TC_M * 4;
+};
+
 __global__ void __launch_bounds__(EN_THREADS, 1)
     tc_enc_fwd_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
-                      int64_t G, const uint8_t* __restrict__ wpack, int tiles_per_split, int log1p_in, int xvec,
+                      int64_t G, const uint8_t* __restrict__ wpack, int chunks_per_split, int log1p_in,
                       float* __restrict__ ypart /*[nsplit][B][128]*/, float* __restrict__ rowsum_part /*[nsplit][B]*/) {
-  using L = EnSmem;
+  using L = En1Smem;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
-  uint64_t *wfull = bars, *afull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
+  uint64_t *wfull = bars, *afull = bars + 2, *empty = bars + 4, *rfull = bars + 6, *rempty = bars + 8, *accfull = bars + 10;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
   float* s_red = reinterpret_cast<float*>(smem + L::RED);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t r0 = (int64_t)blockIdx.x * TC_M;
   const int valid = (int)min((int64_t)TC_M, B - r0);
-  const int nKT = (int)((G + TC_NT - 1) / TC_NT);
-  const int t0 = blockIdx.y * tiles_per_split;
-  const int ntiles = max(0, min(nKT, t0 + tiles_per_split) - t0);
+  const int nKC = (int)((G + TC_M - 1) / TC_M);  // 128-gene chunks
+  const int c0 = blockIdx.y * chunks_per_split;
+  const int nchunks = max(0, min(nKC, c0 + chunks_per_split) - c0);
+  const int ntiles = 4 * nchunks;  // 32-gene K-tiles (the packed We covers whole chunks, zero padded)
 
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < EN_NS; ++i) {
+    for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&wfull[i], 1);
       tc::mbar_init(&afull[i], EN_CONV_WARPS);
       tc::mbar_init(&empty[i], 1);
+      tc::mbar_init(&rfull[i], 1);
+      tc::mbar_init(&rempty[i], EN_CONV_WARPS);
     }
     tc::mbar_init(accfull, 1);
     tc::fence_mbar_init();
@@ -118,21 +144,44 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   const uint32_t tmem_base = *s_tmem;
 
   if (warp == 0) {
+    // ===== raw producer: per chunk one 512-byte bulk copy per minibatch row (lane owns rows lane + 32 i)
+    const float* rp[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int rr = lane + 32 * i;
+      rp[i] = (rr < valid) ? x + (row_idx ? row_idx[r0 + rr] : r0 + rr) * ldx : nullptr;
+    }
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c & 1;
+      const int64_t gt = (int64_t)(c0 + c) * TC_M;
+      const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - gt) * 4;
+      if (lane == 0) {
+        tc::mbar_wait(&rempty[s], ((c >> 1) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&rfull[s], (uint32_t)valid * rowbytes);
+      }
+      __syncwarp();
+      uint8_t* dst = smem + L::RAW + s * L::RAW_BYTES;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (rp[i]) tc::bulk_g2s(dst + (lane + 32 * i) * L::RAW_ROW, rp[i] + gt, rowbytes, &rfull[s]);
+    }
+  } else if (warp == 3) {
+    // ===== We producer: one packed 32-gene K-tile per stage
     if (lane == 0) {
       for (int j = 0; j < ntiles; ++j) {
-        const int s = j % EN_NS;
-        tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+        const int s = j & 1;
+        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
         tc::mbar_arrive_expect_tx(&wfull[s], 2 * EN_BLK);
-        tc::bulk_g2s(smem + L::W + s * 2 * EN_BLK, wpack + (size_t)(t0 + j) * 2 * EN_BLK, 2 * EN_BLK, &wfull[s]);
+        tc::bulk_g2s(smem + L::W + s * 2 * EN_BLK, wpack + ((size_t)c0 * 4 + j) * 2 * EN_BLK, 2 * EN_BLK, &wfull[s]);
       }
     }
   } else if (warp == 1) {
     if (lane == 0 && ntiles > 0) {
       constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_H, 0, 0);
       for (int j = 0; j < ntiles; ++j) {
-        const int s = j % EN_NS;
-        tc::mbar_wait(&wfull[s], (j / EN_NS) & 1);
-        tc::mbar_wait(&afull[s], (j / EN_NS) & 1);
+        const int s = j & 1;
+        tc::mbar_wait(&wfull[s], (j >> 1) & 1);
+        tc::mbar_wait(&afull[s], (j >> 1) & 1);
         tc::fence_after_sync();
         const uint32_t a = tc::smem_u32(smem + L::A + s * 2 * EN_BLK), w = tc::smem_u32(smem + L::W + s * 2 * EN_BLK);
         en_mma3(tmem_base, a, a + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16,
@@ -142,38 +191,43 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       tc::mma_commit(accfull);
     }
   } else if (warp >= 4) {
-    // ===== converters: thread = (row r, chunk cg of 8 genes inside the 32-gene K-tile)
+    // ===== converters: thread = (row r, chunk cg of 8 genes inside each 32-gene K-tile)
     const int q = warp & 3, cg = (warp - 4) >> 2;
     const int r = 32 * q + lane;
     const bool rvalid = r < valid;
-    const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
-    const float* xrow = x + grow * ldx;
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
     float rowsum = 0.f;
-    float xn[8];
-    if (ntiles > 0) en_load8(xrow, (int64_t)t0 * TC_NT + 8 * cg, G, rvalid, xvec, xn);
-    for (int j = 0; j < ntiles; ++j) {
-      const int s = j % EN_NS;
-      float xc[8];
+    for (int c = 0; c < nchunks; ++c) {
+      const int rs = c & 1;
+      tc::mbar_wait(&rfull[rs], (c >> 1) & 1);
+      const uint8_t* raw = smem + L::RAW + rs * L::RAW_BYTES + r * L::RAW_ROW + cg * 32;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) xc[i] = xn[i];
-      if (j + 1 < ntiles) en_load8(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xn);
-      float v[8];
+      for (int sub = 0; sub < 4; ++sub) {
+        const int j = 4 * c + sub, s = j & 1;
+        const int64_t gb = (int64_t)(c0 + c) * TC_M + sub * TC_NT + 8 * cg;
+        const float4 x0 = *reinterpret_cast<const float4*>(raw + sub * 128);
+        const float4 x1 = *reinterpret_cast<const float4*>(raw + sub * 128 + 16);
+        float xc[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        float v[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        rowsum += xc[i];
-        v[i] = (log1p_in ? fm::flog(1.f + xc[i]) : xc[i]) * sX;
-        v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
+        for (int i = 0; i < 8; ++i) {
+          xc[i] = (rvalid && gb + i < G) ? xc[i] : 0.f;  // rows / genes beyond the edge were not copied
+          rowsum += xc[i];
+          v[i] = (log1p_in ? fm::flog(1.f + xc[i]) : xc[i]) * sX;
+          v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
+        }
+        uint4 hi, lo;
+        tc::split8(v, hi, lo);
+        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
+        uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
+        *reinterpret_cast<uint4*>(a) = hi;
+        *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
+        tc::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&afull[s]);
       }
-      uint4 hi, lo;
-      tc::split8(v, hi, lo);
-      tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
-      uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
-      *reinterpret_cast<uint4*>(a) = hi;
-      *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
-      tc::fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&afull[s]);
+      if (lane == 0) tc::mbar_arrive(&rempty[rs]);  // raw chunk consumed by this warp
     }
     s_red[cg * TC_M + r] = rowsum;
     asm volatile("bar.sync 1, %0;" ::"n"(32 * EN_CONV_WARPS) : "memory");
@@ -305,6 +359,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *dfull = bars, *xfull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
+  uint64_t *rfull = bars + 4 * EN_NS, *rempty = bars + 5 * EN_NS;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -318,6 +373,8 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       tc::mbar_init(&dfull[i], 1);
       tc::mbar_init(&xfull[i], EN_CONV_WARPS);
       tc::mbar_init(&empty[i], 1);
+      tc::mbar_init(&rfull[i], 1);
+      tc::mbar_init(&rempty[i], EN_CONV_WARPS);
     }
     tc::mbar_init(accfull, 1);
     tc::fence_mbar_init();
@@ -329,13 +386,27 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   const uint32_t tmem_base = *s_tmem;
 
   if (warp == 0) {
-    if (lane == 0) {
-      for (int j = 0; j < ntiles; ++j) {
-        const int s = j % EN_NS;
+    // ===== producer: dy tile (one bulk copy) + the raw count tile (lane = row: one bulk copy each)
+    const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - g0) * 4;
+    auto row_id = [&](int j) -> int64_t {
+      const int64_t b = (int64_t)(rt0 + j) * TC_NT + lane;
+      return (j < ntiles && b < B) ? (row_idx ? row_idx[b] : b) : -1;
+    };
+    int64_t rid = row_id(0);
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j % EN_NS;
+      const int64_t ridn = row_id(j + 1);
+      const int nvalid = (int)min((int64_t)TC_NT, B - (int64_t)(rt0 + j) * TC_NT);
+      if (lane == 0) {
         tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
         tc::mbar_arrive_expect_tx(&dfull[s], 2 * TC_BLK32);
         tc::bulk_g2s(smem + L::A + s * 2 * EN_BLK, dypack + (size_t)(rt0 + j) * 2 * TC_BLK32, 2 * TC_BLK32, &dfull[s]);
+        tc::mbar_wait(&rempty[s], ((j / EN_NS) & 1) ^ 1);
+        tc::mbar_arrive_expect_tx(&rfull[s], (uint32_t)nvalid * rowbytes);
       }
+      __syncwarp();
+      if (rid >= 0) tc::bulk_g2s(smem + L::RAW + s * EN_RAW1 + lane * EN_RAW2_ROW, x + rid * ldx + g0, rowbytes, &rfull[s]);
+      rid = ridn;
     }
   } else if (warp == 1) {
     if (lane == 0 && ntiles > 0) {
@@ -358,26 +429,20 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     const int gc = warp - 4;
     const int64_t gb = g0 + 8 * gc;
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
-    auto row_id = [&](int j) -> int64_t {  // -1 = padded row
-      const int64_t b = (int64_t)(rt0 + j) * TC_NT + lane;
-      return (j < ntiles && b < B) ? (row_idx ? row_idx[b] : b) : -1;
-    };
-    float xn[8];
-    int64_t rid1 = row_id(1);        // row of tile j + 1 (register-prefetched next)
-    if (ntiles > 0) {
-      const int64_t rid0 = row_id(0);
-      en_load8(x + (rid0 < 0 ? 0 : rid0) * ldx, gb, G, rid0 >= 0, xvec, xn);
-    }
     for (int j = 0; j < ntiles; ++j) {
       const int s = j % EN_NS;
-      float v[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) v[i] = xn[i];
-      if (j + 1 < ntiles) en_load8(x + (rid1 < 0 ? 0 : rid1) * ldx, gb, G, rid1 >= 0, xvec, xn);
-      rid1 = row_id(j + 2);
+      const bool rvalid = (int64_t)(rt0 + j) * TC_NT + lane < B;
+      tc::mbar_wait(&rfull[s], (j / EN_NS) & 1);
+      const uint8_t* raw = smem + L::RAW + s * EN_RAW1 + lane * EN_RAW2_ROW + gc * 32;
+      const float4 x0 = *reinterpret_cast<const float4*>(raw);
+      const float4 x1 = *reinterpret_cast<const float4*>(raw + 16);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&rempty[s]);
+      float v[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        v[i] = (log1p_in ? fm::flog(1.f + v[i]) : v[i]) * sX;
+        const float xv = (rvalid && gb + i < G) ? v[i] : 0.f;
+        v[i] = (log1p_in ? fm::flog(1.f + xv) : xv) * sX;
         v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
       }
       uint4 hi, lo;
@@ -425,17 +490,18 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
 // host side
 // ---------------------------------------------------------------------------------------
 struct EnFwdPlan {
-  int64_t nKT, rowtiles;
-  int nsplit, tiles_per_split;
+  int64_t nKT, rowtiles;          // nKT = packed 32-gene K-tiles (whole 128-gene chunks)
+  int nsplit, tiles_per_split;    // split-K in 128-gene chunks
   size_t off_w, off_y, off_rs, total;
 };
 static EnFwdPlan en_fwd_plan(int64_t B, int64_t K) {
   EnFwdPlan p;
-  p.nKT = cdiv(K, TC_NT);
+  const int64_t nKC = cdiv(K, TC_M);
+  p.nKT = 4 * nKC;
   p.rowtiles = cdiv(B, TC_M);
-  int64_t ns = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), std::max<int64_t>(1, p.nKT / 4));
-  p.tiles_per_split = (int)cdiv(p.nKT, ns);
-  p.nsplit = (int)cdiv(p.nKT, p.tiles_per_split);
+  int64_t ns = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), std::max<int64_t>(1, nKC / 2));
+  p.tiles_per_split = (int)cdiv(nKC, ns);
+  p.nsplit = (int)cdiv(nKC, p.tiles_per_split);
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   p.off_w = 0;
   p.off_y = al((size_t)p.nKT * 2 * EN_BLK);
@@ -463,18 +529,20 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
   uint8_t* wpack = w8 + p.off_w;
   float* ypart = (float*)(w8 + p.off_y);
   float* rs = (float*)(w8 + p.off_rs);
-  tc_pack_we_kernel<<<(unsigned)cdiv(p.nKT * 4 * TC_M, 256), 256, 0, st>>>(W, ldw, K, wpack);
+  tc_pack_we_kernel<<<(unsigned)cdiv(p.nKT * 4 * TC_M, 256), 256, 0, st>>>(W, ldw, K, p.nKT, wpack);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc pack)");
   static bool attr = false;
   if (!attr) {
-    int rc = en_set_smem((const void*)tc_enc_fwd_kernel, "scvi_linear_fwd");
-    if (rc) return rc;
+    cudaError_t e = cudaFuncSetAttribute(tc_enc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)En1Smem::TOTAL + 128);
+    if (e != cudaSuccess) {
+      set_error("scvi_linear_fwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
+      return SCVI_ECUDA;
+    }
     attr = true;
   }
-  const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
   dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
-  tc_enc_fwd_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
-                                                                 (flags & SCVI_LIN_LOG1P) ? 1 : 0, xvec, ypart, rs);
+  tc_enc_fwd_kernel<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
+                                                                  (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc)");
   tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 256, 0, st>>>(
       ypart, rs, p.nsplit, B, bias, y, ldy, (flags & SCVI_LIN_LIBRARY) ? library : nullptr, bn_partials);

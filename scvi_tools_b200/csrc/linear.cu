@@ -393,7 +393,9 @@ int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
       set_error("scvi_linear_fwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, ldy %% 4 == 0");
       return SCVI_EUNSUPPORTED;
     }
-    return tc_enc_fwd(x, ldx, row_idx, B, K, W, ldw, bias, flags, y, ldy, library, bn_partials, ws, (cudaStream_t)stream);
+    // the bulk-copy row gather needs 16-byte aligned rows; otherwise the FFMA kernel below does the work
+    if ((K % 4 == 0) && (ldx % 4 == 0) && ((uintptr_t)x % 16 == 0))
+      return tc_enc_fwd(x, ldx, row_idx, B, K, W, ldw, bias, flags, y, ldy, library, bn_partials, ws, (cudaStream_t)stream);
   }
   const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && (ldw % 4 == 0) && ((uintptr_t)x % 16 == 0) &&
                    ((uintptr_t)W % 16 == 0);
@@ -429,11 +431,12 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
   const int n_extra = (int)(n_w_cols - K);
   float* slabs = (float*)ws;
   const int64_t S = dw_splits(B, K, N);
-  const bool tc = (flags & SCVI_LIN_TC) != 0;
+  bool tc = (flags & SCVI_LIN_TC) != 0;
   if (tc && (N != 128 || n_extra != 0 || ldw != K || !(flags & SCVI_LIN_LOG1P))) {
     set_error("scvi_linear_bwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, contiguous dW");
     return SCVI_EUNSUPPORTED;
   }
+  tc = tc && (K % 4 == 0) && (ldx % 4 == 0) && ((uintptr_t)x % 16 == 0) && (lddy % 4 == 0) && ((uintptr_t)dy % 16 == 0);
   float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * K + N * K;
   if (dW && tc) {
     int rc = tc_enc_dw(x, ldx, row_idx, B, K, dy, lddy, flags, dW, ws, st);
