@@ -158,6 +158,34 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
                     const float* g_kl, float* da, int64_t ldda, float* dWm, float* dbm, float* dWv,
                     float* dbv, void* ws, void* stream);
 
+/* ---- a3/a4/a9 fused: the whole [B, n_hidden] middle of the step in a few launches -------------
+ * For the fused training plan (n_hidden == 128, n_latent <= 16, n_latent + n_batch <= 80) these two
+ * calls replace the sequence scvi_bn_finalize, scvi_bn_act_drop_fwd, scvi_latent_fwd, scvi_linear_fwd
+ * (decoder FCLayers layer 0), scvi_bn_finalize, scvi_bn_act_drop_fwd and its mirror in backward; same
+ * math, same reference lines, per-64-row-tile partials merged in fixed order by every CTA.
+ * y1 / bn_partials1: output of scvi_linear_fwd for the encoder layer.  cov_cols: int32 [B], absolute
+ * column of Wd ([H, n_w_cols]) selected by the batch covariate (NULL = none).
+ * ws: scvi_mid_ws_bytes() bytes, the SAME buffer for the forward and the backward of one step. */
+int64_t scvi_mid_ws_bytes(int64_t B, int64_t L, int64_t n_w_cols);
+int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t H, int64_t L, const float* gamma1,
+                 const float* beta1, float* running_mean1, float* running_var1, const uint8_t* drop_mask,
+                 float drop_scale, const float* noise, const float* Wm, const float* bm, const float* Wv,
+                 const float* bv, float var_eps, const float* Wd, int64_t n_w_cols, const float* bd,
+                 const int32_t* cov_cols, const float* gamma2, const float* beta2, float* running_mean2,
+                 float* running_var2, float bn_eps, float momentum, float* a1, float* q_m, float* q_v, float* z,
+                 float* kl, float* y2, float* h, float* mean1, float* rstd1, float* mean2, float* rstd2, void* ws,
+                 void* stream);
+/* dh = d(loss)/d(h); g_kl [B] = d(loss)/d(kl).  Writes dy1 [B,H] (gradient w.r.t. the encoder layer's
+ * pre-BatchNorm output) and every parameter gradient of the middle (any may be NULL). */
+int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const float* rstd2, const float* gamma2,
+                 const float* beta2, const float* z, const float* Wd, int64_t n_w_cols, const int32_t* cov_cols,
+                 const float* g_kl, const float* q_m, const float* q_v, const float* noise, float var_eps,
+                 const float* Wm, const float* Wv, const float* a1, const float* y1, const float* mean1,
+                 const float* rstd1, const float* gamma1, const float* beta1, const uint8_t* drop_mask,
+                 float drop_scale, int64_t B, int64_t H, int64_t L, float* dy1, float* dgamma2, float* dbeta2,
+                 float* dWd, float* dbd, float* dWm, float* dbm, float* dWv, float* dbv, float* dgamma1, float* dbeta1,
+                 float* db_enc, void* ws, void* stream);
+
 /* ---- a5/a6/a7/a8/a9: fused decoder heads + softmax + library scaling + NB/ZINB NLL ----
  * replaces DecoderSCVI.forward's heads (src/scvi/nn/_base_components.py:436-441:
  * px_scale = softmax(Linear(h)), px_dropout = Linear(h), px_rate = exp(library) * px_scale),

@@ -42,6 +42,11 @@ SIGNATURES = {
     "scvi_latent_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, F32, P, P, P, P, P]),
     "scvi_latent_bwd_ws_bytes": (I64, [I64, I64, I64]),
     "scvi_latent_bwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, F32, P, P, P, P, P, P, P, I64, P, P, P, P, P, P]),
+    "scvi_mid_ws_bytes": (I64, [I64, I64, I64]),
+    "scvi_mid_fwd": (C.c_int, [P, P, I64, I64, I64, P, P, P, P, P, F32, P, P, P, P, P, F32, P, I64, P, P, P, P, P, P,
+                               F32, F32, P, P, P, P, P, P, P, P, P, P, P, P, P]),
+    "scvi_mid_bwd": (C.c_int, [P, P, P, P, P, P, P, P, I64, P, P, P, P, P, F32, P, P, P, P, P, P, P, P, P, F32, I64, I64,
+                               I64, P, P, P, P, P, P, P, P, P, P, P, P, P, P]),
     "scvi_decoder_nll_fwd_ws_bytes": (I64, [I64, I64, I64, I32, I32]),
     "scvi_decoder_nll_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, I64, P, P, I32, I32, P, P, P, P, I64, P, P]),
     "scvi_decoder_nll_bwd_ws_bytes": (I64, [I64, I64, I64, I32]),

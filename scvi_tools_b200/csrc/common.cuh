@@ -31,10 +31,10 @@ static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 // out[e] = sum_t part[t * stride + e], e < n, in a fixed order (deterministic): 32 column lanes x 32
 // tile groups per block, serial inside a group, then a fixed-order merge of the 32 group sums.
-// The result row is scattered to up to 4 destination segments: dst[i][e - begin[i]] for begin[i] <= e < end[i].
+// The result row is scattered to up to 8 destination segments: dst[i][e - begin[i]] for begin[i] <= e < end[i].
 struct ColsumSegs {
-  float* dst[4];
-  int64_t begin[4], end[4];
+  float* dst[8];
+  int64_t begin[8], end[8];
   int n;
 };
 int launch_colsum(const float* part, int64_t T, int64_t stride, int64_t n, const ColsumSegs& segs, cudaStream_t st,

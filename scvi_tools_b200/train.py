@@ -174,6 +174,11 @@ class FusedTrainingPlan:
             query("scvi_decoder_nll_bwd_ws_bytes", B, H, G, lik),
         )
         self.ws = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        ncols = L + (self.nb if self.nb > 1 else 0)
+        # fused middle (BN/ReLU/dropout, latent heads + KL, decoder hidden layer and their backward)
+        self.use_mid = H == 128 and L <= 16 and ncols <= 80
+        self.ws_mid = (torch.empty(int(query("scvi_mid_ws_bytes", B, L, ncols)), dtype=torch.uint8, device=dev)
+                       if self.use_mid else None)
         nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik, self.module.precision)
         self.ws_fwd = torch.empty(int(nf), dtype=torch.uint8, device=dev) if nf > 0 else None
         self.enc_tc = _lib.LIN_TC if (self.module.precision == _lib.PREC_TC and H == 128) else 0
@@ -196,26 +201,22 @@ class FusedTrainingPlan:
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
              None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc, _p(self.y1), H, _p(self.library), _p(self.part1),
              _p(self.ws_enc), st)
-        call("scvi_bn_finalize", _p(self.part1), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn1_rm), _p(self.bn1_rv),
-             _p(self.mean1), _p(self.rstd1), st)
         drop = self.p_drop > 0
-        call("scvi_bn_act_drop_fwd", _p(self.y1), H, B, H, _p(self.mean1), _p(self.rstd1), _p(P[ENC + "1.weight"]),
-             _p(P[ENC + "1.bias"]), 1, _p(self.mask) if drop else None, 1.0 / (1.0 - self.p_drop) if drop else 1.0,
-             _p(self.a1), H, st)
-        # ---- latent heads + rsample + KL
-        call("scvi_latent_fwd", _p(self.a1), H, B, H, L, _p(P["z_encoder.mean_encoder.weight"]),
-             _p(P["z_encoder.mean_encoder.bias"]), _p(P["z_encoder.var_encoder.weight"]),
-             _p(P["z_encoder.var_encoder.bias"]), _p(self.noise), self.module.z_encoder.var_eps, _p(self.q_m),
-             _p(self.q_v), _p(self.z), _p(self.kl), st)
-        # ---- decoder layer 0 with the batch covariate as a weight-column gather
+        dscale = 1.0 / (1.0 - self.p_drop) if drop else 1.0
         inj = self.nb > 1
         ncols = L + (self.nb if inj else 0)
-        call("scvi_linear_fwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, _p(P[DEC + "0.bias"]),
-             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.y2), H, None, _p(self.part2), None, st)
-        call("scvi_bn_finalize", _p(self.part2), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn2_rm), _p(self.bn2_rv),
-             _p(self.mean2), _p(self.rstd2), st)
-        call("scvi_bn_act_drop_fwd", _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
-             _p(P[DEC + "1.bias"]), 1, None, 1.0, _p(self.h), H, st)
+        if self.use_mid:
+            call("scvi_mid_fwd", _p(self.y1), _p(self.part1), B, H, L, _p(P[ENC + "1.weight"]), _p(P[ENC + "1.bias"]),
+                 _p(self.bn1_rm), _p(self.bn1_rv), _p(self.mask) if drop else None, dscale, _p(self.noise),
+                 _p(P["z_encoder.mean_encoder.weight"]), _p(P["z_encoder.mean_encoder.bias"]),
+                 _p(P["z_encoder.var_encoder.weight"]), _p(P["z_encoder.var_encoder.bias"]),
+                 self.module.z_encoder.var_eps, _p(P[DEC + "0.weight"]), ncols, _p(P[DEC + "0.bias"]),
+                 _p(self.cov_cols) if inj else None, _p(P[DEC + "1.weight"]), _p(P[DEC + "1.bias"]), _p(self.bn2_rm),
+                 _p(self.bn2_rv), BN_EPS, BN_MOMENTUM, _p(self.a1), _p(self.q_m), _p(self.q_v), _p(self.z), _p(self.kl),
+                 _p(self.y2), _p(self.h), _p(self.mean1), _p(self.rstd1), _p(self.mean2), _p(self.rstd2),
+                 _p(self.ws_mid), st)
+        else:
+            self._middle_forward_unfused(st, B, H, L, drop, dscale, inj, ncols)
         # ---- fused heads + softmax + likelihood
         Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
         Wp = P.get("decoder.px_dropout_decoder.weight")
@@ -236,6 +237,50 @@ class FusedTrainingPlan:
              _p(Gd["px_r"]), _p(self.ws), st)
         n += 3
         self._after_head_grads(st)
+        if self.use_mid:
+            call("scvi_mid_bwd", _p(self.dh), _p(self.y2), _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
+                 _p(P[DEC + "1.bias"]), _p(self.z), _p(P[DEC + "0.weight"]), ncols, _p(self.cov_cols) if inj else None,
+                 _p(self.g_kl), _p(self.q_m), _p(self.q_v), _p(self.noise), self.module.z_encoder.var_eps,
+                 _p(P["z_encoder.mean_encoder.weight"]), _p(P["z_encoder.var_encoder.weight"]), _p(self.a1), _p(self.y1),
+                 _p(self.mean1), _p(self.rstd1), _p(P[ENC + "1.weight"]), _p(P[ENC + "1.bias"]),
+                 _p(self.mask) if drop else None, dscale, B, H, L, _p(self.dy1), _p(Gd[DEC + "1.weight"]),
+                 _p(Gd[DEC + "1.bias"]), _p(Gd[DEC + "0.weight"]), _p(Gd[DEC + "0.bias"]),
+                 _p(Gd["z_encoder.mean_encoder.weight"]), _p(Gd["z_encoder.mean_encoder.bias"]),
+                 _p(Gd["z_encoder.var_encoder.weight"]), _p(Gd["z_encoder.var_encoder.bias"]), _p(Gd[ENC + "1.weight"]),
+                 _p(Gd[ENC + "1.bias"]), _p(Gd[ENC + "0.bias"]), _p(self.ws_mid), st)
+        else:
+            self._middle_backward_unfused(st, B, H, L, drop, dscale, inj, ncols)
+        call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
+             _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
+             None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0, _p(self.ws), st)
+        n += 3 + 6 + 2 + 3 + 4
+        self.kernel_launches_per_step = n + 2  # + adam, counter
+
+    def _middle_forward_unfused(self, st, B, H, L, drop, dscale, inj, ncols):
+        P = self.P
+        call("scvi_bn_finalize", _p(self.part1), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn1_rm), _p(self.bn1_rv),
+             _p(self.mean1), _p(self.rstd1), st)
+        drop = self.p_drop > 0
+        call("scvi_bn_act_drop_fwd", _p(self.y1), H, B, H, _p(self.mean1), _p(self.rstd1), _p(P[ENC + "1.weight"]),
+             _p(P[ENC + "1.bias"]), 1, _p(self.mask) if drop else None, 1.0 / (1.0 - self.p_drop) if drop else 1.0,
+             _p(self.a1), H, st)
+        # ---- latent heads + rsample + KL
+        call("scvi_latent_fwd", _p(self.a1), H, B, H, L, _p(P["z_encoder.mean_encoder.weight"]),
+             _p(P["z_encoder.mean_encoder.bias"]), _p(P["z_encoder.var_encoder.weight"]),
+             _p(P["z_encoder.var_encoder.bias"]), _p(self.noise), self.module.z_encoder.var_eps, _p(self.q_m),
+             _p(self.q_v), _p(self.z), _p(self.kl), st)
+        # ---- decoder layer 0 with the batch covariate as a weight-column gather
+        inj = self.nb > 1
+        ncols = L + (self.nb if inj else 0)
+        call("scvi_linear_fwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, _p(P[DEC + "0.bias"]),
+             _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.y2), H, None, _p(self.part2), None, st)
+        call("scvi_bn_finalize", _p(self.part2), B, H, 1, BN_EPS, BN_MOMENTUM, _p(self.bn2_rm), _p(self.bn2_rv),
+             _p(self.mean2), _p(self.rstd2), st)
+        call("scvi_bn_act_drop_fwd", _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
+             _p(P[DEC + "1.bias"]), 1, None, 1.0, _p(self.h), H, st)
+
+    def _middle_backward_unfused(self, st, B, H, L, drop, dscale, inj, ncols):
+        P, Gd = self.P, self.Gd
         call("scvi_bn_act_drop_bwd", _p(self.dh), H, _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2),
              _p(P[DEC + "1.weight"]), _p(P[DEC + "1.bias"]), 1, None, 1.0, 1, _p(self.dy2), H, _p(Gd[DEC + "1.weight"]),
              _p(Gd[DEC + "1.bias"]), _p(self.ws), st)
@@ -251,11 +296,6 @@ class FusedTrainingPlan:
              _p(P[ENC + "1.weight"]), _p(P[ENC + "1.bias"]), 1, _p(self.mask) if drop else None,
              1.0 / (1.0 - self.p_drop) if drop else 1.0, 1, _p(self.dy1), H, _p(Gd[ENC + "1.weight"]),
              _p(Gd[ENC + "1.bias"]), _p(self.ws), st)
-        call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
-             _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0,
-             _p(self.ws), st)
-        n += 3 + 6 + 2 + 3 + 4
-        self.kernel_launches_per_step = n + 2  # + adam, counter
 
     def _after_head_grads(self, st):
         """Hook between the decoder-head backward and the rest (data-parallel overlap point)."""

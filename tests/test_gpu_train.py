@@ -10,27 +10,31 @@ from tests._golden import load_vae_case, rel_err
 pytestmark = pytest.mark.gpu
 
 
-def _plan_from_case(name, **kw):
+def _plan_from_case(name, precision=0, use_mid=True, **kw):
     import scvi_tools_b200 as S
     from scvi_tools_b200.data import DeviceResidentCounts
     from scvi_tools_b200.train import FusedTrainingPlan
 
     P, inp, out = load_vae_case(name)
     G = P["px_r"].shape[0]
-    m = S.VAE(n_input=G, n_batch=inp["n_batch"], gene_likelihood=inp["likelihood"])
+    m = S.VAE(n_input=G, n_batch=inp["n_batch"], gene_likelihood=inp["likelihood"], precision=precision)
     sd = m.state_dict()
     sd.update({k: v.clone() for k, v in P.items()})
     m.load_state_dict(sd)
     m.train()
     data = DeviceResidentCounts(inp["x"], batch=inp["batch"].reshape(-1), device="cuda:0")
     plan = FusedTrainingPlan(m, data, batch_size=inp["x"].shape[0], n_epochs_kl_warmup=None, max_kl_weight=inp["kl_weight"], **kw)
+    plan.use_mid = plan.use_mid and use_mid
     return plan, m, P, inp, out
 
 
+@pytest.mark.parametrize("variant", ["fp32", "tc", "fp32-unfused-middle"])
 @pytest.mark.parametrize("name", ["c1_zinb", "c1_nb", "ragged_zinb", "onebatch_nb"])
-def test_two_adam_steps_match_reference_trajectory(name):
-    """Parameters after 2 x (fwd, bwd, Adam) == what the reference module + torch.optim.Adam reach."""
-    plan, m, P, inp, out = _plan_from_case(name, use_cuda_graph=False)
+def test_two_adam_steps_match_reference_trajectory(name, variant):
+    """Parameters after 2 x (fwd, bwd, Adam) == what the reference module + torch.optim.Adam reach,
+    for the FFMA kernels, the tcgen05 kernels (decoder + encoder) and the unfused middle sequence."""
+    plan, m, P, inp, out = _plan_from_case(name, precision=1 if variant == "tc" else 0,
+                                           use_mid=variant != "fp32-unfused-middle", use_cuda_graph=False)
     plan.set_epoch(0)
     B = inp["x"].shape[0]
     idx = torch.arange(B, device="cuda:0")
