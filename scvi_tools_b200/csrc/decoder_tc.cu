@@ -17,7 +17,7 @@
 
 namespace scvi {
 
-constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_EPI_WARPS = 16;
 constexpr int TC_THREADS = 32 * (4 + TC_EPI_WARPS);
 
 // ---------------------------------------------------------------------------------------
@@ -77,6 +77,7 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
     if (gconst) {
 #pragma unroll
       for (int q = 0; q < TC_GC; ++q) gconst[e * TC_GC + q] = o[q];
+      gconst[nT * TC_N * TC_GC + e] = o[3];  // contiguous copy of the scale bias for the LSE pass
     }
     if (packed32) {
       float* gc32 = reinterpret_cast<float*>(packed32 + (e / TC_NT) * st32 + (size_t)nheads * 2 * TC_BLK32) + (e % TC_NT) * TC_GC;
@@ -114,8 +115,8 @@ struct TcSmem {
   static constexpr uint32_t STAGE0 = 2 * TC_OPER_BYTES;
   static constexpr uint32_t BARS = STAGE0 + 2 * TC_STAGE_BYTES;  // 8 mbarriers
   static constexpr uint32_t TMEM_PTR = BARS + 8 * 8;
-  static constexpr uint32_t RED = TMEM_PTR + 16;                 // [2 halves][128 rows][2] floats
-  static constexpr uint32_t LGX1 = RED + 2 * TC_M * 2 * 4;       // lgamma(x+1) table
+  static constexpr uint32_t RED = TMEM_PTR + 16;                 // [4 column parts][128 rows][2] floats
+  static constexpr uint32_t LGX1 = RED + 4 * TC_M * 2 * 4;       // lgamma(x+1) table
   static constexpr uint32_t TOTAL = LGX1 + fm::LGX1_TABLE * 4;
 };
 
@@ -169,6 +170,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
   const int t0 = blockIdx.y * tiles_per_split;
   const int t1 = min(nT, t0 + tiles_per_split);
   const int ntiles = max(0, t1 - t0);
+  const float* __restrict__ bias_pad = gconst + (int64_t)nT * TC_N * TC_GC;  // contiguous scale bias
 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < 2; ++i) {
@@ -225,8 +227,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       }
     }
   } else if (warp >= 4) {
-    // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column half)
-    const int q = warp & 3, half = (warp - 4) >> 2;
+    // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column part of 32 genes)
+    const int q = warp & 3, part = (warp - 4) >> 2;
     const int r = 32 * q + lane;
     const bool rvalid = r < valid;
     const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
@@ -259,27 +261,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       tc::mbar_wait(&tfull[buf], (j >> 1) & 1);
       tc::fence_after_sync();
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        const int col0 = 64 * half + 16 * c;
+      for (int c = 0; c < 2; ++c) {
+        const int col0 = 32 * part + 16 * c;
         float sv[16], pv[16];
         tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 0) * TC_N + col0, sv);
         if (NHEADS == 2) tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 1) * TC_N + col0, pv);
         tc::tmem_ld_wait();
         const int64_t gb = g0 + col0;
         if (MODE == 0) {
+          // log2 domain: t = logit * log2(e); running (max, sum 2^(t - max))
           float tm = -INFINITY;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            sv[i] = fmaf(sv[i], TC_RESCALE, gconst[(gb + i) * TC_GC + 3]);
-            if (gb + i < G) tm = fmaxf(tm, sv[i]);
+          for (int k = 0; k < 4; ++k) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bias_pad + gb + 4 * k);  // warp-uniform address
+            sv[4 * k + 0] = fmaf(sv[4 * k + 0], TC_RESCALE * fm::LOG2E, b4.x * fm::LOG2E);
+            sv[4 * k + 1] = fmaf(sv[4 * k + 1], TC_RESCALE * fm::LOG2E, b4.y * fm::LOG2E);
+            sv[4 * k + 2] = fmaf(sv[4 * k + 2], TC_RESCALE * fm::LOG2E, b4.z * fm::LOG2E);
+            sv[4 * k + 3] = fmaf(sv[4 * k + 3], TC_RESCALE * fm::LOG2E, b4.w * fm::LOG2E);
           }
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (gb + i < G) tm = fmaxf(tm, sv[i]);
           if (tm > m_run) {
-            l_run *= expf(m_run - tm);
+            l_run *= fm::ex2(m_run - tm);  // m_run = -inf first time: 2^(-inf) = 0
             m_run = tm;
           }
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            if (gb + i < G) l_run += expf(sv[i] - m_run);
+            if (gb + i < G) l_run += fm::ex2(sv[i] - m_run);
         } else if (rvalid) {
           float xq[16];
           if (xvec) {  // 4 x 16-byte streaming loads (row start and G are multiples of 4 floats)
@@ -311,24 +320,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[buf]);
     }
-    // combine the two column halves of each row and write this split's partial
-    float a0 = MODE == 0 ? m_run : nll, a1 = MODE == 0 ? l_run : S;
-    if (half == 1) {
-      s_red[r * 2 + 0] = a0;
-      s_red[r * 2 + 1] = a1;
-    }
+    // combine the four column parts of each row and write this split's partial
+    float a0 = MODE == 0 ? m_run * fm::LN2 : nll, a1 = MODE == 0 ? l_run : S;  // (max, sumexp) in natural units
+    s_red[(part * TC_M + r) * 2 + 0] = a0;
+    s_red[(part * TC_M + r) * 2 + 1] = a1;
     asm volatile("bar.sync 1, %0;" ::"n"(32 * TC_EPI_WARPS) : "memory");
-    if (half == 0 && rvalid) {
-      const float b0 = s_red[r * 2 + 0], b1 = s_red[r * 2 + 1];
+    if (part == 0 && rvalid) {
       float2 o;
       if (MODE == 0) {
-        const float mn = fmaxf(a0, b0);
+        float mn = a0;
+#pragma unroll
+        for (int p2 = 1; p2 < 4; ++p2) mn = fmaxf(mn, s_red[(p2 * TC_M + r) * 2]);
+        float l = 0.f;
+#pragma unroll
+        for (int p2 = 0; p2 < 4; ++p2) {
+          const float b0 = s_red[(p2 * TC_M + r) * 2], b1 = s_red[(p2 * TC_M + r) * 2 + 1];
+          l += (b0 == -INFINITY) ? 0.f : b1 * expf(b0 - mn);
+        }
         o.x = mn;
-        o.y = (a0 == -INFINITY ? 0.f : a1 * expf(a0 - mn)) + (b0 == -INFINITY ? 0.f : b1 * expf(b0 - mn));
+        o.y = l;
         *reinterpret_cast<float2*>(lse_part + ((int64_t)blockIdx.y * B + r0 + r) * 2) = o;
       } else {
-        o.x = a0 + b0;
-        o.y = a1 + b1;
+        o.x = 0.f;
+        o.y = 0.f;
+#pragma unroll
+        for (int p2 = 0; p2 < 4; ++p2) {
+          o.x += s_red[(p2 * TC_M + r) * 2];
+          o.y += s_red[(p2 * TC_M + r) * 2 + 1];
+        }
         *reinterpret_cast<float2*>(out_part + ((int64_t)blockIdx.y * B + r0 + r) * 2) = o;
       }
     }
@@ -380,7 +399,7 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   p.off_packed = 0;
   p.off_gconst = al(p.off_packed + (size_t)p.nT * nheads * 2 * TC_M * TC_H * sizeof(__half));
-  p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * TC_GC * sizeof(float));
+  p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * (TC_GC + 1) * sizeof(float));
   const int64_t nT32 = cdiv(G, TC_NT);
   int64_t ns2 = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), nT32);
   p.tiles_per_split2 = (int)cdiv(nT32, ns2);

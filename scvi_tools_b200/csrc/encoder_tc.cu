@@ -262,21 +262,21 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
 }
 
 // y = sum_split ypart + bias; library = log(sum_split rowsum); per-64-row-tile BatchNorm statistics.
-// block = one BN tile (64 rows) x 128 columns, 256 threads: thread (col, half) owns 32 rows of one column.
-__global__ void __launch_bounds__(256)
+// block = one BN tile (64 rows) x 128 columns, 512 threads: thread (col, row group) owns 16 rows of one column.
+__global__ void __launch_bounds__(512)
     tc_enc_fwd_combine_kernel(const float* __restrict__ ypart, const float* __restrict__ rowsum_part, int nsplit,
                               int64_t B, const float* __restrict__ bias, float* __restrict__ y, int64_t ldy,
                               float* __restrict__ library, float* __restrict__ bn_partials) {
-  __shared__ float s_sum[2][TC_H], s_m2[2][TC_H];
-  const int col = threadIdx.x & 127, half = threadIdx.x >> 7;
+  __shared__ float s_scr[4][TC_H];
+  const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
   const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
   const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
   const float bv = bias ? bias[col] : 0.f;
-  float vals[32];
+  float vals[16];
   float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < 32; ++i) {
-    const int rr = half * 32 + i;
+  for (int i = 0; i < 16; ++i) {
+    const int rr = rg * 16 + i;
     float v = 0.f;
     if (rr < cnt) {
       v = bv;
@@ -286,21 +286,22 @@ __global__ void __launch_bounds__(256)
     }
     vals[i] = v;
   }
-  s_sum[half][col] = s;
+  s_scr[rg][col] = s;
   __syncthreads();
-  const float mean = (s_sum[0][col] + s_sum[1][col]) / (float)cnt;
+  const float mean = ((s_scr[0][col] + s_scr[1][col]) + (s_scr[2][col] + s_scr[3][col])) / (float)cnt;
+  __syncthreads();
   float m2 = 0.f;
 #pragma unroll
-  for (int i = 0; i < 32; ++i)
-    if (half * 32 + i < cnt) {
+  for (int i = 0; i < 16; ++i)
+    if (rg * 16 + i < cnt) {
       const float d = vals[i] - mean;
       m2 = fmaf(d, d, m2);
     }
-  s_m2[half][col] = m2;
+  s_scr[rg][col] = m2;
   __syncthreads();
-  if (half == 0 && bn_partials) {
+  if (rg == 0 && bn_partials) {
     bn_partials[((int64_t)blockIdx.x * 2 + 0) * TC_H + col] = mean;
-    bn_partials[((int64_t)blockIdx.x * 2 + 1) * TC_H + col] = s_m2[0][col] + s_m2[1][col];
+    bn_partials[((int64_t)blockIdx.x * 2 + 1) * TC_H + col] = (s_scr[0][col] + s_scr[1][col]) + (s_scr[2][col] + s_scr[3][col]);
   }
   if (library && threadIdx.x < cnt) {
     float t = 0.f;
@@ -312,12 +313,16 @@ __global__ void __launch_bounds__(256)
 // ---------------------------------------------------------------------------------------
 // E2: dWe = dy^T log1p(x)
 // ---------------------------------------------------------------------------------------
-// max |src| over n floats -> *out (as uint bits; out must be zeroed)
-__global__ void tc_absmax_kernel(const float* __restrict__ src, int64_t ld, int64_t B, int N, unsigned int* out) {
+// max |src[b, 0..N)| -> *out (as uint bits; out must be zeroed).  N % 4 == 0, rows 16-byte aligned.
+__global__ void __launch_bounds__(256)
+    tc_absmax_kernel(const float* __restrict__ src, int64_t ld, int64_t B, int N, unsigned int* out) {
   float m = 0.f;
-  const int64_t total = B * N;
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x)
-    m = fmaxf(m, fabsf(src[(e / N) * ld + e % N]));
+  const int n4 = N >> 2;
+  const int64_t total = B * n4;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = *reinterpret_cast<const float4*>(src + (e / n4) * ld + 4 * (e % n4));
+    m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+  }
   m = warp_max(m);
   if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));
 }
@@ -544,7 +549,7 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
   tc_enc_fwd_kernel<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
                                                                   (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc)");
-  tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 256, 0, st>>>(
+  tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 512, 0, st>>>(
       ypart, rs, p.nsplit, B, bias, y, ldy, (flags & SCVI_LIN_LIBRARY) ? library : nullptr, bn_partials);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc combine)");
   return SCVI_OK;
@@ -586,7 +591,7 @@ int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, in
     set_error("scvi_linear_bwd: cudaMemsetAsync failed: %s", cudaGetErrorString(ce));
     return SCVI_ECUDA;
   }
-  tc_absmax_kernel<<<148, 256, 0, st>>>(dy, lddy, B, TC_H, scal);
+  tc_absmax_kernel<<<(unsigned)std::min<int64_t>(cdiv(B * (TC_H / 4), 256), 148 * 8), 256, 0, st>>>(dy, lddy, B, TC_H, scal);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc absmax)");
   tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, (const float*)scal, dypack);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc pack)");
