@@ -35,8 +35,8 @@ N_CELLS, N_GENES, N_BATCH, N_HIDDEN, N_LATENT = 1_000_000, 2000, 8, 128, 10
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-size", type=int, default=8192)
     ap.add_argument("--cells", type=int, default=N_CELLS)
@@ -176,125 +176,128 @@ def run_reference_arm(a):
 # GPU arm
 # ----------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+    """Samples SM clocks / throttle reasons during the timed region (NVML every 20 ms; nvidia-smi
+    subprocess every 100 ms if NVML cannot be loaded)."""
 
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.sm, self.mx, self.reasons = index, [], 0.0, set()
+        self._stop_evt = threading.Event()
+        self.nv = self.h = None
+        try:
+            import pynvml as nv
+
+            nv.nvmlInit()
+            self.nv, self.h = nv, nv.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown,
+                         "hw_thermal_slowdown": nv.nvmlClocksEventReasonHwThermalSlowdown,
+                         "sw_thermal_slowdown": nv.nvmlClocksEventReasonSwThermalSlowdown,
+                         "sw_power_cap": nv.nvmlClocksEventReasonSwPowerCap}
+        except Exception:
+            self.nv = None
+
+    def _sample_nvml(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        for name, bit in self.bits.items():
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                              "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+        r = [c.strip() for c in out.strip().split(",")]
+        self.sm.append(float(r[0]))
+        self.mx = max(self.mx, float(r[1]))
+        for name, v in zip(self.NAMES, r[2:6]):
+            if v.lower().startswith("active"):
+                self.reasons.add(name)
 
     def run(self):
         while not self._stop_evt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in out.strip().split(",")])
+                if self.nv is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._stop_evt.wait(0.1)
+            self._stop_evt.wait(0.02 if self.nv is not None else 0.1)
 
     def stop(self):
         self._stop_evt.set()
         self.join(timeout=5)
-        sm, mx, reasons = [], 0.0, set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx = max(mx, float(r[1]))
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            except Exception:
-                pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.mx or None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
-def algorithmic_bytes(a, B):
-    """algorithmic bytes per launch of each kernel (fp32)."""
-    G, H, L = a.genes, N_HIDDEN, N_LATENT
+def algorithmic_bytes(a, B, n_arena):
+    """SURVEY.md section 8(d) / DESIGN.md section 4: algorithmic HBM bytes per launch of the main kernels (fp32
+    operands, every input read once, every output written once), keyed by the launch label."""
+    G, H = a.genes, N_HIDDEN
     heads = 2 if a.likelihood == "zinb" else 1
-    W = heads * (4 * G * H + 4 * G) + 4 * G
+    W = heads * 4 * G * H  # head weights, fp32
     return {
-        "decoder_nll_fwd": B * (4 * G + 4 * H + 4 + 8) + B * (4 + 8) + W,
-        "decoder_nll_bwd": B * (4 * G + 4 * H + 12 + 4 * H) + 2 * W,
-        "encoder_l0_fwd": B * (4 * G + 8) + 4 * G * H + 4 * H + B * (4 * H + 4),
-        "encoder_l0_bwd": B * (4 * G + 8 + 4 * H) + 4 * G * H + 4 * H,
-        "adam": None,  # 28 bytes / parameter, filled by the caller
-        "gather_rows": 2 * 4 * B * G + 8 * B,
+        # K2: x rows + h + (lse, library) in; dh + (reconst, S) out; head weights + 5 per-gene constants in
+        "scvi_decoder_nll_fwd(tc nll+dh)": B * (4 * G + 4 * H + 16) + B * (4 * H + 8) + W + 20 * G,
+        # K1: h + scale-head weights + bias in; (max, sumexp) out
+        "scvi_decoder_nll_fwd(tc lse)": B * (4 * H) + 4 * G * H + 4 * G + 8 * B,
+        # K3: x rows + h + 4 row constants in; head weights in; dW, db, dpx_r out
+        "scvi_decoder_nll_bwd(tc dW)": B * (4 * G + 4 * H + 16) + W + 20 * G + W + heads * 4 * G + 4 * G,
+        # E1: x rows + W in; y + library out
+        "scvi_linear_fwd(tc)": B * (4 * G + 8) + 4 * G * H + B * (4 * H + 4),
+        # E2: x rows + dy in; dW out
+        "scvi_linear_bwd(tc dW)": B * (4 * G + 8 + 4 * H) + 4 * G * H,
+        "scvi_gather_rows": 2 * 4 * B * G + 8 * B,
+        "scvi_adam_step_graph": 28 * n_arena,
     }
 
 
-def time_kernels(plan, a, reps=10):
-    """CUDA-event timing of the individual kernels of the step (eager launches on the current stream,
-    rows gathered at random from the >L2 resident matrix so nothing is cache-resident)."""
+def profile_step(plan, a, reps=20):
+    """Per-kernel durations of the eager step, measured with CUDA events recorded by the library behind
+    every launch (scvi_profile_begin/_end) on the launching stream.  Rows are gathered at random from the
+    resident matrix (> L2) and a delay kernel keeps the launch queue full, so consecutive events bracket
+    one kernel.  Returns {label: {ms, launches_per_step}}."""
     import ctypes as C
 
-    from scvi_tools_b200 import _lib
-    from scvi_tools_b200._lib import call
-    from scvi_tools_b200.train import DEC, ENC, _p
+    from scvi_tools_b200._lib import call, load
 
-    B, G, H = plan.B, plan.G, plan.H
-    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    P, Gd, X = plan.P, plan.Gd, plan.data.X
-    lik = _lib.LIK_ZINB if plan.zinb else _lib.LIK_NB
-    Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
-    Wp, bp = P.get("decoder.px_dropout_decoder.weight"), P.get("decoder.px_dropout_decoder.bias")
-    out = torch.empty(B, G, device=plan.dev)
-
-    def k_dec_fwd():
-        call("scvi_decoder_nll_fwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),
-             X.stride(0), _p(plan.idx), _p(plan.library), lik, plan.module.precision, _p(plan.reconst), _p(plan.stats),
-             _p(plan.g_rec), _p(plan.dh), H, _p(plan.ws_fwd), st)
-
-    def k_dec_bwd():
-        call("scvi_decoder_nll_bwd", _p(plan.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X),
-             X.stride(0), _p(plan.idx), _p(plan.library), _p(plan.stats), _p(plan.g_rec), lik, plan.module.precision,
-             None, H, _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
-             _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
-             _p(Gd["px_r"]), _p(plan.ws), st)
-
-    def k_enc_fwd():
-        call("scvi_linear_fwd", _p(X), X.stride(0), _p(plan.idx), B, G, H, _p(P[ENC + "0.weight"]), G,
-             _p(P[ENC + "0.bias"]), None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | plan.enc_tc, _p(plan.y1), H,
-             _p(plan.library), _p(plan.part1), _p(plan.ws_enc), st)
-
-    def k_enc_bwd():
-        call("scvi_linear_bwd", _p(X), X.stride(0), _p(plan.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
-             _lib.LIN_LOG1P | plan.enc_tc, _p(plan.dy1), H, _p(Gd[ENC + "0.weight"]), _p(Gd[ENC + "0.bias"]), None, 0,
-             _p(plan.ws), st)
-
-    def k_gather():
-        call("scvi_gather_rows", _p(X), X.shape[0], G, X.stride(0), _p(plan.idx), B, _p(out), G, st)
-
-    snap = (plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.step_counter.clone())
-
-    def k_adam():
-        plan._adam(st)
-
-    res = {}
-    ab = algorithmic_bytes(a, B)
-    ab["adam"] = 28 * plan.n_arena
-    for name, fn in (("decoder_nll_fwd", k_dec_fwd), ("decoder_nll_bwd", k_dec_bwd), ("encoder_l0_fwd", k_enc_fwd),
-                     ("encoder_l0_bwd", k_enc_bwd), ("gather_rows", k_gather), ("adam", k_adam)):
-        ts = []
-        for r in range(reps + 2):
-            plan.idx.copy_(torch.randint(0, X.shape[0], (B,), device=plan.dev))
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            fn()
-            e1.record()
-            e1.synchronize()
-            if r >= 2:
-                ts.append(e0.elapsed_time(e1))
-        ms = float(np.mean(ts))
-        res[name] = {"ms": ms, "algorithmic_bytes": ab[name], "GBps": ab[name] / ms / 1e6}
-    for dst, src in zip((plan.p, plan.m, plan.v, plan.step_counter), snap, strict=True):
+    lib = load()
+    X = plan.data.X
+    state = (plan.p, plan.m, plan.v, plan.step_counter, plan.bn1_rm, plan.bn1_rv, plan.bn2_rm, plan.bn2_rv,
+             plan.bn1_nbt, plan.bn2_nbt)
+    snap = [t.clone() for t in state]
+    out = torch.empty(plan.B, plan.G, device=plan.dev)
+    tot, cnt = {}, {}
+    buf = C.create_string_buffer(1 << 16)
+    for r in range(reps + 2):
+        plan.idx.copy_(torch.randint(0, X.shape[0], (plan.B,), device=plan.dev))
+        torch.cuda.synchronize()
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        call("scvi_profile_begin", st, 3000)
+        plan._whole_step()
+        call("scvi_gather_rows", X.data_ptr(), X.shape[0], plan.G, X.stride(0), plan.idx.data_ptr(), plan.B,
+             out.data_ptr(), plan.G, st)
+        n = lib.scvi_profile_end(buf, len(buf))
+        if n < 0:
+            raise RuntimeError("scvi_profile_end: " + lib.scvi_last_error_string().decode())
+        if r < 2:
+            continue
+        for ln in buf.value.decode().splitlines():
+            name, c, ms = ln.split("\t")
+            tot[name] = tot.get(name, 0.0) + float(ms)
+            cnt[name] = cnt.get(name, 0) + int(c)
+    for dst, src in zip(state, snap, strict=True):
         dst.copy_(src)
-    return res
+    return {k: {"ms": tot[k] / cnt[k], "launches_per_step": cnt[k] / reps} for k in tot}
 
 
 def run_b200_arm(a):
@@ -352,6 +355,7 @@ def run_b200_arm(a):
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop()
     loss_end = float(plan.out3[0])
+    launches_per_step = plan.kernel_launches_per_step  # this library's kernels recorded in the step graph
     if world > 1:
         t = torch.tensor([ms], device=dev)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
@@ -418,7 +422,7 @@ def run_b200_arm(a):
         plan.data = data
         plan.batch_cols = (data.batch + plan.L).to(torch.int32)
         plan._graphs = None
-        kern = time_kernels(plan, a)
+        kern = profile_step(plan, a)
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -427,12 +431,29 @@ def run_b200_arm(a):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
         step_ms = ms / K
-        dom = max(("decoder_nll_fwd", "decoder_nll_bwd", "encoder_l0_fwd", "encoder_l0_bwd"), key=lambda k: kern[k]["ms"])
-        roof = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["GBps"], "peak": peak, "unit": "GB/s",
-                "frac": kern[dom]["GBps"] / peak, "traffic": None, "peak_source": peak_src,
-                "share_of_step": kern[dom]["ms"] / step_ms}
-        for k in kern:
-            kern[k]["frac_of_hbm_peak"] = kern[k]["GBps"] / peak
+        ab = algorithmic_bytes(a, B, plan.n_arena)
+        for k, v in kern.items():
+            v["algorithmic_bytes"] = ab.get(k)
+            if ab.get(k):
+                v["GBps"] = ab[k] / v["ms"] / 1e6
+                v["frac_of_hbm_peak"] = v["GBps"] / peak
+        step_kernels = {k: v for k, v in kern.items() if k != "scvi_gather_rows"}
+        dom = max(step_kernels, key=lambda k: step_kernels[k]["ms"] * step_kernels[k]["launches_per_step"])
+        eager_ms = sum(v["ms"] * v["launches_per_step"] for v in step_kernels.values())
+        traffic = None
+        try:  # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
+            tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+            ent = tr.get(dom)
+            if ent and ent["batch_size"] == B and ent["genes"] == a.genes and ent["likelihood"] == a.likelihood:
+                traffic = ent["dram_bytes_per_launch"]
+        except Exception:
+            pass
+        roof = {"bound": "hbm", "kernel": dom, "achieved": kern[dom].get("GBps"), "peak": peak, "unit": "GB/s",
+                "frac": (kern[dom]["GBps"] / peak) if kern[dom].get("GBps") else None, "traffic": traffic,
+                "algorithmic_bytes": kern[dom]["algorithmic_bytes"], "kernel_ms": kern[dom]["ms"],
+                "peak_source": peak_src, "share_of_step": kern[dom]["ms"] * kern[dom]["launches_per_step"] / eager_ms,
+                "note": "HBM is the nearest roofline of the step's streaming kernels; the dominant kernel is limited "
+                        "by SFU/issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4)"}
         cpu = None if a.no_cpu_baseline else cpu_baseline(a, a.cpu_seconds)
         line = {
             "metric": "SCVI train cells/sec", "value": value, "unit": "cells/s", "n_gpus": world, "steps": K,
@@ -444,7 +465,8 @@ def run_b200_arm(a):
                                 f"({a.cells * a.genes * 4 / 1e9:.1f} GB)",
                        "precision": ("tcgen05 fp16 hi/lo split GEMMs, fp32 accumulate (fp32-grade, parity-tested)"
                                      if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": plan.kernel_launches_per_step * K,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
+            "launches_per_step": launches_per_step,
             "roofline": roof, "kernels": kern, "cpu_baseline": cpu, "final_loss": loss_end,
         }
     if world > 1:

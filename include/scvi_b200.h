@@ -48,8 +48,16 @@ extern "C" {
 #define SCVI_PREC_FP32 0   /* FFMA, fp32 everywhere: the parity path */
 #define SCVI_PREC_TC 1     /* tcgen05 tensor-core path (when built) */
 
-int scvi_b200_abi_version(void); /* 2 */
+int scvi_b200_abi_version(void); /* 3 */
 const char* scvi_last_error_string(void);
+/* number of kernels this library has launched (or recorded into a stream capture) since load */
+int64_t scvi_launch_count(void);
+/* Per-kernel event timing of eager launches on `stream` (bench.py's roofline leg; never inside a stream
+ * capture).  _begin queues a `delay_us` spin kernel so the host runs ahead and the kernels execute
+ * back to back; _end synchronises and writes "label\tlaunches\ttotal_ms\n" lines (labels = the names in
+ * this library's launch checks), returning the text length or -1. */
+int scvi_profile_begin(void* stream, int64_t delay_us);
+int64_t scvi_profile_end(char* buf, int64_t cap);
 
 /* ---- a1: minibatch row gather --------------------------------------------------------
  * replaces AnnTorchDataset.__getitem__ (src/scvi/data/_anntorchdataset.py:115-169,
@@ -111,12 +119,15 @@ int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
  * columns receive the per-category column sums of dy -- the one-hot GEMM as a segmented
  * sum), db [N] (nullable), dx [B,K] (nullable; not available with SCVI_LIN_LOG1P).
  * `ws` is a caller-owned workspace of scvi_linear_bwd_ws_bytes() bytes (split-B partial
- * slabs reduced in fixed order: deterministic, no atomics).  n_w_cols = total columns of W. */
+ * slabs reduced in fixed order: deterministic, no atomics).  n_w_cols = total columns of W.
+ * dy_absmax_part (nullable; used by SCVI_LIN_TC): n_absmax_part floats whose maximum is max |dy|
+ * (as produced by scvi_mid_bwd) -- saves the pass over dy that fixes the operand scale. */
 int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols);
 int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov,
                     int flags, const float* dy, int64_t lddy, float* dW, float* db, float* dx,
-                    int64_t lddx, void* ws, void* stream);
+                    int64_t lddx, const float* dy_absmax_part, int64_t n_absmax_part, void* ws,
+                    void* stream);
 
 /* ---- a3: BatchNorm1d(momentum .01, eps 1e-3) + ReLU + Dropout --------------------------
  * replaces nn.BatchNorm1d / nn.ReLU / nn.Dropout of FCLayers._build_layer
@@ -176,7 +187,10 @@ int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t 
                  float* kl, float* y2, float* h, float* mean1, float* rstd1, float* mean2, float* rstd2, void* ws,
                  void* stream);
 /* dh = d(loss)/d(h); g_kl [B] = d(loss)/d(kl).  Writes dy1 [B,H] (gradient w.r.t. the encoder layer's
- * pre-BatchNorm output) and every parameter gradient of the middle (any may be NULL). */
+ * pre-BatchNorm output) and every parameter gradient of the middle (any may be NULL).
+ * dy1_absmax_part (nullable): float[scvi_mid_n_tiles(B)], max |dy1| per row tile -- hand it to
+ * scvi_linear_bwd(SCVI_LIN_TC) to skip that call's own pass over dy. */
+int64_t scvi_mid_n_tiles(int64_t B);
 int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const float* rstd2, const float* gamma2,
                  const float* beta2, const float* z, const float* Wd, int64_t n_w_cols, const int32_t* cov_cols,
                  const float* g_kl, const float* q_m, const float* q_v, const float* noise, float var_eps,
@@ -184,7 +198,7 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
                  const float* rstd1, const float* gamma1, const float* beta1, const uint8_t* drop_mask,
                  float drop_scale, int64_t B, int64_t H, int64_t L, float* dy1, float* dgamma2, float* dbeta2,
                  float* dWd, float* dbd, float* dWm, float* dbm, float* dWv, float* dbv, float* dgamma1, float* dbeta1,
-                 float* db_enc, void* ws, void* stream);
+                 float* db_enc, float* dy1_absmax_part, void* ws, void* stream);
 
 /* ---- a5/a6/a7/a8/a9: fused decoder heads + softmax + library scaling + NB/ZINB NLL ----
  * replaces DecoderSCVI.forward's heads (src/scvi/nn/_base_components.py:436-441:
@@ -211,14 +225,16 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                          int likelihood, int precision, float* reconst, float* row_stats,
                          const float* g_reconst, float* dh, int64_t lddh, void* ws, void* stream);
 /* g_reconst [B] = d(loss)/d(reconst).  Writes dh [B,H], dWs/dWp [G,H], dbs/dbp [G], dpx_r [G].
- * ws: scvi_decoder_nll_bwd_ws_bytes(). */
+ * ws: scvi_decoder_nll_bwd_ws_bytes().  fwd_ws (nullable; SCVI_PREC_TC only): the workspace of the
+ * scvi_decoder_nll_fwd call this backward belongs to (same B, G, likelihood, weights), still intact --
+ * the packed weight tiles in it are reused instead of being rebuilt. */
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
 int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r,
                          const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
                          const float* row_stats, const float* g_reconst, int likelihood, int precision,
                          float* dh, int64_t lddh, float* dWs, float* dbs, float* dWp, float* dbp,
-                         float* dpx_r, void* ws, void* stream);
+                         float* dpx_r, void* ws, const void* fwd_ws, void* stream);
 /* materialising variant for inference-time getters (px.scale / px.mu / px.zi_logits):
  * any of the three outputs may be NULL. */
 int scvi_decoder_params_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
@@ -233,9 +249,9 @@ int scvi_decoder_params_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, i
 int scvi_adam_step(float* p, const float* g, float* m, float* v, int64_t n, int64_t step, float lr,
                    float beta1, float beta2, float eps, float weight_decay, float grad_scale,
                    void* stream);
-/* CUDA-graph friendly variant: the 1-based step is `*step_counter + 1` read on the device; the
- * counter is incremented after the update, so a captured graph replays with the right bias
- * correction every time. */
+/* CUDA-graph friendly variant: the 1-based step is `step_counter[0] + 1` read on the device; the
+ * last block of the update increments it, so a captured graph replays with the right bias
+ * correction every time.  step_counter is int64[2]: {steps done, arrival ticket (keep 0)}. */
 int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, int64_t* step_counter,
                          float lr, float beta1, float beta2, float eps, float weight_decay,
                          float grad_scale, void* stream);
@@ -245,6 +261,21 @@ int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n
  * weight of src/scvi/train/_trainingplans.py:521-532 changes per epoch without re-capture). */
 int scvi_elbo_reduce(const float* reconst, const float* kl, int64_t B, float kl_weight,
                      const float* kl_weight_dev, float* out3, void* stream);
+/* ---- step prologue: everything the minibatch step needs that does not depend on the counts ------
+ * One launch replacing, per step: the nn.Dropout mask of the encoder hidden layer and the rsample
+ * noise (src/scvi/nn/_base_components.py:95-104,286-289), the one-hot batch covariate
+ * (cov_cols[b] = batch_cols[idx[b]], src/scvi/nn/_base_components.py:139-169), the backward seeds
+ * of the ELBO mean (as scvi_elbo_seed) and the BatchNorm num_batches_tracked increments.
+ * mask [B,H] bytes (1 = keep, P(keep) = 1 - p_drop), noise [B,L] ~ N(0,1): Philox4x32-10 keyed by
+ * `seed`, counter = (element, *step_counter, stream_id) -- the device-side step makes a captured CUDA
+ * graph draw fresh numbers at every replay; stream_id (< 65536) separates data-parallel ranks.  These
+ * are this library's own random streams (torch's generator is not reproduced).  Every output pointer is
+ * nullable (skipped). */
+int scvi_step_prologue(uint64_t seed, const int64_t* step_counter, int64_t stream_id, int64_t B, int64_t H,
+                       int64_t L, float p_drop, uint8_t* mask, float* noise, const int64_t* idx,
+                       const int32_t* batch_cols, int32_t* cov_cols, float kl_weight,
+                       const float* kl_weight_dev, float scale, float* g_reconst, float* g_kl,
+                       int64_t* nbt1, int64_t* nbt2, void* stream);
 /* backward seeds of that mean: g_reconst[b] = scale / B, g_kl[b] = scale * kl_weight / B */
 int scvi_elbo_seed(int64_t B, float kl_weight, const float* kl_weight_dev, float scale, float* g_reconst,
                    float* g_kl, void* stream);

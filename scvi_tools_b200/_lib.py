@@ -22,6 +22,9 @@ F32 = C.c_float
 SIGNATURES = {
     "scvi_b200_abi_version": (C.c_int, []),
     "scvi_last_error_string": (C.c_char_p, []),
+    "scvi_launch_count": (C.c_int64, []),
+    "scvi_profile_begin": (C.c_int, [P, I64]),
+    "scvi_profile_end": (C.c_int64, [P, I64]),
     "scvi_gather_rows": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
     "scvi_gather_i64": (C.c_int, [P, I64, P, I64, P, P]),
     "scvi_gather_rows_u16": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
@@ -33,7 +36,7 @@ SIGNATURES = {
     "scvi_linear_fwd_ws_bytes": (I64, [I64, I64, I64, I32]),
     "scvi_linear_fwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, P, P, I32, I32, P, I64, P, P, P, P]),
     "scvi_linear_bwd_ws_bytes": (I64, [I64, I64, I64, I64]),
-    "scvi_linear_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, I64, P, I32, I32, P, I64, P, P, P, I64, P, P]),
+    "scvi_linear_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, I64, P, I32, I32, P, I64, P, P, P, I64, P, I64, P, P]),
     "scvi_bn_finalize": (C.c_int, [P, I64, I64, I32, F32, F32, P, P, P, P, P]),
     "scvi_bn_partials": (C.c_int, [P, I64, I64, I64, P, P]),
     "scvi_bn_act_drop_fwd": (C.c_int, [P, I64, I64, I64, P, P, P, P, I32, P, F32, P, I64, P]),
@@ -46,19 +49,21 @@ SIGNATURES = {
     "scvi_mid_fwd": (C.c_int, [P, P, I64, I64, I64, P, P, P, P, P, F32, P, P, P, P, P, F32, P, I64, P, P, P, P, P, P,
                                F32, F32, P, P, P, P, P, P, P, P, P, P, P, P, P]),
     "scvi_mid_bwd": (C.c_int, [P, P, P, P, P, P, P, P, I64, P, P, P, P, P, F32, P, P, P, P, P, P, P, P, P, F32, I64, I64,
-                               I64, P, P, P, P, P, P, P, P, P, P, P, P, P, P]),
+                               I64, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P]),
+    "scvi_mid_n_tiles": (I64, [I64]),
     "scvi_decoder_nll_fwd_ws_bytes": (I64, [I64, I64, I64, I32, I32]),
     "scvi_decoder_nll_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, I64, P, P, I32, I32, P, P, P, P, I64, P, P]),
     "scvi_decoder_nll_bwd_ws_bytes": (I64, [I64, I64, I64, I32]),
     "scvi_decoder_nll_bwd": (
         C.c_int,
-        [P, I64, I64, I64, I64, P, P, P, P, P, P, I64, P, P, P, P, I32, I32, P, I64, P, P, P, P, P, P, P],
+        [P, I64, I64, I64, I64, P, P, P, P, P, P, I64, P, P, P, P, I32, I32, P, I64, P, P, P, P, P, P, P, P],
     ),
     "scvi_decoder_params_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, P, P, I64, P]),
     "scvi_adam_step": (C.c_int, [P, P, P, P, I64, I64, F32, F32, F32, F32, F32, F32, P]),
     "scvi_adam_step_graph": (C.c_int, [P, P, P, P, I64, P, F32, F32, F32, F32, F32, F32, P]),
     "scvi_elbo_reduce": (C.c_int, [P, P, I64, F32, P, P, P]),
     "scvi_elbo_seed": (C.c_int, [I64, F32, P, F32, P, P, P]),
+    "scvi_step_prologue": (C.c_int, [C.c_uint64, P, I64, I64, I64, I64, F32, P, P, P, P, P, F32, P, F32, P, P, P, P, P]),
 }
 
 _lib = None

@@ -19,10 +19,9 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
 }
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
-                            float* __restrict__ v, int64_t n, const int64_t* __restrict__ step_counter,
-                            int64_t step_host, float lr, float beta1, float beta2, float eps, float wd,
-                            float grad_scale) {
-  const int64_t step = step_counter ? (*step_counter + 1) : step_host;
+                            float* __restrict__ v, int64_t n, int64_t* step_counter, int64_t step_host, float lr,
+                            float beta1, float beta2, float eps, float wd, float grad_scale) {
+  const int64_t step = step_counter ? (*reinterpret_cast<volatile int64_t*>(step_counter) + 1) : step_host;
   const double bc1 = 1.0 - pow((double)beta1, (double)step);
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   const float step_size = (float)((double)lr / bc1);
@@ -44,9 +43,20 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
   for (int64_t i = 4 * n4 + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
     adam_elem(p[i], g[i], m[i], v[i], grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+  // device-side step counter: every block has read it above, so the last block to finish may bump it
+  // (step_counter[1] is the arrival ticket)
+  if (step_counter) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      unsigned long long* ticket = reinterpret_cast<unsigned long long*>(step_counter + 1);
+      if (atomicAdd(ticket, 1ull) == (unsigned long long)gridDim.x - 1) {
+        *ticket = 0ull;
+        step_counter[0] = step;
+      }
+    }
+  }
 }
-
-__global__ void counter_inc_kernel(int64_t* c) { *c += 1; }
 
 // out[0] = mean(reconst + klw * kl), out[1] = sum reconst, out[2] = sum kl  (single block, fixed order)
 __global__ void elbo_reduce_kernel(const float* __restrict__ reconst, const float* __restrict__ kl, int64_t B,
@@ -109,10 +119,6 @@ static int adam_launch(float* p, const float* g, float* m, float* v, int64_t n, 
   const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(cdiv(n, 4), 256), 148 * 8);
   adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(p, g, m, v, n, counter, step, lr, beta1, beta2, eps, wd, grad_scale);
   SCVI_LAUNCH_CHECK(name);
-  if (counter) {
-    counter_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(counter);
-    SCVI_LAUNCH_CHECK(name);
-  }
   return SCVI_OK;
 }
 

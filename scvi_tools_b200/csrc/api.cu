@@ -2,10 +2,50 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+#include <map>
+#include <string>
+#include <vector>
+
 #include "common.cuh"
 
 namespace scvi {
 static thread_local char g_err[512] = "";
+static std::atomic<long long> g_launches{0};
+
+// Per-kernel event profiler (scvi_profile_begin / _end): every launch of this library records an event
+// behind itself on the profiled stream; a delay kernel in front keeps the queue full so consecutive
+// events bracket one kernel's execution.  Not for use during stream capture.
+struct ProfRec {
+  std::string name;
+  cudaEvent_t ev;
+};
+static bool g_prof = false;
+static cudaStream_t g_prof_stream = nullptr;
+static cudaEvent_t g_prof_start = nullptr;
+static std::vector<ProfRec> g_prof_recs;
+
+void count_launch(const char* name) {
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  if (g_prof) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) == cudaSuccess) {
+      cudaEventRecord(e, g_prof_stream);
+      g_prof_recs.push_back({name ? name : "?", e});
+    }
+  }
+}
+
+__global__ void prof_delay_kernel(long long ns) {
+  long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  for (;;) {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (t - t0 >= ns) break;
+    __nanosleep(1000);
+  }
+}
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -60,6 +100,72 @@ int launch_colsum(const float* part, int64_t T, int64_t stride, int64_t n, const
 }  // namespace scvi
 
 extern "C" {
-int scvi_b200_abi_version(void) { return 2; }
+int scvi_b200_abi_version(void) { return 3; }
 const char* scvi_last_error_string(void) { return scvi::g_err; }
+int64_t scvi_launch_count(void) { return (int64_t)scvi::g_launches.load(std::memory_order_relaxed); }
+
+int scvi_profile_begin(void* stream, int64_t delay_us) {
+  using namespace scvi;
+  if (g_prof) {
+    set_error("scvi_profile_begin: a profile is already open");
+    return SCVI_EINVAL;
+  }
+  g_prof_stream = (cudaStream_t)stream;
+  g_prof_recs.clear();
+  if (delay_us > 0) prof_delay_kernel<<<1, 1, 0, g_prof_stream>>>(delay_us * 1000);
+  if (cudaEventCreate(&g_prof_start) != cudaSuccess || cudaEventRecord(g_prof_start, g_prof_stream) != cudaSuccess) {
+    set_error("scvi_profile_begin: %s", cudaGetErrorString(cudaGetLastError()));
+    return SCVI_ECUDA;
+  }
+  g_prof = true;
+  return SCVI_OK;
+}
+
+int64_t scvi_profile_end(char* buf, int64_t cap) {
+  using namespace scvi;
+  if (!g_prof) {
+    set_error("scvi_profile_end: no open profile");
+    return -1;
+  }
+  g_prof = false;
+  std::vector<std::string> order;
+  std::map<std::string, std::pair<long long, double>> agg;
+  cudaEvent_t prev = g_prof_start;
+  bool ok = true;
+  if (!g_prof_recs.empty()) ok = cudaEventSynchronize(g_prof_recs.back().ev) == cudaSuccess;
+  for (auto& r : g_prof_recs) {
+    float ms = 0.f;
+    if (ok && cudaEventElapsedTime(&ms, prev, r.ev) != cudaSuccess) ok = false;
+    auto it = agg.find(r.name);
+    if (it == agg.end()) {
+      order.push_back(r.name);
+      agg[r.name] = {1, (double)ms};
+    } else {
+      it->second.first += 1;
+      it->second.second += ms;
+    }
+    if (prev != g_prof_start) cudaEventDestroy(prev);
+    prev = r.ev;
+  }
+  if (prev != g_prof_start) cudaEventDestroy(prev);
+  cudaEventDestroy(g_prof_start);
+  g_prof_recs.clear();
+  if (!ok) {
+    cudaGetLastError();
+    set_error("scvi_profile_end: event timing failed");
+    return -1;
+  }
+  std::string out;
+  char line[384];
+  for (auto& n : order) {
+    snprintf(line, sizeof(line), "%s\t%lld\t%.6f\n", n.c_str(), agg[n].first, agg[n].second);
+    out += line;
+  }
+  if ((int64_t)out.size() + 1 > cap) {
+    set_error("scvi_profile_end: buffer too small (%lld bytes needed)", (long long)out.size() + 1);
+    return -1;
+  }
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return (int64_t)out.size();
+}
 }

@@ -9,6 +9,7 @@
 namespace scvi {
 
 void set_error(const char* fmt, ...);
+void count_launch(const char* name);  // one call per kernel launch of this library (scvi_launch_count, profiler)
 
 #define SCVI_REQUIRE(cond, ...)          \
   do {                                   \
@@ -20,6 +21,7 @@ void set_error(const char* fmt, ...);
 
 #define SCVI_LAUNCH_CHECK(name)                                                   \
   do {                                                                            \
+    scvi::count_launch(name);                                                     \
     cudaError_t e__ = cudaGetLastError();                                         \
     if (e__ != cudaSuccess) {                                                     \
       scvi::set_error("%s: CUDA launch failed: %s", name, cudaGetErrorString(e__)); \

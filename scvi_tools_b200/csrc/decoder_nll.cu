@@ -643,7 +643,8 @@ int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood);
 int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
                           const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
-                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, cudaStream_t st);
+                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
+                          cudaStream_t st);
 }  // namespace scvi
 
 extern "C" {
@@ -692,7 +693,7 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   if (dh)  // FFMA path: the dh kernel of the backward, run right after the forward
     return scvi_decoder_nll_bwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, row_stats, g_reconst,
                                 likelihood, precision, dh, lddh, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
-                                stream);
+                                nullptr, stream);
   return SCVI_OK;
 }
 
@@ -726,7 +727,8 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                          const float* bs, const float* Wp, const float* bp, const float* px_r, const float* x,
                          int64_t ldx, const int64_t* row_idx, const float* library, const float* row_stats,
                          const float* g_reconst, int likelihood, int precision, float* dh, int64_t lddh,
-                         float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, void* stream) {
+                         float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
+                         void* stream) {
   using namespace scvi;
   const char* name = "scvi_decoder_nll_bwd";
   const bool zinb = likelihood == SCVI_LIK_ZINB;
@@ -755,7 +757,7 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   }
   if (want_dw && precision == SCVI_PREC_TC && H == 128)
     return tc_decoder_nll_bwd_dw(h, ldh, B, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, row_stats, g_reconst, likelihood,
-                                 dWs, dbs, dWp, dbp, dpx_r, ws, st);
+                                 dWs, dbs, dWp, dbp, dpx_r, ws, fwd_ws, st);
   if (want_dw) {
     const int64_t S = dw_row_splits(B, G);
     const int nheads = zinb ? 2 : 1;

@@ -412,6 +412,14 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
   return p;
 }
 
+// where the forward workspace keeps the packed 128-gene weight tiles and the gene-constant table
+// (the backward reuses them when handed the forward workspace)
+void tc_decoder_fwd_ws_offsets(int64_t B, int64_t G, int nheads, size_t* off_packed, size_t* off_gconst) {
+  const TcPlan p = tc_plan(B, G, nheads);
+  *off_packed = p.off_packed;
+  *off_gconst = p.off_gconst;
+}
+
 int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood) {
   (void)H;
   return (int64_t)tc_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;

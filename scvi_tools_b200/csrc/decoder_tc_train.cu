@@ -417,12 +417,13 @@ int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t 
 // =======================================================================================
 namespace scvi {
 
-// h fp32 [B, H] -> per 32-row tile {h hi block, h lo block, row constants}; also the global bounds that
-// fix the staged-operand scales of K3: scal[0] = max_b 3 u_b exp(library_b) >= |ds|, scal[1] = max_b |u_b|.
+// h fp32 [B, H] -> per 32-row tile {h hi block, h lo block, row constants}; also per-tile bounds that fix
+// the staged-operand scales of K3 (which takes their maximum -- no atomics, no zero-fill):
+// scal[t][0] = max_b 3 u_b exp(library_b) >= |ds|, scal[t][1] = max_b |u_b| over the rows b of tile t.
 __global__ void __launch_bounds__(512)
     tc_pack_h32_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, const float* __restrict__ row_stats,
                        const float* __restrict__ g_reconst, const int64_t* __restrict__ row_idx,
-                       uint8_t* __restrict__ hpack, unsigned int* __restrict__ scal) {
+                       uint8_t* __restrict__ hpack, float* __restrict__ scal /*[nR][2]*/) {
   const int64_t t = blockIdx.x;
   const int r = threadIdx.x & 31, kc = threadIdx.x >> 5;
   const int64_t b = t * TC_NT + r;
@@ -444,7 +445,7 @@ __global__ void __launch_bounds__(512)
   *reinterpret_cast<uint4*>(base + TC_BLK32 + kc * TC_NT * 16 + r * 16) = lo;
   if (kc == 0) {
     float* rc = reinterpret_cast<float*>(base + 2 * TC_BLK32) + r * TC_ROWC;
-    float krow = 0.f, u = 0.f, uSe = 0.f, ok = 0.f;
+    float krow = 0.f, u = 0.f, uSe = 0.f, ok = 0.f, b_ds = 0.f, b_dp = 0.f;
     int64_t rid = 0;
     if (b < B) {
       const float4 st = *reinterpret_cast<const float4*>(row_stats + b * 4);  // (max, sumexp, exp(lib)/sumexp, S)
@@ -454,9 +455,12 @@ __global__ void __launch_bounds__(512)
       uSe = u * st.w / L;
       ok = 1.f;
       rid = row_idx ? row_idx[b] : b;
-      atomicMax(&scal[0], __float_as_uint(3.f * fabsf(u) * L));
-      atomicMax(&scal[1], __float_as_uint(fabsf(u)));
+      b_ds = 3.f * fabsf(u) * L;
+      b_dp = fabsf(u);
     }
+    b_ds = warp_max(b_ds);  // kc == 0 is exactly warp 0
+    b_dp = warp_max(b_dp);
+    if (r == 0) *reinterpret_cast<float2*>(scal + 2 * t) = make_float2(b_ds, b_dp);
     rc[0] = krow; rc[1] = u; rc[2] = uSe; rc[3] = ok;
     rc[4] = __uint_as_float((uint32_t)(rid & 0xffffffffu));
     rc[5] = __uint_as_float((uint32_t)((uint64_t)rid >> 32));
@@ -491,6 +495,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
   uint64_t *sfull = bars + 8, *sempty = bars + 9, *accfull = bars + 10, *wfull = bars + 11;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
   float* s_red = reinterpret_cast<float*>(smem + L::RED);
+  float* s_bound = reinterpret_cast<float*>(smem + L::TMEM_PTR + 8);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t g0 = (int64_t)blockIdx.x * TC_M;
@@ -513,6 +518,20 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     tc::fence_mbar_init();
   }
   if (warp == 2) tc::tmem_alloc(s_tmem, 512);
+  if (warp == 3) {  // global operand bounds = max over the per-tile bounds
+    float b0 = 0.f, b1 = 0.f;
+    for (int i = lane; i < nR; i += 32) {
+      const float2 v = *reinterpret_cast<const float2*>(scal + 2 * i);
+      b0 = fmaxf(b0, v.x);
+      b1 = fmaxf(b1, v.y);
+    }
+    b0 = warp_max(b0);
+    b1 = warp_max(b1);
+    if (lane == 0) {
+      s_bound[0] = b0;
+      s_bound[1] = b1;
+    }
+  }
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
@@ -581,7 +600,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     const fm::GeneK gk = load_gene_k(gcp);
     const float bsv = gcp[3], bpv = gcp[4];
     // staged-operand scales from the global bounds (powers of two)
-    const float bound_ds = fmaxf(scal[0], 1e-30f), bound_dp = fmaxf(scal[1], 1e-30f);
+    const float bound_ds = fmaxf(s_bound[0], 1e-30f), bound_dp = fmaxf(s_bound[1], 1e-30f);
     const int e_ds = max(-100, min(100, (int)ceilf(log2f(bound_ds)))), e_dp = max(-100, min(100, (int)ceilf(log2f(bound_dp))));
     const float sc_ds = tc::pow2i(14 - e_ds), sc_dp = tc::pow2i(TC_DP_SCALE_LOG2 - e_dp);
     const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
@@ -720,6 +739,8 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
                                      __half* __restrict__ packed, uint8_t* __restrict__ packed32,
                                      float* __restrict__ gconst);
 
+void tc_decoder_fwd_ws_offsets(int64_t B, int64_t G, int nheads, size_t* off_packed, size_t* off_gconst);
+
 struct TtBwdPlan {
   int64_t nT, nR;
   int splits, tiles_per_split;
@@ -738,7 +759,7 @@ static TtBwdPlan tt_bwd_plan(int64_t B, int64_t G, int nheads) {
   p.off_gconst = al((size_t)p.nT * nheads * 2 * TC_OPER_BYTES);
   p.off_hpack = al(p.off_gconst + (size_t)p.nT * TC_M * TC_GC * sizeof(float));
   p.off_scal = al(p.off_hpack + (size_t)p.nR * TC_H32_STAGE_BYTES);
-  p.off_slabW = al(p.off_scal + 256);
+  p.off_slabW = al(p.off_scal + (size_t)p.nR * 2 * sizeof(float));
   p.off_slabv = al(p.off_slabW + (size_t)p.splits * nheads * G * TC_H * sizeof(float));
   p.total = al(p.off_slabv + (size_t)p.splits * 3 * G * sizeof(float));
   return p;
@@ -772,7 +793,8 @@ static int tt_launch_k3(const TtBwdPlan& p, int64_t B, int64_t G, const uint8_t*
 int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
                           const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
-                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, cudaStream_t st) {
+                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
+                          cudaStream_t st) {
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   const int nheads = zinb ? 2 : 1;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): ws must be 256-byte aligned");
@@ -782,21 +804,23 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
   __half* packed = (__half*)(w8 + p.off_packed);
   float* gconst = (float*)(w8 + p.off_gconst);
   uint8_t* hpack = w8 + p.off_hpack;
-  unsigned int* scal = (unsigned int*)(w8 + p.off_scal);
+  float* scal = (float*)(w8 + p.off_scal);
   float* slabW = (float*)(w8 + p.off_slabW);
   float* slabv = (float*)(w8 + p.off_slabv);
-  cudaError_t ce = cudaMemsetAsync(scal, 0, 8, st);
-  if (ce != cudaSuccess) {
-    set_error("scvi_decoder_nll_bwd: cudaMemsetAsync failed: %s", cudaGetErrorString(ce));
-    return SCVI_ECUDA;
+  if (fwd_ws) {  // packed weights + gene constants of the matching forward call
+    size_t fwd_off_packed, fwd_off_gconst;
+    tc_decoder_fwd_ws_offsets(B, G, nheads, &fwd_off_packed, &fwd_off_gconst);
+    packed = (__half*)((uint8_t*)fwd_ws + fwd_off_packed);
+    gconst = (float*)((uint8_t*)fwd_ws + fwd_off_gconst);
+  } else {
+    const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
+    tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
+    SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack W)");
   }
-  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
-  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
-  SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack W)");
   tc_pack_h32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(h, ldh, B, row_stats, g_reconst, row_idx, hpack, scal);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack h)");
-  int rc = zinb ? tt_launch_k3<true>(p, B, G, (const uint8_t*)packed, gconst, hpack, (const float*)scal, x, ldx, slabW, slabv, st)
-                : tt_launch_k3<false>(p, B, G, (const uint8_t*)packed, gconst, hpack, (const float*)scal, x, ldx, slabW, slabv, st);
+  int rc = zinb ? tt_launch_k3<true>(p, B, G, (const uint8_t*)packed, gconst, hpack, scal, x, ldx, slabW, slabv, st)
+                : tt_launch_k3<false>(p, B, G, (const uint8_t*)packed, gconst, hpack, scal, x, ldx, slabW, slabv, st);
   if (rc) return rc;
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc dW)");
   const int64_t GH = G * TC_H;

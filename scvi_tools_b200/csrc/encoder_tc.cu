@@ -313,9 +313,10 @@ __global__ void __launch_bounds__(512)
 // ---------------------------------------------------------------------------------------
 // E2: dWe = dy^T log1p(x)
 // ---------------------------------------------------------------------------------------
-// max |src[b, 0..N)| -> *out (as uint bits; out must be zeroed).  N % 4 == 0, rows 16-byte aligned.
+// max |src[b, 0..N)| per block -> part[blockIdx.x] (no atomics, no zero-fill).  N % 4 == 0, rows 16-byte aligned.
 __global__ void __launch_bounds__(256)
-    tc_absmax_kernel(const float* __restrict__ src, int64_t ld, int64_t B, int N, unsigned int* out) {
+    tc_absmax_kernel(const float* __restrict__ src, int64_t ld, int64_t B, int N, float* __restrict__ part) {
+  __shared__ float s_m[8];
   float m = 0.f;
   const int n4 = N >> 2;
   const int64_t total = B * n4;
@@ -324,18 +325,35 @@ __global__ void __launch_bounds__(256)
     m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
   }
   m = warp_max(m);
-  if ((threadIdx.x & 31) == 0) atomicMax(out, __float_as_uint(m));
+  if ((threadIdx.x & 31) == 0) s_m[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = threadIdx.x < 8 ? s_m[threadIdx.x] : 0.f;
+    m = warp_max(m);
+    if (threadIdx.x == 0) part[blockIdx.x] = m;
+  }
 }
 
 // dy fp32 [B, 128] -> per 32-row tile {hi, lo} blocks, addr(r, kc) = kc * 512 + r * 16, scaled by
-// 2^(14 - ceil(log2(absmax)))
+// 2^(14 - ceil(log2(absmax))), absmax = max over the n_part partial maxima (also written to *absmax_out)
 __global__ void __launch_bounds__(512)
-    tc_pack_rows32_kernel(const float* __restrict__ src, int64_t ld, int64_t B, const float* __restrict__ absmax,
-                          uint8_t* __restrict__ out) {
+    tc_pack_rows32_kernel(const float* __restrict__ src, int64_t ld, int64_t B, const float* __restrict__ absmax_part,
+                          int n_part, float* __restrict__ absmax_out, uint8_t* __restrict__ out) {
+  __shared__ float s_am;
   const int64_t t = blockIdx.x;
   const int r = threadIdx.x & 31, kc = threadIdx.x >> 5;
   const int64_t b = t * TC_NT + r;
-  const int e = max(-100, min(100, (int)ceilf(log2f(fmaxf(*absmax, 1e-30f)))));
+  if (kc == 0) {
+    float m = 0.f;
+    for (int i = r; i < n_part; i += 32) m = fmaxf(m, absmax_part[i]);
+    m = warp_max(m);
+    if (r == 0) {
+      s_am = m;
+      if (t == 0) *absmax_out = m;
+    }
+  }
+  __syncthreads();
+  const int e = max(-100, min(100, (int)ceilf(log2f(fmaxf(s_am, 1e-30f)))));
   const float sc = tc::pow2i(14 - e);
   float v[8];
   if (b < B) {
@@ -555,6 +573,7 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
   return SCVI_OK;
 }
 
+constexpr int EN_ABSMAX_BLOCKS = 148 * 8;
 struct EnDwPlan {
   int64_t nT, nR;
   int nsplit, tiles_per_split;
@@ -570,7 +589,7 @@ static EnDwPlan en_dw_plan(int64_t B, int64_t K) {
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   p.off_dy = 0;
   p.off_scal = al((size_t)p.nR * 2 * TC_BLK32);
-  p.off_slab = al(p.off_scal + 256);
+  p.off_slab = al(p.off_scal + (EN_ABSMAX_BLOCKS + 8) * sizeof(float));
   p.total = al(p.off_slab + (size_t)p.nsplit * TC_M * K * sizeof(float));
   return p;
 }
@@ -578,22 +597,23 @@ int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_dw_plan(B,
 
 // dW[128, K] (row stride ldw == K) = dy^T f(x)
 int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
-              int flags, float* dW, void* ws, cudaStream_t st) {
+              int flags, float* dW, const float* dy_absmax_part, int64_t n_absmax_part, void* ws, cudaStream_t st) {
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_linear_bwd(SCVI_LIN_TC): ws must be 256-byte aligned");
+  SCVI_REQUIRE(!dy_absmax_part || n_absmax_part > 0, "scvi_linear_bwd(SCVI_LIN_TC): empty dy_absmax_part");
   SCVI_REQUIRE(lddy % 4 == 0 && ((uintptr_t)dy % 16 == 0), "scvi_linear_bwd(SCVI_LIN_TC): dy must be 16-byte aligned");
   const EnDwPlan p = en_dw_plan(B, K);
   uint8_t* w8 = (uint8_t*)ws;
   uint8_t* dypack = w8 + p.off_dy;
-  unsigned int* scal = (unsigned int*)(w8 + p.off_scal);
+  float* scal = (float*)(w8 + p.off_scal);  // [0] = max |dy|, [8...] = per-block partial maxima
   float* slab = (float*)(w8 + p.off_slab);
-  cudaError_t ce = cudaMemsetAsync(scal, 0, 4, st);
-  if (ce != cudaSuccess) {
-    set_error("scvi_linear_bwd: cudaMemsetAsync failed: %s", cudaGetErrorString(ce));
-    return SCVI_ECUDA;
+  if (!dy_absmax_part) {
+    const int nb = (int)std::min<int64_t>(cdiv(B * (TC_H / 4), 256), EN_ABSMAX_BLOCKS);
+    tc_absmax_kernel<<<nb, 256, 0, st>>>(dy, lddy, B, TC_H, scal + 8);
+    SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc absmax)");
+    dy_absmax_part = scal + 8;
+    n_absmax_part = nb;
   }
-  tc_absmax_kernel<<<(unsigned)std::min<int64_t>(cdiv(B * (TC_H / 4), 256), 148 * 8), 256, 0, st>>>(dy, lddy, B, TC_H, scal);
-  SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc absmax)");
-  tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, (const float*)scal, dypack);
+  tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, dy_absmax_part, (int)n_absmax_part, scal, dypack);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc pack)");
   static bool attr = false;
   if (!attr) {
@@ -603,7 +623,7 @@ int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, in
   }
   const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
   dim3 grid((unsigned)p.nT, (unsigned)p.nsplit);
-  tc_enc_dw_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, (const float*)scal,
+  tc_enc_dw_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, scal,
                                                                 p.tiles_per_split, (flags & SCVI_LIN_LOG1P) ? 1 : 0,
                                                                 xvec, slab);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc dW)");

@@ -370,7 +370,7 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
                cudaStream_t st);
 int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K);
 int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
-              int flags, float* dW, void* ws, cudaStream_t st);
+              int flags, float* dW, const float* dy_absmax_part, int64_t n_absmax_part, void* ws, cudaStream_t st);
 }  // namespace scvi
 
 extern "C" {
@@ -419,8 +419,8 @@ int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_co
 
 int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov, int flags,
-                    const float* dy, int64_t lddy, float* dW, float* db, float* dx, int64_t lddx, void* ws,
-                    void* stream) {
+                    const float* dy, int64_t lddy, float* dW, float* db, float* dx, int64_t lddx,
+                    const float* dy_absmax_part, int64_t n_absmax_part, void* ws, void* stream) {
   using namespace scvi;
   SCVI_REQUIRE(x && dy && ws, "scvi_linear_bwd: NULL pointer");
   SCVI_REQUIRE(B > 0 && K > 0 && N > 0 && ldx >= K && lddy >= N && n_w_cols >= K && ldw >= n_w_cols,
@@ -439,7 +439,7 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
   tc = tc && (K % 4 == 0) && (ldx % 4 == 0) && ((uintptr_t)x % 16 == 0) && (lddy % 4 == 0) && ((uintptr_t)dy % 16 == 0);
   float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * K + N * K;
   if (dW && tc) {
-    int rc = tc_enc_dw(x, ldx, row_idx, B, K, dy, lddy, flags, dW, ws, st);
+    int rc = tc_enc_dw(x, ldx, row_idx, B, K, dy, lddy, flags, dW, dy_absmax_part, n_absmax_part, ws, st);
     if (rc) return rc;
   } else if (dW) {
     const bool vec = (K % 4 == 0) && (N % 4 == 0) && (ldx % 4 == 0) && (lddy % 4 == 0) &&

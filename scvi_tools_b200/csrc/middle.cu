@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(MD_THREADS)
                     const float* __restrict__ rstd1, const float* __restrict__ gamma1, const float* __restrict__ beta1,
                     const uint8_t* __restrict__ mask, float drop_scale, const float* __restrict__ bpart1, int64_t B,
                     float* __restrict__ dy1, float* __restrict__ dgamma1, float* __restrict__ dbeta1,
-                    float* __restrict__ ppart, int64_t prec, int64_t dbe_off) {
+                    float* __restrict__ ppart, int64_t prec, int64_t dbe_off, float* __restrict__ absmax_part) {
   __shared__ float s_scr[4 * MD_H];
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(MD_THREADS)
   }
   const float invB = 1.f / (float)B;
   const float mu = mean1[col], rs = rstd1[col], g = gamma1[col], b = beta1[col];
-  float cs = 0.f;
+  float cs = 0.f, am = 0.f;
 #pragma unroll 4
   for (int i = 0; i < 16; ++i) {
     const int r = rg * 16 + i;
@@ -462,6 +462,7 @@ __global__ void __launch_bounds__(MD_THREADS)
       const float v = rs * g * (d - S1 * invB - xhat * (S2 * invB));
       dy1[o] = v;
       cs += v;
+      am = fmaxf(am, fabsf(v));
     }
   }
   s_scr[rg * MD_H + col] = cs;
@@ -469,11 +470,24 @@ __global__ void __launch_bounds__(MD_THREADS)
   if (rg == 0)
     ppart[(int64_t)blockIdx.x * prec + dbe_off + col] =
         (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
+  if (absmax_part) {  // max |dy1| of this tile (operand scale of the tensor-core dW kernel downstream)
+    __syncthreads();
+    am = warp_max(am);
+    if ((threadIdx.x & 31) == 0) s_scr[threadIdx.x >> 5] = am;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      am = threadIdx.x < MD_THREADS / 32 ? s_scr[threadIdx.x] : 0.f;
+      am = warp_max(am);
+      if (threadIdx.x == 0) absmax_part[blockIdx.x] = am;
+    }
+  }
 }
 
 }  // namespace scvi
 
 extern "C" {
+
+int64_t scvi_mid_n_tiles(int64_t B) { return scvi::cdiv(B, scvi::MD_ROWS); }
 
 int64_t scvi_mid_ws_bytes(int64_t B, int64_t L, int64_t ncols) {
   const int64_t T = scvi::cdiv(B, scvi::MD_ROWS);
@@ -533,7 +547,7 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
                  const float* rstd1, const float* gamma1, const float* beta1, const uint8_t* drop_mask,
                  float drop_scale, int64_t B, int64_t H, int64_t L, float* dy1, float* dgamma2, float* dbeta2,
                  float* dWd, float* dbd, float* dWm, float* dbm, float* dWv, float* dbv, float* dgamma1, float* dbeta1,
-                 float* db_enc, void* ws, void* stream) {
+                 float* db_enc, float* dy1_absmax_part, void* ws, void* stream) {
   using namespace scvi;
   SCVI_REQUIRE(dh && y2 && mean2 && rstd2 && gamma2 && beta2 && z && Wd && q_m && q_v && noise && Wm && Wv && a1 && y1 &&
                    mean1 && rstd1 && gamma1 && beta1 && dy1 && ws,
@@ -552,7 +566,6 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
   float* bpart1 = bpart2 + T * 2 * MD_H;
   float* da1 = bpart1 + T * 2 * MD_H;
   float* ppart = da1 + B * MD_H;
-  float* tot = ppart + T * prec;
   mid_bwd0_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(dh, y2, mean2, rstd2, gamma2, beta2, B, bpart2);
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 0)");
   MidBwdArgs A;
@@ -576,7 +589,8 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 1)");
   const int64_t dbe_off = prec - MD_H;
   mid_bwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(da1, y1, mean1, rstd1, gamma1, beta1, drop_mask, drop_scale,
-                                                     bpart1, B, dy1, dgamma1, dbeta1, ppart, prec, dbe_off);
+                                                     bpart1, B, dy1, dgamma1, dbeta1, ppart, prec, dbe_off,
+                                                     dy1_absmax_part);
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 2)");
   // one deterministic column sum over the per-tile records, scattered to the 7 gradient tensors
   ColsumSegs segs{};

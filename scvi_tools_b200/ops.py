@@ -201,8 +201,8 @@ class FusedLinear(torch.autograd.Function):
         dx = torch.empty(B, n_in, dtype=torch.float32, device=dy.device) if need_x else None
         ws = _ws(query("scvi_linear_bwd_ws_bytes", B, n_in, N, ncols), dy.device)
         call("scvi_linear_bwd", _ptr(x), x.stride(0), _ptr(row_idx), B, n_in, N, _ptr(W), W.stride(0), ncols,
-             _ptr(cov_cols), n_cov, flags, _ptr(dy), dy.stride(0), _ptr(dW), _ptr(db), _ptr(dx), n_in, _ptr(ws),
-             _stream())
+             _ptr(cov_cols), n_cov, flags, _ptr(dy), dy.stride(0), _ptr(dW), _ptr(db), _ptr(dx), n_in, None, 0,
+             _ptr(ws), _stream())
         return dx, dW, db, None, None, None, None, None
 
 
@@ -363,7 +363,7 @@ class DecoderNLL(torch.autograd.Function):
         ws = _ws(query("scvi_decoder_nll_bwd_ws_bytes", B, H, G, likelihood), dev)
         call("scvi_decoder_nll_bwd", _ptr(h), h.stride(0), B, H, G, _ptr(Ws), _ptr(bs), _ptr(Wp), _ptr(bp), _ptr(px_r),
              _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), _ptr(stats), _ptr(g), likelihood, precision, _ptr(dh_k),
-             H, _ptr(dWs), _ptr(dbs), _ptr(dWp), _ptr(dbp), _ptr(dr), _ptr(ws), _stream())
+             H, _ptr(dWs), _ptr(dbs), _ptr(dWp), _ptr(dbp), _ptr(dr), _ptr(ws), None, _stream())
         return dh, dWs, dbs, dWp, dbp, dr, None, None, None, None, None
 
 

@@ -132,7 +132,7 @@ class FusedTrainingPlan:
             prm.data = view  # the module's parameter now lives in the arena
             self.P[k] = view
             self.Gd[k] = self.g[offs[k] : offs[k] + n].view(prm.shape)
-        self.step_counter = torch.zeros(1, dtype=torch.int64, device=dev)
+        self.step_counter = torch.zeros(2, dtype=torch.int64, device=dev)  # {steps done, Adam's arrival ticket}
         self.klw = torch.zeros(1, dtype=torch.float32, device=dev)
         # make sure the BN buffers are on the device
         self.module.to(dev)
@@ -156,7 +156,6 @@ class FusedTrainingPlan:
         self.library = f(B)
         self.maskb = torch.ones(B, H, dtype=torch.bool, device=dev)
         self.mask = self.maskb.view(torch.uint8)  # keep-mask, 1 byte per element
-        self.u = f(B, H)
         self.B_cur = B
         self.noise = f(B, L)
         self.q_m, self.q_v, self.z, self.dz = f(B, L), f(B, L), f(B, L), f(B, L)
@@ -179,6 +178,7 @@ class FusedTrainingPlan:
         self.use_mid = H == 128 and L <= 16 and ncols <= 80
         self.ws_mid = (torch.empty(int(query("scvi_mid_ws_bytes", B, L, ncols)), dtype=torch.uint8, device=dev)
                        if self.use_mid else None)
+        self.dy1_amax = f(int(query("scvi_mid_n_tiles", B)))  # max |dy1| per row tile (mid_bwd -> encoder dW)
         nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik, self.module.precision)
         self.ws_fwd = torch.empty(int(nf), dtype=torch.uint8, device=dev) if nf > 0 else None
         self.enc_tc = _lib.LIN_TC if (self.module.precision == _lib.PREC_TC and H == 128) else 0
@@ -196,7 +196,6 @@ class FusedTrainingPlan:
         ldx = X.stride(0)
         lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
         prec = self.module.precision
-        n = 0
         # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
              None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc, _p(self.y1), H, _p(self.library), _p(self.part1),
@@ -221,21 +220,18 @@ class FusedTrainingPlan:
         Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
         Wp = P.get("decoder.px_dropout_decoder.weight")
         bp = P.get("decoder.px_dropout_decoder.bias")
-        # the ELBO is a mean over the minibatch, so d(loss)/d(reconst) = 1/B is known before the forward:
-        # the fused kernel emits dh together with the likelihood
-        call("scvi_elbo_seed", B, 0.0, _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), st)
+        # the ELBO is a mean over the minibatch, so d(loss)/d(reconst) = 1/B is known before the forward
+        # (seeded by the step prologue): the fused kernel emits dh together with the likelihood
         call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
              _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), _p(self.g_rec), _p(self.dh), H,
              _p(self.ws_fwd), st)
         call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
-        n += 10
         # ---- backward
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
              _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, None, H,
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
-             _p(Gd["px_r"]), _p(self.ws), st)
-        n += 3
+             _p(Gd["px_r"]), _p(self.ws), _p(self.ws_fwd) if prec == _lib.PREC_TC else None, st)
         self._after_head_grads(st)
         if self.use_mid:
             call("scvi_mid_bwd", _p(self.dh), _p(self.y2), _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
@@ -247,14 +243,13 @@ class FusedTrainingPlan:
                  _p(Gd[DEC + "1.bias"]), _p(Gd[DEC + "0.weight"]), _p(Gd[DEC + "0.bias"]),
                  _p(Gd["z_encoder.mean_encoder.weight"]), _p(Gd["z_encoder.mean_encoder.bias"]),
                  _p(Gd["z_encoder.var_encoder.weight"]), _p(Gd["z_encoder.var_encoder.bias"]), _p(Gd[ENC + "1.weight"]),
-                 _p(Gd[ENC + "1.bias"]), _p(Gd[ENC + "0.bias"]), _p(self.ws_mid), st)
+                 _p(Gd[ENC + "1.bias"]), _p(Gd[ENC + "0.bias"]), _p(self.dy1_amax), _p(self.ws_mid), st)
         else:
             self._middle_backward_unfused(st, B, H, L, drop, dscale, inj, ncols)
         call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
              _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
-             None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0, _p(self.ws), st)
-        n += 3 + 6 + 2 + 3 + 4
-        self.kernel_launches_per_step = n + 2  # + adam, counter
+             None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0,
+             _p(self.dy1_amax) if self.use_mid else None, self.dy1_amax.numel() if self.use_mid else 0, _p(self.ws), st)
 
     def _middle_forward_unfused(self, st, B, H, L, drop, dscale, inj, ncols):
         P = self.P
@@ -286,7 +281,7 @@ class FusedTrainingPlan:
              _p(Gd[DEC + "1.bias"]), _p(self.ws), st)
         call("scvi_linear_bwd", _p(self.z), L, None, B, L, H, _p(P[DEC + "0.weight"]), ncols, ncols,
              _p(self.cov_cols) if inj else None, 1 if inj else 0, 0, _p(self.dy2), H, _p(Gd[DEC + "0.weight"]),
-             _p(Gd[DEC + "0.bias"]), _p(self.dz), L, _p(self.ws), st)
+             _p(Gd[DEC + "0.bias"]), _p(self.dz), L, None, 0, _p(self.ws), st)
         call("scvi_latent_bwd", _p(self.a1), H, B, H, L, _p(P["z_encoder.mean_encoder.weight"]),
              _p(P["z_encoder.var_encoder.weight"]), _p(self.noise), self.module.z_encoder.var_eps, _p(self.q_m),
              _p(self.q_v), None, None, _p(self.dz), _p(self.g_kl), _p(self.da1), H,
@@ -305,19 +300,19 @@ class FusedTrainingPlan:
              _p(self.step_counter), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1.0 / self.world, st)
 
     # ------------------------------------------------------------------ driving the step
-    def _draw_rng(self):
-        """Dropout keep-mask and reparameterisation noise from torch's CUDA generator (graph-safe)."""
-        if self.p_drop > 0:
-            self.u.uniform_()
-            torch.ge(self.u, self.p_drop, out=self.maskb)
-        self.noise.normal_()
+    def _prologue(self, st, feed_rng: bool = True):
+        """Dropout keep-mask, reparameterisation noise, batch-covariate columns, ELBO backward seeds and the
+        BatchNorm step counters in one launch (library Philox streams keyed by seed / step / rank)."""
+        B = self.B_cur
+        drop = feed_rng and self.p_drop > 0
+        call("scvi_step_prologue", self.seed, _p(self.step_counter), self.rank, B, self.H, self.L, self.p_drop,
+             _p(self.mask) if drop else None, _p(self.noise) if feed_rng else None, _p(self.idx),
+             _p(self.batch_cols) if self.nb > 1 else None, _p(self.cov_cols) if self.nb > 1 else None, 0.0,
+             _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), _p(self.bn1_nbt), _p(self.bn2_nbt), st)
 
     def _whole_step(self, feed_rng: bool = True):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        if feed_rng:
-            self._draw_rng()
-        if self.nb > 1:
-            torch.index_select(self.batch_cols, 0, self.idx[: self.B_cur], out=self.cov_cols.view(-1)[: self.B_cur])
+        self._prologue(st, feed_rng)
         self._forward_backward(st)
         if self.world > 1:
             torch.distributed.all_reduce(self.g, group=self.pg)  # sum; Adam applies 1/world
@@ -330,11 +325,13 @@ class FusedTrainingPlan:
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):  # warm-up outside capture (lazy module loading, cudaFuncSetAttribute)
-            snap = (self.p.clone(), self.m.clone(), self.v.clone(), self.step_counter.clone(),
-                    self.bn1_rm.clone(), self.bn1_rv.clone(), self.bn2_rm.clone(), self.bn2_rv.clone())
+            state = (self.p, self.m, self.v, self.step_counter, self.bn1_rm, self.bn1_rv, self.bn2_rm, self.bn2_rv,
+                     self.bn1_nbt, self.bn2_nbt)
+            snap = tuple(t.clone() for t in state)
+            n0 = query("scvi_launch_count")
             self._whole_step()
-            for dst, src in zip((self.p, self.m, self.v, self.step_counter, self.bn1_rm, self.bn1_rv, self.bn2_rm,
-                                 self.bn2_rv), snap, strict=True):
+            self.kernel_launches_per_step = query("scvi_launch_count") - n0  # this library's kernels only
+            for dst, src in zip(state, snap, strict=True):
                 dst.copy_(src)
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
@@ -347,9 +344,7 @@ class FusedTrainingPlan:
             g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
             with torch.cuda.graph(g1):
                 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-                self._draw_rng()
-                if self.nb > 1:
-                    torch.index_select(self.batch_cols, 0, self.idx, out=self.cov_cols.view(-1))
+                self._prologue(st)
                 self._forward_backward(st)
             with torch.cuda.graph(g2):
                 self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream))
@@ -385,8 +380,6 @@ class FusedTrainingPlan:
                 self._graphs[0].replay()
                 torch.distributed.all_reduce(self.g, group=self.pg)
                 self._graphs[1].replay()
-        self.bn1_nbt.add_(1)
-        self.bn2_nbt.add_(1)
         self.global_step += 1
         return self.out3
 

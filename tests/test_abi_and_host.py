@@ -32,7 +32,7 @@ def test_library_exports_every_declared_symbol():
         assert name in _lib.SIGNATURES, f"{name} missing from the ctypes table"
         assert len(_lib.SIGNATURES[name][1]) == nargs, f"{name}: header has {nargs} args"
     assert set(_lib.SIGNATURES) == set(decls)
-    assert lib.scvi_b200_abi_version() == 2
+    assert lib.scvi_b200_abi_version() == 3
 
 
 def test_workspace_queries_are_pure_host_functions():

@@ -117,3 +117,91 @@ def test_ragged_last_batch_and_epoch_coverage():
     hist = plan.fit(max_epochs=1)
     assert hist[0]["n_cells"] == 300  # 128 + 128 + 44 (last batch smaller, as drop_last=False)
     assert np.isfinite(hist[0]["train_loss"])
+
+
+def test_step_prologue_random_streams_and_seeds():
+    """Library Philox streams: keep-rate of the dropout mask, N(0,1) moments of the noise, fresh draws per
+    step / rank, reproducible for the same (seed, step, rank); covariate columns and ELBO seeds exact."""
+    import ctypes as C
+
+    from scvi_tools_b200._lib import call
+
+    dev = "cuda:0"
+    B, H, L, p = 4096, 128, 10, 0.1
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    ptr = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    counter = torch.zeros(2, dtype=torch.int64, device=dev)
+    idx = torch.randperm(10000, device=dev)[:B]
+    batch_cols = torch.randint(10, 18, (10000,), dtype=torch.int32, device=dev)
+    klw = torch.tensor([0.25], device=dev)
+    nbt = torch.zeros(2, dtype=torch.int64, device=dev)
+
+    def draw(seed, step, rank):
+        counter[0] = step
+        mask = torch.zeros(B, H, dtype=torch.uint8, device=dev)
+        noise = torch.zeros(B, L, device=dev)
+        cov = torch.zeros(B, dtype=torch.int32, device=dev)
+        gr, gk = torch.zeros(B, device=dev), torch.zeros(B, device=dev)
+        call("scvi_step_prologue", seed, ptr(counter), rank, B, H, L, p, ptr(mask), ptr(noise), ptr(idx), ptr(batch_cols),
+             ptr(cov), 0.0, ptr(klw), 1.0, ptr(gr), ptr(gk), ptr(nbt[0:]), ptr(nbt[1:]), st)
+        torch.cuda.synchronize()
+        return mask, noise, cov, gr, gk
+
+    mask, noise, cov, gr, gk = draw(7, 0, 0)
+    assert set(mask.unique().tolist()) <= {0, 1}
+    n = B * H
+    assert abs(float(mask.float().mean()) - (1 - p)) < 5 * np.sqrt(p * (1 - p) / n)
+    # rows and columns are not correlated copies of each other
+    assert abs(float(mask[:, 0].float().mean()) - (1 - p)) < 0.03 and abs(float(mask[0].float().mean()) - (1 - p)) < 0.15
+    z = noise.double().flatten()
+    m = z.numel()
+    assert abs(float(z.mean())) < 5 / np.sqrt(m)
+    assert abs(float(z.var()) - 1.0) < 5 * np.sqrt(2.0 / m)
+    assert abs(float((z**3).mean())) < 5 * np.sqrt(15.0 / m)
+    assert abs(float((z**4).mean()) - 3.0) < 5 * np.sqrt(96.0 / m)
+    assert float(z.abs().max()) < 6.5
+    assert torch.equal(cov, batch_cols[idx])
+    assert torch.allclose(gr, torch.full_like(gr, 1.0 / B)) and torch.allclose(gk, torch.full_like(gk, 0.25 / B))
+    assert nbt.tolist() == [1, 1]
+    # reproducible, and fresh per step / rank / seed
+    mask2, noise2, *_ = draw(7, 0, 0)
+    assert torch.equal(mask, mask2) and torch.equal(noise, noise2)
+    for args in ((7, 1, 0), (7, 0, 1), (8, 0, 0)):
+        mask3, noise3, *_ = draw(*args)
+        assert float((mask3 != mask).float().mean()) > 0.1
+        assert abs(float((noise3 * noise).mean())) < 5 / np.sqrt(m)
+    # ragged sizes (tail paths of the 16-wide mask / 4-wide noise stores)
+    Bs, Hs, Ls = 37, 7, 3
+    mk = torch.full((Bs * Hs + 16,), 9, dtype=torch.uint8, device=dev)
+    nz = torch.full((Bs * Ls + 4,), 9.0, device=dev)
+    call("scvi_step_prologue", 1, ptr(counter), 0, Bs, Hs, Ls, 0.5, ptr(mk), ptr(nz), None, None, None, 0.0, None, 1.0,
+         None, None, None, None, st)
+    torch.cuda.synchronize()
+    assert int(mk[: Bs * Hs].max()) <= 1 and mk[Bs * Hs :].eq(9).all()
+    assert nz[Bs * Ls :].eq(9.0).all() and float(nz[: Bs * Ls].abs().max()) < 6.5
+
+
+def test_adam_graph_counter_advances_without_extra_kernel():
+    import ctypes as C
+
+    from scvi_tools_b200._lib import call
+
+    dev = "cuda:0"
+    n = 300_001
+    torch.manual_seed(0)
+    p = torch.randn(n + 3, device=dev)[:n]
+    p = torch.randn(((n + 3) // 4) * 4, device=dev)
+    g = torch.randn_like(p)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    ref = torch.nn.Parameter(p.clone())
+    opt = torch.optim.Adam([ref], lr=1e-3, eps=0.01, weight_decay=1e-6)
+    counter = torch.zeros(2, dtype=torch.int64, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for step in range(3):
+        call("scvi_adam_step_graph", C.c_void_p(p.data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(m.data_ptr()),
+             C.c_void_p(v.data_ptr()), p.numel(), C.c_void_p(counter.data_ptr()), 1e-3, 0.9, 0.999, 0.01, 1e-6, 1.0, st)
+        ref.grad = g.clone()
+        opt.step()
+        torch.cuda.synchronize()
+        assert counter.tolist() == [step + 1, 0]
+    assert rel_err(p.cpu(), ref.detach().cpu()) < 1e-6
