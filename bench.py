@@ -283,7 +283,9 @@ def profile_step(plan, a, reps=20):
         torch.cuda.synchronize()
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         call("scvi_profile_begin", st, 3000)
-        plan._whole_step()
+        plan._prologue(st)  # the step without the data-parallel all-reduce (this leg runs on rank 0 only)
+        plan._forward_backward(st)
+        plan._adam(st)
         call("scvi_gather_rows", X.data_ptr(), X.shape[0], plan.G, X.stride(0), plan.idx.data_ptr(), plan.B,
              out.data_ptr(), plan.G, st)
         n = lib.scvi_profile_end(buf, len(buf))
