@@ -85,6 +85,15 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
       for (int q = 0; q < TC_GC; ++q) gc32[q] = o[q];
     }
   }
+  // lgd tables: lgamma(x + theta) - lgamma(theta) - lgamma(x + 1), x < LGT, per gene (double precision)
+  if (packed32 && e < nT * TC_N * fm::LGT) {
+    const int64_t g = e / fm::LGT;
+    const int xx = (int)(e % fm::LGT);
+    const double theta = (g < G) ? (double)expf(px_r[g]) : 1.0;
+    const float v = xx == 0 ? 0.f : (float)(lgamma((double)xx + theta) - lgamma(theta) - lgamma((double)xx + 1.0));
+    float* tab = reinterpret_cast<float*>(packed32 + (g / TC_NT) * st32 + (size_t)nheads * 2 * TC_BLK32 + TC_GC32_BYTES);
+    tab[(g % TC_NT) * fm::LGT + xx] = v;
+  }
 }
 
 // h tile: fp32 [rows, H] -> scaled fp16 hi / lo blocks in shared memory (same layout as the packed W)
@@ -470,8 +479,8 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
   float* gconst = (float*)(w8 + p.off_gconst);
   float* lse = (float*)(w8 + p.off_lse);
   float* outp = (float*)(w8 + p.off_out);
-  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
   uint8_t* packed32 = dh ? w8 + p.off_packed32 : nullptr;
+  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * (packed32 ? fm::LGT : 1));
   tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, packed32, gconst);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
   const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);

@@ -237,6 +237,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[s]);  // logits buffer drained
       const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
+      const float* tab = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32 + TC_GC32_BYTES) +
+                         8 * cg * fm::LGT;
       float a1[8], a2[8], a3[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
         const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
         const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
         float ll, g1, dpi, mu;
-        fm::elem_fwd<ZINB>(xq[i], sl, pl, krow, gk, eps, s_lgx1, ll, g1, dpi, mu);
+        fm::elem_fwd_tab<ZINB>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu);
         const bool ok = rvalid && (gb + i < G);
         nll -= ok ? ll : 0.f;
         S += ok ? g1 : 0.f;

@@ -31,8 +31,11 @@ constexpr int TC_GC = 8;  // floats per gene in the constant table:
 constexpr int TC_NT = 32;
 constexpr uint32_t TC_BLK32 = TC_NT * TC_H * 2;
 constexpr uint32_t TC_GC32_BYTES = TC_NT * TC_GC * 4;  // gene constants of one 32-gene tile: 1 KB
-// packed32 tile (global): [Ws hi][Ws lo]([Wp hi][Wp lo])[gene constants]
-__host__ __device__ constexpr uint32_t tc_w32_stage_bytes(int nheads) { return nheads * 2 * TC_BLK32 + TC_GC32_BYTES; }
+constexpr uint32_t TC_LGT32_BYTES = TC_NT * fm::LGT * 4;  // lgamma-difference tables of one 32-gene tile: 8 KB
+// packed32 tile (global): [Ws hi][Ws lo]([Wp hi][Wp lo])[gene constants][lgd tables]
+__host__ __device__ constexpr uint32_t tc_w32_stage_bytes(int nheads) {
+  return nheads * 2 * TC_BLK32 + TC_GC32_BYTES + TC_LGT32_BYTES;
+}
 
 constexpr int TC_ROWC = 8;  // floats per row in the row-constant table of the dW kernel
 constexpr uint32_t TC_H32_STAGE_BYTES = 2 * TC_BLK32 + TC_NT * TC_ROWC * 4;  // [h hi][h lo][row constants]: 17 KB

@@ -36,6 +36,21 @@ void fm_elem_fwd(int zinb, int n, const float* x, const float* s, const float* p
     out[4 * i] = ll; out[4 * i + 1] = g1; out[4 * i + 2] = dpi; out[4 * i + 3] = mu;
   }
 }
+// table-driven branch-free variant (the per-gene table is built here the way the pack kernel builds it)
+void fm_elem_fwd_tab(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
+                     const float* theta, float eps, float* out) {
+  std::vector<float> lgx1(LGX1_TABLE), tab(LGT);
+  for (int i = 0; i < LGX1_TABLE; ++i) lgx1[i] = (float)std::lgamma((double)i + 1.0);
+  for (int i = 0; i < n; ++i) {
+    const GeneK g = make_gene(theta[i], eps);
+    for (int k = 0; k < LGT; ++k)
+      tab[k] = k == 0 ? 0.f : (float)(std::lgamma((double)k + (double)theta[i]) - std::lgamma((double)theta[i]) - std::lgamma(k + 1.0));
+    float ll, g1, dpi, mu;
+    if (zinb) elem_fwd_tab<true>(x[i], s[i], pi[i], krow[i], g, eps, tab.data(), lgx1.data(), ll, g1, dpi, mu);
+    else elem_fwd_tab<false>(x[i], s[i], pi[i], krow[i], g, eps, tab.data(), lgx1.data(), ll, g1, dpi, mu);
+    out[4 * i] = ll; out[4 * i + 1] = g1; out[4 * i + 2] = dpi; out[4 * i + 3] = mu;
+  }
+}
 // out[n][4] = g1, dpi, dth, mu
 void fm_elem_bwd(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
                  const float* theta, float eps, float* out) {

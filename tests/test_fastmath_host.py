@@ -71,6 +71,14 @@ def test_elem_fwd_bwd_vs_float64(lib, zinb):
     gsc = 1.0 + np.abs(g1) + x
     assert np.max(np.abs(out[:, 1] - g1) / gsc) < 5e-6
     assert np.max(np.abs(out[:, 2] - dpi)) < 1e-5
+    # table-driven branch-free variant of the fused training kernel: same bars
+    ot = np.empty((n, 4), dtype=np.float32)
+    lib.fm_elem_fwd_tab(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(ot))
+    assert np.max(np.abs(ot[:, 3] - mu) / mu) < 2e-6
+    assert np.max(np.abs(ot[:, 0] - ll) / scale) < 5e-6
+    assert np.mean(np.abs(ot[small, 0] - ll[small])) < 5e-6
+    assert np.max(np.abs(ot[:, 1] - g1) / gsc) < 5e-6
+    assert np.max(np.abs(ot[:, 2] - dpi)) < 1e-5
     ob = np.empty((n, 4), dtype=np.float32)
     lib.fm_elem_bwd(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(ob))
     assert np.max(np.abs(ob[:, 0] - g1) / gsc) < 5e-6
