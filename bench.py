@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--cells", type=int, default=N_CELLS)
     ap.add_argument("--genes", type=int, default=N_GENES)
     ap.add_argument("--likelihood", default="zinb", choices=["zinb", "nb"])
+    ap.add_argument("--batches", type=int, default=N_BATCH, help="number of batch-covariate categories")
     ap.add_argument("--precision", default="tc", choices=["tc", "fp32"],
                     help="GEMM arithmetic of the fused decoder kernels: tc = tcgen05 error-compensated fp16 split "
                          "(fp32-grade accuracy, parity-tested), fp32 = FFMA")
@@ -51,7 +52,7 @@ def parse():
 
 
 def workload_name(a):
-    return (f"SCVI {a.likelihood} VAE train step, synthetic {a.cells} cells x {a.genes} genes, {N_BATCH} batches, "
+    return (f"SCVI {a.likelihood} VAE train step, synthetic {a.cells} cells x {a.genes} genes, {a.batches} batches, "
             f"n_hidden={N_HIDDEN}, n_latent={N_LATENT}, batch_size={a.batch_size} per GPU")
 
 
@@ -93,13 +94,13 @@ class CpuReferenceStep:
         torch.manual_seed(0)
         import scvi_tools_b200 as S  # only to obtain identically-initialised parameters (host tensors)
 
-        m = S.VAE(n_input=a.genes, n_batch=N_BATCH, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT)
+        m = S.VAE(n_input=a.genes, n_batch=a.batches, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT)
         self.P = {k: v.detach().clone() for k, v in m.state_dict().items()}
         self.keys = O.trained_keys(a.likelihood)
         self.M = {k: torch.zeros_like(self.P[k]) for k in self.keys}
         self.V = {k: torch.zeros_like(self.P[k]) for k in self.keys}
         self.X = synth_counts_host(n_rows, a.genes, seed=0)
-        self.batch = (np.arange(n_rows) * N_BATCH // n_rows).astype(np.int64)
+        self.batch = (np.arange(n_rows) * a.batches // n_rows).astype(np.int64)
         self.a = a
         self.t = 0
         self.rng = np.random.default_rng(1)
@@ -113,7 +114,7 @@ class CpuReferenceStep:
         bi = torch.from_numpy(self.batch[idx]).view(-1, 1)
         mask = torch.rand(B, N_HIDDEN, generator=self.g) >= 0.1
         noise = torch.randn(B, N_LATENT, generator=self.g)
-        out, grads = O.loss_and_grads(self.P, x, bi, n_batch=N_BATCH, gene_likelihood=a.likelihood, kl_weight=0.0,
+        out, grads = O.loss_and_grads(self.P, x, bi, n_batch=a.batches, gene_likelihood=a.likelihood, kl_weight=0.0,
                                       drop_mask=mask, noise=noise)
         self.t += 1
         for k in self.keys:
@@ -302,6 +303,51 @@ def profile_step(plan, a, reps=20):
     return {k: {"ms": tot[k] / cnt[k], "launches_per_step": cnt[k] / reps} for k in tot}
 
 
+def time_logprob_kernels(a, dev, peak, reps=10):
+    """BASELINE.json's second metric: achieved HBM GB/s of the standalone NB / ZINB log-likelihood kernels
+    (`NegativeBinomial.log_prob` on materialised mu/theta/pi) on [32768, G] operands (> L2), CUDA events."""
+    import ctypes as C
+
+    from scvi_tools_b200._lib import call
+
+    B, G = 32768, a.genes
+    gen = torch.Generator(device=dev).manual_seed(5)
+    x = torch.poisson(torch.full((B, G), 3.0, device=dev), generator=gen)
+    mu = torch.rand(B, G, device=dev, generator=gen) * 5 + 0.01
+    pi = torch.randn(B, G, device=dev, generator=gen)
+    theta = torch.rand(G, device=dev, generator=gen) * 3 + 0.1
+    out, go = torch.empty(B, G, device=dev), torch.ones(B, G, device=dev)
+    dmu, dpi = torch.empty(B, G, device=dev), torch.empty(B, G, device=dev)
+    dth = torch.empty((B + 63) // 64, G, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    p = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    legs = {
+        "nb_logprob_fwd": (12 * B * G + 4 * G, lambda: call("scvi_nb_logprob_fwd", p(x), G, p(mu), G, p(theta), 0, B, G, 1e-8,
+                                                           p(out), G, None, st)),
+        "zinb_logprob_fwd": (16 * B * G + 4 * G, lambda: call("scvi_zinb_logprob_fwd", p(x), G, p(mu), G, p(theta), 0, p(pi), G,
+                                                             B, G, 1e-8, p(out), G, None, st)),
+        "nb_logprob_bwd": (20 * B * G, lambda: call("scvi_nb_logprob_bwd", p(x), G, p(mu), G, p(theta), 0, p(go), G, B, G, 1e-8,
+                                                     p(dmu), p(dth), st)),
+        "zinb_logprob_bwd": (28 * B * G, lambda: call("scvi_zinb_logprob_bwd", p(x), G, p(mu), G, p(theta), 0, p(pi), G, p(go), G,
+                                                       B, G, 1e-8, p(dmu), p(dth), p(dpi), st)),
+    }
+    res = {}
+    for name, (nbytes, fn) in legs.items():
+        ts = []
+        for r in range(reps + 3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            e1.synchronize()
+            if r >= 3:
+                ts.append(e0.elapsed_time(e1))
+        ms = float(np.median(ts))
+        res[name] = {"ms": ms, "algorithmic_bytes": nbytes, "GBps": nbytes / ms / 1e6, "frac_of_hbm_peak": nbytes / ms / 1e6 / peak,
+                     "shape": [B, G]}
+    return res
+
+
 def run_b200_arm(a):
     import scvi_tools_b200 as S
     from scvi_tools_b200.data import DeviceResidentCounts
@@ -323,10 +369,10 @@ def run_b200_arm(a):
     B, K, W = a.batch_size, a.steps, max(a.warmup, 3)
 
     X = synth_counts_device(a.cells, a.genes, dev, seed=rank)
-    batch = (torch.arange(a.cells, device=dev) * N_BATCH // a.cells)
+    batch = (torch.arange(a.cells, device=dev) * a.batches // a.cells)
     data = DeviceResidentCounts(X, batch=batch, device=dev)
     torch.manual_seed(0)
-    m = S.VAE(n_input=a.genes, n_batch=N_BATCH, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT,
+    m = S.VAE(n_input=a.genes, n_batch=a.batches, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT,
               precision=1 if a.precision == "tc" else 0).train()
     plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True)
     plan.set_epoch(0)
@@ -367,7 +413,7 @@ def run_b200_arm(a):
     # ---- end to end: pinned host minibatches -> H2D (copy stream, double buffered) -> step -> loss D2H
     n_host = 4
     host_x = [torch.from_numpy(synth_counts_host(B, a.genes, seed=100 + i)).pin_memory() for i in range(n_host)]
-    host_b = [torch.randint(0, N_BATCH, (B,), dtype=torch.int64).pin_memory() for i in range(n_host)]
+    host_b = [torch.randint(0, a.batches, (B,), dtype=torch.int64).pin_memory() for i in range(n_host)]
     stage = DeviceResidentCounts(torch.zeros(2 * B, a.genes), batch=torch.zeros(2 * B, dtype=torch.int64), device=dev)
     plan.data = stage
     plan.batch_cols = torch.zeros(2 * B, dtype=torch.int32, device=dev)
@@ -456,6 +502,8 @@ def run_b200_arm(a):
                 "peak_source": peak_src, "share_of_step": kern[dom]["ms"] * kern[dom]["launches_per_step"] / eager_ms,
                 "note": "HBM is the nearest roofline of the step's streaming kernels; the dominant kernel is limited "
                         "by SFU/issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4)"}
+        del plan.data, data, X  # free the resident matrix before the standalone-kernel leg
+        logprob = time_logprob_kernels(a, dev, peak)
         cpu = None if a.no_cpu_baseline else cpu_baseline(a, a.cpu_seconds)
         line = {
             "metric": "SCVI train cells/sec", "value": value, "unit": "cells/s", "n_gpus": world, "steps": K,
@@ -469,7 +517,7 @@ def run_b200_arm(a):
                                      if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "launches_per_step": launches_per_step,
-            "roofline": roof, "kernels": kern, "cpu_baseline": cpu, "final_loss": loss_end,
+            "roofline": roof, "kernels": kern, "nb_loss_kernel_hbm": logprob, "cpu_baseline": cpu, "final_loss": loss_end,
         }
     if world > 1:
         torch.distributed.barrier()

@@ -213,19 +213,26 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
     uint8_t* stg = smem + L::STG;
     float nll = 0.f, S = 0.f;
+    // x for this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
+    // land during tile j's math, so the fence.proxy.async at the end of the tile (which drains this thread's
+    // outstanding loads) never waits on them.
+    auto load_x = [&](int jj, float (&dst)[8]) {
+      const int64_t gbb = (int64_t)(t0 + jj) * TC_NT + 8 * cg;
+      if (rvalid && xvec) {
+        const float4 t4 = (gbb < G) ? ld_stream4(xrow + gbb) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 u4 = (gbb + 4 < G) ? ld_stream4(xrow + gbb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        dst[0] = t4.x; dst[1] = t4.y; dst[2] = t4.z; dst[3] = t4.w; dst[4] = u4.x; dst[5] = u4.y; dst[6] = u4.z; dst[7] = u4.w;
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = (rvalid && gbb + i < G) ? __ldg(xrow + gbb + i) : 0.f;
+      }
+    };
+    float xq[8], xn[8];
+    if (ntiles > 0) load_x(0, xq);
     for (int j = 0; j < ntiles; ++j) {
       const int s = j & 1;
       const int64_t gb = (int64_t)(t0 + j) * TC_NT + 8 * cg;
-      // x for this thread's 8 genes (issued before the wait so the loads overlap it)
-      float xq[8];
-      if (rvalid && xvec) {
-        float4 t4 = (gb < G) ? ld_stream4(xrow + gb) : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 u4 = (gb + 4 < G) ? ld_stream4(xrow + gb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        xq[0] = t4.x; xq[1] = t4.y; xq[2] = t4.z; xq[3] = t4.w; xq[4] = u4.x; xq[5] = u4.y; xq[6] = u4.z; xq[7] = u4.w;
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) xq[i] = (rvalid && gb + i < G) ? __ldg(xrow + gb + i) : 0.f;
-      }
+      if (j + 1 < ntiles) load_x(j + 1, xn);
       tc::mbar_wait(&tfull[s], (j >> 1) & 1);
       tc::mbar_wait(&wfull[s], (j >> 1) & 1);  // acquire the bulk-copied gene constants
       tc::fence_after_sync();
@@ -274,6 +281,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(sfull);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) xq[i] = xn[i];
     }
     // per-row partials of this gene split: combine the 4 column groups
     s_red[(cg * TC_M + r) * 2 + 0] = nll;

@@ -190,6 +190,56 @@ SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g
   }
 }
 
+// ---- the same likelihoods with mu given (standalone log_prob kernels) -------------------------------------
+// lgamma(x + theta) - lgamma(theta) - lgamma(x + 1); exactly 0 at x == 0 as in the reference
+SCVI_FM float lgd_series(float x, const GeneK& g, const float* __restrict__ lgx1) {
+  return x == 0.f ? 0.f : lgamma_pos(x + g.theta) - g.lg_theta - lgamma_x1(x, lgx1);
+}
+
+template <bool ZINB>
+SCVI_FM float ll_mu(float x, float mu, float pi, const GeneK& g, float eps, const float* __restrict__ lgx1) {
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + mu + eps);
+  const float d_log = -flog(fmaf(mu, g.rth, 1.f));  // log(theta+eps) - log(theta+mu+eps)
+  const float lgd = lgd_series(x, g, lgx1);
+  if (!ZINB) return fmaf(g.theta, d_log, fmaf(x, flog(me * rT), lgd));
+  const bool zero = x < eps;
+  const float a = fmaf(g.theta, d_log, -pi);
+  const float spn = fmaxf(-pi, 0.f) + flog(1.f + ex2(-fabsf(pi) * LOG2E));  // softplus(-pi)
+  const float oa = 1.f + ex2(-fabsf(a) * LOG2E);
+  const float lsel = flog(zero ? oa : me * rT);
+  const float ll = (zero ? fmaxf(a, 0.f) : a) - spn + (zero ? 1.f : x) * lsel + lgd;
+  return x == eps ? 0.f : ll;  // x == eps: both reference masks are 0
+}
+
+// d(ll)/d(mu), d(ll)/d(theta), d(ll)/d(pi)
+template <bool ZINB>
+SCVI_FM void grad_mu(float x, float mu, float pi, const GeneK& g, float eps, float& dmu, float& dth, float& dpi) {
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + mu + eps);
+  const float d_log = -flog(fmaf(mu, g.rth, 1.f));
+  const float da_dth = d_log + g.theta * (g.rth - rT);
+  const float dgd = x == 0.f ? 0.f : digamma_pos_fast(x + g.theta) - g.dg_theta;
+  if (!ZINB) {
+    dmu = fmaf(x, rcp(me) - rT, -g.theta * rT);
+    dth = da_dth - x * rT + dgd;
+    dpi = 0.f;
+    return;
+  }
+  const bool zero = x < eps;
+  const float a = fmaf(g.theta, d_log, -pi);
+  const float ep = ex2(-fabsf(pi) * LOG2E);
+  const float rp = rcp(1.f + ep);
+  const float ea = ex2(-fabsf(a) * LOG2E);
+  const float r1 = rcp(zero ? 1.f + ea : me);
+  const float sa = a >= 0.f ? r1 : ea * r1;  // sigmoid(a) when zero
+  const float e_rp = ep * rp;
+  dmu = zero ? -sa * g.theta * rT : fmaf(x, r1 - rT, -g.theta * rT);
+  dth = zero ? sa * da_dth : da_dth - x * rT + dgd;
+  dpi = zero ? (pi >= 0.f ? e_rp : rp) - sa : -(pi >= 0.f ? rp : e_rp);
+  if (x == eps) dmu = dth = dpi = 0.f;
+}
+
 // One element of the backward: g1 = -mu * d(ll)/d(mu), dpi = d(ll)/d(pi), dth = d(ll)/d(theta), mu.
 template <bool ZINB>
 SCVI_FM void elem_bwd(float x, float s, float pi, float krow, const GeneK& g, float eps, float& g1, float& dpi,

@@ -4,6 +4,7 @@
 // src/scvi/distributions/_negative_binomial.py:36-135,445-459,573-586).
 // HBM-bound.  Algorithmic bytes: NB fwd 12*B*G + 4*G, ZINB fwd 16*B*G + 4*G,
 // NB bwd 20*B*G, ZINB bwd 28*B*G (+ dtheta partials) -- SURVEY.md section 8(d).
+#include "fastmath.cuh"
 #include "likelihood.cuh"
 
 namespace scvi {
@@ -77,6 +78,92 @@ __global__ void __launch_bounds__(LP_THREADS)
   if (THETA_PER_GENE && dtheta) dtheta[(int64_t)blockIdx.y * G + g] = dth_acc;  // per-row-tile partial
 }
 
+// ---- vectorised fast path: per-gene theta, 16-byte aligned rows -------------------------------------------
+// thread = 4 consecutive genes (one 16-byte column) x a tile of SCVI_BN_TILE rows; per-gene constants of the 4
+// genes live in registers; hand-written SFU math (fastmath.cuh) keeps the kernels on the HBM roofline:
+// NB forward 6 SFU ops per element, ZINB 9.
+constexpr int LP4_THREADS = 128;
+
+__device__ __forceinline__ fm::GeneK lp_gene_k(float theta, float eps) {
+  fm::GeneK k;
+  k.theta = theta;
+  k.log_theta = logf(theta + eps);
+  k.lg_theta = lgammaf(theta);
+  k.rth = 1.f / (theta + eps);
+  k.dg_theta = digamma_pos(theta);
+  return k;
+}
+
+template <bool ZINB>
+__global__ void __launch_bounds__(LP4_THREADS)
+    logprob_fwd4_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
+                        const float* __restrict__ theta, const float* __restrict__ pi, int64_t ldpi, int64_t B,
+                        int64_t G, float eps, float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support) {
+  __shared__ float s_lgx1[fm::LGX1_TABLE];
+  for (int i = threadIdx.x; i < fm::LGX1_TABLE; i += LP4_THREADS) s_lgx1[i] = lgammaf((float)i + 1.f);
+  __syncthreads();
+  const int64_t g = ((int64_t)blockIdx.x * LP4_THREADS + threadIdx.x) * 4;
+  const int64_t r0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
+  const int64_t r1 = min(r0 + (int64_t)SCVI_BN_TILE, B);
+  if (g >= G) return;  // G % 4 == 0 on this path
+  const float4 th = *reinterpret_cast<const float4*>(theta + g);
+  const fm::GeneK k0 = lp_gene_k(th.x, eps), k1 = lp_gene_k(th.y, eps), k2 = lp_gene_k(th.z, eps), k3 = lp_gene_k(th.w, eps);
+  bool bad = false;
+#pragma unroll 4
+  for (int64_t r = r0; r < r1; ++r) {
+    const float4 xv = ld_stream4(x + r * ldx + g);
+    const float4 m = ld_stream4(mu + r * ldmu + g);
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ZINB) p = ld_stream4(pi + r * ldpi + g);
+    float4 o;
+    o.x = fm::ll_mu<ZINB>(xv.x, m.x, p.x, k0, eps, s_lgx1);
+    o.y = fm::ll_mu<ZINB>(xv.y, m.y, p.y, k1, eps, s_lgx1);
+    o.z = fm::ll_mu<ZINB>(xv.z, m.z, p.z, k2, eps, s_lgx1);
+    o.w = fm::ll_mu<ZINB>(xv.w, m.w, p.w, k3, eps, s_lgx1);
+    bad |= (xv.x < 0.f) || (xv.x != floorf(xv.x)) || (xv.y < 0.f) || (xv.y != floorf(xv.y)) || (xv.z < 0.f) ||
+           (xv.z != floorf(xv.z)) || (xv.w < 0.f) || (xv.w != floorf(xv.w));
+    *reinterpret_cast<float4*>(out + r * ldo + g) = o;
+  }
+  if (bad_support != nullptr && bad) *bad_support = 1;
+}
+
+template <bool ZINB>
+__global__ void __launch_bounds__(LP4_THREADS)
+    logprob_bwd4_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
+                        const float* __restrict__ theta, const float* __restrict__ pi, int64_t ldpi,
+                        const float* __restrict__ gout, int64_t ldg, int64_t B, int64_t G, float eps,
+                        float* __restrict__ dmu, float* __restrict__ dtheta, float* __restrict__ dpi) {
+  const int64_t g = ((int64_t)blockIdx.x * LP4_THREADS + threadIdx.x) * 4;
+  const int64_t r0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
+  const int64_t r1 = min(r0 + (int64_t)SCVI_BN_TILE, B);
+  if (g >= G) return;
+  const float4 th = *reinterpret_cast<const float4*>(theta + g);
+  const fm::GeneK k0 = lp_gene_k(th.x, eps), k1 = lp_gene_k(th.y, eps), k2 = lp_gene_k(th.z, eps), k3 = lp_gene_k(th.w, eps);
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (int64_t r = r0; r < r1; ++r) {
+    const float4 xv = ld_stream4(x + r * ldx + g);
+    const float4 m = ld_stream4(mu + r * ldmu + g);
+    const float4 go = ld_stream4(gout + r * ldg + g);
+    float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ZINB) p = ld_stream4(pi + r * ldpi + g);
+    float4 a, b, d;
+    fm::grad_mu<ZINB>(xv.x, m.x, p.x, k0, eps, a.x, b.x, d.x);
+    fm::grad_mu<ZINB>(xv.y, m.y, p.y, k1, eps, a.y, b.y, d.y);
+    fm::grad_mu<ZINB>(xv.z, m.z, p.z, k2, eps, a.z, b.z, d.z);
+    fm::grad_mu<ZINB>(xv.w, m.w, p.w, k3, eps, a.w, b.w, d.w);
+    if (dmu) *reinterpret_cast<float4*>(dmu + r * G + g) = make_float4(go.x * a.x, go.y * a.y, go.z * a.z, go.w * a.w);
+    if (ZINB && dpi) *reinterpret_cast<float4*>(dpi + r * G + g) = make_float4(go.x * d.x, go.y * d.y, go.z * d.z, go.w * d.w);
+    acc.x = fmaf(go.x, b.x, acc.x);
+    acc.y = fmaf(go.y, b.y, acc.y);
+    acc.z = fmaf(go.z, b.z, acc.z);
+    acc.w = fmaf(go.w, b.w, acc.w);
+  }
+  if (dtheta) *reinterpret_cast<float4*>(dtheta + (int64_t)blockIdx.y * G + g) = acc;  // per-row-tile partial
+}
+
+static inline bool lp_al16(const void* p) { return p == nullptr || ((uintptr_t)p % 16) == 0; }
+
 // out[n] (+)= sum_t partials[t, n], fixed order
 __global__ void colsum_partials_kernel(const float* __restrict__ p, int64_t T, int64_t N, float* __restrict__ out,
                                        int accumulate) {
@@ -96,6 +183,13 @@ static int launch_fwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu
   if (B == 0 || G == 0) return SCVI_OK;
   dim3 grid((unsigned)cdiv(G, LP_THREADS), (unsigned)cdiv(B, SCVI_BN_TILE));
   SCVI_REQUIRE(grid.y <= 65535, "%s: B too large for one launch (max %d rows)", name, 65535 * SCVI_BN_TILE);
+  if (theta_ld == 0 && G % 4 == 0 && ldx % 4 == 0 && ldmu % 4 == 0 && ldo % 4 == 0 && (!ZINB || ldpi % 4 == 0) && lp_al16(x) &&
+      lp_al16(mu) && lp_al16(theta) && lp_al16(out) && lp_al16(pi)) {
+    grid.x = (unsigned)cdiv(G / 4, LP4_THREADS);
+    logprob_fwd4_kernel<ZINB><<<grid, LP4_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, pi, ldpi, B, G, eps, out, ldo, bad);
+    SCVI_LAUNCH_CHECK(name);
+    return SCVI_OK;
+  }
   if (theta_ld == 0)
     logprob_fwd_kernel<ZINB, true><<<grid, LP_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, 0, pi, ldpi, B, G, eps, out, ldo, bad);
   else
@@ -113,6 +207,13 @@ static int launch_bwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu
   if (B == 0 || G == 0) return SCVI_OK;
   dim3 grid((unsigned)cdiv(G, LP_THREADS), (unsigned)cdiv(B, SCVI_BN_TILE));
   SCVI_REQUIRE(grid.y <= 65535, "%s: B too large for one launch", name);
+  if (theta_ld == 0 && G % 4 == 0 && ldx % 4 == 0 && ldmu % 4 == 0 && ldg % 4 == 0 && (!ZINB || ldpi % 4 == 0) && lp_al16(x) &&
+      lp_al16(mu) && lp_al16(theta) && lp_al16(gout) && lp_al16(pi) && lp_al16(dmu) && lp_al16(dtheta) && lp_al16(dpi)) {
+    grid.x = (unsigned)cdiv(G / 4, LP4_THREADS);
+    logprob_bwd4_kernel<ZINB><<<grid, LP4_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, pi, ldpi, gout, ldg, B, G, eps, dmu, dtheta, dpi);
+    SCVI_LAUNCH_CHECK(name);
+    return SCVI_OK;
+  }
   if (theta_ld == 0)
     logprob_bwd_kernel<ZINB, true><<<grid, LP_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, 0, pi, ldpi, gout, ldg, B, G, eps, dmu, dtheta, dpi);
   else
