@@ -8,7 +8,7 @@
 // (:311-317), the KL of VAE.loss (src/scvi/module/_vae.py:563-565) and FCLayers.forward of the decoder
 // (:148-188).  Every op on this stretch touches ~4 MB: as separate launches they are latency bound.
 //
-// One CTA = one BatchNorm tile of SCVI_BN_TILE (64) rows, 512 threads.  Batch statistics cross CTAs through
+// One CTA = one tile of MD_ROWS rows, 512 threads.  Batch statistics cross CTAs through
 // per-tile partials (mean, M2 / sums) that every CTA of the NEXT kernel merges redundantly in a fixed
 // order (deterministic, no grid barrier, no atomics).
 #include "common.cuh"
@@ -16,47 +16,43 @@
 namespace scvi {
 
 constexpr int MD_H = 128;
-constexpr int MD_ROWS = SCVI_BN_TILE;  // 64
+constexpr int MD_ROWS = 32;            // rows per CTA (two CTAs per SM hide each other's latency)
+constexpr int MD_RPT = MD_ROWS / 4;    // rows per thread: thread = (column, one of 4 row groups)
 constexpr int MD_THREADS = 512;
 constexpr int MD_LMAX = 16;            // n_latent <= 16
 constexpr int MD_WD_LD = 81;           // decoder layer-0 weight row stride in smem (n_latent + n_batch <= 80)
 
-// merge per-tile (mean, M2) partials [T][2][128] -> batch mean / biased variance of column `col`
-// (Chan's formula; 4 thread groups x T/4 tiles, then a fixed-order merge).  All 512 threads call it.
-__device__ __forceinline__ void md_merge_stats(const float* __restrict__ part, int64_t B, float* s_scratch /*[3][4][128]*/,
-                                               float& mean_out, float& var_out, float& cnt_out) {
+// merge per-tile (mean, M2) partials [T][2][128] -> batch mean / biased variance of column `col`:
+//   mean = sum_t n_t mean_t / B,   M2 = sum_t (M2_t + n_t (mean_t - mean)^2)
+// two passes of independent loads (no serial dependence through divisions), 4 thread groups x T/4 tiles each,
+// partial sums merged in a fixed order.  All 512 threads call it.
+__device__ __forceinline__ void md_merge_stats(const float* __restrict__ part, int64_t B, int tile_rows,
+                                               float* s_scratch /*[4][128]*/, float& mean_out, float& var_out,
+                                               float& cnt_out) {
   const int col = threadIdx.x & 127, grp = threadIdx.x >> 7;
-  const int64_t T = (B + MD_ROWS - 1) / MD_ROWS;
-  float cnt = 0.f, mean = 0.f, m2 = 0.f;
-  for (int64_t t = grp; t < T; t += 4) {
-    const float cb = (float)min((int64_t)MD_ROWS, B - t * MD_ROWS);
-    const float mb = part[(t * 2 + 0) * MD_H + col];
-    const float m2b = part[(t * 2 + 1) * MD_H + col];
-    const float tot = cnt + cb;
-    const float delta = mb - mean;
-    mean += delta * (cb / tot);
-    m2 += m2b + delta * delta * (cnt * cb / tot);
-    cnt = tot;
-  }
-  s_scratch[(0 * 4 + grp) * MD_H + col] = cnt;
-  s_scratch[(1 * 4 + grp) * MD_H + col] = mean;
-  s_scratch[(2 * 4 + grp) * MD_H + col] = m2;
+  const int64_t T = (B + tile_rows - 1) / tile_rows;
+  const float tr = (float)tile_rows;
+  const float c_last = (float)(B - (T - 1) * tile_rows);
+  float s = 0.f;
+#pragma unroll 4
+  for (int64_t t = grp; t < T; t += 4) s = fmaf(t == T - 1 ? c_last : tr, part[(t * 2 + 0) * MD_H + col], s);
+  s_scratch[grp * MD_H + col] = s;
   __syncthreads();
-  cnt = 0.f; mean = 0.f; m2 = 0.f;
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const float cb = s_scratch[(0 * 4 + g) * MD_H + col];
-    if (cb == 0.f) continue;
-    const float tot = cnt + cb;
-    const float delta = s_scratch[(1 * 4 + g) * MD_H + col] - mean;
-    mean += delta * (cb / tot);
-    m2 += s_scratch[(2 * 4 + g) * MD_H + col] + delta * delta * (cnt * cb / tot);
-    cnt = tot;
+  const float mean = ((s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col])) / (float)B;
+  __syncthreads();
+  float m2 = 0.f;
+#pragma unroll 4
+  for (int64_t t = grp; t < T; t += 4) {
+    const float d = part[(t * 2 + 0) * MD_H + col] - mean;
+    m2 += fmaf(t == T - 1 ? c_last : tr, d * d, part[(t * 2 + 1) * MD_H + col]);
   }
+  s_scratch[grp * MD_H + col] = m2;
+  __syncthreads();
+  m2 = (s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col]);
   __syncthreads();
   mean_out = mean;
-  var_out = m2 / cnt;
-  cnt_out = cnt;
+  var_out = m2 / (float)B;
+  cnt_out = (float)B;
 }
 
 // out[col] = sum_t part[t][which][col] (fixed order), all 512 threads
@@ -72,20 +68,20 @@ __device__ __forceinline__ float md_merge_sum(const float* __restrict__ part, in
   return tot;
 }
 
-// per-tile (mean, M2) of a column from the 4 row groups' 16 values each
-__device__ __forceinline__ void md_tile_stats(const float (&vals)[16], int rg, int col, int cnt, float* s_scratch,
+// per-tile (mean, M2) of a column from the 4 row groups' MD_RPT values each
+__device__ __forceinline__ void md_tile_stats(const float (&vals)[MD_RPT], int rg, int col, int cnt, float* s_scratch,
                                               float* __restrict__ part_out /*[2][128] of this tile*/) {
   float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) s += (rg * 16 + i < cnt) ? vals[i] : 0.f;
+  for (int i = 0; i < MD_RPT; ++i) s += (rg * MD_RPT + i < cnt) ? vals[i] : 0.f;
   s_scratch[rg * MD_H + col] = s;
   __syncthreads();
   const float mean = ((s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col])) / (float)cnt;
   __syncthreads();
   float m2 = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i)
-    if (rg * 16 + i < cnt) {
+  for (int i = 0; i < MD_RPT; ++i)
+    if (rg * MD_RPT + i < cnt) {
       const float d = vals[i] - mean;
       m2 = fmaf(d, d, m2);
     }
@@ -136,7 +132,7 @@ __global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
   for (int e = tid; e < MD_H * A.ncols; e += MD_THREADS) s_Wd[(e / A.ncols) * MD_WD_LD + e % A.ncols] = A.Wd[e];
 
   float mean, var, n;
-  md_merge_stats(A.part1, A.B, s_scr, mean, var, n);
+  md_merge_stats(A.part1, A.B, SCVI_BN_TILE, s_scr, mean, var, n);
   const float rstd = 1.f / sqrtf(var + A.bn_eps);
   if (blockIdx.x == 0 && rg == 0) {
     A.mean1[col] = mean;
@@ -146,8 +142,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
   }
   const float g1 = A.gamma1[col], b1 = A.beta1[col];
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     float a = 0.f;
     if (r < cnt) {
       const int64_t o = (r0 + r) * MD_H + col;
@@ -196,10 +192,10 @@ __global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
   }
   // decoder hidden layer: y2 = z Wd[:, :L]^T + Wd[:, cov] + bd
   const float bdv = A.bd ? A.bd[col] : 0.f;
-  float vals[16];
+  float vals[MD_RPT];
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     float v = 0.f;
     if (r < cnt) {
       v = bdv;
@@ -223,7 +219,7 @@ __global__ void __launch_bounds__(MD_THREADS)
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
   float mean, var, n;
-  md_merge_stats(part2, B, s_scr, mean, var, n);
+  md_merge_stats(part2, B, MD_ROWS, s_scr, mean, var, n);
   const float rstd = 1.f / sqrtf(var + bn_eps);
   if (blockIdx.x == 0 && rg == 0) {
     mean2[col] = mean;
@@ -233,8 +229,8 @@ __global__ void __launch_bounds__(MD_THREADS)
   }
   const float g = gamma2[col], b = beta2[col];
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     if (r < cnt) {
       const int64_t o = (r0 + r) * MD_H + col;
       h[o] = fmaxf((y2[o] - mean) * (rstd * g) + b, 0.f);
@@ -257,8 +253,8 @@ __global__ void __launch_bounds__(MD_THREADS)
   const float mu = mean2[col], rs = rstd2[col], g = gamma2[col], b = beta2[col];
   float s1 = 0.f, s2 = 0.f;
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     if (r < cnt) {
       const int64_t o = (r0 + r) * MD_H + col;
       const float xhat = (y2[o] - mu) * rs;
@@ -333,8 +329,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   {
     const float mu = A.mean2[col], rs = A.rstd2[col], g = A.gamma2[col], b = A.beta2[col];
 #pragma unroll 4
-    for (int i = 0; i < 16; ++i) {
-      const int r = rg * 16 + i;
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
       float v = 0.f;
       if (r < cnt) {
         const int64_t o = (r0 + r) * MD_H + col;
@@ -384,8 +380,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
     const float mu = A.mean1[col], rs = A.rstd1[col], g = A.gamma1[col], b = A.beta1[col];
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll 2
-    for (int i = 0; i < 16; ++i) {
-      const int r = rg * 16 + i;
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
       if (r < cnt) {
         float s = 0.f;
         for (int j = 0; j < L2; ++j) s = fmaf(s_dq[r * L2 + j], s_W[j * 129 + col], s);
@@ -405,8 +401,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   }
   // a1 tile -> s_t for the latent weight gradients
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     s_t[r * MD_H + col] = (r < cnt) ? A.a1[(r0 + r) * MD_H + col] : 0.f;
   }
   __syncthreads();
@@ -451,8 +447,8 @@ __global__ void __launch_bounds__(MD_THREADS)
   const float mu = mean1[col], rs = rstd1[col], g = gamma1[col], b = beta1[col];
   float cs = 0.f, am = 0.f;
 #pragma unroll 4
-  for (int i = 0; i < 16; ++i) {
-    const int r = rg * 16 + i;
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
     if (r < cnt) {
       const int64_t o = (r0 + r) * MD_H + col;
       const float xhat = (y1[o] - mu) * rs;

@@ -95,7 +95,7 @@ __device__ __forceinline__ fm::GeneK lp_gene_k(float theta, float eps) {
 }
 
 template <bool ZINB>
-__global__ void __launch_bounds__(LP4_THREADS)
+__global__ void __launch_bounds__(LP4_THREADS, 8)
     logprob_fwd4_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
                         const float* __restrict__ theta, const float* __restrict__ pi, int64_t ldpi, int64_t B,
                         int64_t G, float eps, float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support) {
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(LP4_THREADS)
   const float4 th = *reinterpret_cast<const float4*>(theta + g);
   const fm::GeneK k0 = lp_gene_k(th.x, eps), k1 = lp_gene_k(th.y, eps), k2 = lp_gene_k(th.z, eps), k3 = lp_gene_k(th.w, eps);
   bool bad = false;
-#pragma unroll 4
+#pragma unroll 8
   for (int64_t r = r0; r < r1; ++r) {
     const float4 xv = ld_stream4(x + r * ldx + g);
     const float4 m = ld_stream4(mu + r * ldmu + g);
