@@ -34,14 +34,14 @@ __device__ __forceinline__ void md_merge_stats(const float* __restrict__ part, i
   const float tr = (float)tile_rows;
   const float c_last = (float)(B - (T - 1) * tile_rows);
   float s = 0.f;
-#pragma unroll 4
+#pragma unroll 16
   for (int64_t t = grp; t < T; t += 4) s = fmaf(t == T - 1 ? c_last : tr, part[(t * 2 + 0) * MD_H + col], s);
   s_scratch[grp * MD_H + col] = s;
   __syncthreads();
   const float mean = ((s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col])) / (float)B;
   __syncthreads();
   float m2 = 0.f;
-#pragma unroll 4
+#pragma unroll 16
   for (int64_t t = grp; t < T; t += 4) {
     const float d = part[(t * 2 + 0) * MD_H + col] - mean;
     m2 += fmaf(t == T - 1 ? c_last : tr, d * d, part[(t * 2 + 1) * MD_H + col]);
@@ -55,17 +55,22 @@ __device__ __forceinline__ void md_merge_stats(const float* __restrict__ part, i
   cnt_out = (float)B;
 }
 
-// out[col] = sum_t part[t][which][col] (fixed order), all 512 threads
-__device__ __forceinline__ float md_merge_sum(const float* __restrict__ part, int64_t T, int n_which, int which,
-                                              float* s_scratch /*[4][128]*/) {
+// (S1, S2)[col] = sum_t part[t][0 / 1][col] (fixed order), all 512 threads
+__device__ __forceinline__ void md_merge_sum2(const float* __restrict__ part, int64_t T, float* s_scratch /*[8][128]*/,
+                                              float& S1, float& S2) {
   const int col = threadIdx.x & 127, grp = threadIdx.x >> 7;
-  float s = 0.f;
-  for (int64_t t = grp; t < T; t += 4) s += part[(t * n_which + which) * MD_H + col];
-  s_scratch[grp * MD_H + col] = s;
+  float a = 0.f, b = 0.f;
+#pragma unroll 8
+  for (int64_t t = grp; t < T; t += 4) {
+    a += part[(t * 2 + 0) * MD_H + col];
+    b += part[(t * 2 + 1) * MD_H + col];
+  }
+  s_scratch[grp * MD_H + col] = a;
+  s_scratch[(4 + grp) * MD_H + col] = b;
   __syncthreads();
-  const float tot = (s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col]);
+  S1 = (s_scratch[col] + s_scratch[MD_H + col]) + (s_scratch[2 * MD_H + col] + s_scratch[3 * MD_H + col]);
+  S2 = (s_scratch[4 * MD_H + col] + s_scratch[5 * MD_H + col]) + (s_scratch[6 * MD_H + col] + s_scratch[7 * MD_H + col]);
   __syncthreads();
-  return tot;
 }
 
 // per-tile (mean, M2) of a column from the 4 row groups' MD_RPT values each
@@ -319,8 +324,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   for (int e = tid; e < MD_ROWS * L; e += MD_THREADS) s_z[e] = (e / L < cnt) ? A.z[r0 * L + e] : 0.f;
   if (tid < MD_ROWS) s_cat[tid] = (A.cov_cols && tid < cnt) ? A.cov_cols[r0 + tid] : -1;
 
-  const float S1 = md_merge_sum(A.bpart2, T, 2, 0, s_scr);
-  const float S2 = md_merge_sum(A.bpart2, T, 2, 1, s_scr);
+  float S1, S2;
+  md_merge_sum2(A.bpart2, T, s_scr, S1, S2);
   if (blockIdx.x == 0 && rg == 0) {
     if (A.dbeta2) A.dbeta2[col] = S1;
     if (A.dgamma2) A.dgamma2[col] = S2;
@@ -432,13 +437,13 @@ __global__ void __launch_bounds__(MD_THREADS)
                     const uint8_t* __restrict__ mask, float drop_scale, const float* __restrict__ bpart1, int64_t B,
                     float* __restrict__ dy1, float* __restrict__ dgamma1, float* __restrict__ dbeta1,
                     float* __restrict__ ppart, int64_t prec, int64_t dbe_off, float* __restrict__ absmax_part) {
-  __shared__ float s_scr[4 * MD_H];
+  __shared__ float s_scr[8 * MD_H];
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
   const int64_t T = (B + MD_ROWS - 1) / MD_ROWS;
-  const float S1 = md_merge_sum(bpart1, T, 2, 0, s_scr);
-  const float S2 = md_merge_sum(bpart1, T, 2, 1, s_scr);
+  float S1, S2;
+  md_merge_sum2(bpart1, T, s_scr, S1, S2);
   if (blockIdx.x == 0 && rg == 0) {
     if (dbeta1) dbeta1[col] = S1;
     if (dgamma1) dgamma1[col] = S2;
