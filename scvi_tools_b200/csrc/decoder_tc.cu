@@ -85,6 +85,16 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
       for (int q = 0; q < TC_GC; ++q) gc32[q] = o[q];
     }
   }
+  // dgd tables for the dW kernel: digamma(x + theta) - digamma(theta) = sum_{k<x} 1/(theta + k), x < DGT, row
+  // stride DGT_LD, stored behind the gene constants and the contiguous bias copy
+  if (gconst && e < nT * TC_N * fm::DGT_LD) {
+    const int64_t g = e / fm::DGT_LD;
+    const int xx = (int)(e % fm::DGT_LD);
+    const double theta = (g < G) ? (double)expf(px_r[g]) : 1.0;
+    double acc = 0.0;
+    for (int k = 0; k < xx && k < fm::DGT; ++k) acc += 1.0 / (theta + (double)k);
+    gconst[nT * TC_N * (TC_GC + 1) + e] = (float)acc;
+  }
   // lgd tables: lgamma(x + theta) - lgamma(theta) - lgamma(x + 1), x < LGT, per gene (double precision)
   if (packed32 && e < nT * TC_N * fm::LGT) {
     const int64_t g = e / fm::LGT;
@@ -408,7 +418,7 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   p.off_packed = 0;
   p.off_gconst = al(p.off_packed + (size_t)p.nT * nheads * 2 * TC_M * TC_H * sizeof(__half));
-  p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * (TC_GC + 1) * sizeof(float));
+  p.off_lse = al(p.off_gconst + (size_t)p.nT * TC_N * TC_GCONST_FLOATS * sizeof(float));
   const int64_t nT32 = cdiv(G, TC_NT);
   int64_t ns2 = std::min<int64_t>(std::max<int64_t>(1, 148 / std::max<int64_t>(1, p.rowtiles)), nT32);
   p.tiles_per_split2 = (int)cdiv(nT32, ns2);
@@ -480,7 +490,7 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
   float* lse = (float*)(w8 + p.off_lse);
   float* outp = (float*)(w8 + p.off_out);
   uint8_t* packed32 = dh ? w8 + p.off_packed32 : nullptr;
-  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * (packed32 ? fm::LGT : 1));
+  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * fm::LGT);
   tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, packed32, gconst);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
   const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);

@@ -488,8 +488,12 @@ struct K3Smem {
   static constexpr uint32_t BARS = STG + NH * 2 * TT_ABLK;
   static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;                // [3][4 row groups][128 genes]
-  static constexpr uint32_t TOTAL = RED + 3 * 4 * TC_M * 4;
+  static constexpr uint32_t DGTAB = RED + 3 * 4 * TC_M * 4;     // [128 genes][DGT_LD] digamma-difference table
+  static constexpr uint32_t DGTAB_BYTES = TC_M * fm::DGT_LD * 4;
+  static constexpr uint32_t TOTAL = DGTAB + DGTAB_BYTES;
 };
+static_assert(K3Smem<true>::DGTAB % 16 == 0 && K3Smem<true>::DGTAB_BYTES % 16 == 0, "bulk copy alignment");
+static_assert(K3Smem<true>::TOTAL + 128 <= 232448, "K3 shared memory");
 
 template <bool ZINB>
 __global__ void __launch_bounds__(TT_THREADS, 1)
@@ -552,10 +556,14 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
   if (warp == 0) {
     if (lane == 0 && ntiles > 0) {
       // resident weight tile of this CTA's 128 genes: NH x {hi, lo} blocks, contiguous in packed128
-      tc::mbar_arrive_expect_tx(wfull, NH * 2 * TC_OPER_BYTES);
+      tc::mbar_arrive_expect_tx(wfull, NH * 2 * TC_OPER_BYTES + L::DGTAB_BYTES);
       const uint8_t* src = packed128 + (size_t)blockIdx.x * NH * 2 * TC_OPER_BYTES;
       for (int i = 0; i < NH * 2; ++i)
         tc::bulk_g2s(smem + L::W + i * TC_OPER_BYTES, src + (size_t)i * TC_OPER_BYTES, TC_OPER_BYTES, wfull);
+      // this CTA's 128 rows of the dgd table (stored behind the gene constants and the bias copy)
+      const int nT128 = (int)((G + TC_M - 1) / TC_M);
+      tc::bulk_g2s(smem + L::DGTAB, gconst + (size_t)nT128 * TC_M * (TC_GC + 1) + (size_t)blockIdx.x * TC_M * fm::DGT_LD,
+                   L::DGTAB_BYTES, wfull);
       for (int j = 0; j < ntiles; ++j) {
         const int s = j & 1;
         tc::mbar_wait(&hempty[s], ((j >> 1) & 1) ^ 1);
@@ -616,6 +624,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     const float sc_ds = tc::pow2i(14 - e_ds), sc_dp = tc::pow2i(TC_DP_SCALE_LOG2 - e_dp);
     const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
     uint8_t* stg = smem + L::STG;
+    const float* dgt = reinterpret_cast<const float*>(smem + L::DGTAB) + gl * fm::DGT_LD;
+    if (ntiles > 0) tc::mbar_wait(wfull, 0);  // acquire the bulk-copied dgd table (it lands with the weight tile)
     float cs = 0.f, cp = 0.f, cr = 0.f;
     for (int j = 0; j < ntiles; ++j) {
       const int s = j & 1;
@@ -644,7 +654,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
         const float sl = fmaf(sv[i], TC_RESCALE, bsv);
         const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
         float g1, dpi, dth, mu;
-        fm::elem_bwd<ZINB>(xq[i], sl, pl, rc.x, gk, eps, g1, dpi, dth, mu);
+        fm::elem_bwd_tab<ZINB>(xq[i], sl, pl, rc.x, gk, eps, dgt, g1, dpi, dth, mu);
         const bool ok = gvalid && rc.w != 0.f;
         const float ds = ok ? rc.y * g1 - mu * rc.z : 0.f;
         const float dp = ok ? -rc.y * dpi : 0.f;
@@ -768,7 +778,7 @@ static TtBwdPlan tt_bwd_plan(int64_t B, int64_t G, int nheads) {
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   p.off_packed = 0;
   p.off_gconst = al((size_t)p.nT * nheads * 2 * TC_OPER_BYTES);
-  p.off_hpack = al(p.off_gconst + (size_t)p.nT * TC_M * TC_GC * sizeof(float));
+  p.off_hpack = al(p.off_gconst + (size_t)p.nT * TC_M * TC_GCONST_FLOATS * sizeof(float));
   p.off_scal = al(p.off_hpack + (size_t)p.nR * TC_H32_STAGE_BYTES);
   p.off_slabW = al(p.off_scal + (size_t)p.nR * 2 * sizeof(float));
   p.off_slabv = al(p.off_slabW + (size_t)p.splits * nheads * G * TC_H * sizeof(float));
@@ -824,7 +834,7 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
     packed = (__half*)((uint8_t*)fwd_ws + fwd_off_packed);
     gconst = (float*)((uint8_t*)fwd_ws + fwd_off_gconst);
   } else {
-    const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N);
+    const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * fm::DGT_LD);
     tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, nullptr, gconst);
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack W)");
   }

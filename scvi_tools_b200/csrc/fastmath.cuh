@@ -280,5 +280,44 @@ SCVI_FM void elem_bwd(float x, float s, float pi, float krow, const GeneK& g, fl
   }
 }
 
+// Table-driven, branch-free backward element (genes-owned dW kernel): dgd(x, theta) = digamma(x + theta) -
+// digamma(theta) = sum_{k<x} 1/(theta + k) is read from a per-gene table of DGT entries (row stride DGT_LD, odd:
+// conflict-free when a warp's lanes own consecutive genes); x >= DGT or non-integer x uses the series.
+constexpr int DGT = 48, DGT_LD = 49;
+
+template <bool ZINB>
+SCVI_FM void elem_bwd_tab(float x, float s, float pi, float krow, const GeneK& g, float eps,
+                          const float* __restrict__ tab /*[DGT] of this gene*/, float& g1, float& dpi, float& dth,
+                          float& mu) {
+  mu = ex2(fmaf(s, LOG2E, krow));
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + mu + eps);
+  const float d_log = -flog(fmaf(mu, g.rth, 1.f));
+  const float da_dth = d_log + g.theta * (g.rth - rT);
+  const int xi = (int)x;
+  float dgd;
+  if (x < (float)DGT && (float)xi == x) dgd = tab[xi];
+  else dgd = digamma_pos_fast(x + g.theta) - g.dg_theta;  // rare
+  const float base = g.theta * mu * rT;
+  const float nz_dth = da_dth - x * rT + dgd;
+  if (ZINB) {
+    const bool zero = x < eps;
+    const float a = fmaf(g.theta, d_log, -pi);
+    const float ep = ex2(-fabsf(pi) * LOG2E);
+    const float rp = rcp(1.f + ep);
+    const float ea = ex2(-fabsf(a) * LOG2E);
+    const float r1 = rcp(zero ? 1.f + ea : me);
+    const float sa = a >= 0.f ? r1 : ea * r1;  // sigmoid(a) when zero
+    const float e_rp = ep * rp;
+    g1 = base * (zero ? sa : fmaf(-x, r1, 1.f));
+    dpi = zero ? (pi >= 0.f ? e_rp : rp) - sa : -(pi >= 0.f ? rp : e_rp);
+    dth = zero ? sa * da_dth : nz_dth;
+  } else {
+    g1 = base * fmaf(-x, rcp(me), 1.f);
+    dpi = 0.f;
+    dth = nz_dth;  // x == 0: dgd = 0 and x * rT = 0
+  }
+}
+
 }  // namespace fm
 }  // namespace scvi

@@ -27,6 +27,10 @@ constexpr uint32_t TC_STAGE_BYTES = 2 * TC_OPER_BYTES;  // hi + lo
 constexpr int TC_GC = 8;  // floats per gene in the constant table:
                           // theta, log(theta+eps), lgamma(theta), bs, bp, 1/(theta+eps), digamma(theta), 0
 
+// floats per gene of the gconst workspace region: [constants TC_GC][contiguous scale bias 1][dgd table DGT_LD]
+// (three consecutive arrays over the padded gene count, not interleaved)
+constexpr int TC_GCONST_FLOATS = TC_GC + 1 + fm::DGT_LD;
+
 // 32-row blocks (narrow tiles of the training kernels): one fp16 block 32 x 128 = 8 KB
 constexpr int TC_NT = 32;
 constexpr uint32_t TC_BLK32 = TC_NT * TC_H * 2;

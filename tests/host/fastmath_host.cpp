@@ -62,6 +62,23 @@ void fm_elem_bwd(int zinb, int n, const float* x, const float* s, const float* p
     out[4 * i] = g1; out[4 * i + 1] = dpi; out[4 * i + 2] = dth; out[4 * i + 3] = mu;
   }
 }
+// table-driven branch-free backward element; the dgd table is built as the pack kernel builds it
+void fm_elem_bwd_tab(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
+                     const float* theta, float eps, float* out) {
+  std::vector<float> tab(DGT_LD);
+  for (int i = 0; i < n; ++i) {
+    const GeneK g = make_gene(theta[i], eps);
+    double acc = 0.0;
+    for (int k = 0; k < DGT_LD; ++k) {
+      tab[k] = (float)acc;
+      if (k < DGT) acc += 1.0 / ((double)theta[i] + k);
+    }
+    float g1, dpi, dth, mu;
+    if (zinb) elem_bwd_tab<true>(x[i], s[i], pi[i], krow[i], g, eps, tab.data(), g1, dpi, dth, mu);
+    else elem_bwd_tab<false>(x[i], s[i], pi[i], krow[i], g, eps, tab.data(), g1, dpi, dth, mu);
+    out[4 * i] = g1; out[4 * i + 1] = dpi; out[4 * i + 2] = dth; out[4 * i + 3] = mu;
+  }
+}
 void fm_lgamma(int n, const float* z, float* out) { for (int i = 0; i < n; ++i) out[i] = lgamma_pos(z[i]); }
 void fm_digamma(int n, const float* z, float* out) { for (int i = 0; i < n; ++i) out[i] = digamma_pos_fast(z[i]); }
 }

@@ -85,6 +85,12 @@ def test_elem_fwd_bwd_vs_float64(lib, zinb):
     assert np.max(np.abs(ob[:, 1] - dpi)) < 1e-5
     tsc = 1.0 + np.abs(dth) + x / theta
     assert np.max(np.abs(ob[:, 2] - dth) / tsc) < 1e-5
+    # table-driven branch-free variant of the dW kernel: same bars
+    obt = np.empty((n, 4), dtype=np.float32)
+    lib.fm_elem_bwd_tab(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(obt))
+    assert np.max(np.abs(obt[:, 0] - g1) / gsc) < 5e-6
+    assert np.max(np.abs(obt[:, 1] - dpi)) < 1e-5
+    assert np.max(np.abs(obt[:, 2] - dth) / tsc) < 1e-5
 
 
 def test_lgamma_digamma_series(lib):
