@@ -46,6 +46,9 @@ def parse():
     ap.add_argument("--precision", default="tc", choices=["tc", "fp32"],
                     help="GEMM arithmetic of the fused decoder kernels: tc = tcgen05 error-compensated fp16 split "
                          "(fp32-grade accuracy, parity-tested), fp32 = FFMA")
+    ap.add_argument("--unsorted-batches", action="store_true",
+                    help="feed each minibatch's row ids in shuffled order (default: ascending within the minibatch, "
+                         "as FusedTrainingPlan.fit does -- same cells, better DRAM page / TLB locality)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -378,6 +381,8 @@ def run_b200_arm(a):
     plan.set_epoch(0)
     order = torch.randperm(a.cells, device=dev)
     n_chunks = a.cells // B
+    if not a.unsorted_batches:  # a minibatch is a set: ascending row ids inside each one
+        order[: n_chunks * B] = order[: n_chunks * B].view(n_chunks, B).sort(dim=1).values.reshape(-1)
 
     def chunk(i):
         j = i % n_chunks

@@ -390,6 +390,13 @@ class FusedTrainingPlan:
         for epoch in range(self.current_epoch, self.current_epoch + max_epochs):
             self.set_epoch(epoch)
             order = epoch_indices(self.data.n_obs, self.rank, self.world, epoch, self.seed, shuffle).to(self.dev)
+            # a minibatch is a set of cells: ascending row ids inside each one cost nothing (one sort per epoch)
+            # and give the row gathers better DRAM page / TLB locality
+            nfull = order.numel() // self.B
+            if nfull:
+                order[: nfull * self.B] = order[: nfull * self.B].view(nfull, self.B).sort(dim=1).values.reshape(-1)
+            if order.numel() > nfull * self.B:
+                order[nfull * self.B :] = order[nfull * self.B :].sort().values
             acc = torch.zeros(3, dtype=torch.float64, device=self.dev)
             n_cells = 0
             for s in range(0, order.numel(), self.B):
