@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--unsorted-batches", action="store_true",
                     help="feed each minibatch's row ids in shuffled order (default: ascending within the minibatch, "
                          "as FusedTrainingPlan.fit does -- same cells, better DRAM page / TLB locality)")
+    ap.add_argument("--ddp-mode", default="split", choices=["graph", "overlap", "split"],
+                    help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -280,6 +282,7 @@ def profile_step(plan, a, reps=20):
              plan.bn1_nbt, plan.bn2_nbt)
     snap = [t.clone() for t in state]
     out = torch.empty(plan.B, plan.G, device=plan.dev)
+    world, plan.world = plan.world, 1  # this leg runs on rank 0 only: no collectives
     tot, cnt = {}, {}
     buf = C.create_string_buffer(1 << 16)
     for r in range(reps + 2):
@@ -303,6 +306,7 @@ def profile_step(plan, a, reps=20):
             cnt[name] = cnt.get(name, 0) + int(c)
     for dst, src in zip(state, snap, strict=True):
         dst.copy_(src)
+    plan.world = world
     return {k: {"ms": tot[k] / cnt[k], "launches_per_step": cnt[k] / reps} for k in tot}
 
 
@@ -377,7 +381,8 @@ def run_b200_arm(a):
     torch.manual_seed(0)
     m = S.VAE(n_input=a.genes, n_batch=a.batches, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT,
               precision=1 if a.precision == "tc" else 0).train()
-    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True)
+    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True,
+                             ddp_mode=a.ddp_mode)
     plan.set_epoch(0)
     order = torch.randperm(a.cells, device=dev)
     n_chunks = a.cells // B
@@ -524,15 +529,25 @@ def run_b200_arm(a):
             "launches_per_step": launches_per_step,
             "roofline": roof, "kernels": kern, "nb_loss_kernel_hbm": logprob, "cpu_baseline": cpu, "final_loss": loss_end,
         }
-    if world > 1:
-        torch.distributed.barrier()
-        torch.distributed.destroy_process_group()
     if line is not None:
         print(json.dumps(line), flush=True)
+    if world > 1:
+        # the step graphs hold captured NCCL kernels: release them before the communicator goes away, and do not
+        # wait on the communicator teardown (it can block on graph-captured collectives)
+        plan._graphs = None
+        torch.cuda.synchronize()
+        torch.distributed.barrier()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
     a = parse()
+    if os.environ.get("SCVI_BENCH_FAULT"):  # debugging aid: dump all Python stacks if the run hangs
+        import faulthandler
+
+        faulthandler.dump_traceback_later(float(os.environ["SCVI_BENCH_FAULT"]), exit=True)
     if a.impl == "reference":
         run_reference_arm(a)
     else:
