@@ -9,9 +9,10 @@ from . import _lib
 from .distributions import NegativeBinomial, ZeroInflatedNegativeBinomial, log_nb_positive, log_zinb_positive
 from .module import MODULE_KEYS, REGISTRY_KEYS, VAE, LossOutput
 from .nn import DecoderSCVI, Encoder, FCLayers, rng_feed
+from .model import SCVI  # noqa: E402  (after the module classes it builds on)
 
 __all__ = [
-    "VAE", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
+    "SCVI", "VAE", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
     "NegativeBinomial", "ZeroInflatedNegativeBinomial", "log_nb_positive", "log_zinb_positive", "rng_feed",
 ]
 __version__ = "0.1.0"

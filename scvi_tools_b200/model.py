@@ -1,0 +1,156 @@
+"""`SCVI`-shaped driver over the B200 kernels: construct -> `train()` -> the post-training getters.
+
+Mirrors the calls a user of `scvi.model.SCVI` makes right around the hot path:
+`train` (reference src/scvi/model/base/_training_mixin.py + src/scvi/train/_trainingplans.py:427-532),
+`get_latent_representation` / `get_elbo` / `get_reconstruction_error`
+(src/scvi/model/base/_vaemixin.py:32-101,196-268,270-383; src/scvi/model/base/_log_likelihood.py:20-136) and
+`get_normalized_expression` (src/scvi/model/base/_rnamixin.py:155-330, the `library_size` / `transform_batch`
+semantics).  The counts live in HBM (`DeviceResidentCounts`); there is no AnnData registry here -- the caller
+hands in the count matrix and the integer batch codes that `AnnDataManager` would have produced.
+"""
+
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from .data import DeviceResidentCounts
+from .module import MODULE_KEYS, VAE
+from .train import FusedTrainingPlan
+
+
+def get_max_epochs_heuristic(n_obs: int, epochs_cap: int = 400, decay_at_n_obs: int = 20_000) -> int:
+    """Reference src/scvi/model/_utils.py `get_max_epochs_heuristic`: min(round(20000 / n_obs * 400), 400)."""
+    return max(1, int(min(round((decay_at_n_obs / n_obs) * epochs_cap), epochs_cap)))
+
+
+class SCVI:
+    """single-cell Variational Inference on a device-resident count matrix.
+
+    Parameters follow `scvi.model.SCVI.__init__` (src/scvi/model/_scvi.py): n_hidden, n_latent, n_layers,
+    dropout_rate, dispersion, gene_likelihood, latent_distribution and further `VAE` keyword arguments.
+    `X`: [n_obs, n_vars] counts (numpy / torch, any device); `batch`: [n_obs] integer batch codes or None.
+    """
+
+    def __init__(self, X, batch=None, n_hidden: int = 128, n_latent: int = 10, n_layers: int = 1,
+                 dropout_rate: float = 0.1, dispersion: str = "gene", gene_likelihood: str = "zinb",
+                 latent_distribution: str = "normal", device="cuda:0", **model_kwargs):
+        self.device = torch.device(device)
+        self.data = X if isinstance(X, DeviceResidentCounts) else DeviceResidentCounts(X, batch=batch, device=self.device)
+        n_batch = int(self.data.batch.max().item()) + 1 if self.data.n_obs else 1
+        self.summary = {"n_obs": self.data.n_obs, "n_vars": self.data.n_vars, "n_batch": n_batch}
+        self.module = VAE(n_input=self.data.n_vars, n_batch=n_batch, n_hidden=n_hidden, n_latent=n_latent,
+                          n_layers=n_layers, dropout_rate=dropout_rate, dispersion=dispersion,
+                          gene_likelihood=gene_likelihood, latent_distribution=latent_distribution,
+                          **model_kwargs).to(self.device)
+        self.is_trained_ = False
+        self.history_: list[dict] = []
+        self._plan: FusedTrainingPlan | None = None
+
+    # ------------------------------------------------------------------ training
+    def train(self, max_epochs: int | None = None, batch_size: int = 128, lr: float = 1e-3, eps: float = 0.01,
+              weight_decay: float = 1e-6, n_epochs_kl_warmup: int | None = 400, n_steps_kl_warmup: int | None = None,
+              max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, shuffle: bool = True, seed: int = 0,
+              process_group=None, use_cuda_graph: bool = True):
+        """`SCVI.train`: `max_epochs` defaults to the reference heuristic; optimizer and KL warm-up defaults are
+        `TrainingPlan`'s (Adam lr 1e-3, eps 0.01, weight decay 1e-6, 400 warm-up epochs).  Returns the per-epoch
+        history (train loss, reconstruction loss, KL per cell)."""
+        if max_epochs is None:
+            max_epochs = get_max_epochs_heuristic(self.data.n_obs)
+        self.module.train()
+        new_plan = self._plan is None or self._plan.B != batch_size or self._plan.pg is not process_group
+        if new_plan:
+            self._plan = FusedTrainingPlan(
+                self.module, self.data, batch_size=batch_size, lr=lr, eps=eps, weight_decay=weight_decay,
+                n_epochs_kl_warmup=n_epochs_kl_warmup, n_steps_kl_warmup=n_steps_kl_warmup,
+                max_kl_weight=max_kl_weight, min_kl_weight=min_kl_weight, seed=seed, use_cuda_graph=use_cuda_graph,
+                process_group=process_group)
+        hist = self._plan.fit(max_epochs=max_epochs, shuffle=shuffle)
+        self.history_.extend(hist)
+        self.module.eval()
+        self.is_trained_ = True
+        return hist
+
+    # ------------------------------------------------------------------ getters
+    def _batches(self, indices, batch_size):
+        n = self.data.n_obs
+        idx = torch.arange(n, device=self.device) if indices is None else torch.as_tensor(
+            np.asarray(indices), dtype=torch.int64, device=self.device)
+        for s in range(0, idx.numel(), batch_size):
+            yield self.data.minibatch(idx[s : s + batch_size])
+
+    @torch.inference_mode()
+    def get_latent_representation(self, indices=None, give_mean: bool = True, batch_size: int = 8192,
+                                  return_dist: bool = False):
+        """Mean of q(z | x) per cell (`give_mean`), a sample otherwise, or (mean, variance) with `return_dist`."""
+        self.module.eval()
+        zs, means, variances = [], [], []
+        for tensors in self._batches(indices, batch_size):
+            out = self.module.inference(**self.module._get_inference_input(tensors))
+            qz = out[MODULE_KEYS.QZ_KEY]
+            if return_dist:
+                means.append(qz.loc)
+                variances.append(qz.scale.square())
+            else:
+                zs.append(qz.loc if give_mean else out[MODULE_KEYS.Z_KEY])
+        if return_dist:
+            return torch.cat(means).cpu().numpy(), torch.cat(variances).cpu().numpy()
+        return torch.cat(zs).cpu().numpy()
+
+    @torch.inference_mode()
+    def get_elbo(self, indices=None, batch_size: int = 8192, return_mean: bool = True):
+        """`-(reconstruction loss + KL)` averaged over the cells (the reference's sign: `-compute_elbo`)."""
+        self.module.eval()
+        vals = []
+        for tensors in self._batches(indices, batch_size):
+            _, _, lo = self.module(tensors, get_inference_input_kwargs={"full_forward_pass": True})
+            vals.append(lo.reconstruction_loss["reconstruction_loss"] + lo.kl_local["kl_divergence_z"]
+                        + lo.kl_local.get("kl_divergence_l", 0.0))
+        v = torch.cat(vals)
+        return -float(v.mean()) if return_mean else -v.cpu().numpy()
+
+    @torch.inference_mode()
+    def get_reconstruction_error(self, indices=None, batch_size: int = 8192, return_mean: bool = True):
+        """`{"reconstruction_loss": -log p(x | z)}` averaged over the cells (or per cell)."""
+        self.module.eval()
+        vals = []
+        for tensors in self._batches(indices, batch_size):
+            _, _, lo = self.module(tensors, loss_kwargs={"kl_weight": 1},
+                                   get_inference_input_kwargs={"full_forward_pass": True})
+            vals.append(lo.reconstruction_loss["reconstruction_loss"])
+        v = torch.cat(vals)
+        return {"reconstruction_loss": float(v.mean()) if return_mean else v.cpu().numpy()}
+
+    @torch.inference_mode()
+    def get_normalized_expression(self, indices=None, transform_batch=None, library_size=1, n_samples: int = 1,
+                                  batch_size: int = 4096, gene_indices=None):
+        """Decoded expression `px_scale * library_size` (`library_size="latent"`: `px_rate`), averaged over the
+        batches in `transform_batch` (None = each cell's own batch) and over `n_samples` posterior draws."""
+        self.module.eval()
+        key = "mu" if library_size == "latent" else "scale"
+        scaling = 1.0 if library_size == "latent" else float(library_size)
+        tb = [None] if transform_batch is None else (list(transform_batch) if np.ndim(transform_batch) else [transform_batch])
+        gsel = None if gene_indices is None else torch.as_tensor(np.asarray(gene_indices), device=self.device)
+        out = []
+        for tensors in self._batches(indices, batch_size):
+            per_batch = []
+            for b in tb:
+                _, gen = self.module(tensors, inference_kwargs={"n_samples": n_samples},
+                                     generative_kwargs={"transform_batch": b}, compute_loss=False)
+                e = gen["px"].get_normalized(key) * scaling
+                if n_samples > 1:
+                    e = e.mean(0)
+                per_batch.append(e if gsel is None else e[..., gsel])
+            out.append(torch.stack(per_batch).mean(0))
+        return torch.cat(out).cpu().numpy()
+
+    # ------------------------------------------------------------------ persistence
+    def state_dict(self):
+        return self.module.state_dict()
+
+    def load_state_dict(self, sd):
+        """Load a state dict with the reference's keys (`scvi.module.VAE.state_dict()`); marks the model trained."""
+        self.module.load_state_dict(sd)
+        self._plan = None  # the parameter arena is rebuilt on the next train()
+        self.is_trained_ = True
+        self.module.eval()

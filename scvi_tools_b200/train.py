@@ -416,7 +416,8 @@ class FusedTrainingPlan:
         """Train for `max_epochs` over this rank's shard; returns the per-epoch history
         (train loss, ELBO pieces per cell) -- the numbers `TrainingPlan` logs."""
         history = []
-        for epoch in range(self.current_epoch, self.current_epoch + max_epochs):
+        first = self.current_epoch
+        for epoch in range(first, first + max_epochs):
             self.set_epoch(epoch)
             order = epoch_indices(self.data.n_obs, self.rank, self.world, epoch, self.seed, shuffle).to(self.dev)
             # a minibatch is a set of cells: ascending row ids inside each one cost nothing (one sort per epoch)
@@ -445,5 +446,5 @@ class FusedTrainingPlan:
                                 "reconstruction_loss": float(a[1]) / max(n_cells, 1),
                                 "kl_local": float(a[2]) / max(n_cells, 1), "n_cells": n_cells,
                                 "kl_weight": float(self.klw.item())})
-        self.current_epoch += max_epochs
+        self.current_epoch = first + max_epochs
         return history

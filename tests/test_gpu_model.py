@@ -1,0 +1,85 @@
+"""GPU: the `SCVI`-shaped driver (train + post-training getters) against quantities recorded from the
+unmodified reference module in eval mode (tests/golden/getters_*.npz, oracle/make_golden_getters.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import scvi_oracle as O
+from tests._golden import GOLD, load_vae_case, max_rel, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _model_from_case(name):
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.model import SCVI
+
+    P, inp, _ = load_vae_case(name)
+    model = SCVI(inp["x"], batch=inp["batch"].reshape(-1), gene_likelihood=inp["likelihood"])
+    assert model.summary["n_batch"] == inp["n_batch"]
+    sd = model.state_dict()
+    sd.update({k: v.clone() for k, v in P.items()})
+    model.load_state_dict(sd)
+    gold = np.load(os.path.join(GOLD, f"getters_{name}.npz"))
+    return S, model, inp, gold
+
+
+@pytest.mark.parametrize("name", ["c1_zinb", "onebatch_nb"])
+def test_getters_match_reference_eval_mode(name):
+    S, model, inp, gold = _model_from_case(name)
+    noise = torch.from_numpy(inp["noise"])
+    qm, qv = model.get_latent_representation(return_dist=True)
+    assert rel_err(qm, gold["qz_mean"]) < 1e-5 and rel_err(qv, gold["qz_var"]) < 1e-5
+    assert rel_err(model.get_latent_representation(), gold["qz_mean"]) < 1e-5
+    # indices + small batches walk the same cells
+    sub = np.array([5, 3, 47, 0, 41])
+    assert rel_err(model.get_latent_representation(indices=sub, batch_size=2), gold["qz_mean"][sub]) < 1e-5
+    with S.rng_feed(noise=[noise]):
+        elbo = model.get_elbo(return_mean=False)
+    assert max_rel(elbo, -(gold["reconst"] + gold["kl_z"])) < 1e-5
+    with S.rng_feed(noise=[noise]):
+        assert abs(model.get_elbo() + float((gold["reconst"] + gold["kl_z"]).mean())) < 1e-5 * abs(float(gold["reconst"].mean()))
+    with S.rng_feed(noise=[noise]):
+        rec = model.get_reconstruction_error(return_mean=False)["reconstruction_loss"]
+    assert max_rel(rec, gold["reconst"]) < 1e-5
+    with S.rng_feed(noise=[noise]):
+        scale = model.get_normalized_expression()
+    assert rel_err(scale, gold["px_scale"]) < 1e-5
+    np.testing.assert_allclose(scale.sum(1), 1.0, rtol=1e-5)
+    with S.rng_feed(noise=[noise]):
+        assert rel_err(model.get_normalized_expression(library_size=1e4), 1e4 * gold["px_scale"]) < 1e-5
+    with S.rng_feed(noise=[noise]):
+        assert rel_err(model.get_normalized_expression(library_size="latent"), gold["px_mu"]) < 1e-5
+    nb = inp["n_batch"]
+    with S.rng_feed(noise=[noise] * nb):
+        tb = model.get_normalized_expression(transform_batch=list(range(nb)), gene_indices=[0, 7, 9])
+    want = np.mean([gold[f"px_scale_tb{b}"] for b in range(nb)], axis=0)[:, [0, 7, 9]]
+    assert rel_err(tb, want) < 1e-5
+    with S.rng_feed(noise=[noise]):
+        assert rel_err(model.get_normalized_expression(transform_batch=nb - 1), gold[f"px_scale_tb{nb - 1}"]) < 1e-5
+
+
+def test_train_then_getters_end_to_end():
+    """`SCVI(...).train()` lowers the ELBO; getters run on the trained, arena-backed parameters; a state-dict
+    round trip into a fresh model reproduces them."""
+    from scvi_tools_b200.model import SCVI, get_max_epochs_heuristic
+
+    assert get_max_epochs_heuristic(400) == 400 and get_max_epochs_heuristic(1_000_000) == 8
+    X, batch = O.synthetic_iid(1200, 200, 3, seed=2)
+    torch.manual_seed(0)
+    model = SCVI(X, batch=batch, gene_likelihood="nb")
+    before = model.get_reconstruction_error()["reconstruction_loss"]
+    hist = model.train(max_epochs=8, batch_size=256)
+    assert model.is_trained_ and len(hist) == 8 and hist[-1]["train_loss"] < hist[0]["train_loss"]
+    after = model.get_reconstruction_error()["reconstruction_loss"]
+    assert np.isfinite(after) and after < before
+    z = model.get_latent_representation()
+    assert z.shape == (1200, 10) and np.isfinite(z).all()
+    assert np.isfinite(model.get_elbo())
+    fresh = SCVI(X, batch=batch, gene_likelihood="nb")
+    fresh.load_state_dict({k: v.clone() for k, v in model.state_dict().items()})
+    np.testing.assert_allclose(fresh.get_latent_representation(), z, rtol=1e-6, atol=1e-6)
+    hist2 = model.train(max_epochs=2, batch_size=256)  # continues from the same plan / optimizer state
+    assert hist2[0]["epoch"] == 8
