@@ -51,6 +51,8 @@ def parse():
                          "as FusedTrainingPlan.fit does -- same cells, better DRAM page / TLB locality)")
     ap.add_argument("--ddp-mode", default="split", choices=["graph", "overlap", "split"],
                     help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode)")
+    ap.add_argument("--e2e-dtype", default="auto", choices=["auto", "u16", "f32"],
+                    help="host count type of the e2e leg: auto = narrowest lossless (uint8 / uint16 / float32)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
@@ -421,40 +423,31 @@ def run_b200_arm(a):
     value = K * B * world / (ms / 1e3)
 
     # ---- end to end: pinned host minibatches -> H2D (copy stream, double buffered) -> step -> loss D2H
+    # The host side keeps the counts in the narrowest lossless integer type (HostStreamedCounts: uint8 here,
+    # uint16 for counts >= 256, fp32 otherwise); the device expands them to the fp32 rows bit-exactly.
+    from scvi_tools_b200.data import HostStreamedCounts, narrowest_count_dtype
+
     n_host = 4
-    host_x = [torch.from_numpy(synth_counts_host(B, a.genes, seed=100 + i)).pin_memory() for i in range(n_host)]
+    host_f32 = [torch.from_numpy(synth_counts_host(B, a.genes, seed=100 + i)) for i in range(n_host)]
+    hdt = torch.float32 if a.e2e_dtype == "f32" else max(
+        (narrowest_count_dtype(x) for x in host_f32), key=lambda d: torch.empty(0, dtype=d).element_size())
+    if a.e2e_dtype == "u16" and hdt == torch.uint8:
+        hdt = torch.uint16
+    host_x = [x.to(hdt).pin_memory() for x in host_f32]
     host_b = [torch.randint(0, a.batches, (B,), dtype=torch.int64).pin_memory() for i in range(n_host)]
-    stage = DeviceResidentCounts(torch.zeros(2 * B, a.genes), batch=torch.zeros(2 * B, dtype=torch.int64), device=dev)
-    plan.data = stage
-    plan.batch_cols = torch.zeros(2 * B, dtype=torch.int32, device=dev)
-    plan._graphs = None  # re-capture against the staging matrix
-    copy_stream = torch.cuda.Stream()
-    ready = [torch.cuda.Event(), torch.cuda.Event()]
-    freed = [torch.cuda.Event(), torch.cuda.Event()]
-    half_idx = [torch.arange(B, device=dev), torch.arange(B, 2 * B, device=dev)]
+    feeder = HostStreamedCounts(torch.zeros(1, a.genes), batch=None, batch_size=B, device=dev, dtype=hdt)
+    plan.attach_streamed(feeder)
     loss_host = torch.zeros(3).pin_memory()
 
-    def h2d(i):
-        s = i % 2
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(freed[s])
-            stage.X[s * B : (s + 1) * B].copy_(host_x[i % n_host], non_blocking=True)
-            stage.batch[s * B : (s + 1) * B].copy_(host_b[i % n_host], non_blocking=True)
-            plan.batch_cols[s * B : (s + 1) * B] = (stage.batch[s * B : (s + 1) * B] + plan.L).to(torch.int32)
-            ready[s].record(copy_stream)
-
     def e2e_loop(n):
-        for s in range(2):
-            freed[s].record()
-        h2d(0)
+        feeder.submit(0, host_x=host_x[0], host_b=host_b[0])
         for i in range(n):
-            if i + 1 < n:
-                h2d(i + 1)
             s = i % 2
-            torch.cuda.current_stream().wait_event(ready[s])
-            plan.training_step(half_idx[s])
-            freed[s].record()
+            plan.training_step(feeder.acquire(s))
+            feeder.release(s)
             loss_host.copy_(plan.out3, non_blocking=True)
+            if i + 1 < n:  # the next minibatch crosses PCIe while this step computes (its slot was freed by step i-1)
+                feeder.submit((i + 1) % 2, host_x=host_x[(i + 1) % n_host], host_b=host_b[(i + 1) % n_host])
             torch.cuda.current_stream().synchronize()  # the user reads the loss every step
 
     e2e_loop(W)
@@ -471,8 +464,11 @@ def run_b200_arm(a):
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         ms_e2e = float(t)
     e2e = {"value": K * B * world / (ms_e2e / 1e3), "unit": "cells/s",
-           "h2d_bytes_per_step": B * a.genes * 4 + B * 8, "d2h_bytes_per_step": 12,
-           "how": "pinned host minibatch -> cudaMemcpyAsync on a copy stream (double buffered) -> fused step -> loss D2H + sync each step"}
+           "h2d_bytes_per_step": B * a.genes * host_x[0].element_size() + B * 8, "d2h_bytes_per_step": 12,
+           "host_dtype": str(hdt).replace("torch.", ""),
+           "how": "pinned host minibatch in the narrowest lossless count type -> cudaMemcpyAsync on a copy stream "
+                  "(double buffered) -> exact expansion to fp32 rows (scvi_gather_rows_u8/_u16) -> fused step -> "
+                  "loss D2H + sync each step"}
 
     # ---- per-kernel roofline (rank 0)
     line = None

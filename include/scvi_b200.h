@@ -69,9 +69,14 @@ int scvi_gather_rows(const float* X, int64_t n_rows, int64_t G, int64_t ldx, con
 /* out[b] = src[idx[b]] for the int64 `batch` / `labels` columns (shape (B,1) in the reference) */
 int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int64_t B, int64_t* out,
                     void* stream);
-/* same gather from a uint16-compressed resident matrix (counts < 65536), densified to fp32 */
+/* same gather from a compact integer matrix -- resident in HBM, or a minibatch staged from pinned host
+ * memory -- in the narrowest lossless count type (uint16: counts < 65536; uint8: counts < 256), densified
+ * to fp32 exactly (`data[indexes].astype(float32)`, src/scvi/data/_anntorchdataset.py:143-147, for an
+ * integer-typed `adata.X`).  idx == NULL means the identity (expand rows 0..B-1 in place order). */
 int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t ldx,
                          const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
+int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx,
+                        const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
 
 /* ---- a7/a8: standalone likelihood kernels ("NB-loss kernel") --------------------------
  * replace log_nb_positive / log_zinb_positive

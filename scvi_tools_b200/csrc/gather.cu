@@ -26,15 +26,58 @@ __global__ void gather_rows_kernel(const float* __restrict__ X, int64_t ldx, con
   }
 }
 
-__global__ void gather_rows_u16_kernel(const uint16_t* __restrict__ X, int64_t ldx,
-                                       const int64_t* __restrict__ idx, int64_t B, int64_t G,
-                                       float* __restrict__ out, int64_t ldo) {
+// Compact resident / staged counts: T = uint8_t or uint16_t (the narrowest integer type that holds the
+// counts losslessly).  out[b, :] = (float)X[idx ? idx[b] : b, :] -- exact, every such integer is an fp32 value.
+// VEC: one 16-byte load (16 / 8 counts) per thread and 4 / 2 float4 stores; rows must be 16-byte aligned.
+template <typename T, bool VEC>
+__global__ void gather_rows_int_kernel(const T* __restrict__ X, int64_t ldx, const int64_t* __restrict__ idx,
+                                       int64_t B, int64_t G, float* __restrict__ out, int64_t ldo) {
+  constexpr int PER = 16 / (int)sizeof(T);  // counts per 16-byte load
   for (int64_t b = blockIdx.y; b < B; b += gridDim.y) {
-    const uint16_t* src = X + idx[b] * ldx;
+    const T* src = X + (idx ? idx[b] : b) * ldx;
     float* dst = out + b * ldo;
-    for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
-      dst[i] = (float)src[i];
+    if (VEC) {
+      const int64_t nv = G / PER;
+      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (int64_t)gridDim.x * blockDim.x) {
+        uint4 raw;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w)
+                     : "l"(src + PER * i));
+        const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+        float4* d4 = reinterpret_cast<float4*>(dst + PER * i);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (sizeof(T) == 1) {
+            d4[k] = make_float4((float)(w[k] & 0xffu), (float)((w[k] >> 8) & 0xffu), (float)((w[k] >> 16) & 0xffu),
+                                (float)(w[k] >> 24));
+          } else if ((k & 1) == 0) {
+            d4[k >> 1] = make_float4((float)(w[k] & 0xffffu), (float)(w[k] >> 16), (float)(w[k + 1] & 0xffffu),
+                                     (float)(w[k + 1] >> 16));
+          }
+        }
+      }
+      for (int64_t i = nv * PER + blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = (float)src[i];
+    } else {
+      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = (float)src[i];
+    }
   }
+}
+
+template <typename T>
+static int launch_gather_int(const T* X, int64_t ldx, const int64_t* idx, int64_t B, int64_t G, float* out,
+                             int64_t ldo, cudaStream_t st, const char* name) {
+  constexpr int PER = 16 / (int)sizeof(T);
+  const bool vec = (ldx % PER == 0) && ((uintptr_t)X % 16 == 0) && (ldo % 4 == 0) && ((uintptr_t)out % 16 == 0) &&
+                   G >= PER;
+  dim3 grid((unsigned)std::min<int64_t>(cdiv(G, (vec ? PER : 1) * 2 * 256), 64), (unsigned)std::min<int64_t>(B, 65535));
+  if (vec)
+    gather_rows_int_kernel<T, true><<<grid, 256, 0, st>>>(X, ldx, idx, B, G, out, ldo);
+  else
+    gather_rows_int_kernel<T, false><<<grid, 256, 0, st>>>(X, ldx, idx, B, G, out, ldo);
+  SCVI_LAUNCH_CHECK(name);
+  return SCVI_OK;
 }
 
 __global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ idx, int64_t B,
@@ -70,13 +113,21 @@ int scvi_gather_rows(const float* X, int64_t n_rows, int64_t G, int64_t ldx, con
 int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx,
                          int64_t B, float* out, int64_t ldo, void* stream) {
   using namespace scvi;
-  SCVI_REQUIRE(X && idx && out, "scvi_gather_rows_u16: NULL pointer");
+  SCVI_REQUIRE(X && out, "scvi_gather_rows_u16: NULL pointer");
   SCVI_REQUIRE(n_rows >= 0 && G >= 0 && B >= 0 && ldx >= G && ldo >= G, "scvi_gather_rows_u16: bad shape");
+  SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_u16: identity expansion of more rows than the matrix holds");
   if (B == 0 || G == 0) return SCVI_OK;
-  dim3 grid((unsigned)std::min<int64_t>(cdiv(G, 16 * 256), 64), (unsigned)std::min<int64_t>(B, 65535));
-  gather_rows_u16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ldx, idx, B, G, out, ldo);
-  SCVI_LAUNCH_CHECK("scvi_gather_rows_u16");
-  return SCVI_OK;
+  return launch_gather_int<uint16_t>(X, ldx, idx, B, G, out, ldo, (cudaStream_t)stream, "scvi_gather_rows_u16");
+}
+
+int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx,
+                        int64_t B, float* out, int64_t ldo, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(X && out, "scvi_gather_rows_u8: NULL pointer");
+  SCVI_REQUIRE(n_rows >= 0 && G >= 0 && B >= 0 && ldx >= G && ldo >= G, "scvi_gather_rows_u8: bad shape");
+  SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_u8: identity expansion of more rows than the matrix holds");
+  if (B == 0 || G == 0) return SCVI_OK;
+  return launch_gather_int<uint8_t>(X, ldx, idx, B, G, out, ldo, (cudaStream_t)stream, "scvi_gather_rows_u8");
 }
 
 int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int64_t B, int64_t* out,

@@ -45,19 +45,131 @@ def epoch_indices(n_obs: int, rank: int, world: int, epoch: int, seed: int = 0, 
     return idx[rank:total:world].contiguous()
 
 
+def narrowest_count_dtype(X) -> torch.dtype:
+    """uint8 / uint16 when every entry of `X` is an integer in range (the expansion to fp32 is then exact),
+    else float32."""
+    X = torch.as_tensor(X)
+    if X.numel() == 0:
+        return torch.float32
+    lo, hi = float(X.min()), float(X.max())
+    if lo < 0 or hi >= 65536:
+        return torch.float32
+    if X.dtype.is_floating_point and not bool((X == X.round()).all()):
+        return torch.float32
+    return torch.uint8 if hi < 256 else torch.uint16
+
+
+class HostStreamedCounts:
+    """Count matrix kept in pinned HOST memory (for data that should not, or does not, live in HBM) and fed to
+    the training step minibatch by minibatch -- the reference's `AnnDataLoader` route
+    (src/scvi/dataloaders/_ann_dataloader.py:21-138 + the Lightning host->device copy), made PCIe-frugal: the
+    matrix is stored once in the narrowest lossless integer type (`narrowest_count_dtype`), a minibatch crosses
+    PCIe in that type on a copy stream (double buffered) and `scvi_gather_rows_u8/_u16` expands it to the fp32
+    rows the kernels read -- bit-identical to `data[indexes].astype(float32)`.
+
+    `stage` is a `DeviceResidentCounts` of 2 x batch_size rows; the plan trains on rows `slot*B .. slot*B+n`.
+    """
+
+    def __init__(self, X, batch=None, batch_size: int = 128, device="cuda", dtype: torch.dtype | None = None):
+        self.dev = torch.device(device)
+        X = torch.as_tensor(np.asarray(X.toarray()) if hasattr(X, "toarray") else X)
+        self.dtype = narrowest_count_dtype(X) if dtype is None else dtype
+        self.host = X.to(self.dtype).contiguous().pin_memory()
+        n = X.shape[0]
+        b = torch.zeros(n, dtype=torch.int64) if batch is None else torch.as_tensor(np.asarray(batch)).reshape(-1).to(torch.int64)
+        self.host_batch = b.contiguous().pin_memory()
+        self.B = int(batch_size)
+        G = X.shape[1]
+        self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G), batch=torch.zeros(2 * self.B, dtype=torch.int64),
+                                          device=self.dev)
+        self._compact = None if self.dtype == torch.float32 else torch.empty(2 * self.B, G, dtype=self.dtype, device=self.dev)
+        self._pin = [torch.empty(self.B, G, dtype=self.dtype).pin_memory() for _ in range(2)]
+        self._pin_b = [torch.empty(self.B, dtype=torch.int64).pin_memory() for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=self.dev)
+        self.ready = [torch.cuda.Event(), torch.cuda.Event()]
+        self.freed = [torch.cuda.Event(), torch.cuda.Event()]
+        for e in self.freed:
+            e.record()
+        self.slot_rows = [torch.arange(self.B, device=self.dev), torch.arange(self.B, 2 * self.B, device=self.dev)]
+        self.on_batch = None  # callable(lo, n) run on the copy stream after a slot's batch codes landed
+
+    @property
+    def n_obs(self) -> int:
+        return self.host.shape[0]
+
+    @property
+    def n_vars(self) -> int:
+        return self.host.shape[1]
+
+    @property
+    def h2d_bytes_per_row(self) -> int:
+        return self.n_vars * self.host.element_size() + 8
+
+    def submit(self, slot: int, rows=None, host_x: torch.Tensor | None = None, host_b: torch.Tensor | None = None) -> int:
+        """Enqueue the copy of one minibatch into staging slot `slot` (0 / 1): either rows `rows` (host int64
+        indices) of the host matrix -- gathered into a pinned buffer first -- or an already formed pinned
+        minibatch (`host_x` in this object's dtype, `host_b`).  Returns the number of cells."""
+        if host_x is None:
+            rows = torch.as_tensor(rows, dtype=torch.int64)
+            n = rows.numel()
+            self.freed[slot].synchronize()  # the pinned buffer of this slot is reused
+            torch.index_select(self.host, 0, rows, out=self._pin[slot][:n])
+            torch.index_select(self.host_batch, 0, rows, out=self._pin_b[slot][:n])
+            host_x, host_b = self._pin[slot][:n], self._pin_b[slot][:n]
+        n = host_x.shape[0]
+        lo = slot * self.B
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.freed[slot])
+            if self._compact is None:
+                self.stage.X[lo : lo + n].copy_(host_x, non_blocking=True)
+            else:
+                self._compact[lo : lo + n].copy_(host_x, non_blocking=True)
+                ops.gather_rows(self._compact[lo : lo + n], None, out=self.stage.X[lo : lo + n])
+            self.stage.batch[lo : lo + n].copy_(host_b, non_blocking=True)
+            if self.on_batch is not None:
+                self.on_batch(lo, n)
+            self.ready[slot].record(self.copy_stream)
+        return n
+
+    def minibatch(self, idx) -> dict:
+        """Synchronous `{X, batch, labels}` dict of the cells `idx` (getters; same contract as
+        `DeviceResidentCounts.minibatch`)."""
+        rows = torch.as_tensor(idx).to("cpu", torch.int64).reshape(-1)
+        x = self.host.index_select(0, rows).to(self.dev)
+        X = x if self.dtype == torch.float32 else ops.gather_rows(x, None)
+        b = self.host_batch.index_select(0, rows).to(self.dev).view(-1, 1)
+        return {"X": X, "batch": b, "labels": torch.zeros_like(b)}
+
+    def acquire(self, slot: int, n: int | None = None) -> torch.Tensor:
+        """Make the current stream wait for slot `slot`; returns the stage row ids of its cells."""
+        torch.cuda.current_stream().wait_event(self.ready[slot])
+        return self.slot_rows[slot] if n is None or n == self.B else self.slot_rows[slot][:n]
+
+    def release(self, slot: int):
+        """Call after the step that read slot `slot` has been enqueued."""
+        self.freed[slot].record()
+
+
 class DeviceResidentCounts:
     """Count matrix [N, G] (fp32, or uint16-compressed) + batch / label columns resident in HBM."""
 
-    def __init__(self, X, batch=None, labels=None, device="cuda", compress_u16: bool = False):
+    def __init__(self, X, batch=None, labels=None, device="cuda", compress_u16: bool = False,
+                 compress: str | None = None):
         dev = torch.device(device)
         if isinstance(X, np.ndarray):
             X = torch.from_numpy(X)
         if hasattr(X, "toarray"):  # scipy sparse: densify once on the host (reference :152 does it per batch)
             X = torch.from_numpy(np.asarray(X.toarray()))
-        if compress_u16:
+        if compress == "auto":
+            X = X.to(narrowest_count_dtype(X))
+        elif compress_u16 or compress == "u16":
             if float(X.max()) >= 65536 or float(X.min()) < 0:
                 raise ValueError("uint16 residency needs counts in [0, 65535]")
             X = X.to(torch.uint16)
+        elif compress == "u8":
+            if float(X.max()) >= 256 or float(X.min()) < 0:
+                raise ValueError("uint8 residency needs counts in [0, 255]")
+            X = X.to(torch.uint8)
         elif X.dtype != torch.float32:
             X = X.to(torch.float32)
         self.X = X.to(dev).contiguous()

@@ -14,7 +14,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from .data import DeviceResidentCounts
+from .data import DeviceResidentCounts, HostStreamedCounts
 from .module import MODULE_KEYS, VAE
 from .train import FusedTrainingPlan
 
@@ -30,14 +30,19 @@ class SCVI:
     Parameters follow `scvi.model.SCVI.__init__` (src/scvi/model/_scvi.py): n_hidden, n_latent, n_layers,
     dropout_rate, dispersion, gene_likelihood, latent_distribution and further `VAE` keyword arguments.
     `X`: [n_obs, n_vars] counts (numpy / torch, any device); `batch`: [n_obs] integer batch codes or None.
+    `X` may also be a `DeviceResidentCounts` (counts in HBM, the default built from an array) or a
+    `HostStreamedCounts` (counts stay in pinned host memory and stream over PCIe in compact integer form).
     """
 
     def __init__(self, X, batch=None, n_hidden: int = 128, n_latent: int = 10, n_layers: int = 1,
                  dropout_rate: float = 0.1, dispersion: str = "gene", gene_likelihood: str = "zinb",
                  latent_distribution: str = "normal", device="cuda:0", **model_kwargs):
         self.device = torch.device(device)
-        self.data = X if isinstance(X, DeviceResidentCounts) else DeviceResidentCounts(X, batch=batch, device=self.device)
-        n_batch = int(self.data.batch.max().item()) + 1 if self.data.n_obs else 1
+        self.data = X if isinstance(X, (DeviceResidentCounts, HostStreamedCounts)) else DeviceResidentCounts(
+            X, batch=batch, device=self.device)
+        self.streamed = isinstance(self.data, HostStreamedCounts)
+        codes = self.data.host_batch if self.streamed else self.data.batch
+        n_batch = int(codes.max().item()) + 1 if self.data.n_obs else 1
         self.summary = {"n_obs": self.data.n_obs, "n_vars": self.data.n_vars, "n_batch": n_batch}
         self.module = VAE(n_input=self.data.n_vars, n_batch=n_batch, n_hidden=n_hidden, n_latent=n_latent,
                           n_layers=n_layers, dropout_rate=dropout_rate, dispersion=dispersion,
@@ -59,13 +64,19 @@ class SCVI:
             max_epochs = get_max_epochs_heuristic(self.data.n_obs)
         self.module.train()
         new_plan = self._plan is None or self._plan.B != batch_size or self._plan.pg is not process_group
+        if self.streamed and self.data.B != batch_size:
+            raise ValueError(f"HostStreamedCounts was built for batch_size={self.data.B}, train() got {batch_size}")
         if new_plan:
             self._plan = FusedTrainingPlan(
-                self.module, self.data, batch_size=batch_size, lr=lr, eps=eps, weight_decay=weight_decay,
+                self.module, self.data.stage if self.streamed else self.data, batch_size=batch_size, lr=lr, eps=eps,
+                weight_decay=weight_decay,
                 n_epochs_kl_warmup=n_epochs_kl_warmup, n_steps_kl_warmup=n_steps_kl_warmup,
                 max_kl_weight=max_kl_weight, min_kl_weight=min_kl_weight, seed=seed, use_cuda_graph=use_cuda_graph,
                 process_group=process_group)
-        hist = self._plan.fit(max_epochs=max_epochs, shuffle=shuffle)
+        if self.streamed:
+            hist = self._plan.fit_streamed(self.data, max_epochs=max_epochs, shuffle=shuffle)
+        else:
+            hist = self._plan.fit(max_epochs=max_epochs, shuffle=shuffle)
         self.history_.extend(hist)
         self.module.eval()
         self.is_trained_ = True
@@ -74,8 +85,9 @@ class SCVI:
     # ------------------------------------------------------------------ getters
     def _batches(self, indices, batch_size):
         n = self.data.n_obs
-        idx = torch.arange(n, device=self.device) if indices is None else torch.as_tensor(
-            np.asarray(indices), dtype=torch.int64, device=self.device)
+        idev = "cpu" if self.streamed else self.device
+        idx = torch.arange(n, device=idev) if indices is None else torch.as_tensor(
+            np.asarray(indices), dtype=torch.int64, device=idev)
         for s in range(0, idx.numel(), batch_size):
             yield self.data.minibatch(idx[s : s + batch_size])
 

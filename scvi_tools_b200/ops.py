@@ -52,22 +52,32 @@ def _ws(nbytes, device):
 # --------------------------------------------------------------------------------------
 # a1: gather
 # --------------------------------------------------------------------------------------
-def gather_rows(X: torch.Tensor, idx: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
-    """``X[idx].astype(float32)`` on the device (reference src/scvi/data/_anntorchdataset.py:143-147)."""
-    idx = _check(idx, "idx", torch.int64).contiguous()
-    B, G = idx.numel(), X.shape[1]
+def gather_rows(X: torch.Tensor, idx: torch.Tensor | None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """``X[idx].astype(float32)`` on the device (reference src/scvi/data/_anntorchdataset.py:143-147).
+    ``X`` is float32, or a compact uint16 / uint8 count matrix (expanded exactly); ``idx=None`` with a
+    compact ``X`` expands all its rows in order (the staged-minibatch case)."""
+    if idx is None:
+        if X.dtype == torch.float32:
+            raise TypeError("gather_rows: idx=None (expand in place order) is for compact integer matrices")
+        B = X.shape[0]
+    else:
+        idx = _check(idx, "idx", torch.int64).contiguous()
+        B = idx.numel()
+    G = X.shape[1]
     if out is None:
         out = torch.empty(B, G, dtype=torch.float32, device=X.device)
     if B == 0:
         return out
+    ip = _ptr(idx) if idx is not None else None
     if X.dtype == torch.float32:
         X = _rowmajor(X, "X")
-        call("scvi_gather_rows", _ptr(X), X.shape[0], G, X.stride(0), _ptr(idx), B, _ptr(out), out.stride(0), _stream())
-    elif X.dtype == torch.uint16:
-        X = _rowmajor(X, "X", torch.uint16)
-        call("scvi_gather_rows_u16", _ptr(X), X.shape[0], G, X.stride(0), _ptr(idx), B, _ptr(out), out.stride(0), _stream())
+        call("scvi_gather_rows", _ptr(X), X.shape[0], G, X.stride(0), ip, B, _ptr(out), out.stride(0), _stream())
+    elif X.dtype in (torch.uint16, torch.uint8):
+        X = _rowmajor(X, "X", X.dtype)
+        fn = "scvi_gather_rows_u16" if X.dtype == torch.uint16 else "scvi_gather_rows_u8"
+        call(fn, _ptr(X), X.shape[0], G, X.stride(0), ip, B, _ptr(out), out.stride(0), _stream())
     else:
-        raise TypeError(f"resident count matrix must be float32 or uint16, got {X.dtype}")
+        raise TypeError(f"count matrix must be float32, uint16 or uint8, got {X.dtype}")
     return out
 
 

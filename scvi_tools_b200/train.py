@@ -412,6 +412,54 @@ class FusedTrainingPlan:
         self.global_step += 1
         return self.out3
 
+    def attach_streamed(self, host):
+        """Train from pinned-host minibatches (`HostStreamedCounts`): the step reads rows of `host.stage`, which
+        the copy stream fills one slot ahead of the compute stream."""
+        if host.B != self.B or host.n_vars != self.G:
+            raise ValueError("HostStreamedCounts batch size / gene count differ from the plan's")
+        self.data = host.stage
+        self.batch_cols = torch.zeros(2 * self.B, dtype=torch.int32, device=self.dev)
+        L = self.L
+
+        def batch_codes_to_columns(lo, n):  # runs on the copy stream, right after the batch codes landed
+            self.batch_cols[lo : lo + n].copy_(host.stage.batch[lo : lo + n] + L)
+
+        host.on_batch = batch_codes_to_columns
+        self._graphs = None  # re-capture against the staging matrix
+        self.host = host
+
+    def fit_streamed(self, host, max_epochs: int, shuffle: bool = True, drop_last: bool = False):
+        """`fit` for host-resident counts: minibatch i+1 crosses PCIe (compact integer rows) while step i runs."""
+        if getattr(self, "host", None) is not host:
+            self.attach_streamed(host)
+        history = []
+        first = self.current_epoch
+        for epoch in range(first, first + max_epochs):
+            self.set_epoch(epoch)
+            order = epoch_indices(host.n_obs, self.rank, self.world, epoch, self.seed, shuffle)
+            chunks = [order[s : s + self.B] for s in range(0, order.numel(), self.B)]
+            chunks = [c.sort().values for c in chunks if not (c.numel() < self.B and (drop_last or c.numel() < 2))]
+            acc = torch.zeros(3, dtype=torch.float64, device=self.dev)
+            n_cells = 0
+            if chunks:
+                host.submit(0, chunks[0])
+            for i, c in enumerate(chunks):
+                rows = host.acquire(i % 2, c.numel())
+                out = self.training_step(rows)
+                host.release(i % 2)
+                if i + 1 < len(chunks):  # host gather + H2D of the next minibatch overlap this step
+                    host.submit((i + 1) % 2, chunks[i + 1])
+                acc[0] += out[0].double() * c.numel()
+                acc[1:] += out[1:].double()
+                n_cells += c.numel()
+            a = acc.cpu()
+            history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
+                            "reconstruction_loss": float(a[1]) / max(n_cells, 1),
+                            "kl_local": float(a[2]) / max(n_cells, 1), "n_cells": n_cells,
+                            "kl_weight": float(self.klw.item())})
+        self.current_epoch = first + max_epochs
+        return history
+
     def fit(self, max_epochs: int, shuffle: bool = True, drop_last: bool = False, log_every_epoch: bool = True):
         """Train for `max_epochs` over this rank's shard; returns the per-epoch history
         (train loss, ELBO pieces per cell) -- the numbers `TrainingPlan` logs."""

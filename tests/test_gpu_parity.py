@@ -189,6 +189,36 @@ def test_gather_bit_exact():
     assert empty.shape == (0, 2000)
 
 
+@pytest.mark.parametrize("G", [2000, 333, 16, 5])
+@pytest.mark.parametrize("dt", ["u8", "u16"])
+def test_compact_count_gather_bit_exact(G, dt):
+    """uint8 / uint16 count matrices (resident or staged from pinned host memory) expand to exactly the
+    fp32 rows `data[indexes].astype(float32)` gives, with an index (gather) and without (in-order expand);
+    vectorised and scalar tails, unaligned row pitches, extreme values."""
+    from scvi_tools_b200 import ops
+    from scvi_tools_b200.data import narrowest_count_dtype
+
+    rng = np.random.default_rng(G)
+    hi = 256 if dt == "u8" else 65536
+    npdt = np.uint8 if dt == "u8" else np.uint16
+    X = rng.integers(0, hi, size=(257, G)).astype(npdt)
+    X[0, :] = hi - 1
+    X[1, :] = 0
+    Xd = torch.from_numpy(X).to(dev())
+    assert narrowest_count_dtype(torch.from_numpy(X.astype(np.float32))) == (torch.uint8 if dt == "u8" else torch.uint16)
+    for B in (1, 77, 257):
+        idx = rng.integers(0, X.shape[0], size=B)
+        got = ops.gather_rows(Xd, torch.from_numpy(idx).to(dev()))
+        assert got.dtype == torch.float32 and np.array_equal(got.cpu().numpy(), X[idx].astype(np.float32))
+    assert np.array_equal(ops.gather_rows(Xd, None).cpu().numpy(), X.astype(np.float32))
+    # a row-sliced view (rows 3..) and a column-sliced view (pitch > G, odd offsets -> scalar path)
+    assert np.array_equal(ops.gather_rows(Xd[3:40], None).cpu().numpy(), X[3:40].astype(np.float32))
+    if G > 8:
+        assert np.array_equal(ops.gather_rows(Xd[:, 1 : G - 2], None).cpu().numpy(), X[:, 1 : G - 2].astype(np.float32))
+    assert narrowest_count_dtype(torch.tensor([[0.5, 1.0]])) == torch.float32
+    assert narrowest_count_dtype(torch.tensor([[70000.0]])) == torch.float32
+
+
 @pytest.mark.parametrize(("B", "G", "nb", "lik"), [(300, 2000, 8, "zinb"), (129, 4000, 32, "nb"), (64, 512, 2, "zinb")])
 def test_vae_step_vs_oracle_seeded(B, G, nb, lik):
     """BASELINE.json configs[1]/[2] shapes (G=2000 zinb 8 batches, G=4000 nb 32 batches) at an

@@ -106,6 +106,36 @@ def test_graph_training_learns_and_is_finite():
     assert np.isfinite(float(lo.loss))
 
 
+@pytest.mark.parametrize("count_max", [40, 1000])
+def test_streamed_host_counts_train_like_resident_counts(count_max):
+    """`HostStreamedCounts` (pinned host matrix in uint8 / uint16, double-buffered H2D, on-device expansion)
+    feeds the plan the same fp32 rows as the HBM-resident matrix: identical weights after two epochs,
+    ragged last minibatch included."""
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.data import DeviceResidentCounts, HostStreamedCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+
+    X, batch = O.synthetic_iid(700, 192, 3, seed=2)
+    X = np.minimum(X * (count_max / 40.0), count_max).round().astype(np.float32)
+    out = []
+    for streamed in (False, True):
+        torch.manual_seed(0)
+        m = S.VAE(n_input=192, n_batch=3).train()
+        if streamed:
+            host = HostStreamedCounts(X, batch=batch, batch_size=256, device="cuda:0")
+            assert host.dtype == (torch.uint8 if count_max < 256 else torch.uint16)
+            plan = FusedTrainingPlan(m, host.stage, batch_size=256, seed=3)
+            hist = plan.fit_streamed(host, max_epochs=2)
+        else:
+            plan = FusedTrainingPlan(m, DeviceResidentCounts(X, batch=batch, device="cuda:0"), batch_size=256, seed=3)
+            hist = plan.fit(max_epochs=2)
+        assert hist[-1]["n_cells"] == X.shape[0]  # 2 full minibatches + a ragged one
+        out.append(({k: v.detach().clone() for k, v in m.state_dict().items()}, hist))
+    for k in out[0][0]:
+        assert torch.equal(out[0][0][k], out[1][0][k]), k
+    assert out[0][1][-1]["train_loss"] == out[1][1][-1]["train_loss"]
+
+
 def test_ragged_last_batch_and_epoch_coverage():
     import scvi_tools_b200 as S
     from scvi_tools_b200.data import DeviceResidentCounts
