@@ -13,6 +13,7 @@ loads, with ``importlib``, exactly these reference files where they lie (nothing
     src/scvi/module/_constants.py          src/scvi/module/base/_decorators.py
     src/scvi/module/base/_embedding_mixin.py   src/scvi/module/base/_base_module.py
     src/scvi/module/_vae.py
+    src/scvi/module/_utils.py  src/scvi/module/_classifier.py  src/scvi/module/_scanvae.py   (SCANVI, 8f rank 1)
 
 It only works where ``/root/reference`` exists (the build container).  It is used by
 ``oracle/make_golden.py`` (to generate ``tests/golden/*.npz``) and by the
@@ -116,15 +117,24 @@ def load():
     base.LossOutput = bm.LossOutput
     base.BaseModuleClass = bm.BaseModuleClass
     base.BaseMinifiedModeModuleClass = bm.BaseMinifiedModeModuleClass
+    base.SupervisedModuleClass = bm.SupervisedModuleClass
     em = _load("scvi.module.base._embedding_mixin", "module/base/_embedding_mixin.py")
     base.EmbeddingModuleMixin = em.EmbeddingModuleMixin
     module.base = base
     vae = _load("scvi.module._vae", "module/_vae.py")
     module.VAE = vae.VAE
+    _load("scvi.module._utils", "module/_utils.py")
+    cls = _load("scvi.module._classifier", "module/_classifier.py")
+    module.Classifier = cls.Classifier
+    scanvae = _load("scvi.module._scanvae", "module/_scanvae.py")
+    module.SCANVAE = scanvae.SCANVAE
     scvi.module = module
 
     _LOADED = types.SimpleNamespace(
         VAE=vae.VAE,
+        SCANVAE=scanvae.SCANVAE,
+        Classifier=cls.Classifier,
+        Decoder=bc.Decoder,
         FCLayers=bc.FCLayers,
         Encoder=bc.Encoder,
         DecoderSCVI=bc.DecoderSCVI,

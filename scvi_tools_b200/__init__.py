@@ -9,10 +9,11 @@ from . import _lib
 from .distributions import NegativeBinomial, ZeroInflatedNegativeBinomial, log_nb_positive, log_zinb_positive
 from .module import MODULE_KEYS, REGISTRY_KEYS, VAE, LossOutput
 from .nn import DecoderSCVI, Encoder, FCLayers, rng_feed
+from .scanvi import SCANVAE, Classifier, Decoder
 from .model import SCVI  # noqa: E402  (after the module classes it builds on)
 
 __all__ = [
-    "SCVI", "VAE", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
+    "SCVI", "VAE", "SCANVAE", "Classifier", "Decoder", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
     "NegativeBinomial", "ZeroInflatedNegativeBinomial", "log_nb_positive", "log_zinb_positive", "rng_feed",
 ]
 __version__ = "0.1.0"

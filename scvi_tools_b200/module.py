@@ -360,7 +360,7 @@ class VAE(nn.Module):
         cats = torch.split(cat_covs, 1, dim=1) if (cat_covs is not None and self.encode_covariates) else ()
         dense_cov = cont_covs is not None and self.encode_covariates
         library = None
-        if dense_cov or x.dim() != 2:
+        if dense_cov or x.dim() != 2 or not self.z_encoder.encoder.is_fusable():
             if self.use_observed_lib_size:
                 library = torch.log(x.sum(1)).unsqueeze(1)
             x_ = torch.log1p(x) if self.log_variational else x

@@ -161,6 +161,10 @@ class FCLayers(nn.Module):
             and (drop is None or type(drop) is nn.Dropout)
         )
 
+    def is_fusable(self) -> bool:
+        """True when every layer is Linear -> (BatchNorm) -> (ReLU) -> (Dropout), the form the kernels cover."""
+        return all(self._layer_is_fusable(layers) for layers in self.fc_layers)
+
     def forward(self, x: torch.Tensor, *cat_list: int, cont: torch.Tensor | None = None, _first_flags: int = 0,
                 _row_idx: torch.Tensor | None = None):
         """``x`` [B, n_in]; ``cat_list`` one (B,1) integer tensor per categorical covariate.

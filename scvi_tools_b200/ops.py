@@ -336,6 +336,7 @@ class DecoderNLL(torch.autograd.Function):
             row_idx = _check(row_idx, "row_idx", torch.int64).contiguous()
         B, H = h.shape
         G = Ws.shape[0]
+        ctx.lib_shape = library.shape
         library = _check(library, "library").reshape(-1).contiguous()
         dev = h.device
         reconst = torch.empty(B, dtype=torch.float32, device=dev)
@@ -374,7 +375,10 @@ class DecoderNLL(torch.autograd.Function):
         call("scvi_decoder_nll_bwd", _ptr(h), h.stride(0), B, H, G, _ptr(Ws), _ptr(bs), _ptr(Wp), _ptr(bp), _ptr(px_r),
              _ptr(x), x.stride(0), _ptr(row_idx), _ptr(library), _ptr(stats), _ptr(g), likelihood, precision, _ptr(dh_k),
              H, _ptr(dWs), _ptr(dbs), _ptr(dWp), _ptr(dbp), _ptr(dr), _ptr(ws), None, _stream())
-        return dh, dWs, dbs, dWp, dbp, dr, None, None, None, None, None
+        # encoded library size (use_observed_lib_size=False): mu = exp(library) * px_scale, so
+        # d(reconst)/d(library) = sum_g mu * d(reconst)/d(mu) -- the forward's fourth row statistic
+        dlib = (g * stats[:, 3]).reshape(ctx.lib_shape) if ctx.needs_input_grad[7] else None
+        return dh, dWs, dbs, dWp, dbp, dr, None, dlib, None, None, None
 
 
 def decoder_params(h, Ws, bs, Wp, bp, library, want_scale=True, want_rate=True, want_dropout=True):

@@ -77,6 +77,7 @@ def test_plan_gradients_equal_autograd_path():
     plan.cov_cols.copy_((torch.from_numpy(inp["batch"]).cuda() + plan.L).to(torch.int32))
     import ctypes
 
+    plan._prologue(ctypes.c_void_p(st), feed_rng=False)  # ELBO backward seeds (1/B, kl_weight/B); keeps the fed mask / noise
     plan._forward_backward(ctypes.c_void_p(st))
     for k in plan.keys:
         assert rel_err(plan.Gd[k].cpu(), auto[k].cpu()) < 1e-5 or float(auto[k].abs().max()) < 1e-5, k
