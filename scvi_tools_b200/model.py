@@ -134,6 +134,18 @@ class SCVI:
         return {"reconstruction_loss": float(v.mean()) if return_mean else v.cpu().numpy()}
 
     @torch.inference_mode()
+    def get_marginal_ll(self, indices=None, n_mc_samples: int = 1000, n_mc_samples_per_pass: int = 50,
+                        batch_size: int = 4096, return_mean: bool = True):
+        """Importance-sampled marginal log-likelihood log p(x) (reference `VAEMixin.get_marginal_ll`,
+        src/scvi/model/base/_vaemixin.py:102-194, over `VAE.marginal_ll`): mean over cells or per cell."""
+        self.module.eval()
+        vals = [self.module.marginal_ll(tensors, n_mc_samples, return_mean=False,
+                                        n_mc_samples_per_pass=min(n_mc_samples_per_pass, n_mc_samples))
+                for tensors in self._batches(indices, batch_size)]
+        v = torch.cat(vals)
+        return float(v.mean()) if return_mean else v.numpy()
+
+    @torch.inference_mode()
     def get_normalized_expression(self, indices=None, transform_batch=None, library_size=1, n_samples: int = 1,
                                   batch_size: int = 4096, gene_indices=None):
         """Decoded expression `px_scale * library_size` (`library_size="latent"`: `px_rate`), averaged over the

@@ -20,7 +20,7 @@ from torch.nn.functional import one_hot
 
 from . import _lib
 from .distributions import NegativeBinomial, ZeroInflatedNegativeBinomial
-from .nn import DecoderSCVI, Encoder
+from .nn import DecoderSCVI, Encoder, _next_noise
 
 
 class _REGISTRY_KEYS_NT(NamedTuple):  # reference src/scvi/_constants.py:4-21
@@ -380,12 +380,15 @@ class VAE(nn.Module):
         if not self.use_observed_lib_size:
             x_in = torch.log1p(x) if (self.log_variational and enc_in is x) else enc_in
             ql, library = self.l_encoder(x_in, batch_index, *cats)
-        if n_samples > 1:
-            z = self.z_encoder.z_transformation(qz.sample((n_samples,)))
+        if n_samples > 1:  # `qz.sample((n_samples,))` (:402-411), drawn on the device (or from `rng_feed`)
+            with torch.no_grad():
+                untran_z = qz.loc + qz.scale * _next_noise((n_samples, *qz.loc.shape), qz.loc.device)
+            z = self.z_encoder.z_transformation(untran_z)
             if self.use_observed_lib_size:
                 library = library.unsqueeze(0).expand((n_samples, library.size(0), library.size(1)))
             else:
-                library = ql.sample((n_samples,))
+                with torch.no_grad():
+                    library = ql.loc + ql.scale * _next_noise((n_samples, *ql.loc.shape), ql.loc.device)
         return {MODULE_KEYS.Z_KEY: z, MODULE_KEYS.QZ_KEY: qz, MODULE_KEYS.QL_KEY: ql, MODULE_KEYS.LIBRARY_KEY: library}
 
     @auto_move_data
@@ -479,6 +482,62 @@ class VAE(nn.Module):
             kl_local={MODULE_KEYS.KL_L_KEY: kl_l, MODULE_KEYS.KL_Z_KEY: kl_z},
             extra_metrics=extra,
         )
+
+    # ------------------------------------------------------------------ marginal likelihood
+    @torch.inference_mode()
+    def marginal_ll(self, tensors, n_mc_samples: int, return_mean: bool = False, n_mc_samples_per_pass: int = 1):
+        """Importance-sampled log p(x) per cell (reference _vae.py:665-747): logsumexp over `n_mc_samples` draws
+        z ~ q(z|x) of `log p(z) + log p(x|z) - log q(z|x)` (+ the library terms when it is encoded) - log n.
+
+        In eval mode with the fused decoder the draws of one pass are flattened into the row dimension and the
+        fused decoder + likelihood kernel reads each cell's counts once per draw through its row index -- no
+        [n_samples, B, G] tensor (the reference materialises four) is ever formed."""
+        import warnings
+
+        n_per = int(n_mc_samples_per_pass)
+        if n_per > n_mc_samples:
+            warnings.warn("Number of chunks is larger than the total number of samples, setting it to the number "
+                          "of samples", RuntimeWarning, stacklevel=2)
+            n_per = n_mc_samples
+        dev = self.device
+        tensors = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in tensors.items()}
+        x = tensors[REGISTRY_KEYS.X_KEY]
+        batch_index = tensors[REGISTRY_KEYS.BATCH_KEY]
+        B = x.shape[0]
+        to_sum = []
+        for _ in range(int(np.ceil(n_mc_samples / n_per))):
+            inf = self.inference(**self._get_inference_input(tensors, full_forward_pass=True), n_samples=n_per)
+            qz, ql = inf[MODULE_KEYS.QZ_KEY], inf[MODULE_KEYS.QL_KEY]
+            z, library = inf[MODULE_KEYS.Z_KEY], inf[MODULE_KEYS.LIBRARY_KEY]
+            cont = tensors.get(REGISTRY_KEYS.CONT_COVS_KEY, None)
+            cat = tensors.get(REGISTRY_KEYS.CAT_COVS_KEY, None)
+            flat = (not self.training and self.dispersion == "gene" and not self.use_size_factor_key
+                    and cont is None and cat is None and self.decoder.scale_activation == "softmax"
+                    and self.decoder.px_decoder.is_fusable() and self.n_hidden in (64, 128, 256))
+            if flat:
+                S = n_per if z.dim() == 3 else 1
+                zf = z.reshape(S * B, -1)
+                h = self.decoder.hidden(zf, batch_index.repeat(S, 1))
+                rows = torch.arange(B, device=dev).repeat(S)
+                reconst = self.decoder.nll(h, library.reshape(S * B, 1).contiguous(), x, self.px_r, self.gene_likelihood,
+                                           rows, self.precision)
+                reconst = reconst.view(S, B) if z.dim() == 3 else reconst
+            else:
+                gen = self.generative(**self._get_generative_input(tensors, inf))
+                px = gen[MODULE_KEYS.PX_KEY]
+                reconst = px.nll(x) if isinstance(px, FusedCountDistribution) else -px.log_prob(x).sum(-1)
+            p_z = Normal(torch.zeros_like(qz.loc), torch.ones_like(qz.scale)).log_prob(z).sum(dim=-1)
+            q_z_x = qz.log_prob(z).sum(dim=-1)
+            log_prob_sum = p_z - reconst - q_z_x
+            if not self.use_observed_lib_size:
+                m, v = self._compute_local_library_params(batch_index)
+                log_prob_sum = log_prob_sum + Normal(m, v.sqrt()).log_prob(library).sum(dim=-1) \
+                    - ql.log_prob(library).sum(dim=-1)
+            if n_per == 1:
+                log_prob_sum = log_prob_sum.unsqueeze(0)
+            to_sum.append(log_prob_sum)
+        batch_log_lkl = torch.logsumexp(torch.cat(to_sum, dim=0), dim=0) - np.log(n_mc_samples)
+        return torch.mean(batch_log_lkl).item() if return_mean else batch_log_lkl.cpu()
 
     # ------------------------------------------------------------------ forward
     @auto_move_data

@@ -248,6 +248,10 @@ class FCLayers(nn.Module):
                 if isinstance(layer, nn.BatchNorm1d) and x.dim() == 3:
                     x = torch.cat([layer(s).unsqueeze(0) for s in x], dim=0)
                     continue
+                if isinstance(layer, nn.Dropout):  # same keep-mask source (and `rng_feed`) as the fused path
+                    if self.training and layer.p > 0:
+                        x = x * (_next_mask(x.shape, layer.p, x.device).to(x.dtype) / (1.0 - layer.p))
+                    continue
                 if self._is_linear_layer(layer) and self.inject_into_layer(i):
                     cl = [c.unsqueeze(0).expand((x.size(0), c.size(0), c.size(1))) for c in covs] if x.dim() == 3 else covs
                     x = torch.cat((x, *cl), dim=-1)

@@ -61,6 +61,27 @@ def test_getters_match_reference_eval_mode(name):
         assert rel_err(model.get_normalized_expression(transform_batch=nb - 1), gold[f"px_scale_tb{nb - 1}"]) < 1e-5
 
 
+@pytest.mark.parametrize("fx", ["marginal_c1_zinb_6x3", "marginal_c1_zinb_4x1", "marginal_onebatch_nb_5x5"])
+def test_marginal_ll_matches_reference(fx):
+    """`get_marginal_ll` / `VAE.marginal_ll`: the importance samples flattened into the fused kernel's row
+    dimension give the reference's per-cell log p(x) for the same normal draws."""
+    gold = np.load(os.path.join(GOLD, fx + ".npz"))
+    S, model, inp, _ = _model_from_case(str(gold["src"]))
+    noises = [torch.from_numpy(gold[f"noise::{i}"]) for i in range(sum(k.startswith("noise::") for k in gold.files))]
+    n_mc, n_per = int(gold["n_mc"]), int(gold["n_per"])
+    with S.rng_feed(noise=noises):
+        ll = model.get_marginal_ll(n_mc_samples=n_mc, n_mc_samples_per_pass=n_per, return_mean=False)
+    assert ll.shape == gold["marginal_ll"].shape
+    assert max_rel(ll, gold["marginal_ll"]) < 1e-5
+    with S.rng_feed(noise=noises):
+        mean = model.get_marginal_ll(n_mc_samples=n_mc, n_mc_samples_per_pass=n_per)
+    assert abs(mean - float(gold["marginal_ll"].mean())) < 1e-5 * abs(float(gold["marginal_ll"].mean()))
+    # training mode takes the generic per-sample route (BatchNorm per importance-sample slice) and stays finite
+    model.module.train()
+    assert np.isfinite(model.module.marginal_ll(model.data.minibatch(torch.arange(16, device="cuda:0")), 4, True, 2))
+    model.module.eval()
+
+
 def test_train_then_getters_end_to_end():
     """`SCVI(...).train()` lowers the ELBO; getters run on the trained, arena-backed parameters; a state-dict
     round trip into a fresh model reproduces them."""
