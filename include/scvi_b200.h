@@ -78,6 +78,16 @@ int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t l
 int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx,
                         const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
 
+/* same gather from a CSR matrix resident in HBM (sparse `adata.X`: `data[indexes].toarray()`,
+ * src/scvi/data/_anntorchdataset.py:143-152; torch-sparse conversion src/scvi/data/_utils.py:50-87):
+ * indptr int64 [n_rows+1]; indices uint16 (index_bytes 2, G <= 65536) or int32 (4); values float32
+ * (value_kind 0), uint16 (1) or uint8 (2).  Rows are densified to fp32 exactly; duplicates within a
+ * row are not summed (canonical CSR expected).  Column ids outside [0, G) are skipped and counted in
+ * *n_bad (device counter, nullable). */
+int scvi_gather_rows_csr(const int64_t* indptr, const void* indices, int index_bytes, const void* values,
+                         int value_kind, int64_t n_rows, int64_t G, const int64_t* idx, int64_t B,
+                         float* out, int64_t ldo, unsigned long long* n_bad, void* stream);
+
 /* ---- a7/a8: standalone likelihood kernels ("NB-loss kernel") --------------------------
  * replace log_nb_positive / log_zinb_positive
  * (src/scvi/distributions/_negative_binomial.py:99-135, :36-96) as called by

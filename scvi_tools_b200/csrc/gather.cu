@@ -80,6 +80,38 @@ static int launch_gather_int(const T* X, int64_t ldx, const int64_t* idx, int64_
   return SCVI_OK;
 }
 
+// CSR-resident counts: out[b, :] = dense row (idx ? idx[b] : b) of the sparse matrix -- the reference's
+// `data[indexes].toarray().astype(float32)` (src/scvi/data/_anntorchdataset.py:143-152).  One CTA per row:
+// zero-fill with 16-byte stores, barrier, scatter the row's non-zeros.  IT = uint16_t / int32_t column ids,
+// VT = float / uint16_t / uint8_t values.  Column ids >= G are skipped and counted in *n_bad (host raises).
+template <typename IT, typename VT>
+__global__ void gather_rows_csr_kernel(const int64_t* __restrict__ indptr, const IT* __restrict__ indices,
+                                       const VT* __restrict__ values, const int64_t* __restrict__ idx, int64_t B,
+                                       int64_t G, float* __restrict__ out, int64_t ldo, int vec,
+                                       unsigned long long* __restrict__ n_bad) {
+  for (int64_t b = blockIdx.x; b < B; b += gridDim.x) {
+    const int64_t row = idx ? idx[b] : b;
+    float* dst = out + b * ldo;
+    if (vec) {
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int64_t i = threadIdx.x; i < (G >> 2); i += blockDim.x) reinterpret_cast<float4*>(dst)[i] = z;
+      for (int64_t i = (G & ~(int64_t)3) + threadIdx.x; i < G; i += blockDim.x) dst[i] = 0.f;
+    } else {
+      for (int64_t i = threadIdx.x; i < G; i += blockDim.x) dst[i] = 0.f;
+    }
+    __syncthreads();
+    const int64_t p0 = indptr[row], p1 = indptr[row + 1];
+    for (int64_t p = p0 + threadIdx.x; p < p1; p += blockDim.x) {
+      const int64_t c = (int64_t)indices[p];
+      if (c >= 0 && c < G)
+        dst[c] = (float)values[p];
+      else if (n_bad)
+        atomicAdd(n_bad, 1ull);
+    }
+    __syncthreads();  // the next row of this CTA may alias nothing, but keep the phases separate
+  }
+}
+
 __global__ void gather_i64_kernel(const int64_t* __restrict__ src, const int64_t* __restrict__ idx, int64_t B,
                                   int64_t* __restrict__ out) {
   int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -128,6 +160,36 @@ int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx
   SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_u8: identity expansion of more rows than the matrix holds");
   if (B == 0 || G == 0) return SCVI_OK;
   return launch_gather_int<uint8_t>(X, ldx, idx, B, G, out, ldo, (cudaStream_t)stream, "scvi_gather_rows_u8");
+}
+
+int scvi_gather_rows_csr(const int64_t* indptr, const void* indices, int index_bytes, const void* values,
+                         int value_kind, int64_t n_rows, int64_t G, const int64_t* idx, int64_t B, float* out,
+                         int64_t ldo, unsigned long long* n_bad, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(indptr && out, "scvi_gather_rows_csr: NULL pointer");
+  SCVI_REQUIRE(index_bytes == 2 || index_bytes == 4, "scvi_gather_rows_csr: index_bytes must be 2 (uint16) or 4 (int32)");
+  SCVI_REQUIRE(value_kind >= 0 && value_kind <= 2, "scvi_gather_rows_csr: value_kind must be 0 (f32), 1 (u16) or 2 (u8)");
+  SCVI_REQUIRE(n_rows >= 0 && G >= 0 && B >= 0 && ldo >= G, "scvi_gather_rows_csr: bad shape");
+  SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_csr: identity expansion of more rows than the matrix holds");
+  if (B == 0 || G == 0) return SCVI_OK;
+  const int vec = (ldo % 4 == 0) && ((uintptr_t)out % 16 == 0);
+  const unsigned grid = (unsigned)std::min<int64_t>(B, 148 * 16);
+  cudaStream_t st = (cudaStream_t)stream;
+#define SCVI_CSR_LAUNCH(IT, VT)                                                                                  \
+  gather_rows_csr_kernel<IT, VT><<<grid, 256, 0, st>>>(indptr, (const IT*)indices, (const VT*)values, idx, B, G, \
+                                                       out, ldo, vec, n_bad)
+  if (index_bytes == 2) {
+    if (value_kind == 0) SCVI_CSR_LAUNCH(uint16_t, float);
+    else if (value_kind == 1) SCVI_CSR_LAUNCH(uint16_t, uint16_t);
+    else SCVI_CSR_LAUNCH(uint16_t, uint8_t);
+  } else {
+    if (value_kind == 0) SCVI_CSR_LAUNCH(int32_t, float);
+    else if (value_kind == 1) SCVI_CSR_LAUNCH(int32_t, uint16_t);
+    else SCVI_CSR_LAUNCH(int32_t, uint8_t);
+  }
+#undef SCVI_CSR_LAUNCH
+  SCVI_LAUNCH_CHECK("scvi_gather_rows_csr");
+  return SCVI_OK;
 }
 
 int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int64_t B, int64_t* out,

@@ -150,6 +150,73 @@ class HostStreamedCounts:
         self.freed[slot].record()
 
 
+class DeviceResidentCSR:
+    """Sparse count matrix resident in HBM in CSR form -- int64 row pointers, uint16 column ids (int32 when
+    n_vars > 65536) and values in the narrowest lossless count type -- with the same minibatch contract as
+    `DeviceResidentCounts`: `minibatch(idx)` densifies the rows on the device (`scvi_gather_rows_csr`), the
+    reference's `data[indexes].toarray().astype(float32)` (src/scvi/data/_anntorchdataset.py:143-152) without
+    the host round trip.  At ~10 % density a 1M x 2000 matrix takes 0.6 GB instead of 8 GB dense fp32.
+
+    `X`: scipy.sparse matrix (any format), or a `(indptr, indices, data, shape)` tuple of arrays."""
+
+    def __init__(self, X, batch=None, labels=None, device="cuda"):
+        dev = torch.device(device)
+        if hasattr(X, "tocsr"):
+            X = X.tocsr()
+            X.sum_duplicates()
+            X.sort_indices()
+            indptr, indices, values, shape = X.indptr, X.indices, X.data, X.shape
+        else:
+            indptr, indices, values, shape = X
+        indptr = torch.as_tensor(np.asarray(indptr)).to(torch.int64)
+        indices = torch.as_tensor(np.asarray(indices))
+        values = torch.as_tensor(np.asarray(values))
+        self.shape = (int(shape[0]), int(shape[1]))
+        if indptr.numel() != self.shape[0] + 1 or int(indptr[-1]) != indices.numel() or indices.numel() != values.numel():
+            raise ValueError("inconsistent CSR arrays")
+        if indices.numel() and (int(indices.min()) < 0 or int(indices.max()) >= self.shape[1]):
+            raise ValueError("CSR column index out of range")
+        vdt = narrowest_count_dtype(values)
+        idt = torch.uint16 if self.shape[1] <= 65536 else torch.int32
+        self.indptr = indptr.to(dev).contiguous()
+        np_idt = np.uint16 if idt == torch.uint16 else np.int32
+        self.indices = torch.from_numpy(indices.numpy().astype(np_idt)).to(dev).contiguous()
+        self.values = values.to(vdt).to(dev).contiguous()
+        n = self.shape[0]
+
+        def col(v):
+            if v is None:
+                return torch.zeros(n, dtype=torch.int64, device=dev)
+            v = torch.as_tensor(np.asarray(v) if not isinstance(v, torch.Tensor) else v)
+            return v.reshape(-1).to(torch.int64).to(dev).contiguous()
+
+        self.batch = col(batch)
+        self.labels = col(labels)
+
+    @property
+    def n_obs(self) -> int:
+        return self.shape[0]
+
+    @property
+    def n_vars(self) -> int:
+        return self.shape[1]
+
+    @property
+    def nbytes(self) -> int:
+        return sum(t.numel() * t.element_size() for t in (self.indptr, self.indices, self.values))
+
+    def densify(self, idx: torch.Tensor | None, out: torch.Tensor | None = None) -> torch.Tensor:
+        return ops.gather_rows_csr(self.indptr, self.indices, self.values, self.n_vars, idx, out=out)
+
+    def minibatch(self, idx: torch.Tensor) -> dict:
+        idx = idx.to(self.indptr.device, dtype=torch.int64)
+        return {
+            "X": self.densify(idx),
+            "batch": ops.gather_i64(self.batch, idx).view(-1, 1),
+            "labels": ops.gather_i64(self.labels, idx).view(-1, 1),
+        }
+
+
 class DeviceResidentCounts:
     """Count matrix [N, G] (fp32, or uint16-compressed) + batch / label columns resident in HBM."""
 

@@ -14,7 +14,7 @@ from __future__ import annotations
 import numpy as np
 import torch
 
-from .data import DeviceResidentCounts, HostStreamedCounts
+from .data import DeviceResidentCounts, DeviceResidentCSR, HostStreamedCounts
 from .module import MODULE_KEYS, VAE
 from .train import FusedTrainingPlan
 
@@ -38,9 +38,14 @@ class SCVI:
                  dropout_rate: float = 0.1, dispersion: str = "gene", gene_likelihood: str = "zinb",
                  latent_distribution: str = "normal", device="cuda:0", **model_kwargs):
         self.device = torch.device(device)
-        self.data = X if isinstance(X, (DeviceResidentCounts, HostStreamedCounts)) else DeviceResidentCounts(
-            X, batch=batch, device=self.device)
+        if isinstance(X, (DeviceResidentCounts, DeviceResidentCSR, HostStreamedCounts)):
+            self.data = X
+        elif hasattr(X, "tocsr"):  # scipy sparse stays sparse in HBM
+            self.data = DeviceResidentCSR(X, batch=batch, device=self.device)
+        else:
+            self.data = DeviceResidentCounts(X, batch=batch, device=self.device)
         self.streamed = isinstance(self.data, HostStreamedCounts)
+        self.sparse = isinstance(self.data, DeviceResidentCSR)
         codes = self.data.host_batch if self.streamed else self.data.batch
         n_batch = int(codes.max().item()) + 1 if self.data.n_obs else 1
         self.summary = {"n_obs": self.data.n_obs, "n_vars": self.data.n_vars, "n_batch": n_batch}
@@ -68,19 +73,30 @@ class SCVI:
             raise ValueError(f"HostStreamedCounts was built for batch_size={self.data.B}, train() got {batch_size}")
         if new_plan:
             self._plan = FusedTrainingPlan(
-                self.module, self.data.stage if self.streamed else self.data, batch_size=batch_size, lr=lr, eps=eps,
+                self.module, self._plan_counts(batch_size), batch_size=batch_size, lr=lr, eps=eps,
                 weight_decay=weight_decay,
                 n_epochs_kl_warmup=n_epochs_kl_warmup, n_steps_kl_warmup=n_steps_kl_warmup,
                 max_kl_weight=max_kl_weight, min_kl_weight=min_kl_weight, seed=seed, use_cuda_graph=use_cuda_graph,
                 process_group=process_group)
         if self.streamed:
             hist = self._plan.fit_streamed(self.data, max_epochs=max_epochs, shuffle=shuffle)
+        elif self.sparse:
+            hist = self._plan.fit_csr(self.data, max_epochs=max_epochs, shuffle=shuffle)
         else:
             hist = self._plan.fit(max_epochs=max_epochs, shuffle=shuffle)
         self.history_.extend(hist)
         self.module.eval()
         self.is_trained_ = True
         return hist
+
+    def _plan_counts(self, batch_size):
+        """The dense fp32 rows the plan's kernels read: the resident matrix itself, or a staging matrix."""
+        if self.streamed:
+            return self.data.stage
+        if self.sparse:
+            return DeviceResidentCounts(torch.zeros(batch_size, self.data.n_vars),
+                                        batch=torch.zeros(batch_size, dtype=torch.int64), device=self.device)
+        return self.data
 
     # ------------------------------------------------------------------ getters
     def _batches(self, indices, batch_size):

@@ -81,6 +81,29 @@ def gather_rows(X: torch.Tensor, idx: torch.Tensor | None, out: torch.Tensor | N
     return out
 
 
+def gather_rows_csr(indptr, indices, values, n_vars: int, idx: torch.Tensor | None, out: torch.Tensor | None = None,
+                    n_bad: torch.Tensor | None = None) -> torch.Tensor:
+    """Dense fp32 rows ``idx`` (None = all rows in order) of a CSR matrix resident on the device
+    (reference ``data[indexes].toarray().astype(float32)``, src/scvi/data/_anntorchdataset.py:143-152)."""
+    indptr = _check(indptr, "indptr", torch.int64).contiguous()
+    n_rows = indptr.numel() - 1
+    if indices.dtype not in (torch.uint16, torch.int32) or values.dtype not in (torch.float32, torch.uint16, torch.uint8):
+        raise TypeError("CSR indices must be uint16 / int32 and values float32 / uint16 / uint8")
+    _check(indices, "indices", indices.dtype)
+    _check(values, "values", values.dtype)
+    if idx is not None:
+        idx = _check(idx, "idx", torch.int64).contiguous()
+    B = n_rows if idx is None else idx.numel()
+    if out is None:
+        out = torch.empty(B, n_vars, dtype=torch.float32, device=indptr.device)
+    if B == 0:
+        return out
+    kind = {torch.float32: 0, torch.uint16: 1, torch.uint8: 2}[values.dtype]
+    call("scvi_gather_rows_csr", _ptr(indptr), _ptr(indices.contiguous()), indices.element_size(),
+         _ptr(values.contiguous()), kind, n_rows, n_vars, _ptr(idx), B, _ptr(out), out.stride(0), _ptr(n_bad), _stream())
+    return out
+
+
 def gather_i64(src: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     src = _check(src, "src", torch.int64).contiguous().view(-1)
     idx = _check(idx, "idx", torch.int64).contiguous()

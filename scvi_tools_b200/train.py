@@ -24,6 +24,7 @@ from . import _lib
 from ._lib import call, query
 from .data import DeviceResidentCounts, epoch_indices
 from .ops import BN_EPS, BN_MOMENTUM
+from .ops import gather_i64 as ops_gather_i64
 
 
 def compute_kl_weight(epoch, step, n_epochs_kl_warmup=400, n_steps_kl_warmup=None, max_kl_weight=1.0,
@@ -452,6 +453,46 @@ class FusedTrainingPlan:
                 acc[0] += out[0].double() * c.numel()
                 acc[1:] += out[1:].double()
                 n_cells += c.numel()
+            a = acc.cpu()
+            history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
+                            "reconstruction_loss": float(a[1]) / max(n_cells, 1),
+                            "kl_local": float(a[2]) / max(n_cells, 1), "n_cells": n_cells,
+                            "kl_weight": float(self.klw.item())})
+        self.current_epoch = first + max_epochs
+        return history
+
+    def fit_csr(self, csr, max_epochs: int, shuffle: bool = True, drop_last: bool = False):
+        """`fit` for CSR-resident counts (`DeviceResidentCSR`): each minibatch is densified on the device into a
+        fixed fp32 staging matrix of `batch_size` rows (one `scvi_gather_rows_csr` launch ahead of the step graph);
+        the step itself is unchanged and reads staging rows 0..n-1."""
+        if getattr(self, "csr", None) is not csr:
+            if csr.n_vars != self.G:
+                raise ValueError("DeviceResidentCSR gene count differs from the plan's")
+            if self.data.n_obs != self.B:  # the plan was built on something else: swap in a staging matrix
+                self.data = DeviceResidentCounts(torch.zeros(self.B, self.G),
+                                                 batch=torch.zeros(self.B, dtype=torch.int64), device=self.dev)
+            self.batch_cols = torch.zeros(self.B, dtype=torch.int32, device=self.dev)
+            self._graphs = None
+            self.csr = csr
+            self._stage_rows = torch.arange(self.B, device=self.dev)
+        history = []
+        first = self.current_epoch
+        for epoch in range(first, first + max_epochs):
+            self.set_epoch(epoch)
+            order = epoch_indices(csr.n_obs, self.rank, self.world, epoch, self.seed, shuffle).to(self.dev)
+            acc = torch.zeros(3, dtype=torch.float64, device=self.dev)
+            n_cells = 0
+            for s in range(0, order.numel(), self.B):
+                chunk = order[s : s + self.B].sort().values
+                n = chunk.numel()
+                if n < self.B and (drop_last or n < 2):
+                    break
+                csr.densify(chunk, out=self.data.X[:n])
+                self.batch_cols[:n].copy_(ops_gather_i64(csr.batch, chunk) + self.L)
+                out = self.training_step(self._stage_rows[:n])
+                acc[0] += out[0].double() * n
+                acc[1:] += out[1:].double()
+                n_cells += n
             a = acc.cpu()
             history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
                             "reconstruction_loss": float(a[1]) / max(n_cells, 1),

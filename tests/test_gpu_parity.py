@@ -219,6 +219,48 @@ def test_compact_count_gather_bit_exact(G, dt):
     assert narrowest_count_dtype(torch.tensor([[70000.0]])) == torch.float32
 
 
+@pytest.mark.parametrize(("G", "density", "vmax"), [(2000, 0.1, 40), (333, 0.5, 3000), (70000, 0.001, 5), (17, 0.0, 1)])
+def test_csr_resident_gather_bit_exact(G, density, vmax):
+    """CSR-resident counts densify on the device to exactly `X[idx].toarray().astype(float32)` (uint16 / int32
+    column ids, uint8 / uint16 / float32 values, empty rows, empty matrix, unaligned row pitches)."""
+    import scipy.sparse as sp
+
+    from scvi_tools_b200 import ops
+    from scvi_tools_b200.data import DeviceResidentCSR
+
+    rng = np.random.default_rng(G)
+    n = 300
+    X = sp.random(n, G, density=density, format="csr", random_state=rng,
+                  data_rvs=lambda k: rng.integers(1, vmax + 1, size=k).astype(np.float32))
+    X = X.astype(np.float32)
+    batch = rng.integers(0, 3, size=n)
+    csr = DeviceResidentCSR(X, batch=batch, device=dev())
+    assert csr.indices.dtype == (torch.uint16 if G <= 65536 else torch.int32)
+    if X.nnz:  # an empty matrix keeps float32 values (nothing to narrow)
+        assert csr.values.dtype == (torch.uint8 if vmax < 256 else torch.uint16)
+    dense = np.asarray(X.toarray(), dtype=np.float32)
+    for B in (1, 77, 300):
+        idx = rng.integers(0, n, size=B)
+        mb = csr.minibatch(torch.from_numpy(idx))
+        assert mb["X"].dtype == torch.float32 and np.array_equal(mb["X"].cpu().numpy(), dense[idx])
+        assert np.array_equal(mb["batch"].cpu().numpy().ravel(), batch[idx])
+    assert np.array_equal(csr.densify(None).cpu().numpy(), dense)
+    # into a padded staging buffer (row pitch > G, odd pitch -> scalar zero fill); stale contents are overwritten
+    stage = torch.full((64, G + 3), 7.0, device=dev())
+    idx = torch.from_numpy(rng.integers(0, n, size=64)).to(dev())
+    csr.densify(idx, out=stage[:, :G])
+    assert np.array_equal(stage[:, :G].cpu().numpy(), dense[idx.cpu().numpy()]) and bool((stage[:, G:] == 7.0).all())
+    # non-integer values stay float32
+    Xf = X.copy()
+    Xf.data = Xf.data + 0.5
+    if Xf.nnz:
+        cf = DeviceResidentCSR(Xf, device=dev())
+        assert cf.values.dtype == torch.float32
+        assert np.array_equal(cf.densify(None).cpu().numpy(), np.asarray(Xf.toarray(), dtype=np.float32))
+    with pytest.raises(ValueError):
+        DeviceResidentCSR((np.array([0, 1]), np.array([G]), np.array([1.0]), (1, G)), device=dev())
+
+
 @pytest.mark.parametrize(("B", "G", "nb", "lik"), [(300, 2000, 8, "zinb"), (129, 4000, 32, "nb"), (64, 512, 2, "zinb")])
 def test_vae_step_vs_oracle_seeded(B, G, nb, lik):
     """BASELINE.json configs[1]/[2] shapes (G=2000 zinb 8 batches, G=4000 nb 32 batches) at an

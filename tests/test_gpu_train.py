@@ -137,6 +137,30 @@ def test_streamed_host_counts_train_like_resident_counts(count_max):
     assert out[0][1][-1]["train_loss"] == out[1][1][-1]["train_loss"]
 
 
+def test_csr_resident_counts_train_like_dense_counts():
+    """`SCVI` on a scipy CSR matrix (kept sparse in HBM, densified per minibatch on the device) ends with
+    exactly the weights of training on the dense matrix; the getters walk the sparse matrix too."""
+    import scipy.sparse as sp
+
+    from scvi_tools_b200.model import SCVI
+
+    X, batch = O.synthetic_iid(600, 160, 2, seed=4)
+    X = X * (np.random.default_rng(0).random(X.shape) < 0.3)  # sparser, as real scRNA counts
+    out = []
+    for sparse in (False, True):
+        torch.manual_seed(0)
+        model = SCVI(sp.csr_matrix(X) if sparse else X, batch=batch, gene_likelihood="nb")
+        assert model.sparse == sparse
+        hist = model.train(max_epochs=2, batch_size=256, seed=5)
+        assert hist[-1]["n_cells"] == X.shape[0]
+        out.append((model.state_dict(), hist, model.get_latent_representation(indices=[3, 599, 0, 41])))
+    for k in out[0][0]:
+        assert torch.equal(out[0][0][k], out[1][0][k]), k
+    assert out[0][1][-1]["train_loss"] == out[1][1][-1]["train_loss"]
+    assert np.array_equal(out[0][2], out[1][2])
+    assert model.data.nbytes < X.size * 4 / 3
+
+
 def test_ragged_last_batch_and_epoch_coverage():
     import scvi_tools_b200 as S
     from scvi_tools_b200.data import DeviceResidentCounts
