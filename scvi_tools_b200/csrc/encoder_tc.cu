@@ -16,7 +16,14 @@
 namespace scvi {
 
 constexpr int EN_CONV_WARPS = 16;
-constexpr int EN_THREADS = 32 * (4 + EN_CONV_WARPS);
+// raw-count loaders: warps 0, 2 and the two warps after the converters.  Each warp instruction copies one
+// 512-byte row segment with 32 x cp.async 16 B (LDGSTS): tools/ubench_gather.cu measures 4.5 TB/s chip-wide
+// for this scheme against 2.4 TB/s for one 512-byte bulk copy per row (the TMA engine retires ~32 M copies/s/SM)
+constexpr int EN_LOAD_WARPS = 4;
+constexpr int EN_THREADS = 32 * (4 + EN_CONV_WARPS + 2);
+__device__ __forceinline__ int en_loader_id(int warp) {
+  return warp == 0 ? 0 : warp == 2 ? 1 : warp >= 4 + EN_CONV_WARPS ? 2 + warp - (4 + EN_CONV_WARPS) : -1;
+}
 constexpr int EN_NS = 4;                          // pipeline stages
 constexpr uint32_t EN_BLK = TC_M * TC_NT * 2;     // 128 x 32 fp16 block = 8 KB
 constexpr int EN_X_SCALE_LOG2 = 11;               // log1p(x) <= 16 -> < 2^15
@@ -131,7 +138,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       tc::mbar_init(&wfull[i], 1);
       tc::mbar_init(&afull[i], EN_CONV_WARPS);
       tc::mbar_init(&empty[i], 1);
-      tc::mbar_init(&rfull[i], 1);
+      tc::mbar_init(&rfull[i], 32 * EN_LOAD_WARPS);
       tc::mbar_init(&rempty[i], EN_CONV_WARPS);
     }
     tc::mbar_init(accfull, 1);
@@ -142,28 +149,35 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *s_tmem;
+  const int lid = en_loader_id(warp);
 
-  if (warp == 0) {
-    // ===== raw producer: per chunk one 512-byte bulk copy per minibatch row (lane owns rows lane + 32 i)
+  if (lid >= 0) {
+    // ===== raw producers: per chunk, loader warp `lid` copies the 512-byte segments of rows lid, lid + 4, ...
+    // (one warp instruction = one row segment; lane owns the row pointers of rows lane + 32 k)
     const float* rp[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int rr = lane + 32 * i;
-      rp[i] = (rr < valid) ? x + (row_idx ? row_idx[r0 + rr] : r0 + rr) * ldx : nullptr;
+    for (int k = 0; k < 4; ++k) {
+      const int rr = lane + 32 * k;
+      rp[k] = (rr < valid) ? x + (row_idx ? row_idx[r0 + rr] : r0 + rr) * ldx : nullptr;
     }
     for (int c = 0; c < nchunks; ++c) {
       const int s = c & 1;
       const int64_t gt = (int64_t)(c0 + c) * TC_M;
       const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - gt) * 4;
-      if (lane == 0) {
-        tc::mbar_wait(&rempty[s], ((c >> 1) & 1) ^ 1);
-        tc::mbar_arrive_expect_tx(&rfull[s], (uint32_t)valid * rowbytes);
-      }
-      __syncwarp();
-      uint8_t* dst = smem + L::RAW + s * L::RAW_BYTES;
+      const bool lane_on = (uint32_t)lane * 16 < rowbytes;
+      tc::mbar_wait(&rempty[s], ((c >> 1) & 1) ^ 1);
+      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * L::RAW_BYTES) + lane * 16;
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (rp[i]) tc::bulk_g2s(dst + (lane + 32 * i) * L::RAW_ROW, rp[i] + gt, rowbytes, &rfull[s]);
+      for (int k = 0; k < 4; ++k) {
+#pragma unroll
+        for (int i = 0; i < 32 / EN_LOAD_WARPS; ++i) {
+          const int sl = lid + EN_LOAD_WARPS * i;
+          const float* p = reinterpret_cast<const float*>(
+              __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(rp[k]), sl));
+          if (p && lane_on) tc::cp_async16(dst0 + (32 * k + sl) * L::RAW_ROW, p + gt + lane * 4);
+        }
+      }
+      tc::cp_async_mbar_arrive_noinc(&rfull[s]);
     }
   } else if (warp == 3) {
     // ===== We producer: one packed 32-gene K-tile per stage
@@ -396,7 +410,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       tc::mbar_init(&dfull[i], 1);
       tc::mbar_init(&xfull[i], EN_CONV_WARPS);
       tc::mbar_init(&empty[i], 1);
-      tc::mbar_init(&rfull[i], 1);
+      tc::mbar_init(&rfull[i], 32 * EN_LOAD_WARPS);
       tc::mbar_init(&rempty[i], EN_CONV_WARPS);
     }
     tc::mbar_init(accfull, 1);
@@ -407,10 +421,13 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *s_tmem;
+  const int lid = en_loader_id(warp);
 
-  if (warp == 0) {
-    // ===== producer: dy tile (one bulk copy) + the raw count tile (lane = row: one bulk copy each)
+  if (lid >= 0) {
+    // ===== raw producers: per 32-row tile, loader warp `lid` copies the 512-byte gene segments of rows
+    // lid, lid + 4, ... (one warp instruction = one row segment); lane l holds the id of the tile's row l
     const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - g0) * 4;
+    const bool lane_on = (uint32_t)lane * 16 < rowbytes;
     auto row_id = [&](int j) -> int64_t {
       const int64_t b = (int64_t)(rt0 + j) * TC_NT + lane;
       return (j < ntiles && b < B) ? (row_idx ? row_idx[b] : b) : -1;
@@ -419,17 +436,26 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     for (int j = 0; j < ntiles; ++j) {
       const int s = j % EN_NS;
       const int64_t ridn = row_id(j + 1);
-      const int nvalid = (int)min((int64_t)TC_NT, B - (int64_t)(rt0 + j) * TC_NT);
-      if (lane == 0) {
+      tc::mbar_wait(&rempty[s], ((j / EN_NS) & 1) ^ 1);
+      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * EN_RAW1) + lane * 16;
+#pragma unroll
+      for (int i = 0; i < TC_NT / EN_LOAD_WARPS; ++i) {
+        const int rr = lid + EN_LOAD_WARPS * i;
+        const int64_t r = __shfl_sync(0xffffffffu, rid, rr);
+        if (r >= 0 && lane_on) tc::cp_async16(dst0 + rr * EN_RAW2_ROW, x + r * ldx + g0 + lane * 4);
+      }
+      tc::cp_async_mbar_arrive_noinc(&rfull[s]);
+      rid = ridn;
+    }
+  } else if (warp == 3) {
+    // ===== dy producer: one packed 32-row tile per stage (bulk copy)
+    if (lane == 0) {
+      for (int j = 0; j < ntiles; ++j) {
+        const int s = j % EN_NS;
         tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
         tc::mbar_arrive_expect_tx(&dfull[s], 2 * TC_BLK32);
         tc::bulk_g2s(smem + L::A + s * 2 * EN_BLK, dypack + (size_t)(rt0 + j) * 2 * TC_BLK32, 2 * TC_BLK32, &dfull[s]);
-        tc::mbar_wait(&rempty[s], ((j / EN_NS) & 1) ^ 1);
-        tc::mbar_arrive_expect_tx(&rfull[s], (uint32_t)nvalid * rowbytes);
       }
-      __syncwarp();
-      if (rid >= 0) tc::bulk_g2s(smem + L::RAW + s * EN_RAW1 + lane * EN_RAW2_ROW, x + rid * ldx + g0, rowbytes, &rfull[s]);
-      rid = ridn;
     }
   } else if (warp == 1) {
     if (lane == 0 && ntiles > 0) {

@@ -36,8 +36,15 @@ class SCVI:
 
     def __init__(self, X, batch=None, n_hidden: int = 128, n_latent: int = 10, n_layers: int = 1,
                  dropout_rate: float = 0.1, dispersion: str = "gene", gene_likelihood: str = "zinb",
-                 latent_distribution: str = "normal", device="cuda:0", **model_kwargs):
+                 latent_distribution: str = "normal", device="cuda:0", var_names=None, **model_kwargs):
         self.device = torch.device(device)
+        # the reference's `init_params_` record (BaseModelClass._get_init_params, _base_model.py:747-774)
+        self.init_params_ = {
+            "non_kwargs": {"n_hidden": n_hidden, "n_latent": n_latent, "n_layers": n_layers,
+                           "dropout_rate": dropout_rate, "dispersion": dispersion,
+                           "gene_likelihood": gene_likelihood, "latent_distribution": latent_distribution},
+            "kwargs": {"kwargs": dict(model_kwargs)},
+        }
         if isinstance(X, (DeviceResidentCounts, DeviceResidentCSR, HostStreamedCounts)):
             self.data = X
         elif hasattr(X, "tocsr"):  # scipy sparse stays sparse in HBM
@@ -53,6 +60,10 @@ class SCVI:
                           n_layers=n_layers, dropout_rate=dropout_rate, dispersion=dispersion,
                           gene_likelihood=gene_likelihood, latent_distribution=latent_distribution,
                           **model_kwargs).to(self.device)
+        self.var_names = (np.asarray(var_names) if var_names is not None
+                          else np.array([str(i) for i in range(self.data.n_vars)]))
+        if self.var_names.shape[0] != self.data.n_vars:
+            raise ValueError("var_names length differs from the number of genes")
         self.is_trained_ = False
         self.history_: list[dict] = []
         self._plan: FusedTrainingPlan | None = None
@@ -185,6 +196,66 @@ class SCVI:
         return torch.cat(out).cpu().numpy()
 
     # ------------------------------------------------------------------ persistence
+    def save(self, dir_path: str, prefix: str | None = None, overwrite: bool = False, **torch_save_kwargs):
+        """Write `<dir_path>/<prefix>model.pt` in the reference's layout (`BaseModelClass.save`,
+        src/scvi/model/base/_base_model.py:792-905; keys from src/scvi/model/base/_constants.py): a `torch.save`d
+        dict {"model_state_dict", "var_names", "attr_dict"} where the state dict has the reference module's keys
+        (plus its empty "pyro_param_store" entry) and `attr_dict` holds the trailing-underscore attributes
+        (`init_params_`, `is_trained_`, `history_`, `summary_stats_`).  No AnnData is written: there is no AnnData
+        registry in this driver, so `attr_dict` carries no `registry_`."""
+        import os
+
+        if os.path.exists(dir_path) and not overwrite:
+            raise ValueError(f"{dir_path} already exists. Please provide another directory for saving.")
+        os.makedirs(dir_path, exist_ok=True)
+        sd = {k: v.detach().cpu() for k, v in self.module.state_dict().items()}
+        sd["pyro_param_store"] = {"params": {}, "constraints": {}}
+        attr = {"init_params_": self.init_params_, "is_trained_": self.is_trained_, "history_": self.history_,
+                "summary_stats_": dict(self.summary)}
+        torch.save({"model_state_dict": sd, "var_names": self.var_names, "attr_dict": attr},
+                   os.path.join(dir_path, f"{prefix or ''}model.pt"), **torch_save_kwargs)
+
+    @classmethod
+    def load(cls, dir_path: str, X, batch=None, prefix: str | None = None, device="cuda:0", var_names=None):
+        """Rebuild a model from `<dir_path>/<prefix>model.pt` written by `save` -- or by the reference's
+        `SCVI.save` (same keys; `registry_` and unknown attributes are ignored) -- on the counts `X`
+        (`BaseModelClass.load`, _base_model.py:907-1040; `_load_saved_files` / `_initialize_model`,
+        src/scvi/model/base/_save_load.py:69-165).  `var_names`, when given, must equal the saved ones
+        (`_validate_var_names`)."""
+        import os
+
+        path = os.path.join(dir_path, f"{prefix or ''}model.pt")
+        try:
+            blob = torch.load(path, map_location="cpu", weights_only=False)
+        except FileNotFoundError as exc:
+            raise ValueError(f"Failed to load model file at {path}.") from exc
+        sd = dict(blob["model_state_dict"])
+        sd.pop("pyro_param_store", None)
+        attr = dict(blob["attr_dict"])
+        if "init_params_" not in attr:
+            raise ValueError("No init_params_ were saved by the model.")
+        init = attr.pop("init_params_")
+        if "non_kwargs" in init:
+            non_kwargs = dict(init["non_kwargs"])
+            kwargs = {k: v for j in init["kwargs"].values() for k, v in j.items()}
+        else:  # pre-0.15 flat layout
+            non_kwargs = {k: v for k, v in init.items() if not isinstance(v, dict)}
+            kwargs = {k: v for j in init.values() if isinstance(j, dict) for k, v in j.items()}
+            non_kwargs.pop("use_cuda", None)
+        for k in ("datamodule", "registry", "adata"):
+            non_kwargs.pop(k, None)
+        saved_names = blob.get("var_names")
+        if var_names is not None and saved_names is not None and not np.array_equal(
+                np.asarray(var_names).astype(str), np.asarray(saved_names).astype(str)):
+            raise ValueError("var_names for the passed data do not match those of the saved model")
+        model = cls(X, batch=batch, device=device, var_names=saved_names if var_names is None else var_names,
+                    **non_kwargs, **kwargs)
+        model.module.load_state_dict(sd)
+        model.module.eval()
+        model.is_trained_ = bool(attr.get("is_trained_", True))
+        model.history_ = attr.get("history_", []) if isinstance(attr.get("history_", []), list) else []
+        return model
+
     def state_dict(self):
         return self.module.state_dict()
 

@@ -82,6 +82,53 @@ def test_marginal_ll_matches_reference(fx):
     model.module.eval()
 
 
+def test_save_load_round_trip_and_reference_shaped_checkpoint(tmp_path):
+    """`model.pt` in the reference's layout: our own save -> load reproduces the getters bit for bit; a checkpoint
+    shaped like the reference's own (`model_state_dict` incl. `pyro_param_store`, `var_names`, `attr_dict` with
+    `init_params_` and a `registry_` this driver ignores) loads too."""
+    from scvi_tools_b200.model import SCVI
+
+    S, model, inp, gold = _model_from_case("c1_zinb")
+    names = np.array([f"gene_{i}" for i in range(inp["x"].shape[1])])
+    model.var_names = names
+    model.is_trained_ = True
+    d = str(tmp_path / "m")
+    model.save(d)
+    with pytest.raises(ValueError):
+        model.save(d)
+    model.save(d, overwrite=True)
+    blob = torch.load(os.path.join(d, "model.pt"), weights_only=False)
+    assert set(blob) == {"model_state_dict", "var_names", "attr_dict"}
+    assert "pyro_param_store" in blob["model_state_dict"] and "init_params_" in blob["attr_dict"]
+    m2 = SCVI.load(d, inp["x"], batch=inp["batch"].reshape(-1), var_names=names)
+    assert m2.is_trained_ and np.array_equal(m2.var_names, names)
+    assert np.array_equal(m2.get_latent_representation(), model.get_latent_representation())
+    with pytest.raises(ValueError):
+        SCVI.load(d, inp["x"], batch=inp["batch"].reshape(-1), var_names=names[::-1])
+    with pytest.raises(ValueError):
+        SCVI.load(str(tmp_path / "nowhere"), inp["x"])
+    # a reference-shaped file: the golden state dict (reference keys), SCVI.__init__'s recorded arguments
+    P, _, _ = load_vae_case("c1_zinb")
+    sd = {k: v.clone() for k, v in model.state_dict().items()}
+    sd.update({k: v.clone() for k, v in P.items()})
+    sd["pyro_param_store"] = {"params": {}, "constraints": {}}
+    ref_blob = {
+        "model_state_dict": sd, "var_names": names,
+        "attr_dict": {"init_params_": {"non_kwargs": {"n_hidden": 128, "n_latent": 10, "n_layers": 1,
+                                                        "dropout_rate": 0.1, "dispersion": "gene",
+                                                        "gene_likelihood": "zinb", "use_observed_lib_size": True,
+                                                        "latent_distribution": "normal"},
+                                       "kwargs": {"kwargs": {}}},
+                      "is_trained_": True, "registry_": {"scvi_version": "1.5.0", "model_name": "SCVI"},
+                      "history_": None, "train_indices_": np.arange(3)},
+    }
+    d2 = tmp_path / "ref"
+    d2.mkdir()
+    torch.save(ref_blob, str(d2 / "model.pt"))
+    m3 = SCVI.load(str(d2), inp["x"], batch=inp["batch"].reshape(-1))
+    assert rel_err(m3.get_latent_representation(), gold["qz_mean"]) < 1e-5
+
+
 def test_train_then_getters_end_to_end():
     """`SCVI(...).train()` lowers the ELBO; getters run on the trained, arena-backed parameters; a state-dict
     round trip into a fresh model reproduces them."""

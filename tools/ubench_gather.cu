@@ -1,6 +1,8 @@
 // Micro-benchmark: how fast can one SM pull random 8000-byte-pitch row segments into shared memory?
 //   mode 0: 1-D bulk copies (TMA engine), `lanes` issuing lanes of one warp, S bytes per copy
 //   mode 1: loader warps, ld.global.v4 -> st.shared (nw warps, U loads in flight per thread)
+//   mode 2: loader warps, cp.async 16 B (LDGSTS, no registers): one warp instruction = one row segment of
+//           512 B (S = 512) -- completion through cp.async.mbarrier.arrive.noinc on the stage's mbarrier
 // Build: nvcc -O3 -gencode arch=compute_100a,code=sm_100a -o ubench_gather ubench_gather.cu
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -39,8 +41,8 @@ __global__ void __launch_bounds__(1024, 1) k(const float* __restrict__ x, int64_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int stage_bytes = 128 * pitch;
   if (threadIdx.x == 0) {
-    mbar_init(&bars[0], 1);
-    mbar_init(&bars[1], 1);
+    mbar_init(&bars[0], MODE == 2 ? nw * 32 : 1);
+    mbar_init(&bars[1], MODE == 2 ? nw * 32 : 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
@@ -61,6 +63,24 @@ __global__ void __launch_bounds__(1024, 1) k(const float* __restrict__ x, int64_
           for (int r = 0; r < 128; ++r)
             bulk_g2s(buf + s * stage_bytes + r * pitch, x + (int64_t)myrows[r] * ldx + col, S, &bars[s]);
         }
+      }
+      if (nbatch >= 1) mbar_wait(&bars[(nbatch - 1) & 1], ((nbatch - 1) >> 1) & 1);
+      if (nbatch >= 2) mbar_wait(&bars[(nbatch - 2) & 1], ((nbatch - 2) >> 1) & 1);
+    }
+  } else if (MODE == 2) {
+    if (warp < nw) {
+      const int segs = S / 512;  // 512-byte pieces per row segment
+      for (int b = 0; b < nbatch; ++b) {
+        const int s = b & 1;
+        if (b >= 2) mbar_wait(&bars[s], ((b >> 1) - 1) & 1);
+        const int64_t col = (int64_t)(b % ncols_chunks) * (S / 4);
+        for (int r = warp; r < 128; r += nw) {
+          const float* src = x + (int64_t)myrows[r] * ldx + col + lane * 4;
+          const uint32_t dst = smem_u32(buf + s * stage_bytes + r * pitch + lane * 16);
+          for (int g = 0; g < segs; ++g)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + g * 512), "l"(src + g * 128) : "memory");
+        }
+        asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&bars[s])) : "memory");
       }
       if (nbatch >= 1) mbar_wait(&bars[(nbatch - 1) & 1], ((nbatch - 1) >> 1) & 1);
       if (nbatch >= 2) mbar_wait(&bars[(nbatch - 2) & 1], ((nbatch - 2) >> 1) & 1);
@@ -122,6 +142,7 @@ int main() {
   const int smem_max = 200 * 1024;
   cudaFuncSetAttribute(k<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
   cudaFuncSetAttribute(k<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
+  cudaFuncSetAttribute(k<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max);
   auto run = [&](int mode, int S, int pad, int lanes, int nw) {
     const int pitch = S + pad;
     const int ncc = (int)(G * 4 / S);
@@ -132,7 +153,8 @@ int main() {
     for (int rep = 0; rep < 5; ++rep) {
       cudaEventRecord(e0);
       if (mode == 0) k<0><<<nsm, 1024, smem>>>(x, G, rows, nbatch, S, pitch, lanes, nw, ncc, sink);
-      else k<1><<<nsm, 1024, smem>>>(x, G, rows, nbatch, S, pitch, lanes, nw, ncc, sink);
+      else if (mode == 1) k<1><<<nsm, 1024, smem>>>(x, G, rows, nbatch, S, pitch, lanes, nw, ncc, sink);
+      else k<2><<<nsm, 1024, smem>>>(x, G, rows, nbatch, S, pitch, lanes, nw, ncc, sink);
       cudaEventRecord(e1);
       cudaEventSynchronize(e1);
       float ms;
@@ -153,5 +175,7 @@ int main() {
   for (int S : {128, 512}) {
     for (int nw : {4, 8, 16, 32}) run(1, S, 16, 0, nw);
   }
+  for (int nw : {1, 2, 4, 8}) run(2, 512, 16, 0, nw);
+  if (getenv("UBENCH_1K")) for (int nw : {2, 4}) run(2, 1024, 16, 0, nw);
   return 0;
 }
