@@ -47,6 +47,8 @@ extern "C" {
 /* GEMM arithmetic of the fused decoder kernels */
 #define SCVI_PREC_FP32 0   /* FFMA, fp32 everywhere: the parity path */
 #define SCVI_PREC_TC 1     /* tcgen05 tensor-core path (when built) */
+#define SCVI_PREC_PREPACKED 0x100 /* OR-ed into `precision` of scvi_decoder_nll_fwd: the workspace already holds the
+                                     packed weight tiles (scvi_decoder_nll_prepack ran on the current weights) */
 
 int scvi_b200_abi_version(void); /* 3 */
 const char* scvi_last_error_string(void);
@@ -239,6 +241,14 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                          const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
                          int likelihood, int precision, float* reconst, float* row_stats,
                          const float* g_reconst, float* dh, int64_t lddh, void* ws, void* stream);
+/* The parameter-only part of scvi_decoder_nll_fwd (SCVI_PREC_TC: fp16 hi/lo weight tiles, per-gene constants,
+ * lgamma / digamma difference tables) written into the forward's workspace `ws` (same B, H, G, likelihood;
+ * want_dh = the forward will be called with dh != NULL).  It depends on the weights only, so a caller can run
+ * it on a second stream while the encoder computes and then call scvi_decoder_nll_fwd with
+ * precision | SCVI_PREC_PREPACKED.  No-op for SCVI_PREC_FP32. */
+int scvi_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs, const float* Wp,
+                             const float* bp, const float* px_r, int likelihood, int precision, int want_dh,
+                             void* ws, void* stream);
 /* g_reconst [B] = d(loss)/d(reconst).  Writes dh [B,H], dWs/dWp [G,H], dbs/dbp [G], dpx_r [G].
  * ws: scvi_decoder_nll_bwd_ws_bytes().  fwd_ws (nullable; SCVI_PREC_TC only): the workspace of the
  * scvi_decoder_nll_fwd call this backward belongs to (same B, G, likelihood, weights), still intact --

@@ -55,6 +55,7 @@ SIGNATURES = {
     "scvi_mid_n_tiles": (I64, [I64]),
     "scvi_decoder_nll_fwd_ws_bytes": (I64, [I64, I64, I64, I32, I32]),
     "scvi_decoder_nll_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, I64, P, P, I32, I32, P, P, P, P, I64, P, P]),
+    "scvi_decoder_nll_prepack": (C.c_int, [I64, I64, I64, P, P, P, P, P, I32, I32, I32, P, P]),
     "scvi_decoder_nll_bwd_ws_bytes": (I64, [I64, I64, I64, I32]),
     "scvi_decoder_nll_bwd": (
         C.c_int,
@@ -108,3 +109,4 @@ BN_TILE = 64
 LIK_NB, LIK_ZINB = 0, 1
 LIN_LOG1P, LIN_LIBRARY, LIN_TC = 1, 2, 4
 PREC_FP32, PREC_TC = 0, 1
+PREC_PREPACKED = 0x100

@@ -638,7 +638,10 @@ int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood)
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
                        const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
-                       float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws, cudaStream_t st);
+                       float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws, cudaStream_t st,
+                       bool prepacked);
+int tc_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs, const float* Wp,
+                           const float* bp, const float* px_r, int likelihood, bool want_dh, void* ws, cudaStream_t st);
 int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood);
 int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
                           const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
@@ -670,9 +673,11 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                    ((uintptr_t)row_stats % 16 == 0),
                "scvi_decoder_nll_fwd: h / Ws / Wp / row_stats must be 16-byte aligned");
   if (B == 0) return SCVI_OK;
+  const bool prepacked = (precision & SCVI_PREC_PREPACKED) != 0;
+  precision &= ~SCVI_PREC_PREPACKED;
   if (precision == SCVI_PREC_TC)
     return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, likelihood, reconst,
-                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream);
+                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream, prepacked);
   if (precision != SCVI_PREC_FP32) {
     set_error("scvi_decoder_nll_fwd: unknown precision %d", precision);
     return SCVI_EUNSUPPORTED;
@@ -695,6 +700,19 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                                 likelihood, precision, dh, lddh, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
                                 nullptr, stream);
   return SCVI_OK;
+}
+
+int scvi_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs, const float* Wp,
+                             const float* bp, const float* px_r, int likelihood, int precision, int want_dh,
+                             void* ws, void* stream) {
+  using namespace scvi;
+  const bool zinb = likelihood == SCVI_LIK_ZINB;
+  SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "scvi_decoder_nll_prepack: unknown likelihood %d", likelihood);
+  SCVI_REQUIRE(Ws && bs && px_r && (!zinb || (Wp && bp)), "scvi_decoder_nll_prepack: NULL pointer");
+  SCVI_REQUIRE(B >= 0 && G > 0 && H > 0, "scvi_decoder_nll_prepack: bad shape");
+  if (precision != SCVI_PREC_TC) return SCVI_OK;  // the FFMA path has nothing to prepare
+  if (B == 0) return SCVI_OK;
+  return tc_decoder_nll_prepack(B, H, G, Ws, bs, Wp, bp, px_r, likelihood, want_dh != 0, ws, (cudaStream_t)stream);
 }
 
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood) {

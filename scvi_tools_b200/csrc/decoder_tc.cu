@@ -470,11 +470,33 @@ int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t 
                      const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
                      cudaStream_t st);
 
+// The parameter-only part of tc_decoder_nll_fwd (packed fp16 weight tiles, per-gene constants and tables)
+// into the same workspace layout: lets the caller run it on another stream while the encoder computes.
+int tc_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs, const float* Wp,
+                           const float* bp, const float* px_r, int likelihood, bool want_dh, void* ws, cudaStream_t st) {
+  const bool zinb = likelihood == SCVI_LIK_ZINB;
+  if (H != TC_H) {
+    set_error("scvi_decoder_nll_prepack: n_hidden must be %d (got %lld)", TC_H, (long long)H);
+    return SCVI_EUNSUPPORTED;
+  }
+  SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_prepack: ws must be 256-byte aligned");
+  const int nheads = zinb ? 2 : 1;
+  const TcPlan p = tc_plan(B, G, nheads);
+  uint8_t* w8 = (uint8_t*)ws;
+  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * fm::LGT);
+  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f,
+                                                                    (__half*)(w8 + p.off_packed),
+                                                                    want_dh ? w8 + p.off_packed32 : nullptr,
+                                                                    (float*)(w8 + p.off_gconst));
+  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
+  return SCVI_OK;
+}
+
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
                        const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
                        float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
-                       cudaStream_t st) {
+                       cudaStream_t st, bool prepacked) {
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   if (H != TC_H) {
     set_error("scvi_decoder_nll_fwd(SCVI_PREC_TC): n_hidden must be %d (got %lld)", TC_H, (long long)H);
@@ -490,9 +512,11 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
   float* lse = (float*)(w8 + p.off_lse);
   float* outp = (float*)(w8 + p.off_out);
   uint8_t* packed32 = dh ? w8 + p.off_packed32 : nullptr;
-  const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * fm::LGT);
-  tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, packed32, gconst);
-  SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
+  if (!prepacked) {
+    const int64_t items = std::max<int64_t>(p.nT * nheads * TC_KC * TC_N, p.nT * TC_N * fm::LGT);
+    tc_pack_heads_kernel<<<(unsigned)cdiv(items, 256), 256, 0, st>>>(Ws, bs, Wp, bp, px_r, G, nheads, 1e-8f, packed, packed32, gconst);
+    SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc pack)");
+  }
   const int xvec = (ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0);
   int rc;
   if (dh) {  // training: LSE pass, then the fused NLL + dh kernel

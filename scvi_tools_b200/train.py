@@ -100,6 +100,8 @@ class FusedTrainingPlan:
         self._build_arena()
         self._alloc_step_buffers()
         self._graphs = None
+        self._side = None
+        self.overlap = True  # independent launches on a second stream / parallel graph branches
         if self.world > 1:
             self._comm = torch.cuda.Stream(device=self.dev)
             self._ev_heads_ready, self._ev_heads_reduced = torch.cuda.Event(), torch.cuda.Event()
@@ -199,9 +201,14 @@ class FusedTrainingPlan:
         self.ws_enc = torch.empty(int(ne), dtype=torch.uint8, device=dev) if ne > 0 else None
 
     # ------------------------------------------------------------------ the step
-    def _forward_backward(self, st):
+    def _forward_backward(self, st, overlap: bool = False):
         """Kernel sequence of one minibatch: forward, ELBO, backward into the gradient arena.
-        Rows are read from the resident matrix through `self.idx`.  `st` = cudaStream_t."""
+        Rows are read from the resident matrix through `self.idx`.  `st` = cudaStream_t of the current stream.
+
+        `overlap`: the launches that depend on nothing the main chain is computing run on a second stream
+        (fork / join with events, captured as parallel branches of the step graph): the decoder-head packing
+        (weights only) next to the encoder + middle forward, the ELBO scalar reduction (not needed by the
+        backward, whose seeds come from the step prologue) next to the decoder backward."""
         B, G, H, L = self.B_cur, self.G, self.H, self.L
         P, Gd, X = self.P, self.Gd, self.data.X
         if X.dtype != torch.float32:
@@ -209,6 +216,18 @@ class FusedTrainingPlan:
         ldx = X.stride(0)
         lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
         prec = self.module.precision
+        Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
+        Wp = P.get("decoder.px_dropout_decoder.weight")
+        bp = P.get("decoder.px_dropout_decoder.bias")
+        overlap = overlap and prec == _lib.PREC_TC
+        main = torch.cuda.current_stream()
+        if overlap:
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=self.dev)
+            side = self._side
+            side.wait_stream(main)
+            call("scvi_decoder_nll_prepack", B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), lik, prec, 1,
+                 _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
         # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
              None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc, _p(self.y1), H, _p(self.library), _p(self.part1),
@@ -230,15 +249,19 @@ class FusedTrainingPlan:
         else:
             self._middle_forward_unfused(st, B, H, L, drop, dscale, inj, ncols)
         # ---- fused heads + softmax + likelihood
-        Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
-        Wp = P.get("decoder.px_dropout_decoder.weight")
-        bp = P.get("decoder.px_dropout_decoder.bias")
         # the ELBO is a mean over the minibatch, so d(loss)/d(reconst) = 1/B is known before the forward
         # (seeded by the step prologue): the fused kernel emits dh together with the likelihood
+        if overlap:
+            main.wait_stream(side)  # packed weight tiles ready
         call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), lik, prec, _p(self.reconst), _p(self.stats), _p(self.g_rec), _p(self.dh), H,
-             _p(self.ws_fwd), st)
-        call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
+             _p(self.idx), _p(self.library), lik, prec | (_lib.PREC_PREPACKED if overlap else 0), _p(self.reconst),
+             _p(self.stats), _p(self.g_rec), _p(self.dh), H, _p(self.ws_fwd), st)
+        if overlap:
+            side.wait_stream(main)
+            call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3),
+                 C.c_void_p(side.cuda_stream))
+        else:
+            call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         # ---- backward
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
              _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, None, H,
@@ -263,6 +286,8 @@ class FusedTrainingPlan:
              _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
              None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0,
              _p(self.dy1_amax) if self.use_mid else None, self.dy1_amax.numel() if self.use_mid else 0, _p(self.ws), st)
+        if overlap:
+            main.wait_stream(side)  # join: the ELBO scalars are part of the step's result
 
     def _middle_forward_unfused(self, st, B, H, L, drop, dscale, inj, ncols):
         P = self.P
@@ -344,7 +369,7 @@ class FusedTrainingPlan:
     def _whole_step(self, feed_rng: bool = True):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         self._prologue(st, feed_rng)
-        self._forward_backward(st)
+        self._forward_backward(st, overlap=self.overlap)
         self._reduce_gradients()
         self._adam(st)
 
@@ -375,7 +400,7 @@ class FusedTrainingPlan:
             with torch.cuda.graph(g1):
                 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
                 self._prologue(st)
-                self._forward_backward(st)
+                self._forward_backward(st, overlap=self.overlap)
             with torch.cuda.graph(g2):
                 self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream))
             self._graphs = (g1, g2)
