@@ -23,8 +23,11 @@ import sys
 import threading
 import time
 
-import numpy as np
-import torch
+# NCCL's version banner (NCCL_DEBUG=VERSION/INFO on some boxes) must not land on stdout next to the JSON line
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
