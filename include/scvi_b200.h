@@ -114,6 +114,20 @@ int scvi_zinb_logprob_bwd(const float* x, int64_t ldx, const float* mu, int64_t 
                           const float* theta, int64_t theta_ld, const float* pi, int64_t ldpi,
                           const float* gout, int64_t ldg, int64_t B, int64_t G, float eps, float* dmu,
                           float* dtheta, float* dpi, void* stream);
+/* ---- negative-binomial mixture likelihood (TOTALVI proteins) ----------
+ * replaces log_mixture_nb with a shared inverse dispersion (theta_2 = None) as called by
+ * NegativeBinomialMixture.log_prob (src/scvi/distributions/_negative_binomial.py:138-216, :589-717):
+ *   out = logsumexp(log NB(x; mu1, theta), log NB(x; mu2, theta) - pi) - softplus(-pi),  pi = mixture logit.
+ * x, mu1, mu2, pi, out are [B,P] with row strides ld*; theta is [P] (theta_ld = 0) or [B,P].
+ * backward: same conventions as scvi_nb_logprob_bwd (dtheta per-row-tile partials when theta_ld == 0). */
+int scvi_mixture_nb_logprob_fwd(const float* x, int64_t ldx, const float* mu1, int64_t ldmu1, const float* mu2,
+                                int64_t ldmu2, const float* theta, int64_t theta_ld, const float* pi,
+                                int64_t ldpi, int64_t B, int64_t P, float eps, float* out, int64_t ldo,
+                                int32_t* bad_support, void* stream);
+int scvi_mixture_nb_logprob_bwd(const float* x, int64_t ldx, const float* mu1, int64_t ldmu1, const float* mu2,
+                                int64_t ldmu2, const float* theta, int64_t theta_ld, const float* pi,
+                                int64_t ldpi, const float* gout, int64_t ldg, int64_t B, int64_t P, float eps,
+                                float* dmu1, float* dmu2, float* dtheta, float* dpi, void* stream);
 /* out[n] = sum_t partials[t, n] in fixed order (deterministic) */
 int scvi_colsum_partials(const float* partials, int64_t n_tiles, int64_t N, float* out, int accumulate,
                          void* stream);

@@ -142,6 +142,8 @@ def load():
         ZeroInflatedNegativeBinomial=nbm.ZeroInflatedNegativeBinomial,
         log_nb_positive=nbm.log_nb_positive,
         log_zinb_positive=nbm.log_zinb_positive,
+        log_mixture_nb=nbm.log_mixture_nb,
+        NegativeBinomialMixture=nbm.NegativeBinomialMixture,
         LossOutput=bm.LossOutput,
         MODULE_KEYS=mconst.MODULE_KEYS,
         REGISTRY_KEYS=scvi.REGISTRY_KEYS,

@@ -6,7 +6,8 @@ Importing the package does not need a GPU; running any op does (there is no CPU 
 """
 
 from . import _lib
-from .distributions import NegativeBinomial, ZeroInflatedNegativeBinomial, log_nb_positive, log_zinb_positive
+from .distributions import (NegativeBinomial, NegativeBinomialMixture, ZeroInflatedNegativeBinomial, log_mixture_nb,
+                            log_nb_positive, log_zinb_positive)
 from .module import MODULE_KEYS, REGISTRY_KEYS, VAE, LossOutput
 from .nn import DecoderSCVI, Encoder, FCLayers, rng_feed
 from .scanvi import SCANVAE, Classifier, Decoder
@@ -14,6 +15,6 @@ from .model import SCVI  # noqa: E402  (after the module classes it builds on)
 
 __all__ = [
     "SCVI", "VAE", "SCANVAE", "Classifier", "Decoder", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
-    "NegativeBinomial", "ZeroInflatedNegativeBinomial", "log_nb_positive", "log_zinb_positive", "rng_feed",
+    "NegativeBinomial", "ZeroInflatedNegativeBinomial", "NegativeBinomialMixture", "log_mixture_nb", "log_nb_positive", "log_zinb_positive", "rng_feed",
 ]
 __version__ = "0.1.0"

@@ -34,6 +34,9 @@ SIGNATURES = {
     "scvi_zinb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),
     "scvi_nb_logprob_bwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, P, P]),
     "scvi_zinb_logprob_bwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, P, P, P]),
+    "scvi_mixture_nb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),
+    "scvi_mixture_nb_logprob_bwd": (
+        C.c_int, [P, I64, P, I64, P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, P, P, P, P]),
     "scvi_colsum_partials": (C.c_int, [P, I64, I64, P, I32, P]),
     "scvi_linear_fwd_ws_bytes": (I64, [I64, I64, I64, I32]),
     "scvi_linear_fwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I64, P, P, I32, I32, P, I64, P, P, P, P]),

@@ -157,3 +157,75 @@ class ZeroInflatedNegativeBinomial(NegativeBinomial):
         elif os.environ.get("SCVI_B200_SYNC_VALIDATE", "1") == "1" and not out.requires_grad:
             self.check_support()
         return out
+
+
+def log_mixture_nb(x, mu_1, mu_2, theta_1, theta_2, pi_logits, eps: float = 1e-8, log_fn=None, lgamma_fn=None):
+    """Log-likelihood of a two-component NB mixture (reference :138-216); `pi_logits` is the logit of
+    belonging to the first (background, for totalVI) component.  One shared inverse dispersion
+    (`theta_2 is None`, the totalVI case) runs as one fused kernel; two dispersions combine the NB kernel
+    outputs."""
+    if theta_2 is None:
+        return ops.mixture_nb_log_prob(x, mu_1, mu_2, theta_1, pi_logits, eps)
+    log_nb_1 = ops.nb_log_prob(x, mu_1, theta_1, eps)
+    log_nb_2 = ops.nb_log_prob(x, mu_2, theta_2, eps)
+    return torch.logsumexp(torch.stack((log_nb_1, log_nb_2 - pi_logits)), dim=0) - torch.nn.functional.softplus(-pi_logits)
+
+
+class NegativeBinomialMixture(Distribution):
+    """Negative binomial mixture (reference :589-717): components (`mu1`, `theta1`) and (`mu2`, `theta2` or
+    `theta1`), `mixture_logits` = logit of component 1."""
+
+    arg_constraints = {}
+    support = constraints.nonnegative_integer
+
+    def __init__(self, mu1, mu2, theta1, mixture_logits, theta2=None, validate_args: bool = False):
+        self._theta1_compact = theta1
+        self.mu1, self.theta1, self.mu2, self.mixture_logits = broadcast_all(mu1, theta1, mu2, mixture_logits)
+        super().__init__(batch_shape=self.mu1.shape, validate_args=False)
+        self._validate_args = bool(validate_args)
+        self.theta2 = broadcast_all(mu1, theta2) if theta2 is not None else None
+        self._theta2_arg = theta2
+        self._bad = None
+
+    @property
+    def mean(self):
+        pi = self.mixture_probs
+        return pi * self.mu1 + (1 - pi) * self.mu2
+
+    def get_normalized(self, key):
+        if key == "mu":
+            return self.rate
+        if key == "scale":
+            return self.scale
+        raise ValueError(f"normalized key {key} not recognized")
+
+    @lazy_property
+    def mixture_probs(self):
+        return logits_to_probs(self.mixture_logits, is_binary=True)
+
+    @torch.inference_mode()
+    def sample(self, sample_shape=None):
+        sample_shape = sample_shape or torch.Size()
+        mixing = torch.distributions.Bernoulli(self.mixture_probs).sample()
+        mu = self.mu1 * mixing + self.mu2 * (1 - mixing)
+        theta = self.theta1 if self.theta2 is None else self.theta1 * mixing + self.theta2[1] * (1 - mixing)
+        rate = torch.clamp(Gamma(concentration=theta, rate=theta / mu).sample(sample_shape), max=1e8)
+        return PoissonTorch(rate).sample()
+
+    def check_support(self):
+        if self._bad is not None and int(self._bad.item()) != 0:
+            warnings.warn(_SUPPORT_MSG, UserWarning, stacklevel=2)
+            return False
+        return True
+
+    def log_prob(self, value):
+        if self._theta2_arg is not None:
+            return log_mixture_nb(value, self.mu1, self.mu2, self.theta1, self._theta2_arg, self.mixture_logits)
+        self._bad = torch.zeros(1, dtype=torch.int32, device=value.device)
+        out = ops.mixture_nb_log_prob(value, self.mu1, self.mu2, self._theta1_compact, self.mixture_logits, 1e-8, self._bad)
+        if os.environ.get("SCVI_B200_SYNC_VALIDATE", "1") == "1" and not out.requires_grad:
+            self.check_support()  # the reference warns on out-of-support values (:690-697)
+        return out
+
+    def __repr__(self):
+        return f"{self.__class__.__name__}(mu1: {tuple(self.mu1.shape)}, theta1: {tuple(self.theta1.shape)})"

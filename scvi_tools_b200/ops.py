@@ -184,6 +184,65 @@ def zinb_log_prob(x, mu, theta, pi, eps=1e-8, bad_flag=None):
     return _LogProb.apply(x, mu, theta, pi, eps, bad_flag)
 
 
+class _MixtureLogProb(torch.autograd.Function):
+    """log_mixture_nb with one shared inverse dispersion (reference _negative_binomial.py:138-216)."""
+
+    @staticmethod
+    def forward(ctx, x, mu1, mu2, theta, pi, eps, bad_flag):
+        shape = torch.broadcast_shapes(x.shape, mu1.shape, mu2.shape, theta.shape, pi.shape)
+        Pn = shape[-1]
+        per_col = theta.numel() == Pn and (theta.dim() == 1 or all(s == 1 for s in theta.shape[:-1]))
+        ex = lambda t, n: _check(t, n).expand(shape).reshape(-1, Pn).contiguous()  # noqa: E731
+        xe, m1, m2, pie = ex(x, "x"), ex(mu1, "mu1"), ex(mu2, "mu2"), ex(pi, "pi_logits")
+        the = _check(theta, "theta").reshape(-1).contiguous() if per_col else ex(theta, "theta")
+        B = xe.shape[0]
+        out = torch.empty(B, Pn, dtype=torch.float32, device=x.device)
+        if B > 0 and Pn > 0:
+            call("scvi_mixture_nb_logprob_fwd", _ptr(xe), Pn, _ptr(m1), Pn, _ptr(m2), Pn, _ptr(the),
+                 0 if per_col else Pn, _ptr(pie), Pn, B, Pn, eps, _ptr(out), Pn, _ptr(bad_flag), _stream())
+        ctx.save_for_backward(xe, m1, m2, the, pie)
+        ctx.meta = (shape, mu1.shape, mu2.shape, theta.shape, pi.shape, per_col, eps)
+        return out.view(shape)
+
+    @staticmethod
+    def backward(ctx, gout):
+        xe, m1, m2, the, pie = ctx.saved_tensors
+        shape, s1, s2, sth, spi, per_col, eps = ctx.meta
+        B, Pn = xe.shape
+        g = gout.expand(shape).reshape(B, Pn).contiguous().float()
+        n1, n2, nth, npi = ctx.needs_input_grad[1:5]
+        d1 = torch.empty_like(m1) if n1 else None
+        d2 = torch.empty_like(m1) if n2 else None
+        dpi = torch.empty_like(m1) if npi else None
+        T = (B + _lib.BN_TILE - 1) // _lib.BN_TILE
+        dth = torch.empty((T, Pn) if per_col else (B, Pn), dtype=torch.float32, device=xe.device) if nth else None
+        if B > 0 and Pn > 0:
+            call("scvi_mixture_nb_logprob_bwd", _ptr(xe), Pn, _ptr(m1), Pn, _ptr(m2), Pn, _ptr(the),
+                 0 if per_col else Pn, _ptr(pie), Pn, _ptr(g), Pn, B, Pn, eps, _ptr(d1), _ptr(d2), _ptr(dth),
+                 _ptr(dpi), _stream())
+        elif nth:
+            dth.zero_()
+        if nth and per_col and T > 0:
+            red = torch.empty(Pn, dtype=torch.float32, device=xe.device)
+            call("scvi_colsum_partials", _ptr(dth), T, Pn, _ptr(red), 0, _stream())
+            dth = red.view(sth)
+        elif nth and per_col:
+            dth = torch.zeros(sth, dtype=torch.float32, device=xe.device)
+        elif nth:
+            dth = dth.view(shape).sum_to_size(sth)
+        if n1:
+            d1 = d1.view(shape).sum_to_size(s1)
+        if n2:
+            d2 = d2.view(shape).sum_to_size(s2)
+        if npi:
+            dpi = dpi.view(shape).sum_to_size(spi)
+        return None, d1, d2, dth, dpi, None, None
+
+
+def mixture_nb_log_prob(x, mu1, mu2, theta, pi_logits, eps=1e-8, bad_flag=None):
+    return _MixtureLogProb.apply(x, mu1, mu2, theta, pi_logits, eps, bad_flag)
+
+
 # --------------------------------------------------------------------------------------
 # a2 / a3: FCLayers linear layer with covariate injection
 # --------------------------------------------------------------------------------------
