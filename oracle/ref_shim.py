@@ -14,6 +14,7 @@ loads, with ``importlib``, exactly these reference files where they lie (nothing
     src/scvi/module/base/_embedding_mixin.py   src/scvi/module/base/_base_module.py
     src/scvi/module/_vae.py
     src/scvi/module/_utils.py  src/scvi/module/_classifier.py  src/scvi/module/_scanvae.py   (SCANVI, 8f rank 1)
+    src/scvi/module/_totalvae.py                                                             (TOTALVI, 8f rank 2)
 
 It only works where ``/root/reference`` exists (the build container).  It is used by
 ``oracle/make_golden.py`` (to generate ``tests/golden/*.npz``) and by the
@@ -101,7 +102,7 @@ def load():
     emb = _load("scvi.nn._embedding", "nn/_embedding.py")
     nn.Embedding = emb.Embedding
     bc = _load("scvi.nn._base_components", "nn/_base_components.py")
-    for k in ("FCLayers", "Encoder", "DecoderSCVI", "Decoder"):
+    for k in ("FCLayers", "Encoder", "DecoderSCVI", "Decoder", "DecoderTOTALVI", "EncoderTOTALVI"):
         setattr(nn, k, getattr(bc, k))
     scvi.nn = nn
 
@@ -128,11 +129,20 @@ def load():
     module.Classifier = cls.Classifier
     scanvae = _load("scvi.module._scanvae", "module/_scanvae.py")
     module.SCANVAE = scanvae.SCANVAE
+    # _totalvae.py imports BaseModelClass for a type annotation only
+    model_pkg = _pkg("scvi.model")
+    model_base = _pkg("scvi.model.base")
+    model_base.BaseModelClass = object
+    model_pkg.base = model_base
+    scvi.model = model_pkg
+    totalvae = _load("scvi.module._totalvae", "module/_totalvae.py")
+    module.TOTALVAE = totalvae.TOTALVAE
     scvi.module = module
 
     _LOADED = types.SimpleNamespace(
         VAE=vae.VAE,
         SCANVAE=scanvae.SCANVAE,
+        TOTALVAE=totalvae.TOTALVAE,
         Classifier=cls.Classifier,
         Decoder=bc.Decoder,
         FCLayers=bc.FCLayers,

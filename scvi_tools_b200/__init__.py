@@ -11,10 +11,11 @@ from .distributions import (NegativeBinomial, NegativeBinomialMixture, ZeroInfla
 from .module import MODULE_KEYS, REGISTRY_KEYS, VAE, LossOutput
 from .nn import DecoderSCVI, Encoder, FCLayers, rng_feed
 from .scanvi import SCANVAE, Classifier, Decoder
+from .totalvi import TOTALVAE, DecoderTOTALVI, EncoderTOTALVI
 from .model import SCVI  # noqa: E402  (after the module classes it builds on)
 
 __all__ = [
-    "SCVI", "VAE", "SCANVAE", "Classifier", "Decoder", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
+    "SCVI", "VAE", "SCANVAE", "Classifier", "Decoder", "TOTALVAE", "EncoderTOTALVI", "DecoderTOTALVI", "LossOutput", "MODULE_KEYS", "REGISTRY_KEYS", "FCLayers", "Encoder", "DecoderSCVI",
     "NegativeBinomial", "ZeroInflatedNegativeBinomial", "NegativeBinomialMixture", "log_mixture_nb", "log_nb_positive", "log_zinb_positive", "rng_feed",
 ]
 __version__ = "0.1.0"
