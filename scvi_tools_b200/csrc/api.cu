@@ -80,6 +80,7 @@ __global__ void colsum_flat_kernel(const float* __restrict__ part, int64_t T, in
   const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;
   float tot = 0.f;
+#pragma unroll 4
   for (int64_t t = 0; t < T; ++t) tot += part[t * stride + e];
   for (int i = 0; i < segs.n; ++i)
     if (segs.dst[i] && e >= segs.begin[i] && e < segs.end[i]) segs.dst[i][e - segs.begin[i]] = tot;

@@ -357,6 +357,7 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
     m = mn;
   }
   float nll = 0.f, S = 0.f;
+#pragma unroll 8
   for (int sp = 0; sp < nsplit; ++sp) {
     const float2 o = *reinterpret_cast<const float2*>(out_part + ((int64_t)sp * B + b) * 2);
     nll += o.x;
@@ -368,6 +369,7 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
   }
   if (dh) {
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
+#pragma unroll 8
     for (int sp = 0; sp < nsplit; ++sp) {
       const float4 va = *reinterpret_cast<const float4*>(dh_part + (((int64_t)sp * 2 + 0) * B + b) * TC_H + 4 * lane);
       const float4 vb = *reinterpret_cast<const float4*>(dh_part + (((int64_t)sp * 2 + 1) * B + b) * TC_H + 4 * lane);
@@ -729,6 +731,7 @@ static __global__ void tt_bwd_reduce_kernel(const float* __restrict__ slabW, con
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (e < GH) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f), p = s;
+#pragma unroll 4
     for (int64_t t = 0; t < splits; ++t) {
       const float4 a = *reinterpret_cast<const float4*>(slabW + (t * nheads + 0) * GH + e);
       s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
@@ -743,6 +746,7 @@ static __global__ void tt_bwd_reduce_kernel(const float* __restrict__ slabW, con
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (g < G) {
     float a = 0.f, b = 0.f, c = 0.f;
+#pragma unroll 4
     for (int64_t t = 0; t < splits; ++t) {
       a += slabv[(t * 3 + 0) * G + g];
       b += slabv[(t * 3 + 1) * G + g];

@@ -286,20 +286,24 @@ __global__ void __launch_bounds__(512)
   const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
   const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
   const float bv = bias ? bias[col] : 0.f;
+  // split outermost, the thread's 16 rows innermost: 16 independent loads in flight per split (the per-element
+  // summation order bias + split 0 + split 1 + ... is unchanged)
   float vals[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) vals[i] = (rg * 16 + i < cnt) ? bv : 0.f;
+  for (int sp = 0; sp < nsplit; ++sp) {
+    const float* yp = ypart + ((int64_t)sp * B + r0 + rg * 16) * TC_H + col;
+#pragma unroll
+    for (int i = 0; i < 16; ++i)
+      if (rg * 16 + i < cnt) vals[i] += yp[i * TC_H];
+  }
   float s = 0.f;
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const int rr = rg * 16 + i;
-    float v = 0.f;
-    if (rr < cnt) {
-      v = bv;
-      for (int sp = 0; sp < nsplit; ++sp) v += ypart[((int64_t)sp * B + r0 + rr) * TC_H + col];
-      y[(r0 + rr) * ldy + col] = v;
-      s += v;
+  for (int i = 0; i < 16; ++i)
+    if (rg * 16 + i < cnt) {
+      y[(r0 + rg * 16 + i) * ldy + col] = vals[i];
+      s += vals[i];
     }
-    vals[i] = v;
-  }
   s_scr[rg][col] = s;
   __syncthreads();
   const float mean = ((s_scr[0][col] + s_scr[1][col]) + (s_scr[2][col] + s_scr[3][col])) / (float)cnt;
@@ -319,6 +323,7 @@ __global__ void __launch_bounds__(512)
   }
   if (library && threadIdx.x < cnt) {
     float t = 0.f;
+#pragma unroll 8
     for (int sp = 0; sp < nsplit; ++sp) t += rowsum_part[(int64_t)sp * B + r0 + threadIdx.x];
     library[r0 + threadIdx.x] = logf(t);
   }
