@@ -146,18 +146,29 @@ __global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
     if (A.rv1) A.rv1[col] = (1.f - A.momentum) * A.rv1[col] + A.momentum * (var * n / fmaxf(n - 1.f, 1.f));
   }
   const float g1 = A.gamma1[col], b1 = A.beta1[col];
-#pragma unroll 4
-  for (int i = 0; i < MD_RPT; ++i) {
-    const int r = rg * MD_RPT + i;
-    float a = 0.f;
-    if (r < cnt) {
+  {  // all of the thread's loads first (independent, in flight together), then the math
+    float yv[MD_RPT];
+    uint8_t mk[MD_RPT];
+#pragma unroll
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
       const int64_t o = (r0 + r) * MD_H + col;
-      const float u = (A.y1[o] - mean) * (rstd * g1) + b1;
-      a = fmaxf(u, 0.f);
-      if (A.mask) a = A.mask[o] ? a * A.drop_scale : 0.f;
-      A.a1[o] = a;
+      yv[i] = (r < cnt) ? A.y1[o] : 0.f;
+      mk[i] = (r < cnt && A.mask) ? A.mask[o] : (uint8_t)1;
     }
-    s_a[r * MD_H + col] = a;
+#pragma unroll
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
+      float a = 0.f;
+      if (r < cnt) {
+        const int64_t o = (r0 + r) * MD_H + col;
+        const float u = (yv[i] - mean) * (rstd * g1) + b1;
+        a = fmaxf(u, 0.f);
+        if (A.mask) a = mk[i] ? a * A.drop_scale : 0.f;
+        A.a1[o] = a;
+      }
+      s_a[r * MD_H + col] = a;
+    }
   }
   __syncthreads();
   // latent heads: 64 x 2L dot products of length 128
@@ -257,13 +268,20 @@ __global__ void __launch_bounds__(MD_THREADS)
   const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
   const float mu = mean2[col], rs = rstd2[col], g = gamma2[col], b = beta2[col];
   float s1 = 0.f, s2 = 0.f;
-#pragma unroll 4
+  float yv[MD_RPT], dv[MD_RPT];  // dh is loaded whatever the ReLU mask says: no load waits on another
+#pragma unroll
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
+    const int64_t o = (r0 + r) * MD_H + col;
+    yv[i] = (r < cnt) ? y2[o] : 0.f;
+    dv[i] = (r < cnt) ? dh[o] : 0.f;
+  }
+#pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
     if (r < cnt) {
-      const int64_t o = (r0 + r) * MD_H + col;
-      const float xhat = (y2[o] - mu) * rs;
-      const float d = (xhat * g + b > 0.f) ? dh[o] : 0.f;
+      const float xhat = (yv[i] - mu) * rs;
+      const float d = (xhat * g + b > 0.f) ? dv[i] : 0.f;
       s1 += d;
       s2 = fmaf(d, xhat, s2);
     }
@@ -324,6 +342,15 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   for (int e = tid; e < MD_ROWS * L; e += MD_THREADS) s_z[e] = (e / L < cnt) ? A.z[r0 * L + e] : 0.f;
   if (tid < MD_ROWS) s_cat[tid] = (A.cov_cols && tid < cnt) ? A.cov_cols[r0 + tid] : -1;
 
+  // the thread's y2 / dh values: loaded ahead of the partial merge so their latency hides behind it
+  float yv2[MD_RPT], dv2[MD_RPT];
+#pragma unroll
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
+    const int64_t o = (r0 + r) * MD_H + col;
+    yv2[i] = (r < cnt) ? A.y2[o] : 0.f;
+    dv2[i] = (r < cnt) ? A.dh[o] : 0.f;
+  }
   float S1, S2;
   md_merge_sum2(A.bpart2, T, s_scr, S1, S2);
   if (blockIdx.x == 0 && rg == 0) {
@@ -333,14 +360,13 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   const float invB = 1.f / (float)A.B;
   {
     const float mu = A.mean2[col], rs = A.rstd2[col], g = A.gamma2[col], b = A.beta2[col];
-#pragma unroll 4
+#pragma unroll
     for (int i = 0; i < MD_RPT; ++i) {
       const int r = rg * MD_RPT + i;
       float v = 0.f;
       if (r < cnt) {
-        const int64_t o = (r0 + r) * MD_H + col;
-        const float xhat = (A.y2[o] - mu) * rs;
-        const float d = (xhat * g + b > 0.f) ? A.dh[o] : 0.f;
+        const float xhat = (yv2[i] - mu) * rs;
+        const float d = (xhat * g + b > 0.f) ? dv2[i] : 0.f;
         v = rs * g * (d - S1 * invB - xhat * (S2 * invB));
       }
       s_t[r * MD_H + col] = v;  // dy2
@@ -384,7 +410,16 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   {
     const float mu = A.mean1[col], rs = A.rstd1[col], g = A.gamma1[col], b = A.beta1[col];
     float s1 = 0.f, s2 = 0.f;
-#pragma unroll 2
+    float y1v[MD_RPT];
+    uint8_t mk[MD_RPT];
+#pragma unroll
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
+      const int64_t o = (r0 + r) * MD_H + col;
+      y1v[i] = (r < cnt) ? A.y1[o] : 0.f;
+      mk[i] = (r < cnt && A.mask) ? A.mask[o] : (uint8_t)1;
+    }
+#pragma unroll
     for (int i = 0; i < MD_RPT; ++i) {
       const int r = rg * MD_RPT + i;
       if (r < cnt) {
@@ -392,9 +427,9 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
         for (int j = 0; j < L2; ++j) s = fmaf(s_dq[r * L2 + j], s_W[j * 129 + col], s);
         const int64_t o = (r0 + r) * MD_H + col;
         A.da1[o] = s;
-        const float xhat = (A.y1[o] - mu) * rs;
+        const float xhat = (y1v[i] - mu) * rs;
         float d = s;
-        if (A.mask) d = A.mask[o] ? d * A.drop_scale : 0.f;
+        if (A.mask) d = mk[i] ? d * A.drop_scale : 0.f;
         if (!(xhat * g + b > 0.f)) d = 0.f;
         s1 += d;
         s2 = fmaf(d, xhat, s2);
@@ -405,7 +440,7 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
     s_scr[(4 + rg) * MD_H + col] = s2;
   }
   // a1 tile -> s_t for the latent weight gradients
-#pragma unroll 4
+#pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
     s_t[r * MD_H + col] = (r < cnt) ? A.a1[(r0 + r) * MD_H + col] : 0.f;
