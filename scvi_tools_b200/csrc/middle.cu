@@ -11,9 +11,12 @@
 // One CTA = one tile of MD_ROWS rows, 512 threads.  Batch statistics cross CTAs through
 // per-tile partials (mean, M2 / sums) that every CTA of the NEXT kernel merges redundantly in a fixed
 // order (deterministic, no grid barrier, no atomics).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace scvi {
+namespace cg = cooperative_groups;
 
 constexpr int MD_H = 128;
 constexpr int MD_ROWS = 32;            // rows per CTA (two CTAs per SM hide each other's latency)
@@ -21,6 +24,55 @@ constexpr int MD_RPT = MD_ROWS / 4;    // rows per thread: thread = (column, one
 constexpr int MD_THREADS = 512;
 constexpr int MD_LMAX = 16;            // n_latent <= 16
 constexpr int MD_WD_LD = 81;           // decoder layer-0 weight row stride in smem (n_latent + n_batch <= 80)
+// The kernels that produce per-tile column statistics run as thread-block clusters of MD_CL CTAs: rank 0 sums
+// the cluster's tile partials through distributed shared memory (rank order: deterministic) and writes ONE
+// partial per cluster, so the consumers merge T / 8 partials (8 MB of L2 traffic per kernel instead of 64 MB
+// at B = 8192).  The grid is padded to a multiple of MD_CL; padded CTAs only take part in the cluster barriers.
+constexpr int MD_CL = 8;
+__host__ __device__ inline int64_t md_clusters(int64_t B) { return (B + MD_ROWS * MD_CL - 1) / (MD_ROWS * MD_CL); }
+
+// s_cl[2][128] of every CTA of the cluster -> part[cluster][2][128] (sums).  All threads of all CTAs call it.
+__device__ __forceinline__ void md_cluster_sum2(float* s_cl, float* __restrict__ part) {
+  cg::cluster_group cl = cg::this_cluster();
+  cl.sync();
+  const int col = threadIdx.x & 127, q = threadIdx.x >> 7;
+  if (cl.block_rank() == 0 && q < 2) {
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) acc += cl.map_shared_rank(s_cl, k)[q * MD_H + col];
+    part[((int64_t)(blockIdx.x / MD_CL) * 2 + q) * MD_H + col] = acc;
+  }
+  cl.sync();  // the other CTAs' shared memory stays alive until rank 0 has read it
+}
+
+// s_cl = (mean[128], M2[128]) of every CTA's tile -> part[cluster][2][128] = (mean, M2) of the cluster's rows
+// (count-weighted merge, rank order).  Tiles past the end of the batch have count 0.
+__device__ __forceinline__ void md_cluster_stats(float* s_cl, int64_t B, float* __restrict__ part) {
+  cg::cluster_group cl = cg::this_cluster();
+  cl.sync();
+  if (cl.block_rank() == 0 && threadIdx.x < MD_H) {
+    const int col = threadIdx.x;
+    const int64_t cid = blockIdx.x / MD_CL, r0c = cid * MD_CL * MD_ROWS;
+    float n[MD_CL], m[MD_CL], ntot = 0.f, msum = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) {
+      n[k] = (float)max((int64_t)0, min((int64_t)MD_ROWS, B - (r0c + (int64_t)k * MD_ROWS)));
+      m[k] = cl.map_shared_rank(s_cl, k)[col];
+      ntot += n[k];
+      msum = fmaf(n[k], m[k], msum);
+    }
+    const float mean = msum / ntot;
+    float m2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) {
+      const float d = m[k] - mean;
+      m2 += fmaf(n[k], d * d, cl.map_shared_rank(s_cl, k)[MD_H + col]);
+    }
+    part[(cid * 2 + 0) * MD_H + col] = mean;
+    part[(cid * 2 + 1) * MD_H + col] = m2;
+  }
+  cl.sync();
+}
 
 // merge per-tile (mean, M2) partials [T][2][128] -> batch mean / biased variance of column `col`:
 //   mean = sum_t n_t mean_t / B,   M2 = sum_t (M2_t + n_t (mean_t - mean)^2)
@@ -116,7 +168,7 @@ struct MidFwdArgs {
 };
 
 // forward, stage 1: BN1 + ReLU + Dropout -> latent heads, z, KL -> decoder hidden pre-activation y2 + its tile stats
-__global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
+__device__ __forceinline__ void mid_fwd_body(const MidFwdArgs& A, float* s_cl) {
   extern __shared__ __align__(16) float sm[];
   float* s_a = sm;                          // [64][128]
   float* s_W = s_a + MD_ROWS * MD_H;        // [2L][129]  latent heads (Wm | Wv)
@@ -221,7 +273,14 @@ __global__ void __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
     }
     vals[i] = v;
   }
-  md_tile_stats(vals, rg, col, cnt, s_scr, A.part2 + (int64_t)blockIdx.x * 2 * MD_H);
+  md_tile_stats(vals, rg, col, cnt, s_scr, s_cl);
+}
+
+__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
+  __shared__ float s_cl[2 * MD_H];
+  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_fwd_body(A, s_cl);
+  else if (threadIdx.x < 2 * MD_H) s_cl[threadIdx.x] = 0.f;  // a CTA that pads the grid: an empty tile
+  md_cluster_stats(s_cl, A.B, A.part2);
 }
 
 // forward, stage 2: BN2 + ReLU -> h
@@ -235,7 +294,7 @@ __global__ void __launch_bounds__(MD_THREADS)
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
   float mean, var, n;
-  md_merge_stats(part2, B, MD_ROWS, s_scr, mean, var, n);
+  md_merge_stats(part2, B, MD_ROWS * MD_CL, s_scr, mean, var, n);
   const float rstd = 1.f / sqrtf(var + bn_eps);
   if (blockIdx.x == 0 && rg == 0) {
     mean2[col] = mean;
@@ -258,14 +317,15 @@ __global__ void __launch_bounds__(MD_THREADS)
 // backward
 // ---------------------------------------------------------------------------------------
 // stage 0: per-tile column sums of du2 = dh * 1[u2 > 0] and du2 * xhat2  (BatchNorm-2 backward, phase 1)
-__global__ void __launch_bounds__(MD_THREADS)
+__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS)
     mid_bwd0_kernel(const float* __restrict__ dh, const float* __restrict__ y2, const float* __restrict__ mean2,
                     const float* __restrict__ rstd2, const float* __restrict__ gamma2, const float* __restrict__ beta2,
-                    int64_t B, float* __restrict__ bpart2 /*[T][2][128]*/) {
+                    int64_t B, float* __restrict__ bpart2 /*[clusters][2][128]*/) {
   __shared__ float s_scr[8 * MD_H];
+  __shared__ float s_cl[2 * MD_H];
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
-  const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
+  const int cnt = (int)max((int64_t)0, min((int64_t)MD_ROWS, B - r0));  // 0 in the CTAs that pad the grid
   const float mu = mean2[col], rs = rstd2[col], g = gamma2[col], b = beta2[col];
   float s1 = 0.f, s2 = 0.f;
   float yv[MD_RPT], dv[MD_RPT];  // dh is loaded whatever the ReLU mask says: no load waits on another
@@ -290,10 +350,10 @@ __global__ void __launch_bounds__(MD_THREADS)
   s_scr[(4 + rg) * MD_H + col] = s2;
   __syncthreads();
   if (rg == 0) {
-    float* o = bpart2 + (int64_t)blockIdx.x * 2 * MD_H;
-    o[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
-    o[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
+    s_cl[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
+    s_cl[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
   }
+  md_cluster_sum2(s_cl, bpart2);
 }
 
 struct MidBwdArgs {
@@ -318,7 +378,7 @@ __host__ __device__ inline int64_t md_rec_floats(int ncols, int L) { return (int
 
 // stage 1: BN2 backward -> dy2 -> dWd / dbd partials, dz -> latent backward -> da1, dWm / dWv / dbm / dbv partials
 //          -> BN1 backward phase 1 (per-tile sums of du1, du1 * xhat1)
-__global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
+__device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, float* s_cl) {
   extern __shared__ __align__(16) float sm[];
   float* s_t = sm;                           // [64][128]  dy2, later a1
   float* s_W = s_t + MD_ROWS * MD_H;         // [2L][129]
@@ -331,7 +391,6 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   const int L = A.L, L2 = 2 * A.L, ncols = A.ncols;
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, A.B - r0);
-  const int64_t T = (A.B + MD_ROWS - 1) / MD_ROWS;
   float* rec = A.ppart + (int64_t)blockIdx.x * A.prec;
 
   for (int e = tid; e < L2 * MD_H; e += MD_THREADS) {
@@ -352,7 +411,7 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
     dv2[i] = (r < cnt) ? A.dh[o] : 0.f;
   }
   float S1, S2;
-  md_merge_sum2(A.bpart2, T, s_scr, S1, S2);
+  md_merge_sum2(A.bpart2, md_clusters(A.B), s_scr, S1, S2);
   if (blockIdx.x == 0 && rg == 0) {
     if (A.dbeta2) A.dbeta2[col] = S1;
     if (A.dgamma2) A.dgamma2[col] = S2;
@@ -447,9 +506,8 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   }
   __syncthreads();
   if (rg == 0) {
-    float* o = A.bpart1 + (int64_t)blockIdx.x * 2 * MD_H;
-    o[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
-    o[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
+    s_cl[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
+    s_cl[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
   }
   // dW latent [j][c] partial = sum_r dq[r][j] a1[r][c]
   float* recL = rec + (int64_t)MD_H * ncols + MD_H;
@@ -465,6 +523,13 @@ __global__ void __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   }
 }
 
+__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
+  __shared__ float s_cl[2 * MD_H];
+  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_bwd1_body(A, s_cl);
+  else if (threadIdx.x < 2 * MD_H) s_cl[threadIdx.x] = 0.f;  // a CTA that pads the grid
+  md_cluster_sum2(s_cl, A.bpart1);
+}
+
 // stage 2: BN1 backward phase 2 -> dy1 (+ per-tile column sums = gradient of the encoder Linear bias)
 __global__ void __launch_bounds__(MD_THREADS)
     mid_bwd2_kernel(const float* __restrict__ da1, const float* __restrict__ y1, const float* __restrict__ mean1,
@@ -476,9 +541,8 @@ __global__ void __launch_bounds__(MD_THREADS)
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
   const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
-  const int64_t T = (B + MD_ROWS - 1) / MD_ROWS;
   float S1, S2;
-  md_merge_sum2(bpart1, T, s_scr, S1, S2);
+  md_merge_sum2(bpart1, md_clusters(B), s_scr, S1, S2);
   if (blockIdx.x == 0 && rg == 0) {
     if (dbeta1) dbeta1[col] = S1;
     if (dgamma1) dgamma1[col] = S2;
@@ -568,7 +632,7 @@ int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t 
     }
     attr = true;
   }
-  mid_fwd_kernel<<<(unsigned)T, MD_THREADS, smem, st>>>(A);
+  mid_fwd_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
   SCVI_LAUNCH_CHECK("scvi_mid_fwd(stage 1)");
   mid_fwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(y2, part2, gamma2, beta2, running_mean2, running_var2, bn_eps,
                                                      momentum, B, h, mean2, rstd2);
@@ -602,7 +666,7 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
   float* bpart1 = bpart2 + T * 2 * MD_H;
   float* da1 = bpart1 + T * 2 * MD_H;
   float* ppart = da1 + B * MD_H;
-  mid_bwd0_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(dh, y2, mean2, rstd2, gamma2, beta2, B, bpart2);
+  mid_bwd0_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, 0, st>>>(dh, y2, mean2, rstd2, gamma2, beta2, B, bpart2);
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 0)");
   MidBwdArgs A;
   A.dh = dh; A.y2 = y2; A.mean2 = mean2; A.rstd2 = rstd2; A.gamma2 = gamma2; A.beta2 = beta2; A.bpart2 = bpart2;
@@ -621,7 +685,7 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
     }
     attr = true;
   }
-  mid_bwd1_kernel<<<(unsigned)T, MD_THREADS, smem, st>>>(A);
+  mid_bwd1_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 1)");
   const int64_t dbe_off = prec - MD_H;
   mid_bwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(da1, y1, mean1, rstd1, gamma1, beta1, drop_mask, drop_scale,
