@@ -283,31 +283,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       for (int c = 0; c < 2; ++c) {
         const int col0 = 32 * part + 16 * c;
         float sv[16], pv[16];
+        const int64_t gb = g0 + col0;
+        float4 b4[4];  // scale-head bias of this chunk (warp-uniform addresses): in flight behind the TMEM load
+        if (MODE == 0) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) b4[k] = *reinterpret_cast<const float4*>(bias_pad + gb + 4 * k);
+        }
         tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 0) * TC_N + col0, sv);
         if (NHEADS == 2) tc::tmem_ld16(tmem_base + lane_sel + (buf * NHEADS + 1) * TC_N + col0, pv);
         tc::tmem_ld_wait();
-        const int64_t gb = g0 + col0;
         if (MODE == 0) {
           // log2 domain: t = logit * log2(e); running (max, sum 2^(t - max))
           float tm = -INFINITY;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const float4 b4 = *reinterpret_cast<const float4*>(bias_pad + gb + 4 * k);  // warp-uniform address
-            sv[4 * k + 0] = fmaf(sv[4 * k + 0], TC_RESCALE * fm::LOG2E, b4.x * fm::LOG2E);
-            sv[4 * k + 1] = fmaf(sv[4 * k + 1], TC_RESCALE * fm::LOG2E, b4.y * fm::LOG2E);
-            sv[4 * k + 2] = fmaf(sv[4 * k + 2], TC_RESCALE * fm::LOG2E, b4.z * fm::LOG2E);
-            sv[4 * k + 3] = fmaf(sv[4 * k + 3], TC_RESCALE * fm::LOG2E, b4.w * fm::LOG2E);
+            sv[4 * k + 0] = fmaf(sv[4 * k + 0], TC_RESCALE * fm::LOG2E, b4[k].x * fm::LOG2E);
+            sv[4 * k + 1] = fmaf(sv[4 * k + 1], TC_RESCALE * fm::LOG2E, b4[k].y * fm::LOG2E);
+            sv[4 * k + 2] = fmaf(sv[4 * k + 2], TC_RESCALE * fm::LOG2E, b4[k].z * fm::LOG2E);
+            sv[4 * k + 3] = fmaf(sv[4 * k + 3], TC_RESCALE * fm::LOG2E, b4[k].w * fm::LOG2E);
           }
+          // genes of this chunk inside [0, G): 16 everywhere but at the ragged end (no per-element 64-bit test)
+          const int nv = (int)max((int64_t)0, min((int64_t)16, G - gb));
+          if (nv == 16) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (gb + i < G) tm = fmaxf(tm, sv[i]);
+            for (int i = 0; i < 16; ++i) tm = fmaxf(tm, sv[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (i < nv) tm = fmaxf(tm, sv[i]);
+          }
           if (tm > m_run) {
             l_run *= fm::ex2(m_run - tm);  // m_run = -inf first time: 2^(-inf) = 0
             m_run = tm;
           }
+          if (nv == 16) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (gb + i < G) l_run += fm::ex2(sv[i] - m_run);
+            for (int i = 0; i < 16; ++i) l_run += fm::ex2(sv[i] - m_run);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (i < nv) l_run += fm::ex2(sv[i] - m_run);
+          }
         } else if (rvalid) {
           float xq[16];
           if (xvec) {  // 4 x 16-byte streaming loads (row start and G are multiples of 4 floats)
