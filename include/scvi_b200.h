@@ -204,7 +204,7 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
  * For the fused training plan (n_hidden == 128, n_latent <= 16, n_latent + n_batch <= 80) these two
  * calls replace the sequence scvi_bn_finalize, scvi_bn_act_drop_fwd, scvi_latent_fwd, scvi_linear_fwd
  * (decoder FCLayers layer 0), scvi_bn_finalize, scvi_bn_act_drop_fwd and its mirror in backward; same
- * math, same reference lines, per-64-row-tile partials merged in fixed order by every CTA.
+ * math, same reference lines, per-32-row-tile partials merged per cluster of 8 CTAs, then in fixed order by every consumer CTA.
  * y1 / bn_partials1: output of scvi_linear_fwd for the encoder layer.  cov_cols: int32 [B], absolute
  * column of Wd ([H, n_w_cols]) selected by the batch covariate (NULL = none).
  * ws: scvi_mid_ws_bytes() bytes, the SAME buffer for the forward and the backward of one step. */

@@ -8,9 +8,10 @@
 // (:311-317), the KL of VAE.loss (src/scvi/module/_vae.py:563-565) and FCLayers.forward of the decoder
 // (:148-188).  Every op on this stretch touches ~4 MB: as separate launches they are latency bound.
 //
-// One CTA = one tile of MD_ROWS rows, 512 threads.  Batch statistics cross CTAs through
-// per-tile partials (mean, M2 / sums) that every CTA of the NEXT kernel merges redundantly in a fixed
-// order (deterministic, no grid barrier, no atomics).
+// One CTA = one tile of MD_ROWS rows, 512 threads.  Batch statistics cross CTAs through partials (mean, M2 /
+// sums): the producing kernel runs as clusters of MD_CL CTAs and writes one partial per cluster (merged through
+// distributed shared memory), every CTA of the NEXT kernel merges the cluster partials redundantly in a
+// fixed order (deterministic, no grid barrier, no atomics).
 #include <cooperative_groups.h>
 
 #include "common.cuh"
