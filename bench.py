@@ -52,8 +52,16 @@ def parse():
     ap.add_argument("--unsorted-batches", action="store_true",
                     help="feed each minibatch's row ids in shuffled order (default: ascending within the minibatch, "
                          "as FusedTrainingPlan.fit does -- same cells, better DRAM page / TLB locality)")
-    ap.add_argument("--ddp-mode", default="split", choices=["graph", "overlap", "split"],
-                    help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode)")
+    ap.add_argument("--ddp-mode", default="p2p", choices=["p2p", "graph", "overlap", "split"],
+                    help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode): p2p = this library's fused "
+                         "all-reduce + Adam over NVLink peer memory, the others = NCCL routes")
+    ap.add_argument("--blocks", type=int, default=5,
+                    help="the timed region is repeated this many times (each EXACTLY --steps steps between "
+                         "barrier + synchronize); ms_per_step is the median block")
+    ap.add_argument("--zero-frac", type=float, default=0.3,
+                    help="fraction of structural zeros in the synthetic counts (0.3 = synthetic_iid; 0.9 ~ real scRNA)")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the extra workloads of the default line (B=128, 90%%-zeros counts, config C3)")
     ap.add_argument("--e2e-dtype", default="auto", choices=["auto", "u16", "f32"],
                     help="host count type of the e2e leg: auto = narrowest lossless (uint8 / uint16 / float32)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -69,9 +77,9 @@ def workload_name(a):
 # ----------------------------------------------------------------------------------------------
 # synthetic data
 # ----------------------------------------------------------------------------------------------
-def synth_counts_device(n, g, device, seed=0, chunk=65536):
-    """NB(5, 0.3) x Bernoulli(0.7) (reference src/scvi/data/_built_in_data/_synthetic.py:54-58),
-    generated on the device in chunks: Gamma(5, scale=(1-p)/p) -> Poisson."""
+def synth_counts_device(n, g, device, seed=0, chunk=65536, zero_frac=0.3):
+    """NB(5, 0.3) x Bernoulli(1 - zero_frac) (reference src/scvi/data/_built_in_data/_synthetic.py:54-58 with
+    zero_frac = 0.3), generated on the device in chunks: Gamma(5, scale=(1-p)/p) -> Poisson."""
     gen = torch.Generator(device=device).manual_seed(seed)
     X = torch.empty(n, g, dtype=torch.float32, device=device)
     conc = torch.full((1,), 5.0, device=device)
@@ -79,9 +87,16 @@ def synth_counts_device(n, g, device, seed=0, chunk=65536):
         e = min(n, s + chunk)
         lam = torch._standard_gamma(conc.expand(e - s, g), generator=gen) * (0.7 / 0.3)
         cnt = torch.poisson(lam, generator=gen)
-        keep = torch.rand(e - s, g, device=device, generator=gen) < 0.7
+        keep = torch.rand(e - s, g, device=device, generator=gen) >= zero_frac
         X[s:e] = cnt * keep
     return X
+
+
+def config_dict(a, world):
+    """The `config` object both arms print (the reference arm times the same workload on the host cores)."""
+    return {"workload": workload_name(a), "parallelism": f"dp{world}", "global_batch": a.batch_size * world,
+            "cells": a.cells, "genes": a.genes, "batches": a.batches, "likelihood": a.likelihood,
+            "batch_size_per_gpu": a.batch_size, "n_hidden": N_HIDDEN, "n_latent": N_LATENT}
 
 
 def synth_counts_host(n, g, seed=0):
@@ -174,7 +189,8 @@ def run_reference_arm(a):
         "impl": "reference", "metric": "SCVI train cells/sec", "value": v, "unit": "cells/s", "n_gpus": a.gpus,
         "steps": done, "warmup": a.warmup, "ms_per_step": 1e3 * el / done, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(a), "timing": "host perf_counter; CPU arm"},
+        "config": config_dict(a, int(os.environ.get("WORLD_SIZE", "1"))),
+        "details": {"timing": "host perf_counter; CPU arm (rank 0 only)"},
         "cpu_baseline": {"value": v, "unit": "cells/s", "cores": cores, "kind": "port",
                          "sample": f"{done} steps of {a.batch_size} cells (oracle port of the reference step, torch CPU, {cores} threads)"},
         "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -360,10 +376,63 @@ def time_logprob_kernels(a, dev, peak, reps=10):
     return res
 
 
-def run_b200_arm(a):
+def timed_blocks(step, K, R, barrier, world, dev):
+    """R repetitions of the contract's timed region: barrier + synchronize, EXACTLY K steps between two CUDA events
+    on the launching stream, barrier + synchronize; each block's time is the max over ranks.  Returns the list (ms)."""
+    out, n = [], 0
+    for _ in range(R):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _i in range(K):
+            step(n)
+            n += 1
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            ms = float(t)
+        out.append(ms)
+    return out
+
+
+def make_plan(a, data, B, pg, genes=None, likelihood=None, batches=None, seed=0):
     import scvi_tools_b200 as S
-    from scvi_tools_b200.data import DeviceResidentCounts
     from scvi_tools_b200.train import FusedTrainingPlan
+
+    torch.manual_seed(seed)
+    m = S.VAE(n_input=genes or a.genes, n_batch=batches or a.batches, gene_likelihood=likelihood or a.likelihood,
+              n_hidden=N_HIDDEN, n_latent=N_LATENT, precision=1 if a.precision == "tc" else 0).train()
+    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True, ddp_mode=a.ddp_mode)
+    plan.set_epoch(0)
+    return plan
+
+
+def minibatch_order(n_cells, B, dev, sort=True, seed=0):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    order = torch.randperm(n_cells, device=dev, generator=g)
+    n_chunks = n_cells // B
+    if sort:  # a minibatch is a set: ascending row ids inside each one (as FusedTrainingPlan.fit does)
+        order[: n_chunks * B] = order[: n_chunks * B].view(n_chunks, B).sort(dim=1).values.reshape(-1)
+    return order, n_chunks
+
+
+def quick_rate(plan, n_cells, B, dev, K, R, W, barrier, world):
+    """cells/s of `plan` on resident counts: W warm-up steps, median of R blocks of K steps."""
+    order, n_chunks = minibatch_order(n_cells, B, dev, seed=1)
+    for i in range(W):
+        plan.training_step(order[(i % n_chunks) * B : (i % n_chunks + 1) * B])
+    ms = timed_blocks(lambda i: plan.training_step(order[((W + i) % n_chunks) * B : ((W + i) % n_chunks + 1) * B]),
+                      K, R, barrier, world, dev)
+    med = float(np.median(ms))
+    return {"cells_per_s": K * B * world / (med / 1e3), "ms_per_step": med / K, "steps": K, "blocks_ms": ms,
+            "final_loss": float(plan.out3[0])}
+
+
+def run_b200_arm(a):
+    from scvi_tools_b200.data import DeviceResidentCounts, HostStreamedCounts, narrowest_count_dtype
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -378,21 +447,15 @@ def run_b200_arm(a):
 
         dist.init_process_group("nccl", device_id=dev)
         pg = dist.group.WORLD
-    B, K, W = a.batch_size, a.steps, max(a.warmup, 3)
+    # under data parallelism the first steps also warm NCCL / peer mappings / clocks on every rank: >= 20
+    B, K, R = a.batch_size, a.steps, max(a.blocks, 1)
+    W = max(a.warmup, 3) if world == 1 else max(a.warmup, 20)
 
-    X = synth_counts_device(a.cells, a.genes, dev, seed=rank)
+    X = synth_counts_device(a.cells, a.genes, dev, seed=rank, zero_frac=a.zero_frac)
     batch = (torch.arange(a.cells, device=dev) * a.batches // a.cells)
     data = DeviceResidentCounts(X, batch=batch, device=dev)
-    torch.manual_seed(0)
-    m = S.VAE(n_input=a.genes, n_batch=a.batches, gene_likelihood=a.likelihood, n_hidden=N_HIDDEN, n_latent=N_LATENT,
-              precision=1 if a.precision == "tc" else 0).train()
-    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True,
-                             ddp_mode=a.ddp_mode)
-    plan.set_epoch(0)
-    order = torch.randperm(a.cells, device=dev)
-    n_chunks = a.cells // B
-    if not a.unsorted_batches:  # a minibatch is a set: ascending row ids inside each one
-        order[: n_chunks * B] = order[: n_chunks * B].view(n_chunks, B).sort(dim=1).values.reshape(-1)
+    plan = make_plan(a, data, B, pg)
+    order, n_chunks = minibatch_order(a.cells, B, dev, sort=not a.unsorted_batches)
 
     def chunk(i):
         j = i % n_chunks
@@ -409,87 +472,133 @@ def run_b200_arm(a):
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(K):
-        plan.training_step(chunk(W + i))
-    e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
+    blocks_ms = timed_blocks(lambda i: plan.training_step(chunk(W + i)), K, R, barrier, world, dev)
     clocks = sampler.stop()
+    ms = float(np.median(blocks_ms))
     loss_end = float(plan.out3[0])
     launches_per_step = plan.kernel_launches_per_step  # this library's kernels recorded in the step graph
-    if world > 1:
-        t = torch.tensor([ms], device=dev)
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ms = float(t)
     value = K * B * world / (ms / 1e3)
 
-    # ---- end to end: pinned host minibatches -> H2D (copy stream, double buffered) -> step -> loss D2H
-    # The host side keeps the counts in the narrowest lossless integer type (HostStreamedCounts: uint8 here,
-    # uint16 for counts >= 256, fp32 otherwise); the device expands them to the fp32 rows bit-exactly.
-    from scvi_tools_b200.data import HostStreamedCounts, narrowest_count_dtype
+    # ---- data-parallel checks: replicas identical after the timed steps; cost of the exchange
+    ddp = None
+    if world > 1:
+        torch.cuda.synchronize()
+        bits = plan.p.view(torch.int32).to(torch.int64)
+        sig = torch.stack([bits.sum(), (bits * torch.arange(1, bits.numel() + 1, device=dev)).sum()])
+        sigs = [torch.empty_like(sig) for _ in range(world)]
+        torch.distributed.all_gather(sigs, sig)
+        same = all(torch.equal(sigs[0], t) for t in sigs)
+        solo = make_plan(a, data, B, None)  # the same step without any exchange, on this rank alone
+        solo_rate = quick_rate(solo, a.cells, B, dev, K, min(R, 3), 5, barrier, 1)
+        t = torch.tensor([solo_rate["ms_per_step"]], device=dev)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ddp = {"mode": plan.ddp_mode, "params_identical_across_ranks": bool(same),
+               "param_checksum": [int(v) for v in sigs[0].tolist()],
+               "single_rank_ms_per_step": float(t), "exchange_exposed_us": 1e3 * (ms / K - float(t)),
+               "numerical_test": "tests/test_gpu_multigpu.py (bit-equality with single-process arithmetic, N=2)"}
+        del solo
+        if not same:
+            print("bench.py: replicas diverged", file=sys.stderr)
 
-    n_host = 4
-    host_f32 = [torch.from_numpy(synth_counts_host(B, a.genes, seed=100 + i)) for i in range(n_host)]
-    hdt = torch.float32 if a.e2e_dtype == "f32" else max(
-        (narrowest_count_dtype(x) for x in host_f32), key=lambda d: torch.empty(0, dtype=d).element_size())
+    # ---- end to end (A): counts stay in pinned HOST memory (the whole matrix, narrowest lossless integer type);
+    # every step submits its random row ids, the rows cross PCIe inside the timed region (gathered by the GPU
+    # straight from the mapped host pages, or by the host threads + a copy-engine H2D), are expanded to fp32
+    # rows on the device, the fused step runs, and the loss is copied back and read on the host every step.
+    n_host_rows = a.cells
+    hdt = torch.float32 if a.e2e_dtype == "f32" else narrowest_count_dtype(X[: min(a.cells, 262144)])
     if a.e2e_dtype == "u16" and hdt == torch.uint8:
         hdt = torch.uint16
-    host_x = [x.to(hdt).pin_memory() for x in host_f32]
-    host_b = [torch.randint(0, a.batches, (B,), dtype=torch.int64).pin_memory() for i in range(n_host)]
-    feeder = HostStreamedCounts(torch.zeros(1, a.genes), batch=None, batch_size=B, device=dev, dtype=hdt)
-    plan.attach_streamed(feeder)
+    if hdt != torch.float32 and float(X.max()) >= (256 if hdt == torch.uint8 else 65536):
+        hdt = torch.uint16 if float(X.max()) < 65536 else torch.float32
+    host_mat = torch.empty(n_host_rows, a.genes, dtype=hdt, pin_memory=True)
+    for s0 in range(0, n_host_rows, 65536):
+        host_mat[s0 : s0 + 65536].copy_(X[s0 : s0 + 65536].to(hdt))
+    host_batch = batch.cpu()
+    order_host = order.cpu()
     loss_host = [torch.zeros(3).pin_memory() for _ in range(2)]
     loss_done = [torch.cuda.Event(), torch.cuda.Event()]
     losses = []
 
-    def e2e_loop(n):
-        # every step's loss is copied to the host and read there; the read of step i happens after step i+1 has
-        # been enqueued (one step of lookahead, as a logger thread would), so the GPU never idles on the host
-        losses.clear()
-        feeder.submit(0, host_x=host_x[0], host_b=host_b[0])
-        for i in range(n):
-            s = i % 2
-            plan.training_step(feeder.acquire(s))
-            feeder.release(s)
-            loss_host[s].copy_(plan.out3, non_blocking=True)
-            loss_done[s].record()
-            if i + 1 < n:  # the next minibatch crosses PCIe while this step computes (its slot was freed by step i-1)
-                feeder.submit((i + 1) % 2, host_x=host_x[(i + 1) % n_host], host_b=host_b[(i + 1) % n_host])
-            if i > 0:
-                loss_done[1 - s].synchronize()
-                losses.append(float(loss_host[1 - s][0]))
-        if n > 0:
-            loss_done[(n - 1) % 2].synchronize()
-            losses.append(float(loss_host[(n - 1) % 2][0]))
+    def run_e2e(feeder, submit):
+        plan.attach_streamed(feeder)
 
-    e2e_loop(W)
-    barrier()
-    t0 = torch.cuda.Event(enable_timing=True)
-    t1 = torch.cuda.Event(enable_timing=True)
-    t0.record()
-    e2e_loop(K)
-    t1.record()
-    barrier()
-    ms_e2e = t0.elapsed_time(t1)
-    if world > 1:
-        t = torch.tensor([ms_e2e], device=dev)
-        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
-        ms_e2e = float(t)
-    e2e = {"value": K * B * world / (ms_e2e / 1e3), "unit": "cells/s",
-           "h2d_bytes_per_step": B * a.genes * host_x[0].element_size() + B * 8, "d2h_bytes_per_step": 12,
-           "host_dtype": str(hdt).replace("torch.", ""), "losses_read_on_host": len(losses),
-           "how": "pinned host minibatch in the narrowest lossless count type -> cudaMemcpyAsync on a copy stream "
-                  "(double buffered) -> exact expansion to fp32 rows (scvi_gather_rows_u8/_u16) -> fused step -> "
-                  "loss D2H each step, read on the host one step behind the launch"}
+        def loop(n, base):
+            # every step's loss is copied to the host and read there; the read of step i happens after step i+1
+            # has been enqueued (one step of lookahead, as a logger thread would), so the GPU never idles on it
+            losses.clear()
+            submit(0, base)
+            for i in range(n):
+                s = i % 2
+                plan.training_step(feeder.acquire(s))
+                feeder.release(s)
+                loss_host[s].copy_(plan.out3, non_blocking=True)
+                loss_done[s].record()
+                if i + 1 < n:  # the next minibatch crosses PCIe while this step computes
+                    submit((i + 1) % 2, base + i + 1)
+                if i > 0:
+                    loss_done[1 - s].synchronize()
+                    losses.append(float(loss_host[1 - s][0]))
+            if n > 0:
+                loss_done[(n - 1) % 2].synchronize()
+                losses.append(float(loss_host[(n - 1) % 2][0]))
+
+        loop(W, 0)
+        out, base = [], W
+        for _ in range(R):
+            barrier()
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            loop(K, base)
+            t1.record()
+            barrier()
+            base += K
+            msb = t0.elapsed_time(t1)
+            if world > 1:
+                t = torch.tensor([msb], device=dev)
+                torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+                msb = float(t)
+            out.append(msb)
+        return float(np.median(out)), out
+
+    def rows_of(i):
+        j = i % n_chunks
+        return order_host[j * B : (j + 1) * B]
+
+    legs = {}
+    for name, devg in (("device_gather", True), ("host_gather", False)):
+        feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg)
+        if devg and not feeder.device_gather:
+            continue
+        med, allb = run_e2e(feeder, lambda slot, i, f=feeder: f.submit(slot, rows=rows_of(i)))
+        legs[name] = {"cells_per_s": K * B * world / (med / 1e3), "ms_per_step": med / K, "blocks_ms": allb}
+        del feeder
+    # (B) round-1 figure for continuity: 4 pre-formed pinned minibatches cycled (no per-step row gather)
+    n_pre = 4
+    pre_x = [host_mat[i * B : (i + 1) * B].clone().pin_memory() for i in range(n_pre)]
+    pre_b = [host_batch[i * B : (i + 1) * B].clone().pin_memory() for i in range(n_pre)]
+    feeder = HostStreamedCounts(torch.zeros(1, a.genes), batch=None, batch_size=B, device=dev, dtype=hdt,
+                                device_gather=False)
+    med, allb = run_e2e(feeder, lambda slot, i: feeder.submit(slot, host_x=pre_x[i % n_pre], host_b=pre_b[i % n_pre]))
+    legs["preformed_minibatches"] = {"cells_per_s": K * B * world / (med / 1e3), "ms_per_step": med / K, "blocks_ms": allb}
+    best = max((k for k in legs if k != "preformed_minibatches"), key=lambda k: legs[k]["cells_per_s"])
+    e2e = {"value": legs[best]["cells_per_s"], "unit": "cells/s",
+           "h2d_bytes_per_step": B * a.genes * host_mat.element_size() + B * 8 + B * 8, "d2h_bytes_per_step": 12,
+           "host_dtype": str(hdt).replace("torch.", ""), "losses_read_on_host": len(losses), "route": best,
+           "routes": legs, "host_matrix_rows": n_host_rows,
+           "how": "whole count matrix in pinned host memory (narrowest lossless count type); per step: random row ids "
+                  "-> rows over PCIe (device_gather: a gather kernel reads the mapped host pages; host_gather: "
+                  "index_select on the host threads + cudaMemcpyAsync), exact expansion to fp32 rows, fused step, "
+                  "loss D2H each step read on the host one step behind the launch; preformed_minibatches = the "
+                  "round-1 figure (no per-step row gather), kept for continuity"}
+    del host_mat, pre_x
 
     # ---- per-kernel roofline (rank 0)
     line = None
+    extras = {}
+    plan.data = data
+    plan.batch_cols = (data.batch + plan.L).to(torch.int32)
+    plan._graphs = None
     if rank == 0:
-        plan.data = data
-        plan.batch_cols = (data.batch + plan.L).to(torch.int32)
-        plan._graphs = None
         kern = profile_step(plan, a)
         peaks = {}
         try:
@@ -498,7 +607,6 @@ def run_b200_arm(a):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
-        step_ms = ms / K
         ab = algorithmic_bytes(a, B, plan.n_arena)
         for k, v in kern.items():
             v["algorithmic_bytes"] = ab.get(k)
@@ -521,28 +629,61 @@ def run_b200_arm(a):
                 "algorithmic_bytes": kern[dom]["algorithmic_bytes"], "kernel_ms": kern[dom]["ms"],
                 "peak_source": peak_src, "share_of_step": kern[dom]["ms"] * kern[dom]["launches_per_step"] / eager_ms,
                 "note": "HBM is the nearest roofline of the step's streaming kernels; the dominant kernel is limited "
-                        "by SFU/issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4)"}
-        del plan.data, data, X  # free the resident matrix before the standalone-kernel leg
+                        "by the issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4)"}
+    # ---- the other workloads SURVEY 8(d) asks for, as extra keys of the same line (every rank runs them: the
+    # plans are data-parallel); each is W' warm-up steps + the median of 3 blocks of K steps
+    if not a.no_extras:
+        Kx, Rx = K, 3
+        # reference default minibatch (src/scvi/model/base/_training_mixin.py:78)
+        p128 = make_plan(a, data, 128, pg, seed=1)
+        extras["batch_size_128"] = quick_rate(p128, a.cells, 128, dev, max(Kx, 50), Rx, W, barrier, world)
+        del p128
+        # ~90 % zeros (real scRNA-seq sparsity): thin the resident matrix in place, same shape
+        if a.zero_frac < 0.85:
+            keep = (1.0 - 0.9) / (1.0 - a.zero_frac)
+            g = torch.Generator(device=dev).manual_seed(77 + rank)
+            for s0 in range(0, a.cells, 65536):
+                X[s0 : s0 + 65536].mul_(torch.rand(X[s0 : s0 + 65536].shape, device=dev, generator=g) < keep)
+            psp = make_plan(a, data, B, pg, seed=2)
+            extras["zeros_90pct"] = quick_rate(psp, a.cells, B, dev, Kx, Rx, W, barrier, world)
+            del psp
+    del plan.data, data, X  # free the resident matrix before the standalone-kernel leg
+    if not a.no_extras and not (a.genes == 4000 and a.likelihood == "nb" and a.batches == 32):
+        # BASELINE.json configs[2]: 1M x 4000 genes, NB, 32 batches
+        import copy
+
+        a3 = copy.copy(a)
+        a3.genes, a3.likelihood, a3.batches = 4000, "nb", 32
+        X3 = synth_counts_device(a.cells, 4000, dev, seed=50 + rank, zero_frac=a.zero_frac)
+        d3 = DeviceResidentCounts(X3, batch=torch.arange(a.cells, device=dev) * 32 // a.cells, device=dev)
+        p3 = make_plan(a3, d3, B, pg, seed=3)
+        extras["c3_1Mx4000_nb_32batches"] = quick_rate(p3, a.cells, B, dev, K, 3, W, barrier, world)
+        extras["c3_1Mx4000_nb_32batches"]["workload"] = workload_name(a3)
+        del p3, d3, X3
+    if rank == 0:
         logprob = time_logprob_kernels(a, dev, peak)
         cpu = None if a.no_cpu_baseline else cpu_baseline(a, a.cpu_seconds)
+        cfg = config_dict(a, world)
         line = {
             "metric": "SCVI train cells/sec", "value": value, "unit": "cells/s", "n_gpus": world, "steps": K,
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "parallelism": f"dp{world}",
-                       "global_batch": B * world,
-                       "cache": "inputs larger than L2: rows gathered at random from the HBM-resident count matrix "
-                                f"({a.cells * a.genes * 4 / 1e9:.1f} GB)",
-                       "precision": ("tcgen05 fp16 hi/lo split GEMMs, fp32 accumulate (fp32-grade, parity-tested)"
-                                     if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True},
+            "dtype": "f32", "data": "synthetic", "config": cfg,
+            "details": {"cache": "inputs larger than L2: rows gathered at random from the HBM-resident count matrix "
+                                 f"({a.cells * a.genes * 4 / 1e9:.1f} GB)",
+                        "precision": ("tcgen05 fp16 hi/lo split GEMMs, fp32 accumulate (fp32-grade, parity-tested)"
+                                      if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True,
+                        "timing": f"median of {R} blocks of exactly {K} steps, each between barrier+synchronize, "
+                                  "CUDA events on the launching stream, max over ranks",
+                        "blocks_ms": blocks_ms, "zero_frac": a.zero_frac},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
-            "launches_per_step": launches_per_step,
-            "roofline": roof, "kernels": kern, "nb_loss_kernel_hbm": logprob, "cpu_baseline": cpu, "final_loss": loss_end,
+            "launches_per_step": launches_per_step, "ddp_check": ddp,
+            "roofline": roof, "kernels": kern, "nb_loss_kernel_hbm": logprob, "cpu_baseline": cpu,
+            "final_loss": loss_end, "also": extras,
         }
     if line is not None:
         print(json.dumps(line), flush=True)
     if world > 1:
-        # the step graphs hold captured NCCL kernels: release them before the communicator goes away, and do not
+        # the step graphs hold captured collectives: release them before the communicator goes away, and do not
         # wait on the communicator teardown (it can block on graph-captured collectives)
         plan._graphs = None
         torch.cuda.synchronize()

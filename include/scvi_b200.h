@@ -319,6 +319,36 @@ int scvi_step_prologue(uint64_t seed, const int64_t* step_counter, int64_t strea
 int scvi_elbo_seed(int64_t B, float kl_weight, const float* kl_weight_dev, float scale, float* g_reconst,
                    float* g_kl, void* stream);
 
+
+/* Device address of page-locked (pinned, mapped) host memory: lets scvi_gather_rows_u8/_u16/scvi_gather_rows read a
+ * count matrix that stays in HOST memory row by row over PCIe -- the minibatch gather of
+ * AnnTorchDataset.__getitem__ (src/scvi/data/_anntorchdataset.py:143-147) done by the GPU, no host-side copy. */
+int scvi_host_device_pointer(const void* host_ptr, void** dev_ptr);
+
+/* ---- a13: data-parallel gradient mean fused with the optimizer, over NVLink peer memory -------------------
+ * replaces torch DDP's gradient all-reduce (mean over replicas) followed by Adam.step under
+ * `Trainer(strategy="ddp")` (reference tests/model/test_multigpu.py:29-36, src/scvi/model/_utils.py:25-34,
+ * src/scvi/train/_trainingplans.py:475-519).  Single node: every rank allocates one exchange segment
+ * (scvi_comm_alloc: cudaMalloc + zero fill + cudaIpcGetMemHandle, handle = 64 opaque bytes to ship to the other
+ * ranks), opens the others' (scvi_comm_open, peer access enabled lazily) and lays it out as
+ *     [gradient arena, step parity 0][gradient arena, step parity 1] ... [control block, scvi_comm_ctrl_bytes()]
+ * scvi_allreduce_adam(slot): cross-GPU arrival barrier on the slot's flags (bounded wait: a missing peer traps),
+ * g = sum_r peer_g[r][begin:end] in rank order (bit-identical on every rank), then the Adam update of
+ * p/m/v[begin:end] with grad_scale 1/world, exactly scvi_adam_step_graph's arithmetic.  peer_g / peer_ctrl are HOST
+ * arrays of `world` device pointers (this rank's own buffers at [rank]); every rank must issue the same sequence of
+ * calls per slot.  The caller alternates the gradient buffer (parity) between consecutive steps.  advance_counter:
+ * bump step_counter[0] when done (last bucket of the step).  g_sum (nullable): also store the reduced slice.
+ * blocks: grid size (0 = default). */
+int64_t scvi_comm_ctrl_bytes(void);
+int scvi_comm_alloc(int64_t bytes, void** dev_ptr, void* ipc_handle64);
+int scvi_comm_open(const void* ipc_handle64, void** dev_ptr);
+int scvi_comm_close(void* dev_ptr);
+int scvi_comm_free(void* dev_ptr);
+int scvi_allreduce_adam(const void* const* peer_g, void* const* peer_ctrl, int world, int rank, int slot,
+                        float* p, float* m, float* v, float* g_sum, int64_t begin, int64_t end,
+                        int64_t* step_counter, int advance_counter, float lr, float beta1, float beta2,
+                        float eps, float weight_decay, int blocks, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

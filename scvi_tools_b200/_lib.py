@@ -67,6 +67,13 @@ SIGNATURES = {
     "scvi_decoder_params_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, P, P, I64, P]),
     "scvi_adam_step": (C.c_int, [P, P, P, P, I64, I64, F32, F32, F32, F32, F32, F32, P]),
     "scvi_adam_step_graph": (C.c_int, [P, P, P, P, I64, P, F32, F32, F32, F32, F32, F32, P]),
+    "scvi_host_device_pointer": (C.c_int, [P, C.POINTER(C.c_void_p)]),
+    "scvi_comm_ctrl_bytes": (I64, []),
+    "scvi_comm_alloc": (C.c_int, [I64, C.POINTER(C.c_void_p), P]),
+    "scvi_comm_open": (C.c_int, [P, C.POINTER(C.c_void_p)]),
+    "scvi_comm_close": (C.c_int, [P]),
+    "scvi_comm_free": (C.c_int, [P]),
+    "scvi_allreduce_adam": (C.c_int, [P, P, I32, I32, I32, P, P, P, P, I64, I64, P, I32, F32, F32, F32, F32, F32, I32, P]),
     "scvi_elbo_reduce": (C.c_int, [P, P, I64, F32, P, P, P]),
     "scvi_elbo_seed": (C.c_int, [I64, F32, P, F32, P, P, P]),
     "scvi_step_prologue": (C.c_int, [C.c_uint64, P, I64, I64, I64, I64, F32, P, P, P, P, P, F32, P, F32, P, P, P, P, P]),

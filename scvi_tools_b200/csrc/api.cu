@@ -46,6 +46,20 @@ __global__ void prof_delay_kernel(long long ns) {
     __nanosleep(1000);
   }
 }
+int smem_optin(const void* func, int bytes, std::atomic<uint64_t>& done, const char* who) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+  const uint64_t bit = 1ull << (dev & 63);
+  if (done.load(std::memory_order_acquire) & bit) return SCVI_OK;
+  cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess) {
+    set_error("%s: cannot reserve %d B of shared memory: %s", who, bytes, cudaGetErrorString(e));
+    return SCVI_ECUDA;
+  }
+  done.fetch_or(bit, std::memory_order_release);
+  return SCVI_OK;
+}
+
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
@@ -104,6 +118,20 @@ extern "C" {
 int scvi_b200_abi_version(void) { return 3; }
 const char* scvi_last_error_string(void) { return scvi::g_err; }
 int64_t scvi_launch_count(void) { return (int64_t)scvi::g_launches.load(std::memory_order_relaxed); }
+
+int scvi_host_device_pointer(const void* host_ptr, void** dev_ptr) {
+  using namespace scvi;
+  SCVI_REQUIRE(host_ptr && dev_ptr, "scvi_host_device_pointer: NULL pointer");
+  void* d = nullptr;
+  cudaError_t e = cudaHostGetDevicePointer(&d, const_cast<void*>(host_ptr), 0);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("scvi_host_device_pointer: %s (the buffer must be page-locked, mapped host memory)", cudaGetErrorString(e));
+    return SCVI_ECUDA;
+  }
+  *dev_ptr = d;
+  return SCVI_OK;
+}
 
 int scvi_profile_begin(void* stream, int64_t delay_us) {
   using namespace scvi;

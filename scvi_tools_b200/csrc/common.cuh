@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
+
 #include "scvi_b200.h"
 
 namespace scvi {
@@ -30,6 +32,11 @@ void count_launch(const char* name);  // one call per kernel launch of this libr
   } while (0)
 
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// Opt a kernel into `bytes` of dynamic shared memory, once per (call site, device): `done` is the call site's
+// bit mask of devices already configured (the attribute is per device; setting it twice is harmless, so the
+// benign race of two host threads on one device needs no lock).
+int smem_optin(const void* func, int bytes, std::atomic<uint64_t>& done, const char* who);
 
 // out[e] = sum_t part[t * stride + e], e < n, in a fixed order (deterministic): 32 column lanes x 32
 // tile groups per block, serial inside a group, then a fixed-order merge of the 32 group sums.

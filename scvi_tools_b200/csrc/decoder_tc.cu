@@ -465,15 +465,8 @@ static int tc_launch_fwd(const TcPlan& p, const float* h, int64_t ldh, int64_t B
                          const float* gconst, const float* x, int64_t ldx, const int64_t* row_idx,
                          const float* library, int xvec, float* lse, float* outp, cudaStream_t st) {
   auto k = tc_decoder_fwd_kernel<MODE, ZINB>;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TcSmem::TOTAL + 1024);
-    if (e != cudaSuccess) {
-      set_error("tc_decoder_fwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)k, (int)TcSmem::TOTAL + 1024, optin, "tc_decoder_fwd")) return rc;
   dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
   k<<<grid, TC_THREADS, TcSmem::TOTAL + 1024, st>>>(h, ldh, B, G, packed, gconst, x, ldx, row_idx, library,
                                                      p.tiles_per_split, p.nsplit, 1e-8f, xvec, lse, outp);

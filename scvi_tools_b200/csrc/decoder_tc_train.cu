@@ -391,15 +391,8 @@ static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const
                         int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, cudaStream_t st) {
   auto k = tc_nll_dh_kernel<ZINB>;
   constexpr int smem = (int)K2Smem<ZINB>::TOTAL + 128;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      set_error("tc_nll_dh: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)k, smem, optin, "tc_nll_dh")) return rc;
   dim3 grid((unsigned)cdiv(B, TC_M), (unsigned)nsplit);
   k<<<grid, TT_THREADS, smem, st>>>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, tiles_per_split,
                                     1e-8f, xvec, out_part, dh_part);
@@ -800,15 +793,8 @@ static int tt_launch_k3(const TtBwdPlan& p, int64_t B, int64_t G, const uint8_t*
                         float* slabv, cudaStream_t st) {
   auto k = tc_dw_kernel<ZINB>;
   constexpr int smem = (int)K3Smem<ZINB>::TOTAL + 128;
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) {
-      set_error("tc_dw: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)k, smem, optin, "tc_dw")) return rc;
   dim3 grid((unsigned)p.nT, (unsigned)p.splits);
   k<<<grid, TT_THREADS, smem, st>>>(B, G, packed, gconst, hpack, scal, x, ldx, p.tiles_per_split, 1e-8f, slabW, slabv);
   return SCVI_OK;

@@ -565,15 +565,6 @@ static EnFwdPlan en_fwd_plan(int64_t B, int64_t K) {
 }
 int64_t tc_enc_fwd_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_fwd_plan(B, K).total; }
 
-static int en_set_smem(const void* fn, const char* name) {
-  cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)EnSmem::TOTAL + 128);
-  if (e != cudaSuccess) {
-    set_error("%s: cannot reserve shared memory: %s", name, cudaGetErrorString(e));
-    return SCVI_ECUDA;
-  }
-  return SCVI_OK;
-}
-
 int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
                const float* bias, int flags, float* y, int64_t ldy, float* library, float* bn_partials, void* ws,
                cudaStream_t st) {
@@ -585,15 +576,8 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
   float* rs = (float*)(w8 + p.off_rs);
   tc_pack_we_kernel<<<(unsigned)cdiv(p.nKT * 4 * TC_M, 256), 256, 0, st>>>(W, ldw, K, p.nKT, wpack);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc pack)");
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(tc_enc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)En1Smem::TOTAL + 128);
-    if (e != cudaSuccess) {
-      set_error("scvi_linear_fwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)tc_enc_fwd_kernel, (int)En1Smem::TOTAL + 128, optin, "scvi_linear_fwd")) return rc;
   dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
   tc_enc_fwd_kernel<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
                                                                   (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
@@ -646,12 +630,8 @@ int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, in
   }
   tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, dy_absmax_part, (int)n_absmax_part, scal, dypack);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc pack)");
-  static bool attr = false;
-  if (!attr) {
-    int rc = en_set_smem((const void*)tc_enc_dw_kernel, "scvi_linear_bwd");
-    if (rc) return rc;
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)tc_enc_dw_kernel, (int)EnSmem::TOTAL + 128, optin, "scvi_linear_bwd")) return rc;
   const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
   dim3 grid((unsigned)p.nT, (unsigned)p.nsplit);
   tc_enc_dw_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, scal,

@@ -147,13 +147,10 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   SCVI_REQUIRE(a && Wm && Wv && noise && q_m && q_v && da && ws, "scvi_latent_bwd: NULL pointer");
   SCVI_REQUIRE(B > 0 && H > 0 && L > 0 && L <= 32 && lda >= H && ldda >= H, "scvi_latent_bwd: bad shape");
   const size_t smem = sizeof(float) * ((size_t)2 * L * H + (size_t)LATB_ROWS * H + (size_t)LATB_ROWS * 2 * L);
-  static bool attr_set = false;
+  static std::atomic<uint64_t> optin{0};
   if (smem > 48 * 1024) {
     SCVI_REQUIRE(smem <= 200 * 1024, "scvi_latent_bwd: H*L too large for shared memory");
-    if (!attr_set) {
-      cudaFuncSetAttribute(latent_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      attr_set = true;
-    }
+    if (int rc = smem_optin((const void*)latent_bwd_kernel, 200 * 1024, optin, "scvi_latent_bwd")) return rc;
   }
   const int64_t ctas = cdiv(B, LATB_ROWS);
   float* partW = (float*)ws;

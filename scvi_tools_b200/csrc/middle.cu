@@ -624,15 +624,8 @@ int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t 
   A.part2 = part2; A.mean1 = mean1; A.rstd1 = rstd1;
   const size_t smem = sizeof(float) * ((size_t)MD_ROWS * MD_H + 2 * MD_LMAX * 129 + MD_H * MD_WD_LD +
                                        MD_ROWS * 2 * MD_LMAX + 2 * MD_ROWS * MD_LMAX + 12 * MD_H);
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(mid_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-      set_error("scvi_mid_fwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)mid_fwd_kernel, (int)smem, optin, "scvi_mid_fwd")) return rc;
   mid_fwd_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
   SCVI_LAUNCH_CHECK("scvi_mid_fwd(stage 1)");
   mid_fwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(y2, part2, gamma2, beta2, running_mean2, running_var2, bn_eps,
@@ -677,15 +670,8 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
   A.ppart = ppart; A.prec = prec; A.dgamma2 = dgamma2; A.dbeta2 = dbeta2;
   const size_t smem = sizeof(float) * ((size_t)MD_ROWS * MD_H + 2 * MD_LMAX * 129 + MD_H * MD_WD_LD + MD_ROWS * MD_LMAX +
                                        MD_ROWS * 2 * MD_LMAX + 12 * MD_H);
-  static bool attr = false;
-  if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(mid_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-      set_error("scvi_mid_bwd: cannot reserve shared memory: %s", cudaGetErrorString(e));
-      return SCVI_ECUDA;
-    }
-    attr = true;
-  }
+  static std::atomic<uint64_t> optin{0};
+  if (int rc = smem_optin((const void*)mid_bwd1_kernel, (int)smem, optin, "scvi_mid_bwd")) return rc;
   mid_bwd1_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
   SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 1)");
   const int64_t dbe_off = prec - MD_H;

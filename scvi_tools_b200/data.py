@@ -12,12 +12,14 @@ count data over PCIe.
 
 from __future__ import annotations
 
+import ctypes as C
 import math
 
 import numpy as np
 import torch
 
 from . import ops
+from ._lib import call
 
 
 def epoch_indices(n_obs: int, rank: int, world: int, epoch: int, seed: int = 0, shuffle: bool = True,
@@ -68,9 +70,16 @@ class HostStreamedCounts:
     rows the kernels read -- bit-identical to `data[indexes].astype(float32)`.
 
     `stage` is a `DeviceResidentCounts` of 2 x batch_size rows; the plan trains on rows `slot*B .. slot*B+n`.
+
+    `submit(rows=...)` gathers the minibatch rows ON THE DEVICE, straight out of the pinned host matrix (the
+    pinned pages are mapped into the GPU's address space): only the 8-byte row ids are copied first, then one
+    gather kernel on the copy stream pulls the compact rows over PCIe and expands them into the staging slot --
+    no host-side copy, no host thread touching count data.  `device_gather=False` keeps the host-side
+    `index_select` into a pinned buffer followed by a plain H2D copy.
     """
 
-    def __init__(self, X, batch=None, batch_size: int = 128, device="cuda", dtype: torch.dtype | None = None):
+    def __init__(self, X, batch=None, batch_size: int = 128, device="cuda", dtype: torch.dtype | None = None,
+                 device_gather: bool = True):
         self.dev = torch.device(device)
         X = torch.as_tensor(np.asarray(X.toarray()) if hasattr(X, "toarray") else X)
         self.dtype = narrowest_count_dtype(X) if dtype is None else dtype
@@ -92,6 +101,19 @@ class HostStreamedCounts:
             e.record()
         self.slot_rows = [torch.arange(self.B, device=self.dev), torch.arange(self.B, 2 * self.B, device=self.dev)]
         self.on_batch = None  # callable(lo, n) run on the copy stream after a slot's batch codes landed
+        self.device_gather = False
+        if device_gather and n > 0:
+            try:  # device addresses of the pinned matrix / batch codes (UVA: normally the same numbers)
+                dx, db = C.c_void_p(), C.c_void_p()
+                with torch.cuda.device(self.dev):
+                    call("scvi_host_device_pointer", C.c_void_p(self.host.data_ptr()), C.byref(dx))
+                    call("scvi_host_device_pointer", C.c_void_p(self.host_batch.data_ptr()), C.byref(db))
+                self._dev_x, self._dev_b = int(dx.value), int(db.value)
+                self._pin_idx = [torch.empty(self.B, dtype=torch.int64).pin_memory() for _ in range(2)]
+                self._dev_idx = torch.empty(2 * self.B, dtype=torch.int64, device=self.dev)
+                self.device_gather = True
+            except RuntimeError:
+                self.device_gather = False
 
     @property
     def n_obs(self) -> int:
@@ -109,6 +131,8 @@ class HostStreamedCounts:
         """Enqueue the copy of one minibatch into staging slot `slot` (0 / 1): either rows `rows` (host int64
         indices) of the host matrix -- gathered into a pinned buffer first -- or an already formed pinned
         minibatch (`host_x` in this object's dtype, `host_b`).  Returns the number of cells."""
+        if host_x is None and self.device_gather:
+            return self._submit_device_gather(slot, torch.as_tensor(rows, dtype=torch.int64))
         if host_x is None:
             rows = torch.as_tensor(rows, dtype=torch.int64)
             n = rows.numel()
@@ -126,6 +150,28 @@ class HostStreamedCounts:
                 self._compact[lo : lo + n].copy_(host_x, non_blocking=True)
                 ops.gather_rows(self._compact[lo : lo + n], None, out=self.stage.X[lo : lo + n])
             self.stage.batch[lo : lo + n].copy_(host_b, non_blocking=True)
+            if self.on_batch is not None:
+                self.on_batch(lo, n)
+            self.ready[slot].record(self.copy_stream)
+        return n
+
+    def _submit_device_gather(self, slot: int, rows: torch.Tensor) -> int:
+        n = rows.numel()
+        lo = slot * self.B
+        G = self.n_vars
+        self.freed[slot].synchronize()  # the pinned index buffer of this slot is reused
+        self._pin_idx[slot][:n].copy_(rows)
+        fn = {torch.uint8: "scvi_gather_rows_u8", torch.uint16: "scvi_gather_rows_u16",
+              torch.float32: "scvi_gather_rows"}[self.dtype]
+        with torch.cuda.stream(self.copy_stream):
+            st = C.c_void_p(self.copy_stream.cuda_stream)
+            idx = self._dev_idx[lo : lo + n]
+            idx.copy_(self._pin_idx[slot][:n], non_blocking=True)
+            out = self.stage.X[lo : lo + n]
+            call(fn, C.c_void_p(self._dev_x), self.n_obs, G, self.host.stride(0), C.c_void_p(idx.data_ptr()), n,
+                 C.c_void_p(out.data_ptr()), out.stride(0), st)
+            call("scvi_gather_i64", C.c_void_p(self._dev_b), self.n_obs, C.c_void_p(idx.data_ptr()), n,
+                 C.c_void_p(self.stage.batch[lo : lo + n].data_ptr()), st)
             if self.on_batch is not None:
                 self.on_batch(lo, n)
             self.ready[slot].record(self.copy_stream)

@@ -32,11 +32,18 @@ class SCVI:
     `X`: [n_obs, n_vars] counts (numpy / torch, any device); `batch`: [n_obs] integer batch codes or None.
     `X` may also be a `DeviceResidentCounts` (counts in HBM, the default built from an array) or a
     `HostStreamedCounts` (counts stay in pinned host memory and stream over PCIe in compact integer form).
+    `precision` (a `VAE` keyword, not recorded in `init_params_`): None = tcgen05 kernels when n_hidden == 128
+    (what `bench.py` times), FFMA fp32 kernels otherwise; 0 / 1 force the FFMA / tensor-core path.
+
+    Differences from `scvi.model.SCVI.train` kept deliberately: every cell is a training cell (the reference
+    holds out 10 % by default, `train_size=0.9`, for a validation loop this driver does not run), and there is
+    no early stopping / checkpoint callback.
     """
 
     def __init__(self, X, batch=None, n_hidden: int = 128, n_latent: int = 10, n_layers: int = 1,
                  dropout_rate: float = 0.1, dispersion: str = "gene", gene_likelihood: str = "zinb",
-                 latent_distribution: str = "normal", device="cuda:0", var_names=None, **model_kwargs):
+                 latent_distribution: str = "normal", device="cuda:0", var_names=None, precision: int | None = None,
+                 **model_kwargs):
         self.device = torch.device(device)
         # the reference's `init_params_` record (BaseModelClass._get_init_params, _base_model.py:747-774)
         self.init_params_ = {
@@ -59,7 +66,7 @@ class SCVI:
         self.module = VAE(n_input=self.data.n_vars, n_batch=n_batch, n_hidden=n_hidden, n_latent=n_latent,
                           n_layers=n_layers, dropout_rate=dropout_rate, dispersion=dispersion,
                           gene_likelihood=gene_likelihood, latent_distribution=latent_distribution,
-                          **model_kwargs).to(self.device)
+                          precision=precision, **model_kwargs).to(self.device)
         self.var_names = (np.asarray(var_names) if var_names is not None
                           else np.array([str(i) for i in range(self.data.n_vars)]))
         if self.var_names.shape[0] != self.data.n_vars:
@@ -79,7 +86,12 @@ class SCVI:
         if max_epochs is None:
             max_epochs = get_max_epochs_heuristic(self.data.n_obs)
         self.module.train()
-        new_plan = self._plan is None or self._plan.B != batch_size or self._plan.pg is not process_group
+        hyper = (batch_size, lr, eps, weight_decay, n_epochs_kl_warmup, n_steps_kl_warmup, max_kl_weight, min_kl_weight,
+                 seed, use_cuda_graph)
+        # a changed optimizer / warm-up / seed argument takes effect: the plan (and its Adam state) is rebuilt
+        new_plan = (self._plan is None or self._plan.pg is not process_group
+                    or getattr(self, "_plan_hyper", None) != hyper)
+        self._plan_hyper = hyper
         if self.streamed and self.data.B != batch_size:
             raise ValueError(f"HostStreamedCounts was built for batch_size={self.data.B}, train() got {batch_size}")
         if new_plan:

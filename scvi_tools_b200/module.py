@@ -219,7 +219,7 @@ class VAE(nn.Module):
         extra_encoder_kwargs: dict | None = None,
         extra_decoder_kwargs: dict | None = None,
         batch_embedding_kwargs: dict | None = None,
-        precision: int = _lib.PREC_FP32,
+        precision: int | None = None,
     ):
         super().__init__()
         if gene_likelihood not in ("zinb", "nb"):
@@ -245,6 +245,13 @@ class VAE(nn.Module):
         self.use_observed_lib_size = use_size_factor_key or use_observed_lib_size
         self.extra_payload_autotune = extra_payload_autotune
         self.batch_representation = batch_representation
+        # GEMM arithmetic of the fused kernels: None = the tcgen05 path (error-compensated fp16 split, fp32
+        # accumulate, held to the same parity tolerances) whenever its shape constraint n_hidden == 128 holds,
+        # FFMA fp32 otherwise; _lib.PREC_FP32 / _lib.PREC_TC force one
+        if precision is None:
+            precision = _lib.PREC_TC if n_hidden == 128 else _lib.PREC_FP32
+        if precision == _lib.PREC_TC and n_hidden != 128:
+            raise ValueError("precision=PREC_TC needs n_hidden == 128")
         self.precision = precision
         self._minified_data_type = None
 
@@ -428,7 +435,7 @@ class VAE(nn.Module):
         else:
             px_r = None
 
-        h = self.decoder.hidden(dec_in, batch_index, *cats, y) if False else self.decoder.hidden(dec_in, batch_index, *cats)
+        h = self.decoder.hidden(dec_in, batch_index, *cats)
         fused = self.dispersion == "gene" and self.decoder.supports_fused_nll(h) and size_factor.dim() == 2
         if fused:
             px = FusedCountDistribution(self.decoder, h, size_factor, px_r, self.gene_likelihood, self.dispersion,

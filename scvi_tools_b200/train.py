@@ -69,7 +69,7 @@ class FusedTrainingPlan:
                  eps: float = 0.01, weight_decay: float = 1e-6, betas=(0.9, 0.999),
                  n_epochs_kl_warmup: int | None = 400, n_steps_kl_warmup: int | None = None,
                  max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, seed: int = 0,
-                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "split"):
+                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "p2p"):
         m = module
         self._check_supported(m)
         self.module, self.data = m, data
@@ -80,17 +80,28 @@ class FusedTrainingPlan:
         self.seed = seed
         self.use_cuda_graph = use_cuda_graph
         self.pg = process_group
-        # data parallel gradient exchange: "split" = forward+backward graph | eager all-reduce | Adam graph;
-        # "graph" = the all-reduce captured inside one step graph; "overlap" = additionally start the decoder-head
-        # gradients (2/3 of the arena, ready first) on a side stream while the rest of the backward runs.
-        # Measured on 8 B200 (profiles/README.md): the three are within 2 % -- the step is paced by the slowest
-        # rank, not by the 3 MB exchange -- so the simplest is the default.
-        if ddp_mode not in ("graph", "overlap", "split"):
-            raise ValueError(f"ddp_mode must be 'graph', 'overlap' or 'split' (got {ddp_mode!r})")
-        self.ddp_mode = ddp_mode
-        self.ddp_overlap = ddp_mode == "overlap"
+        # data parallel gradient exchange (world > 1):
+        #   "p2p"     (default) this library's fused all-reduce + Adam over NVLink peer memory (csrc/comm.cu), one
+        #             captured graph per step parity; the decoder-head bucket (2/3 of the arena, ready after K3) is
+        #             exchanged and updated on a side stream under the rest of the backward, the remainder after it.
+        #             Falls back to "split" when peer memory cannot be mapped on every rank.
+        #   "split"   forward+backward graph | eager ncclAllReduce | Adam graph
+        #   "graph"   the ncclAllReduce captured inside one step graph
+        #   "overlap" as "graph", the decoder-head bucket reduced on a side stream
+        if ddp_mode not in ("p2p", "graph", "overlap", "split"):
+            raise ValueError(f"ddp_mode must be 'p2p', 'graph', 'overlap' or 'split' (got {ddp_mode!r})")
         self.world = 1 if process_group is None else torch.distributed.get_world_size(process_group)
         self.rank = 0 if process_group is None else torch.distributed.get_rank(process_group)
+        self.exchange = None
+        if self.world > 1 and ddp_mode == "p2p":
+            from .comm import PeerGradientExchange
+
+            self.exchange = PeerGradientExchange(self._arena_layout(module)[1], process_group, data.X.device)
+            if not self.exchange.available:
+                self.exchange, ddp_mode = None, "split"
+        self.ddp_mode = ddp_mode
+        self.ddp_overlap = ddp_mode == "overlap"
+        self._n_exec = 0  # whole steps executed so far: its low bit selects the gradient buffer (p2p double buffer)
         self.zinb = m.gene_likelihood == "zinb"
         self.dev = data.X.device
         self.G, self.H, self.L, self.nb = m.n_input, m.n_hidden, m.n_latent, m.n_batch
@@ -105,6 +116,32 @@ class FusedTrainingPlan:
         if self.world > 1:
             self._comm = torch.cuda.Stream(device=self.dev)
             self._ev_heads_ready, self._ev_heads_reduced = torch.cuda.Event(), torch.cuda.Event()
+            # the head-bucket kernel runs beside the rest of the backward: a grid small enough to co-reside
+            self.head_blocks = 48
+            self._sync_initial_state()
+
+    def close(self):
+        """Release the peer-memory exchange segment (data-parallel "p2p" mode); the plan is unusable afterwards."""
+        self._graphs = None
+        if self.exchange is not None:
+            torch.cuda.synchronize()
+            torch.distributed.barrier(group=self.pg)
+            self._g2, self._Gd2 = [], []
+            self.exchange.close()
+            self.exchange = None
+
+    def _sync_initial_state(self):
+        """Every replica starts from rank 0's parameters and BatchNorm buffers, as torch DDP does at construction
+        (`DistributedDataParallel.__init__` -> `_sync_module_states`); the Adam moments and the step counter are
+        zero on every rank."""
+        for t in (self.p, self.bn1_rm, self.bn1_rv, self.bn2_rm, self.bn2_rv, self.bn1_nbt, self.bn2_nbt):
+            torch.distributed.broadcast(t, src=0, group=self.pg)
+
+    def _broadcast_buffers(self):
+        """BN running buffers follow rank 0 (DDP `broadcast_buffers` semantics), once per epoch."""
+        if self.world > 1:
+            for b in (self.bn1_rm, self.bn1_rv, self.bn2_rm, self.bn2_rv):
+                torch.distributed.broadcast(b, src=0, group=self.pg)
 
     @staticmethod
     def _check_supported(m):
@@ -123,22 +160,30 @@ class FusedTrainingPlan:
             )
 
     # ------------------------------------------------------------------ arena
-    def _build_arena(self):
-        named = dict(self.module.named_parameters())
-        keys = [k for k in ARENA_ORDER if not (("px_dropout" in k) and not self.zinb)]
-        self.keys = keys
+    @staticmethod
+    def _arena_layout(module):
+        """(keys, n_floats, offsets, n_head) of the flat arena for `module`."""
+        named = dict(module.named_parameters())
+        zinb = module.gene_likelihood == "zinb"
+        keys = [k for k in ARENA_ORDER if not (("px_dropout" in k) and not zinb)]
         offs, off = {}, 0
         for k in keys:
             offs[k] = off
             off += (named[k].numel() + 3) // 4 * 4  # keep every slice 16-byte aligned
+        return keys, off, offs, offs[keys[N_HEAD_TENSORS if zinb else 3]]
+
+    def _build_arena(self):
+        named = dict(self.module.named_parameters())
+        keys, off, offs, self.n_head = self._arena_layout(self.module)
+        self.keys = keys
         self.n_arena = off
-        self.n_head = offs[keys[N_HEAD_TENSORS if self.zinb else 3]]
         dev = self.dev
         self.p = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.g = torch.zeros(off, dtype=torch.float32, device=dev)
+        # gradient arena(s): inside the peer-mapped exchange segment, one per step parity, under "p2p"
+        self._g2 = self.exchange.g if self.exchange is not None else [torch.zeros(off, dtype=torch.float32, device=dev)]
         self.m = torch.zeros(off, dtype=torch.float32, device=dev)
         self.v = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.P, self.Gd = {}, {}
+        self.P, self._Gd2 = {}, [{} for _ in self._g2]
         for k in keys:
             prm = named[k]
             n = prm.numel()
@@ -146,7 +191,8 @@ class FusedTrainingPlan:
             view.copy_(prm.data.to(dev))
             prm.data = view  # the module's parameter now lives in the arena
             self.P[k] = view
-            self.Gd[k] = self.g[offs[k] : offs[k] + n].view(prm.shape)
+            for g, Gd in zip(self._g2, self._Gd2, strict=True):
+                Gd[k] = g[offs[k] : offs[k] + n].view(prm.shape)
         self.step_counter = torch.zeros(2, dtype=torch.int64, device=dev)  # {steps done, Adam's arrival ticket}
         self.klw = torch.zeros(1, dtype=torch.float32, device=dev)
         # make sure the BN buffers are on the device
@@ -155,6 +201,18 @@ class FusedTrainingPlan:
         self.bn1_rm, self.bn1_rv = sd[ENC + "1.running_mean"], sd[ENC + "1.running_var"]
         self.bn2_rm, self.bn2_rv = sd[DEC + "1.running_mean"], sd[DEC + "1.running_var"]
         self.bn1_nbt, self.bn2_nbt = sd[ENC + "1.num_batches_tracked"], sd[DEC + "1.num_batches_tracked"]
+
+    def _parity(self, n_exec=None):
+        return ((self._n_exec if n_exec is None else n_exec) & 1) if len(self._g2) == 2 else 0
+
+    @property
+    def g(self):
+        """The gradient arena the most recent step wrote (this rank's gradients; under NCCL modes: their sum)."""
+        return self._g2[self._parity(max(self._n_exec - 1, 0))]
+
+    @property
+    def Gd(self):
+        return self._Gd2[self._parity(max(self._n_exec - 1, 0))]
 
     # ------------------------------------------------------------------ buffers
     def _alloc_step_buffers(self):
@@ -201,7 +259,7 @@ class FusedTrainingPlan:
         self.ws_enc = torch.empty(int(ne), dtype=torch.uint8, device=dev) if ne > 0 else None
 
     # ------------------------------------------------------------------ the step
-    def _forward_backward(self, st, overlap: bool = False):
+    def _forward_backward(self, st, overlap: bool = False, parity: int | None = None):
         """Kernel sequence of one minibatch: forward, ELBO, backward into the gradient arena.
         Rows are read from the resident matrix through `self.idx`.  `st` = cudaStream_t of the current stream.
 
@@ -210,7 +268,8 @@ class FusedTrainingPlan:
         (weights only) next to the encoder + middle forward, the ELBO scalar reduction (not needed by the
         backward, whose seeds come from the step prologue) next to the decoder backward."""
         B, G, H, L = self.B_cur, self.G, self.H, self.L
-        P, Gd, X = self.P, self.Gd, self.data.X
+        parity = self._parity() if parity is None else parity
+        P, Gd, X = self.P, self._Gd2[parity], self.data.X
         if X.dtype != torch.float32:
             raise NotImplementedError("fused training reads fp32 resident counts (uint16 residency: gather path)")
         ldx = X.stride(0)
@@ -268,7 +327,7 @@ class FusedTrainingPlan:
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
              _p(Gd["px_r"]), _p(self.ws), _p(self.ws_fwd) if prec == _lib.PREC_TC else None, st)
-        self._after_head_grads(st)
+        self._after_head_grads(st, parity)
         if self.use_mid:
             call("scvi_mid_bwd", _p(self.dh), _p(self.y2), _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
                  _p(P[DEC + "1.bias"]), _p(self.z), _p(P[DEC + "0.weight"]), ncols, _p(self.cov_cols) if inj else None,
@@ -281,7 +340,7 @@ class FusedTrainingPlan:
                  _p(Gd["z_encoder.var_encoder.weight"]), _p(Gd["z_encoder.var_encoder.bias"]), _p(Gd[ENC + "1.weight"]),
                  _p(Gd[ENC + "1.bias"]), _p(Gd[ENC + "0.bias"]), _p(self.dy1_amax), _p(self.ws_mid), st)
         else:
-            self._middle_backward_unfused(st, B, H, L, drop, dscale, inj, ncols)
+            self._middle_backward_unfused(st, B, H, L, drop, dscale, inj, ncols, Gd)
         call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
              _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
              None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0,
@@ -312,8 +371,8 @@ class FusedTrainingPlan:
         call("scvi_bn_act_drop_fwd", _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2), _p(P[DEC + "1.weight"]),
              _p(P[DEC + "1.bias"]), 1, None, 1.0, _p(self.h), H, st)
 
-    def _middle_backward_unfused(self, st, B, H, L, drop, dscale, inj, ncols):
-        P, Gd = self.P, self.Gd
+    def _middle_backward_unfused(self, st, B, H, L, drop, dscale, inj, ncols, Gd):
+        P = self.P
         call("scvi_bn_act_drop_bwd", _p(self.dh), H, _p(self.y2), H, B, H, _p(self.mean2), _p(self.rstd2),
              _p(P[DEC + "1.weight"]), _p(P[DEC + "1.bias"]), 1, None, 1.0, 1, _p(self.dy2), H, _p(Gd[DEC + "1.weight"]),
              _p(Gd[DEC + "1.bias"]), _p(self.ws), st)
@@ -330,48 +389,70 @@ class FusedTrainingPlan:
              1.0 / (1.0 - self.p_drop) if drop else 1.0, 1, _p(self.dy1), H, _p(Gd[ENC + "1.weight"]),
              _p(Gd[ENC + "1.bias"]), _p(self.ws), st)
 
-    def _after_head_grads(self, st):
+    def _after_head_grads(self, st, parity):
         """Between the decoder-head backward and the rest: under data parallelism the head gradients (the first
-        `n_head` floats of the arena) start their all-reduce here, on a side stream."""
-        if self.world > 1 and self.ddp_overlap:
-            main = torch.cuda.current_stream()
-            self._ev_heads_ready.record(main)
-            self._comm.wait_event(self._ev_heads_ready)
-            with torch.cuda.stream(self._comm):
-                torch.distributed.all_reduce(self.g[: self.n_head], group=self.pg)
-                self._ev_heads_reduced.record(self._comm)
-
-    def _reduce_gradients(self):
-        """Sum the gradient arena over the ranks (Adam applies 1/world)."""
-        if self.world == 1:
+        `n_head` floats of the arena) are exchanged here, on a side stream, under the rest of the backward --
+        "p2p": fused peer-memory all-reduce + Adam of that bucket; "overlap": its ncclAllReduce."""
+        if self.world == 1 or not (self.exchange is not None or self.ddp_overlap):
             return
+        main = torch.cuda.current_stream()
+        self._ev_heads_ready.record(main)
+        self._comm.wait_event(self._ev_heads_ready)
+        with torch.cuda.stream(self._comm):
+            if self.exchange is not None:
+                self.exchange.allreduce_adam(parity, 0, self.p, self.m, self.v, 0, self.n_head, self.step_counter,
+                                             False, self.lr, self.betas[0], self.betas[1], self.eps, self.wd,
+                                             C.c_void_p(self._comm.cuda_stream), blocks=self.head_blocks)
+            else:
+                torch.distributed.all_reduce(self._g2[parity][: self.n_head], group=self.pg)
+            self._ev_heads_reduced.record(self._comm)
+
+    def _reduce_gradients(self, parity=0):
+        """NCCL modes: sum the gradient arena over the ranks (Adam applies 1/world)."""
+        if self.world == 1 or self.exchange is not None:
+            return
+        g = self._g2[parity]
         if self.ddp_overlap:
-            torch.distributed.all_reduce(self.g[self.n_head :], group=self.pg)
+            torch.distributed.all_reduce(g[self.n_head :], group=self.pg)
             torch.cuda.current_stream().wait_event(self._ev_heads_reduced)
         else:
-            torch.distributed.all_reduce(self.g, group=self.pg)
+            torch.distributed.all_reduce(g, group=self.pg)
 
-    def _adam(self, st):
-        call("scvi_adam_step_graph", _p(self.p), _p(self.g), _p(self.m), _p(self.v), self.n_arena,
+    def _adam(self, st, parity=None):
+        """The optimizer step; under "p2p" the remaining bucket's fused all-reduce + Adam (which also advances the
+        step counter), after the head bucket's kernel on the side stream has finished."""
+        parity = self._parity() if parity is None else parity
+        if self.exchange is not None and self.world > 1:
+            torch.cuda.current_stream().wait_event(self._ev_heads_reduced)
+            self.exchange.allreduce_adam(parity, 1, self.p, self.m, self.v, self.n_head, self.n_arena,
+                                         self.step_counter, True, self.lr, self.betas[0], self.betas[1], self.eps,
+                                         self.wd, st)
+            return
+        call("scvi_adam_step_graph", _p(self.p), _p(self._g2[parity]), _p(self.m), _p(self.v), self.n_arena,
              _p(self.step_counter), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1.0 / self.world, st)
 
     # ------------------------------------------------------------------ driving the step
-    def _prologue(self, st, feed_rng: bool = True):
+    def _prologue(self, st, feed_rng: bool = True, gen_mask: bool | None = None, gen_noise: bool | None = None):
         """Dropout keep-mask, reparameterisation noise, batch-covariate columns, ELBO backward seeds and the
-        BatchNorm step counters in one launch (library Philox streams keyed by seed / step / rank)."""
+        BatchNorm step counters in one launch (library Philox streams keyed by seed / step / rank).
+        `gen_mask` / `gen_noise` (default: `feed_rng`) select which of the two random buffers are drawn; a
+        buffer the caller filled itself is left alone."""
         B = self.B_cur
-        drop = feed_rng and self.p_drop > 0
+        gen_mask = feed_rng if gen_mask is None else gen_mask
+        gen_noise = feed_rng if gen_noise is None else gen_noise
+        drop = gen_mask and self.p_drop > 0
         call("scvi_step_prologue", self.seed, _p(self.step_counter), self.rank, B, self.H, self.L, self.p_drop,
-             _p(self.mask) if drop else None, _p(self.noise) if feed_rng else None, _p(self.idx),
+             _p(self.mask) if drop else None, _p(self.noise) if gen_noise else None, _p(self.idx),
              _p(self.batch_cols) if self.nb > 1 else None, _p(self.cov_cols) if self.nb > 1 else None, 0.0,
              _p(self.klw), 1.0, _p(self.g_rec), _p(self.g_kl), _p(self.bn1_nbt), _p(self.bn2_nbt), st)
 
-    def _whole_step(self, feed_rng: bool = True):
+    def _whole_step(self, gen_mask: bool = True, gen_noise: bool = True, parity: int | None = None):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        self._prologue(st, feed_rng)
-        self._forward_backward(st, overlap=self.overlap)
-        self._reduce_gradients()
-        self._adam(st)
+        parity = self._parity() if parity is None else parity
+        self._prologue(st, gen_mask=gen_mask, gen_noise=gen_noise)
+        self._forward_backward(st, overlap=self.overlap, parity=parity)
+        self._reduce_gradients(parity)
+        self._adam(st, parity)
 
     def _capture(self):
         """Capture the full-batch step once.  With data parallelism the graph is cut at the gradient
@@ -385,25 +466,28 @@ class FusedTrainingPlan:
             snap = tuple(t.clone() for t in state)
             n0 = query("scvi_launch_count")
             self._whole_step()
+            self._n_exec += 1  # the warm-up is a real exchange on every rank: the parity moves with it
             self.kernel_launches_per_step = query("scvi_launch_count") - n0  # this library's kernels only
             for dst, src in zip(state, snap, strict=True):
                 dst.copy_(src)
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
-        if self.world == 1 or self.ddp_mode != "split":  # NCCL collectives are captured with the kernels
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                self._whole_step()
-            self._graphs = (g,)
-        else:
-            g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g1):
-                st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-                self._prologue(st)
-                self._forward_backward(st, overlap=self.overlap)
-            with torch.cuda.graph(g2):
-                self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream))
-            self._graphs = (g1, g2)
+        self._graphs = []
+        for parity in range(len(self._g2)):  # "p2p": one graph per gradient buffer, replayed alternately
+            if self.world == 1 or self.ddp_mode != "split":  # collectives are captured with the kernels
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self._whole_step(parity=parity)
+                self._graphs.append((g,))
+            else:
+                g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g1):
+                    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+                    self._prologue(st)
+                    self._forward_backward(st, overlap=self.overlap, parity=parity)
+                with torch.cuda.graph(g2):
+                    self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream), parity)
+                self._graphs.append((g1, g2))
 
     def set_epoch(self, epoch: int):
         self.current_epoch = epoch
@@ -417,6 +501,10 @@ class FusedTrainingPlan:
         `noise` (parity tests) force the eager path."""
         n = idx.numel()
         self.idx[:n].copy_(idx, non_blocking=True)
+        if not self.n_epochs_kl_warmup and self.n_steps_kl_warmup:
+            # step-based warm-up: the weight follows `global_step` (reference _trainingplans.py:31-72,248-258)
+            self.klw.fill_(float(compute_kl_weight(self.current_epoch, self.global_step, self.n_epochs_kl_warmup,
+                                                   self.n_steps_kl_warmup, self.max_kl_weight, self.min_kl_weight)))
         fed = drop_mask is not None or noise is not None
         if fed or n != self.B or not self.use_cuda_graph:
             self.B_cur = n
@@ -424,17 +512,21 @@ class FusedTrainingPlan:
                 self.mask[:n].copy_(drop_mask.to(self.dev, dtype=torch.uint8))
             if noise is not None:
                 self.noise[:n].copy_(noise.to(self.dev))
-            self._whole_step(feed_rng=not fed)
+            # whichever of the two was not supplied is drawn from the library streams
+            self._whole_step(gen_mask=drop_mask is None, gen_noise=noise is None)
             self.B_cur = self.B
         else:
             if self._graphs is None:
                 self._capture()
-            if len(self._graphs) == 1:
-                self._graphs[0].replay()
+            parity = self._parity()
+            graphs = self._graphs[parity]
+            if len(graphs) == 1:
+                graphs[0].replay()
             else:  # forward + backward | all-reduce | Adam
-                self._graphs[0].replay()
-                torch.distributed.all_reduce(self.g, group=self.pg)
-                self._graphs[1].replay()
+                graphs[0].replay()
+                torch.distributed.all_reduce(self._g2[parity], group=self.pg)
+                graphs[1].replay()
+        self._n_exec += 1
         self.global_step += 1
         return self.out3
 
@@ -478,6 +570,7 @@ class FusedTrainingPlan:
                 acc[0] += out[0].double() * c.numel()
                 acc[1:] += out[1:].double()
                 n_cells += c.numel()
+            self._broadcast_buffers()
             a = acc.cpu()
             history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
                             "reconstruction_loss": float(a[1]) / max(n_cells, 1),
@@ -518,6 +611,7 @@ class FusedTrainingPlan:
                 acc[0] += out[0].double() * n
                 acc[1:] += out[1:].double()
                 n_cells += n
+            self._broadcast_buffers()
             a = acc.cpu()
             history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),
                             "reconstruction_loss": float(a[1]) / max(n_cells, 1),
@@ -551,9 +645,7 @@ class FusedTrainingPlan:
                 acc[0] += out[0].double() * chunk.numel()
                 acc[1:] += out[1:].double()
                 n_cells += chunk.numel()
-            if self.world > 1:  # BN running buffers follow rank 0 (DDP broadcast_buffers semantics)
-                for b in (self.bn1_rm, self.bn1_rv, self.bn2_rm, self.bn2_rv):
-                    torch.distributed.broadcast(b, src=0, group=self.pg)
+            self._broadcast_buffers()
             if log_every_epoch:
                 a = acc.cpu()
                 history.append({"epoch": epoch, "train_loss": float(a[0]) / max(n_cells, 1),

@@ -1,0 +1,142 @@
+"""GPU: the configuration `bench.py` times, pinned against the CPU oracle at full size.
+
+`FusedTrainingPlan` exactly as the bench builds it -- tcgen05 kernels (`precision=1`), minibatch of 8192 cells
+gathered in place from a >= 100k-row HBM-resident matrix, 2000 genes / ZINB / 8 batches (BASELINE.json
+configs[1]) and 4000 genes / NB / 32 batches (configs[2]) -- with a fed dropout mask and reparameterisation
+noise, against `oracle.loss_and_grads` + `oracle.adam_step` on the host (a fraction of a second per step at
+this size).  Tolerances are the north-star's: ELBO and per-cell reconstruction loss 1e-5 relative, every
+gradient of the arena 1e-4 relative (norm-wise, absolute floor for the mathematically-zero gradients of the
+Linear biases feeding a BatchNorm), parameters after two Adam steps.
+
+Also here: CUDA-graph replay == the eager kernel sequence, bit for bit, with the library's own Philox streams
+(reference contract: `tests/model/test_scvi.py:1245-1259`, same seed => same weights).
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import scvi_oracle as O
+from tests._golden import grad_close, rel_err
+
+pytestmark = pytest.mark.gpu
+
+N_ROWS, B = 100_352, 8192
+
+
+def _resident_counts(dev, G, seed=0, zero_frac=0.3):
+    """NB(5, .3) x Bernoulli(1 - zero_frac), the synthetic_iid recipe, generated on the device."""
+    gen = torch.Generator(device=dev).manual_seed(seed)
+    conc = torch.full((1,), 5.0, device=dev)
+    lam = torch._standard_gamma(conc.expand(N_ROWS, G), generator=gen) * (0.7 / 0.3)
+    x = torch.poisson(lam, generator=gen) * (torch.rand(N_ROWS, G, device=dev, generator=gen) >= zero_frac)
+    return x.contiguous()
+
+
+def _build(dev, G, nb, lik, kl_weight, graph=False, seed=0, counts=None, **kw):
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.data import DeviceResidentCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+
+    X = _resident_counts(dev, G) if counts is None else counts
+    batch = torch.arange(N_ROWS, device=dev) * nb // N_ROWS
+    torch.manual_seed(seed)
+    m = S.VAE(n_input=G, n_batch=nb, gene_likelihood=lik, n_hidden=128, n_latent=10, precision=1).train()
+    P0 = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    plan = FusedTrainingPlan(m, DeviceResidentCounts(X, batch=batch, device=dev), batch_size=B,
+                             n_epochs_kl_warmup=None, max_kl_weight=kl_weight, use_cuda_graph=graph, **kw)
+    plan.set_epoch(0)
+    return plan, m, P0, X, batch
+
+
+@pytest.mark.parametrize("G,nb,lik", [(2000, 8, "zinb"), (4000, 32, "nb")], ids=["c2-2000-zinb-8b", "c3-4000-nb-32b"])
+def test_bench_configuration_step_matches_oracle(G, nb, lik):
+    dev = torch.device("cuda:0")
+    klw = 0.37
+    plan, m, P0, X, batch = _build(dev, G, nb, lik, klw)
+    g = torch.Generator().manual_seed(11)
+    n_steps = 2
+    idxs = [torch.randperm(N_ROWS, generator=g)[:B].sort().values for _ in range(n_steps)]
+    masks = [(torch.rand(B, 128, generator=g) >= 0.1).to(torch.uint8) for _ in range(n_steps)]
+    noises = [torch.randn(B, 10, generator=g) for _ in range(n_steps)]
+    keys = O.trained_keys(lik)
+    torch.set_num_threads(max(1, torch.get_num_threads()))
+    P = {k: v.clone() for k, v in P0.items()}
+    M = {k: torch.zeros_like(P[k]) for k in keys}
+    V = {k: torch.zeros_like(P[k]) for k in keys}
+    for t in range(n_steps):
+        o3 = plan.training_step(idxs[t].to(dev), drop_mask=masks[t], noise=noises[t])
+        torch.cuda.synchronize()
+        x = X[idxs[t].to(dev)].cpu()
+        bi = batch[idxs[t].to(dev)].cpu().view(-1, 1)
+        out, grads = O.loss_and_grads(P, x, bi, n_batch=nb, gene_likelihood=lik, kl_weight=klw, drop_mask=masks[t],
+                                      noise=noises[t])
+        # ---- ELBO, per-cell pieces
+        loss_ref = float(out["loss"])
+        assert abs(float(o3[0]) - loss_ref) <= 1e-5 * abs(loss_ref), (t, float(o3[0]), loss_ref)
+        rec, rec_ref = plan.reconst.cpu().double(), out["reconst"].detach().double()
+        assert float(((rec - rec_ref).abs() / rec_ref.abs()).max()) <= 1e-5, t
+        assert float((plan.kl.cpu().double() - out["kl_z"].detach().double()).abs().max()) <= 1e-4
+        assert abs(float(o3[1]) - float(rec_ref.sum())) <= 1e-5 * abs(float(rec_ref.sum()))
+        # ---- every gradient of the arena
+        scale = max(float(v.abs().max()) for v in grads.values())
+        for k in keys:
+            assert grad_close(plan.Gd[k].cpu(), grads[k], 1e-4, scale), (
+                t, k, rel_err(plan.Gd[k].cpu(), grads[k]))
+        # ---- the reference optimizer on the oracle's gradients
+        for k in keys:
+            P[k], M[k], V[k] = O.adam_step(P[k], grads[k], M[k], V[k], t + 1)
+        P.update(out["bn_buffers"])
+    sd = m.state_dict()
+    for k in keys:
+        upd_ref = (P[k] - P0[k]).numpy()
+        upd = sd[k].cpu().numpy() - P0[k].numpy()
+        assert np.linalg.norm(upd - upd_ref) <= 2e-3 * np.linalg.norm(upd_ref) + 1e-6 * np.sqrt(upd.size), k
+        assert rel_err(sd[k].cpu(), P[k]) < 1e-5, k
+    for k in out["bn_buffers"]:
+        assert rel_err(sd[k].cpu(), P[k]) < 1e-5, k
+
+
+def test_bench_configuration_on_sparse_counts_matches_oracle():
+    """The ~90 %-zeros count distribution of SURVEY 8(d) (real scRNA sparsity): the zero-count fast paths of the
+    fused likelihood kernels against the oracle, full size."""
+    dev = torch.device("cuda:0")
+    G, nb, lik, klw = 2000, 8, "zinb", 1.0
+    X = _resident_counts(dev, G, seed=3, zero_frac=0.9)
+    plan, m, P0, X, batch = _build(dev, G, nb, lik, klw, counts=X)
+    g = torch.Generator().manual_seed(5)
+    idx = torch.randperm(N_ROWS, generator=g)[:B].sort().values
+    mask = (torch.rand(B, 128, generator=g) >= 0.1).to(torch.uint8)
+    noise = torch.randn(B, 10, generator=g)
+    o3 = plan.training_step(idx.to(dev), drop_mask=mask, noise=noise)
+    torch.cuda.synchronize()
+    out, grads = O.loss_and_grads(P0, X[idx.to(dev)].cpu(), batch[idx.to(dev)].cpu().view(-1, 1), n_batch=nb,
+                                  gene_likelihood=lik, kl_weight=klw, drop_mask=mask, noise=noise)
+    assert abs(float(o3[0]) - float(out["loss"])) <= 1e-5 * abs(float(out["loss"]))
+    rec, rec_ref = plan.reconst.cpu().double(), out["reconst"].detach().double()
+    assert float(((rec - rec_ref).abs() / rec_ref.abs()).max()) <= 1e-5
+    scale = max(float(v.abs().max()) for v in grads.values())
+    for k in O.trained_keys(lik):
+        assert grad_close(plan.Gd[k].cpu(), grads[k], 1e-4, scale), (k, rel_err(plan.Gd[k].cpu(), grads[k]))
+
+
+@pytest.mark.parametrize("G,nb,lik", [(2000, 8, "zinb"), (4000, 32, "nb")], ids=["c2", "c3"])
+def test_graph_replay_equals_eager_sequence_bitwise(G, nb, lik):
+    """Same seed, same minibatches: the captured graph (side-stream prepack included) and the eager launch
+    sequence end with bit-identical parameter / Adam arenas and BatchNorm buffers."""
+    dev = torch.device("cuda:0")
+    X = _resident_counts(dev, G, seed=1)
+    g = torch.Generator().manual_seed(2)
+    idxs = [torch.randperm(N_ROWS, generator=g)[:B].sort().values.to(dev) for _ in range(4)]
+    res = []
+    for graph in (False, True):
+        plan, m, _, _, _ = _build(dev, G, nb, lik, 0.5, graph=graph, seed=7, counts=X)
+        losses = []
+        for ix in idxs:
+            losses.append(plan.training_step(ix).clone())
+        torch.cuda.synchronize()
+        assert (plan._graphs is not None) == graph
+        res.append((plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.bn1_rm.clone(), plan.bn1_rv.clone(),
+                    plan.bn2_rm.clone(), plan.bn2_rv.clone(), plan.step_counter.clone(), torch.stack(losses)))
+    for a, b in zip(res[0], res[1], strict=True):
+        assert torch.equal(a, b)
+    assert int(res[0][7][0]) == 4 and torch.isfinite(res[0][8]).all()

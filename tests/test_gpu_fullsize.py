@@ -1,5 +1,6 @@
 """GPU: size-independent properties at the bench workload's full shapes (BASELINE.json configs[1]: 100k cells x
-2000 genes, 8 batches, ZINB, n_hidden 128, minibatch 8192) -- sizes the CPU oracle does not finish in seconds.
+2000 genes, 8 batches, ZINB, n_hidden 128, minibatch 8192).  The direct oracle comparison at these shapes is
+tests/test_gpu_benchconfig.py; the properties below need no oracle.
 
 * the minibatch gather (fp32 / uint8 / uint16 / CSR residency) equals an independent indexing of the same matrix
   bit for bit, and round-trips through the compact formats;

@@ -1,0 +1,139 @@
+"""GPU (>= 2 devices; skipped on one): the data-parallel step, numerically.
+
+What torch DDP guarantees the reference (`Trainer(strategy="ddp")`, reference tests/model/test_multigpu.py:29-36):
+replicas start equal, every step applies the MEAN of the per-replica gradients, replicas stay equal.  Checked for
+every `ddp_mode` of `FusedTrainingPlan` (the fused peer-memory all-reduce + Adam "p2p" and the three NCCL
+routes):
+
+* replicas built from different seeds hold rank 0's parameters after construction (initial broadcast);
+* one step with fed dropout masks / noise: parameters and Adam moments equal -- bit for bit -- Adam applied to
+  (g_0 + g_1) / 2, with g_r the gradient a single-process plan computes on rank r's minibatch (BatchNorm
+  statistics per replica, as under DDP);
+* CUDA-graph replay == eager sequence over several steps with the library's rank-keyed random streams, and the
+  parameter arenas are identical on all ranks afterwards.
+"""
+import os
+import traceback
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+MODES = ["p2p", "split", "overlap", "graph"]
+
+
+def _worker(rank, world, port, q):
+    try:
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        import scvi_tools_b200 as S
+        from oracle import scvi_oracle as O
+        from scvi_tools_b200._lib import call
+        from scvi_tools_b200.data import DeviceResidentCounts
+        from scvi_tools_b200.train import FusedTrainingPlan
+
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        pg = dist.group.WORLD
+        N, G, nb, B = 4096, 512, 3, 256
+        X, batch = O.synthetic_iid(N + 2, G, nb, seed=0)
+        data = DeviceResidentCounts(X, batch=batch, device=dev)
+        n_obs = data.n_obs
+
+        def build(pgroup, graph, mode="p2p", lik="zinb", seed=0):
+            torch.manual_seed(seed)
+            m = S.VAE(n_input=G, n_batch=nb, gene_likelihood=lik, precision=1).train()
+            kw = {} if pgroup is None else {"process_group": pgroup, "ddp_mode": mode}
+            plan = FusedTrainingPlan(m, data, batch_size=B, n_epochs_kl_warmup=None, max_kl_weight=0.5,
+                                     use_cuda_graph=graph, seed=3, **kw)
+            plan.set_epoch(0)
+            return plan
+
+        def inputs(r, step):
+            g = torch.Generator().manual_seed(1000 * step + r)
+            idx = torch.randperm(n_obs, generator=g)[:B].sort().values
+            mask = (torch.rand(B, 128, generator=g) >= 0.1).to(torch.uint8)
+            noise = torch.randn(B, 10, generator=g)
+            return idx, mask, noise
+
+        for mode in MODES:
+            # ---- initial broadcast + one fed step against single-process arithmetic
+            plan = build(pg, False, mode, seed=11 * rank)  # deliberately different initial weights per rank
+            if mode == "p2p":
+                assert plan.exchange is not None and plan.ddp_mode == "p2p", "peer memory could not be mapped"
+            p0 = plan.p.clone()
+            both = [torch.empty_like(p0) for _ in range(world)]
+            dist.all_gather(both, p0)
+            assert all(torch.equal(both[0], b) for b in both), f"{mode}: replicas differ after construction"
+            idx, mask, noise = inputs(rank, 0)
+            plan.training_step(idx.to(dev), drop_mask=mask, noise=noise)
+            torch.cuda.synchronize()
+            gsum = torch.zeros_like(p0)
+            for r in range(world):
+                single = build(None, False)
+                single.p.copy_(p0)
+                ix, mk, nz = inputs(r, 0)
+                single.training_step(ix.to(dev), drop_mask=mk, noise=nz)
+                gsum += single.g  # world == 2: a + b is order-independent
+            exp_p, exp_m, exp_v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            call("scvi_adam_step", C.c_void_p(exp_p.data_ptr()), C.c_void_p(gsum.data_ptr()), C.c_void_p(exp_m.data_ptr()),
+                 C.c_void_p(exp_v.data_ptr()), exp_p.numel(), 1, 1e-3, 0.9, 0.999, 0.01, 1e-6, 1.0 / world, st)
+            torch.cuda.synchronize()
+            assert float((exp_p - p0).abs().max()) > 0
+            for name, got, want in (("p", plan.p, exp_p), ("m", plan.m, exp_m), ("v", plan.v, exp_v)):
+                assert torch.equal(got, want), (mode, name, float((got - want).abs().max()))
+            assert int(plan.step_counter[0]) == 1
+            if hasattr(plan, "close"):
+                plan.close()
+            # ---- graph replay == eager sequence; replicas stay identical
+            end = []
+            for graph in (True, False):
+                plan = build(pg, graph, mode)
+                for step in range(5):
+                    ix, _, _ = inputs(rank, 10 + step)
+                    plan.training_step(ix.to(dev))
+                torch.cuda.synchronize()
+                end.append((plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.bn1_rm.clone(), plan.bn2_rv.clone()))
+                assert int(plan.step_counter[0]) == 5
+                plan.close()
+            for a, b in zip(end[0], end[1], strict=True):
+                assert torch.equal(a, b), f"{mode}: graph replay differs from the eager sequence"
+            both = [torch.empty_like(end[0][0]) for _ in range(world)]
+            dist.all_gather(both, end[0][0])
+            assert all(torch.equal(both[0], b) for b in both), f"{mode}: replicas diverged"
+            assert torch.isfinite(end[0][0]).all()
+        dist.barrier()
+        q.put((rank, "ok"))
+    except Exception:  # noqa: BLE001
+        q.put((rank, traceback.format_exc()))
+    finally:
+        os._exit(0)  # graph-captured NCCL kernels can block communicator teardown
+
+
+@pytest.mark.timeout(900)
+def test_two_rank_step_matches_single_process_arithmetic():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = 29700 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=800)
+        if p.is_alive():
+            p.kill()
+            pytest.fail("data-parallel worker hung")
+    res = dict(q.get() for _ in range(2))
+    for r in range(2):
+        assert res[r] == "ok", f"rank {r}:\n{res[r]}"
