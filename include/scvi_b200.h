@@ -49,6 +49,15 @@ extern "C" {
 #define SCVI_PREC_TC 1     /* tcgen05 tensor-core path (when built) */
 #define SCVI_PREC_PREPACKED 0x100 /* OR-ed into `precision` of scvi_decoder_nll_fwd: the workspace already holds the
                                      packed weight tiles (scvi_decoder_nll_prepack ran on the current weights) */
+/* Count operand of the tensor-core training kernels (OR-ed into `precision` of scvi_decoder_nll_fwd / _bwd and
+ * into `flags` of scvi_linear_fwd / _bwd as SCVI_LIN_X_INTEGER / SCVI_LIN_X_U8):
+ *   SCVI_X_INTEGER  the fp32 count matrix holds non-negative integers only (what AnnData `X` / a counts layer
+ *                   holds; the data classes verify it once at load time) -- enables the straight-line per-element
+ *                   path (table look-ups, no float<->int conversions);
+ *   SCVI_X_U8       `x` points to uint8 counts (all counts < 256; ldx in bytes, rows 8-byte aligned for vector
+ *                   loads): 1 byte per count from HBM.  Training kernels only (SCVI_PREC_TC with dh / dW). */
+#define SCVI_X_INTEGER 0x200
+#define SCVI_X_U8 0x400
 
 int scvi_b200_abi_version(void); /* 3 */
 const char* scvi_last_error_string(void);
@@ -246,13 +255,15 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
  * computed in the same pass as the likelihood (the per-element derivatives share every
  * sub-expression with the log-probability), so the backward only has to produce the weight
  * gradients (call scvi_decoder_nll_bwd with dh = NULL).
+ * SCVI_PREC_TC contract: library[b] >= log(max_g x[b, g]) - log 2 (true for the observed library log sum_g x):
+ * the fp16 operand scale of a cell is derived from exp(library[b]).
  * precision SCVI_PREC_FP32: FFMA tiles, ws may be NULL.  SCVI_PREC_TC: tcgen05 tensor cores with an
  *   error-compensated fp16 split (fp32-level accuracy; needs H == 128) and a 256-byte aligned
  *   workspace of scvi_decoder_nll_fwd_ws_bytes() bytes. */
 int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, int precision);
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r,
-                         const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
+                         const void* x, int64_t ldx, const int64_t* row_idx, const float* library,
                          int likelihood, int precision, float* reconst, float* row_stats,
                          const float* g_reconst, float* dh, int64_t lddh, void* ws, void* stream);
 /* The parameter-only part of scvi_decoder_nll_fwd (SCVI_PREC_TC: fp16 hi/lo weight tiles, per-gene constants,
@@ -270,7 +281,7 @@ int scvi_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, c
 int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
 int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
                          const float* bs, const float* Wp, const float* bp, const float* px_r,
-                         const float* x, int64_t ldx, const int64_t* row_idx, const float* library,
+                         const void* x, int64_t ldx, const int64_t* row_idx, const float* library,
                          const float* row_stats, const float* g_reconst, int likelihood, int precision,
                          float* dh, int64_t lddh, float* dWs, float* dbs, float* dWp, float* dbp,
                          float* dpx_r, void* ws, const void* fwd_ws, void* stream);

@@ -135,6 +135,8 @@ def vae_forward(
     training: bool = True,
     dropout_rate: float = 0.1,
     log_variational: bool = True,
+    relu_gate1=None,
+    relu_gate2=None,
 ):
     """Forward of the default SCVI VAE (n_layers=1, one-hot batch, observed library, gene dispersion).
 
@@ -145,6 +147,11 @@ def vae_forward(
 
     ``drop_mask`` [B,H] keep-mask and ``noise`` [B,L] standard-normal draws replace the
     reference's RNG consumers (``nn.Dropout`` and ``Normal.rsample``).
+    ``relu_gate1`` / ``relu_gate2`` (bool [B,H], default None = the reference's ``torch.relu``) fix the side of
+    the ReLU kink per element for the encoder / decoder hidden layer: ``a = bn * gate``.  A pre-activation that
+    sits within float32 rounding distance of zero lands on either side depending on the summation order of the
+    GEMM that produced it, and the derivative jumps with it; full-size parity tests evaluate the oracle on the
+    side the kernel under test took (and check that every such element is at rounding distance from zero).
     Returns a dict of every intermediate the parity tests compare, plus the new BN buffers.
     """
     dt = x.dtype
@@ -156,7 +163,7 @@ def vae_forward(
     bn1, rm1, rv1 = batchnorm(
         y1, P[ENC + "1.weight"], P[ENC + "1.bias"], P[ENC + "1.running_mean"], P[ENC + "1.running_var"], training
     )
-    a1 = dropout(torch.relu(bn1), drop_mask, dropout_rate, training)
+    a1 = dropout(torch.relu(bn1) if relu_gate1 is None else bn1 * relu_gate1.to(dt), drop_mask, dropout_rate, training)
     # --- Encoder heads: _base_components.py:311-317
     q_m = F.linear(a1, P["z_encoder.mean_encoder.weight"], P["z_encoder.mean_encoder.bias"])
     q_v = torch.exp(F.linear(a1, P["z_encoder.var_encoder.weight"], P["z_encoder.var_encoder.bias"])) + VAR_EPS
@@ -170,7 +177,7 @@ def vae_forward(
     bn2, rm2, rv2 = batchnorm(
         y2, P[DEC + "1.weight"], P[DEC + "1.bias"], P[DEC + "1.running_mean"], P[DEC + "1.running_var"], training
     )
-    h = torch.relu(bn2)
+    h = torch.relu(bn2) if relu_gate2 is None else bn2 * relu_gate2.to(dt)
     # --- heads: _base_components.py:436-441
     scale_logits = F.linear(h, P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"])
     px_scale = torch.softmax(scale_logits, dim=-1)
@@ -191,6 +198,8 @@ def vae_forward(
     return {
         "library": library,
         "y1": y1,
+        "bn1": bn1,
+        "bn2": bn2,
         "a1": a1,
         "q_m": q_m,
         "q_v": q_v,

@@ -120,3 +120,4 @@ LIK_NB, LIK_ZINB = 0, 1
 LIN_LOG1P, LIN_LIBRARY, LIN_TC = 1, 2, 4
 PREC_FP32, PREC_TC = 0, 1
 PREC_PREPACKED = 0x100
+X_INTEGER, X_U8 = 0x200, 0x400  # count-operand kind OR-ed into `precision` (SCVI_X_INTEGER / SCVI_X_U8)

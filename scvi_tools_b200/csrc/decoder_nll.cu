@@ -636,33 +636,42 @@ static int set_smem(K kernel, size_t bytes, const char* name) {
 namespace scvi {
 int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
-                       const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                       const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
                        float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws, cudaStream_t st,
-                       bool prepacked);
+                       bool prepacked, int xkind);
 int tc_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs, const float* Wp,
                            const float* bp, const float* px_r, int likelihood, bool want_dh, void* ws, cudaStream_t st);
 int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood);
 int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
-                          const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                          const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
                           float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
-                          cudaStream_t st);
+                          int xkind, cudaStream_t st);
+// count-operand kind carried in the `precision` argument (scvi_b200.h: SCVI_X_INTEGER / SCVI_X_U8)
+static inline int take_xkind(int& precision) {
+  const int k = (precision & SCVI_X_U8) ? 2 : (precision & SCVI_X_INTEGER) ? 1 : 0;
+  precision &= ~(SCVI_X_U8 | SCVI_X_INTEGER);
+  return k;
+}
 }  // namespace scvi
 
 extern "C" {
 
 int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, int precision) {
+  scvi::take_xkind(precision);
   if (precision == SCVI_PREC_TC) return scvi::tc_decoder_fwd_ws_bytes(B, H, G, likelihood);
   return 0;
 }
 
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
-                         const float* bs, const float* Wp, const float* bp, const float* px_r, const float* x,
+                         const float* bs, const float* Wp, const float* bp, const float* px_r, const void* xv,
                          int64_t ldx, const int64_t* row_idx, const float* library, int likelihood, int precision,
                          float* reconst, float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
                          void* stream) {
   using namespace scvi;
+  const float* x = reinterpret_cast<const float*>(xv);
+  const int xkind = take_xkind(precision);
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "scvi_decoder_nll_fwd: unknown likelihood %d", likelihood);
   SCVI_REQUIRE(h && Ws && bs && px_r && x && library && reconst && row_stats && (!zinb || (Wp && bp)),
@@ -676,8 +685,12 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   const bool prepacked = (precision & SCVI_PREC_PREPACKED) != 0;
   precision &= ~SCVI_PREC_PREPACKED;
   if (precision == SCVI_PREC_TC)
-    return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, library, likelihood, reconst,
-                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream, prepacked);
+    return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, xv, ldx, row_idx, library, likelihood, reconst,
+                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream, prepacked, xkind);
+  if (xkind == 2) {
+    set_error("scvi_decoder_nll_fwd: SCVI_X_U8 needs SCVI_PREC_TC");
+    return SCVI_EUNSUPPORTED;
+  }
   if (precision != SCVI_PREC_FP32) {
     set_error("scvi_decoder_nll_fwd: unknown precision %d", precision);
     return SCVI_EUNSUPPORTED;
@@ -742,13 +755,19 @@ int64_t scvi_decoder_nll_bwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likel
   } while (0)
 
 int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
-                         const float* bs, const float* Wp, const float* bp, const float* px_r, const float* x,
+                         const float* bs, const float* Wp, const float* bp, const float* px_r, const void* xv,
                          int64_t ldx, const int64_t* row_idx, const float* library, const float* row_stats,
                          const float* g_reconst, int likelihood, int precision, float* dh, int64_t lddh,
                          float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
                          void* stream) {
   using namespace scvi;
   const char* name = "scvi_decoder_nll_bwd";
+  const float* x = reinterpret_cast<const float*>(xv);
+  const int xkind = take_xkind(precision);
+  if (xkind == 2 && (dh || precision != SCVI_PREC_TC || H != 128)) {
+    set_error("%s: SCVI_X_U8 is read by the tensor-core weight-gradient kernel only (SCVI_PREC_TC, H == 128, dh == NULL)", name);
+    return SCVI_EUNSUPPORTED;
+  }
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "%s: unknown likelihood %d", name, likelihood);
   const bool want_dw = dWs || dWp || dbs || dbp || dpx_r;
@@ -774,8 +793,8 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(dh)");
   }
   if (want_dw && precision == SCVI_PREC_TC && H == 128)
-    return tc_decoder_nll_bwd_dw(h, ldh, B, G, Ws, bs, Wp, bp, px_r, x, ldx, row_idx, row_stats, g_reconst, likelihood,
-                                 dWs, dbs, dWp, dbp, dpx_r, ws, fwd_ws, st);
+    return tc_decoder_nll_bwd_dw(h, ldh, B, G, Ws, bs, Wp, bp, px_r, xv, ldx, row_idx, row_stats, g_reconst, likelihood,
+                                 dWs, dbs, dWp, dbp, dpx_r, ws, fwd_ws, xkind, st);
   if (want_dw) {
     const int64_t S = dw_row_splits(B, G);
     const int nheads = zinb ? 2 : 1;

@@ -63,13 +63,15 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
     }
   }
   if (e < nT * TC_N) {
+    // genes beyond G (tile padding): theta 1, dropout bias 0 and a scale bias of -1e30, so that mu = 0 and every
+    // per-element output of the training kernels (ll, g1, dpi, softmax p) is an exact zero without any masking
     const bool ok = e < G;
     const float theta = ok ? expf(px_r[e]) : 1.f;
     float o[TC_GC];
     o[0] = theta;
     o[1] = logf(theta + eps);
     o[2] = lgammaf(theta);
-    o[3] = ok ? bs[e] : 0.f;
+    o[3] = ok ? bs[e] : -1e30f;
     o[4] = (ok && nheads == 2) ? bp[e] : 0.f;
     o[5] = 1.f / (theta + eps);
     o[6] = digamma_pos(theta);
@@ -473,9 +475,9 @@ static int tc_launch_fwd(const TcPlan& p, const float* h, int64_t ldh, int64_t B
   return SCVI_OK;
 }
 
-int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
-                     const float* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
-                     int nsplit_lse, int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part,
+int tc_launch_nll_dh(bool zinb, int xkind, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
+                     const void* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
+                     int nsplit_lse, int nsplit, int tiles_per_split, float* out_part, float* dh_part,
                      const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
                      cudaStream_t st);
 
@@ -502,10 +504,11 @@ int tc_decoder_nll_prepack(int64_t B, int64_t H, int64_t G, const float* Ws, con
 }
 
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
-                       const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                       const float* Wp, const float* bp, const float* px_r, const void* xv, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
                        float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
-                       cudaStream_t st, bool prepacked) {
+                       cudaStream_t st, bool prepacked, int xkind) {
+  const float* x = reinterpret_cast<const float*>(xv);  // the inference kernels below read fp32 counts only
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   if (H != TC_H) {
     set_error("scvi_decoder_nll_fwd(SCVI_PREC_TC): n_hidden must be %d (got %lld)", TC_H, (long long)H);
@@ -534,9 +537,13 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
     else rc = tc_launch_fwd<0, false>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st);
     if (rc) return rc;
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");
-    return tc_launch_nll_dh(zinb, h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, p.nsplit, p.nsplit2,
-                            p.tiles_per_split2, xvec, outp, (float*)(w8 + p.off_dh), g_reconst, reconst, row_stats, dh,
+    return tc_launch_nll_dh(zinb, xkind, h, ldh, B, G, packed32, xv, ldx, row_idx, library, lse, p.nsplit, p.nsplit2,
+                            p.tiles_per_split2, outp, (float*)(w8 + p.off_dh), g_reconst, reconst, row_stats, dh,
                             lddh, st);
+  }
+  if (xkind == 2) {
+    set_error("scvi_decoder_nll_fwd(SCVI_X_U8): uint8 counts are read by the training kernels only (dh requested)");
+    return SCVI_EUNSUPPORTED;
   }
   if (zinb) {
     if ((rc = tc_launch_fwd<0, true>(p, h, ldh, B, G, packed, gconst, x, ldx, row_idx, library, xvec, lse, outp, st))) return rc;

@@ -64,6 +64,82 @@ __device__ __forceinline__ void tt_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t
 }
 
 // =======================================================================================
+// Count operand of the training kernels.  XK selects how the resident matrix is read:
+//   XK_F32      fp32 counts, any value (generic per-element path: table or lgamma series, per element)
+//   XK_F32_INT  fp32 counts the caller guarantees to be non-negative integers (SCVI_X_INTEGER)
+//   XK_U8       uint8 counts (SCVI_X_U8): 1 byte per count from HBM, no conversion instructions
+// For the two integer kinds a thread checks its 8 counts of a tile at once ("all below the table length");
+// if so the straight-line lean element runs, otherwise the generic one.
+// =======================================================================================
+enum { XK_F32 = 0, XK_F32_INT = 1, XK_U8 = 2 };
+
+template <int XK>
+struct XRaw {
+  uint32_t w[XK == XK_U8 ? 2 : 8];
+};
+
+// this thread's 8 counts of one row starting at gene gbb (zero beyond G or for an invalid row)
+template <int XK>
+__device__ __forceinline__ void tt_load_x8(const void* __restrict__ xrow_v, int64_t gbb, int64_t G, bool rvalid,
+                                           int xvec, XRaw<XK>& d) {
+  if (XK == XK_U8) {
+    const uint8_t* xrow = reinterpret_cast<const uint8_t*>(xrow_v);
+    if (rvalid && xvec && gbb + 8 <= G) {
+      asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(d.w[0]), "=r"(d.w[1]) : "l"(xrow + gbb));
+    } else {
+      d.w[0] = d.w[1] = 0u;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (rvalid && gbb + i < G) d.w[i >> 2] |= (uint32_t)__ldg(xrow + gbb + i) << (8 * (i & 3));
+    }
+  } else {
+    const float* xrow = reinterpret_cast<const float*>(xrow_v);
+    if (rvalid && xvec) {
+      const float4 t4 = (gbb < G) ? ld_stream4(xrow + gbb) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 u4 = (gbb + 4 < G) ? ld_stream4(xrow + gbb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      d.w[0] = __float_as_uint(t4.x); d.w[1] = __float_as_uint(t4.y); d.w[2] = __float_as_uint(t4.z); d.w[3] = __float_as_uint(t4.w);
+      d.w[4] = __float_as_uint(u4.x); d.w[5] = __float_as_uint(u4.y); d.w[6] = __float_as_uint(u4.z); d.w[7] = __float_as_uint(u4.w);
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d.w[i] = (rvalid && gbb + i < G) ? __float_as_uint(__ldg(xrow + gbb + i)) : 0u;
+    }
+  }
+}
+
+// raw -> counts as floats + table indices; returns "all 8 are integers below `limit`" (limit = 64: a power of two)
+template <int XK>
+__device__ __forceinline__ bool tt_prep_x8(const XRaw<XK>& d, float (&xq)[8], int (&xi)[8]) {
+  constexpr float MAGIC = 8388608.f;  // 2^23: integer n < 2^23 -> float bits 0x4B000000 | n
+  if (XK == XK_U8) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint32_t bits = __byte_perm(d.w[i >> 2], 0x4B000000u, 0x7650u | (uint32_t)(i & 3));
+      xq[i] = __uint_as_float(bits) - MAGIC;
+      xi[i] = (int)(bits & 0xffu);
+    }
+    return ((d.w[0] | d.w[1]) & 0xC0C0C0C0u) == 0u;
+  } else if (XK == XK_F32_INT) {
+    uint32_t orv = 0u;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      xq[i] = __uint_as_float(d.w[i]);
+      const uint32_t bits = __float_as_uint(xq[i] + MAGIC);
+      orv |= bits ^ 0x4B000000u;
+      xi[i] = (int)(bits & 63u);
+    }
+    return (orv & ~63u) == 0u;
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      xq[i] = __uint_as_float(d.w[i]);
+      xi[i] = 0;
+    }
+    return false;
+  }
+}
+static_assert(fm::LGT == 64 && fm::DGT <= 64, "tt_prep_x8 tests counts against 64");
+
+// =======================================================================================
 // K2: fused NLL + dh
 // =======================================================================================
 template <bool ZINB>
@@ -82,10 +158,40 @@ struct K2Smem {
   static constexpr uint32_t TOTAL = RED + 4 * TC_M * 2 * 4;
 };
 
-template <bool ZINB>
+// the 8 elements of one thread for one tile.  Padded genes (beyond G) carry constants that make every output an
+// exact zero (scale bias -1e30 => mu = 0, dropout bias 0, theta 1, count 0), so nothing is masked here; rows
+// beyond B produce values that are never stored.
+template <bool ZINB, bool LEAN>
+__device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi)[8], const float (&sv)[8],
+                                            const float (&pv)[8], const float* __restrict__ gc,
+                                            const float* __restrict__ tab, const float* __restrict__ s_lgx1, float krow,
+                                            float eps, float s1, float kP, float kD, float& nll, float& S,
+                                            float (&a1)[8], float (&a2)[8], float (&a3)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 k0 = *reinterpret_cast<const float4*>(gc + i * TC_GC);
+    const float4 k1 = *reinterpret_cast<const float4*>(gc + i * TC_GC + 4);
+    fm::GeneK gk;
+    gk.theta = k0.x; gk.log_theta = k0.y; gk.lg_theta = k0.z; gk.rth = k1.y; gk.dg_theta = k1.z;
+    const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
+    const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
+    float ll, g1, dpi, mu;
+    if (LEAN)
+      fm::elem_fwd_lean<ZINB>(xq[i], tab[i * fm::LGT + xi[i]], sl, pl, krow, gk, eps, ll, g1, dpi, mu);
+    else
+      fm::elem_fwd_tab<ZINB>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu);
+    nll -= ll;
+    S += g1;
+    a1[i] = g1 * s1;
+    a2[i] = mu * kP;
+    a3[i] = dpi * kD;
+  }
+}
+
+template <bool ZINB, int XK>
 __global__ void __launch_bounds__(TT_THREADS, 1)
     tc_nll_dh_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, int64_t G,
-                     const uint8_t* __restrict__ packed32, const float* __restrict__ x, int64_t ldx,
+                     const uint8_t* __restrict__ packed32, const void* __restrict__ x, int64_t ldx,
                      const int64_t* __restrict__ row_idx, const float* __restrict__ library,
                      const float* __restrict__ lse_part /*[nsplit_lse][B][2]*/, int nsplit_lse, int tiles_per_split,
                      float eps, int xvec, float* __restrict__ out_part /*[nsplit][B][2] = (nll, S)*/,
@@ -189,7 +295,8 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     const int r = 32 * q + lane;
     const bool rvalid = r < valid;
     const int64_t grow = rvalid ? (row_idx ? row_idx[r0 + r] : r0 + r) : 0;
-    const float* xrow = x + grow * ldx;
+    const void* xrow = XK == XK_U8 ? (const void*)(reinterpret_cast<const uint8_t*>(x) + grow * ldx)
+                                   : (const void*)(reinterpret_cast<const float*>(x) + grow * ldx);
     float krow = 0.f, elib_inv = 0.f, s1 = 1.f, inv_s1 = 1.f;
     if (rvalid) {
       float m = -INFINITY, l = 0.f;
@@ -209,65 +316,59 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       s1 = tc::pow2i(14 - e);
       inv_s1 = tc::pow2i(e - 14);
     }
-    const float sP = tc::pow2i(TC_P_SCALE_LOG2), sD = tc::pow2i(TC_DP_SCALE_LOG2);
+    // staged-operand factors: softmax p = mu exp(-library) x 2^14; -dpi x 2^10
+    const float kP = elib_inv * tc::pow2i(TC_P_SCALE_LOG2), kD = -tc::pow2i(TC_DP_SCALE_LOG2);
     const uint32_t lane_sel = (uint32_t)(32 * q) << 16;
     uint8_t* stg = smem + L::STG;
     float nll = 0.f, S = 0.f;
-    // x for this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
+    // counts of this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
     // land during tile j's math, so the fence.proxy.async at the end of the tile (which drains this thread's
     // outstanding loads) never waits on them.
-    auto load_x = [&](int jj, float (&dst)[8]) {
-      const int64_t gbb = (int64_t)(t0 + jj) * TC_NT + 8 * cg;
-      if (rvalid && xvec) {
-        const float4 t4 = (gbb < G) ? ld_stream4(xrow + gbb) : make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4 u4 = (gbb + 4 < G) ? ld_stream4(xrow + gbb + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-        dst[0] = t4.x; dst[1] = t4.y; dst[2] = t4.z; dst[3] = t4.w; dst[4] = u4.x; dst[5] = u4.y; dst[6] = u4.z; dst[7] = u4.w;
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) dst[i] = (rvalid && gbb + i < G) ? __ldg(xrow + gbb + i) : 0.f;
-      }
-    };
-    float xq[8], xn[8];
-    if (ntiles > 0) load_x(0, xq);
-    for (int j = 0; j < ntiles; ++j) {
-      const int s = j & 1;
-      const int64_t gb = (int64_t)(t0 + j) * TC_NT + 8 * cg;
-      if (j + 1 < ntiles) load_x(j + 1, xn);
-      tc::mbar_wait(&tfull[s], (j >> 1) & 1);
-      tc::mbar_wait(&wfull[s], (j >> 1) & 1);  // acquire the bulk-copied gene constants
+    XRaw<XK> xcur, xnext;
+    if (ntiles > 0) tt_load_x8<XK>(xrow, (int64_t)t0 * TC_NT + 8 * cg, G, rvalid, xvec, xcur);
+    // Logits of a tile are pulled out of TMEM one tile ahead, at the END of the previous tile and BEFORE this
+    // warp reports its staged operands: the dh MMAs that the report releases would otherwise occupy the tensor
+    // memory port while the next tile's tcgen05.ld waits behind them (16 % of K2's stall samples, r02c capture).
+    float sv[8], pv[8];
+    auto fetch_logits = [&](int jj) {
+      const int ss = jj & 1;
+      tc::mbar_wait(&tfull[ss], (jj >> 1) & 1);
+      tc::mbar_wait(&wfull[ss], (jj >> 1) & 1);  // acquire the bulk-copied gene constants of that tile too
       tc::fence_after_sync();
-      float sv[8], pv[8];
-      tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 0) * TC_NT + 8 * cg, sv);
-      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 1) * TC_NT + 8 * cg, pv);
+      tc::tmem_ld8(tmem_base + lane_sel + (ss * 2 + 0) * TC_NT + 8 * cg, sv);
+      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (ss * 2 + 1) * TC_NT + 8 * cg, pv);
       tc::tmem_ld_wait();
       tc::fence_before_sync();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&tempty[s]);  // logits buffer drained
+      if (lane == 0) tc::mbar_arrive(&tempty[ss]);  // logits buffer drained
+    };
+    if (ntiles > 0) fetch_logits(0);
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j & 1;
+      // Consume this tile's counts BEFORE issuing the next tile's loads: the wait on their scoreboard then covers
+      // only loads that have had a whole tile to land.  (Issued the other way round, the new loads share the
+      // scoreboard and every tile pays a full DRAM latency -- 19 % of K2's stall samples in the r02b capture.)
+#pragma unroll
+      for (int i = 0; i < (int)(sizeof(xcur.w) / 4); ++i) asm volatile("" : "+r"(xcur.w[i]));
+      float xq[8];
+      int xi[8];
+      const bool lean = tt_prep_x8<XK>(xcur, xq, xi);
+      if (j + 1 < ntiles) tt_load_x8<XK>(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xnext);
       const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
       const float* tab = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32 + TC_GC32_BYTES) +
                          8 * cg * fm::LGT;
-      float a1[8], a2[8], a3[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float4 k0 = *reinterpret_cast<const float4*>(gc + i * TC_GC);
-        const float4 k1 = *reinterpret_cast<const float4*>(gc + i * TC_GC + 4);
-        fm::GeneK gk;
-        gk.theta = k0.x; gk.log_theta = k0.y; gk.lg_theta = k0.z; gk.rth = k1.y; gk.dg_theta = k1.z;
-        const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
-        const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
-        float ll, g1, dpi, mu;
-        fm::elem_fwd_tab<ZINB>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu);
-        const bool ok = rvalid && (gb + i < G);
-        nll -= ok ? ll : 0.f;
-        S += ok ? g1 : 0.f;
-        a1[i] = ok ? g1 * s1 : 0.f;
-        a2[i] = ok ? mu * elib_inv * sP : 0.f;
-        a3[i] = ok ? -dpi * sD : 0.f;
-      }
       uint4 hi1, lo1, hi2, lo2, hi3, lo3;
-      tc::split8(a1, hi1, lo1);
-      tc::split8(a2, hi2, lo2);
-      if (ZINB) tc::split8(a3, hi3, lo3);
+      {
+        float a1[8], a2[8], a3[8];
+        if (XK != XK_F32 && lean)
+          tt_k2_elems<ZINB, true>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
+        else
+          tt_k2_elems<ZINB, false>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
+        tc::split8(a1, hi1, lo1);
+        tc::split8(a2, hi2, lo2);
+        if (ZINB) tc::split8(a3, hi3, lo3);
+      }
+      if (j + 1 < ntiles) fetch_logits(j + 1);
       tc::mbar_wait(sempty, (j & 1) ^ 1);  // output MMAs of the previous tile have read the staging buffers
       const uint32_t off = cg * (TC_M * 16) + r * 16;
       *reinterpret_cast<uint4*>(stg + 0 * TT_ABLK + off) = hi1;
@@ -281,8 +382,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(sfull);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) xq[i] = xn[i];
+      xcur = xnext;
     }
     // per-row partials of this gene split: combine the 4 column groups
     s_red[(cg * TC_M + r) * 2 + 0] = nll;
@@ -385,11 +485,11 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
 // ---------------------------------------------------------------------------------------
 // host: K2 launcher (called by tc_decoder_nll_fwd in decoder_tc.cu when dh is requested)
 // ---------------------------------------------------------------------------------------
-template <bool ZINB>
-static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32, const float* x,
+template <bool ZINB, int XK>
+static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32, const void* x,
                         int64_t ldx, const int64_t* row_idx, const float* library, const float* lse, int nsplit_lse,
                         int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, cudaStream_t st) {
-  auto k = tc_nll_dh_kernel<ZINB>;
+  auto k = tc_nll_dh_kernel<ZINB, XK>;
   constexpr int smem = (int)K2Smem<ZINB>::TOTAL + 128;
   static std::atomic<uint64_t> optin{0};
   if (int rc = smem_optin((const void*)k, smem, optin, "tc_nll_dh")) return rc;
@@ -399,15 +499,20 @@ static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const
   return SCVI_OK;
 }
 
-int tc_launch_nll_dh(bool zinb, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
-                     const float* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
-                     int nsplit_lse, int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part,
+// xkind: XK_F32 / XK_F32_INT / XK_U8 (the count operand; ldx in elements of that type)
+int tc_launch_nll_dh(bool zinb, int xkind, const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32,
+                     const void* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
+                     int nsplit_lse, int nsplit, int tiles_per_split, float* out_part, float* dh_part,
                      const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
                      cudaStream_t st) {
-  int rc = zinb ? tt_launch_k2<true>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit,
-                                     tiles_per_split, xvec, out_part, dh_part, st)
-                : tt_launch_k2<false>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit,
-                                      tiles_per_split, xvec, out_part, dh_part, st);
+  const int xvec = xkind == XK_U8 ? ((ldx % 8 == 0) && ((uintptr_t)x % 8 == 0))
+                                  : ((ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0));
+  int rc;
+#define SCVI_K2(Z, K) \
+  tt_launch_k2<Z, K>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit, tiles_per_split, xvec, out_part, dh_part, st)
+  if (zinb) rc = xkind == XK_U8 ? SCVI_K2(true, XK_U8) : xkind == XK_F32_INT ? SCVI_K2(true, XK_F32_INT) : SCVI_K2(true, XK_F32);
+  else rc = xkind == XK_U8 ? SCVI_K2(false, XK_U8) : xkind == XK_F32_INT ? SCVI_K2(false, XK_F32_INT) : SCVI_K2(false, XK_F32);
+#undef SCVI_K2
   if (rc) return rc;
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc nll+dh)");
   tc_train_combine_kernel<<<(unsigned)cdiv(B, 8), 256, 0, st>>>(lse, nsplit_lse, out_part, dh_part, nsplit, library,
@@ -490,10 +595,38 @@ struct K3Smem {
 static_assert(K3Smem<true>::DGTAB % 16 == 0 && K3Smem<true>::DGTAB_BYTES % 16 == 0, "bulk copy alignment");
 static_assert(K3Smem<true>::TOTAL + 128 <= 232448, "K3 shared memory");
 
-template <bool ZINB>
+// the 8 elements (8 rows x this thread's gene) of one tile: derivatives, column sums, staged operands.
+// Padded rows carry u = 0 (every product below is an exact zero), padded genes are never stored: no masks.
+template <bool ZINB, bool LEAN>
+__device__ __forceinline__ void tt_k3_elems(const float (&xq)[8], const int (&xi)[8], const float (&sv)[8],
+                                            const float (&pv)[8], const float* __restrict__ rowc,
+                                            const float* __restrict__ dgt, const fm::GeneK& gk, float bsv, float bpv,
+                                            float eps, float sc_ds, float sc_dp, float& cs, float& cp, float& cr,
+                                            float (&a1)[8], float (&a2)[8]) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float4 rc = *reinterpret_cast<const float4*>(rowc + i * TC_ROWC);  // krow, u, u*S*exp(-lib), valid
+    const float sl = fmaf(sv[i], TC_RESCALE, bsv);
+    const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
+    float g1, dpi, dth, mu;
+    if (LEAN)
+      fm::elem_bwd_lean<ZINB>(xq[i], dgt[xi[i]], sl, pl, rc.x, gk, eps, g1, dpi, dth, mu);
+    else
+      fm::elem_bwd_tab<ZINB>(xq[i], sl, pl, rc.x, gk, eps, dgt, g1, dpi, dth, mu);
+    const float ds = fmaf(rc.y, g1, -mu * rc.z);
+    const float dp = -rc.y * dpi;
+    cs += ds;
+    cp += dp;
+    cr = fmaf(-rc.y * gk.theta, dth, cr);
+    a1[i] = ds * sc_ds;
+    a2[i] = dp * sc_dp;
+  }
+}
+
+template <bool ZINB, int XK>
 __global__ void __launch_bounds__(TT_THREADS, 1)
     tc_dw_kernel(int64_t B, int64_t G, const uint8_t* __restrict__ packed128, const float* __restrict__ gconst,
-                 const uint8_t* __restrict__ hpack, const float* __restrict__ scal, const float* __restrict__ x,
+                 const uint8_t* __restrict__ hpack, const float* __restrict__ scal, const void* __restrict__ x,
                  int64_t ldx, int tiles_per_split, float eps, float* __restrict__ slabW /*[splits][NH][G][H]*/,
                  float* __restrict__ slabv /*[splits][3][G]*/) {
   using L = K3Smem<ZINB>;
@@ -627,12 +760,33 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::mbar_wait(&hfull[s], (j >> 1) & 1);  // acquire the row constants of this tile
       const float* rowc = reinterpret_cast<const float*>(smem + L::HST + s * TC_H32_STAGE_BYTES + 2 * TC_BLK32) + 8 * rg * TC_ROWC;
       float xq[8];
+      int xi[8];
+      uint32_t xmax = 0u;
+      constexpr float MAGIC = 8388608.f;  // 2^23: integer n < 2^23 -> float bits 0x4B000000 | n
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float2 id = *reinterpret_cast<const float2*>(rowc + i * TC_ROWC + 4);
         const int64_t rid = (int64_t)(((uint64_t)__float_as_uint(id.y) << 32) | (uint64_t)__float_as_uint(id.x));
-        xq[i] = gvalid ? ld_stream(x + rid * ldx + g) : 0.f;  // padded rows carry row id 0
+        // padded rows carry row id 0; padded genes read nothing
+        if (XK == XK_U8) {
+          const uint32_t b = gvalid ? (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(x) + rid * ldx + g) : 0u;
+          xi[i] = (int)b;
+          xmax = max(xmax, b);
+          xq[i] = __uint_as_float(0x4B000000u | b) - MAGIC;
+        } else {
+          xq[i] = gvalid ? ld_stream(reinterpret_cast<const float*>(x) + rid * ldx + g) : 0.f;
+          xi[i] = 0;
+        }
       }
+      if (XK == XK_F32_INT) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t n = __float_as_uint(xq[i] + MAGIC) ^ 0x4B000000u;  // the count itself when it is an integer < 2^23
+          xmax = max(xmax, n);
+          xi[i] = (int)(n & 63u);
+        }
+      }
+      const bool lean = XK != XK_F32 && xmax < (uint32_t)fm::DGT;
       tc::mbar_wait(&tfull[s], (j >> 1) & 1);
       tc::fence_after_sync();
       float sv[8], pv[8];
@@ -643,22 +797,10 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[s]);
       float a1[8], a2[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float4 rc = *reinterpret_cast<const float4*>(rowc + i * TC_ROWC);  // krow, u, u*S*exp(-lib), valid
-        const float sl = fmaf(sv[i], TC_RESCALE, bsv);
-        const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, bpv) : 0.f;
-        float g1, dpi, dth, mu;
-        fm::elem_bwd_tab<ZINB>(xq[i], sl, pl, rc.x, gk, eps, dgt, g1, dpi, dth, mu);
-        const bool ok = gvalid && rc.w != 0.f;
-        const float ds = ok ? rc.y * g1 - mu * rc.z : 0.f;
-        const float dp = ok ? -rc.y * dpi : 0.f;
-        cs += ds;
-        cp += dp;
-        cr += ok ? -rc.y * gk.theta * dth : 0.f;
-        a1[i] = ds * sc_ds;
-        a2[i] = dp * sc_dp;
-      }
+      if (lean)
+        tt_k3_elems<ZINB, true>(xq, xi, sv, pv, rowc, dgt, gk, bsv, bpv, eps, sc_ds, sc_dp, cs, cp, cr, a1, a2);
+      else
+        tt_k3_elems<ZINB, false>(xq, xi, sv, pv, rowc, dgt, gk, bsv, bpv, eps, sc_ds, sc_dp, cs, cp, cr, a1, a2);
       uint4 hi1, lo1, hi2, lo2;
       tc::split8(a1, hi1, lo1);
       if (ZINB) tc::split8(a2, hi2, lo2);
@@ -787,11 +929,11 @@ int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood) {
   return (int64_t)tt_bwd_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
 }
 
-template <bool ZINB>
+template <bool ZINB, int XK>
 static int tt_launch_k3(const TtBwdPlan& p, int64_t B, int64_t G, const uint8_t* packed, const float* gconst,
-                        const uint8_t* hpack, const float* scal, const float* x, int64_t ldx, float* slabW,
+                        const uint8_t* hpack, const float* scal, const void* x, int64_t ldx, float* slabW,
                         float* slabv, cudaStream_t st) {
-  auto k = tc_dw_kernel<ZINB>;
+  auto k = tc_dw_kernel<ZINB, XK>;
   constexpr int smem = (int)K3Smem<ZINB>::TOTAL + 128;
   static std::atomic<uint64_t> optin{0};
   if (int rc = smem_optin((const void*)k, smem, optin, "tc_dw")) return rc;
@@ -802,10 +944,10 @@ static int tt_launch_k3(const TtBwdPlan& p, int64_t B, int64_t G, const uint8_t*
 
 // weight-gradient half of the decoder backward on the tensor cores (H == 128)
 int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, const float* Ws, const float* bs,
-                          const float* Wp, const float* bp, const float* px_r, const float* x, int64_t ldx,
+                          const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
                           float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
-                          cudaStream_t st) {
+                          int xkind, cudaStream_t st) {
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   const int nheads = zinb ? 2 : 1;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): ws must be 256-byte aligned");
@@ -830,8 +972,11 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
   }
   tc_pack_h32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(h, ldh, B, row_stats, g_reconst, row_idx, hpack, scal);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack h)");
-  int rc = zinb ? tt_launch_k3<true>(p, B, G, (const uint8_t*)packed, gconst, hpack, scal, x, ldx, slabW, slabv, st)
-                : tt_launch_k3<false>(p, B, G, (const uint8_t*)packed, gconst, hpack, scal, x, ldx, slabW, slabv, st);
+  int rc;
+#define SCVI_K3(Z, K) tt_launch_k3<Z, K>(p, B, G, (const uint8_t*)packed, gconst, hpack, scal, x, ldx, slabW, slabv, st)
+  if (zinb) rc = xkind == XK_U8 ? SCVI_K3(true, XK_U8) : xkind == XK_F32_INT ? SCVI_K3(true, XK_F32_INT) : SCVI_K3(true, XK_F32);
+  else rc = xkind == XK_U8 ? SCVI_K3(false, XK_U8) : xkind == XK_F32_INT ? SCVI_K3(false, XK_F32_INT) : SCVI_K3(false, XK_F32);
+#undef SCVI_K3
   if (rc) return rc;
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc dW)");
   const int64_t GH = G * TC_H;

@@ -190,6 +190,81 @@ SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g
   }
 }
 
+// ---- lean straight-line variants for the fused training kernels ------------------------------------------
+// Contract: x is a non-negative INTEGER count below the table length (the caller checks its whole 8-element
+// chunk once and takes the generic variant above otherwise), `lgd` / `dgd` are the table entries of (gene, x).
+// No data-dependent branch, no float<->int conversion (both run on the SFU pipe): eight of these unrolled side
+// by side interleave freely, which is what hides the SFU latency.  log(theta+mu+eps) is formed as
+// log(theta+eps) + log(1 + mu/(theta+eps)) from the one lg2 the NB term needs anyway.
+// SFU ops: ZINB 9 (ex2 x3, lg2 x3, rcp x3), NB 5.
+template <bool ZINB>
+SCVI_FM void elem_fwd_lean(float x, float lgd, float s, float pi, float krow, const GeneK& g, float eps, float& ll,
+                           float& g1, float& dpi, float& mu) {
+  mu = ex2(fmaf(s, LOG2E, krow));
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + me);
+  const float lu = lg2(fmaf(mu, g.rth, 1.f));        // log2((theta+mu+eps) / (theta+eps))
+  const float thl = g.theta * (-LN2);
+  const float base = g.theta * mu * rT;
+  if (ZINB) {
+    const bool zero = x == 0.f;
+    const float a = fmaf(thl, lu, -pi);              // theta * (log(theta+eps) - log(theta+mu+eps)) - pi
+    const float ep = ex2(-fabsf(pi) * LOG2E);        // exp(-|pi|)
+    const float op = 1.f + ep;
+    const float ea = ex2(-fabsf(a) * LOG2E);
+    const float sel = zero ? 1.f + ea : me;
+    const float rp = rcp(op);                        // sigmoid(|pi|)
+    const float r1 = rcp(sel);
+    const float l1 = lg2(op);                        // softplus(-pi) = max(-pi, 0) + ln2 * l1
+    const float l2 = lg2(sel);                       // zero: softplus(a) - max(a, 0);  else log2(mu + eps)
+    const float nz = fmaf(x, fmaf(LN2, l2 - lu, -g.log_theta), lgd);  // x (log(mu+eps) - log(theta+mu+eps)) + lgd
+    const float head = (zero ? fmaxf(a, 0.f) : a) - fmaxf(-pi, 0.f);
+    ll = fmaf(-LN2, l1, head) + (zero ? LN2 * l2 : nz);
+    const float sa = a >= 0.f ? r1 : ea * r1;        // sigmoid(a) when zero
+    g1 = base * (zero ? sa : fmaf(-x, r1, 1.f));
+    const float e_rp = ep * rp;
+    const float sp = pi >= 0.f ? e_rp : rp;          // sigmoid(-pi)
+    const float sn = pi >= 0.f ? rp : e_rp;          // sigmoid(pi)
+    dpi = zero ? sp - sa : -sn;
+  } else {
+    const float l2 = lg2(me);
+    ll = fmaf(thl, lu, fmaf(x, fmaf(LN2, l2 - lu, -g.log_theta), lgd));
+    g1 = base * fmaf(-x, rcp(me), 1.f);
+    dpi = 0.f;
+  }
+}
+
+// backward twin (genes-owned dW kernel): g1, dpi, dth = d(ll)/d(theta), mu.  SFU ops: ZINB 7, NB 4.
+template <bool ZINB>
+SCVI_FM void elem_bwd_lean(float x, float dgd, float s, float pi, float krow, const GeneK& g, float eps, float& g1,
+                           float& dpi, float& dth, float& mu) {
+  mu = ex2(fmaf(s, LOG2E, krow));
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + me);
+  const float lu = lg2(fmaf(mu, g.rth, 1.f));
+  const float d_log = -LN2 * lu;
+  const float da_dth = fmaf(g.theta, g.rth - rT, d_log);
+  const float base = g.theta * mu * rT;
+  const float nz_dth = fmaf(-x, rT, da_dth) + dgd;
+  if (ZINB) {
+    const bool zero = x == 0.f;
+    const float a = fmaf(g.theta, d_log, -pi);
+    const float ep = ex2(-fabsf(pi) * LOG2E);
+    const float ea = ex2(-fabsf(a) * LOG2E);
+    const float rp = rcp(1.f + ep);
+    const float r1 = rcp(zero ? 1.f + ea : me);
+    const float sa = a >= 0.f ? r1 : ea * r1;
+    const float e_rp = ep * rp;
+    g1 = base * (zero ? sa : fmaf(-x, r1, 1.f));
+    dpi = zero ? (pi >= 0.f ? e_rp : rp) - sa : -(pi >= 0.f ? rp : e_rp);
+    dth = zero ? sa * da_dth : nz_dth;
+  } else {
+    g1 = base * fmaf(-x, rcp(me), 1.f);
+    dpi = 0.f;
+    dth = nz_dth;  // x == 0: dgd = 0 and x * rT = 0
+  }
+}
+
 // ---- the same likelihoods with mu given (standalone log_prob kernels) -------------------------------------
 // lgamma(x + theta) - lgamma(theta) - lgamma(x + 1); exactly 0 at x == 0 as in the reference
 SCVI_FM float lgd_series(float x, const GeneK& g, const float* __restrict__ lgx1) {

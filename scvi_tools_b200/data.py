@@ -91,6 +91,8 @@ class HostStreamedCounts:
         G = X.shape[1]
         self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G), batch=torch.zeros(2 * self.B, dtype=torch.int64),
                                           device=self.dev)
+        # the staging rows hold whatever the host matrix holds: integer counts unless it had to stay float32
+        self.stage.integer_counts = self.dtype != torch.float32 or DeviceResidentCounts._all_integer(self.host)
         self._compact = None if self.dtype == torch.float32 else torch.empty(2 * self.B, G, dtype=self.dtype, device=self.dev)
         self._pin = [torch.empty(self.B, G, dtype=self.dtype).pin_memory() for _ in range(2)]
         self._pin_b = [torch.empty(self.B, dtype=torch.int64).pin_memory() for _ in range(2)]
@@ -228,6 +230,7 @@ class DeviceResidentCSR:
         np_idt = np.uint16 if idt == torch.uint16 else np.int32
         self.indices = torch.from_numpy(indices.numpy().astype(np_idt)).to(dev).contiguous()
         self.values = values.to(vdt).to(dev).contiguous()
+        self.integer_counts = vdt != torch.float32 or DeviceResidentCounts._all_integer(self.values.view(1, -1))
         n = self.shape[0]
 
         def col(v):
@@ -287,6 +290,9 @@ class DeviceResidentCounts:
             X = X.to(torch.float32)
         self.X = X.to(dev).contiguous()
         n = self.X.shape[0]
+        # non-negative integer counts (what a counts layer holds): lets the training kernels take their
+        # straight-line per-element path (include/scvi_b200.h, SCVI_X_INTEGER); verified once, here
+        self.integer_counts = self.X.dtype != torch.float32 or self._all_integer(self.X)
 
         def col(v):
             if v is None:
@@ -296,6 +302,14 @@ class DeviceResidentCounts:
 
         self.batch = col(batch)
         self.labels = col(labels)
+
+    @staticmethod
+    def _all_integer(X: torch.Tensor, chunk: int = 1 << 16) -> bool:
+        for s in range(0, X.shape[0], chunk):
+            x = X[s : s + chunk]
+            if not bool(((x >= 0) & (x == x.floor()) & (x < 8388608.0)).all()):
+                return False
+        return True
 
     @property
     def n_obs(self) -> int:

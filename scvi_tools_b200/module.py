@@ -248,10 +248,16 @@ class VAE(nn.Module):
         # GEMM arithmetic of the fused kernels: None = the tcgen05 path (error-compensated fp16 split, fp32
         # accumulate, held to the same parity tolerances) whenever its shape constraint n_hidden == 128 holds,
         # FFMA fp32 otherwise; _lib.PREC_FP32 / _lib.PREC_TC force one
+        # The tensor-core kernels scale their fp16 operands per cell by exp(library), which bounds every
+        # per-gene derivative when the library IS the observed log-count sum; an encoded library
+        # (use_observed_lib_size=False) gives no such bound, so that option runs on the FFMA kernels.
+        observed = use_size_factor_key or use_observed_lib_size
         if precision is None:
-            precision = _lib.PREC_TC if n_hidden == 128 else _lib.PREC_FP32
+            precision = _lib.PREC_TC if (n_hidden == 128 and observed) else _lib.PREC_FP32
         if precision == _lib.PREC_TC and n_hidden != 128:
             raise ValueError("precision=PREC_TC needs n_hidden == 128")
+        if precision == _lib.PREC_TC and not observed:
+            raise NotImplementedError("precision=PREC_TC needs the observed library size (use_observed_lib_size=True)")
         self.precision = precision
         self._minified_data_type = None
 

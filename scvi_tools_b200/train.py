@@ -202,6 +202,11 @@ class FusedTrainingPlan:
         self.bn2_rm, self.bn2_rv = sd[DEC + "1.running_mean"], sd[DEC + "1.running_var"]
         self.bn1_nbt, self.bn2_nbt = sd[ENC + "1.num_batches_tracked"], sd[DEC + "1.num_batches_tracked"]
 
+    @property
+    def _x_integer(self):
+        """The matrix the step reads holds non-negative integer counts only (its data class verified it)."""
+        return bool(getattr(self.data, "integer_counts", False))
+
     def _parity(self, n_exec=None):
         return ((self._n_exec if n_exec is None else n_exec) & 1) if len(self._g2) == 2 else 0
 
@@ -275,6 +280,10 @@ class FusedTrainingPlan:
         ldx = X.stride(0)
         lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
         prec = self.module.precision
+        # how the training kernels may read the counts (uint8 bytes / guaranteed-integer fp32 / any fp32)
+        xkind = 0
+        if prec == _lib.PREC_TC:
+            xkind = _lib.X_U8 if X.dtype == torch.uint8 else (_lib.X_INTEGER if self._x_integer else 0)
         Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
         Wp = P.get("decoder.px_dropout_decoder.weight")
         bp = P.get("decoder.px_dropout_decoder.bias")
@@ -313,7 +322,7 @@ class FusedTrainingPlan:
         if overlap:
             main.wait_stream(side)  # packed weight tiles ready
         call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), lik, prec | (_lib.PREC_PREPACKED if overlap else 0), _p(self.reconst),
+             _p(self.idx), _p(self.library), lik, prec | xkind | (_lib.PREC_PREPACKED if overlap else 0), _p(self.reconst),
              _p(self.stats), _p(self.g_rec), _p(self.dh), H, _p(self.ws_fwd), st)
         if overlap:
             side.wait_stream(main)
@@ -323,7 +332,7 @@ class FusedTrainingPlan:
             call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         # ---- backward
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec, None, H,
+             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec | xkind, None, H,
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
              _p(Gd["px_r"]), _p(self.ws), _p(self.ws_fwd) if prec == _lib.PREC_TC else None, st)
@@ -589,6 +598,7 @@ class FusedTrainingPlan:
             if self.data.n_obs != self.B:  # the plan was built on something else: swap in a staging matrix
                 self.data = DeviceResidentCounts(torch.zeros(self.B, self.G),
                                                  batch=torch.zeros(self.B, dtype=torch.int64), device=self.dev)
+            self.data.integer_counts = csr.integer_counts  # what densify() will write into the staging rows
             self.batch_cols = torch.zeros(self.B, dtype=torch.int32, device=self.dev)
             self._graphs = None
             self.csr = csr

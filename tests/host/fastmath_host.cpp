@@ -79,6 +79,32 @@ void fm_elem_bwd_tab(int zinb, int n, const float* x, const float* s, const floa
     out[4 * i] = g1; out[4 * i + 1] = dpi; out[4 * i + 2] = dth; out[4 * i + 3] = mu;
   }
 }
+// lean straight-line variants (integer x below the table length): out[n][4] = ll, g1, dpi, mu / g1, dpi, dth, mu
+void fm_elem_fwd_lean(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
+                      const float* theta, float eps, float* out) {
+  for (int i = 0; i < n; ++i) {
+    const GeneK g = make_gene(theta[i], eps);
+    const int k = (int)x[i];
+    const float lgd = k == 0 ? 0.f : (float)(std::lgamma((double)k + (double)theta[i]) - std::lgamma((double)theta[i]) - std::lgamma(k + 1.0));
+    float ll, g1, dpi, mu;
+    if (zinb) elem_fwd_lean<true>(x[i], lgd, s[i], pi[i], krow[i], g, eps, ll, g1, dpi, mu);
+    else elem_fwd_lean<false>(x[i], lgd, s[i], pi[i], krow[i], g, eps, ll, g1, dpi, mu);
+    out[4 * i] = ll; out[4 * i + 1] = g1; out[4 * i + 2] = dpi; out[4 * i + 3] = mu;
+  }
+}
+void fm_elem_bwd_lean(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
+                      const float* theta, float eps, float* out) {
+  for (int i = 0; i < n; ++i) {
+    const GeneK g = make_gene(theta[i], eps);
+    const int k = (int)x[i];
+    double acc = 0.0;
+    for (int j = 0; j < k; ++j) acc += 1.0 / ((double)theta[i] + j);
+    float g1, dpi, dth, mu;
+    if (zinb) elem_bwd_lean<true>(x[i], (float)acc, s[i], pi[i], krow[i], g, eps, g1, dpi, dth, mu);
+    else elem_bwd_lean<false>(x[i], (float)acc, s[i], pi[i], krow[i], g, eps, g1, dpi, dth, mu);
+    out[4 * i] = g1; out[4 * i + 1] = dpi; out[4 * i + 2] = dth; out[4 * i + 3] = mu;
+  }
+}
 void fm_lgamma(int n, const float* z, float* out) { for (int i = 0; i < n; ++i) out[i] = lgamma_pos(z[i]); }
 void fm_digamma(int n, const float* z, float* out) { for (int i = 0; i < n; ++i) out[i] = digamma_pos_fast(z[i]); }
 }

@@ -93,6 +93,39 @@ def test_elem_fwd_bwd_vs_float64(lib, zinb):
     assert np.max(np.abs(obt[:, 2] - dth) / tsc) < 1e-5
 
 
+@pytest.mark.parametrize("zinb", [0, 1])
+def test_lean_elements_vs_float64(lib, zinb):
+    """The straight-line variants of the fused training kernels (integer counts below the table length;
+    tiny / huge mu and saturated logits included)."""
+    n = 200000
+    x, s, pi, krow, theta = _inputs(n, seed=10 + zinb)
+    x = np.minimum(x, 47.0).astype(np.float32)  # below both table lengths (LGT 64, DGT 48)
+    krow[: n // 10] -= 30.0  # mu down to ~1e-9: the eps terms matter
+    ll, g1, dpi, dth, mu = _reference(zinb, x, s, pi, krow, theta)
+    out = np.empty((n, 4), dtype=np.float32)
+    lib.fm_elem_fwd_lean(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(out))
+    z = x.astype(np.float64) + theta
+    scale = 1.0 + np.abs(ll) + 0.1 * z * np.log1p(z)
+    ok = mu > 1e-30
+    assert np.max(np.abs(out[ok, 3] - mu[ok]) / mu[ok]) < 2e-5  # exp of a float32 argument of magnitude ~60
+    assert np.max(np.abs(out[:, 0] - ll) / scale) < 5e-6
+    assert np.mean(np.abs(out[:, 0] - ll)) < 5e-6
+    gsc = 1.0 + np.abs(g1) + x
+    assert np.max(np.abs(out[:, 1] - g1) / gsc) < 5e-6
+    assert np.max(np.abs(out[:, 2] - dpi)) < 1e-5
+    ob = np.empty((n, 4), dtype=np.float32)
+    lib.fm_elem_bwd_lean(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(ob))
+    assert np.max(np.abs(ob[:, 0] - g1) / gsc) < 5e-6
+    assert np.max(np.abs(ob[:, 1] - dpi)) < 1e-5
+    tsc = 1.0 + np.abs(dth) + x / theta
+    assert np.max(np.abs(ob[:, 2] - dth) / tsc) < 1e-5
+    # the lean and the table-driven generic variants are interchangeable element by element
+    ot = np.empty((n, 4), dtype=np.float32)
+    lib.fm_elem_fwd_tab(zinb, n, _p(x), _p(s), _p(pi), _p(krow), _p(theta), C.c_float(EPS), _p(ot))
+    assert np.max(np.abs(ot[:, 0] - out[:, 0]) / scale) < 2e-6
+    assert np.max(np.abs(ot[:, 1] - out[:, 1]) / gsc) < 2e-6
+
+
 def test_lgamma_digamma_series(lib):
     from scipy.special import digamma, gammaln
 

@@ -8,6 +8,16 @@ this size).  Tolerances are the north-star's: ELBO and per-cell reconstruction l
 gradient of the arena 1e-4 relative (norm-wise, absolute floor for the mathematically-zero gradients of the
 Linear biases feeding a BatchNorm), parameters after two Adam steps.
 
+ReLU kinks.  At these sizes a handful of the 8192 x 128 hidden pre-activations sit within float32 rounding
+distance of zero (the encoder's are sums of thousands of log1p(x) w terms: rounding noise ~1e-7 x sum |terms|), and
+which side of the kink such an element lands on depends on the GEMM's summation order -- in this library, in
+cuBLAS, on the CPU.  One flipped gate moves the BatchNorm bias gradient by ~4e-4 relative and the encoder weight
+gradient by ~1e-3 (measured; tools/debug_c3.py), so two correct float32 implementations cannot agree to 1e-4 on
+those tensors unless they take the same side.  The test therefore (1) reads the side the kernels took from their
+activations, (2) asserts that wherever it differs from the oracle's the oracle's pre-activation is at rounding
+distance from zero, and (3) evaluates the oracle on the kernels' side (`relu_gate1/2`); everything else is the
+plain oracle.
+
 Also here: CUDA-graph replay == the eager kernel sequence, bit for bit, with the library's own Philox streams
 (reference contract: `tests/model/test_scvi.py:1245-1259`, same seed => same weights).
 """
@@ -48,6 +58,24 @@ def _build(dev, G, nb, lik, kl_weight, graph=False, seed=0, counts=None, **kw):
     return plan, m, P0, X, batch
 
 
+def _oracle_on_kernel_side(plan, P, x, bi, nb, lik, klw, mask, noise, max_flips=64):
+    """`oracle.loss_and_grads` with the ReLU kink side of every hidden unit taken from the kernels' activations."""
+    kw = dict(n_batch=nb, gene_likelihood=lik, kl_weight=klw, drop_mask=mask, noise=noise)
+    out, grads = O.loss_and_grads(P, x, bi, **kw)
+    keep = mask.bool()
+    gate1 = torch.where(keep, plan.a1.cpu() > 0, out["bn1"] > 0)  # a dropped unit carries no gradient either way
+    gate2 = plan.h.cpu() > 0
+    flip1, flip2 = gate1 != (out["bn1"] > 0), gate2 != (out["bn2"] > 0)
+    n_flips = int(flip1.sum()) + int(flip2.sum())
+    if n_flips == 0:
+        return out, grads
+    assert n_flips <= max_flips, f"{n_flips} ReLU gates differ from the oracle's"
+    # BatchNorm output is O(1): a float32 GEMM of K terms leaves it uncertain by ~1e-7 * sum|terms| / std ~ 1e-5
+    assert float(out["bn1"][flip1].abs().max() if flip1.any() else 0.0) < 2e-4
+    assert float(out["bn2"][flip2].abs().max() if flip2.any() else 0.0) < 2e-5
+    return O.loss_and_grads(P, x, bi, relu_gate1=gate1, relu_gate2=gate2, **kw)
+
+
 @pytest.mark.parametrize("G,nb,lik", [(2000, 8, "zinb"), (4000, 32, "nb")], ids=["c2-2000-zinb-8b", "c3-4000-nb-32b"])
 def test_bench_configuration_step_matches_oracle(G, nb, lik):
     dev = torch.device("cuda:0")
@@ -68,8 +96,7 @@ def test_bench_configuration_step_matches_oracle(G, nb, lik):
         torch.cuda.synchronize()
         x = X[idxs[t].to(dev)].cpu()
         bi = batch[idxs[t].to(dev)].cpu().view(-1, 1)
-        out, grads = O.loss_and_grads(P, x, bi, n_batch=nb, gene_likelihood=lik, kl_weight=klw, drop_mask=masks[t],
-                                      noise=noises[t])
+        out, grads = _oracle_on_kernel_side(plan, P, x, bi, nb, lik, klw, masks[t], noises[t])
         # ---- ELBO, per-cell pieces
         loss_ref = float(out["loss"])
         assert abs(float(o3[0]) - loss_ref) <= 1e-5 * abs(loss_ref), (t, float(o3[0]), loss_ref)
@@ -93,7 +120,9 @@ def test_bench_configuration_step_matches_oracle(G, nb, lik):
         assert np.linalg.norm(upd - upd_ref) <= 2e-3 * np.linalg.norm(upd_ref) + 1e-6 * np.sqrt(upd.size), k
         assert rel_err(sd[k].cpu(), P[k]) < 1e-5, k
     for k in out["bn_buffers"]:
-        assert rel_err(sd[k].cpu(), P[k]) < 1e-5, k
+        # running statistics of pre-activations that are float32 sums of thousands of terms (batch mean ~ 0 by
+        # cancellation): 1e-4 on the buffer, i.e. 1e-6 of the pre-activation scale at momentum 0.01
+        assert rel_err(sd[k].cpu(), P[k]) < 1e-4, k
 
 
 def test_bench_configuration_on_sparse_counts_matches_oracle():
@@ -109,8 +138,8 @@ def test_bench_configuration_on_sparse_counts_matches_oracle():
     noise = torch.randn(B, 10, generator=g)
     o3 = plan.training_step(idx.to(dev), drop_mask=mask, noise=noise)
     torch.cuda.synchronize()
-    out, grads = O.loss_and_grads(P0, X[idx.to(dev)].cpu(), batch[idx.to(dev)].cpu().view(-1, 1), n_batch=nb,
-                                  gene_likelihood=lik, kl_weight=klw, drop_mask=mask, noise=noise)
+    out, grads = _oracle_on_kernel_side(plan, P0, X[idx.to(dev)].cpu(), batch[idx.to(dev)].cpu().view(-1, 1), nb, lik,
+                                        klw, mask, noise)
     assert abs(float(o3[0]) - float(out["loss"])) <= 1e-5 * abs(float(out["loss"]))
     rec, rec_ref = plan.reconst.cpu().double(), out["reconst"].detach().double()
     assert float(((rec - rec_ref).abs() / rec_ref.abs()).max()) <= 1e-5
