@@ -191,6 +191,24 @@ int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t 
                          const float* mean, const float* rstd, const float* gamma, const float* beta,
                          int relu, const uint8_t* drop_mask, float drop_scale, int training, float* dy,
                          int64_t lddy, float* dgamma, float* dbeta, void* ws, void* stream);
+/* Allocation-free variant of scvi_bn_act_drop_bwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  Same arguments and results as scvi_bn_act_drop_bwd minus
+ * `ws`: the per-tile partial sums live in a scratch array built into the library image
+ * (SCVI_BN_STATIC_SCRATCH_BYTES = 526,592 bytes = scvi_bn_bwd_ws_bytes(16384, 256); every GPU that loads the
+ * library holds it until the process exits).  Shapes with scvi_bn_bwd_ws_bytes(B, N) beyond that are rejected
+ * with SCVI_EINVAL and a message naming both sizes.  The call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine): it resolves the scratch's device address once per device (cudaGetSymbolAddress,
+ * with the calling thread's current device) and launches the same kernels.  ALL calls on a device share the one
+ * array, which keeps the previous call's contents -- every word is rewritten before it is read, so nothing
+ * needs clearing -- and therefore two calls that overlap on the GPU (different streams, or graph branches that
+ * run concurrently) RACE: serialise them on one stream, or use scvi_bn_act_drop_bwd with separate workspaces. */
+#define SCVI_BN_STATIC_SCRATCH_BYTES 526592
+int64_t scvi_bn_static_scratch_bytes(void);
+int scvi_bn_act_drop_bwd_static(const float* da, int64_t ldda, const float* y, int64_t ldy, int64_t B, int64_t N,
+                                const float* mean, const float* rstd, const float* gamma, const float* beta,
+                                int relu, const uint8_t* drop_mask, float drop_scale, int training, float* dy,
+                                int64_t lddy, float* dgamma, float* dbeta, void* stream);
 
 /* ---- a4/a9: latent heads, reparameterisation, Normal KL -------------------------------
  * replaces Encoder.forward's heads (src/scvi/nn/_base_components.py:311-317):

@@ -158,6 +158,41 @@ __global__ void bn_bwd_apply_kernel(const float* __restrict__ da, int64_t ldda, 
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Scratch of the allocation-free entry point scvi_bn_act_drop_bwd_static: lives in the library image
+// (every GPU that loads the library holds these bytes until the process exits).  Layout = the `ws` of
+// scvi_bn_act_drop_bwd: [ceil(B/64)][2][N] per-tile partial sums, then [2][N] column sums.
+// In HOST code `g_bn_static_scratch` is only a stand-in for the symbol, not a device address: the
+// address a kernel may use comes from cudaGetSymbolAddress, looked up once per device below.
+// ---------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_bn_static_scratch[SCVI_BN_STATIC_SCRATCH_BYTES];
+
+static int bn_static_scratch_ptr(void** out) {
+  static std::atomic<void*> cache[64];  // per device ordinal; zero-initialised
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) {
+    set_error("scvi_bn_act_drop_bwd_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    return SCVI_ECUDA;
+  }
+  if (dev < 0 || dev >= 64) {
+    set_error("scvi_bn_act_drop_bwd_static: device ordinal %d out of range", dev);
+    return SCVI_EUNSUPPORTED;
+  }
+  void* p = cache[dev].load(std::memory_order_acquire);
+  if (!p) {  // first call on this device (which is current): resolve the symbol for it
+    e = cudaGetSymbolAddress(&p, g_bn_static_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      set_error("scvi_bn_act_drop_bwd_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return SCVI_ECUDA;
+    }
+    cache[dev].store(p, std::memory_order_release);  // two racing threads store the same address
+  }
+  *out = p;
+  return SCVI_OK;
+}
+
 }  // namespace scvi
 
 extern "C" {
@@ -233,5 +268,27 @@ int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t 
                                               drop_scale, training, sums, dy, lddy);
   SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(apply)");
   return SCVI_OK;
+}
+
+int64_t scvi_bn_static_scratch_bytes(void) { return (int64_t)SCVI_BN_STATIC_SCRATCH_BYTES; }
+
+int scvi_bn_act_drop_bwd_static(const float* da, int64_t ldda, const float* y, int64_t ldy, int64_t B, int64_t N,
+                                const float* mean, const float* rstd, const float* gamma, const float* beta,
+                                int relu, const uint8_t* drop_mask, float drop_scale, int training, float* dy,
+                                int64_t lddy, float* dgamma, float* dbeta, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(B > 0 && N > 0, "scvi_bn_act_drop_bwd_static: bad shape");
+  const int64_t need = scvi_bn_bwd_ws_bytes(B, N);
+  if (need > (int64_t)SCVI_BN_STATIC_SCRATCH_BYTES) {
+    set_error("scvi_bn_act_drop_bwd_static: B=%lld x N=%lld needs %lld bytes of scratch, the built-in scratch holds "
+              "%lld (use scvi_bn_act_drop_bwd with a caller-owned workspace)",
+              (long long)B, (long long)N, (long long)need, (long long)SCVI_BN_STATIC_SCRATCH_BYTES);
+    return SCVI_EINVAL;
+  }
+  void* scratch = nullptr;
+  if (int rc = bn_static_scratch_ptr(&scratch)) return rc;
+  // every partial and both column sums are overwritten before they are read: nothing has to start at zero
+  return scvi_bn_act_drop_bwd(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask, drop_scale, training,
+                              dy, lddy, dgamma, dbeta, scratch, stream);
 }
 }
