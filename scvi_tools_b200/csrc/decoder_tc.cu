@@ -141,23 +141,6 @@ struct TcSmem {
   static constexpr uint32_t TOTAL = LGX1 + fm::LGX1_TABLE * 4;
 };
 
-// issue the 3 x 8 MMAs of one head tile: D = Ahi*Bhi + Ahi*Blo + Alo*Bhi over K = 128
-__device__ __forceinline__ void tc_issue_head(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t b_hi,
-                                              uint32_t b_lo) {
-  constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_N);
-  constexpr uint32_t LBO = TC_M * 16, SBO = 128, KSTEP = 2 * LBO;  // one MMA consumes K = 16 = 2 k-chunks
-#pragma unroll
-  for (int ks = 0; ks < TC_H / 16; ++ks) {
-    const uint64_t ah = tc::smem_desc_kmajor(a_hi + ks * KSTEP, LBO, SBO);
-    const uint64_t al = tc::smem_desc_kmajor(a_lo + ks * KSTEP, LBO, SBO);
-    const uint64_t bh = tc::smem_desc_kmajor(b_hi + ks * KSTEP, LBO, SBO);
-    const uint64_t bl = tc::smem_desc_kmajor(b_lo + ks * KSTEP, LBO, SBO);
-    tc::mma_f16_ss(d_tmem, ah, bh, idesc, ks > 0);
-    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1);
-    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1);
-  }
-}
-
 // ---------------------------------------------------------------------------------------
 // forward.  MODE 0: per-(split,row) online (max, sum-exp) of the scale logits.
 //           MODE 1: per-(split,row) partial (-sum ll, S) given the merged (max, sum-exp).
@@ -228,9 +211,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer
-    if (lane == 0) {
-      const uint32_t a_hi = tc::smem_u32(s_hhi), a_lo = tc::smem_u32(s_hlo);
+    // ===== MMA issuer: warp-uniform loop, one elected lane issues (tc.cuh)
+    {
+      constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_N);
+      const uint32_t leader = tc::elect_one();
+      // A = h tile, B = weight tile of stage 0 (stage 1 = + TC_STAGE_BYTES): both K-major 128 x 128,
+      // LBO = 128*16, SBO = 128, one MMA consumes K = 16 = 2 k-chunks
+      const tc::Oper hA = tc::make_oper(tc::smem_u32(s_hhi), tc::smem_u32(s_hlo), TC_M * 16, 128, 2 * TC_M * 16);
+      const uint32_t st0 = tc::smem_u32(smem + TcSmem::STAGE0);
+      const tc::Oper wB = tc::make_oper(st0, st0 + TC_OPER_BYTES, TC_M * 16, 128, 2 * TC_M * 16);
       int it = 0;
       for (int j = 0; j < ntiles; ++j) {
         const int buf = j & 1;
@@ -240,11 +229,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
           const int s = it & 1;
           tc::mbar_wait(&full[s], (it >> 1) & 1);
           tc::fence_after_sync();
-          const uint32_t b_hi = tc::smem_u32(smem + TcSmem::STAGE0 + s * TC_STAGE_BYTES);
-          tc_issue_head(tmem_base + (buf * NHEADS + hd) * TC_N, a_hi, a_lo, b_hi, b_hi + TC_OPER_BYTES);
-          tc::mma_commit(&empty[s]);  // stage reusable once these MMAs have read it
+          if (leader) {
+            tc::Oper b = wB;
+            b.hi_lo += s * (TC_STAGE_BYTES >> 4);
+            b.lo_lo += s * (TC_STAGE_BYTES >> 4);
+            tc::mma3<TC_H / 16>(tmem_base + (buf * NHEADS + hd) * TC_N, hA, b, idesc, false);
+            tc::mma_commit(&empty[s]);  // stage reusable once these MMAs have read it
+          }
+          __syncwarp();
         }
-        tc::mma_commit(&tfull[buf]);  // accumulators of tile j complete
+        if (leader) tc::mma_commit(&tfull[buf]);  // accumulators of tile j complete
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {

@@ -47,22 +47,6 @@ __device__ __forceinline__ void tt_stage_h(const float* __restrict__ h, int64_t 
   }
 }
 
-// 3-MMA error-compensated product over `ksteps` K-steps of 16: D (+)= A * B with A, B as hi/lo blocks.
-// a_step / b_step = byte advance of the operand start address per K-step.
-__device__ __forceinline__ void tt_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t a_lbo, uint32_t a_sbo,
-                                        uint32_t a_step, uint32_t b_hi, uint32_t b_lo, uint32_t b_lbo, uint32_t b_sbo,
-                                        uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate) {
-  for (int ks = 0; ks < ksteps; ++ks) {
-    const uint64_t ah = tc::smem_desc(a_hi + ks * a_step, a_lbo, a_sbo);
-    const uint64_t al = tc::smem_desc(a_lo + ks * a_step, a_lbo, a_sbo);
-    const uint64_t bh = tc::smem_desc(b_hi + ks * b_step, b_lbo, b_sbo);
-    const uint64_t bl = tc::smem_desc(b_lo + ks * b_step, b_lbo, b_sbo);
-    tc::mma_f16_ss(d_tmem, ah, bh, idesc, (accumulate || ks > 0) ? 1u : 0u);
-    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1u);
-    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1u);
-  }
-}
-
 // =======================================================================================
 // Count operand of the training kernels.  XK selects how the resident matrix is read:
 //   XK_F32      fp32 counts, any value (generic per-element path: table or lgamma series, per element)
@@ -249,24 +233,47 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer
-    if (lane == 0 && ntiles > 0) {
+    // ===== MMA issuer: the warp runs the loop converged, one elected lane issues (tc.cuh, "MMA issue from a
+    // warp-uniform loop")
+    if (ntiles > 0) {
       constexpr uint32_t idescL = tc::idesc_f16_f32(TC_M, TC_NT, 0, 0);  // logits: 128 x 32, both K-major
       constexpr uint32_t idescO = tc::idesc_f16_f32(TC_M, TC_H, 0, 1);   // dh: 128 x 128, B MN-major
-      const uint32_t a_hi = tc::smem_u32(smem + L::H_HI), a_lo = tc::smem_u32(smem + L::H_LO);
+      const uint32_t leader = tc::elect_one();
       const uint32_t stg = tc::smem_u32(smem + L::STG);
+      const uint32_t w0 = tc::smem_u32(smem + L::W0);
+      // A = h tile, K-major (128 rows x 128 hidden): LBO = 128*16, SBO = 128, K-step = 2 chunks
+      const tc::Oper hA = tc::make_oper(tc::smem_u32(smem + L::H_HI), tc::smem_u32(smem + L::H_LO), TC_M * 16, 128, 2 * TC_M * 16);
+      // staged A blocks (K-major, 128 rows x 32 genes): LBO = 128*16, SBO = 128, K-step = 2 chunks
+      const tc::Oper sA1 = tc::make_oper(stg + 0 * TT_ABLK, stg + 1 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16);
+      const tc::Oper sA2 = tc::make_oper(stg + 2 * TT_ABLK, stg + 3 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16);
+      const tc::Oper sA3 = tc::make_oper(stg + 4 * TT_ABLK, stg + 5 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16);
+      // W blocks of weight stage 0 (stage 1 = + WSTAGE): as K-major B of the logits GEMM (N = 32 genes, K = hidden:
+      // LBO = 32*16, SBO = 128, K-step = 2 chunks) and as MN-major B of the dh GEMMs (N = hidden, K = genes:
+      // LBO = 128 (next 8 genes), SBO = 32*16, K-step = 256 B)
+      tc::Oper wL[NH], wO[NH];
+#pragma unroll
+      for (int hd = 0; hd < NH; ++hd) {
+        wL[hd] = tc::make_oper(w0 + hd * 2 * TC_BLK32, w0 + hd * 2 * TC_BLK32 + TC_BLK32, TC_NT * 16, 128, 2 * TC_NT * 16);
+        wO[hd] = tc::make_oper(w0 + hd * 2 * TC_BLK32, w0 + hd * 2 * TC_BLK32 + TC_BLK32, 128, TC_NT * 16, 256);
+      }
+      auto stage_of = [](const tc::Oper& o, int s) {  // the same blocks in weight stage s
+        tc::Oper r = o;
+        r.hi_lo += s * (L::WSTAGE >> 4);
+        r.lo_lo += s * (L::WSTAGE >> 4);
+        return r;
+      };
       auto issue_logits = [&](int j) {
         const int s = j & 1;
         tc::mbar_wait(&wfull[s], (j >> 1) & 1);
         tc::mbar_wait(&tempty[s], ((j >> 1) & 1) ^ 1);
         tc::fence_after_sync();
-        const uint32_t w = tc::smem_u32(smem + L::W0 + s * L::WSTAGE);
+        if (leader) {
 #pragma unroll
-        for (int hd = 0; hd < NH; ++hd)
-          tt_mma3(tmem_base + (s * 2 + hd) * TC_NT, a_hi, a_lo, TC_M * 16, 128, 2 * TC_M * 16,
-                  w + hd * 2 * TC_BLK32, w + hd * 2 * TC_BLK32 + TC_BLK32, TC_NT * 16, 128, 2 * TC_NT * 16, TC_H / 16,
-                  idescL, false);
-        tc::mma_commit(&tfull[s]);
+          for (int hd = 0; hd < NH; ++hd)
+            tc::mma3<TC_H / 16>(tmem_base + (s * 2 + hd) * TC_NT, hA, stage_of(wL[hd], s), idescL, false);
+          tc::mma_commit(&tfull[s]);
+        }
+        __syncwarp();
       };
       issue_logits(0);
       for (int j = 0; j < ntiles; ++j) {
@@ -274,20 +281,17 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
         const int s = j & 1;
         tc::mbar_wait(sfull, j & 1);
         tc::fence_after_sync();
-        const uint32_t w = tc::smem_u32(smem + L::W0 + s * L::WSTAGE);
-        // staged A blocks (K-major, 128 rows x 32 genes): LBO = 128*16, SBO = 128, K-step = 2 chunks
-        // W blocks as MN-major B (N = hidden, K = genes): LBO = 128 (next 8 genes), SBO = 32*16, K-step = 256 B
-        tt_mma3(ACC1, stg + 0 * TT_ABLK, stg + 1 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + TC_BLK32, 128,
-                TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
-        tt_mma3(ACC2, stg + 2 * TT_ABLK, stg + 3 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + TC_BLK32, 128,
-                TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
-        if (ZINB)
-          tt_mma3(ACC3, stg + 4 * TT_ABLK, stg + 5 * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16, w + 2 * TC_BLK32,
-                  w + 3 * TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
-        tc::mma_commit(sempty);      // staging buffers reusable
-        tc::mma_commit(&wempty[s]);  // weight stage reusable
+        if (leader) {
+          tc::mma3<TC_NT / 16>(ACC1, sA1, stage_of(wO[0], s), idescO, j > 0);
+          tc::mma3<TC_NT / 16>(ACC2, sA2, stage_of(wO[0], s), idescO, j > 0);
+          if (ZINB) tc::mma3<TC_NT / 16>(ACC3, sA3, stage_of(wO[NH - 1], s), idescO, j > 0);
+          tc::mma_commit(sempty);      // staging buffers reusable
+          tc::mma_commit(&wempty[s]);  // weight stage reusable
+        }
+        __syncwarp();
       }
-      tc::mma_commit(accfull);
+      if (leader) tc::mma_commit(accfull);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column group cg of 8 genes)
@@ -324,51 +328,41 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     // counts of this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
     // land during tile j's math, so the fence.proxy.async at the end of the tile (which drains this thread's
     // outstanding loads) never waits on them.
+    // counts of this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
+    // land during tile j's math, so the fence.proxy.async at the end of the tile (which drains this thread's
+    // outstanding loads) never waits on them.  (Measured and NOT kept, r02c / r02d: consuming tile j's counts
+    // before issuing tile j + 1's loads, and reading the logits of tile j + 1 out of TMEM before reporting tile
+    // j's staged operands -- 0.472 / 0.487 ms per step against 0.464: the epilogue is not what the tile waits on.)
     XRaw<XK> xcur, xnext;
     if (ntiles > 0) tt_load_x8<XK>(xrow, (int64_t)t0 * TC_NT + 8 * cg, G, rvalid, xvec, xcur);
-    // Logits of a tile are pulled out of TMEM one tile ahead, at the END of the previous tile and BEFORE this
-    // warp reports its staged operands: the dh MMAs that the report releases would otherwise occupy the tensor
-    // memory port while the next tile's tcgen05.ld waits behind them (16 % of K2's stall samples, r02c capture).
-    float sv[8], pv[8];
-    auto fetch_logits = [&](int jj) {
-      const int ss = jj & 1;
-      tc::mbar_wait(&tfull[ss], (jj >> 1) & 1);
-      tc::mbar_wait(&wfull[ss], (jj >> 1) & 1);  // acquire the bulk-copied gene constants of that tile too
-      tc::fence_after_sync();
-      tc::tmem_ld8(tmem_base + lane_sel + (ss * 2 + 0) * TC_NT + 8 * cg, sv);
-      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (ss * 2 + 1) * TC_NT + 8 * cg, pv);
-      tc::tmem_ld_wait();
-      tc::fence_before_sync();
-      __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&tempty[ss]);  // logits buffer drained
-    };
-    if (ntiles > 0) fetch_logits(0);
     for (int j = 0; j < ntiles; ++j) {
       const int s = j & 1;
-      // Consume this tile's counts BEFORE issuing the next tile's loads: the wait on their scoreboard then covers
-      // only loads that have had a whole tile to land.  (Issued the other way round, the new loads share the
-      // scoreboard and every tile pays a full DRAM latency -- 19 % of K2's stall samples in the r02b capture.)
-#pragma unroll
-      for (int i = 0; i < (int)(sizeof(xcur.w) / 4); ++i) asm volatile("" : "+r"(xcur.w[i]));
+      if (j + 1 < ntiles) tt_load_x8<XK>(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xnext);
       float xq[8];
       int xi[8];
       const bool lean = tt_prep_x8<XK>(xcur, xq, xi);
-      if (j + 1 < ntiles) tt_load_x8<XK>(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xnext);
+      tc::mbar_wait(&tfull[s], (j >> 1) & 1);
+      tc::mbar_wait(&wfull[s], (j >> 1) & 1);  // acquire the bulk-copied gene constants
+      tc::fence_after_sync();
+      float sv[8], pv[8];
+      tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 0) * TC_NT + 8 * cg, sv);
+      if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 1) * TC_NT + 8 * cg, pv);
+      tc::tmem_ld_wait();
+      tc::fence_before_sync();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty[s]);  // logits buffer drained
       const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
       const float* tab = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32 + TC_GC32_BYTES) +
                          8 * cg * fm::LGT;
+      float a1[8], a2[8], a3[8];
+      if (XK != XK_F32 && lean)
+        tt_k2_elems<ZINB, true>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
+      else
+        tt_k2_elems<ZINB, false>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
       uint4 hi1, lo1, hi2, lo2, hi3, lo3;
-      {
-        float a1[8], a2[8], a3[8];
-        if (XK != XK_F32 && lean)
-          tt_k2_elems<ZINB, true>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
-        else
-          tt_k2_elems<ZINB, false>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
-        tc::split8(a1, hi1, lo1);
-        tc::split8(a2, hi2, lo2);
-        if (ZINB) tc::split8(a3, hi3, lo3);
-      }
-      if (j + 1 < ntiles) fetch_logits(j + 1);
+      tc::split8(a1, hi1, lo1);
+      tc::split8(a2, hi2, lo2);
+      if (ZINB) tc::split8(a3, hi3, lo3);
       tc::mbar_wait(sempty, (j & 1) ^ 1);  // output MMAs of the previous tile have read the staging buffers
       const uint32_t off = cg * (TC_M * 16) + r * 16;
       *reinterpret_cast<uint4*>(stg + 0 * TT_ABLK + off) = hi1;
@@ -701,24 +695,45 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {  // warp-uniform issue loop (tc.cuh)
       constexpr uint32_t idescL = tc::idesc_f16_f32(TC_M, TC_NT, 0, 0);  // logits^T: 128 genes x 32 rows
       constexpr uint32_t idescO = tc::idesc_f16_f32(TC_M, TC_H, 0, 1);   // dW: 128 genes x 128 hidden, B MN-major
+      const uint32_t leader = tc::elect_one();
       const uint32_t wbase = tc::smem_u32(smem + L::W);
       const uint32_t stg = tc::smem_u32(smem + L::STG);
+      const uint32_t hst = tc::smem_u32(smem + L::HST);
+      // A of the logits^T GEMM = resident weight tile of head hd, K-major (128 genes x 128 hidden)
+      // A of the dW GEMM = staged ds^T / dp^T (K-major: 128 genes x 32 rows)
+      tc::Oper wA[NH], sA[NH];
+#pragma unroll
+      for (int hd = 0; hd < NH; ++hd) {
+        wA[hd] = tc::make_oper(wbase + hd * 2 * TC_OPER_BYTES, wbase + hd * 2 * TC_OPER_BYTES + TC_OPER_BYTES, TC_M * 16, 128,
+                               2 * TC_M * 16);
+        sA[hd] = tc::make_oper(stg + (hd * 2) * TT_ABLK, stg + (hd * 2 + 1) * TT_ABLK, TC_M * 16, 128, 2 * TC_M * 16);
+      }
+      // h tile of stage 0 (stage 1 = + TC_H32_STAGE_BYTES): K-major B of the logits^T GEMM (N = 32 rows, K = hidden)
+      // and MN-major B of the dW GEMM (N = hidden, K = rows)
+      const tc::Oper hL = tc::make_oper(hst, hst + TC_BLK32, TC_NT * 16, 128, 2 * TC_NT * 16);
+      const tc::Oper hO = tc::make_oper(hst, hst + TC_BLK32, 128, TC_NT * 16, 256);
+      auto stage_of = [](const tc::Oper& o, int s) {
+        tc::Oper r = o;
+        r.hi_lo += s * (TC_H32_STAGE_BYTES >> 4);
+        r.lo_lo += s * (TC_H32_STAGE_BYTES >> 4);
+        return r;
+      };
       tc::mbar_wait(wfull, 0);
       auto issue_logits = [&](int j) {
         const int s = j & 1;
         tc::mbar_wait(&hfull[s], (j >> 1) & 1);
         tc::mbar_wait(&tempty[s], ((j >> 1) & 1) ^ 1);
         tc::fence_after_sync();
-        const uint32_t hb = tc::smem_u32(smem + L::HST + s * TC_H32_STAGE_BYTES);
+        if (leader) {
 #pragma unroll
-        for (int hd = 0; hd < NH; ++hd)
-          tt_mma3(tmem_base + (s * 2 + hd) * TC_NT, wbase + hd * 2 * TC_OPER_BYTES,
-                  wbase + hd * 2 * TC_OPER_BYTES + TC_OPER_BYTES, TC_M * 16, 128, 2 * TC_M * 16, hb, hb + TC_BLK32,
-                  TC_NT * 16, 128, 2 * TC_NT * 16, TC_H / 16, idescL, false);
-        tc::mma_commit(&tfull[s]);
+          for (int hd = 0; hd < NH; ++hd)
+            tc::mma3<TC_H / 16>(tmem_base + (s * 2 + hd) * TC_NT, wA[hd], stage_of(hL, s), idescL, false);
+          tc::mma_commit(&tfull[s]);
+        }
+        __syncwarp();
       };
       issue_logits(0);
       for (int j = 0; j < ntiles; ++j) {
@@ -726,16 +741,17 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
         const int s = j & 1;
         tc::mbar_wait(sfull, j & 1);
         tc::fence_after_sync();
-        const uint32_t hb = tc::smem_u32(smem + L::HST + s * TC_H32_STAGE_BYTES);
-        // A = staged ds^T (K-major: 128 genes x 32 rows); B = h tile as MN-major (N = hidden, K = rows)
+        if (leader) {
 #pragma unroll
-        for (int hd = 0; hd < NH; ++hd)
-          tt_mma3(tmem_base + 128 + hd * TC_H, stg + (hd * 2) * TT_ABLK, stg + (hd * 2 + 1) * TT_ABLK, TC_M * 16, 128,
-                  2 * TC_M * 16, hb, hb + TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16, idescO, j > 0);
-        tc::mma_commit(sempty);
-        tc::mma_commit(&hempty[s]);
+          for (int hd = 0; hd < NH; ++hd)
+            tc::mma3<TC_NT / 16>(tmem_base + 128 + hd * TC_H, sA[hd], stage_of(hO, s), idescO, j > 0);
+          tc::mma_commit(sempty);
+          tc::mma_commit(&hempty[s]);
+        }
+        __syncwarp();
       }
-      tc::mma_commit(accfull);
+      if (leader) tc::mma_commit(accfull);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ===== epilogue: thread = (gene lane gl, row group rg of 8 rows)

@@ -28,20 +28,6 @@ constexpr int EN_NS = 4;                          // pipeline stages
 constexpr uint32_t EN_BLK = TC_M * TC_NT * 2;     // 128 x 32 fp16 block = 8 KB
 constexpr int EN_X_SCALE_LOG2 = 11;               // log1p(x) <= 16 -> < 2^15
 
-__device__ __forceinline__ void en_mma3(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, uint32_t a_lbo, uint32_t a_sbo,
-                                        uint32_t a_step, uint32_t b_hi, uint32_t b_lo, uint32_t b_lbo, uint32_t b_sbo,
-                                        uint32_t b_step, int ksteps, uint32_t idesc, bool accumulate) {
-  for (int ks = 0; ks < ksteps; ++ks) {
-    const uint64_t ah = tc::smem_desc(a_hi + ks * a_step, a_lbo, a_sbo);
-    const uint64_t al = tc::smem_desc(a_lo + ks * a_step, a_lbo, a_sbo);
-    const uint64_t bh = tc::smem_desc(b_hi + ks * b_step, b_lbo, b_sbo);
-    const uint64_t bl = tc::smem_desc(b_lo + ks * b_step, b_lbo, b_sbo);
-    tc::mma_f16_ss(d_tmem, ah, bh, idesc, (accumulate || ks > 0) ? 1u : 0u);
-    tc::mma_f16_ss(d_tmem, ah, bl, idesc, 1u);
-    tc::mma_f16_ss(d_tmem, al, bh, idesc, 1u);
-  }
-}
-
 // ---------------------------------------------------------------------------------------
 // pack We fp32 [128, ldw] -> per 32-gene K-tile {hi, lo} blocks, addr(n, kc) = kc * 2048 + n * 16
 // ---------------------------------------------------------------------------------------
@@ -190,19 +176,30 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {  // warp-uniform issue loop, one elected lane issues (tc.cuh)
       constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_H, 0, 0);
+      const uint32_t leader = tc::elect_one();
+      // stage 0 operands (stage 1 = + 2 * EN_BLK): A = converted log1p(x) tile, B = We K-tile; both K-major
+      // 128 x 32: LBO = 128*16, SBO = 128, K-step = 2 chunks
+      const uint32_t a0 = tc::smem_u32(smem + L::A), w0 = tc::smem_u32(smem + L::W);
+      const tc::Oper A0 = tc::make_oper(a0, a0 + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16);
+      const tc::Oper W0 = tc::make_oper(w0, w0 + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16);
       for (int j = 0; j < ntiles; ++j) {
         const int s = j & 1;
         tc::mbar_wait(&wfull[s], (j >> 1) & 1);
         tc::mbar_wait(&afull[s], (j >> 1) & 1);
         tc::fence_after_sync();
-        const uint32_t a = tc::smem_u32(smem + L::A + s * 2 * EN_BLK), w = tc::smem_u32(smem + L::W + s * 2 * EN_BLK);
-        en_mma3(tmem_base, a, a + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16, w, w + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16,
-                TC_NT / 16, idesc, j > 0);
-        tc::mma_commit(&empty[s]);
+        if (leader) {
+          tc::Oper a = A0, w = W0;
+          a.hi_lo += s * ((2 * EN_BLK) >> 4); a.lo_lo += s * ((2 * EN_BLK) >> 4);
+          w.hi_lo += s * ((2 * EN_BLK) >> 4); w.lo_lo += s * ((2 * EN_BLK) >> 4);
+          tc::mma3<TC_NT / 16>(tmem_base, a, w, idesc, j > 0);
+          tc::mma_commit(&empty[s]);
+        }
+        __syncwarp();
       }
-      tc::mma_commit(accfull);
+      if (leader) tc::mma_commit(accfull);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ===== converters: thread = (row r, chunk cg of 8 genes inside each 32-gene K-tile)
@@ -463,20 +460,30 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && ntiles > 0) {
+    if (ntiles > 0) {  // warp-uniform issue loop, one elected lane issues (tc.cuh)
       // D[128 hidden, 128 genes] += dy^T (MN-major A) * log1p(x)^T (MN-major B); K = 32 rows per tile
       constexpr uint32_t idesc = tc::idesc_f16_f32(TC_M, TC_M, 1, 1);
+      const uint32_t leader = tc::elect_one();
+      // stage 0 operands (stage s = + s * 2 * EN_BLK): MN-major 32 x 128 blocks: LBO = 128, SBO = 32*16, K-step 256 B
+      const uint32_t a0 = tc::smem_u32(smem + L::A), b0 = tc::smem_u32(smem + L::W);
+      const tc::Oper A0 = tc::make_oper(a0, a0 + TC_BLK32, 128, TC_NT * 16, 256);
+      const tc::Oper B0 = tc::make_oper(b0, b0 + TC_BLK32, 128, TC_NT * 16, 256);
       for (int j = 0; j < ntiles; ++j) {
         const int s = j % EN_NS;
         tc::mbar_wait(&dfull[s], (j / EN_NS) & 1);
         tc::mbar_wait(&xfull[s], (j / EN_NS) & 1);
         tc::fence_after_sync();
-        const uint32_t a = tc::smem_u32(smem + L::A + s * 2 * EN_BLK), b = tc::smem_u32(smem + L::W + s * 2 * EN_BLK);
-        en_mma3(tmem_base, a, a + TC_BLK32, 128, TC_NT * 16, 256, b, b + TC_BLK32, 128, TC_NT * 16, 256, TC_NT / 16,
-                idesc, j > 0);
-        tc::mma_commit(&empty[s]);
+        if (leader) {
+          tc::Oper a = A0, b = B0;
+          a.hi_lo += s * ((2 * EN_BLK) >> 4); a.lo_lo += s * ((2 * EN_BLK) >> 4);
+          b.hi_lo += s * ((2 * EN_BLK) >> 4); b.lo_lo += s * ((2 * EN_BLK) >> 4);
+          tc::mma3<TC_NT / 16>(tmem_base, a, b, idesc, j > 0);
+          tc::mma_commit(&empty[s]);
+        }
+        __syncwarp();
       }
-      tc::mma_commit(accfull);
+      if (leader) tc::mma_commit(accfull);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ===== converters: thread = (row r of the 32-row tile = lane, chunk gc of 8 genes = warp - 4)

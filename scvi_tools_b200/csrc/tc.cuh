@@ -91,6 +91,62 @@ __device__ __forceinline__ void mma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uin
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// ---- MMA issue from a warp-uniform loop ---------------------------------------------------------------
+// The issuing WARP runs its loop converged (all 32 lanes wait on the mbarriers), one lane elected once issues
+// the MMAs inside `if (leader) { ... }`, and descriptors are passed as two 32-bit words whose low word only
+// needs an integer add to advance the start address.  ptxas then keeps every operand on the uniform datapath:
+// ~3 instructions per MMA (two UMOV + UTCHMMA).  Issued the old way -- inside an `if (lane == 0)` region with
+// 64-bit descriptors rebuilt per MMA -- every MMA sat in its own ELECT / BRA.U.ANY waterfall loop behind ~8
+// dependent uniform-pipe ops: ~70 cycles per MMA, which made the single issuing thread the critical path of the
+// fused decoder kernels (66 MMAs per 32-gene tile ~ 4.3k cycles, measured 2.2 us per tile; r02c capture).
+__device__ __forceinline__ uint32_t elect_one() {  // call with the warp converged; exactly one lane gets 1
+  uint32_t pred = 0;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.b32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+  return pred;
+}
+// descriptor words: lo = start address (>> 4, 14 bits) | LBO (>> 4) << 16;  hi = SBO (>> 4) | version 1 (bit 46)
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__host__ __device__ constexpr uint32_t desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+__device__ __forceinline__ void mma_f16_ss2(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// One operand of the error-compensated product: its fp16 `hi` and `lo` blocks share LBO / SBO and the K-step.
+struct Oper {
+  uint32_t hi_lo, lo_lo;  // low descriptor words of the hi block and of the lo block
+  uint32_t dhi;           // high descriptor word (SBO, version)
+  uint32_t step;          // advance of the start-address field per K-step of 16 (bytes >> 4)
+};
+__device__ __forceinline__ Oper make_oper(uint32_t hi_addr, uint32_t lo_addr, uint32_t lbo, uint32_t sbo, uint32_t step_bytes) {
+  Oper o;
+  o.hi_lo = desc_lo(hi_addr, lbo);
+  o.lo_lo = desc_lo(lo_addr, lbo);
+  o.dhi = desc_hi(sbo);
+  o.step = step_bytes >> 4;
+  return o;
+}
+// D (+)= A * B over KS K-steps of 16 with the 3-MMA split  hi*hi + hi*lo + lo*hi.  Call inside `if (leader)`.
+template <int KS>
+__device__ __forceinline__ void mma3(uint32_t d_tmem, const Oper& a, const Oper& b, uint32_t idesc, bool accumulate) {
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    const uint32_t ah = a.hi_lo + ks * a.step, al = a.lo_lo + ks * a.step;
+    const uint32_t bh = b.hi_lo + ks * b.step, bl = b.lo_lo + ks * b.step;
+    mma_f16_ss2(d_tmem, ah, a.dhi, bh, b.dhi, idesc, (accumulate || ks > 0) ? 1u : 0u);
+    mma_f16_ss2(d_tmem, ah, a.dhi, bl, b.dhi, idesc, 1u);
+    mma_f16_ss2(d_tmem, al, a.dhi, bh, b.dhi, idesc, 1u);
+  }
+}
+
 // mbarrier arrives when all tcgen05 ops issued so far by this thread have completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
