@@ -123,6 +123,18 @@ __device__ __forceinline__ bool tt_prep_x8(const XRaw<XK>& d, float (&xq)[8], in
 }
 static_assert(fm::LGT == 64 && fm::DGT <= 64, "tt_prep_x8 tests counts against 64");
 
+#ifdef SCVI_K2_TRACE
+// Debug build only (make NVFLAGS+=-DSCVI_K2_TRACE): clock64 stamps of CTA (0,0) -- epilogue warp 4, epilogue warp 19
+// and the MMA-issuing warp -- per tile, fetched with scvi_debug_k2_trace (tools/k2_trace.py).
+__device__ long long g_k2_trace[3 * 64 * 8];
+#define K2_TR(who, j, slot)                                                                      \
+  do {                                                                                           \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && lane == 0 && (j) < 64) g_k2_trace[((who) * 64 + (j)) * 8 + (slot)] = clock64(); \
+  } while (0)
+#else
+#define K2_TR(who, j, slot) do {} while (0)
+#endif
+
 // =======================================================================================
 // K2: fused NLL + dh
 // =======================================================================================
@@ -279,7 +291,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       for (int j = 0; j < ntiles; ++j) {
         if (j + 1 < ntiles) issue_logits(j + 1);
         const int s = j & 1;
+        K2_TR(2, j, 0);
         tc::mbar_wait(sfull, j & 1);
+        K2_TR(2, j, 1);
         tc::fence_after_sync();
         if (leader) {
           tc::mma3<TC_NT / 16>(ACC1, sA1, stage_of(wO[0], s), idescO, j > 0);
@@ -289,6 +303,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
           tc::mma_commit(&wempty[s]);  // weight stage reusable
         }
         __syncwarp();
+        K2_TR(2, j, 2);
       }
       if (leader) tc::mma_commit(accfull);
       __syncwarp();
@@ -330,24 +345,37 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
     // outstanding loads) never waits on them.
     // counts of this thread's 8 genes of a tile.  The loads for tile j + 1 are issued at the top of tile j: they
     // land during tile j's math, so the fence.proxy.async at the end of the tile (which drains this thread's
-    // outstanding loads) never waits on them.  (Measured and NOT kept, r02c / r02d: consuming tile j's counts
-    // before issuing tile j + 1's loads, and reading the logits of tile j + 1 out of TMEM before reporting tile
-    // j's staged operands -- 0.472 / 0.487 ms per step against 0.464: the epilogue is not what the tile waits on.)
+    // outstanding loads) never waits on them.  The first use of tile j's counts right behind the issue of tile
+    // j + 1's loads does wait for those too (one scoreboard): ~1200 cycles per tile in the clock64 trace
+    // (SCVI_K2_TRACE, tools/k2_trace.py).  Consuming the counts first removes that wait but not a cycle of the
+    // tile period (6400 cycles either way: the math phase stretches from ~3000 to ~3800 cycles, r02f trace) --
+    // the warps of a scheduler then run their dependent MUFU chains in phase instead of staggered.  Also measured
+    // and not kept: reading tile j + 1's logits out of TMEM before reporting tile j's staged operands (0.487 ms
+    // per step against 0.464).
     XRaw<XK> xcur, xnext;
     if (ntiles > 0) tt_load_x8<XK>(xrow, (int64_t)t0 * TC_NT + 8 * cg, G, rvalid, xvec, xcur);
     for (int j = 0; j < ntiles; ++j) {
       const int s = j & 1;
+      const int trw = warp == 4 ? 0 : warp == 19 ? 1 : 3;
+      if (trw < 3) K2_TR(trw, j, 6);
       if (j + 1 < ntiles) tt_load_x8<XK>(xrow, (int64_t)(t0 + j + 1) * TC_NT + 8 * cg, G, rvalid, xvec, xnext);
+      if (trw < 3) K2_TR(trw, j, 7);
       float xq[8];
       int xi[8];
       const bool lean = tt_prep_x8<XK>(xcur, xq, xi);
+#ifdef SCVI_K2_TRACE
+      asm volatile("" ::"f"(xq[0]), "f"(xq[7]) : "memory");
+#endif
+      if (trw < 3) K2_TR(trw, j, 0);
       tc::mbar_wait(&tfull[s], (j >> 1) & 1);
       tc::mbar_wait(&wfull[s], (j >> 1) & 1);  // acquire the bulk-copied gene constants
+      if (trw < 3) K2_TR(trw, j, 1);
       tc::fence_after_sync();
       float sv[8], pv[8];
       tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 0) * TC_NT + 8 * cg, sv);
       if (ZINB) tc::tmem_ld8(tmem_base + lane_sel + (s * 2 + 1) * TC_NT + 8 * cg, pv);
       tc::tmem_ld_wait();
+      if (trw < 3) K2_TR(trw, j, 2);
       tc::fence_before_sync();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&tempty[s]);  // logits buffer drained
@@ -363,7 +391,12 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::split8(a1, hi1, lo1);
       tc::split8(a2, hi2, lo2);
       if (ZINB) tc::split8(a3, hi3, lo3);
+#ifdef SCVI_K2_TRACE
+      asm volatile("" ::"r"(hi1.x), "r"(lo2.w), "r"(hi3.y) : "memory");  // the math is done before the stamp
+#endif
+      if (trw < 3) K2_TR(trw, j, 3);
       tc::mbar_wait(sempty, (j & 1) ^ 1);  // output MMAs of the previous tile have read the staging buffers
+      if (trw < 3) K2_TR(trw, j, 4);
       const uint32_t off = cg * (TC_M * 16) + r * 16;
       *reinterpret_cast<uint4*>(stg + 0 * TT_ABLK + off) = hi1;
       *reinterpret_cast<uint4*>(stg + 1 * TT_ABLK + off) = lo1;
@@ -374,6 +407,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
         *reinterpret_cast<uint4*>(stg + 5 * TT_ABLK + off) = lo3;
       }
       tc::fence_proxy_async_smem();
+      if (trw < 3) K2_TR(trw, j, 5);
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(sfull);
       xcur = xnext;
@@ -1002,3 +1036,9 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
 }
 
 }  // namespace scvi
+
+#ifdef SCVI_K2_TRACE
+extern "C" int scvi_debug_k2_trace(long long* host_out, int n) {
+  return (int)cudaMemcpyFromSymbol(host_out, scvi::g_k2_trace, sizeof(long long) * (size_t)n);
+}
+#endif
