@@ -439,6 +439,11 @@ def run_b200_arm(a):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (this arm has no CPU fallback)")
+    # stdout carries ONE JSON line: anything a library prints on fd 1 meanwhile (NCCL's version banner ignores
+    # NCCL_DEBUG_FILE on some builds) goes to stderr; fd 1 is restored right before the line is printed
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     pg = None
@@ -680,6 +685,8 @@ def run_b200_arm(a):
             "roofline": roof, "kernels": kern, "nb_loss_kernel_hbm": logprob, "cpu_baseline": cpu,
             "final_loss": loss_end, "also": extras,
         }
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     if line is not None:
         print(json.dumps(line), flush=True)
     if world > 1:
