@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--ddp-mode", default="p2p", choices=["p2p", "graph", "overlap", "split"],
                     help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode): p2p = this library's fused "
                          "all-reduce + Adam over NVLink peer memory, the others = NCCL routes")
+    ap.add_argument("--p2p-buckets", type=int, default=0, help="FusedTrainingPlan.p2p_buckets (ddp-mode p2p)")
     ap.add_argument("--blocks", type=int, default=5,
                     help="the timed region is repeated this many times (each EXACTLY --steps steps between "
                          "barrier + synchronize); ms_per_step is the median block")
@@ -65,6 +66,8 @@ def parse():
     ap.add_argument("--e2e-dtype", default="auto", choices=["auto", "u16", "f32"],
                     help="host count type of the e2e leg: auto = narrowest lossless (uint8 / uint16 / float32)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--value-only", action="store_true",
+                    help="tuning aid: time the resident-counts step only (no e2e / roofline / baseline legs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     return ap.parse_args()
 
@@ -405,7 +408,8 @@ def make_plan(a, data, B, pg, genes=None, likelihood=None, batches=None, seed=0)
     torch.manual_seed(seed)
     m = S.VAE(n_input=genes or a.genes, n_batch=batches or a.batches, gene_likelihood=likelihood or a.likelihood,
               n_hidden=N_HIDDEN, n_latent=N_LATENT, precision=1 if a.precision == "tc" else 0).train()
-    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True, ddp_mode=a.ddp_mode)
+    plan = FusedTrainingPlan(m, data, batch_size=B, process_group=pg, use_cuda_graph=True, ddp_mode=a.ddp_mode,
+                             p2p_buckets=a.p2p_buckets)
     plan.set_epoch(0)
     return plan
 
@@ -504,6 +508,22 @@ def run_b200_arm(a):
         del solo
         if not same:
             print("bench.py: replicas diverged", file=sys.stderr)
+
+    if a.value_only:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        if rank == 0:
+            print(json.dumps({"metric": "SCVI train cells/sec", "value": value, "unit": "cells/s", "n_gpus": world,
+                              "steps": K, "warmup": W, "ms_per_step": ms / K, "config": config_dict(a, world),
+                              "blocks_ms": blocks_ms, "ddp_check": ddp, "clocks": clocks, "partial": "value-only"}),
+                  flush=True)
+        if world > 1:
+            plan._graphs = None
+            torch.cuda.synchronize()
+            torch.distributed.barrier()
+            sys.stdout.flush()
+            os._exit(0)
+        return
 
     # ---- end to end (A): counts stay in pinned HOST memory (the whole matrix, narrowest lossless integer type);
     # every step submits its random row ids, the rows cross PCIe inside the timed region (gathered by the GPU

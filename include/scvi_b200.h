@@ -377,6 +377,15 @@ int scvi_allreduce_adam(const void* const* peer_g, void* const* peer_ctrl, int w
                         float* p, float* m, float* v, float* g_sum, int64_t begin, int64_t end,
                         int64_t* step_counter, int advance_counter, float lr, float beta1, float beta2,
                         float eps, float weight_decay, int blocks, void* stream);
+/* Sharded form of the same exchange (one launch at the end of the step): rank r reduces the r-th 1/world slice of
+ * the gradient arena (rank order), applies Adam to it with its own moments and stores the updated PARAMETERS into
+ * every rank's parameter arena peer_p[*] (the parameter arenas live in the exchange segments too); arrival barrier
+ * on flags `slot`, completion barrier on flags `slot + 1`: when the call's kernel ends, peer_p[rank] holds every
+ * slice.  (N-1)/N of the arena read and written per rank instead of N-1 arenas read; replicas bit-identical by
+ * construction.  m / v are only maintained for the rank's own slice.  n = arena floats (multiple of 4). */
+int scvi_allreduce_adam_sharded(const void* const* peer_g, void* const* peer_p, void* const* peer_ctrl, int world,
+                                int rank, int slot, float* m, float* v, int64_t n, int64_t* step_counter, float lr,
+                                float beta1, float beta2, float eps, float weight_decay, int blocks, void* stream);
 
 #ifdef __cplusplus
 }

@@ -76,6 +76,7 @@ SIGNATURES = {
     "scvi_comm_close": (C.c_int, [P]),
     "scvi_comm_free": (C.c_int, [P]),
     "scvi_allreduce_adam": (C.c_int, [P, P, I32, I32, I32, P, P, P, P, I64, I64, P, I32, F32, F32, F32, F32, F32, I32, P]),
+    "scvi_allreduce_adam_sharded": (C.c_int, [P, P, P, I32, I32, I32, P, P, I64, P, F32, F32, F32, F32, F32, I32, P]),
     "scvi_elbo_reduce": (C.c_int, [P, P, I64, F32, P, P, P]),
     "scvi_elbo_seed": (C.c_int, [I64, F32, P, F32, P, P, P]),
     "scvi_step_prologue": (C.c_int, [C.c_uint64, P, I64, I64, I64, I64, F32, P, P, P, P, P, F32, P, F32, P, P, P, P, P]),

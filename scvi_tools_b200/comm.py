@@ -39,7 +39,7 @@ class PeerGradientExchange:
         self.dev = torch.device(device)
         self.n = int(n_floats)
         self.arena_bytes = (self.n * 4 + 255) // 256 * 256
-        self.ctrl_off = 2 * self.arena_bytes
+        self.ctrl_off = 3 * self.arena_bytes  # [g parity 0][g parity 1][parameters][control block]
         self.nbytes = self.ctrl_off + int(query("scvi_comm_ctrl_bytes"))
         self.base = None
         self.peers: list[int] = []
@@ -77,8 +77,11 @@ class PeerGradientExchange:
         raw = torch.as_tensor(_RawCuda(self.base, self.nbytes), device=self.dev)
         self._raw = raw
         self.g = [raw[i * self.arena_bytes : i * self.arena_bytes + self.n * 4].view(torch.float32) for i in (0, 1)]
+        # the parameter arena of the plan lives here as well: the sharded exchange stores updated slices into it
+        self.p = raw[2 * self.arena_bytes : 2 * self.arena_bytes + self.n * 4].view(torch.float32)
         PV = C.c_void_p * self.world
         self._peer_g = [PV(*[p + i * self.arena_bytes for p in self.peers]) for i in (0, 1)]
+        self._peer_p = PV(*[p + 2 * self.arena_bytes for p in self.peers])
         self._peer_ctrl = PV(*[p + self.ctrl_off for p in self.peers])
         dist.barrier(group=process_group)  # nobody launches before every rank has opened every segment
 
@@ -88,6 +91,19 @@ class PeerGradientExchange:
              C.c_void_p(p.data_ptr()), C.c_void_p(m.data_ptr()), C.c_void_p(v.data_ptr()),
              None if g_sum is None else C.c_void_p(g_sum.data_ptr()), begin, end, C.c_void_p(step_counter.data_ptr()),
              1 if advance else 0, lr, beta1, beta2, eps, wd, blocks, stream)
+
+    def allreduce_adam_sharded(self, parity: int, slot: int, m, v, step_counter, lr, beta1, beta2, eps, wd, stream,
+                               blocks: int = 0):
+        call("scvi_allreduce_adam_sharded", self._peer_g[parity], self._peer_p, self._peer_ctrl, self.world, self.rank,
+             slot, C.c_void_p(m.data_ptr()), C.c_void_p(v.data_ptr()), self.n, C.c_void_p(step_counter.data_ptr()),
+             lr, beta1, beta2, eps, wd, blocks, stream)
+
+    def shard_bounds(self):
+        """[lo, hi) in floats of the slice whose parameters / Adam moments this rank maintains (sharded exchange)."""
+        n4 = self.n // 4
+        chunk = (n4 + self.world - 1) // self.world
+        lo = min(self.rank * chunk, n4)
+        return 4 * lo, 4 * min(lo + chunk, n4)
 
     def close(self):
         """Unmap the peers' segments and free this rank's (call after a barrier + synchronize)."""
@@ -99,6 +115,7 @@ class PeerGradientExchange:
                     pass
         self.peers = []
         self.g = None
+        self.p = None
         self._raw = None
         if self.base:
             call("scvi_comm_free", C.c_void_p(self.base))

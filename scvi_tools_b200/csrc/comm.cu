@@ -144,6 +144,122 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// Sharded variant (reduce-scatter + Adam + all-gather of the PARAMETERS in one launch): rank r owns the r-th
+// slice of the arena, sums that slice over all ranks' gradient buffers (rank order), applies Adam to it with
+// its own moments, and writes the updated parameters into EVERY rank's parameter arena (which therefore lives
+// in the peer-mapped segment too).  Per rank and step: (N-1)/N of the arena read and as much written over
+// NVLink, against (N-1) whole arenas read by the one-shot kernel above -- 2.7 MB each way instead of 21.7 MB at
+// N = 8 -- and 1/N of the Adam work.  Every parameter is produced by exactly one rank with the arithmetic of the
+// single-process step, so the replicas stay bit-identical by construction.  The moments of the other slices are
+// not maintained on this rank.
+// Protocol (slots s = arrival, s + 1 = completion):
+//   1. arrival barrier as above: every rank has finished its backward, so nobody still READS parameters;
+//   2. own slice: reduce, Adam, store p to all ranks;
+//   3. the last block to finish fences (system scope), signals completion to every rank and waits for every
+//      rank's completion signal: when the kernel ends, this rank's parameter arena holds every slice.
+// ---------------------------------------------------------------------------------------
+struct PeerParams {
+  float* p[COMM_MAX_PEERS];
+};
+
+__global__ void __launch_bounds__(256)
+    allreduce_adam_sharded_kernel(PeerTable pt, PeerParams pp, int world, int rank, int slot, float* __restrict__ m,
+                                  float* __restrict__ v, int64_t n, int64_t* step_counter, float lr, float beta1,
+                                  float beta2, float eps, float wd, float grad_scale) {
+  __shared__ int s_fail;
+  unsigned long long* my = pt.ctrl[rank];
+  const unsigned long long seq = *reinterpret_cast<volatile unsigned long long*>(my + COMM_SEQ + 2 * slot) + 1ull;
+  if (threadIdx.x == 0) s_fail = 0;
+  if (blockIdx.x == 0 && threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(pt.ctrl[threadIdx.x] + COMM_FLAGS + slot * COMM_MAX_PEERS + rank, seq);
+  }
+  __syncthreads();
+  if (threadIdx.x < world) {
+    const unsigned long long* f = my + COMM_FLAGS + slot * COMM_MAX_PEERS + threadIdx.x;
+    unsigned spins = 0;
+    while (ld_acquire_sys(f) < seq) {
+      __nanosleep(32);
+      if (++spins > (1u << 26)) {
+        s_fail = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  if (s_fail) {
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+      printf("scvi_b200: gradient exchange timed out (rank %d, slot %d, launch %llu)\n", rank, slot, seq);
+    __trap();
+  }
+  const int64_t step = *reinterpret_cast<volatile int64_t*>(step_counter) + 1;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  const float step_size = (float)((double)lr / bc1);
+  const float bc2_sqrt = (float)sqrt(bc2);
+  const int64_t n4 = n >> 2;  // the arena is padded to a multiple of 4 floats
+  const int64_t chunk = (n4 + world - 1) / world;
+  const int64_t lo = min((int64_t)rank * chunk, n4), hi = min(lo + chunk, n4);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  float* p_own = pp.p[rank];
+  for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    const int64_t e = 4 * i;
+    float4 part[COMM_MAX_PEERS];
+#pragma unroll
+    for (int r = 0; r < COMM_MAX_PEERS; ++r)
+      if (r < world) part[r] = ld_relaxed_sys4(pt.g[r] + e);
+    float4 gg = part[0];
+#pragma unroll
+    for (int r = 1; r < COMM_MAX_PEERS; ++r)
+      if (r < world) {
+        gg.x += part[r].x; gg.y += part[r].y; gg.z += part[r].z; gg.w += part[r].w;
+      }
+    float4 q = *reinterpret_cast<float4*>(p_own + e);
+    float4 mm = *reinterpret_cast<float4*>(m + e);
+    float4 vv = *reinterpret_cast<float4*>(v + e);
+    adam_update(q.x, gg.x, mm.x, vv.x, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_update(q.y, gg.y, mm.y, vv.y, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_update(q.z, gg.z, mm.z, vv.z, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    adam_update(q.w, gg.w, mm.w, vv.w, grad_scale, wd, beta1, beta2, step_size, bc2_sqrt, eps);
+    *reinterpret_cast<float4*>(m + e) = mm;
+    *reinterpret_cast<float4*>(v + e) = vv;
+#pragma unroll
+    for (int r = 0; r < COMM_MAX_PEERS; ++r)
+      if (r < world) *reinterpret_cast<float4*>(pp.p[r] + e) = q;
+  }
+  // ---- completion: last block of this rank signals, then waits for every rank's signal
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();  // this block's parameter stores are visible system-wide before the ticket
+    unsigned long long* ticket = my + COMM_SEQ + 2 * slot + 1;
+    if (atomicAdd(ticket, 1ull) == (unsigned long long)gridDim.x - 1) {
+      __threadfence_system();
+      for (int r = 0; r < world; ++r)
+        st_release_sys(pt.ctrl[r] + COMM_FLAGS + (slot + 1) * COMM_MAX_PEERS + rank, seq);
+      bool ok = true;
+      for (int r = 0; r < world && ok; ++r) {
+        const unsigned long long* f = my + COMM_FLAGS + (slot + 1) * COMM_MAX_PEERS + r;
+        unsigned spins = 0;
+        while (ld_acquire_sys(f) < seq) {
+          __nanosleep(32);
+          if (++spins > (1u << 26)) {
+            ok = false;
+            break;
+          }
+        }
+      }
+      *ticket = 0ull;
+      my[COMM_SEQ + 2 * slot] = seq;
+      step_counter[0] = step;
+      if (!ok) {
+        printf("scvi_b200: parameter exchange timed out (rank %d, launch %llu)\n", rank, seq);
+        __trap();
+      }
+    }
+  }
+}
+
 }  // namespace scvi
 
 extern "C" {
@@ -226,6 +342,34 @@ int scvi_allreduce_adam(const void* const* peer_g, void* const* peer_ctrl, int w
                                                                       step_counter, advance_counter, lr, beta1, beta2,
                                                                       eps, weight_decay, 1.f / (float)world);
   SCVI_LAUNCH_CHECK("scvi_allreduce_adam");
+  return SCVI_OK;
+}
+
+int scvi_allreduce_adam_sharded(const void* const* peer_g, void* const* peer_p, void* const* peer_ctrl, int world,
+                                int rank, int slot, float* m, float* v, int64_t n, int64_t* step_counter, float lr,
+                                float beta1, float beta2, float eps, float weight_decay, int blocks, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(peer_g && peer_p && peer_ctrl && world >= 1 && world <= COMM_MAX_PEERS && rank >= 0 && rank < world,
+               "scvi_allreduce_adam_sharded: world must be 1..%d", COMM_MAX_PEERS);
+  SCVI_REQUIRE(slot >= 0 && slot + 1 < COMM_SLOTS, "scvi_allreduce_adam_sharded: slot must be 0..%d", COMM_SLOTS - 2);
+  SCVI_REQUIRE(m && v && step_counter && n >= 0 && n % 4 == 0,
+               "scvi_allreduce_adam_sharded: bad argument (n must be a multiple of 4 floats)");
+  PeerTable pt{};
+  PeerParams pp{};
+  for (int r = 0; r < world; ++r) {
+    SCVI_REQUIRE(peer_g[r] && peer_p[r] && peer_ctrl[r] && ((uintptr_t)peer_g[r] % 16 == 0) && ((uintptr_t)peer_p[r] % 16 == 0),
+                 "scvi_allreduce_adam_sharded: bad peer pointer %d", r);
+    pt.g[r] = (const float*)peer_g[r];
+    pt.ctrl[r] = (unsigned long long*)peer_ctrl[r];
+    pp.p[r] = (float*)peer_p[r];
+  }
+  const int64_t chunk = cdiv(std::max<int64_t>(n / 4, 1), world);
+  int64_t nb = blocks > 0 ? blocks : 148 * 2;
+  nb = std::max<int64_t>(1, std::min<int64_t>(nb, cdiv(chunk, 256)));
+  allreduce_adam_sharded_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(pt, pp, world, rank, slot, m, v, n, step_counter, lr,
+                                                                               beta1, beta2, eps, weight_decay,
+                                                                               1.f / (float)world);
+  SCVI_LAUNCH_CHECK("scvi_allreduce_adam_sharded");
   return SCVI_OK;
 }
 }

@@ -69,7 +69,7 @@ class FusedTrainingPlan:
                  eps: float = 0.01, weight_decay: float = 1e-6, betas=(0.9, 0.999),
                  n_epochs_kl_warmup: int | None = 400, n_steps_kl_warmup: int | None = None,
                  max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, seed: int = 0,
-                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "p2p"):
+                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "p2p", p2p_buckets: int = 0):
         m = module
         self._check_supported(m)
         self.module, self.data = m, data
@@ -101,6 +101,12 @@ class FusedTrainingPlan:
                 self.exchange, ddp_mode = None, "split"
         self.ddp_mode = ddp_mode
         self.ddp_overlap = ddp_mode == "overlap"
+        # "p2p": 0 (default) = sharded: one launch at the end of the step in which every rank reduces + updates
+        # 1/world of the arena and stores the new parameters into all replicas (csrc/comm.cu); 1 = one launch,
+        # every rank reduces the whole arena (one-shot); 2 = one-shot in two buckets, the decoder-head bucket on
+        # a side stream under the rest of the backward.  Measured on 2 B200 (tools/ddp_modes.sh): 2 buckets
+        # 0.477, 1 bucket 0.467, NCCL routes 0.491-0.497 ms per step against 0.452 on one GPU.
+        self.p2p_buckets = int(p2p_buckets)
         self._n_exec = 0  # whole steps executed so far: its low bit selects the gradient buffer (p2p double buffer)
         self.zinb = m.gene_likelihood == "zinb"
         self.dev = data.X.device
@@ -126,6 +132,15 @@ class FusedTrainingPlan:
         if self.exchange is not None:
             torch.cuda.synchronize()
             torch.distributed.barrier(group=self.pg)
+            # the module's parameters move out of the segment before it is freed
+            new_p = self.p.clone()
+            named = dict(self.module.named_parameters())
+            offs = self._arena_layout(self.module)[2]
+            for k in self.keys:
+                view = new_p[offs[k] : offs[k] + named[k].numel()].view(named[k].shape)
+                named[k].data = view
+                self.P[k] = view
+            self.p = new_p
             self._g2, self._Gd2 = [], []
             self.exchange.close()
             self.exchange = None
@@ -178,7 +193,7 @@ class FusedTrainingPlan:
         self.keys = keys
         self.n_arena = off
         dev = self.dev
-        self.p = torch.zeros(off, dtype=torch.float32, device=dev)
+        self.p = self.exchange.p.zero_() if self.exchange is not None else torch.zeros(off, dtype=torch.float32, device=dev)
         # gradient arena(s): inside the peer-mapped exchange segment, one per step parity, under "p2p"
         self._g2 = self.exchange.g if self.exchange is not None else [torch.zeros(off, dtype=torch.float32, device=dev)]
         self.m = torch.zeros(off, dtype=torch.float32, device=dev)
@@ -402,7 +417,7 @@ class FusedTrainingPlan:
         """Between the decoder-head backward and the rest: under data parallelism the head gradients (the first
         `n_head` floats of the arena) are exchanged here, on a side stream, under the rest of the backward --
         "p2p": fused peer-memory all-reduce + Adam of that bucket; "overlap": its ncclAllReduce."""
-        if self.world == 1 or not (self.exchange is not None or self.ddp_overlap):
+        if self.world == 1 or not ((self.exchange is not None and self.p2p_buckets > 1) or self.ddp_overlap):
             return
         main = torch.cuda.current_stream()
         self._ev_heads_ready.record(main)
@@ -431,9 +446,16 @@ class FusedTrainingPlan:
         """The optimizer step; under "p2p" the remaining bucket's fused all-reduce + Adam (which also advances the
         step counter), after the head bucket's kernel on the side stream has finished."""
         parity = self._parity() if parity is None else parity
+        if self.exchange is not None and self.world > 1 and self.p2p_buckets == 0:
+            self.exchange.allreduce_adam_sharded(parity, 2, self.m, self.v, self.step_counter, self.lr, self.betas[0],
+                                                 self.betas[1], self.eps, self.wd, st)
+            return
         if self.exchange is not None and self.world > 1:
-            torch.cuda.current_stream().wait_event(self._ev_heads_reduced)
-            self.exchange.allreduce_adam(parity, 1, self.p, self.m, self.v, self.n_head, self.n_arena,
+            begin = 0
+            if self.p2p_buckets > 1:
+                torch.cuda.current_stream().wait_event(self._ev_heads_reduced)
+                begin = self.n_head
+            self.exchange.allreduce_adam(parity, 1, self.p, self.m, self.v, begin, self.n_arena,
                                          self.step_counter, True, self.lr, self.betas[0], self.betas[1], self.eps,
                                          self.wd, st)
             return

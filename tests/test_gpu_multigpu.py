@@ -20,7 +20,8 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-MODES = ["p2p", "split", "overlap", "graph"]
+# (ddp_mode, p2p_buckets): sharded / one-shot / one-shot in two buckets over peer memory, then the NCCL routes
+MODES = [("p2p", 0), ("p2p", 1), ("p2p", 2), ("split", 0), ("overlap", 0), ("graph", 0)]
 
 
 def _worker(rank, world, port, q):
@@ -46,10 +47,10 @@ def _worker(rank, world, port, q):
         data = DeviceResidentCounts(X, batch=batch, device=dev)
         n_obs = data.n_obs
 
-        def build(pgroup, graph, mode="p2p", lik="zinb", seed=0):
+        def build(pgroup, graph, mode="p2p", lik="zinb", seed=0, buckets=0):
             torch.manual_seed(seed)
             m = S.VAE(n_input=G, n_batch=nb, gene_likelihood=lik, precision=1).train()
-            kw = {} if pgroup is None else {"process_group": pgroup, "ddp_mode": mode}
+            kw = {} if pgroup is None else {"process_group": pgroup, "ddp_mode": mode, "p2p_buckets": buckets}
             plan = FusedTrainingPlan(m, data, batch_size=B, n_epochs_kl_warmup=None, max_kl_weight=0.5,
                                      use_cuda_graph=graph, seed=3, **kw)
             plan.set_epoch(0)
@@ -62,9 +63,9 @@ def _worker(rank, world, port, q):
             noise = torch.randn(B, 10, generator=g)
             return idx, mask, noise
 
-        for mode in MODES:
+        for mode, buckets in MODES:
             # ---- initial broadcast + one fed step against single-process arithmetic
-            plan = build(pg, False, mode, seed=11 * rank)  # deliberately different initial weights per rank
+            plan = build(pg, False, mode, seed=11 * rank, buckets=buckets)  # deliberately different initial weights per rank
             if mode == "p2p":
                 assert plan.exchange is not None and plan.ddp_mode == "p2p", "peer memory could not be mapped"
             p0 = plan.p.clone()
@@ -87,24 +88,31 @@ def _worker(rank, world, port, q):
                  C.c_void_p(exp_v.data_ptr()), exp_p.numel(), 1, 1e-3, 0.9, 0.999, 0.01, 1e-6, 1.0 / world, st)
             torch.cuda.synchronize()
             assert float((exp_p - p0).abs().max()) > 0
-            for name, got, want in (("p", plan.p, exp_p), ("m", plan.m, exp_m), ("v", plan.v, exp_v)):
-                assert torch.equal(got, want), (mode, name, float((got - want).abs().max()))
+            lo, hi = 0, p0.numel()
+            if mode == "p2p" and buckets == 0:  # sharded: this rank keeps the Adam moments of its own slice only
+                lo, hi = plan.exchange.shard_bounds()
+                assert 0 <= lo < hi <= p0.numel()
+            assert torch.equal(plan.p, exp_p), (mode, buckets, "p", float((plan.p - exp_p).abs().max()))
+            for name, got, want in (("m", plan.m, exp_m), ("v", plan.v, exp_v)):
+                assert torch.equal(got[lo:hi], want[lo:hi]), (mode, buckets, name, float((got - want).abs().max()))
             assert int(plan.step_counter[0]) == 1
             if hasattr(plan, "close"):
                 plan.close()
             # ---- graph replay == eager sequence; replicas stay identical
             end = []
             for graph in (True, False):
-                plan = build(pg, graph, mode)
+                plan = build(pg, graph, mode, buckets=buckets)
                 for step in range(5):
                     ix, _, _ = inputs(rank, 10 + step)
                     plan.training_step(ix.to(dev))
                 torch.cuda.synchronize()
-                end.append((plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.bn1_rm.clone(), plan.bn2_rv.clone()))
+                lo, hi = plan.exchange.shard_bounds() if (mode == "p2p" and buckets == 0) else (0, plan.p.numel())
+                end.append((plan.p.clone(), plan.m[lo:hi].clone(), plan.v[lo:hi].clone(), plan.bn1_rm.clone(),
+                            plan.bn2_rv.clone()))
                 assert int(plan.step_counter[0]) == 5
                 plan.close()
             for a, b in zip(end[0], end[1], strict=True):
-                assert torch.equal(a, b), f"{mode}: graph replay differs from the eager sequence"
+                assert torch.equal(a, b), f"{mode}/{buckets}: graph replay differs from the eager sequence"
             both = [torch.empty_like(end[0][0]) for _ in range(world)]
             dist.all_gather(both, end[0][0])
             assert all(torch.equal(both[0], b) for b in both), f"{mode}: replicas diverged"
