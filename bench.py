@@ -55,7 +55,8 @@ def parse():
     ap.add_argument("--ddp-mode", default="p2p", choices=["p2p", "graph", "overlap", "split"],
                     help="multi-GPU gradient exchange (FusedTrainingPlan.ddp_mode): p2p = this library's fused "
                          "all-reduce + Adam over NVLink peer memory, the others = NCCL routes")
-    ap.add_argument("--p2p-buckets", type=int, default=0, help="FusedTrainingPlan.p2p_buckets (ddp-mode p2p)")
+    ap.add_argument("--p2p-buckets", type=int, default=None,
+                    help="FusedTrainingPlan.p2p_buckets (ddp-mode p2p): default = one-shot up to 2 GPUs, sharded beyond")
     ap.add_argument("--blocks", type=int, default=5,
                     help="the timed region is repeated this many times (each EXACTLY --steps steps between "
                          "barrier + synchronize); ms_per_step is the median block")

@@ -69,7 +69,7 @@ class FusedTrainingPlan:
                  eps: float = 0.01, weight_decay: float = 1e-6, betas=(0.9, 0.999),
                  n_epochs_kl_warmup: int | None = 400, n_steps_kl_warmup: int | None = None,
                  max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, seed: int = 0,
-                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "p2p", p2p_buckets: int = 0):
+                 use_cuda_graph: bool = True, process_group=None, ddp_mode: str = "p2p", p2p_buckets: int | None = None):
         m = module
         self._check_supported(m)
         self.module, self.data = m, data
@@ -101,11 +101,16 @@ class FusedTrainingPlan:
                 self.exchange, ddp_mode = None, "split"
         self.ddp_mode = ddp_mode
         self.ddp_overlap = ddp_mode == "overlap"
-        # "p2p": 0 (default) = sharded: one launch at the end of the step in which every rank reduces + updates
-        # 1/world of the arena and stores the new parameters into all replicas (csrc/comm.cu); 1 = one launch,
-        # every rank reduces the whole arena (one-shot); 2 = one-shot in two buckets, the decoder-head bucket on
-        # a side stream under the rest of the backward.  Measured on 2 B200 (tools/ddp_modes.sh): 2 buckets
-        # 0.477, 1 bucket 0.467, NCCL routes 0.491-0.497 ms per step against 0.452 on one GPU.
+        # "p2p" forms: 0 = sharded: one launch at the end of the step in which every rank reduces + updates 1/world
+        # of the arena and stores the new parameters into all replicas (csrc/comm.cu); 1 = one launch, every rank
+        # reduces the whole arena (one-shot); 2 = one-shot in two buckets, the decoder-head bucket on a side
+        # stream under the rest of the backward.  Measured (tools/ddp_modes.sh, profiles/r02_ddp_modes.txt), ms
+        # per step against 0.452-0.455 on one GPU:   2 GPUs: 0.473 / 0.467 / 0.476, NCCL routes 0.494-0.500;
+        # 8 GPUs: 0.491 / 0.506 / 0.509.  Default (None): one-shot up to 2 ranks, sharded beyond.
+        if p2p_buckets is None:
+            p2p_buckets = 1 if self.world <= 2 else 0
+        if p2p_buckets not in (0, 1, 2):
+            raise ValueError("p2p_buckets must be None, 0, 1 or 2")
         self.p2p_buckets = int(p2p_buckets)
         self._n_exec = 0  # whole steps executed so far: its low bit selects the gradient buffer (p2p double buffer)
         self.zinb = m.gene_likelihood == "zinb"

@@ -1,7 +1,8 @@
 #!/bin/bash
 # usage: tools/ddp_modes.sh N  -- step time of every data-parallel exchange mode at N GPUs (value leg only)
 N=$1
-for mode in "p2p --p2p-buckets 0" "p2p --p2p-buckets 2" "p2p --p2p-buckets 1" "split" "overlap" "graph"; do
+if [ -n "$2" ]; then MODES=("p2p --p2p-buckets 0" "p2p --p2p-buckets 1" "p2p --p2p-buckets 2"); else MODES=("p2p --p2p-buckets 0" "p2p --p2p-buckets 2" "p2p --p2p-buckets 1" "split" "overlap" "graph"); fi
+for mode in "${MODES[@]}"; do
   tag=$(echo $mode | tr -d ' -')
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29520 \
     bench.py --gpus $N --steps 50 --warmup 20 --no-extras --no-cpu-baseline --value-only --ddp-mode $mode \
