@@ -210,6 +210,24 @@ int scvi_bn_act_drop_bwd_static(const float* da, int64_t ldda, const float* y, i
                                 int relu, const uint8_t* drop_mask, float drop_scale, int training, float* dy,
                                 int64_t lddy, float* dgamma, float* dbeta, void* stream);
 
+/* ---- a3 / f4: LayerNorm variant of the above and the batch-embedding gradient ---------------------------
+ * scvi_ln_act_drop_fwd / _bwd replace nn.LayerNorm(n_out, elementwise_affine=False) -> nn.ReLU -> nn.Dropout of
+ * FCLayers._build_layer with use_layer_norm (src/scvi/nn/_base_components.py:102-115): every ROW of y is normalised
+ * with its own mean and biased variance (eps inside the square root; torch's default 1e-5).
+ *   a = keep * drop_scale * act((y - mean_row) * rstd_row);   stats [B,2] = (mean, rstd) per row (nullable in fwd),
+ * consumed by the backward:  dy = rstd * (g - mean_n g - xhat * mean_n(g * xhat)),  g = da through dropout and ReLU. */
+int scvi_ln_act_drop_fwd(const float* y, int64_t ldy, int64_t B, int64_t N, float eps, int relu,
+                         const uint8_t* drop_mask, float drop_scale, float* a, int64_t lda, float* stats,
+                         void* stream);
+int scvi_ln_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t ldy, int64_t B, int64_t N,
+                         const float* stats, int relu, const uint8_t* drop_mask, float drop_scale, float* dy,
+                         int64_t lddy, void* stream);
+/* Gradient of `scvi.nn.Embedding` (src/scvi/nn/_embedding.py:29-98, used for batch_representation="embedding",
+ * src/scvi/module/_vae.py:218-236,385-396,489-498): dW[e, :] = sum over the cells b with idx[b] == e of g[b, :],
+ * rows visited in order (deterministic).  The forward is scvi_gather_rows on the table. */
+int scvi_embedding_bwd(const float* g, int64_t ldg, const int64_t* idx, int64_t B, int64_t D, int64_t n_emb,
+                       float* dW, void* stream);
+
 /* ---- a4/a9: latent heads, reparameterisation, Normal KL -------------------------------
  * replaces Encoder.forward's heads (src/scvi/nn/_base_components.py:311-317):
  *   q_m = a Wm^T + bm;  q_v = exp(a Wv^T + bv) + var_eps;  z = q_m + sqrt(q_v) * noise

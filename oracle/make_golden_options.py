@@ -150,6 +150,24 @@ def vae_option_case(name, G, n_batch, B, seed, kl_weight, vae_kwargs, n_labels=0
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(1)
+    only = sys.argv[1] if len(sys.argv) > 1 else None  # e.g. "embedding": (re)generate that group only
+    if only is None:
+        main_round1()
+    if only in (None, "embedding"):
+        main_embedding()
+
+
+def main_embedding():
+    only = "embedding"
+    # batch_representation="embedding" (src/scvi/nn/_embedding.py, src/scvi/module/_vae.py:218-236,385-396,489-498)
+    vae_option_case("opt_embedding_zinb", 88, 4, 60, 18, 0.6,
+                    {"batch_representation": "embedding", "gene_likelihood": "zinb"})
+    vae_option_case("opt_embedding_enc_nb", 76, 3, 52, 19, 0.8,
+                    {"batch_representation": "embedding", "encode_covariates": True, "gene_likelihood": "nb",
+                     "batch_embedding_kwargs": {"embedding_dim": 7}}, n_cont=1)
+
+
+def main_round1():
     vae_option_case("opt_genebatch_zinb", 96, 3, 64, 10, 0.5, {"dispersion": "gene-batch", "gene_likelihood": "zinb"})
     vae_option_case("opt_genelabel_nb", 80, 2, 48, 11, 1.0, {"dispersion": "gene-label", "gene_likelihood": "nb"}, n_labels=4)
     vae_option_case("opt_genecell_zinb", 72, 2, 40, 12, 0.3, {"dispersion": "gene-cell", "gene_likelihood": "zinb"})

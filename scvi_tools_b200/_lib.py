@@ -49,6 +49,9 @@ SIGNATURES = {
     "scvi_bn_act_drop_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, P, P, P, I32, P, F32, I32, P, I64, P, P, P, P]),
     "scvi_bn_static_scratch_bytes": (I64, []),
     "scvi_bn_act_drop_bwd_static": (C.c_int, [P, I64, P, I64, I64, I64, P, P, P, P, I32, P, F32, I32, P, I64, P, P, P]),
+    "scvi_ln_act_drop_fwd": (C.c_int, [P, I64, I64, I64, F32, I32, P, F32, P, I64, P, P]),
+    "scvi_ln_act_drop_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, I32, P, F32, P, I64, P]),
+    "scvi_embedding_bwd": (C.c_int, [P, I64, P, I64, I64, I64, P, P]),
     "scvi_latent_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, F32, P, P, P, P, P]),
     "scvi_latent_bwd_ws_bytes": (I64, [I64, I64, I64]),
     "scvi_latent_bwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, F32, P, P, P, P, P, P, P, I64, P, P, P, P, P, P]),

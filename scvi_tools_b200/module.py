@@ -20,7 +20,7 @@ from torch.nn.functional import one_hot
 
 from . import _lib
 from .distributions import NegativeBinomial, ZeroInflatedNegativeBinomial
-from .nn import DecoderSCVI, Encoder, _next_noise
+from .nn import DecoderSCVI, Embedding, Encoder, _next_noise
 
 
 class _REGISTRY_KEYS_NT(NamedTuple):  # reference src/scvi/_constants.py:4-21
@@ -226,9 +226,7 @@ class VAE(nn.Module):
             raise NotImplementedError(
                 f"gene_likelihood={gene_likelihood!r}: the B200 hot path implements 'zinb' and 'nb' (DESIGN.md)"
             )
-        if batch_representation == "embedding":
-            raise NotImplementedError("batch_representation='embedding' is out of scope of the B200 hot path")
-        if batch_representation != "one-hot":
+        if batch_representation not in ("one-hot", "embedding"):
             raise ValueError("`batch_representation` must be one of 'one-hot', 'embedding'.")
         self.dispersion = dispersion
         self.n_latent = n_latent
@@ -283,7 +281,16 @@ class VAE(nn.Module):
         ln_enc = use_layer_norm in ("encoder", "both")
         ln_dec = use_layer_norm in ("decoder", "both")
         n_input_encoder = n_input + n_continuous_cov * encode_covariates
-        cat_list = [n_batch] + list([] if n_cats_per_cov is None else n_cats_per_cov)
+        batch_dim = 0
+        if batch_representation == "embedding":
+            # the batch enters as a learned vector concatenated to the layer inputs instead of one-hot columns
+            # (reference _vae.py:218-236)
+            self.init_embedding(REGISTRY_KEYS.BATCH_KEY, n_batch, **(batch_embedding_kwargs or {}))
+            batch_dim = self.get_embedding(REGISTRY_KEYS.BATCH_KEY).embedding_dim
+            n_input_encoder += batch_dim * encode_covariates
+            cat_list = list([] if n_cats_per_cov is None else n_cats_per_cov)
+        else:
+            cat_list = [n_batch] + list([] if n_cats_per_cov is None else n_cats_per_cov)
         encoder_cat_list = cat_list if encode_covariates else None
         enc_kw = extra_encoder_kwargs or {}
         self.z_encoder = Encoder(
@@ -300,10 +307,42 @@ class VAE(nn.Module):
         )
         dec_kw = extra_decoder_kwargs or {}
         self.decoder = DecoderSCVI(
-            n_latent + n_continuous_cov, n_input, n_cat_list=cat_list, n_layers=n_layers, n_hidden=n_hidden,
+            n_latent + n_continuous_cov + batch_dim, n_input, n_cat_list=cat_list, n_layers=n_layers, n_hidden=n_hidden,
             inject_covariates=deeply_inject_covariates, use_batch_norm=bn_dec, use_layer_norm=ln_dec,
             scale_activation="softplus" if use_size_factor_key else "softmax", **dec_kw,
         )
+
+    # ------------------------------------------------------------------ embeddings
+    # `EmbeddingModuleMixin` (reference src/scvi/module/base/_embedding_mixin.py:8-50): tables live in a ModuleDict
+    # registered as `_embeddings_dict`, which fixes the state_dict key `_embeddings_dict.<key>.weight`.
+    @property
+    def embeddings_dict(self) -> nn.ModuleDict:
+        if not hasattr(self, "_embeddings_dict"):
+            self._embeddings_dict = nn.ModuleDict()
+        return self._embeddings_dict
+
+    def add_embedding(self, key: str, embedding: Embedding, overwrite: bool = False) -> None:
+        if key in self.embeddings_dict and not overwrite:
+            raise KeyError(f"Embedding {key} already exists.")
+        self.embeddings_dict[key] = embedding
+
+    def remove_embedding(self, key: str) -> None:
+        if key not in self.embeddings_dict:
+            raise KeyError(f"Embedding {key} not found.")
+        del self.embeddings_dict[key]
+
+    def get_embedding(self, key: str) -> Embedding:
+        if key not in self.embeddings_dict:
+            raise KeyError(f"Embedding {key} not found.")
+        return self.embeddings_dict[key]
+
+    def init_embedding(self, key: str, num_embeddings: int, embedding_dim: int = 5, **kwargs) -> None:
+        self.add_embedding(key, Embedding(num_embeddings, embedding_dim, **kwargs))
+
+    def compute_embedding(self, key: str, indices: torch.Tensor) -> torch.Tensor:
+        indices = indices.flatten() if indices.ndim > 1 else indices
+        emb = self.get_embedding(key)
+        return emb(indices.to(emb.weight.device))
 
     # ------------------------------------------------------------------ plumbing
     @property
@@ -371,20 +410,25 @@ class VAE(nn.Module):
         """Encoder pass (reference _vae.py:360-417).  `log1p(x)` and `library = log(sum x)` are
         fused into the first encoder GEMM when no dense covariate is concatenated to x."""
         cats = torch.split(cat_covs, 1, dim=1) if (cat_covs is not None and self.encode_covariates) else ()
-        dense_cov = cont_covs is not None and self.encode_covariates
+        embed = self.batch_representation == "embedding"
+        # with the embedding representation the encoders take no batch category (reference _vae.py:385-396)
+        bcat = () if embed else (batch_index,)
+        dense_cov = (cont_covs is not None or embed) and self.encode_covariates
         library = None
         if dense_cov or x.dim() != 2 or not self.z_encoder.encoder.is_fusable():
             if self.use_observed_lib_size:
                 library = torch.log(x.sum(1)).unsqueeze(1)
             x_ = torch.log1p(x) if self.log_variational else x
-            enc_in = torch.cat((x_, cont_covs), dim=-1) if dense_cov else x_
-            qz, z = self.z_encoder(enc_in, batch_index, *cats)
+            enc_in = torch.cat((x_, cont_covs), dim=-1) if (cont_covs is not None and self.encode_covariates) else x_
+            if embed and self.encode_covariates:
+                enc_in = torch.cat([enc_in, self.compute_embedding(REGISTRY_KEYS.BATCH_KEY, batch_index)], dim=-1)
+            qz, z = self.z_encoder(enc_in, *bcat, *cats)
         else:
             flags = (_lib.LIN_LOG1P if self.log_variational else 0) | (
                 _lib.LIN_LIBRARY if self.use_observed_lib_size else 0
             )
             enc_in = x  # the transform happens inside the kernel
-            out = self.z_encoder(x, batch_index, *cats, _first_flags=flags)
+            out = self.z_encoder(x, *bcat, *cats, _first_flags=flags)
             if self.use_observed_lib_size:
                 qz, z, library = out
             else:
@@ -392,7 +436,7 @@ class VAE(nn.Module):
         ql = None
         if not self.use_observed_lib_size:
             x_in = torch.log1p(x) if (self.log_variational and enc_in is x) else enc_in
-            ql, library = self.l_encoder(x_in, batch_index, *cats)
+            ql, library = self.l_encoder(x_in, *bcat, *cats)
         if n_samples > 1:  # `qz.sample((n_samples,))` (:402-411), drawn on the device (or from `rng_feed`)
             with torch.no_grad():
                 untran_z = qz.loc + qz.scale * _next_noise((n_samples, *qz.loc.shape), qz.loc.device)
@@ -441,7 +485,11 @@ class VAE(nn.Module):
         else:
             px_r = None
 
-        h = self.decoder.hidden(dec_in, batch_index, *cats)
+        if self.batch_representation == "embedding":  # reference _vae.py:489-498
+            dec_in = torch.cat([dec_in, self.compute_embedding(REGISTRY_KEYS.BATCH_KEY, batch_index)], dim=-1)
+            h = self.decoder.hidden(dec_in, *cats)
+        else:
+            h = self.decoder.hidden(dec_in, batch_index, *cats)
         fused = self.dispersion == "gene" and self.decoder.supports_fused_nll(h) and size_factor.dim() == 2
         if fused:
             px = FusedCountDistribution(self.decoder, h, size_factor, px_r, self.gene_likelihood, self.dispersion,

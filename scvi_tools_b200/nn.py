@@ -65,6 +65,54 @@ def _identity(x):
     return x
 
 
+class Embedding(nn.Embedding):
+    """`scvi.nn.Embedding` (reference src/scvi/nn/_embedding.py:29-98): an embedding table that can be grown
+    (`extend`) and that accepts a checkpoint whose table has a different number of rows.  On CUDA the lookup is
+    this library's row gather and its gradient a fixed-order segmented sum."""
+
+    @classmethod
+    def extend(cls, embedding: "Embedding", init, freeze_prev: bool = True) -> "Embedding":
+        """New table = the old rows followed by `init` fresh N(0,1) rows (int) or by copies of the rows listed in
+        `init` (list of int).  With `freeze_prev` the old rows receive no gradient."""
+        old = embedding.weight
+        if isinstance(init, int):
+            if init <= 0:
+                raise ValueError(f"`init` must be greater than 0, got {init}")
+            extra = torch.empty((init, embedding.embedding_dim), device=old.device)
+            nn.init.normal_(extra)
+        elif isinstance(init, list):
+            extra = old[init].clone()
+        else:
+            raise TypeError(f"`init` must be an `int` or a `list[int]`, got {type(init)}")
+        table = torch.cat([old.clone(), extra], dim=0)
+        grown = cls(num_embeddings=table.shape[0], embedding_dim=table.shape[1], _weight=table,
+                    padding_idx=embedding.padding_idx, max_norm=embedding.max_norm, norm_type=embedding.norm_type,
+                    scale_grad_by_freq=embedding.scale_grad_by_freq, sparse=embedding.sparse)
+        if freeze_prev:
+            n_old = embedding.num_embeddings
+
+            def _zero_old_rows(grad):
+                grad = grad.clone()
+                grad[:n_old] = 0.0
+                return grad
+
+            grown.weight.register_hook(_zero_old_rows)
+        return grown
+
+    def _load_from_state_dict(self, state_dict, *args, **kwargs):
+        key = [k for k in state_dict.keys() if "weight" in k][0]
+        self.weight = nn.Parameter(state_dict[key])
+        self.num_embeddings, self.embedding_dim = self.weight.shape[0], self.weight.shape[1]
+        return super()._load_from_state_dict(state_dict, *args, **kwargs)
+
+    def forward(self, indices: torch.Tensor) -> torch.Tensor:
+        plain = self.padding_idx is None and self.max_norm is None and not self.scale_grad_by_freq and not self.sparse
+        if self.weight.is_cuda and plain and self.weight.dtype == torch.float32:
+            flat = indices.reshape(-1).to(torch.int64)
+            return ops.EmbeddingRows.apply(self.weight, flat).reshape(*indices.shape, self.embedding_dim)
+        return super().forward(indices)
+
+
 class FCLayers(nn.Module):
     """Fully-connected stack: Linear (+ covariate injection) -> BatchNorm -> LayerNorm -> activation -> Dropout.
 
@@ -156,7 +204,8 @@ class FCLayers(nn.Module):
             len(layers) == 5
             and type(lin) is nn.Linear
             and (bn is None or type(bn) is nn.BatchNorm1d)
-            and ln is None
+            # LayerNorm (no affine) has its own kernel; stacked on a BatchNorm it runs composed
+            and (ln is None or (bn is None and type(ln) is nn.LayerNorm and not ln.elementwise_affine))
             and (act is None or type(act) is nn.ReLU)
             and (drop is None or type(drop) is nn.Dropout)
         )
@@ -194,7 +243,7 @@ class FCLayers(nn.Module):
         # covariate columns of W: [x | cont | one-hot(cat_0) | one-hot(cat_1) ...]
         library = None
         for i, layers in enumerate(self.fc_layers):
-            lin, bn, _, act, drop = layers
+            lin, bn, ln, act, drop = layers
             inject = self.inject_into_layer(i) and self.n_cov > 0
             n_dense = lin.in_features - (sum(self.n_cat_list) if inject else 0)
             if inject and cont is not None:
@@ -218,11 +267,14 @@ class FCLayers(nn.Module):
             if flags & _lib.LIN_LIBRARY:
                 library = lib
             use_drop = drop is not None and self.training and drop.p > 0
-            if bn is None and act is None and not use_drop:
+            if bn is None and ln is None and act is None and not use_drop:
                 x = y
                 continue
             mask = _next_mask(y.shape, drop.p, y.device) if use_drop else None
             scale = 1.0 / (1.0 - drop.p) if use_drop else 1.0
+            if ln is not None:
+                x = ops.LNActDrop.apply(y, mask, scale, act is not None, ln.eps)
+                continue
             x = ops.BNActDrop.apply(
                 y, part, bn.weight if bn is not None else None, bn.bias if bn is not None else None,
                 bn.running_mean if bn is not None else None, bn.running_var if bn is not None else None,

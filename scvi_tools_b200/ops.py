@@ -398,6 +398,58 @@ class LatentHeads(torch.autograd.Function):
         return da, dWm, dbm, dWv, dbv, None, None
 
 
+class LNActDrop(torch.autograd.Function):
+    """nn.LayerNorm(n_out, elementwise_affine=False) -> ReLU -> Dropout of FCLayers._build_layer
+    (reference _base_components.py:102-115, `use_layer_norm`)."""
+
+    @staticmethod
+    def forward(ctx, y, mask, drop_scale, relu, eps):
+        y = _rowmajor(y, "y")
+        B, N = y.shape
+        a = torch.empty(B, N, dtype=torch.float32, device=y.device)
+        stats = torch.empty(B, 2, dtype=torch.float32, device=y.device)
+        if mask is not None:
+            mask = _check(mask, "drop_mask", torch.uint8).contiguous()
+        call("scvi_ln_act_drop_fwd", _ptr(y), y.stride(0), B, N, float(eps), int(relu), _ptr(mask), float(drop_scale),
+             _ptr(a), N, _ptr(stats), _stream())
+        ctx.save_for_backward(y, stats, mask)
+        ctx.meta = (float(drop_scale), bool(relu))
+        return a
+
+    @staticmethod
+    def backward(ctx, da):
+        y, stats, mask = ctx.saved_tensors
+        drop_scale, relu = ctx.meta
+        da = _rowmajor(da.float(), "da")
+        B, N = y.shape
+        dy = torch.empty(B, N, dtype=torch.float32, device=y.device)
+        call("scvi_ln_act_drop_bwd", _ptr(da), da.stride(0), _ptr(y), y.stride(0), B, N, _ptr(stats), int(relu),
+             _ptr(mask), drop_scale, _ptr(dy), N, _stream())
+        return dy, None, None, None, None
+
+
+class EmbeddingRows(torch.autograd.Function):
+    """`scvi.nn.Embedding.forward` (reference _embedding.py:29, nn.Embedding): rows `idx` of the table; the
+    gradient is a per-row segmented sum in fixed order."""
+
+    @staticmethod
+    def forward(ctx, weight, idx):
+        weight = _rowmajor(weight, "weight")
+        idx = _check(idx, "idx", torch.int64).reshape(-1).contiguous()
+        ctx.save_for_backward(idx)
+        ctx.shape = tuple(weight.shape)
+        return gather_rows(weight, idx)
+
+    @staticmethod
+    def backward(ctx, g):
+        (idx,) = ctx.saved_tensors
+        n_emb, D = ctx.shape
+        g = _rowmajor(g.float(), "g")
+        dW = torch.empty(n_emb, D, dtype=torch.float32, device=g.device)
+        call("scvi_embedding_bwd", _ptr(g), g.stride(0), _ptr(idx), idx.numel(), D, n_emb, _ptr(dW), _stream())
+        return dW, None
+
+
 # --------------------------------------------------------------------------------------
 # a5-a9: fused decoder heads + softmax + NB/ZINB NLL
 # --------------------------------------------------------------------------------------

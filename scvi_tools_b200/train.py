@@ -168,6 +168,7 @@ class FusedTrainingPlan:
         ok = (
             m.n_layers == 1 and m.dispersion == "gene" and m.use_observed_lib_size and m.log_variational
             and not m.encode_covariates and m.latent_distribution == "normal" and not m.use_size_factor_key
+            and m.batch_representation == "one-hot"
             and m.n_hidden in (64, 128, 256) and m.n_latent <= 32
             and m.z_encoder.encoder.use_batch_norm and m.decoder.px_decoder.use_batch_norm
             and not m.z_encoder.encoder.use_layer_norm and not m.decoder.px_decoder.use_layer_norm

@@ -129,6 +129,33 @@ def test_save_load_round_trip_and_reference_shaped_checkpoint(tmp_path):
     assert rel_err(m3.get_latent_representation(), gold["qz_mean"]) < 1e-5
 
 
+def test_checkpoint_with_reference_module_weights_loads_and_reproduces_reference_outputs():
+    """tests/golden/ref_checkpoint/model.pt (oracle/make_golden_checkpoint.py): weights, key constants and expected
+    outputs all come from the unmodified reference module.  `SCVI.load` on it reproduces the reference's latent
+    means, px_scale and per-cell reconstruction loss for the recorded cells."""
+    from scvi_tools_b200.model import SCVI
+    from tests._golden import GOLD
+
+    e = np.load(os.path.join(GOLD, "ref_checkpoint_expect.npz"))
+    model = SCVI.load(os.path.join(GOLD, "ref_checkpoint"), e["X"], batch=e["batch"], var_names=e["var_names"])
+    assert model.is_trained_ and model.module.gene_likelihood == "nb"
+    idx = e["idx"]
+    assert rel_err(model.get_latent_representation(indices=idx), e["qzm"]) < 1e-5
+    # decode the posterior mean, as the recording did (no random draw)
+    mod = model.module
+    t = model.data.minibatch(torch.as_tensor(idx, device=model.device))
+    with torch.inference_mode():
+        inf = mod.inference(**mod._get_inference_input(t))
+        gi = mod._get_generative_input(t, inf)
+        gi["z"] = inf["qz"].loc
+        px = mod.generative(**gi)["px"]
+        rec = px.nll(t["X"]) if hasattr(px, "nll") else -px.log_prob(t["X"]).sum(-1)
+        scale = px.scale
+    assert rel_err(scale.cpu(), e["px_scale"]) < 1e-5
+    assert float(((rec.cpu().double() - torch.from_numpy(e["reconst"]).double()).abs()
+                  / torch.from_numpy(e["reconst"]).double().abs()).max()) < 1e-5
+
+
 def test_train_then_getters_end_to_end():
     """`SCVI(...).train()` lowers the ELBO; getters run on the trained, arena-backed parameters; a state-dict
     round trip into a fresh model reproduces them."""

@@ -14,7 +14,7 @@ from tests._golden import GOLD, grad_close, max_rel, rel_err
 pytestmark = pytest.mark.gpu
 
 CASES = ["opt_genebatch_zinb", "opt_genelabel_nb", "opt_genecell_zinb", "opt_libenc_nb", "opt_covs_zinb",
-         "opt_layernorm_nb", "opt_deep_noinject_zinb", "opt_nologvar_nb"]
+         "opt_layernorm_nb", "opt_deep_noinject_zinb", "opt_nologvar_nb", "opt_embedding_zinb", "opt_embedding_enc_nb"]
 
 
 def load_option_case(name):
