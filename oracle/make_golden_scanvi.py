@@ -11,6 +11,7 @@ eval-mode `classify` (the `SCANVI.predict` path, posterior mean) on the same cel
 
 from __future__ import annotations
 
+import json
 import os
 import sys
 
@@ -70,8 +71,50 @@ def scanvi_case(name, G, n_batch, n_labels, B, B_lab, seed, kl_weight, ratio, kw
     save_case(name, kwargs, tensors, m, feed, out, extra_in)
 
 
+def scanvi_trajectory(name, G, n_batch, n_labels, B, B_lab, seed, n_steps, kwargs_extra):
+    """`SemiSupervisedTrainingPlan.training_step` x n_steps on the unmodified reference module
+    (src/scvi/train/_trainingplans.py:936-969): loss(full minibatch, labelled minibatch, classification_ratio 50,
+    kl_weight epoch / 400) -> backward -> torch.optim.Adam(lr 1e-3, eps 0.01, weight_decay 1e-6) over the
+    parameters that require grad (:475-482)."""
+    R = ref_shim.load()
+    kwargs = dict(n_input=G, n_batch=n_batch, n_labels=n_labels, **kwargs_extra)
+    torch.manual_seed(seed)
+    m = R.SCANVAE(**kwargs)
+    perturb_(m, seed + 3)
+    m.train()
+    P0 = {k: v.detach().clone() for k, v in m.state_dict().items()}
+    opt = torch.optim.Adam(filter(lambda p: p.requires_grad, m.parameters()), lr=1e-3, eps=0.01, weight_decay=1e-6)
+    tensors, out = {}, {}
+    with RecordingFeed(seed + 2) as feed:
+        for t in range(n_steps):
+            full = make_inputs(400, G, n_batch, B, seed + 10 * t, n_labels=n_labels)
+            lab = make_inputs(400, G, n_batch, B_lab, seed + 10 * t + 5, n_labels=n_labels)
+            for k, v in full.items():
+                tensors[f"s{t}::full::{k}"] = v
+            for k, v in lab.items():
+                tensors[f"s{t}::lab::{k}"] = v
+            klw = t / 400.0  # _compute_kl_weight(epoch=t, step, n_epochs_kl_warmup=400)
+            opt.zero_grad()
+            _, _, lo = m(full, loss_kwargs={"kl_weight": klw, "labelled_tensors": lab, "classification_ratio": 50})
+            lo.loss.backward()
+            opt.step()
+            out[f"loss{t}"] = lo.loss.detach().numpy()
+            out[f"classification_loss{t}"] = lo.classification_loss.detach().numpy()
+    out["loss"] = out[f"loss{n_steps - 1}"]
+    for k, v in m.state_dict().items():
+        out["param_after::" + k] = v.detach().clone().numpy()
+    trained = [k for k, p in m.named_parameters() if p.grad is not None]
+    extra_in = {"n_steps": np.int64(n_steps), "trained": np.array(json.dumps(trained))}
+    for k, v in P0.items():
+        extra_in["param::" + k] = v.numpy()
+    save_case(name, kwargs, tensors, m, feed, out, extra_in)
+
+
 def main():
     torch.set_num_threads(1)
+    if len(sys.argv) > 1 and sys.argv[1] == "trajectory":
+        scanvi_trajectory("scanvi_trajectory", 90, 2, 5, 64, 32, 30, 3, {"gene_likelihood": "zinb"})
+        return
     scanvi_case("scanvi_zinb_labelled", 100, 2, 4, 64, 24, 20, 0.5, 50.0, {"gene_likelihood": "zinb"})
     scanvi_case("scanvi_nb_unlabelled", 80, 3, 20, 40, 0, 21, 1.0, 50.0, {"gene_likelihood": "nb"})
     scanvi_case("scanvi_linear_classifier", 64, 1, 3, 48, 16, 22, 0.25, 50.0,
