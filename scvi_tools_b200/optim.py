@@ -1,0 +1,83 @@
+"""`ArenaAdam`: torch.optim.Adam semantics (reference src/scvi/train/_trainingplans.py:475-482: lr 1e-3, eps 0.01,
+weight decay 1e-6 added to the gradient) for the autograd-driven plans, as ONE launch of the library's
+multi-tensor Adam (`scvi_adam_step`) over a flat parameter / gradient / moment arena.
+
+The arena is laid out at the first `step()` over the parameters that hold a gradient by then (torch's Adam skips
+parameters whose `.grad` is None; so does this one -- and it refuses, loudly, a parameter that starts receiving
+gradient later, because its moments would have no slot).  Parameters and their `.grad` become views of the arena:
+autograd accumulates straight into it, `zero_grad()` is one memset.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from ._lib import call
+
+
+class ArenaAdam:
+    def __init__(self, named_parameters, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 0.01,
+                 weight_decay: float = 1e-6):
+        """`named_parameters`: a callable returning (name, parameter) pairs, e.g. `module.named_parameters`."""
+        self._named = named_parameters
+        self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
+        self.arena = None
+        self.names: list[str] = []
+        self._frozen: list[str] = []
+
+    def _build(self):
+        params = [(k, p) for k, p in self._named() if p.requires_grad and p.grad is not None]
+        if not params:
+            raise RuntimeError("no parameter received a gradient")
+        dev = params[0][1].device
+        if dev.type != "cuda":
+            raise RuntimeError("ArenaAdam: parameters must live on a CUDA device (there is no CPU path)")
+        offs, off = [], 0
+        for _, p in params:
+            offs.append(off)
+            off += (p.numel() + 3) // 4 * 4
+        P = torch.zeros(off, dtype=torch.float32, device=dev)
+        G = torch.zeros_like(P)
+        for (_, p), o in zip(params, offs, strict=True):
+            n = p.numel()
+            P[o : o + n].copy_(p.data.reshape(-1))
+            G[o : o + n].copy_(p.grad.reshape(-1))
+            p.data = P[o : o + n].view(p.shape)
+            p.grad = G[o : o + n].view(p.shape)
+        self.arena = {"p": P, "g": G, "m": torch.zeros_like(P), "v": torch.zeros_like(P), "step": 0, "offs": offs}
+        self.names = [k for k, _ in params]
+        taken = set(self.names)
+        self._frozen = [k for k, p in self._named() if p.requires_grad and k not in taken]
+
+    def zero_grad(self):
+        if self.arena is not None:
+            self.arena["g"].zero_()
+        else:
+            for _, p in self._named():
+                p.grad = None
+
+    def step(self):
+        if self.arena is None:
+            self._build()
+        a = self.arena
+        named = dict(self._named())
+        for k in self._frozen:
+            if named[k].grad is not None:
+                raise RuntimeError(f"parameter {k} received a gradient after the optimizer arena was laid out")
+        # autograd accumulates into the arena views in place; should it have swapped a `.grad` tensor, fold it back
+        for k, off in zip(self.names, a["offs"], strict=True):
+            p = named[k]
+            n = p.numel()
+            view = a["g"][off : off + n]
+            if p.grad is None:
+                view.zero_()
+            elif p.grad.data_ptr() != view.data_ptr():
+                view.copy_(p.grad.reshape(-1))
+                p.grad = view.view(p.shape)
+        a["step"] += 1
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        call("scvi_adam_step", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
+             C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(), a["step"], self.lr,
+             self.betas[0], self.betas[1], self.eps, self.wd, 1.0, st)

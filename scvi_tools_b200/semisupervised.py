@@ -21,15 +21,14 @@ library's multi-tensor Adam over one flat arena (`scvi_adam_step`), the minibatc
 
 from __future__ import annotations
 
-import ctypes as C
 import warnings
 from math import ceil, floor
 
 import numpy as np
 import torch
 
-from ._lib import call
 from .data import DeviceResidentCounts
+from .optim import ArenaAdam
 from .train import compute_kl_weight
 
 
@@ -199,8 +198,7 @@ class SemiSupervisedTrainingPlan:
 
     `training_step(batch)` accepts what the reference's `_split_semisupervised_batch` accepts: a `(full, labelled)`
     pair, or one dict (used for both roles when it carries labels, i.e. has the "labels" key and
-    `labelled_from_single=True`).  The optimizer state lives in one flat arena over the parameters that received a
-    gradient in the first step (torch's Adam skips parameters whose gradient is None: so does this one)."""
+    `labelled_from_single=True`).  The optimizer is `ArenaAdam` (optim.py)."""
 
     def __init__(self, module, n_classes: int, *, classification_ratio: float = 50, lr: float = 1e-3,
                  weight_decay: float = 1e-6, eps: float = 0.01, betas=(0.9, 0.999),
@@ -215,7 +213,7 @@ class SemiSupervisedTrainingPlan:
         self.loss_kwargs["classification_ratio"] = classification_ratio
         self.current_epoch = 0
         self.global_step = 0
-        self._arena = None
+        self.optimizer = ArenaAdam(module.named_parameters, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
 
     @property
     def kl_weight(self):
@@ -228,62 +226,8 @@ class SemiSupervisedTrainingPlan:
             return batch[0], batch[1]
         return batch, None
 
-    # ------------------------------------------------------------------ optimizer arena
-    def _build_arena(self):
-        """Flat p / g / m / v arenas over the parameters that hold a gradient after the first backward; parameters
-        and their `.grad` become views, so autograd accumulates straight into the gradient arena."""
-        params = [(k, p) for k, p in self.module.named_parameters() if p.requires_grad and p.grad is not None]
-        if not params:
-            raise RuntimeError("no parameter received a gradient")
-        dev = params[0][1].device
-        offs, off = [], 0
-        for _, p in params:
-            offs.append(off)
-            off += (p.numel() + 3) // 4 * 4
-        P = torch.zeros(off, dtype=torch.float32, device=dev)
-        G = torch.zeros_like(P)
-        for (k, p), o in zip(params, offs, strict=True):
-            n = p.numel()
-            P[o : o + n].copy_(p.data.reshape(-1))
-            G[o : o + n].copy_(p.grad.reshape(-1))
-            p.data = P[o : o + n].view(p.shape)
-            p.grad = G[o : o + n].view(p.shape)
-        self._arena = {"p": P, "g": G, "m": torch.zeros_like(P), "v": torch.zeros_like(P),
-                       "names": [k for k, _ in params], "step": 0}
-        self._frozen = [k for k, p in self.module.named_parameters() if p.requires_grad and k not in set(self._arena["names"])]
-
-    def _optimizer_step(self):
-        if self._arena is None:
-            self._build_arena()
-        a = self._arena
-        named = dict(self.module.named_parameters())
-        for k in self._frozen:
-            if named[k].grad is not None:
-                raise RuntimeError(f"parameter {k} received a gradient after the optimizer arena was laid out")
-        # autograd accumulates into the arena views in place; should it ever have swapped a `.grad` tensor, fold it back
-        off = 0
-        for k in a["names"]:
-            p = named[k]
-            n = p.numel()
-            view = a["g"][off : off + n]
-            if p.grad is None:
-                view.zero_()
-            elif p.grad.data_ptr() != view.data_ptr():
-                view.copy_(p.grad.reshape(-1))
-                p.grad = view.view(p.shape)
-            off += (n + 3) // 4 * 4
-        a["step"] += 1
-        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        call("scvi_adam_step", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()), C.c_void_p(a["m"].data_ptr()),
-             C.c_void_p(a["v"].data_ptr()), a["p"].numel(), a["step"], self.lr, self.betas[0], self.betas[1], self.eps,
-             self.wd, 1.0, st)
-
     def zero_grad(self):
-        if self._arena is not None:
-            self._arena["g"].zero_()
-        else:
-            for p in self.module.parameters():
-                p.grad = None
+        self.optimizer.zero_grad()
 
     # ------------------------------------------------------------------ steps
     def training_step(self, batch):
@@ -295,7 +239,7 @@ class SemiSupervisedTrainingPlan:
         self.zero_grad()
         _, _, lo = self.module(full, loss_kwargs=kw)
         lo.loss.backward()
-        self._optimizer_step()
+        self.optimizer.step()
         self.global_step += 1
         return lo
 

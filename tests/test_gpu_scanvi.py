@@ -98,7 +98,7 @@ def test_semisupervised_plan_three_steps_match_reference_trajectory():
             ce = float(out[f"classification_loss{t}"])
             assert abs(float(lo.classification_loss) - ce) <= 2e-5 * abs(ce), t
     trained = set(json.loads(str(c["extra"]["trained"])))
-    assert set(plan._arena["names"]) == trained
+    assert set(plan.optimizer.names) == trained
     sd = m.state_dict()
     for k, v0 in c["params"].items():
         after = out["param_after::" + k]
