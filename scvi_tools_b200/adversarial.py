@@ -23,6 +23,7 @@ import numpy as np
 import torch
 import torch.nn.functional as F
 
+from .graphed import WholeStepGraph
 from .optim import ArenaAdam
 from .scanvi import Classifier
 from .train import compute_kl_weight
@@ -54,7 +55,8 @@ class AdversarialTrainingPlan:
                  reduce_lr_on_plateau: bool = False, lr_factor: float = 0.6, lr_patience: int = 30,
                  lr_threshold: float = 0.0, lr_scheduler_metric: str = "elbo_validation", lr_min: float = 0.0,
                  adversarial_classifier: bool | Classifier = False, scale_adversarial_loss: float | str = "auto",
-                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, n_batch: int | None = None, **loss_kwargs):
+                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, n_batch: int | None = None,
+                 use_cuda_graph: bool = False, **loss_kwargs):
         self.module = module
         self.n_steps_kl_warmup, self.n_epochs_kl_warmup = n_steps_kl_warmup, n_epochs_kl_warmup
         self.max_kl_weight, self.min_kl_weight = max_kl_weight, min_kl_weight
@@ -76,11 +78,14 @@ class AdversarialTrainingPlan:
             self.adversarial_classifier = adversarial_classifier
             if adversarial_classifier is not False:
                 self.n_output_classifier = n_batch
-        self.opt1 = ArenaAdam(module.named_parameters, lr=lr, eps=eps, weight_decay=weight_decay)
+        self.opt1 = ArenaAdam(module.named_parameters, lr=lr, eps=eps, weight_decay=weight_decay, capturable=use_cuda_graph)
         self.opt2 = None
         if self.adversarial_classifier is not False:
             self.opt2 = ArenaAdam(self.adversarial_classifier.named_parameters, lr=1e-3, eps=0.01,
-                                  weight_decay=weight_decay)
+                                  weight_decay=weight_decay, capturable=use_cuda_graph)
+        # whole step (both backward passes, both optimizers) as one CUDA graph per minibatch shape: graphed.py
+        self._graph = WholeStepGraph(self._step) if use_cuda_graph else None
+        self._klw = None
         self.reduce_lr_on_plateau = reduce_lr_on_plateau
         self.lr_scheduler_metric = lr_scheduler_metric
         self.scheduler = _Plateau(self.opt1, lr_factor, lr_patience, lr_threshold, lr_min) if reduce_lr_on_plateau else None
@@ -99,18 +104,19 @@ class AdversarialTrainingPlan:
         target = one_hot.to(logp.dtype) if predict_true_class else (1 - one_hot).to(logp.dtype) / (n - 1)
         return -(logp * target).sum(dim=1).mean()
 
-    def training_step(self, batch):
+    def _step(self, inputs):
+        batch, klw = inputs
         kw = dict(self.loss_kwargs)
-        klw = self.kl_weight
         kw["kl_weight"] = klw
         kappa = 1 - klw if self.scale_adversarial_loss == "auto" else self.scale_adversarial_loss
         batch_tensor = batch["batch"]
-        self.module.train()
         inf, _, lo = self.module(batch, loss_kwargs=kw)
         z = inf["z"]
         loss = lo.loss
         fool = None
-        if kappa > 0 and self.adversarial_classifier is not False:
+        # a device-resident kappa (graph mode) cannot steer a host branch: the fool term is then always evaluated
+        # and contributes exactly kappa * fool = 0 once the warm-up is over
+        if self.adversarial_classifier is not False and (isinstance(kappa, torch.Tensor) or kappa > 0):
             self.adversarial_classifier.train()
             fool = self.loss_adversarial_classifier(z, batch_tensor, False)
             loss = loss + fool * kappa
@@ -123,9 +129,20 @@ class AdversarialTrainingPlan:
             self.opt2.zero_grad()
             adv.backward()
             self.opt2.step()
+        last = {"train_loss": loss.detach(), "fool_loss": None if fool is None else fool.detach(),
+                "classifier_loss": None if adv is None else adv.detach(), "kappa": kappa}
+        return lo.detach_(), last
+
+    def training_step(self, batch):
+        self.module.train()
+        if self._graph is None:
+            lo, self.last = self._step((batch, self.kl_weight))
+        else:
+            if self._klw is None:
+                self._klw = torch.zeros((), dtype=torch.float32, device=batch["X"].device)
+            self._klw.fill_(self.kl_weight)
+            lo, self.last = self._graph((batch, self._klw))
         self.global_step += 1
-        self.last = {"train_loss": loss.detach(), "fool_loss": None if fool is None else fool.detach(),
-                     "classifier_loss": None if adv is None else adv.detach(), "kappa": kappa}
         return lo
 
     @torch.no_grad()
@@ -140,14 +157,16 @@ class AdversarialTrainingPlan:
         first = self.current_epoch
         for epoch in range(first, first + max_epochs):
             self.current_epoch = epoch
-            acc = torch.zeros(3, dtype=torch.float64)
+            acc = None  # accumulated on the device: no per-step host read
             n_cells = 0
             for b in batches():
                 lo = self.training_step(b)
                 n = lo.n_obs_minibatch
-                acc += torch.tensor([float(self.last["train_loss"]) * n, float(lo.reconstruction_loss_sum),
-                                     float(lo.kl_local_sum)], dtype=torch.float64)
+                vec = torch.stack([self.last["train_loss"] * n, lo.reconstruction_loss_sum.detach(),
+                                   lo.kl_local_sum.detach()]).double()
+                acc = vec if acc is None else acc + vec
                 n_cells += n
+            acc = torch.zeros(3, dtype=torch.float64) if acc is None else acc.cpu()
             rec = {"epoch": epoch, "train_loss": float(acc[0]) / max(n_cells, 1),
                    "reconstruction_loss_train": float(acc[1]) / max(n_cells, 1),
                    "kl_local_train": float(acc[2]) / max(n_cells, 1), "kl_weight": self.kl_weight, "lr": self.opt1.lr}
@@ -163,7 +182,10 @@ class AdversarialTrainingPlan:
                 rec["kl_local_validation"] = float(v[1]) / max(nv, 1)
                 rec["elbo_validation"] = rec["reconstruction_loss_validation"] + rec["kl_local_validation"]
             if self.scheduler is not None and self.lr_scheduler_metric in rec and np.isfinite(rec[self.lr_scheduler_metric]):
+                lr_before = self.opt1.lr
                 self.scheduler.step(rec[self.lr_scheduler_metric])
+                if self._graph is not None and self.opt1.lr != lr_before:
+                    self._graph.invalidate()  # the rate is a launch argument of the captured Adam
             history.append(rec)
         self.current_epoch = first + max_epochs
         return history

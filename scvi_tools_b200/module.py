@@ -103,6 +103,20 @@ class LossOutput:
     def dict_sum(dictionary):
         return _dict_sum(dictionary)
 
+    def detach_(self):
+        """Drop every reference to the autograd graph (after `backward`): the record then only carries values."""
+        def d(v):
+            if isinstance(v, torch.Tensor):
+                return v.detach()
+            if isinstance(v, dict):
+                return {k: d(x) for k, x in v.items()}
+            return v
+
+        for f in ("loss", "reconstruction_loss", "kl_local", "kl_global", "classification_loss", "logits", "true_labels",
+                  "extra_metrics", "reconstruction_loss_sum", "kl_local_sum", "kl_global_sum"):
+            setattr(self, f, d(getattr(self, f)))
+        return self
+
     @property
     def extra_metrics_keys(self):
         return self.extra_metrics.keys()

@@ -19,9 +19,12 @@ from ._lib import call
 
 class ArenaAdam:
     def __init__(self, named_parameters, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 0.01,
-                 weight_decay: float = 1e-6):
-        """`named_parameters`: a callable returning (name, parameter) pairs, e.g. `module.named_parameters`."""
+                 weight_decay: float = 1e-6, capturable: bool = False):
+        """`named_parameters`: a callable returning (name, parameter) pairs, e.g. `module.named_parameters`.
+        `capturable`: keep the step count on the device (`scvi_adam_step_graph`), so that `step()` can be captured
+        into a CUDA graph; a learning-rate change then needs a re-capture (the rate is a launch argument)."""
         self._named = named_parameters
+        self.capturable = capturable
         self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
         self.arena = None
         self.names: list[str] = []
@@ -46,7 +49,8 @@ class ArenaAdam:
             G[o : o + n].copy_(p.grad.reshape(-1))
             p.data = P[o : o + n].view(p.shape)
             p.grad = G[o : o + n].view(p.shape)
-        self.arena = {"p": P, "g": G, "m": torch.zeros_like(P), "v": torch.zeros_like(P), "step": 0, "offs": offs}
+        self.arena = {"p": P, "g": G, "m": torch.zeros_like(P), "v": torch.zeros_like(P), "step": 0, "offs": offs,
+                      "counter": torch.zeros(2, dtype=torch.int64, device=dev)}
         self.names = [k for k, _ in params]
         taken = set(self.names)
         self._frozen = [k for k, p in self._named() if p.requires_grad and k not in taken]
@@ -78,6 +82,18 @@ class ArenaAdam:
                 p.grad = view.view(p.shape)
         a["step"] += 1
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        if self.capturable:
+            call("scvi_adam_step_graph", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
+                 C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(),
+                 C.c_void_p(a["counter"].data_ptr()), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1.0, st)
+            return
         call("scvi_adam_step", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
              C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(), a["step"], self.lr,
              self.betas[0], self.betas[1], self.eps, self.wd, 1.0, st)
+
+    @property
+    def n_steps(self) -> int:
+        """Steps applied so far (device counter when capturable: this read synchronises)."""
+        if self.arena is None:
+            return 0
+        return int(self.arena["counter"][0]) if self.capturable else self.arena["step"]

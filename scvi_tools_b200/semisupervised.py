@@ -28,6 +28,7 @@ import numpy as np
 import torch
 
 from .data import DeviceResidentCounts
+from .graphed import WholeStepGraph
 from .optim import ArenaAdam
 from .train import compute_kl_weight
 
@@ -203,9 +204,12 @@ class SemiSupervisedTrainingPlan:
     def __init__(self, module, n_classes: int, *, classification_ratio: float = 50, lr: float = 1e-3,
                  weight_decay: float = 1e-6, eps: float = 0.01, betas=(0.9, 0.999),
                  n_steps_kl_warmup: int | None = None, n_epochs_kl_warmup: int | None = 400,
-                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, **loss_kwargs):
+                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, use_cuda_graph: bool = False, **loss_kwargs):
         self.module = module
         self.n_classes = n_classes
+        # whole step (zero_grad, forward, backward, Adam) as one CUDA graph per minibatch shape: graphed.py
+        self._graph = WholeStepGraph(self._step) if use_cuda_graph else None
+        self._klw = None
         self.lr, self.wd, self.eps, self.betas = lr, weight_decay, eps, betas
         self.n_steps_kl_warmup, self.n_epochs_kl_warmup = n_steps_kl_warmup, n_epochs_kl_warmup
         self.max_kl_weight, self.min_kl_weight = max_kl_weight, min_kl_weight
@@ -213,7 +217,8 @@ class SemiSupervisedTrainingPlan:
         self.loss_kwargs["classification_ratio"] = classification_ratio
         self.current_epoch = 0
         self.global_step = 0
-        self.optimizer = ArenaAdam(module.named_parameters, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        self.optimizer = ArenaAdam(module.named_parameters, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                                   capturable=use_cuda_graph)
 
     @property
     def kl_weight(self):
@@ -230,16 +235,27 @@ class SemiSupervisedTrainingPlan:
         self.optimizer.zero_grad()
 
     # ------------------------------------------------------------------ steps
-    def training_step(self, batch):
-        full, labelled = self._split_semisupervised_batch(batch)
+    def _step(self, inputs):
+        full, labelled, klw = inputs
         kw = dict(self.loss_kwargs)
-        kw["kl_weight"] = self.kl_weight
+        kw["kl_weight"] = klw
         kw["labelled_tensors"] = labelled
-        self.module.train()
         self.zero_grad()
         _, _, lo = self.module(full, loss_kwargs=kw)
         lo.loss.backward()
         self.optimizer.step()
+        return lo.detach_()
+
+    def training_step(self, batch):
+        full, labelled = self._split_semisupervised_batch(batch)
+        self.module.train()
+        if self._graph is None:
+            lo = self._step((full, labelled, self.kl_weight))
+        else:
+            if self._klw is None:
+                self._klw = torch.zeros((), dtype=torch.float32, device=full["X"].device)
+            self._klw.fill_(self.kl_weight)  # the KL warm-up weight is graph INPUT, not a captured constant
+            lo = self._graph((full, labelled, self._klw))
         self.global_step += 1
         return lo
 
@@ -269,18 +285,18 @@ class SemiSupervisedTrainingPlan:
         for epoch in range(first, first + max_epochs):
             self.current_epoch = epoch
             loader.resample_labels()  # SubSampleLabels callback: on_train_epoch_start
-            tot = torch.zeros(4, dtype=torch.float64)
+            tot = None  # [loss * n, reconstruction sum, kl sum] accumulated on the device: no per-step host read
             n_cells = n_steps = 0
             last = None
             for batch in loader:
                 lo = self.training_step(batch)
                 n = lo.n_obs_minibatch
-                tot[0] += float(lo.loss) * n
-                tot[1] += float(lo.reconstruction_loss_sum)
-                tot[2] += float(lo.kl_local_sum)
+                vec = torch.stack([lo.loss.detach() * n, lo.reconstruction_loss_sum.detach(), lo.kl_local_sum.detach()]).double()
+                tot = vec if tot is None else tot + vec
                 n_cells += n
                 n_steps += 1
                 last = lo
+            tot = torch.zeros(3, dtype=torch.float64) if tot is None else tot.cpu()
             rec = {"epoch": epoch, "train_loss": float(tot[0]) / max(n_cells, 1),
                    "reconstruction_loss": float(tot[1]) / max(n_cells, 1), "kl_local": float(tot[2]) / max(n_cells, 1),
                    "n_cells": n_cells, "n_steps": n_steps, "kl_weight": self.kl_weight}

@@ -453,7 +453,7 @@ class TOTALVAE(nn.Module):
 
         kl_div_back_pro_full = kl(Normal(py_["back_alpha"], py_["back_beta"]), inference_outputs["back_mean_prior"])
         lkl_back_pro_full = -torch.distributions.LogNormal(
-            torch.tensor([0.0], device=x.device), torch.tensor([1.0], device=x.device)).log_prob(per_batch_efficiency)
+            x.new_zeros(1), x.new_ones(1)).log_prob(per_batch_efficiency)
         lkl_protein_expressed = -1e-3 * torch.distributions.Bernoulli(logits=py_["mixing"]).log_prob(
             torch.ones_like(py_["mixing"]))
         if pro_batch_mask_minibatch is not None:

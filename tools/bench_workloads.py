@@ -56,7 +56,7 @@ def scanvi(a, dev):
     data = DeviceResidentCounts(X, batch=torch.arange(a.cells) * 4 // a.cells, labels=labels, device=dev)
     torch.manual_seed(0)
     m = SCANVAE(n_input=a.genes, n_batch=4, n_labels=a.labels, gene_likelihood="zinb").to(dev)
-    plan = SemiSupervisedTrainingPlan(m, n_classes=a.labels)
+    plan = SemiSupervisedTrainingPlan(m, n_classes=a.labels, use_cuda_graph=not a.eager)
     B = a.batch_size
     lab_idx = torch.nonzero(labels != a.labels).view(-1).to(dev)
 
@@ -84,7 +84,7 @@ def totalvi(a, dev):
     batch = (torch.arange(a.cells, device=dev) * nb // a.cells).view(-1, 1)
     torch.manual_seed(0)
     m = TOTALVAE(n_input_genes=a.genes, n_input_proteins=a.proteins, n_batch=nb).to(dev)
-    plan = AdversarialTrainingPlan(m, adversarial_classifier=True, n_batch=nb)
+    plan = AdversarialTrainingPlan(m, lr=4e-3, adversarial_classifier=True, n_batch=nb, use_cuda_graph=not a.eager)
     B = a.batch_size
 
     def step(i):
@@ -108,6 +108,7 @@ if __name__ == "__main__":
     ap.add_argument("--proteins", type=int, default=100)
     ap.add_argument("--batch-size", type=int, default=None)
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--eager", action="store_true", help="no whole-step CUDA graph")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     if a.which == "scanvi":
@@ -116,5 +117,5 @@ if __name__ == "__main__":
     else:
         a.cells, a.genes, a.batch_size = a.cells or 200_000, a.genes or 4000, a.batch_size or 256
         line = totalvi(a, dev)
-    line.update({"n_gpus": 1, "data": "synthetic", "dtype": "f32"})
+    line.update({"n_gpus": 1, "data": "synthetic", "dtype": "f32", "whole_step_cuda_graph": not a.eager})
     print(json.dumps(line))
