@@ -168,31 +168,82 @@ struct MidFwdArgs {
   float *a1, *q_m, *q_v, *z, *kl, *y2, *part2, *mean1, *rstd1;
 };
 
+// Shared-memory geometry of the two heavy tile bodies.  Their small dense products (32 rows x {2L, L, ncols}
+// outputs, K = 128 or 32) used to be one-output-per-thread dot products fed by two shared-memory loads per FMA:
+// ~12k (forward) / ~22k (backward) shared-memory wavefronts per tile, which is what bounded mid_fwd / mid_bwd1
+// (r02 ncu: 26 / 33 us for 25 MB of traffic).  Now: operands a thread reuses live in registers (its own 8 rows of
+// the tile, its column of a weight matrix), rows of small matrices are read as broadcast 128-bit loads, K = 128
+// products are split over the 32 lanes (4 consecutive k each) and merged through a padded transpose buffer.
+// LC = n_latent as a compile-time constant (10, the reference default) or 16 (any n_latent <= 16, zero padded).
+constexpr int MD_ZLD = 16;          // row stride of z-like [32][L] tiles (float4 aligned)
+constexpr int MD_QLD = 32;          // row stride of [32][2L] tiles
+constexpr int MD_WT_LD = MD_H + 4;  // row stride of [j][128] weight rows (float4 aligned, skewed banks)
+constexpr int MD_PP_LD = 36;        // transpose buffer: [value][lane] with the lane stride padded for 128-bit reads
+template <int LC>
+__host__ __device__ constexpr int md_dt_off() { return LC == 10 ? 10 : 16; }  // offset of the second L-block of a 2L row
+__host__ __device__ inline size_t md_fwd_smem_floats(int L, int ncols) {
+  const int LCp = L == 10 ? 10 : 16;
+  return (size_t)MD_ROWS * MD_H + 2 * MD_LMAX * MD_WT_LD + (size_t)(ncols - L) * MD_H + MD_ROWS * MD_QLD + 2 * MD_ROWS * MD_ZLD +
+         12 * MD_H + (size_t)(MD_THREADS / 32) * 2 * LCp * MD_PP_LD;
+}
+__host__ __device__ inline size_t md_bwd_smem_floats(int L, int ncols) {
+  const int LCp = L == 10 ? 10 : 16;
+  const size_t red = (size_t)4 * 2 * LCp * MD_H, pp = (size_t)(MD_THREADS / 32) * 2 * LCp * MD_PP_LD;
+  return (size_t)MD_ROWS * MD_H + MD_LMAX * MD_WT_LD + 2 * MD_ROWS * MD_ZLD + MD_ROWS * MD_QLD + 12 * MD_H +
+         (size_t)(ncols - L) * MD_H + (red > pp ? red : pp);
+}
+
+// sum over the warp's 32 lanes of NV per-lane values p[0..NV): lane v < NV returns the total of p[v] (lanes summed
+// in order 0..31), through the warp's own transpose buffer pp[NV][MD_PP_LD].
+template <int NV>
+__device__ __forceinline__ float md_lane_transpose_sum(const float (&p)[NV], float* pp, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int v = 0; v < NV; ++v) pp[v * MD_PP_LD + lane] = p[v];
+  __syncwarp();
+  float tot = 0.f;
+  if (lane < NV) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float4 q = *reinterpret_cast<const float4*>(pp + lane * MD_PP_LD + 4 * k);
+      tot += q.x; tot += q.y; tot += q.z; tot += q.w;
+    }
+  }
+  return tot;
+}
+
 // forward, stage 1: BN1 + ReLU + Dropout -> latent heads, z, KL -> decoder hidden pre-activation y2 + its tile stats
-__device__ __forceinline__ void mid_fwd_body(const MidFwdArgs& A, float* s_cl) {
+template <int LC>
+__device__ __forceinline__ void mid_fwd_body(const MidFwdArgs& A, const int64_t tile, float* stats_out /*[2][128]*/) {
   extern __shared__ __align__(16) float sm[];
-  float* s_a = sm;                          // [64][128]
-  float* s_W = s_a + MD_ROWS * MD_H;        // [2L][129]  latent heads (Wm | Wv)
-  float* s_Wd = s_W + 2 * MD_LMAX * 129;    // [128][MD_WD_LD]
-  float* s_q = s_Wd + MD_H * MD_WD_LD;      // [64][2L]
-  float* s_z = s_q + MD_ROWS * 2 * MD_LMAX; // [64][L]
-  float* s_klt = s_z + MD_ROWS * MD_LMAX;   // [64][L]
-  float* s_scr = s_klt + MD_ROWS * MD_LMAX; // [12][128]
-  const int tid = threadIdx.x, col = tid & 127, rg = tid >> 7;
-  const int L = A.L, L2 = 2 * A.L;
-  const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
+  constexpr int L2C = 2 * LC, DT = md_dt_off<LC>();
+  const int L = LC == 10 ? 10 : A.L;
+  const int ncat = A.ncols - L;
+  float* s_a = sm;                                // [32][128]
+  float* s_W = s_a + MD_ROWS * MD_H;              // [2 * 16][MD_WT_LD]  latent heads: rows 0..L-1 = Wm, DT.. = Wv
+  float* s_Wc = s_W + 2 * MD_LMAX * MD_WT_LD;     // [ncat][128]  covariate columns of Wd, column-major
+  float* s_q = s_Wc + ncat * MD_H;                // [32][MD_QLD]
+  float* s_z = s_q + MD_ROWS * MD_QLD;            // [32][MD_ZLD]
+  float* s_klt = s_z + MD_ROWS * MD_ZLD;          // [32][MD_ZLD]
+  float* s_scr = s_klt + MD_ROWS * MD_ZLD;        // [12][128]
+  float* s_pp = s_scr + 12 * MD_H;                // [16 warps][2 LC][MD_PP_LD]
+  const int tid = threadIdx.x, col = tid & 127, rg = tid >> 7, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = tile * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, A.B - r0);
 
-  for (int e = tid; e < L2 * MD_H; e += MD_THREADS) {
+  for (int e = tid; e < L2C * MD_H; e += MD_THREADS) {
     const int j = e / MD_H, c = e % MD_H;
-    s_W[j * 129 + c] = (j < L) ? A.Wm[j * MD_H + c] : A.Wv[(j - L) * MD_H + c];
+    const int l = j < LC ? j : j - LC;
+    float v = 0.f;
+    if (l < L) v = (j < LC) ? A.Wm[l * MD_H + c] : A.Wv[l * MD_H + c];
+    s_W[(j < LC ? l : DT + l) * MD_WT_LD + c] = v;
   }
-  for (int e = tid; e < MD_H * A.ncols; e += MD_THREADS) s_Wd[(e / A.ncols) * MD_WD_LD + e % A.ncols] = A.Wd[e];
+  for (int e = tid; e < ncat * MD_H; e += MD_THREADS) s_Wc[e] = A.Wd[(e % MD_H) * A.ncols + L + e / MD_H];
 
   float mean, var, n;
   md_merge_stats(A.part1, A.B, SCVI_BN_TILE, s_scr, mean, var, n);
   const float rstd = 1.f / sqrtf(var + A.bn_eps);
-  if (blockIdx.x == 0 && rg == 0) {
+  if (tile == 0 && rg == 0) {
     A.mean1[col] = mean;
     A.rstd1[col] = rstd;
     if (A.rm1) A.rm1[col] = (1.f - A.momentum) * A.rm1[col] + A.momentum * mean;
@@ -224,23 +275,35 @@ __device__ __forceinline__ void mid_fwd_body(const MidFwdArgs& A, float* s_cl) {
     }
   }
   __syncthreads();
-  // latent heads: 64 x 2L dot products of length 128
-  for (int o = tid; o < MD_ROWS * L2; o += MD_THREADS) {
-    const int r = o / L2, j = o % L2;
-    const float* ar = s_a + r * MD_H;
-    const float* wr = s_W + j * 129;
-    float s = (j < L) ? A.bm[j] : A.bv[j - L];
-#pragma unroll 8
-    for (int c = 0; c < MD_H; ++c) s = fmaf(ar[c], wr[c], s);
-    s_q[r * L2 + j] = s;
+  // latent heads q[r][j] = b[j] + sum_c a[r][c] W[j][c]: warp w takes rows 2w, 2w + 1; lane = 4 consecutive c
+  {
+    const float4 a0 = *reinterpret_cast<const float4*>(s_a + (2 * warp) * MD_H + 4 * lane);
+    const float4 a1v = *reinterpret_cast<const float4*>(s_a + (2 * warp + 1) * MD_H + 4 * lane);
+    float p0[L2C], p1[L2C];
+#pragma unroll
+    for (int j = 0; j < L2C; ++j) {
+      const float4 w = *reinterpret_cast<const float4*>(s_W + (j < LC ? j : DT + j - LC) * MD_WT_LD + 4 * lane);
+      p0[j] = fmaf(a0.w, w.w, fmaf(a0.z, w.z, fmaf(a0.y, w.y, a0.x * w.x)));
+      p1[j] = fmaf(a1v.w, w.w, fmaf(a1v.z, w.z, fmaf(a1v.y, w.y, a1v.x * w.x)));
+    }
+    float* pp = s_pp + warp * (L2C * MD_PP_LD);
+    const float t0 = md_lane_transpose_sum<L2C>(p0, pp, lane);
+    const float t1 = md_lane_transpose_sum<L2C>(p1, pp, lane);
+    if (lane < L2C) {
+      const int l = lane < LC ? lane : lane - LC;
+      const float bias = l < L ? (lane < LC ? A.bm[l] : A.bv[l]) : 0.f;
+      const int o = lane < LC ? l : DT + l;
+      s_q[(2 * warp) * MD_QLD + o] = t0 + bias;
+      s_q[(2 * warp + 1) * MD_QLD + o] = t1 + bias;
+    }
   }
   __syncthreads();
-  for (int o = tid; o < MD_ROWS * L; o += MD_THREADS) {
-    const int r = o / L, l = o % L;
+  for (int o = tid; o < MD_ROWS * MD_ZLD; o += MD_THREADS) {
+    const int r = o / MD_ZLD, l = o % MD_ZLD;
     float zv = 0.f, klt = 0.f;
-    if (r < cnt) {
-      const float m = s_q[r * L2 + l];
-      const float v = expf(s_q[r * L2 + L + l]) + A.var_eps;
+    if (r < cnt && l < L) {
+      const float m = s_q[r * MD_QLD + l];
+      const float v = expf(s_q[r * MD_QLD + DT + l]) + A.var_eps;
       const float sd = sqrtf(v);
       const float s2 = sd * sd;
       const int64_t i = (r0 + r) * L + l;
@@ -250,92 +313,111 @@ __device__ __forceinline__ void mid_fwd_body(const MidFwdArgs& A, float* s_cl) {
       A.z[i] = zv;
       klt = 0.5f * (s2 + m * m - 1.f - logf(s2));
     }
-    s_z[r * L + l] = zv;
-    s_klt[r * L + l] = klt;
+    s_z[o] = zv;
+    s_klt[o] = klt;
   }
+  // this thread's column of the latent block of Wd (registers), while the z tile is being written
+  float wd[LC];
+#pragma unroll
+  for (int l = 0; l < LC; ++l) wd[l] = l < L ? A.Wd[col * A.ncols + l] : 0.f;
   __syncthreads();
   if (tid < cnt) {
     float s = 0.f;
-    for (int l = 0; l < L; ++l) s += s_klt[tid * L + l];
+    for (int l = 0; l < L; ++l) s += s_klt[tid * MD_ZLD + l];
     A.kl[r0 + tid] = s;
   }
   // decoder hidden layer: y2 = z Wd[:, :L]^T + Wd[:, cov] + bd
   const float bdv = A.bd ? A.bd[col] : 0.f;
   float vals[MD_RPT];
-#pragma unroll 4
+#pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
     float v = 0.f;
     if (r < cnt) {
       v = bdv;
-      for (int l = 0; l < L; ++l) v = fmaf(s_z[r * L + l], s_Wd[col * MD_WD_LD + l], v);
-      if (A.cov_cols) v += s_Wd[col * MD_WD_LD + A.cov_cols[r0 + r]];
+      float zr[(LC + 3) / 4 * 4];
+#pragma unroll
+      for (int k = 0; k < (LC + 3) / 4; ++k)
+        *reinterpret_cast<float4*>(zr + 4 * k) = *reinterpret_cast<const float4*>(s_z + r * MD_ZLD + 4 * k);
+#pragma unroll
+      for (int l = 0; l < LC; ++l) v = fmaf(zr[l], wd[l], v);
+      if (A.cov_cols) v += s_Wc[(A.cov_cols[r0 + r] - L) * MD_H + col];
       A.y2[(r0 + r) * MD_H + col] = v;
     }
     vals[i] = v;
   }
-  md_tile_stats(vals, rg, col, cnt, s_scr, s_cl);
+  md_tile_stats(vals, rg, col, cnt, s_scr, stats_out);
 }
 
-__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS) mid_fwd_kernel(MidFwdArgs A) {
+template <int LC>
+__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS, LC == 10 ? 2 : 1) mid_fwd_kernel(MidFwdArgs A) {
   __shared__ float s_cl[2 * MD_H];
-  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_fwd_body(A, s_cl);
+  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_fwd_body<LC>(A, blockIdx.x, s_cl);
   else if (threadIdx.x < 2 * MD_H) s_cl[threadIdx.x] = 0.f;  // a CTA that pads the grid: an empty tile
   md_cluster_stats(s_cl, A.B, A.part2);
 }
 
 // forward, stage 2: BN2 + ReLU -> h
-__global__ void __launch_bounds__(MD_THREADS)
-    mid_fwd2_kernel(const float* __restrict__ y2, const float* __restrict__ part2, const float* __restrict__ gamma2,
-                    const float* __restrict__ beta2, float* __restrict__ rm2, float* __restrict__ rv2, float bn_eps,
-                    float momentum, int64_t B, float* __restrict__ h, float* __restrict__ mean2,
-                    float* __restrict__ rstd2) {
-  __shared__ float s_scr[12 * MD_H];
+struct MidFwd2Args {
+  const float *y2, *part2, *gamma2, *beta2;
+  float *rm2, *rv2;
+  float bn_eps, momentum;
+  int64_t B;
+  float *h, *mean2, *rstd2;
+};
+__device__ __forceinline__ void mid_fwd2_body(const MidFwd2Args& A, const int64_t tile, float* s_scr /*[12][128]*/) {
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
-  const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
-  const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
-  float mean, var, n;
-  md_merge_stats(part2, B, MD_ROWS * MD_CL, s_scr, mean, var, n);
-  const float rstd = 1.f / sqrtf(var + bn_eps);
-  if (blockIdx.x == 0 && rg == 0) {
-    mean2[col] = mean;
-    rstd2[col] = rstd;
-    if (rm2) rm2[col] = (1.f - momentum) * rm2[col] + momentum * mean;
-    if (rv2) rv2[col] = (1.f - momentum) * rv2[col] + momentum * (var * n / fmaxf(n - 1.f, 1.f));
-  }
-  const float g = gamma2[col], b = beta2[col];
-#pragma unroll 4
+  const int64_t r0 = tile * MD_ROWS;
+  const int cnt = (int)min((int64_t)MD_ROWS, A.B - r0);
+  float yv[MD_RPT];  // loaded ahead of the merge
+#pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
-    if (r < cnt) {
-      const int64_t o = (r0 + r) * MD_H + col;
-      h[o] = fmaxf((y2[o] - mean) * (rstd * g) + b, 0.f);
-    }
+    yv[i] = (r < cnt) ? A.y2[(r0 + r) * MD_H + col] : 0.f;
   }
+  float mean, var, n;
+  md_merge_stats(A.part2, A.B, MD_ROWS * MD_CL, s_scr, mean, var, n);
+  const float rstd = 1.f / sqrtf(var + A.bn_eps);
+  if (tile == 0 && rg == 0) {
+    A.mean2[col] = mean;
+    A.rstd2[col] = rstd;
+    if (A.rm2) A.rm2[col] = (1.f - A.momentum) * A.rm2[col] + A.momentum * mean;
+    if (A.rv2) A.rv2[col] = (1.f - A.momentum) * A.rv2[col] + A.momentum * (var * n / fmaxf(n - 1.f, 1.f));
+  }
+  const float g = A.gamma2[col], b = A.beta2[col];
+#pragma unroll
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
+    if (r < cnt) A.h[(r0 + r) * MD_H + col] = fmaxf((yv[i] - mean) * (rstd * g) + b, 0.f);
+  }
+}
+__global__ void __launch_bounds__(MD_THREADS) mid_fwd2_kernel(MidFwd2Args A) {
+  __shared__ float s_scr[12 * MD_H];
+  mid_fwd2_body(A, blockIdx.x, s_scr);
 }
 
 // ---------------------------------------------------------------------------------------
 // backward
 // ---------------------------------------------------------------------------------------
 // stage 0: per-tile column sums of du2 = dh * 1[u2 > 0] and du2 * xhat2  (BatchNorm-2 backward, phase 1)
-__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS)
-    mid_bwd0_kernel(const float* __restrict__ dh, const float* __restrict__ y2, const float* __restrict__ mean2,
-                    const float* __restrict__ rstd2, const float* __restrict__ gamma2, const float* __restrict__ beta2,
-                    int64_t B, float* __restrict__ bpart2 /*[clusters][2][128]*/) {
-  __shared__ float s_scr[8 * MD_H];
-  __shared__ float s_cl[2 * MD_H];
+struct MidBwd0Args {
+  const float *dh, *y2, *mean2, *rstd2, *gamma2, *beta2;
+  int64_t B;
+};
+__device__ __forceinline__ void mid_bwd0_body(const MidBwd0Args& A, const int64_t tile, float* s_scr /*[8][128]*/,
+                                              float* sums_out /*[2][128]*/) {
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
-  const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
-  const int cnt = (int)max((int64_t)0, min((int64_t)MD_ROWS, B - r0));  // 0 in the CTAs that pad the grid
-  const float mu = mean2[col], rs = rstd2[col], g = gamma2[col], b = beta2[col];
+  const int64_t r0 = tile * MD_ROWS;
+  const int cnt = (int)max((int64_t)0, min((int64_t)MD_ROWS, A.B - r0));  // 0 in the CTAs that pad the grid
+  const float mu = A.mean2[col], rs = A.rstd2[col], g = A.gamma2[col], b = A.beta2[col];
   float s1 = 0.f, s2 = 0.f;
   float yv[MD_RPT], dv[MD_RPT];  // dh is loaded whatever the ReLU mask says: no load waits on another
 #pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
     const int64_t o = (r0 + r) * MD_H + col;
-    yv[i] = (r < cnt) ? y2[o] : 0.f;
-    dv[i] = (r < cnt) ? dh[o] : 0.f;
+    yv[i] = (r < cnt) ? A.y2[o] : 0.f;
+    dv[i] = (r < cnt) ? A.dh[o] : 0.f;
   }
 #pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
@@ -351,9 +433,16 @@ __global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS)
   s_scr[(4 + rg) * MD_H + col] = s2;
   __syncthreads();
   if (rg == 0) {
-    s_cl[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
-    s_cl[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
+    sums_out[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
+    sums_out[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
   }
+  __syncthreads();
+}
+__global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS)
+    mid_bwd0_kernel(MidBwd0Args A, float* __restrict__ bpart2 /*[clusters][2][128]*/) {
+  __shared__ float s_scr[8 * MD_H];
+  __shared__ float s_cl[2 * MD_H];
+  mid_bwd0_body(A, blockIdx.x, s_scr, s_cl);
   md_cluster_sum2(s_cl, bpart2);
 }
 
@@ -379,30 +468,39 @@ __host__ __device__ inline int64_t md_rec_floats(int ncols, int L) { return (int
 
 // stage 1: BN2 backward -> dy2 -> dWd / dbd partials, dz -> latent backward -> da1, dWm / dWv / dbm / dbv partials
 //          -> BN1 backward phase 1 (per-tile sums of du1, du1 * xhat1)
-__device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, float* s_cl) {
+template <int LC>
+__device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, const int64_t tile, float* sums_out /*[2][128]*/) {
   extern __shared__ __align__(16) float sm[];
-  float* s_t = sm;                           // [64][128]  dy2, later a1
-  float* s_W = s_t + MD_ROWS * MD_H;         // [2L][129]
-  float* s_Wd = s_W + 2 * MD_LMAX * 129;     // [128][MD_WD_LD]
-  float* s_z = s_Wd + MD_H * MD_WD_LD;       // [64][L]
-  float* s_dq = s_z + MD_ROWS * MD_LMAX;     // [64][2L]
-  float* s_scr = s_dq + MD_ROWS * 2 * MD_LMAX;  // [12][128]
+  constexpr int L2C = 2 * LC, DT = md_dt_off<LC>(), ZV = (LC + 3) / 4, QV = (LC == 10) ? 5 : 8;
+  const int L = LC == 10 ? 10 : A.L;
+  const int ncols = A.ncols, ncat = ncols - L;
+  float* s_t = sm;                               // [32][128]  dy2
+  float* s_WdT = s_t + MD_ROWS * MD_H;           // [16][MD_WT_LD]  Wd[:, l] as rows
+  float* s_z = s_WdT + MD_LMAX * MD_WT_LD;       // [32][MD_ZLD]
+  float* s_dz = s_z + MD_ROWS * MD_ZLD;          // [32][MD_ZLD]   (unused slots stay 0)
+  float* s_dq = s_dz + MD_ROWS * MD_ZLD;         // [32][MD_QLD]   dm at 0.., dt at DT..
+  float* s_scr = s_dq + MD_ROWS * MD_QLD;        // [12][128]
+  float* s_acc = s_scr + 12 * MD_H;              // [ncat][128]  covariate columns of dWd
+  float* s_red = s_acc + ncat * MD_H;            // [4][2 LC][128] cross-row-group partials / transpose buffers
   __shared__ int s_cat[MD_ROWS];
-  const int tid = threadIdx.x, col = tid & 127, rg = tid >> 7;
-  const int L = A.L, L2 = 2 * A.L, ncols = A.ncols;
-  const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
+  const int tid = threadIdx.x, col = tid & 127, rg = tid >> 7, warp = tid >> 5, lane = tid & 31;
+  const int64_t r0 = tile * MD_ROWS;
   const int cnt = (int)min((int64_t)MD_ROWS, A.B - r0);
-  float* rec = A.ppart + (int64_t)blockIdx.x * A.prec;
+  float* rec = A.ppart + tile * A.prec;
 
-  for (int e = tid; e < L2 * MD_H; e += MD_THREADS) {
-    const int j = e / MD_H, c = e % MD_H;
-    s_W[j * 129 + c] = (j < L) ? A.Wm[j * MD_H + c] : A.Wv[(j - L) * MD_H + c];
+  for (int e = tid; e < LC * MD_H; e += MD_THREADS) {
+    const int l = e / MD_H, n = e % MD_H;
+    s_WdT[l * MD_WT_LD + n] = l < L ? A.Wd[n * ncols + l] : 0.f;
   }
-  for (int e = tid; e < MD_H * ncols; e += MD_THREADS) s_Wd[(e / ncols) * MD_WD_LD + e % ncols] = A.Wd[e];
-  for (int e = tid; e < MD_ROWS * L; e += MD_THREADS) s_z[e] = (e / L < cnt) ? A.z[r0 * L + e] : 0.f;
-  if (tid < MD_ROWS) s_cat[tid] = (A.cov_cols && tid < cnt) ? A.cov_cols[r0 + tid] : -1;
+  for (int e = tid; e < MD_ROWS * MD_ZLD; e += MD_THREADS) {
+    const int r = e / MD_ZLD, l = e % MD_ZLD;
+    s_z[e] = (r < cnt && l < L) ? A.z[(r0 + r) * L + l] : 0.f;
+  }
+  for (int e = tid; e < MD_ROWS * MD_QLD; e += MD_THREADS) s_dq[e] = 0.f;
+  for (int e = tid; e < ncat * MD_H; e += MD_THREADS) s_acc[e] = 0.f;
+  if (tid < MD_ROWS) s_cat[tid] = (A.cov_cols && tid < cnt) ? A.cov_cols[r0 + tid] - L : -1;
 
-  // the thread's y2 / dh values: loaded ahead of the partial merge so their latency hides behind it
+  // the thread's y2 / dh values: loads issued ahead of the partial merge
   float yv2[MD_RPT], dv2[MD_RPT];
 #pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
@@ -413,11 +511,12 @@ __device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, float* s_cl) 
   }
   float S1, S2;
   md_merge_sum2(A.bpart2, md_clusters(A.B), s_scr, S1, S2);
-  if (blockIdx.x == 0 && rg == 0) {
+  if (tile == 0 && rg == 0) {
     if (A.dbeta2) A.dbeta2[col] = S1;
     if (A.dgamma2) A.dgamma2[col] = S2;
   }
   const float invB = 1.f / (float)A.B;
+  float dy[MD_RPT];  // dy2 of this thread's 8 rows (0 past the end of the batch)
   {
     const float mu = A.mean2[col], rs = A.rstd2[col], g = A.gamma2[col], b = A.beta2[col];
 #pragma unroll
@@ -429,64 +528,123 @@ __device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, float* s_cl) 
         const float d = (xhat * g + b > 0.f) ? dv2[i] : 0.f;
         v = rs * g * (d - S1 * invB - xhat * (S2 * invB));
       }
-      s_t[r * MD_H + col] = v;  // dy2
+      dy[i] = v;
+      s_t[r * MD_H + col] = v;
     }
   }
   __syncthreads();
-  // dWd[n][j] partial: thread (n = col, rg) handles columns j = rg, rg + 4, ...; j == ncols is the bias
-  for (int j = rg; j <= ncols; j += 4) {
-    float s = 0.f;
-    if (j < L) {
-      for (int r = 0; r < cnt; ++r) s = fmaf(s_t[r * MD_H + col], s_z[r * L + j], s);
-    } else if (j < ncols) {
-      for (int r = 0; r < cnt; ++r) s += (s_cat[r] == j) ? s_t[r * MD_H + col] : 0.f;
-    } else {
-      for (int r = 0; r < cnt; ++r) s += s_t[r * MD_H + col];
+  // ---- dWd[col][l] (latent block) and dbd[col]: own 8 rows from registers, z rows as broadcast 128-bit loads
+  {
+    float acc[LC + 1];
+#pragma unroll
+    for (int l = 0; l <= LC; ++l) acc[l] = 0.f;
+#pragma unroll
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
+      float zr[ZV * 4];
+#pragma unroll
+      for (int k = 0; k < ZV; ++k)
+        *reinterpret_cast<float4*>(zr + 4 * k) = *reinterpret_cast<const float4*>(s_z + r * MD_ZLD + 4 * k);
+#pragma unroll
+      for (int l = 0; l < LC; ++l) acc[l] = fmaf(dy[i], zr[l], acc[l]);
+      acc[LC] += dy[i];
     }
-    if (j < ncols) rec[col * ncols + j] = s;
-    else rec[MD_H * ncols + col] = s;
+#pragma unroll
+    for (int l = 0; l <= LC; ++l) s_red[(rg * (LC + 1) + l) * MD_H + col] = acc[l];
   }
-  // dz[r][l] = sum_n dy2[r][n] Wd[n][l]; then the latent backward per (r, l)
-  for (int o = tid; o < MD_ROWS * L; o += MD_THREADS) {
-    const int r = o / L, l = o % L;
-    float dm = 0.f, dt = 0.f;
-    if (r < cnt) {
-      float dz = 0.f;
-#pragma unroll 8
-      for (int n = 0; n < MD_H; ++n) dz = fmaf(s_t[r * MD_H + n], s_Wd[n * MD_WD_LD + l], dz);
+  // ---- dWd covariate columns: rows in order, row group rg owns the categories c with c % 4 == rg
+  if (ncat > 0) {
+    for (int r = 0; r < cnt; ++r) {
+      const int c = s_cat[r];
+      if (c >= 0 && (c & 3) == rg) s_acc[c * MD_H + col] += s_t[r * MD_H + col];
+    }
+  }
+  // ---- dz[r][l] = sum_n dy2[r][n] Wd[n][l]: warp w takes rows 2w, 2w + 1; lane = 4 consecutive n
+  float p0[LC], p1[LC];
+  {
+    const float4 d0 = *reinterpret_cast<const float4*>(s_t + (2 * warp) * MD_H + 4 * lane);
+    const float4 d1 = *reinterpret_cast<const float4*>(s_t + (2 * warp + 1) * MD_H + 4 * lane);
+#pragma unroll
+    for (int l = 0; l < LC; ++l) {
+      const float4 w = *reinterpret_cast<const float4*>(s_WdT + l * MD_WT_LD + 4 * lane);
+      p0[l] = fmaf(d0.w, w.w, fmaf(d0.z, w.z, fmaf(d0.y, w.y, d0.x * w.x)));
+      p1[l] = fmaf(d1.w, w.w, fmaf(d1.z, w.z, fmaf(d1.y, w.y, d1.x * w.x)));
+    }
+  }
+  __syncthreads();
+  for (int o = tid; o < (LC + 1) * MD_H; o += MD_THREADS) {
+    const int l = o >> 7, c = o & 127;
+    const float v = (s_red[(0 * (LC + 1) + l) * MD_H + c] + s_red[(1 * (LC + 1) + l) * MD_H + c]) +
+                    (s_red[(2 * (LC + 1) + l) * MD_H + c] + s_red[(3 * (LC + 1) + l) * MD_H + c]);
+    if (l == LC) rec[MD_H * ncols + c] = v;
+    else if (l < L) rec[c * ncols + l] = v;
+  }
+  for (int o = tid; o < ncat * MD_H; o += MD_THREADS) rec[(o & 127) * ncols + L + (o >> 7)] = s_acc[o];
+  __syncthreads();  // s_red is reused as the warps' transpose buffers
+  {
+    float* pp = s_red + warp * (L2C * MD_PP_LD);
+    const float t0 = md_lane_transpose_sum<LC>(p0, pp, lane);
+    const float t1 = md_lane_transpose_sum<LC>(p1, pp, lane);
+    if (lane < LC) {
+      s_dz[(2 * warp) * MD_ZLD + lane] = t0;
+      s_dz[(2 * warp + 1) * MD_ZLD + lane] = t1;
+    }
+  }
+  __syncthreads();
+  // ---- latent backward per (r, l)
+  for (int o = tid; o < MD_ROWS * MD_ZLD; o += MD_THREADS) {
+    const int r = o / MD_ZLD, l = o % MD_ZLD;
+    if (r < cnt && l < L) {
+      const float dz = s_dz[o];
       const int64_t i = (r0 + r) * L + l;
       const float m = A.q_m[i], v = A.q_v[i];
       const float gk = A.g_kl ? A.g_kl[r0 + r] : 0.f;
-      dm = dz + gk * m;
       const float sd = sqrtf(v);
       const float dv = dz * A.noise[i] / (2.f * sd) + gk * 0.5f * (1.f - 1.f / v);
-      dt = dv * (v - A.var_eps);
+      s_dq[r * MD_QLD + l] = dz + gk * m;
+      s_dq[r * MD_QLD + DT + l] = dv * (v - A.var_eps);
     }
-    s_dq[r * L2 + l] = dm;
-    s_dq[r * L2 + L + l] = dt;
+  }
+  // the thread's y1 / mask / a1 values for the two loops below: in flight across the barrier
+  float a1v[MD_RPT], y1v[MD_RPT];
+  uint8_t mk[MD_RPT];
+#pragma unroll
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
+    const int64_t o = (r0 + r) * MD_H + col;
+    a1v[i] = (r < cnt) ? A.a1[o] : 0.f;
+    y1v[i] = (r < cnt) ? A.y1[o] : 0.f;
+    mk[i] = (r < cnt && A.mask) ? A.mask[o] : (uint8_t)1;
   }
   __syncthreads();
-  // da1[r][c] = sum_j dq[r][j] W[j][c]; BN1 backward phase 1 on the fly
+  // ---- da1[r][col] = sum_j dq[r][j] W[j][col] (this thread's column of the head weights in registers); BN1
+  //      backward phase 1 on the fly
   {
+    float w[L2C];
+#pragma unroll
+    for (int l = 0; l < LC; ++l) {
+      w[l] = l < L ? A.Wm[l * MD_H + col] : 0.f;
+      w[LC + l] = l < L ? A.Wv[l * MD_H + col] : 0.f;
+    }
     const float mu = A.mean1[col], rs = A.rstd1[col], g = A.gamma1[col], b = A.beta1[col];
     float s1 = 0.f, s2 = 0.f;
-    float y1v[MD_RPT];
-    uint8_t mk[MD_RPT];
 #pragma unroll
     for (int i = 0; i < MD_RPT; ++i) {
       const int r = rg * MD_RPT + i;
-      const int64_t o = (r0 + r) * MD_H + col;
-      y1v[i] = (r < cnt) ? A.y1[o] : 0.f;
-      mk[i] = (r < cnt && A.mask) ? A.mask[o] : (uint8_t)1;
-    }
+      float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < MD_RPT; ++i) {
-      const int r = rg * MD_RPT + i;
+      for (int k = 0; k < QV; ++k) {
+        const float4 q = *reinterpret_cast<const float4*>(s_dq + r * MD_QLD + 4 * k);
+        const float qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int o = 4 * k + e;  // slot in the row: dm at 0 .. LC-1, dt at DT .. DT+LC-1
+          if (o < LC) s = fmaf(qq[e], w[o], s);
+          else if (o >= DT && o < DT + LC) s = fmaf(qq[e], w[LC + o - DT], s);
+        }
+      }
       if (r < cnt) {
-        float s = 0.f;
-        for (int j = 0; j < L2; ++j) s = fmaf(s_dq[r * L2 + j], s_W[j * 129 + col], s);
-        const int64_t o = (r0 + r) * MD_H + col;
-        A.da1[o] = s;
+        A.da1[(r0 + r) * MD_H + col] = s;
         const float xhat = (y1v[i] - mu) * rs;
         float d = s;
         if (A.mask) d = mk[i] ? d * A.drop_scale : 0.f;
@@ -495,73 +653,109 @@ __device__ __forceinline__ void mid_bwd1_body(const MidBwdArgs& A, float* s_cl) 
         s2 = fmaf(d, xhat, s2);
       }
     }
-    __syncthreads();  // all threads are done reading dy2 from s_t
     s_scr[rg * MD_H + col] = s1;
     s_scr[(4 + rg) * MD_H + col] = s2;
   }
-  // a1 tile -> s_t for the latent weight gradients
+  // ---- dW latent partials over the own 8 rows: acc[j] = sum_i dq[r_i][j] a1[r_i][col]
+  {
+    float acc[L2C];
 #pragma unroll
-  for (int i = 0; i < MD_RPT; ++i) {
-    const int r = rg * MD_RPT + i;
-    s_t[r * MD_H + col] = (r < cnt) ? A.a1[(r0 + r) * MD_H + col] : 0.f;
+    for (int j = 0; j < L2C; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < MD_RPT; ++i) {
+      const int r = rg * MD_RPT + i;
+#pragma unroll
+      for (int k = 0; k < QV; ++k) {
+        const float4 q = *reinterpret_cast<const float4*>(s_dq + r * MD_QLD + 4 * k);
+        const float qq[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int o = 4 * k + e;
+          if (o < LC) acc[o] = fmaf(qq[e], a1v[i], acc[o]);
+          else if (o >= DT && o < DT + LC) acc[LC + o - DT] = fmaf(qq[e], a1v[i], acc[LC + o - DT]);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < L2C; ++j) s_red[(rg * L2C + j) * MD_H + col] = acc[j];
   }
   __syncthreads();
   if (rg == 0) {
-    s_cl[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
-    s_cl[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
+    sums_out[col] = (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
+    sums_out[MD_H + col] = (s_scr[4 * MD_H + col] + s_scr[5 * MD_H + col]) + (s_scr[6 * MD_H + col] + s_scr[7 * MD_H + col]);
   }
-  // dW latent [j][c] partial = sum_r dq[r][j] a1[r][c]
+  // dW latent [j][c]: rows 0..L-1 = dWm, L..2L-1 = dWv (contiguous in the record)
   float* recL = rec + (int64_t)MD_H * ncols + MD_H;
-  for (int j = rg; j < L2; j += 4) {
-    float s = 0.f;
-    for (int r = 0; r < cnt; ++r) s = fmaf(s_dq[r * L2 + j], s_t[r * MD_H + col], s);
-    recL[j * MD_H + col] = s;  // rows 0..L-1 = dWm, L..2L-1 = dWv (contiguous)
+  for (int o = tid; o < L2C * MD_H; o += MD_THREADS) {
+    const int j = o >> 7, c = o & 127;
+    const int l = j < LC ? j : j - LC;
+    if (l < L) {
+      const float v = (s_red[(0 * L2C + j) * MD_H + c] + s_red[(1 * L2C + j) * MD_H + c]) +
+                      (s_red[(2 * L2C + j) * MD_H + c] + s_red[(3 * L2C + j) * MD_H + c]);
+      recL[((j < LC ? 0 : L) + l) * MD_H + c] = v;
+    }
   }
-  if (tid < L2) {
-    float s = 0.f;
-    for (int r = 0; r < cnt; ++r) s += s_dq[r * L2 + tid];
-    recL[(int64_t)L2 * MD_H + tid] = s;  // dbm | dbv
+  if (tid < 2 * L) {
+    const int o = tid < L ? tid : DT + tid - L;
+    float sb = 0.f;
+    for (int r = 0; r < cnt; ++r) sb += s_dq[r * MD_QLD + o];
+    recL[(int64_t)2 * L * MD_H + tid] = sb;  // dbm | dbv
   }
 }
 
+template <int LC>
 __global__ void __cluster_dims__(MD_CL, 1, 1) __launch_bounds__(MD_THREADS) mid_bwd1_kernel(MidBwdArgs A) {
   __shared__ float s_cl[2 * MD_H];
-  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_bwd1_body(A, s_cl);
+  if ((int64_t)blockIdx.x * MD_ROWS < A.B) mid_bwd1_body<LC>(A, blockIdx.x, s_cl);
   else if (threadIdx.x < 2 * MD_H) s_cl[threadIdx.x] = 0.f;  // a CTA that pads the grid
   md_cluster_sum2(s_cl, A.bpart1);
 }
 
 // stage 2: BN1 backward phase 2 -> dy1 (+ per-tile column sums = gradient of the encoder Linear bias)
-__global__ void __launch_bounds__(MD_THREADS)
-    mid_bwd2_kernel(const float* __restrict__ da1, const float* __restrict__ y1, const float* __restrict__ mean1,
-                    const float* __restrict__ rstd1, const float* __restrict__ gamma1, const float* __restrict__ beta1,
-                    const uint8_t* __restrict__ mask, float drop_scale, const float* __restrict__ bpart1, int64_t B,
-                    float* __restrict__ dy1, float* __restrict__ dgamma1, float* __restrict__ dbeta1,
-                    float* __restrict__ ppart, int64_t prec, int64_t dbe_off, float* __restrict__ absmax_part) {
-  __shared__ float s_scr[8 * MD_H];
+struct MidBwd2Args {
+  const float *da1, *y1, *mean1, *rstd1, *gamma1, *beta1;
+  const uint8_t* mask;
+  float drop_scale;
+  const float* bpart1;
+  int64_t B;
+  float *dy1, *dgamma1, *dbeta1, *ppart;
+  int64_t prec, dbe_off;
+  float* absmax_part;
+};
+__device__ __forceinline__ void mid_bwd2_body(const MidBwd2Args& A, const int64_t tile, float* s_scr /*[8][128]*/) {
   const int col = threadIdx.x & 127, rg = threadIdx.x >> 7;
-  const int64_t r0 = (int64_t)blockIdx.x * MD_ROWS;
-  const int cnt = (int)min((int64_t)MD_ROWS, B - r0);
-  float S1, S2;
-  md_merge_sum2(bpart1, md_clusters(B), s_scr, S1, S2);
-  if (blockIdx.x == 0 && rg == 0) {
-    if (dbeta1) dbeta1[col] = S1;
-    if (dgamma1) dgamma1[col] = S2;
+  const int64_t r0 = tile * MD_ROWS;
+  const int cnt = (int)min((int64_t)MD_ROWS, A.B - r0);
+  float yv[MD_RPT], dv[MD_RPT];  // loaded ahead of the merge
+  uint8_t mk[MD_RPT];
+#pragma unroll
+  for (int i = 0; i < MD_RPT; ++i) {
+    const int r = rg * MD_RPT + i;
+    const int64_t o = (r0 + r) * MD_H + col;
+    yv[i] = (r < cnt) ? A.y1[o] : 0.f;
+    dv[i] = (r < cnt) ? A.da1[o] : 0.f;
+    mk[i] = (r < cnt && A.mask) ? A.mask[o] : (uint8_t)1;
   }
-  const float invB = 1.f / (float)B;
-  const float mu = mean1[col], rs = rstd1[col], g = gamma1[col], b = beta1[col];
+  float S1, S2;
+  md_merge_sum2(A.bpart1, md_clusters(A.B), s_scr, S1, S2);
+  if (tile == 0 && rg == 0) {
+    if (A.dbeta1) A.dbeta1[col] = S1;
+    if (A.dgamma1) A.dgamma1[col] = S2;
+  }
+  const float invB = 1.f / (float)A.B;
+  const float mu = A.mean1[col], rs = A.rstd1[col], g = A.gamma1[col], b = A.beta1[col];
   float cs = 0.f, am = 0.f;
-#pragma unroll 4
+#pragma unroll
   for (int i = 0; i < MD_RPT; ++i) {
     const int r = rg * MD_RPT + i;
     if (r < cnt) {
       const int64_t o = (r0 + r) * MD_H + col;
-      const float xhat = (y1[o] - mu) * rs;
-      float d = da1[o];
-      if (mask) d = mask[o] ? d * drop_scale : 0.f;
+      const float xhat = (yv[i] - mu) * rs;
+      float d = dv[i];
+      if (A.mask) d = mk[i] ? d * A.drop_scale : 0.f;
       if (!(xhat * g + b > 0.f)) d = 0.f;
       const float v = rs * g * (d - S1 * invB - xhat * (S2 * invB));
-      dy1[o] = v;
+      A.dy1[o] = v;
       cs += v;
       am = fmaxf(am, fabsf(v));
     }
@@ -569,19 +763,201 @@ __global__ void __launch_bounds__(MD_THREADS)
   s_scr[rg * MD_H + col] = cs;
   __syncthreads();
   if (rg == 0)
-    ppart[(int64_t)blockIdx.x * prec + dbe_off + col] =
+    A.ppart[tile * A.prec + A.dbe_off + col] =
         (s_scr[col] + s_scr[MD_H + col]) + (s_scr[2 * MD_H + col] + s_scr[3 * MD_H + col]);
-  if (absmax_part) {  // max |dy1| of this tile (operand scale of the tensor-core dW kernel downstream)
-    __syncthreads();
+  __syncthreads();
+  if (A.absmax_part) {  // max |dy1| of this tile (operand scale of the tensor-core dW kernel downstream)
     am = warp_max(am);
     if ((threadIdx.x & 31) == 0) s_scr[threadIdx.x >> 5] = am;
     __syncthreads();
     if (threadIdx.x < 32) {
       am = threadIdx.x < MD_THREADS / 32 ? s_scr[threadIdx.x] : 0.f;
       am = warp_max(am);
-      if (threadIdx.x == 0) absmax_part[blockIdx.x] = am;
+      if (threadIdx.x == 0) A.absmax_part[tile] = am;
+    }
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(MD_THREADS) mid_bwd2_kernel(MidBwd2Args A) {
+  __shared__ float s_scr[8 * MD_H];
+  mid_bwd2_body(A, blockIdx.x, s_scr);
+}
+
+// ---------------------------------------------------------------------------------------
+// One cooperative launch per direction: the same tile bodies, phases separated by grid barriers instead of kernel
+// boundaries.  Every CTA walks its tiles (tile = blockIdx.x, + gridDim.x, ...) in every phase; the batch statistics
+// cross CTAs as per-tile partials -> per-group partials (groups of MD_CL tiles, merged by one CTA per group with
+// the arithmetic of the cluster merge above: results are bit-identical to the multi-launch path) -> redundant
+// merge of the T / 8 group partials in every consumer.  Launched with cudaLaunchAttributeCooperative (all CTAs
+// co-resident: 2 per SM), also inside captured graphs.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ void md_group_stats(const float* tpart /*[T][2][128]*/, int64_t T, int64_t B, int64_t g,
+                                               float* gpart /*[groups][2][128]*/) {
+  if (threadIdx.x < MD_H) {
+    const int col = threadIdx.x;
+    const int64_t r0c = g * MD_CL * MD_ROWS;
+    float n[MD_CL], m[MD_CL], q[MD_CL], ntot = 0.f, msum = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) {
+      const int64_t t = g * MD_CL + k;
+      n[k] = (float)max((int64_t)0, min((int64_t)MD_ROWS, B - (r0c + (int64_t)k * MD_ROWS)));
+      m[k] = t < T ? __ldcg(tpart + (t * 2 + 0) * MD_H + col) : 0.f;
+      q[k] = t < T ? __ldcg(tpart + (t * 2 + 1) * MD_H + col) : 0.f;
+      ntot += n[k];
+      msum = fmaf(n[k], m[k], msum);
+    }
+    const float mean = msum / ntot;
+    float m2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) {
+      const float d = m[k] - mean;
+      m2 += fmaf(n[k], d * d, q[k]);
+    }
+    gpart[(g * 2 + 0) * MD_H + col] = mean;
+    gpart[(g * 2 + 1) * MD_H + col] = m2;
+  }
+}
+__device__ __forceinline__ void md_group_sum2(const float* tpart, int64_t T, int64_t g, float* gpart) {
+  if (threadIdx.x < 2 * MD_H) {
+    const int col = threadIdx.x & 127, q = threadIdx.x >> 7;
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < MD_CL; ++k) {
+      const int64_t t = g * MD_CL + k;
+      acc += t < T ? __ldcg(tpart + (t * 2 + q) * MD_H + col) : 0.f;
+    }
+    gpart[(g * 2 + q) * MD_H + col] = acc;
+  }
+}
+
+struct MidFwdCoop {
+  MidFwdArgs a;
+  MidFwd2Args a2;
+  float* tpart;  // [T][2][128]
+};
+template <int LC>
+__global__ void __launch_bounds__(MD_THREADS) mid_fwd_coop_kernel(MidFwdCoop C) {
+  extern __shared__ __align__(16) float sm[];
+  cg::grid_group grid = cg::this_grid();
+  const int64_t B = C.a.B, T = (B + MD_ROWS - 1) / MD_ROWS, NG = md_clusters(B);
+  for (int64_t t = blockIdx.x; t < T; t += gridDim.x) {
+    mid_fwd_body<LC>(C.a, t, C.tpart + t * 2 * MD_H);
+    __syncthreads();
+  }
+  grid.sync();
+  for (int64_t g = blockIdx.x; g < NG; g += gridDim.x) md_group_stats(C.tpart, T, B, g, C.a.part2);
+  grid.sync();
+  for (int64_t t = blockIdx.x; t < T; t += gridDim.x) {
+    mid_fwd2_body(C.a2, t, sm);
+    __syncthreads();
+  }
+}
+
+struct MidBwdCoop {
+  MidBwd0Args a0;
+  MidBwdArgs a1;
+  MidBwd2Args a2;
+  float *tpart, *bpart2, *bpart1;
+  ColsumSegs segs;
+};
+template <int LC>
+__global__ void __launch_bounds__(MD_THREADS) mid_bwd_coop_kernel(MidBwdCoop C) {
+  extern __shared__ __align__(16) float sm[];
+  cg::grid_group grid = cg::this_grid();
+  const int64_t B = C.a1.B, T = (B + MD_ROWS - 1) / MD_ROWS, NG = md_clusters(B);
+  for (int64_t t = blockIdx.x; t < T; t += gridDim.x) mid_bwd0_body(C.a0, t, sm, C.tpart + t * 2 * MD_H);
+  grid.sync();
+  for (int64_t g = blockIdx.x; g < NG; g += gridDim.x) md_group_sum2(C.tpart, T, g, C.bpart2);
+  grid.sync();
+  for (int64_t t = blockIdx.x; t < T; t += gridDim.x) {
+    mid_bwd1_body<LC>(C.a1, t, C.tpart + t * 2 * MD_H);
+    __syncthreads();
+  }
+  grid.sync();
+  for (int64_t g = blockIdx.x; g < NG; g += gridDim.x) md_group_sum2(C.tpart, T, g, C.bpart1);
+  grid.sync();
+  for (int64_t t = blockIdx.x; t < T; t += gridDim.x) mid_bwd2_body(C.a2, t, sm);
+  grid.sync();
+  // column sums over the T per-tile records (the arithmetic of colsum_kernel: record t goes to group t % 32, groups
+  // are summed serially, the 32 group sums merged in order), 32 columns per unit
+  {
+    float(*red)[33] = reinterpret_cast<float(*)[33]>(sm);
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // ty < 16: this thread runs groups ty and ty + 16
+    const int64_t n = C.a1.prec, stride = C.a1.prec;
+    const float* part = C.a1.ppart;
+    for (int64_t u = blockIdx.x; u * 32 < n; u += gridDim.x) {
+      const int64_t e = u * 32 + tx;
+      float sa = 0.f, sb = 0.f;
+      if (e < n) {
+#pragma unroll 4
+        for (int64_t t = ty; t < T; t += 32) {
+          sa += __ldcg(part + t * stride + e);
+          if (t + 16 < T) sb += __ldcg(part + (t + 16) * stride + e);
+        }
+      }
+      red[ty][tx] = sa;
+      red[ty + 16][tx] = sb;
+      __syncthreads();
+      if (ty == 0 && e < n) {
+        float tot = 0.f;
+#pragma unroll
+        for (int g = 0; g < 32; ++g) tot += red[g][tx];
+        for (int i = 0; i < C.segs.n; ++i)
+          if (C.segs.dst[i] && e >= C.segs.begin[i] && e < C.segs.end[i]) C.segs.dst[i][e - C.segs.begin[i]] = tot;
+      }
+      __syncthreads();
     }
   }
+}
+
+// grid of a cooperative launch: every CTA resident at once (occupancy x SMs, cached per device), at most `want`
+#define SCVI_CUDA_OK(call)                                                         \
+  do {                                                                             \
+    cudaError_t e__ = (call);                                                      \
+    if (e__ != cudaSuccess) {                                                      \
+      scvi::set_error("scvi_mid: %s failed: %s", #call, cudaGetErrorString(e__)); \
+      return SCVI_ECUDA;                                                           \
+    }                                                                              \
+  } while (0)
+static int md_coop_grid(const void* kernel, size_t smem, int64_t want, std::atomic<int> (&cache)[64], int* grid_out) {
+  int dev = 0;
+  SCVI_CUDA_OK(cudaGetDevice(&dev));
+  std::atomic<int>& c = cache[dev & 63];
+  int cap = c.load(std::memory_order_relaxed);
+  if (cap == 0) {
+    int coop = 0, sms = 0, nb = 0;
+    SCVI_CUDA_OK(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    SCVI_CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    SCVI_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, MD_THREADS, smem));
+    cap = coop ? nb * sms : -1;
+    c.store(cap, std::memory_order_relaxed);
+  }
+  if (cap <= 0) {
+    set_error("scvi_mid: cooperative launch unavailable on this device");
+    return SCVI_EUNSUPPORTED;
+  }
+  *grid_out = (int)std::min<int64_t>(want, cap);
+  return SCVI_OK;
+}
+template <typename Args>
+static int md_coop_launch(void (*kernel)(Args), const Args& args, int grid, size_t smem, cudaStream_t st) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(MD_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr{};
+  attr.id = cudaLaunchAttributeCooperative;
+  attr.val.cooperative = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  SCVI_CUDA_OK(cudaLaunchKernelEx(&cfg, kernel, args));
+  return SCVI_OK;
+}
+// SCVI_MID_COOP=0 selects the multi-launch path (kept for A/B measurements and as the reference of the bit-equality test)
+static bool md_use_coop() {
+  const char* e = getenv("SCVI_MID_COOP");  // read per call: the test flips it inside one process
+  return e && e[0] == '1';
 }
 
 }  // namespace scvi
@@ -593,7 +969,7 @@ int64_t scvi_mid_n_tiles(int64_t B) { return scvi::cdiv(B, scvi::MD_ROWS); }
 int64_t scvi_mid_ws_bytes(int64_t B, int64_t L, int64_t ncols) {
   const int64_t T = scvi::cdiv(B, scvi::MD_ROWS);
   const int64_t prec = scvi::md_rec_floats((int)ncols, (int)L);
-  return 4 * (3 * T * 2 * scvi::MD_H + B * scvi::MD_H + (T + 1) * prec) + 1024;
+  return 4 * (4 * T * 2 * scvi::MD_H + B * scvi::MD_H + (T + 1) * prec) + 1024;
 }
 
 int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t H, int64_t L, const float* gamma1,
@@ -622,14 +998,33 @@ int scvi_mid_fwd(const float* y1, const float* bn_partials1, int64_t B, int64_t 
   A.var_eps = var_eps; A.Wd = Wd; A.bd = bd; A.cov_cols = cov_cols; A.ncols = (int)n_w_cols; A.bn_eps = bn_eps;
   A.momentum = momentum; A.B = B; A.L = (int)L; A.a1 = a1; A.q_m = q_m; A.q_v = q_v; A.z = z; A.kl = kl; A.y2 = y2;
   A.part2 = part2; A.mean1 = mean1; A.rstd1 = rstd1;
-  const size_t smem = sizeof(float) * ((size_t)MD_ROWS * MD_H + 2 * MD_LMAX * 129 + MD_H * MD_WD_LD +
-                                       MD_ROWS * 2 * MD_LMAX + 2 * MD_ROWS * MD_LMAX + 12 * MD_H);
-  static std::atomic<uint64_t> optin{0};
-  if (int rc = smem_optin((const void*)mid_fwd_kernel, (int)smem, optin, "scvi_mid_fwd")) return rc;
-  mid_fwd_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
+  const size_t smem = sizeof(float) * md_fwd_smem_floats((int)L, (int)n_w_cols);
+  // the opt-in is made once per device: for the largest covariate block this entry point accepts
+  const size_t smem_max = sizeof(float) * md_fwd_smem_floats(L == 10 ? 10 : 1, MD_WD_LD - 1);
+  MidFwd2Args A2;
+  A2.y2 = y2; A2.part2 = part2; A2.gamma2 = gamma2; A2.beta2 = beta2; A2.rm2 = running_mean2; A2.rv2 = running_var2;
+  A2.bn_eps = bn_eps; A2.momentum = momentum; A2.B = B; A2.h = h; A2.mean2 = mean2; A2.rstd2 = rstd2;
+  auto kc = (L == 10) ? mid_fwd_coop_kernel<10> : mid_fwd_coop_kernel<16>;
+  auto k1 = (L == 10) ? mid_fwd_kernel<10> : mid_fwd_kernel<16>;
+  const int which = L == 10 ? 0 : 1;  // per-kernel "configured" masks / caches
+  if (md_use_coop()) {
+    MidFwdCoop C;
+    C.a = A; C.a2 = A2;
+    C.tpart = (float*)ws + 3 * T * 2 * MD_H + B * MD_H + (T + 1) * md_rec_floats((int)n_w_cols, (int)L);
+    static std::atomic<uint64_t> optin_c[2];
+    if (int rc = smem_optin((const void*)kc, (int)smem_max, optin_c[which], "scvi_mid_fwd")) return rc;
+    int grid = 0;
+    static std::atomic<int> cap_c[2][64];
+    if (int rc = md_coop_grid((const void*)kc, smem, T, cap_c[which], &grid)) return rc;
+    if (int rc = md_coop_launch(kc, C, grid, smem, st)) return rc;
+    SCVI_LAUNCH_CHECK("scvi_mid_fwd(cooperative)");
+    return SCVI_OK;
+  }
+  static std::atomic<uint64_t> optin[2];
+  if (int rc = smem_optin((const void*)k1, (int)smem_max, optin[which], "scvi_mid_fwd")) return rc;
+  k1<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
   SCVI_LAUNCH_CHECK("scvi_mid_fwd(stage 1)");
-  mid_fwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(y2, part2, gamma2, beta2, running_mean2, running_var2, bn_eps,
-                                                     momentum, B, h, mean2, rstd2);
+  mid_fwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(A2);
   SCVI_LAUNCH_CHECK("scvi_mid_fwd(stage 2)");
   return SCVI_OK;
 }
@@ -660,39 +1055,60 @@ int scvi_mid_bwd(const float* dh, const float* y2, const float* mean2, const flo
   float* bpart1 = bpart2 + T * 2 * MD_H;
   float* da1 = bpart1 + T * 2 * MD_H;
   float* ppart = da1 + B * MD_H;
-  mid_bwd0_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, 0, st>>>(dh, y2, mean2, rstd2, gamma2, beta2, B, bpart2);
-  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 0)");
+  MidBwd0Args A0;
+  A0.dh = dh; A0.y2 = y2; A0.mean2 = mean2; A0.rstd2 = rstd2; A0.gamma2 = gamma2; A0.beta2 = beta2; A0.B = B;
   MidBwdArgs A;
   A.dh = dh; A.y2 = y2; A.mean2 = mean2; A.rstd2 = rstd2; A.gamma2 = gamma2; A.beta2 = beta2; A.bpart2 = bpart2;
   A.z = z; A.Wd = Wd; A.cov_cols = cov_cols; A.ncols = ncols; A.g_kl = g_kl; A.q_m = q_m; A.q_v = q_v; A.noise = noise;
   A.var_eps = var_eps; A.Wm = Wm; A.Wv = Wv; A.a1 = a1; A.y1 = y1; A.mean1 = mean1; A.rstd1 = rstd1; A.gamma1 = gamma1;
   A.beta1 = beta1; A.mask = drop_mask; A.drop_scale = drop_scale; A.B = B; A.L = (int)L; A.da1 = da1; A.bpart1 = bpart1;
   A.ppart = ppart; A.prec = prec; A.dgamma2 = dgamma2; A.dbeta2 = dbeta2;
-  const size_t smem = sizeof(float) * ((size_t)MD_ROWS * MD_H + 2 * MD_LMAX * 129 + MD_H * MD_WD_LD + MD_ROWS * MD_LMAX +
-                                       MD_ROWS * 2 * MD_LMAX + 12 * MD_H);
-  static std::atomic<uint64_t> optin{0};
-  if (int rc = smem_optin((const void*)mid_bwd1_kernel, (int)smem, optin, "scvi_mid_bwd")) return rc;
-  mid_bwd1_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
-  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 1)");
   const int64_t dbe_off = prec - MD_H;
-  mid_bwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(da1, y1, mean1, rstd1, gamma1, beta1, drop_mask, drop_scale,
-                                                     bpart1, B, dy1, dgamma1, dbeta1, ppart, prec, dbe_off,
-                                                     dy1_absmax_part);
-  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 2)");
+  MidBwd2Args A2;
+  A2.da1 = da1; A2.y1 = y1; A2.mean1 = mean1; A2.rstd1 = rstd1; A2.gamma1 = gamma1; A2.beta1 = beta1; A2.mask = drop_mask;
+  A2.drop_scale = drop_scale; A2.bpart1 = bpart1; A2.B = B; A2.dy1 = dy1; A2.dgamma1 = dgamma1; A2.dbeta1 = dbeta1;
+  A2.ppart = ppart; A2.prec = prec; A2.dbe_off = dbe_off; A2.absmax_part = dy1_absmax_part;
   // one deterministic column sum over the per-tile records, scattered to the 7 gradient tensors
   ColsumSegs segs{};
-  int64_t o = 0;
-  auto add = [&](float* dst, int64_t n) {
-    segs.dst[segs.n] = dst; segs.begin[segs.n] = o; segs.end[segs.n] = o + n; ++segs.n;
-    o += n;
-  };
-  add(dWd, (int64_t)MD_H * ncols);
-  add(dbd, MD_H);
-  add(dWm, L * MD_H);
-  add(dWv, L * MD_H);
-  add(dbm, L);
-  add(dbv, L);
-  add(db_enc, MD_H);
+  {
+    int64_t o = 0;
+    auto add = [&](float* dst, int64_t n) {
+      segs.dst[segs.n] = dst; segs.begin[segs.n] = o; segs.end[segs.n] = o + n; ++segs.n;
+      o += n;
+    };
+    add(dWd, (int64_t)MD_H * ncols);
+    add(dbd, MD_H);
+    add(dWm, L * MD_H);
+    add(dWv, L * MD_H);
+    add(dbm, L);
+    add(dbv, L);
+    add(db_enc, MD_H);
+  }
+  const size_t smem = sizeof(float) * md_bwd_smem_floats((int)L, ncols);
+  const size_t smem_max = sizeof(float) * md_bwd_smem_floats(L == 10 ? 10 : 1, MD_WD_LD - 1);
+  auto kc = (L == 10) ? mid_bwd_coop_kernel<10> : mid_bwd_coop_kernel<16>;
+  auto k1 = (L == 10) ? mid_bwd1_kernel<10> : mid_bwd1_kernel<16>;
+  const int which = L == 10 ? 0 : 1;
+  if (md_use_coop()) {
+    MidBwdCoop C;
+    C.a0 = A0; C.a1 = A; C.a2 = A2; C.tpart = ppart + (T + 1) * prec; C.bpart2 = bpart2; C.bpart1 = bpart1; C.segs = segs;
+    static std::atomic<uint64_t> optin_c[2];
+    if (int rc = smem_optin((const void*)kc, (int)smem_max, optin_c[which], "scvi_mid_bwd")) return rc;
+    int grid = 0;
+    static std::atomic<int> cap_c[2][64];
+    if (int rc = md_coop_grid((const void*)kc, smem, std::max<int64_t>(T, cdiv(prec, 32)), cap_c[which], &grid)) return rc;
+    if (int rc = md_coop_launch(kc, C, grid, smem, st)) return rc;
+    SCVI_LAUNCH_CHECK("scvi_mid_bwd(cooperative)");
+    return SCVI_OK;
+  }
+  mid_bwd0_kernel<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, 0, st>>>(A0, bpart2);
+  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 0)");
+  static std::atomic<uint64_t> optin[2];
+  if (int rc = smem_optin((const void*)k1, (int)smem_max, optin[which], "scvi_mid_bwd")) return rc;
+  k1<<<(unsigned)(md_clusters(B) * MD_CL), MD_THREADS, smem, st>>>(A);
+  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 1)");
+  mid_bwd2_kernel<<<(unsigned)T, MD_THREADS, 0, st>>>(A2);
+  SCVI_LAUNCH_CHECK("scvi_mid_bwd(stage 2)");
   return launch_colsum(ppart, T, prec, prec, segs, st, "scvi_mid_bwd(reduce)");
 }
 }

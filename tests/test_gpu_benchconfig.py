@@ -169,3 +169,38 @@ def test_graph_replay_equals_eager_sequence_bitwise(G, nb, lik):
     for a, b in zip(res[0], res[1], strict=True):
         assert torch.equal(a, b)
     assert int(res[0][7][0]) == 4 and torch.isfinite(res[0][8]).all()
+
+
+@pytest.mark.parametrize("B_,graph", [(8192, True), (8192, False), (1000, False), (100, False), (20000, False)])
+def test_cooperative_middle_equals_multi_launch_middle_bitwise(B_, graph, monkeypatch):
+    """`scvi_mid_fwd` / `scvi_mid_bwd` as one cooperative launch each (grid barriers between the phases) against the
+    multi-launch path they replace (SCVI_MID_COOP=0): same tile bodies, same merge arithmetic, so parameters, Adam
+    moments, BatchNorm buffers and losses are identical bit for bit -- at the benched size (with and without graph
+    replay), ragged sizes, and a minibatch with more row tiles than co-resident CTAs (20000 rows = 625 tiles)."""
+    from scvi_tools_b200.data import DeviceResidentCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+    import scvi_tools_b200 as S
+
+    dev = torch.device("cuda:0")
+    G, nb = 512, 5
+    n_rows = max(4 * B_, 4096)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    X = torch.poisson(torch.rand(n_rows, G, device=dev, generator=gen) * 6.0, generator=gen)
+    batch = torch.arange(n_rows, device=dev) * nb // n_rows
+    g = torch.Generator().manual_seed(2)
+    idxs = [torch.randperm(n_rows, generator=g)[:B_].sort().values.to(dev) for _ in range(4)]
+    res = []
+    for coop in ("0", "1"):
+        monkeypatch.setenv("SCVI_MID_COOP", coop)
+        torch.manual_seed(7)
+        m = S.VAE(n_input=G, n_batch=nb, gene_likelihood="zinb", n_hidden=128, n_latent=10, precision=1).train()
+        plan = FusedTrainingPlan(m, DeviceResidentCounts(X, batch=batch, device=dev), batch_size=B_,
+                                 n_epochs_kl_warmup=None, max_kl_weight=0.5, use_cuda_graph=graph, seed=3)
+        plan.set_epoch(0)
+        losses = [plan.training_step(ix).clone() for ix in idxs]
+        torch.cuda.synchronize()
+        res.append((plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.bn1_rm.clone(), plan.bn1_rv.clone(),
+                    plan.bn2_rm.clone(), plan.bn2_rv.clone(), torch.stack(losses), plan.g.clone()))
+    for a, b in zip(res[0], res[1], strict=True):
+        assert torch.equal(a, b), float((a - b).abs().max())
+    assert torch.isfinite(res[1][7]).all() and float(res[1][0].abs().sum()) > 0
