@@ -67,6 +67,8 @@ def parse():
     ap.add_argument("--e2e-dtype", default="auto", choices=["auto", "u16", "f32"],
                     help="host count type of the e2e leg: auto = narrowest lossless (uint8 / uint16 / float32)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--resident", default="auto", choices=["auto", "u8", "f32"],
+                    help="type of the HBM-resident count matrix: uint8 when every count is < 256 (auto), or fp32")
     ap.add_argument("--value-only", action="store_true",
                     help="tuning aid: time the resident-counts step only (no e2e / roofline / baseline legs)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
@@ -318,8 +320,8 @@ def profile_step(plan, a, reps=20):
         plan._prologue(st)  # the step without the data-parallel all-reduce (this leg runs on rank 0 only)
         plan._forward_backward(st)
         plan._adam(st)
-        call("scvi_gather_rows", X.data_ptr(), X.shape[0], plan.G, X.stride(0), plan.idx.data_ptr(), plan.B,
-             out.data_ptr(), plan.G, st)
+        call("scvi_gather_rows_u8" if X.dtype == torch.uint8 else "scvi_gather_rows", X.data_ptr(), X.shape[0], plan.G,
+             X.stride(0), plan.idx.data_ptr(), plan.B, out.data_ptr(), plan.G, st)
         n = lib.scvi_profile_end(buf, len(buf))
         if n < 0:
             raise RuntimeError("scvi_profile_end: " + lib.scvi_last_error_string().decode())
@@ -402,6 +404,16 @@ def timed_blocks(step, K, R, barrier, world, dev):
     return out
 
 
+def resident_type(a, X):
+    """"u8" when the resident matrix can be kept as uint8 counts (tcgen05 kernels, every count < 256), else None."""
+    if a.resident == "f32" or a.precision != "tc":
+        return None
+    ok = float(X.max()) < 256.0
+    if a.resident == "u8" and not ok:
+        raise SystemExit("--resident u8: counts >= 256 present")
+    return "u8" if ok else None
+
+
 def make_plan(a, data, B, pg, genes=None, likelihood=None, batches=None, seed=0):
     import scvi_tools_b200 as S
     from scvi_tools_b200.train import FusedTrainingPlan
@@ -463,7 +475,11 @@ def run_b200_arm(a):
 
     X = synth_counts_device(a.cells, a.genes, dev, seed=rank, zero_frac=a.zero_frac)
     batch = (torch.arange(a.cells, device=dev) * a.batches // a.cells)
-    data = DeviceResidentCounts(X, batch=batch, device=dev)
+    compress = resident_type(a, X)
+    data = DeviceResidentCounts(X, batch=batch, device=dev, compress=compress)
+    if compress:
+        del X
+        X = data.X
     plan = make_plan(a, data, B, pg)
     order, n_chunks = minibatch_order(a.cells, B, dev, sort=not a.unsorted_batches)
 
@@ -531,7 +547,8 @@ def run_b200_arm(a):
     # straight from the mapped host pages, or by the host threads + a copy-engine H2D), are expanded to fp32
     # rows on the device, the fused step runs, and the loss is copied back and read on the host every step.
     n_host_rows = a.cells
-    hdt = torch.float32 if a.e2e_dtype == "f32" else narrowest_count_dtype(X[: min(a.cells, 262144)])
+    hdt = (torch.float32 if a.e2e_dtype == "f32" else torch.uint8 if X.dtype == torch.uint8
+           else narrowest_count_dtype(X[: min(a.cells, 262144)]))
     if a.e2e_dtype == "u16" and hdt == torch.uint8:
         hdt = torch.uint16
     if hdt != torch.float32 and float(X.max()) >= (256 if hdt == torch.uint8 else 65536):
@@ -591,8 +608,11 @@ def run_b200_arm(a):
         return order_host[j * B : (j + 1) * B]
 
     legs = {}
+    # uint8 host counts + tcgen05 kernels: the H2D copy lands in the uint8 rows the step reads (no expansion kernel)
+    compact = hdt == torch.uint8 and a.precision == "tc" and a.resident != "f32"
     for name, devg in (("device_gather", True), ("host_gather", False)):
-        feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg)
+        feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg,
+                                    compact_stage=compact and not devg)
         if devg and not feeder.device_gather:
             continue
         med, allb = run_e2e(feeder, lambda slot, i, f=feeder: f.submit(slot, rows=rows_of(i)))
@@ -603,7 +623,7 @@ def run_b200_arm(a):
     pre_x = [host_mat[i * B : (i + 1) * B].clone().pin_memory() for i in range(n_pre)]
     pre_b = [host_batch[i * B : (i + 1) * B].clone().pin_memory() for i in range(n_pre)]
     feeder = HostStreamedCounts(torch.zeros(1, a.genes), batch=None, batch_size=B, device=dev, dtype=hdt,
-                                device_gather=False)
+                                device_gather=False, compact_stage=compact)
     med, allb = run_e2e(feeder, lambda slot, i: feeder.submit(slot, host_x=pre_x[i % n_pre], host_b=pre_b[i % n_pre]))
     legs["preformed_minibatches"] = {"cells_per_s": K * B * world / (med / 1e3), "ms_per_step": med / K, "blocks_ms": allb}
     best = max((k for k in legs if k != "preformed_minibatches"), key=lambda k: legs[k]["cells_per_s"])
@@ -613,7 +633,8 @@ def run_b200_arm(a):
            "routes": legs, "host_matrix_rows": n_host_rows,
            "how": "whole count matrix in pinned host memory (narrowest lossless count type); per step: random row ids "
                   "-> rows over PCIe (device_gather: a gather kernel reads the mapped host pages; host_gather: "
-                  "index_select on the host threads + cudaMemcpyAsync), exact expansion to fp32 rows, fused step, "
+                  "index_select on the host threads + cudaMemcpyAsync; uint8 counts land in the uint8 staging rows the "
+                  "tcgen05 kernels read, device_gather expands to fp32 rows), fused step, "
                   "loss D2H each step read on the host one step behind the launch; preformed_minibatches = the "
                   "round-1 figure (no per-step row gather), kept for continuity"}
     del host_mat, pre_x
@@ -681,7 +702,8 @@ def run_b200_arm(a):
         a3 = copy.copy(a)
         a3.genes, a3.likelihood, a3.batches = 4000, "nb", 32
         X3 = synth_counts_device(a.cells, 4000, dev, seed=50 + rank, zero_frac=a.zero_frac)
-        d3 = DeviceResidentCounts(X3, batch=torch.arange(a.cells, device=dev) * 32 // a.cells, device=dev)
+        d3 = DeviceResidentCounts(X3, batch=torch.arange(a.cells, device=dev) * 32 // a.cells, device=dev,
+                                  compress=resident_type(a, X3))
         p3 = make_plan(a3, d3, B, pg, seed=3)
         extras["c3_1Mx4000_nb_32batches"] = quick_rate(p3, a.cells, B, dev, K, 3, W, barrier, world)
         extras["c3_1Mx4000_nb_32batches"]["workload"] = workload_name(a3)
@@ -695,7 +717,9 @@ def run_b200_arm(a):
             "warmup": W, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic", "config": cfg,
             "details": {"cache": "inputs larger than L2: rows gathered at random from the HBM-resident count matrix "
-                                 f"({a.cells * a.genes * 4 / 1e9:.1f} GB)",
+                                 f"({a.cells * a.genes * (1 if compress else 4) / 1e9:.1f} GB)",
+                        "resident_counts": ("uint8 (every count < 256; the kernels' arithmetic is the fp32 path's, "
+                                            "bit for bit)" if compress else "float32"),
                         "precision": ("tcgen05 fp16 hi/lo split GEMMs, fp32 accumulate (fp32-grade, parity-tested)"
                                       if a.precision == "tc" else "fp32 FFMA GEMMs"), "cuda_graph": True,
                         "timing": f"median of {R} blocks of exactly {K} steps, each between barrier+synchronize, "

@@ -58,6 +58,9 @@ extern "C" {
  *                   loads): 1 byte per count from HBM.  Training kernels only (SCVI_PREC_TC with dh / dW). */
 #define SCVI_X_INTEGER 0x200
 #define SCVI_X_U8 0x400
+#define SCVI_LIN_X_U8 SCVI_X_U8 /* scvi_linear_fwd / _bwd with SCVI_LIN_TC: `x` points to uint8 counts, ldx in bytes,
+                                   rows 16-byte aligned; the converters look log1p(count) up in a 256-entry table
+                                   built from the fp32 path's own arithmetic (results bit-identical to fp32 counts) */
 
 int scvi_b200_abi_version(void); /* 3 */
 const char* scvi_last_error_string(void);
@@ -151,7 +154,7 @@ int scvi_colsum_partials(const float* partials, int64_t n_tiles, int64_t N, floa
  * cov_cols[b, c] is the absolute column of W (>= K) selected by covariate c of cell b.
  * bn_partials (nullable) [ceil(B/SCVI_BN_TILE), 2, N] receives per-tile (mean, M2) of y. */
 int64_t scvi_linear_fwd_ws_bytes(int64_t B, int64_t K, int64_t N, int flags); /* 0 unless SCVI_LIN_TC */
-int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+int scvi_linear_fwd(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols,
                     int n_cov, int flags, float* y, int64_t ldy, float* library, float* bn_partials,
                     void* ws, void* stream);
@@ -163,7 +166,7 @@ int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
  * dy_absmax_part (nullable; used by SCVI_LIN_TC): n_absmax_part floats whose maximum is max |dy|
  * (as produced by scvi_mid_bwd) -- saves the pass over dy that fixes the operand scale. */
 int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols);
-int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+int scvi_linear_bwd(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov,
                     int flags, const float* dy, int64_t lddy, float* dW, float* db, float* dx,
                     int64_t lddx, const float* dy_absmax_part, int64_t n_absmax_part, void* ws,

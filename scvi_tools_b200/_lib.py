@@ -124,6 +124,7 @@ def query(name: str, *args) -> int:
 BN_TILE = 64
 LIK_NB, LIK_ZINB = 0, 1
 LIN_LOG1P, LIN_LIBRARY, LIN_TC = 1, 2, 4
+LIN_X_U8 = 0x400  # scvi_linear_fwd / _bwd: uint8 counts (with LIN_TC)
 PREC_FP32, PREC_TC = 0, 1
 PREC_PREPACKED = 0x100
 X_INTEGER, X_U8 = 0x200, 0x400  # count-operand kind OR-ed into `precision` (SCVI_X_INTEGER / SCVI_X_U8)

@@ -64,7 +64,8 @@ struct EnSmem {
   static constexpr uint32_t BARS = RAW + EN_NS * EN_RAW1;
   static constexpr uint32_t TMEM_PTR = BARS + 32 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;         // [4][128] row-sum partials
-  static constexpr uint32_t TOTAL = RED + 4 * TC_M * 4;
+  static constexpr uint32_t LUT = RED + 4 * TC_M * 4;    // 256 x (hi | lo << 16), uint8 counts
+  static constexpr uint32_t TOTAL = LUT + 256 * 4;
 };
 static_assert(EN_RAW2 <= EN_RAW1, "raw stage size");
 
@@ -79,6 +80,45 @@ __device__ __forceinline__ void en_load8(const float* __restrict__ xrow, int64_t
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = (rvalid && gb + i < G) ? __ldg(xrow + gb + i) : 0.f;
   }
+}
+
+// ---- uint8 counts (SCVI_LIN_X_U8): the loaders move 1 byte per count (128-byte row segments, 8 x cp.async 16 B,
+// four rows per warp instruction) and the converters replace log1p + scale + clamp + fp16 split by ONE shared-memory
+// look-up per count: lut[c] = (hi | lo << 16) of exactly the value the fp32 path computes for the count c (built with
+// the same flog / split8 at kernel start: the MMA operands, hence the results, are bit-identical to the fp32 path).
+constexpr uint32_t EN_RAW8_ROW = TC_M + 16;  // 128 counts + 16 B pad (cp.async needs 16-byte aligned rows)
+__device__ __forceinline__ void en_build_lut(uint32_t* lut, int log1p_in, int tid, int nthreads) {
+  const float sX = tc::pow2i(EN_X_SCALE_LOG2);
+  for (int t = tid; t < 32; t += nthreads) {
+    float v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xc = (float)(8 * t + i);
+      v[i] = (log1p_in ? fm::flog(1.f + xc) : xc) * sX;
+      v[i] = fminf(fmaxf(v[i], -60000.f), 60000.f);
+    }
+    uint4 hi, lo;
+    tc::split8(v, hi, lo);
+    const uint32_t h[4] = {hi.x, hi.y, hi.z, hi.w}, l[4] = {lo.x, lo.y, lo.z, lo.w};
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      lut[8 * t + 2 * p] = __byte_perm(h[p], l[p], 0x5410);
+      lut[8 * t + 2 * p + 1] = __byte_perm(h[p], l[p], 0x7632);
+    }
+  }
+}
+// 8 counts (two 32-bit words of bytes) -> the staged operand chunk {8 hi halves, 8 lo halves}
+__device__ __forceinline__ void en_lut8(const uint32_t* __restrict__ lut, uint32_t b0, uint32_t b1, uint4& hi, uint4& lo) {
+  const uint32_t w0 = lut[b0 & 0xff], w1 = lut[(b0 >> 8) & 0xff], w2 = lut[(b0 >> 16) & 0xff], w3 = lut[b0 >> 24];
+  const uint32_t w4 = lut[b1 & 0xff], w5 = lut[(b1 >> 8) & 0xff], w6 = lut[(b1 >> 16) & 0xff], w7 = lut[b1 >> 24];
+  hi = make_uint4(__byte_perm(w0, w1, 0x5410), __byte_perm(w2, w3, 0x5410), __byte_perm(w4, w5, 0x5410), __byte_perm(w6, w7, 0x5410));
+  lo = make_uint4(__byte_perm(w0, w1, 0x7632), __byte_perm(w2, w3, 0x7632), __byte_perm(w4, w5, 0x7632), __byte_perm(w6, w7, 0x7632));
+}
+// keep the first n (0..8) bytes of the pair (b0, b1)
+__device__ __forceinline__ void en_keep_bytes(uint32_t& b0, uint32_t& b1, int n) {
+  n = max(0, min(8, n));
+  b0 &= n >= 4 ? 0xffffffffu : ((1u << (8 * n)) - 1u);
+  b1 &= n >= 8 ? 0xffffffffu : (n <= 4 ? 0u : ((1u << (8 * (n - 4))) - 1u));
 }
 
 // ---------------------------------------------------------------------------------------
@@ -96,11 +136,14 @@ struct En1Smem {
   static constexpr uint32_t BARS = RAW + 2 * RAW_BYTES;
   static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;
-  static constexpr uint32_t TOTAL = RED + 4 * TC_M * 4;
+  static constexpr uint32_t LUT = RED + 4 * TC_M * 4;    // 256 x (hi | lo << 16)
+  static constexpr uint32_t RAW8_BYTES = TC_M * EN_RAW8_ROW;  // uint8 chunk: 18 KB
+  static constexpr uint32_t TOTAL = LUT + 256 * 4;
 };
 
+template <bool U8>
 __global__ void __launch_bounds__(EN_THREADS, 1)
-    tc_enc_fwd_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+    tc_enc_fwd_kernel(const void* __restrict__ xv, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
                       int64_t G, const uint8_t* __restrict__ wpack, int chunks_per_split, int log1p_in,
                       float* __restrict__ ypart /*[nsplit][B][128]*/, float* __restrict__ rowsum_part /*[nsplit][B]*/) {
   using L = En1Smem;
@@ -110,6 +153,9 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   uint64_t *wfull = bars, *afull = bars + 2, *empty = bars + 4, *rfull = bars + 6, *rempty = bars + 8, *accfull = bars + 10;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
   float* s_red = reinterpret_cast<float*>(smem + L::RED);
+  uint32_t* s_lut = reinterpret_cast<uint32_t*>(smem + L::LUT);
+  const float* x = reinterpret_cast<const float*>(xv);
+  const uint8_t* x8 = reinterpret_cast<const uint8_t*>(xv);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t r0 = (int64_t)blockIdx.x * TC_M;
@@ -131,13 +177,43 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     tc::fence_mbar_init();
   }
   if (warp == 2) tc::tmem_alloc(s_tmem, 128);
+  if (U8) en_build_lut(s_lut, log1p_in, tid, EN_THREADS);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *s_tmem;
   const int lid = en_loader_id(warp);
 
-  if (lid >= 0) {
+  if (lid >= 0 && U8) {
+    // ===== raw producers, uint8 counts: a row segment of a chunk is 128 B = 8 x 16 B, one warp instruction copies
+    // the segments of 4 rows (lane = (row lane / 8, piece lane % 8)); lane owns the pointers of rows lane + 32 k
+    const uint8_t* rp[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int rr = lane + 32 * k;
+      rp[k] = (rr < valid) ? x8 + (row_idx ? row_idx[r0 + rr] : r0 + rr) * ldx : nullptr;
+    }
+    const int piece = lane & 7, rsub = lane >> 3;
+    for (int c = 0; c < nchunks; ++c) {
+      const int s = c & 1;
+      const int64_t gt = (int64_t)(c0 + c) * TC_M;
+      const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - gt);
+      const bool lane_on = (uint32_t)piece * 16 < rowbytes;
+      tc::mbar_wait(&rempty[s], ((c >> 1) & 1) ^ 1);
+      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * L::RAW8_BYTES) + piece * 16;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+#pragma unroll
+        for (int i = 0; i < 8 / EN_LOAD_WARPS; ++i) {
+          const int rr = 4 * (lid + EN_LOAD_WARPS * i) + rsub;  // row 32 k + rr of the tile
+          const uint8_t* p = reinterpret_cast<const uint8_t*>(
+              __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(rp[k]), rr));
+          if (p && lane_on) tc::cp_async16(dst0 + (32 * k + rr) * EN_RAW8_ROW, p + gt + piece * 16);
+        }
+      }
+      tc::cp_async_mbar_arrive_noinc(&rfull[s]);
+    }
+  } else if (lid >= 0) {
     // ===== raw producers: per chunk, loader warp `lid` copies the 512-byte segments of rows lid, lid + 4, ...
     // (one warp instruction = one row segment; lane owns the row pointers of rows lane + 32 k)
     const float* rp[4];
@@ -208,7 +284,35 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     const bool rvalid = r < valid;
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
     float rowsum = 0.f;
-    for (int c = 0; c < nchunks; ++c) {
+    uint32_t isum = 0;  // uint8 counts: exact integer row sum (< 2^24: equals the fp32 sum bit for bit)
+    for (int c = 0; U8 && c < nchunks; ++c) {
+      const int rs = c & 1;
+      tc::mbar_wait(&rfull[rs], (c >> 1) & 1);
+      const uint8_t* raw = smem + L::RAW + rs * L::RAW8_BYTES + r * EN_RAW8_ROW + cg * 8;
+      const int64_t gt = (int64_t)(c0 + c) * TC_M;
+      const bool partial = gt + TC_M > G;  // genes beyond G were not copied: stale bytes
+#pragma unroll
+      for (int sub = 0; sub < 4; ++sub) {
+        const int j = 4 * c + sub, s = j & 1;
+        uint2 b = *reinterpret_cast<const uint2*>(raw + sub * TC_NT);
+        if (partial) en_keep_bytes(b.x, b.y, (int)(G - (gt + sub * TC_NT + 8 * cg)));
+        isum = __dp4a(b.x, 0x01010101u, isum);
+        isum = __dp4a(b.y, 0x01010101u, isum);
+        uint4 hi, lo;
+        en_lut8(s_lut, b.x, b.y, hi, lo);
+        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
+        uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
+        *reinterpret_cast<uint4*>(a) = hi;
+        *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
+        tc::fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&afull[s]);
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&rempty[rs]);
+    }
+    if (U8) rowsum = (float)isum;
+    for (int c = 0; !U8 && c < nchunks; ++c) {
       const int rs = c & 1;
       tc::mbar_wait(&rfull[rs], (c >> 1) & 1);
       const uint8_t* raw = smem + L::RAW + rs * L::RAW_BYTES + r * L::RAW_ROW + cg * 32;
@@ -389,8 +493,9 @@ __global__ void __launch_bounds__(512)
   *reinterpret_cast<uint4*>(base + TC_BLK32 + kc * TC_NT * 16 + r * 16) = lo;
 }
 
+template <bool U8>
 __global__ void __launch_bounds__(EN_THREADS, 1)
-    tc_enc_dw_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
+    tc_enc_dw_kernel(const void* __restrict__ xv, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
                      int64_t G, const uint8_t* __restrict__ dypack, const float* __restrict__ absmax,
                      int tiles_per_split, int log1p_in, int xvec, float* __restrict__ slab /*[nsplit][128][G]*/) {
   using L = EnSmem;  // A region = dy tiles (bulk copied), W region = converted log1p(x)^T tiles
@@ -400,6 +505,9 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   uint64_t *dfull = bars, *xfull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
   uint64_t *rfull = bars + 4 * EN_NS, *rempty = bars + 5 * EN_NS;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+  uint32_t* s_lut = reinterpret_cast<uint32_t*>(smem + L::LUT);
+  const float* x = reinterpret_cast<const float*>(xv);
+  const uint8_t* x8 = reinterpret_cast<const uint8_t*>(xv);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t g0 = (int64_t)blockIdx.x * TC_M;
@@ -419,13 +527,38 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     tc::fence_mbar_init();
   }
   if (warp == 2) tc::tmem_alloc(s_tmem, 128);
+  if (U8) en_build_lut(s_lut, log1p_in, tid, EN_THREADS);
   tc::fence_before_sync();
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *s_tmem;
   const int lid = en_loader_id(warp);
 
-  if (lid >= 0) {
+  if (lid >= 0 && U8) {
+    // ===== raw producers, uint8 counts: a row's 128 genes are 8 x 16 B; one warp instruction copies 4 rows
+    const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - g0);
+    const int piece = lane & 7, rsub = lane >> 3;
+    const bool lane_on = (uint32_t)piece * 16 < rowbytes;
+    auto row_id = [&](int j) -> int64_t {
+      const int64_t b = (int64_t)(rt0 + j) * TC_NT + lane;
+      return (j < ntiles && b < B) ? (row_idx ? row_idx[b] : b) : -1;
+    };
+    int64_t rid = row_id(0);
+    for (int j = 0; j < ntiles; ++j) {
+      const int s = j % EN_NS;
+      const int64_t ridn = row_id(j + 1);
+      tc::mbar_wait(&rempty[s], ((j / EN_NS) & 1) ^ 1);
+      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * EN_RAW1) + piece * 16;
+#pragma unroll
+      for (int i = 0; i < 8 / EN_LOAD_WARPS; ++i) {
+        const int rr = 4 * (lid + EN_LOAD_WARPS * i) + rsub;
+        const int64_t r = __shfl_sync(0xffffffffu, rid, rr);
+        if (r >= 0 && lane_on) tc::cp_async16(dst0 + rr * EN_RAW8_ROW, x8 + r * ldx + g0 + piece * 16);
+      }
+      tc::cp_async_mbar_arrive_noinc(&rfull[s]);
+      rid = ridn;
+    }
+  } else if (lid >= 0) {
     // ===== raw producers: per 32-row tile, loader warp `lid` copies the 512-byte gene segments of rows
     // lid, lid + 4, ... (one warp instruction = one row segment); lane l holds the id of the tile's row l
     const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - g0) * 4;
@@ -490,7 +623,27 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     const int gc = warp - 4;
     const int64_t gb = g0 + 8 * gc;
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
-    for (int j = 0; j < ntiles; ++j) {
+    for (int j = 0; U8 && j < ntiles; ++j) {
+      const int s = j % EN_NS;
+      const bool rvalid = (int64_t)(rt0 + j) * TC_NT + lane < B;
+      tc::mbar_wait(&rfull[s], (j / EN_NS) & 1);
+      uint2 b = *reinterpret_cast<const uint2*>(smem + L::RAW + s * EN_RAW1 + lane * EN_RAW8_ROW + gc * 8);
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&rempty[s]);
+      // rows past the end of the batch were not copied (they are K entries of the product: must be zero); genes
+      // past G only reach output columns that are never stored
+      if (!rvalid) b = make_uint2(0u, 0u);
+      uint4 hi, lo;
+      en_lut8(s_lut, b.x, b.y, hi, lo);
+      tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
+      uint8_t* o = smem + L::W + s * 2 * EN_BLK + gc * (TC_NT * 16) + lane * 16;
+      *reinterpret_cast<uint4*>(o) = hi;
+      *reinterpret_cast<uint4*>(o + TC_BLK32) = lo;
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&xfull[s]);
+    }
+    for (int j = 0; !U8 && j < ntiles; ++j) {
       const int s = j % EN_NS;
       const bool rvalid = (int64_t)(rt0 + j) * TC_NT + lane < B;
       tc::mbar_wait(&rfull[s], (j / EN_NS) & 1);
@@ -572,9 +725,10 @@ static EnFwdPlan en_fwd_plan(int64_t B, int64_t K) {
 }
 int64_t tc_enc_fwd_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_fwd_plan(B, K).total; }
 
-int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
+int tc_enc_fwd(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
                const float* bias, int flags, float* y, int64_t ldy, float* library, float* bn_partials, void* ws,
                cudaStream_t st) {
+  const bool u8 = (flags & SCVI_LIN_X_U8) != 0;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_linear_fwd(SCVI_LIN_TC): ws must be 256-byte aligned");
   const EnFwdPlan p = en_fwd_plan(B, K);
   uint8_t* w8 = (uint8_t*)ws;
@@ -583,11 +737,12 @@ int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, i
   float* rs = (float*)(w8 + p.off_rs);
   tc_pack_we_kernel<<<(unsigned)cdiv(p.nKT * 4 * TC_M, 256), 256, 0, st>>>(W, ldw, K, p.nKT, wpack);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc pack)");
-  static std::atomic<uint64_t> optin{0};
-  if (int rc = smem_optin((const void*)tc_enc_fwd_kernel, (int)En1Smem::TOTAL + 128, optin, "scvi_linear_fwd")) return rc;
+  static std::atomic<uint64_t> optin[2];
+  auto kern = u8 ? tc_enc_fwd_kernel<true> : tc_enc_fwd_kernel<false>;
+  if (int rc = smem_optin((const void*)kern, (int)En1Smem::TOTAL + 128, optin[u8], "scvi_linear_fwd")) return rc;
   dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
-  tc_enc_fwd_kernel<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
-                                                                  (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
+  kern<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
+                                                     (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc)");
   tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 512, 0, st>>>(
       ypart, rs, p.nsplit, B, bias, y, ldy, (flags & SCVI_LIN_LIBRARY) ? library : nullptr, bn_partials);
@@ -618,8 +773,9 @@ static EnDwPlan en_dw_plan(int64_t B, int64_t K) {
 int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K) { return (int64_t)en_dw_plan(B, K).total; }
 
 // dW[128, K] (row stride ldw == K) = dy^T f(x)
-int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
+int tc_enc_dw(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
               int flags, float* dW, const float* dy_absmax_part, int64_t n_absmax_part, void* ws, cudaStream_t st) {
+  const bool u8 = (flags & SCVI_LIN_X_U8) != 0;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_linear_bwd(SCVI_LIN_TC): ws must be 256-byte aligned");
   SCVI_REQUIRE(!dy_absmax_part || n_absmax_part > 0, "scvi_linear_bwd(SCVI_LIN_TC): empty dy_absmax_part");
   SCVI_REQUIRE(lddy % 4 == 0 && ((uintptr_t)dy % 16 == 0), "scvi_linear_bwd(SCVI_LIN_TC): dy must be 16-byte aligned");
@@ -637,13 +793,13 @@ int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, in
   }
   tc_pack_rows32_kernel<<<(unsigned)p.nR, 512, 0, st>>>(dy, lddy, B, dy_absmax_part, (int)n_absmax_part, scal, dypack);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc pack)");
-  static std::atomic<uint64_t> optin{0};
-  if (int rc = smem_optin((const void*)tc_enc_dw_kernel, (int)EnSmem::TOTAL + 128, optin, "scvi_linear_bwd")) return rc;
+  static std::atomic<uint64_t> optin[2];
+  auto kern = u8 ? tc_enc_dw_kernel<true> : tc_enc_dw_kernel<false>;
+  if (int rc = smem_optin((const void*)kern, (int)EnSmem::TOTAL + 128, optin[u8], "scvi_linear_bwd")) return rc;
   const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
   dim3 grid((unsigned)p.nT, (unsigned)p.nsplit);
-  tc_enc_dw_kernel<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, scal,
-                                                                p.tiles_per_split, (flags & SCVI_LIN_LOG1P) ? 1 : 0,
-                                                                xvec, slab);
+  kern<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, scal, p.tiles_per_split,
+                                                    (flags & SCVI_LIN_LOG1P) ? 1 : 0, xvec, slab);
   SCVI_LAUNCH_CHECK("scvi_linear_bwd(tc dW)");
   return launch_colsum(slab, p.nsplit, TC_M * K, TC_M * K, colsum_seg1(dW, TC_M * K), st, "scvi_linear_bwd(tc reduce)");
 }

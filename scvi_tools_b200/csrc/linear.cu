@@ -365,11 +365,11 @@ static int64_t dw_splits(int64_t B, int64_t K, int64_t N) {
 }
 
 int64_t tc_enc_fwd_ws_bytes(int64_t B, int64_t K);
-int tc_enc_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
+int tc_enc_fwd(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* W, int64_t ldw,
                const float* bias, int flags, float* y, int64_t ldy, float* library, float* bn_partials, void* ws,
                cudaStream_t st);
 int64_t tc_enc_dw_ws_bytes(int64_t B, int64_t K);
-int tc_enc_dw(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
+int tc_enc_dw(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, const float* dy, int64_t lddy,
               int flags, float* dW, const float* dy_absmax_part, int64_t n_absmax_part, void* ws, cudaStream_t st);
 }  // namespace scvi
 
@@ -379,10 +379,11 @@ int64_t scvi_linear_fwd_ws_bytes(int64_t B, int64_t K, int64_t N, int flags) {
   return ((flags & SCVI_LIN_TC) && N == 128) ? scvi::tc_enc_fwd_ws_bytes(B, K) : 0;
 }
 
-int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+int scvi_linear_fwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, const float* bias, const int32_t* cov_cols, int n_cov, int flags,
                     float* y, int64_t ldy, float* library, float* bn_partials, void* ws, void* stream) {
   using namespace scvi;
+  const float* x = (const float*)xv;
   SCVI_REQUIRE(x && W && y, "scvi_linear_fwd: NULL pointer");
   SCVI_REQUIRE(B >= 0 && K > 0 && N > 0 && ldx >= K && ldw >= K && ldy >= N, "scvi_linear_fwd: bad shape");
   SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_fwd: n_cov > 0 but cov_cols is NULL");
@@ -393,9 +394,20 @@ int scvi_linear_fwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
       set_error("scvi_linear_fwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, ldy %% 4 == 0");
       return SCVI_EUNSUPPORTED;
     }
+    if (flags & SCVI_LIN_X_U8) {  // uint8 counts: 16-byte row pieces straight from the resident matrix
+      if ((ldx % 16 != 0) || ((uintptr_t)x % 16 != 0)) {
+        set_error("scvi_linear_fwd(SCVI_LIN_X_U8): the count rows must be 16-byte aligned (ldx %% 16 == 0)");
+        return SCVI_EUNSUPPORTED;
+      }
+      return tc_enc_fwd(xv, ldx, row_idx, B, K, W, ldw, bias, flags, y, ldy, library, bn_partials, ws, (cudaStream_t)stream);
+    }
     // the bulk-copy row gather needs 16-byte aligned rows; otherwise the FFMA kernel below does the work
     if ((K % 4 == 0) && (ldx % 4 == 0) && ((uintptr_t)x % 16 == 0))
       return tc_enc_fwd(x, ldx, row_idx, B, K, W, ldw, bias, flags, y, ldy, library, bn_partials, ws, (cudaStream_t)stream);
+  }
+  if (flags & SCVI_LIN_X_U8) {
+    set_error("scvi_linear_fwd: SCVI_LIN_X_U8 needs SCVI_LIN_TC");
+    return SCVI_EUNSUPPORTED;
   }
   const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && (ldw % 4 == 0) && ((uintptr_t)x % 16 == 0) &&
                    ((uintptr_t)W % 16 == 0);
@@ -417,11 +429,12 @@ int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_co
   return N == 128 ? std::max<int64_t>(ffma, tc_enc_dw_ws_bytes(B, K) + cov) : ffma;
 }
 
-int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
+int scvi_linear_bwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
                     const float* W, int64_t ldw, int64_t n_w_cols, const int32_t* cov_cols, int n_cov, int flags,
                     const float* dy, int64_t lddy, float* dW, float* db, float* dx, int64_t lddx,
                     const float* dy_absmax_part, int64_t n_absmax_part, void* ws, void* stream) {
   using namespace scvi;
+  const float* x = (const float*)xv;
   SCVI_REQUIRE(x && dy && ws, "scvi_linear_bwd: NULL pointer");
   SCVI_REQUIRE(B > 0 && K > 0 && N > 0 && ldx >= K && lddy >= N && n_w_cols >= K && ldw >= n_w_cols,
                "scvi_linear_bwd: bad shape");
@@ -436,10 +449,15 @@ int scvi_linear_bwd(const float* x, int64_t ldx, const int64_t* row_idx, int64_t
     set_error("scvi_linear_bwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, contiguous dW");
     return SCVI_EUNSUPPORTED;
   }
-  tc = tc && (K % 4 == 0) && (ldx % 4 == 0) && ((uintptr_t)x % 16 == 0) && (lddy % 4 == 0) && ((uintptr_t)dy % 16 == 0);
+  const bool u8 = (flags & SCVI_LIN_X_U8) != 0;
+  if (u8 && (!tc || dx || ldx % 16 != 0 || (uintptr_t)x % 16 != 0 || lddy % 4 != 0 || (uintptr_t)dy % 16 != 0)) {
+    set_error("scvi_linear_bwd(SCVI_LIN_X_U8): needs SCVI_LIN_TC, no dx, 16-byte aligned count rows and dy");
+    return SCVI_EUNSUPPORTED;
+  }
+  tc = tc && (u8 || ((K % 4 == 0) && (ldx % 4 == 0))) && ((uintptr_t)x % 16 == 0) && (lddy % 4 == 0) && ((uintptr_t)dy % 16 == 0);
   float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * K + N * K;
   if (dW && tc) {
-    int rc = tc_enc_dw(x, ldx, row_idx, B, K, dy, lddy, flags, dW, dy_absmax_part, n_absmax_part, ws, st);
+    int rc = tc_enc_dw(xv, ldx, row_idx, B, K, dy, lddy, flags, dW, dy_absmax_part, n_absmax_part, ws, st);
     if (rc) return rc;
   } else if (dW) {
     const bool vec = (K % 4 == 0) && (N % 4 == 0) && (ldx % 4 == 0) && (lddy % 4 == 0) &&

@@ -79,7 +79,10 @@ class HostStreamedCounts:
     """
 
     def __init__(self, X, batch=None, batch_size: int = 128, device="cuda", dtype: torch.dtype | None = None,
-                 device_gather: bool = True):
+                 device_gather: bool = True, compact_stage: bool = False):
+        """`compact_stage`: keep the staging rows in uint8 (host matrix of uint8 counts only) -- the tensor-core
+        training kernels read uint8 counts directly (SCVI_X_U8 / SCVI_LIN_X_U8), so the H2D copy lands in the rows
+        the step reads and nothing is expanded."""
         self.dev = torch.device(device)
         X = torch.as_tensor(np.asarray(X.toarray()) if hasattr(X, "toarray") else X)
         self.dtype = narrowest_count_dtype(X) if dtype is None else dtype
@@ -89,11 +92,18 @@ class HostStreamedCounts:
         self.host_batch = b.contiguous().pin_memory()
         self.B = int(batch_size)
         G = X.shape[1]
-        self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G), batch=torch.zeros(2 * self.B, dtype=torch.int64),
-                                          device=self.dev)
+        self.compact_stage = bool(compact_stage) and self.dtype == torch.uint8
+        if self.compact_stage:
+            self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G, dtype=torch.uint8), compress="u8",
+                                              batch=torch.zeros(2 * self.B, dtype=torch.int64), device=self.dev)
+            device_gather = False  # the device-side gather kernels expand to fp32
+        else:
+            self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G), batch=torch.zeros(2 * self.B, dtype=torch.int64),
+                                              device=self.dev)
         # the staging rows hold whatever the host matrix holds: integer counts unless it had to stay float32
         self.stage.integer_counts = self.dtype != torch.float32 or DeviceResidentCounts._all_integer(self.host)
-        self._compact = None if self.dtype == torch.float32 else torch.empty(2 * self.B, G, dtype=self.dtype, device=self.dev)
+        self._compact = (None if (self.dtype == torch.float32 or self.compact_stage)
+                         else torch.empty(2 * self.B, G, dtype=self.dtype, device=self.dev))
         self._pin = [torch.empty(self.B, G, dtype=self.dtype).pin_memory() for _ in range(2)]
         self._pin_b = [torch.empty(self.B, dtype=torch.int64).pin_memory() for _ in range(2)]
         self.copy_stream = torch.cuda.Stream(device=self.dev)
@@ -288,7 +298,14 @@ class DeviceResidentCounts:
             X = X.to(torch.uint8)
         elif X.dtype != torch.float32:
             X = X.to(torch.float32)
-        self.X = X.to(dev).contiguous()
+        if X.dtype == torch.uint8 and X.shape[1] % 16:
+            # the tensor-core kernels copy uint8 rows in 16-byte pieces: rows start 16-byte aligned
+            G = X.shape[1]
+            store = torch.zeros(X.shape[0], (G + 15) // 16 * 16, dtype=torch.uint8, device=dev)
+            store[:, :G].copy_(X)
+            self.X = store[:, :G]
+        else:
+            self.X = X.to(dev).contiguous()
         n = self.X.shape[0]
         # non-negative integer counts (what a counts layer holds): lets the training kernels take their
         # straight-line per-element path (include/scvi_b200.h, SCVI_X_INTEGER); verified once, here

@@ -296,9 +296,15 @@ class FusedTrainingPlan:
         B, G, H, L = self.B_cur, self.G, self.H, self.L
         parity = self._parity() if parity is None else parity
         P, Gd, X = self.P, self._Gd2[parity], self.data.X
-        if X.dtype != torch.float32:
-            raise NotImplementedError("fused training reads fp32 resident counts (uint16 residency: gather path)")
+        if X.dtype == torch.uint8:
+            if not (self.enc_tc and self.module.precision == _lib.PREC_TC):
+                raise NotImplementedError("uint8-resident counts need the tcgen05 kernels (precision=1, n_hidden=128)")
+            if X.stride(0) % 16 or X.data_ptr() % 16:
+                raise ValueError("uint8-resident counts need 16-byte aligned rows (DeviceResidentCounts pads them)")
+        elif X.dtype != torch.float32:
+            raise NotImplementedError("fused training reads fp32 or uint8 resident counts (uint16 residency: gather path)")
         ldx = X.stride(0)
+        x_lin = _lib.LIN_X_U8 if X.dtype == torch.uint8 else 0
         lik = _lib.LIK_ZINB if self.zinb else _lib.LIK_NB
         prec = self.module.precision
         # how the training kernels may read the counts (uint8 bytes / guaranteed-integer fp32 / any fp32)
@@ -319,7 +325,7 @@ class FusedTrainingPlan:
                  _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
         # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
-             None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc, _p(self.y1), H, _p(self.library), _p(self.part1),
+             None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc | x_lin, _p(self.y1), H, _p(self.library), _p(self.part1),
              _p(self.ws_enc), st)
         drop = self.p_drop > 0
         dscale = 1.0 / (1.0 - self.p_drop) if drop else 1.0
@@ -372,7 +378,7 @@ class FusedTrainingPlan:
         else:
             self._middle_backward_unfused(st, B, H, L, drop, dscale, inj, ncols, Gd)
         call("scvi_linear_bwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, G, None, 0,
-             _lib.LIN_LOG1P | self.enc_tc, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
+             _lib.LIN_LOG1P | self.enc_tc | x_lin, _p(self.dy1), H, _p(Gd[ENC + "0.weight"]),
              None if self.use_mid else _p(Gd[ENC + "0.bias"]), None, 0,
              _p(self.dy1_amax) if self.use_mid else None, self.dy1_amax.numel() if self.use_mid else 0, _p(self.ws), st)
         if overlap:

@@ -204,3 +204,46 @@ def test_cooperative_middle_equals_multi_launch_middle_bitwise(B_, graph, monkey
     for a, b in zip(res[0], res[1], strict=True):
         assert torch.equal(a, b), float((a - b).abs().max())
     assert torch.isfinite(res[1][7]).all() and float(res[1][0].abs().sum()) > 0
+
+
+@pytest.mark.parametrize("G,B_,lik", [(2000, 8192, "zinb"), (500, 1000, "nb"), (4000, 300, "zinb")])
+def test_uint8_resident_counts_equal_fp32_resident_counts_bitwise(G, B_, lik):
+    """uint8-resident counts (SCVI_X_U8 / SCVI_LIN_X_U8: 1 byte per count through E1 / K2 / K3 / E2, log1p from a
+    256-entry table built with the fp32 path's own arithmetic) against the same counts resident as fp32: identical
+    parameters, Adam moments, BatchNorm buffers and losses after 3 steps.  G = 500 exercises padded rows (500 % 16
+    != 0) and a partial last 128-gene chunk; B = 1000 / 300 ragged row tiles."""
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.data import DeviceResidentCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+
+    dev = torch.device("cuda:0")
+    nb = 4
+    n_rows = max(4 * B_, 4096)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    X = torch.poisson(torch.rand(n_rows, G, device=dev, generator=gen) * 9.0, generator=gen)
+    X[0, 0], X[1, G - 1] = 255.0, 255.0  # the table's last entry, first and last gene
+    batch = torch.arange(n_rows, device=dev) * nb // n_rows
+    g = torch.Generator().manual_seed(2)
+    idxs = [torch.randperm(n_rows, generator=g)[:B_].sort().values.to(dev) for _ in range(3)]
+    idxs[0][0] = 0
+    idxs[0][1] = 1
+    idxs[0] = idxs[0].sort().values
+    res = []
+    for compress in (None, "u8"):
+        data = DeviceResidentCounts(X, batch=batch, device=dev, compress=compress)
+        assert data.X.dtype == (torch.uint8 if compress else torch.float32)
+        if compress:
+            assert data.X.stride(0) % 16 == 0
+        torch.manual_seed(7)
+        m = S.VAE(n_input=G, n_batch=nb, gene_likelihood=lik, n_hidden=128, n_latent=10, precision=1).train()
+        plan = FusedTrainingPlan(m, data, batch_size=B_, n_epochs_kl_warmup=None, max_kl_weight=0.5,
+                                 use_cuda_graph=False, seed=3)
+        plan.set_epoch(0)
+        losses = [plan.training_step(ix).clone() for ix in idxs]
+        torch.cuda.synchronize()
+        res.append((plan.p.clone(), plan.m.clone(), plan.v.clone(), plan.bn1_rm.clone(), plan.bn2_rv.clone(),
+                    torch.stack(losses), plan.g.clone(), plan.library.clone()))
+    # fp32 resident counts take the integer-count element path (SCVI_X_INTEGER): the same arithmetic as uint8
+    for a, b in zip(res[0], res[1], strict=True):
+        assert torch.equal(a, b), float((a - b).abs().max())
+    assert torch.isfinite(res[1][5]).all()
