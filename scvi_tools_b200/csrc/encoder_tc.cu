@@ -62,7 +62,8 @@ struct EnSmem {
   static constexpr uint32_t W = EN_NS * 2 * EN_BLK;      // EN_NS x {hi, lo}
   static constexpr uint32_t RAW = 2 * EN_NS * 2 * EN_BLK; // EN_NS raw tiles
   static constexpr uint32_t BARS = RAW + EN_NS * EN_RAW1;
-  static constexpr uint32_t TMEM_PTR = BARS + 32 * 8;
+  static constexpr int NRAW8 = 12;                       // uint8 raw ring: 12 x 4.5 KB tiles
+  static constexpr uint32_t TMEM_PTR = BARS + 48 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;         // [4][128] row-sum partials
   static constexpr uint32_t LUT = RED + 4 * TC_M * 4;    // 256 x (hi | lo << 16), uint8 counts
   static constexpr uint32_t TOTAL = LUT + 256 * 4;
@@ -134,23 +135,48 @@ struct En1Smem {
   static constexpr uint32_t RAW_ROW = TC_M * 4 + 16;
   static constexpr uint32_t RAW_BYTES = TC_M * RAW_ROW;  // 66 KB
   static constexpr uint32_t BARS = RAW + 2 * RAW_BYTES;
-  static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
+  static constexpr int NRAW8 = 2;
+  static constexpr uint32_t TMEM_PTR = BARS + 32 * 8;
   static constexpr uint32_t RED = TMEM_PTR + 16;
   static constexpr uint32_t LUT = RED + 4 * TC_M * 4;    // 256 x (hi | lo << 16)
   static constexpr uint32_t RAW8_BYTES = TC_M * EN_RAW8_ROW;  // uint8 chunk: 18 KB
   static constexpr uint32_t TOTAL = LUT + 256 * 4;
 };
 
+// uint8 counts: the raw chunks are 4x smaller, which buys 4 operand stages (the packed We tiles come from L2 with
+// ~1 us of bulk-copy latency each: two stages in flight kept the tensor pipe waiting) and a 4-deep raw ring
+struct En1SmemU8 {
+  static constexpr int NS = 4;
+  static constexpr uint32_t A = 0;
+  static constexpr uint32_t W = NS * 2 * EN_BLK;
+  static constexpr uint32_t RAW = 2 * NS * 2 * EN_BLK;
+  static constexpr int NRAW8 = 4;
+  static constexpr uint32_t RAW8_BYTES = TC_M * EN_RAW8_ROW;
+  static constexpr uint32_t RAW_BYTES = RAW8_BYTES, RAW_ROW = EN_RAW8_ROW;
+  static constexpr uint32_t BARS = RAW + NRAW8 * RAW8_BYTES;
+  static constexpr uint32_t TMEM_PTR = BARS + 32 * 8;
+  static constexpr uint32_t RED = TMEM_PTR + 16;
+  static constexpr uint32_t LUT = RED + 4 * TC_M * 4;
+  static constexpr uint32_t TOTAL = LUT + 256 * 4;
+};
+static_assert(En1SmemU8::TOTAL + 128 <= 232448, "E1 uint8 shared memory");
+template <bool U8>
+struct En1Layout { using type = En1Smem; };
+template <>
+struct En1Layout<true> { using type = En1SmemU8; };
+
 template <bool U8>
 __global__ void __launch_bounds__(EN_THREADS, 1)
     tc_enc_fwd_kernel(const void* __restrict__ xv, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
                       int64_t G, const uint8_t* __restrict__ wpack, int chunks_per_split, int log1p_in,
                       float* __restrict__ ypart /*[nsplit][B][128]*/, float* __restrict__ rowsum_part /*[nsplit][B]*/) {
-  using L = En1Smem;
+  using L = typename En1Layout<U8>::type;
+  constexpr int NS = L::NS;  // operand stages
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
-  uint64_t *wfull = bars, *afull = bars + 2, *empty = bars + 4, *rfull = bars + 6, *rempty = bars + 8, *accfull = bars + 10;
+  uint64_t *wfull = bars, *afull = bars + 4, *empty = bars + 8, *accfull = bars + 12, *rfull = bars + 16, *rempty = bars + 24;
+  constexpr int NRAW = U8 ? L::NRAW8 : 2;  // raw-count ring depth
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
   float* s_red = reinterpret_cast<float*>(smem + L::RED);
   uint32_t* s_lut = reinterpret_cast<uint32_t*>(smem + L::LUT);
@@ -166,10 +192,12 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   const int ntiles = 4 * nchunks;  // 32-gene K-tiles (the packed We covers whole chunks, zero padded)
 
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < NS; ++i) {
       tc::mbar_init(&wfull[i], 1);
-      tc::mbar_init(&afull[i], EN_CONV_WARPS);
+      tc::mbar_init(&afull[i], U8 ? 4 : EN_CONV_WARPS);  // uint8: one group of 4 warps converts a K-tile
       tc::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < NRAW; ++i) {
       tc::mbar_init(&rfull[i], 32 * EN_LOAD_WARPS);
       tc::mbar_init(&rempty[i], EN_CONV_WARPS);
     }
@@ -195,11 +223,11 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     }
     const int piece = lane & 7, rsub = lane >> 3;
     for (int c = 0; c < nchunks; ++c) {
-      const int s = c & 1;
+      const int s = c % NRAW;
       const int64_t gt = (int64_t)(c0 + c) * TC_M;
       const uint32_t rowbytes = (uint32_t)min((int64_t)TC_M, G - gt);
       const bool lane_on = (uint32_t)piece * 16 < rowbytes;
-      tc::mbar_wait(&rempty[s], ((c >> 1) & 1) ^ 1);
+      tc::mbar_wait(&rempty[s], ((c / NRAW) & 1) ^ 1);
       const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * L::RAW8_BYTES) + piece * 16;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -245,8 +273,8 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     // ===== We producer: one packed 32-gene K-tile per stage
     if (lane == 0) {
       for (int j = 0; j < ntiles; ++j) {
-        const int s = j & 1;
-        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
+        const int s = j % NS;
+        tc::mbar_wait(&empty[s], ((j / NS) & 1) ^ 1);
         tc::mbar_arrive_expect_tx(&wfull[s], 2 * EN_BLK);
         tc::bulk_g2s(smem + L::W + s * 2 * EN_BLK, wpack + ((size_t)c0 * 4 + j) * 2 * EN_BLK, 2 * EN_BLK, &wfull[s]);
       }
@@ -261,9 +289,9 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       const tc::Oper A0 = tc::make_oper(a0, a0 + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16);
       const tc::Oper W0 = tc::make_oper(w0, w0 + EN_BLK, TC_M * 16, 128, 2 * TC_M * 16);
       for (int j = 0; j < ntiles; ++j) {
-        const int s = j & 1;
-        tc::mbar_wait(&wfull[s], (j >> 1) & 1);
-        tc::mbar_wait(&afull[s], (j >> 1) & 1);
+        const int s = j % NS;
+        tc::mbar_wait(&wfull[s], (j / NS) & 1);
+        tc::mbar_wait(&afull[s], (j / NS) & 1);
         tc::fence_after_sync();
         if (leader) {
           tc::Oper a = A0, w = W0;
@@ -285,31 +313,43 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
     float rowsum = 0.f;
     uint32_t isum = 0;  // uint8 counts: exact integer row sum (< 2^24: equals the fp32 sum bit for bit)
+    // uint8: converter group cg (4 warps = the 128 rows) takes K-tile `cg` of every 128-gene chunk: a thread converts
+    // the 32 counts of its row in that tile and pays one proxy fence + one barrier hand-off for them
     for (int c = 0; U8 && c < nchunks; ++c) {
-      const int rs = c & 1;
-      tc::mbar_wait(&rfull[rs], (c >> 1) & 1);
-      const uint8_t* raw = smem + L::RAW + rs * L::RAW8_BYTES + r * EN_RAW8_ROW + cg * 8;
-      const int64_t gt = (int64_t)(c0 + c) * TC_M;
-      const bool partial = gt + TC_M > G;  // genes beyond G were not copied: stale bytes
-#pragma unroll
-      for (int sub = 0; sub < 4; ++sub) {
-        const int j = 4 * c + sub, s = j & 1;
-        uint2 b = *reinterpret_cast<const uint2*>(raw + sub * TC_NT);
-        if (partial) en_keep_bytes(b.x, b.y, (int)(G - (gt + sub * TC_NT + 8 * cg)));
-        isum = __dp4a(b.x, 0x01010101u, isum);
-        isum = __dp4a(b.y, 0x01010101u, isum);
-        uint4 hi, lo;
-        en_lut8(s_lut, b.x, b.y, hi, lo);
-        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
-        uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
-        *reinterpret_cast<uint4*>(a) = hi;
-        *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
-        tc::fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&afull[s]);
-      }
+      const int rs = c % NRAW;
+      tc::mbar_wait(&rfull[rs], (c / NRAW) & 1);
+      const uint8_t* raw = smem + L::RAW + rs * L::RAW8_BYTES + r * EN_RAW8_ROW + cg * TC_NT;
+      const int64_t gt = (int64_t)(c0 + c) * TC_M + cg * TC_NT;  // first gene of this thread's 32
+      const int j = 4 * c + cg, s = j % NS;
+      uint4 b0 = *reinterpret_cast<const uint4*>(raw);
+      uint4 b1 = *reinterpret_cast<const uint4*>(raw + 16);
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&rempty[rs]);
+      if (lane == 0) tc::mbar_arrive(&rempty[rs]);  // raw chunk consumed by this warp
+      if (gt + TC_NT > G) {  // genes beyond G were not copied: stale bytes
+        en_keep_bytes(b0.x, b0.y, (int)(G - gt));
+        en_keep_bytes(b0.z, b0.w, (int)(G - gt - 8));
+        en_keep_bytes(b1.x, b1.y, (int)(G - gt - 16));
+        en_keep_bytes(b1.z, b1.w, (int)(G - gt - 24));
+      }
+      isum = __dp4a(b0.x, 0x01010101u, isum); isum = __dp4a(b0.y, 0x01010101u, isum);
+      isum = __dp4a(b0.z, 0x01010101u, isum); isum = __dp4a(b0.w, 0x01010101u, isum);
+      isum = __dp4a(b1.x, 0x01010101u, isum); isum = __dp4a(b1.y, 0x01010101u, isum);
+      isum = __dp4a(b1.z, 0x01010101u, isum); isum = __dp4a(b1.w, 0x01010101u, isum);
+      uint4 hi[4], lo[4];
+      en_lut8(s_lut, b0.x, b0.y, hi[0], lo[0]);
+      en_lut8(s_lut, b0.z, b0.w, hi[1], lo[1]);
+      en_lut8(s_lut, b1.x, b1.y, hi[2], lo[2]);
+      en_lut8(s_lut, b1.z, b1.w, hi[3], lo[3]);
+      tc::mbar_wait(&empty[s], ((j / NS) & 1) ^ 1);
+      uint8_t* a = smem + L::A + s * 2 * EN_BLK + r * 16;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        *reinterpret_cast<uint4*>(a + k * (TC_M * 16)) = hi[k];
+        *reinterpret_cast<uint4*>(a + k * (TC_M * 16) + EN_BLK) = lo[k];
+      }
+      tc::fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&afull[s]);
     }
     if (U8) rowsum = (float)isum;
     for (int c = 0; !U8 && c < nchunks; ++c) {
@@ -318,7 +358,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
       const uint8_t* raw = smem + L::RAW + rs * L::RAW_BYTES + r * L::RAW_ROW + cg * 32;
 #pragma unroll
       for (int sub = 0; sub < 4; ++sub) {
-        const int j = 4 * c + sub, s = j & 1;
+        const int j = 4 * c + sub, s = j % NS;
         const int64_t gb = (int64_t)(c0 + c) * TC_M + sub * TC_NT + 8 * cg;
         const float4 x0 = *reinterpret_cast<const float4*>(raw + sub * 128);
         const float4 x1 = *reinterpret_cast<const float4*>(raw + sub * 128 + 16);
@@ -333,7 +373,7 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
         }
         uint4 hi, lo;
         tc::split8(v, hi, lo);
-        tc::mbar_wait(&empty[s], ((j >> 1) & 1) ^ 1);
+        tc::mbar_wait(&empty[s], ((j / NS) & 1) ^ 1);
         uint8_t* a = smem + L::A + s * 2 * EN_BLK + cg * (TC_M * 16) + r * 16;
         *reinterpret_cast<uint4*>(a) = hi;
         *reinterpret_cast<uint4*>(a + EN_BLK) = lo;
@@ -503,7 +543,10 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *dfull = bars, *xfull = bars + EN_NS, *empty = bars + 2 * EN_NS, *accfull = bars + 3 * EN_NS;
-  uint64_t *rfull = bars + 4 * EN_NS, *rempty = bars + 5 * EN_NS;
+  uint64_t *rfull = bars + 4 * EN_NS, *rempty = bars + 4 * EN_NS + 16;
+  constexpr int NRAW = U8 ? L::NRAW8 : EN_NS;              // raw-count ring depth
+  constexpr uint32_t RAWSZ = U8 ? TC_NT * EN_RAW8_ROW : EN_RAW1;
+  static_assert(L::NRAW8 * TC_NT * EN_RAW8_ROW <= EN_NS * EN_RAW1 && L::NRAW8 <= 16, "uint8 raw ring");
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
   uint32_t* s_lut = reinterpret_cast<uint32_t*>(smem + L::LUT);
   const float* x = reinterpret_cast<const float*>(xv);
@@ -516,12 +559,16 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
   const int ntiles = max(0, min(nR, rt0 + tiles_per_split) - rt0);
 
   if (warp == 1 && lane == 0) {
+    // uint8: a 32-row tile is converted by ONE group of 4 warps (group g takes the tiles j % 4 == g, i.e. stage g):
+    // four tiles are in conversion at once and a thread pays one proxy fence + one barrier hand-off per 32 counts
     for (int i = 0; i < EN_NS; ++i) {
       tc::mbar_init(&dfull[i], 1);
-      tc::mbar_init(&xfull[i], EN_CONV_WARPS);
+      tc::mbar_init(&xfull[i], U8 ? 4 : EN_CONV_WARPS);
       tc::mbar_init(&empty[i], 1);
+    }
+    for (int i = 0; i < NRAW; ++i) {
       tc::mbar_init(&rfull[i], 32 * EN_LOAD_WARPS);
-      tc::mbar_init(&rempty[i], EN_CONV_WARPS);
+      tc::mbar_init(&rempty[i], U8 ? 4 : EN_CONV_WARPS);
     }
     tc::mbar_init(accfull, 1);
     tc::fence_mbar_init();
@@ -545,10 +592,10 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     };
     int64_t rid = row_id(0);
     for (int j = 0; j < ntiles; ++j) {
-      const int s = j % EN_NS;
+      const int s = j % NRAW;
       const int64_t ridn = row_id(j + 1);
-      tc::mbar_wait(&rempty[s], ((j / EN_NS) & 1) ^ 1);
-      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * EN_RAW1) + piece * 16;
+      tc::mbar_wait(&rempty[s], ((j / NRAW) & 1) ^ 1);
+      const uint32_t dst0 = tc::smem_u32(smem + L::RAW + s * RAWSZ) + piece * 16;
 #pragma unroll
       for (int i = 0; i < 8 / EN_LOAD_WARPS; ++i) {
         const int rr = 4 * (lid + EN_LOAD_WARPS * i) + rsub;
@@ -623,22 +670,31 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
     const int gc = warp - 4;
     const int64_t gb = g0 + 8 * gc;
     const float sX = tc::pow2i(EN_X_SCALE_LOG2);
-    for (int j = 0; U8 && j < ntiles; ++j) {
-      const int s = j % EN_NS;
+    static_assert(EN_NS == 4 && EN_CONV_WARPS == 16, "uint8 converter groups");
+    for (int j = (warp - 4) >> 2; U8 && j < ntiles; j += 4) {
+      const int s = j % EN_NS, rs = j % NRAW, wq = (warp - 4) & 3;  // this warp: genes 32 wq .. 32 wq + 31 of row `lane`
       const bool rvalid = (int64_t)(rt0 + j) * TC_NT + lane < B;
-      tc::mbar_wait(&rfull[s], (j / EN_NS) & 1);
-      uint2 b = *reinterpret_cast<const uint2*>(smem + L::RAW + s * EN_RAW1 + lane * EN_RAW8_ROW + gc * 8);
+      tc::mbar_wait(&rfull[rs], (j / NRAW) & 1);
+      const uint8_t* raw = smem + L::RAW + rs * RAWSZ + lane * EN_RAW8_ROW + wq * 32;
+      uint4 b0 = *reinterpret_cast<const uint4*>(raw);
+      uint4 b1 = *reinterpret_cast<const uint4*>(raw + 16);
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&rempty[s]);
+      if (lane == 0) tc::mbar_arrive(&rempty[rs]);
       // rows past the end of the batch were not copied (they are K entries of the product: must be zero); genes
       // past G only reach output columns that are never stored
-      if (!rvalid) b = make_uint2(0u, 0u);
-      uint4 hi, lo;
-      en_lut8(s_lut, b.x, b.y, hi, lo);
+      if (!rvalid) b0 = b1 = make_uint4(0u, 0u, 0u, 0u);
+      uint4 hi[4], lo[4];
+      en_lut8(s_lut, b0.x, b0.y, hi[0], lo[0]);
+      en_lut8(s_lut, b0.z, b0.w, hi[1], lo[1]);
+      en_lut8(s_lut, b1.x, b1.y, hi[2], lo[2]);
+      en_lut8(s_lut, b1.z, b1.w, hi[3], lo[3]);
       tc::mbar_wait(&empty[s], ((j / EN_NS) & 1) ^ 1);
-      uint8_t* o = smem + L::W + s * 2 * EN_BLK + gc * (TC_NT * 16) + lane * 16;
-      *reinterpret_cast<uint4*>(o) = hi;
-      *reinterpret_cast<uint4*>(o + TC_BLK32) = lo;
+      uint8_t* o = smem + L::W + s * 2 * EN_BLK + (4 * wq) * (TC_NT * 16) + lane * 16;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        *reinterpret_cast<uint4*>(o + k * (TC_NT * 16)) = hi[k];
+        *reinterpret_cast<uint4*>(o + k * (TC_NT * 16) + TC_BLK32) = lo[k];
+      }
       tc::fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&xfull[s]);
@@ -690,9 +746,15 @@ __global__ void __launch_bounds__(EN_THREADS, 1)
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] = 0.f;
       }
+      // 8 consecutive genes of one slab row: two 16-byte stores when the row is aligned and the chunk inside G
+      if (xvec && g0 + 32 * cg + 8 * c + 8 <= G) {
+        *reinterpret_cast<float4*>(o + 8 * c) = make_float4(v[0] * k, v[1] * k, v[2] * k, v[3] * k);
+        *reinterpret_cast<float4*>(o + 8 * c + 4) = make_float4(v[4] * k, v[5] * k, v[6] * k, v[7] * k);
+      } else {
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
-        if (g0 + 32 * cg + 8 * c + i < G) o[8 * c + i] = v[i] * k;
+        for (int i = 0; i < 8; ++i)
+          if (g0 + 32 * cg + 8 * c + i < G) o[8 * c + i] = v[i] * k;
+      }
     }
   }
   tc::fence_before_sync();
@@ -739,9 +801,10 @@ int tc_enc_fwd(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, in
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc pack)");
   static std::atomic<uint64_t> optin[2];
   auto kern = u8 ? tc_enc_fwd_kernel<true> : tc_enc_fwd_kernel<false>;
-  if (int rc = smem_optin((const void*)kern, (int)En1Smem::TOTAL + 128, optin[u8], "scvi_linear_fwd")) return rc;
+  const int smem_bytes = (int)(u8 ? En1SmemU8::TOTAL : En1Smem::TOTAL) + 128;
+  if (int rc = smem_optin((const void*)kern, smem_bytes, optin[u8], "scvi_linear_fwd")) return rc;
   dim3 grid((unsigned)p.rowtiles, (unsigned)p.nsplit);
-  kern<<<grid, EN_THREADS, En1Smem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
+  kern<<<grid, EN_THREADS, smem_bytes, st>>>(x, ldx, row_idx, B, K, wpack, p.tiles_per_split,
                                                      (flags & SCVI_LIN_LOG1P) ? 1 : 0, ypart, rs);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd(tc)");
   tc_enc_fwd_combine_kernel<<<(unsigned)cdiv(B, SCVI_BN_TILE), 512, 0, st>>>(
@@ -796,7 +859,7 @@ int tc_enc_dw(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int
   static std::atomic<uint64_t> optin[2];
   auto kern = u8 ? tc_enc_dw_kernel<true> : tc_enc_dw_kernel<false>;
   if (int rc = smem_optin((const void*)kern, (int)EnSmem::TOTAL + 128, optin[u8], "scvi_linear_bwd")) return rc;
-  const int xvec = (ldx % 4 == 0) && (K % 4 == 0) && ((uintptr_t)x % 16 == 0);
+  const int xvec = (K % 4 == 0) && (u8 || ((ldx % 4 == 0) && ((uintptr_t)x % 16 == 0)));  // also: slab rows 16-byte aligned
   dim3 grid((unsigned)p.nT, (unsigned)p.nsplit);
   kern<<<grid, EN_THREADS, EnSmem::TOTAL + 128, st>>>(x, ldx, row_idx, B, K, dypack, scal, p.tiles_per_split,
                                                     (flags & SCVI_LIN_LOG1P) ? 1 : 0, xvec, slab);
