@@ -123,6 +123,7 @@ class FusedTrainingPlan:
         self._alloc_step_buffers()
         self._graphs = None
         self._side = None
+        self._ev_prologue = None
         self.overlap = True  # independent launches on a second stream / parallel graph branches
         if self.world > 1:
             self._comm = torch.cuda.Stream(device=self.dev)
@@ -285,7 +286,7 @@ class FusedTrainingPlan:
         self.ws_enc = torch.empty(int(ne), dtype=torch.uint8, device=dev) if ne > 0 else None
 
     # ------------------------------------------------------------------ the step
-    def _forward_backward(self, st, overlap: bool = False, parity: int | None = None):
+    def _forward_backward(self, st, overlap: bool = False, parity: int | None = None, prologue: dict | None = None):
         """Kernel sequence of one minibatch: forward, ELBO, backward into the gradient arena.
         Rows are read from the resident matrix through `self.idx`.  `st` = cudaStream_t of the current stream.
 
@@ -321,8 +322,17 @@ class FusedTrainingPlan:
                 self._side = torch.cuda.Stream(device=self.dev)
             side = self._side
             side.wait_stream(main)
+            if prologue is not None:
+                # the step prologue (random buffers, covariate columns, backward seeds) feeds the middle of the
+                # step, not the encoder's input layer: it runs beside E1
+                self._prologue(C.c_void_p(side.cuda_stream), **prologue)
+                if self._ev_prologue is None:
+                    self._ev_prologue = torch.cuda.Event()
+                self._ev_prologue.record(side)
             call("scvi_decoder_nll_prepack", B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), lik, prec, 1,
                  _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
+        if prologue is not None and not overlap:
+            self._prologue(st, **prologue)
         # ---- encoder layer 0: log1p + library + GEMM + BN tile stats (reads X rows via idx)
         call("scvi_linear_fwd", _p(X), ldx, _p(self.idx), B, G, H, _p(P[ENC + "0.weight"]), G, _p(P[ENC + "0.bias"]),
              None, 0, _lib.LIN_LOG1P | _lib.LIN_LIBRARY | self.enc_tc | x_lin, _p(self.y1), H, _p(self.library), _p(self.part1),
@@ -331,6 +341,8 @@ class FusedTrainingPlan:
         dscale = 1.0 / (1.0 - self.p_drop) if drop else 1.0
         inj = self.nb > 1
         ncols = L + (self.nb if inj else 0)
+        if overlap and prologue is not None:
+            main.wait_event(self._ev_prologue)
         if self.use_mid:
             call("scvi_mid_fwd", _p(self.y1), _p(self.part1), B, H, L, _p(P[ENC + "1.weight"]), _p(P[ENC + "1.bias"]),
                  _p(self.bn1_rm), _p(self.bn1_rv), _p(self.mask) if drop else None, dscale, _p(self.noise),
@@ -492,8 +504,8 @@ class FusedTrainingPlan:
     def _whole_step(self, gen_mask: bool = True, gen_noise: bool = True, parity: int | None = None):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         parity = self._parity() if parity is None else parity
-        self._prologue(st, gen_mask=gen_mask, gen_noise=gen_noise)
-        self._forward_backward(st, overlap=self.overlap, parity=parity)
+        self._forward_backward(st, overlap=self.overlap, parity=parity,
+                               prologue={"gen_mask": gen_mask, "gen_noise": gen_noise})
         self._reduce_gradients(parity)
         self._adam(st, parity)
 
@@ -526,8 +538,7 @@ class FusedTrainingPlan:
                 g1, g2 = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
                 with torch.cuda.graph(g1):
                     st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-                    self._prologue(st)
-                    self._forward_backward(st, overlap=self.overlap, parity=parity)
+                    self._forward_backward(st, overlap=self.overlap, parity=parity, prologue={})
                 with torch.cuda.graph(g2):
                     self._adam(C.c_void_p(torch.cuda.current_stream().cuda_stream), parity)
                 self._graphs.append((g1, g2))
