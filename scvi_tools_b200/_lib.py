@@ -29,6 +29,7 @@ SIGNATURES = {
     "scvi_gather_i64": (C.c_int, [P, I64, P, I64, P, P]),
     "scvi_gather_rows_u16": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
     "scvi_gather_rows_u8": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
+    "scvi_decoder_dpsi_sums": (C.c_int, [P, I64, P, I64, I64, P, P, C.c_int, C.c_int, P, P]),
     "scvi_gather_rows_csr": (C.c_int, [P, P, C.c_int, P, C.c_int, I64, I64, P, I64, P, I64, P, P]),
     "scvi_nb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),
     "scvi_zinb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),
@@ -124,6 +125,7 @@ def query(name: str, *args) -> int:
 BN_TILE = 64
 LIK_NB, LIK_ZINB = 0, 1
 LIN_LOG1P, LIN_LIBRARY, LIN_TC = 1, 2, 4
+PREC_AOPS = 0x800  # decoder fwd keeps its operands, bwd is a pure GEMM (integer count kinds)
 LIN_X_U8 = 0x400  # scvi_linear_fwd / _bwd: uint8 counts (with LIN_TC)
 PREC_FP32, PREC_TC = 0, 1
 PREC_PREPACKED = 0x100

@@ -634,7 +634,7 @@ static int set_smem(K kernel, size_t bytes, const char* name) {
 }  // namespace scvi
 
 namespace scvi {
-int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood);
+int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, bool aops);
 int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws, const float* bs,
                        const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                        const int64_t* row_idx, const float* library, int likelihood, float* reconst,
@@ -647,11 +647,16 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
                           const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
                           float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
-                          int xkind, cudaStream_t st);
+                          int xkind, const float* library, cudaStream_t st);
+void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops);
+int tc_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
+                 const float* g_reconst, int xkind, float* slab, cudaStream_t st);
 // count-operand kind carried in the `precision` argument (scvi_b200.h: SCVI_X_INTEGER / SCVI_X_U8)
+// bit 4 of the result: SCVI_PREC_AOPS (staged operands kept by the forward / consumed by the backward)
 static inline int take_xkind(int& precision) {
-  const int k = (precision & SCVI_X_U8) ? 2 : (precision & SCVI_X_INTEGER) ? 1 : 0;
-  precision &= ~(SCVI_X_U8 | SCVI_X_INTEGER);
+  int k = (precision & SCVI_X_U8) ? 2 : (precision & SCVI_X_INTEGER) ? 1 : 0;
+  if ((precision & SCVI_PREC_AOPS) && k != 0) k |= 16;
+  precision &= ~(SCVI_X_U8 | SCVI_X_INTEGER | SCVI_PREC_AOPS);
   return k;
 }
 }  // namespace scvi
@@ -659,9 +664,24 @@ static inline int take_xkind(int& precision) {
 extern "C" {
 
 int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, int precision) {
-  scvi::take_xkind(precision);
-  if (precision == SCVI_PREC_TC) return scvi::tc_decoder_fwd_ws_bytes(B, H, G, likelihood);
+  const int xk = scvi::take_xkind(precision);
+  if (precision == SCVI_PREC_TC) return scvi::tc_decoder_fwd_ws_bytes(B, H, G, likelihood, (xk & 16) != 0);
   return 0;
+}
+
+int scvi_decoder_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
+                           const float* g_reconst, int likelihood, int precision, void* fwd_ws, void* stream) {
+  using namespace scvi;
+  const int xk = take_xkind(precision);
+  SCVI_REQUIRE(x && px_r && fwd_ws && B > 0 && G > 0 && ldx >= G, "scvi_decoder_dpsi_sums: bad argument");
+  if (!(xk & 16) || precision != SCVI_PREC_TC) {
+    set_error("scvi_decoder_dpsi_sums: needs SCVI_PREC_TC | SCVI_PREC_AOPS and an integer count kind");
+    return SCVI_EUNSUPPORTED;
+  }
+  size_t off_fmax, off_psi, off_aops;
+  tc_decoder_fwd_ws_aops(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1, &off_fmax, &off_psi, &off_aops);
+  return tc_dpsi_sums(x, ldx, row_idx, B, G, px_r, g_reconst, xk & 15, (float*)((uint8_t*)fwd_ws + off_psi),
+                      (cudaStream_t)stream);
 }
 
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,
@@ -671,7 +691,8 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
                          void* stream) {
   using namespace scvi;
   const float* x = reinterpret_cast<const float*>(xv);
-  const int xkind = take_xkind(precision);
+  const int xkind_full = take_xkind(precision);
+  const int xkind = xkind_full & 15;
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   SCVI_REQUIRE(likelihood == SCVI_LIK_NB || zinb, "scvi_decoder_nll_fwd: unknown likelihood %d", likelihood);
   SCVI_REQUIRE(h && Ws && bs && px_r && x && library && reconst && row_stats && (!zinb || (Wp && bp)),
@@ -686,7 +707,7 @@ int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   precision &= ~SCVI_PREC_PREPACKED;
   if (precision == SCVI_PREC_TC)
     return tc_decoder_nll_fwd(h, ldh, B, H, G, Ws, bs, Wp, bp, px_r, xv, ldx, row_idx, library, likelihood, reconst,
-                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream, prepacked, xkind);
+                              row_stats, g_reconst, dh, lddh, ws, (cudaStream_t)stream, prepacked, xkind_full);
   if (xkind == 2) {
     set_error("scvi_decoder_nll_fwd: SCVI_X_U8 needs SCVI_PREC_TC");
     return SCVI_EUNSUPPORTED;
@@ -763,7 +784,8 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   using namespace scvi;
   const char* name = "scvi_decoder_nll_bwd";
   const float* x = reinterpret_cast<const float*>(xv);
-  const int xkind = take_xkind(precision);
+  const int xkind_full = take_xkind(precision);
+  const int xkind = xkind_full & 15;
   if (xkind == 2 && (dh || precision != SCVI_PREC_TC || H != 128)) {
     set_error("%s: SCVI_X_U8 is read by the tensor-core weight-gradient kernel only (SCVI_PREC_TC, H == 128, dh == NULL)", name);
     return SCVI_EUNSUPPORTED;
@@ -783,7 +805,6 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
     set_error("%s: unknown precision %d", name, precision);
     return SCVI_EUNSUPPORTED;
   }
-  (void)library;
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if (dh) {
@@ -794,7 +815,7 @@ int scvi_decoder_nll_bwd(const float* h, int64_t ldh, int64_t B, int64_t H, int6
   }
   if (want_dw && precision == SCVI_PREC_TC && H == 128)
     return tc_decoder_nll_bwd_dw(h, ldh, B, G, Ws, bs, Wp, bp, px_r, xv, ldx, row_idx, row_stats, g_reconst, likelihood,
-                                 dWs, dbs, dWp, dbp, dpx_r, ws, fwd_ws, xkind, st);
+                                 dWs, dbs, dWp, dbp, dpx_r, ws, fwd_ws, xkind_full, library, st);
   if (want_dw) {
     const int64_t S = dw_row_splits(B, G);
     const int nheads = zinb ? 2 : 1;

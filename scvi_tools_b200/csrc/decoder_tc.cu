@@ -417,10 +417,12 @@ struct TcPlan {
   int64_t nT, rowtiles;
   int nsplit, tiles_per_split;    // LSE / NLL-only kernels: 128-gene tiles
   int nsplit2, tiles_per_split2;  // fused NLL + dh kernel: 32-gene tiles
-  size_t off_packed, off_gconst, off_lse, off_out, off_packed32, off_dh, total;
+  size_t off_packed, off_gconst, off_lse, off_out, off_packed32, off_dh, off_fmax, off_psi, off_aops, total;
 };
+size_t tc_aops_bytes(int64_t B, int64_t G, bool zinb);  // decoder_tc_train.cu
+size_t tc_dpsi_bytes(int64_t B, int64_t G);                // decoder_tc_dw2.cu
 
-static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
+static TcPlan tc_plan(int64_t B, int64_t G, int nheads, bool aops = false) {
   TcPlan p;
   p.nT = cdiv(G, TC_N);
   p.rowtiles = cdiv(B, TC_M);
@@ -440,7 +442,12 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads) {
   p.off_out = al(p.off_lse + (size_t)p.nsplit * B * 2 * sizeof(float));
   p.off_packed32 = al(p.off_out + (size_t)nsmax * B * 2 * sizeof(float));
   p.off_dh = al(p.off_packed32 + (size_t)p.nT * 4 * tc_w32_stage_bytes(nheads));
-  p.total = al(p.off_dh + (size_t)p.nsplit2 * 2 * B * TC_H * sizeof(float));
+  // SCVI_PREC_AOPS: per-block maxima of the GEMM's row factors + the kept operands, behind everything else (the
+  // offsets above do not depend on the flag)
+  p.off_fmax = al(p.off_dh + (size_t)p.nsplit2 * 2 * B * TC_H * sizeof(float));
+  p.off_psi = al(p.off_fmax + (size_t)cdiv(B, 8) * 3 * sizeof(float));
+  p.off_aops = al(p.off_psi + tc_dpsi_bytes(B, G));
+  p.total = aops ? al(p.off_aops + tc_aops_bytes(B, G, nheads == 2)) : p.off_fmax;
   return p;
 }
 
@@ -452,9 +459,16 @@ void tc_decoder_fwd_ws_offsets(int64_t B, int64_t G, int nheads, size_t* off_pac
   *off_gconst = p.off_gconst;
 }
 
-int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood) {
+int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood, bool aops) {
   (void)H;
-  return (int64_t)tc_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
+  return (int64_t)tc_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1, aops).total;
+}
+// where the forward workspace keeps the operands / factor maxima of SCVI_PREC_AOPS (read by the backward)
+void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops) {
+  const TcPlan p = tc_plan(B, G, nheads, true);
+  *off_fmax = p.off_fmax;
+  *off_psi = p.off_psi;
+  *off_aops = p.off_aops;
 }
 
 template <int MODE, bool ZINB>
@@ -474,7 +488,7 @@ int tc_launch_nll_dh(bool zinb, int xkind, const float* h, int64_t ldh, int64_t 
                      const void* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
                      int nsplit_lse, int nsplit, int tiles_per_split, float* out_part, float* dh_part,
                      const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
-                     cudaStream_t st);
+                     uint8_t* aops, float* fmax_part, cudaStream_t st);
 
 // The parameter-only part of tc_decoder_nll_fwd (packed fp16 weight tiles, per-gene constants and tables)
 // into the same workspace layout: lets the caller run it on another stream while the encoder computes.
@@ -504,6 +518,8 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
                        float* row_stats, const float* g_reconst, float* dh, int64_t lddh, void* ws,
                        cudaStream_t st, bool prepacked, int xkind) {
   const float* x = reinterpret_cast<const float*>(xv);  // the inference kernels below read fp32 counts only
+  const bool keep_ops = (xkind & 16) != 0;  // SCVI_PREC_AOPS
+  xkind &= 15;
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   if (H != TC_H) {
     set_error("scvi_decoder_nll_fwd(SCVI_PREC_TC): n_hidden must be %d (got %lld)", TC_H, (long long)H);
@@ -534,7 +550,7 @@ int tc_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_
     SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc lse)");
     return tc_launch_nll_dh(zinb, xkind, h, ldh, B, G, packed32, xv, ldx, row_idx, library, lse, p.nsplit, p.nsplit2,
                             p.tiles_per_split2, outp, (float*)(w8 + p.off_dh), g_reconst, reconst, row_stats, dh,
-                            lddh, st);
+                            lddh, keep_ops ? w8 + p.off_aops : nullptr, keep_ops ? (float*)(w8 + p.off_fmax) : nullptr, st);
   }
   if (xkind == 2) {
     set_error("scvi_decoder_nll_fwd(SCVI_X_U8): uint8 counts are read by the training kernels only (dh requested)");

@@ -157,12 +157,12 @@ struct K2Smem {
 // the 8 elements of one thread for one tile.  Padded genes (beyond G) carry constants that make every output an
 // exact zero (scale bias -1e30 => mu = 0, dropout bias 0, theta 1, count 0), so nothing is masked here; rows
 // beyond B produce values that are never stored.
-template <bool ZINB, bool LEAN>
+template <bool ZINB, bool LEAN, bool DTH>
 __device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi)[8], const float (&sv)[8],
                                             const float (&pv)[8], const float* __restrict__ gc,
                                             const float* __restrict__ tab, const float* __restrict__ s_lgx1, float krow,
                                             float eps, float s1, float kP, float kD, float& nll, float& S,
-                                            float (&a1)[8], float (&a2)[8], float (&a3)[8]) {
+                                            float (&a1)[8], float (&a2)[8], float (&a3)[8], float (&a4)[8]) {
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const float4 k0 = *reinterpret_cast<const float4*>(gc + i * TC_GC);
@@ -171,28 +171,43 @@ __device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi
     gk.theta = k0.x; gk.log_theta = k0.y; gk.lg_theta = k0.z; gk.rth = k1.y; gk.dg_theta = k1.z;
     const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
     const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
-    float ll, g1, dpi, mu;
+    float ll, g1, dpi, mu, dthp = 0.f;
     if (LEAN)
-      fm::elem_fwd_lean<ZINB>(xq[i], tab[i * fm::LGT + xi[i]], sl, pl, krow, gk, eps, ll, g1, dpi, mu);
+      fm::elem_fwd_lean<ZINB, DTH>(xq[i], tab[i * fm::LGT + xi[i]], sl, pl, krow, gk, eps, ll, g1, dpi, mu, &dthp);
     else
-      fm::elem_fwd_tab<ZINB>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu);
+      fm::elem_fwd_tab<ZINB, DTH>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu, &dthp);
     nll -= ll;
     S += g1;
     a1[i] = g1 * s1;
     a2[i] = mu * kP;
     a3[i] = dpi * kD;
+    // d(ll)/d(theta) without its digamma term (K3 as a pure GEMM: DESIGN section 4.3); padded genes give an exact 0
+    if (DTH) a4[i] = fmaxf(dthp, -60000.f);  // dth' <= 0 (log(1 + y) >= y / (1 + y)): one-sided clamp
   }
 }
 
-template <bool ZINB, int XK>
+// Staged operands of K2 kept for the weight-gradient GEMM (SCVI_PREC_AOPS): part p of (row tile rt, 16-row piece o,
+// 32-gene tile t, 8-gene chunk cg) = 16 rows x 16 B at
+//   aops + p * tt_aops_part_bytes + ((((rt * 8 + o) * nT4 + t) * 4 + cg) * 256,    nT4 = tiles padded to whole 128-gene blocks
+// i.e. the 4 KB block [16 gene chunks][16 rows][16 B] of (row piece, 128-gene block) is contiguous: an MN-major A
+// operand of the GEMM, one bulk copy.  Parts: 0/1 = g1 s1 hi/lo, 2/3 = p 2^P hi/lo, 4/5 = dth' hi/lo, 6/7 = -dpi 2^D hi/lo.
+__host__ __device__ inline int64_t tt_nT4(int64_t G) { return ((G + TC_M - 1) / TC_M) * 4; }
+__host__ __device__ inline size_t tt_aops_part_bytes(int64_t B, int64_t G) {
+  return (size_t)((B + TC_M - 1) / TC_M) * 8 * tt_nT4(G) * 4 * 256;
+}
+__host__ __device__ inline int tt_aops_parts(bool zinb) { return zinb ? 8 : 6; }
+size_t tc_aops_bytes(int64_t B, int64_t G, bool zinb) { return tt_aops_part_bytes(B, G) * tt_aops_parts(zinb); }
+
+template <bool ZINB, int XK, bool AOPS>
 __global__ void __launch_bounds__(TT_THREADS, 1)
     tc_nll_dh_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, int64_t G,
                      const uint8_t* __restrict__ packed32, const void* __restrict__ x, int64_t ldx,
                      const int64_t* __restrict__ row_idx, const float* __restrict__ library,
                      const float* __restrict__ lse_part /*[nsplit_lse][B][2]*/, int nsplit_lse, int tiles_per_split,
                      float eps, int xvec, float* __restrict__ out_part /*[nsplit][B][2] = (nll, S)*/,
-                     float* __restrict__ dh_part /*[nsplit][2][B][H]*/) {
+                     float* __restrict__ dh_part /*[nsplit][2][B][H]*/, uint8_t* __restrict__ aops /*nullable*/) {
   using L = K2Smem<ZINB>;
+  constexpr bool DTH = AOPS && XK != XK_F32;  // integer counts: the operands are kept for the dW GEMM
   constexpr int NH = L::NH;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
@@ -382,15 +397,31 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
       const float* tab = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32 + TC_GC32_BYTES) +
                          8 * cg * fm::LGT;
-      float a1[8], a2[8], a3[8];
+      float a1[8], a2[8], a3[8], a4[8];
       if (XK != XK_F32 && lean)
-        tt_k2_elems<ZINB, true>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
+        tt_k2_elems<ZINB, true, DTH>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3, a4);
       else
-        tt_k2_elems<ZINB, false>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
+        tt_k2_elems<ZINB, false, DTH>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3, a4);
       uint4 hi1, lo1, hi2, lo2, hi3, lo3;
       tc::split8(a1, hi1, lo1);
       tc::split8(a2, hi2, lo2);
       if (ZINB) tc::split8(a3, hi3, lo3);
+      if (DTH && aops) {  // keep the operands for the dW GEMM (a warp writes two 256-byte pieces per part)
+        uint4 hi4, lo4;
+        tc::split8(a4, hi4, lo4);
+        const size_t ps = tt_aops_part_bytes(B, G);
+        uint8_t* o = aops + ((((size_t)blockIdx.x * 8 + (r >> 4)) * tt_nT4(G) + (t0 + j)) * 4 + cg) * 256 + (r & 15) * 16;
+        *reinterpret_cast<uint4*>(o + 0 * ps) = hi1;
+        *reinterpret_cast<uint4*>(o + 1 * ps) = lo1;
+        *reinterpret_cast<uint4*>(o + 2 * ps) = hi2;
+        *reinterpret_cast<uint4*>(o + 3 * ps) = lo2;
+        *reinterpret_cast<uint4*>(o + 4 * ps) = hi4;
+        *reinterpret_cast<uint4*>(o + 5 * ps) = lo4;
+        if (ZINB) {
+          *reinterpret_cast<uint4*>(o + 6 * ps) = hi3;
+          *reinterpret_cast<uint4*>(o + 7 * ps) = lo3;
+        }
+      }
 #ifdef SCVI_K2_TRACE
       asm volatile("" ::"r"(hi1.x), "r"(lo2.w), "r"(hi3.y) : "memory");  // the math is done before the stamp
 #endif
@@ -471,11 +502,27 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
                                         const float* __restrict__ out_part, const float* __restrict__ dh_part,
                                         int nsplit, const float* __restrict__ library,
                                         const float* __restrict__ g_reconst, int64_t B, float* __restrict__ reconst,
-                                        float* __restrict__ row_stats, float* __restrict__ dh, int64_t lddh) {
+                                        float* __restrict__ row_stats, float* __restrict__ dh, int64_t lddh,
+                                        float* __restrict__ fmax_part /*[blocks][3], nullable*/) {
   // 32 threads per row (one float4 of dh each), 8 rows per block
+  __shared__ float s_f[8][3];
   const int64_t b = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
-  if (b >= B) return;
+  if (fmax_part) {  // block maxima of the per-row factors (u 2^(e-14), u |S| 2^-P, u): operand scales of the dW GEMM
+    if (lane < 3) s_f[threadIdx.x >> 5][lane] = 0.f;
+    __syncthreads();
+  }
+  if (b >= B) {
+    if (fmax_part) {
+      __syncthreads();
+      if (threadIdx.x < 3) {
+        float m = 0.f;
+        for (int r = 0; r < 8; ++r) m = fmaxf(m, s_f[r][threadIdx.x]);
+        fmax_part[(int64_t)blockIdx.x * 3 + threadIdx.x] = m;
+      }
+    }
+    return;
+  }
   float m = -INFINITY, l = 0.f;
   for (int sp = 0; sp < nsplit_lse; ++sp) {
     const float2 ml = *reinterpret_cast<const float2*>(lse_part + ((int64_t)sp * B + b) * 2);
@@ -494,6 +541,13 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
   if (lane == 0) {
     reconst[b] = nll;
     *reinterpret_cast<float4*>(row_stats + b * 4) = make_float4(m, l, expf(library[b]) / l, S);
+    if (fmax_part) {
+      const float u = fabsf(g_reconst ? g_reconst[b] : 1.f);
+      const int e = max(-100, min(100, (int)ceilf(library[b] * fm::LOG2E)));  // as the fused kernel's operand scale
+      s_f[threadIdx.x >> 5][0] = u * tc::pow2i(e - 14);
+      s_f[threadIdx.x >> 5][1] = u * fabsf(S) * tc::pow2i(-TC_P_SCALE_LOG2);
+      s_f[threadIdx.x >> 5][2] = u;
+    }
   }
   if (dh) {
     float4 a = make_float4(0.f, 0.f, 0.f, 0.f), c = a;
@@ -508,22 +562,31 @@ __global__ void tc_train_combine_kernel(const float* __restrict__ lse_part, int 
     *reinterpret_cast<float4*>(dh + b * lddh + 4 * lane) =
         make_float4(u * (a.x - S * c.x), u * (a.y - S * c.y), u * (a.z - S * c.z), u * (a.w - S * c.w));
   }
+  if (fmax_part) {
+    __syncthreads();
+    if (threadIdx.x < 3) {
+      float mx = 0.f;
+      for (int r = 0; r < 8; ++r) mx = fmaxf(mx, s_f[r][threadIdx.x]);
+      fmax_part[(int64_t)blockIdx.x * 3 + threadIdx.x] = mx;
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------
 // host: K2 launcher (called by tc_decoder_nll_fwd in decoder_tc.cu when dh is requested)
 // ---------------------------------------------------------------------------------------
-template <bool ZINB, int XK>
+template <bool ZINB, int XK, bool AOPS>
 static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const uint8_t* packed32, const void* x,
                         int64_t ldx, const int64_t* row_idx, const float* library, const float* lse, int nsplit_lse,
-                        int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, cudaStream_t st) {
-  auto k = tc_nll_dh_kernel<ZINB, XK>;
+                        int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, uint8_t* aops,
+                        cudaStream_t st) {
+  auto k = tc_nll_dh_kernel<ZINB, XK, AOPS>;
   constexpr int smem = (int)K2Smem<ZINB>::TOTAL + 128;
   static std::atomic<uint64_t> optin{0};
   if (int rc = smem_optin((const void*)k, smem, optin, "tc_nll_dh")) return rc;
   dim3 grid((unsigned)cdiv(B, TC_M), (unsigned)nsplit);
   k<<<grid, TT_THREADS, smem, st>>>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, tiles_per_split,
-                                    1e-8f, xvec, out_part, dh_part);
+                                    1e-8f, xvec, out_part, dh_part, aops);
   return SCVI_OK;
 }
 
@@ -532,19 +595,24 @@ int tc_launch_nll_dh(bool zinb, int xkind, const float* h, int64_t ldh, int64_t 
                      const void* x, int64_t ldx, const int64_t* row_idx, const float* library, const float* lse,
                      int nsplit_lse, int nsplit, int tiles_per_split, float* out_part, float* dh_part,
                      const float* g_reconst, float* reconst, float* row_stats, float* dh, int64_t lddh,
-                     cudaStream_t st) {
+                     uint8_t* aops, float* fmax_part, cudaStream_t st) {
   const int xvec = xkind == XK_U8 ? ((ldx % 8 == 0) && ((uintptr_t)x % 8 == 0))
                                   : ((ldx % 4 == 0) && (G % 4 == 0) && ((uintptr_t)x % 16 == 0));
   int rc;
-#define SCVI_K2(Z, K) \
-  tt_launch_k2<Z, K>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit, tiles_per_split, xvec, out_part, dh_part, st)
-  if (zinb) rc = xkind == XK_U8 ? SCVI_K2(true, XK_U8) : xkind == XK_F32_INT ? SCVI_K2(true, XK_F32_INT) : SCVI_K2(true, XK_F32);
-  else rc = xkind == XK_U8 ? SCVI_K2(false, XK_U8) : xkind == XK_F32_INT ? SCVI_K2(false, XK_F32_INT) : SCVI_K2(false, XK_F32);
+#define SCVI_K2(Z, K, A) \
+  tt_launch_k2<Z, K, A>(h, ldh, B, G, packed32, x, ldx, row_idx, library, lse, nsplit_lse, nsplit, tiles_per_split, xvec, out_part, dh_part, aops, st)
+  const bool keep = aops != nullptr && xkind != XK_F32;
+  if (zinb) rc = xkind == XK_U8 ? (keep ? SCVI_K2(true, XK_U8, true) : SCVI_K2(true, XK_U8, false))
+                 : xkind == XK_F32_INT ? (keep ? SCVI_K2(true, XK_F32_INT, true) : SCVI_K2(true, XK_F32_INT, false))
+                                       : SCVI_K2(true, XK_F32, false);
+  else rc = xkind == XK_U8 ? (keep ? SCVI_K2(false, XK_U8, true) : SCVI_K2(false, XK_U8, false))
+            : xkind == XK_F32_INT ? (keep ? SCVI_K2(false, XK_F32_INT, true) : SCVI_K2(false, XK_F32_INT, false))
+                                  : SCVI_K2(false, XK_F32, false);
 #undef SCVI_K2
   if (rc) return rc;
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc nll+dh)");
   tc_train_combine_kernel<<<(unsigned)cdiv(B, 8), 256, 0, st>>>(lse, nsplit_lse, out_part, dh_part, nsplit, library,
-                                                               g_reconst, B, reconst, row_stats, dh, lddh);
+                                                               g_reconst, B, reconst, row_stats, dh, lddh, fmax_part);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_fwd(tc combine)");
   return SCVI_OK;
 }
@@ -950,6 +1018,13 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
                                      float* __restrict__ gconst);
 
 void tc_decoder_fwd_ws_offsets(int64_t B, int64_t G, int nheads, size_t* off_packed, size_t* off_gconst);
+void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops);
+int64_t tc_decoder_bwd2_ws_bytes(int64_t B, int64_t G, int likelihood);  // decoder_tc_dw2.cu
+int tc_decoder_nll_bwd_dw2(const float* h, int64_t ldh, int64_t B, int64_t G, const float* px_r, const void* x,
+                           int64_t ldx, const int64_t* row_idx, const float* library, const float* row_stats,
+                           const float* g_reconst, int likelihood, float* dWs, float* dbs, float* dWp, float* dbp,
+                           float* dpx_r, void* ws, const uint8_t* aops, const float* fmax_part, const float* slabpsi,
+                           cudaStream_t st);
 
 struct TtBwdPlan {
   int64_t nT, nR;
@@ -976,7 +1051,8 @@ static TtBwdPlan tt_bwd_plan(int64_t B, int64_t G, int nheads) {
 }
 
 int64_t tc_decoder_bwd_ws_bytes(int64_t B, int64_t G, int likelihood) {
-  return (int64_t)tt_bwd_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
+  return std::max<int64_t>((int64_t)tt_bwd_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total,
+                           tc_decoder_bwd2_ws_bytes(B, G, likelihood));
 }
 
 template <bool ZINB, int XK>
@@ -997,9 +1073,19 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
                           const float* Wp, const float* bp, const float* px_r, const void* x, int64_t ldx,
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
                           float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
-                          int xkind, cudaStream_t st) {
+                          int xkind, const float* library, cudaStream_t st) {
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   const int nheads = zinb ? 2 : 1;
+  if (xkind & 16) {  // SCVI_PREC_AOPS: the matching forward kept its operands in fwd_ws -> pure GEMM
+    SCVI_REQUIRE(fwd_ws != nullptr, "scvi_decoder_nll_bwd(SCVI_PREC_AOPS): needs the forward workspace");
+    size_t off_fmax, off_psi, off_aops;
+    tc_decoder_fwd_ws_aops(B, G, nheads, &off_fmax, &off_psi, &off_aops);
+    const uint8_t* f8 = (const uint8_t*)fwd_ws;
+    return tc_decoder_nll_bwd_dw2(h, ldh, B, G, px_r, x, ldx, row_idx, library, row_stats, g_reconst, likelihood, dWs, dbs,
+                                  dWp, dbp, dpx_r, ws, f8 + off_aops, (const float*)(f8 + off_fmax),
+                                  (const float*)(f8 + off_psi), st);
+  }
+  xkind &= 15;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): ws must be 256-byte aligned");
   SCVI_REQUIRE(ldh % 4 == 0 && ((uintptr_t)h % 16 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): h must be 16-byte aligned");
   const TtBwdPlan p = tt_bwd_plan(B, G, nheads);

@@ -17,6 +17,7 @@ BatchNorm in encoder and decoder, no LayerNorm.  Anything else: use the autograd
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -279,7 +280,15 @@ class FusedTrainingPlan:
         self.ws_mid = (torch.empty(int(query("scvi_mid_ws_bytes", B, L, ncols)), dtype=torch.uint8, device=dev)
                        if self.use_mid else None)
         self.dy1_amax = f(int(query("scvi_mid_n_tiles", B)))  # max |dy1| per row tile (mid_bwd -> encoder dW)
-        nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik, self.module.precision)
+        # SCVI_AOPS=1 (integer counts + tcgen05 kernels): the fused likelihood kernel keeps its per-element operands in
+        # the forward workspace and the head-weight gradients are a pure tensor-core GEMM over them (SCVI_PREC_AOPS).
+        # Opt-in: parity-green, the GEMM takes 54 us where the recompute kernel takes 99 us, but keeping the operands
+        # costs the fused kernel ~35 us (it is bound by its instruction count), so the step does not get faster
+        # 
+        self._aops = (_lib.PREC_AOPS if (self.module.precision == _lib.PREC_TC and H == 128 and self._x_integer
+                                         and os.environ.get("SCVI_AOPS", "0") == "1") else 0)
+        nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik,
+                   self.module.precision | (_lib.X_INTEGER | self._aops if self._aops else 0))
         self.ws_fwd = torch.empty(int(nf), dtype=torch.uint8, device=dev) if nf > 0 else None
         self.enc_tc = _lib.LIN_TC if (self.module.precision == _lib.PREC_TC and H == 128) else 0
         ne = query("scvi_linear_fwd_ws_bytes", B, G, H, _lib.LIN_LOG1P | self.enc_tc)
@@ -312,6 +321,7 @@ class FusedTrainingPlan:
         xkind = 0
         if prec == _lib.PREC_TC:
             xkind = _lib.X_U8 if X.dtype == torch.uint8 else (_lib.X_INTEGER if self._x_integer else 0)
+        aops = self._aops if xkind else 0
         Ws, bs = P["decoder.px_scale_decoder.0.weight"], P["decoder.px_scale_decoder.0.bias"]
         Wp = P.get("decoder.px_dropout_decoder.weight")
         bp = P.get("decoder.px_dropout_decoder.bias")
@@ -329,6 +339,9 @@ class FusedTrainingPlan:
                 if self._ev_prologue is None:
                     self._ev_prologue = torch.cuda.Event()
                 self._ev_prologue.record(side)
+            if aops:  # count-only part of the dispersion gradient: needs the counts and the loss weights only
+                call("scvi_decoder_dpsi_sums", _p(X), ldx, _p(self.idx), B, G, _p(P["px_r"]), _p(self.g_rec), lik,
+                     prec | xkind | aops, _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
             call("scvi_decoder_nll_prepack", B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), lik, prec, 1,
                  _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
         if prologue is not None and not overlap:
@@ -361,7 +374,7 @@ class FusedTrainingPlan:
         if overlap:
             main.wait_stream(side)  # packed weight tiles ready
         call("scvi_decoder_nll_fwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), lik, prec | xkind | (_lib.PREC_PREPACKED if overlap else 0), _p(self.reconst),
+             _p(self.idx), _p(self.library), lik, prec | xkind | aops | (_lib.PREC_PREPACKED if overlap else 0), _p(self.reconst),
              _p(self.stats), _p(self.g_rec), _p(self.dh), H, _p(self.ws_fwd), st)
         if overlap:
             side.wait_stream(main)
@@ -370,8 +383,11 @@ class FusedTrainingPlan:
         else:
             call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         # ---- backward
+        if aops and not overlap:
+            call("scvi_decoder_dpsi_sums", _p(X), ldx, _p(self.idx), B, G, _p(P["px_r"]), _p(self.g_rec), lik,
+                 prec | xkind | aops, _p(self.ws_fwd), st)
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
-             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec | xkind, None, H,
+             _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec | xkind | aops, None, H,
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
              _p(Gd.get("decoder.px_dropout_decoder.weight")), _p(Gd.get("decoder.px_dropout_decoder.bias")),
              _p(Gd["px_r"]), _p(self.ws), _p(self.ws_fwd) if prec == _lib.PREC_TC else None, st)
