@@ -612,7 +612,7 @@ def run_b200_arm(a):
     compact = hdt == torch.uint8 and a.precision == "tc" and a.resident != "f32"
     for name, devg in (("device_gather", True), ("host_gather", False)):
         feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg,
-                                    compact_stage=compact and not devg)
+                                    compact_stage=compact)
         if devg and not feeder.device_gather:
             continue
         med, allb = run_e2e(feeder, lambda slot, i, f=feeder: f.submit(slot, rows=rows_of(i)))
@@ -634,7 +634,7 @@ def run_b200_arm(a):
            "how": "whole count matrix in pinned host memory (narrowest lossless count type); per step: random row ids "
                   "-> rows over PCIe (device_gather: a gather kernel reads the mapped host pages; host_gather: "
                   "index_select on the host threads + cudaMemcpyAsync; uint8 counts land in the uint8 staging rows the "
-                  "tcgen05 kernels read, device_gather expands to fp32 rows), fused step, "
+                  "tcgen05 kernels read), fused step, "
                   "loss D2H each step read on the host one step behind the launch; preformed_minibatches = the "
                   "round-1 figure (no per-step row gather), kept for continuity"}
     del host_mat, pre_x

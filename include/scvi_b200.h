@@ -99,6 +99,9 @@ int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int6
  * integer-typed `adata.X`).  idx == NULL means the identity (expand rows 0..B-1 in place order). */
 int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t ldx,
                          const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
+/* uint8 rows copied unexpanded (for the kernels that read uint8 counts, SCVI_X_U8): out[b, :] = X[idx[b], :] */
+int scvi_gather_rows_u8_raw(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx, int64_t B,
+                            uint8_t* out, int64_t ldo, void* stream);
 int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx,
                         const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
 

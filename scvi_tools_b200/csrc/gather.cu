@@ -65,6 +65,32 @@ __global__ void gather_rows_int_kernel(const T* __restrict__ X, int64_t ldx, con
   }
 }
 
+// uint8 rows copied as they are (the tensor-core training kernels read uint8 counts): out[b, :] = X[idx[b], :].
+// With X in pinned host memory (mapped) this is the H2D copy AND the row gather of a host-streamed minibatch.
+template <bool VEC>
+__global__ void gather_rows_u8_raw_kernel(const uint8_t* __restrict__ X, int64_t ldx, const int64_t* __restrict__ idx,
+                                          int64_t B, int64_t G, uint8_t* __restrict__ out, int64_t ldo) {
+  for (int64_t b = blockIdx.y; b < B; b += gridDim.y) {
+    const uint8_t* src = X + (idx ? idx[b] : b) * ldx;
+    uint8_t* dst = out + b * ldo;
+    if (VEC) {
+      const int64_t nv = G >> 4;
+      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (int64_t)gridDim.x * blockDim.x) {
+        uint4 raw;
+        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w)
+                     : "l"(src + 16 * i));
+        *reinterpret_cast<uint4*>(dst + 16 * i) = raw;
+      }
+      for (int64_t i = nv * 16 + blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+    } else {
+      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+    }
+  }
+}
+
 template <typename T>
 static int launch_gather_int(const T* X, int64_t ldx, const int64_t* idx, int64_t B, int64_t G, float* out,
                              int64_t ldo, cudaStream_t st, const char* name) {
@@ -150,6 +176,21 @@ int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t l
   SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_u16: identity expansion of more rows than the matrix holds");
   if (B == 0 || G == 0) return SCVI_OK;
   return launch_gather_int<uint16_t>(X, ldx, idx, B, G, out, ldo, (cudaStream_t)stream, "scvi_gather_rows_u16");
+}
+
+int scvi_gather_rows_u8_raw(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx, int64_t B,
+                            uint8_t* out, int64_t ldo, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(X && out, "scvi_gather_rows_u8_raw: NULL pointer");
+  SCVI_REQUIRE(n_rows >= 0 && G >= 0 && B >= 0 && ldx >= G && ldo >= G, "scvi_gather_rows_u8_raw: bad shape");
+  SCVI_REQUIRE(idx || B <= n_rows, "scvi_gather_rows_u8_raw: identity copy of more rows than the matrix holds");
+  if (B == 0 || G == 0) return SCVI_OK;
+  const bool vec = (ldx % 16 == 0) && ((uintptr_t)X % 16 == 0) && (ldo % 16 == 0) && ((uintptr_t)out % 16 == 0) && G >= 16;
+  dim3 grid(1, (unsigned)std::min<int64_t>(B, 65535));
+  if (vec) gather_rows_u8_raw_kernel<true><<<grid, 128, 0, (cudaStream_t)stream>>>(X, ldx, idx, B, G, out, ldo);
+  else gather_rows_u8_raw_kernel<false><<<grid, 128, 0, (cudaStream_t)stream>>>(X, ldx, idx, B, G, out, ldo);
+  SCVI_LAUNCH_CHECK("scvi_gather_rows_u8_raw");
+  return SCVI_OK;
 }
 
 int scvi_gather_rows_u8(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx,

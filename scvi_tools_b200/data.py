@@ -96,7 +96,6 @@ class HostStreamedCounts:
         if self.compact_stage:
             self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G, dtype=torch.uint8), compress="u8",
                                               batch=torch.zeros(2 * self.B, dtype=torch.int64), device=self.dev)
-            device_gather = False  # the device-side gather kernels expand to fp32
         else:
             self.stage = DeviceResidentCounts(torch.zeros(2 * self.B, G), batch=torch.zeros(2 * self.B, dtype=torch.int64),
                                               device=self.dev)
@@ -173,8 +172,9 @@ class HostStreamedCounts:
         G = self.n_vars
         self.freed[slot].synchronize()  # the pinned index buffer of this slot is reused
         self._pin_idx[slot][:n].copy_(rows)
-        fn = {torch.uint8: "scvi_gather_rows_u8", torch.uint16: "scvi_gather_rows_u16",
-              torch.float32: "scvi_gather_rows"}[self.dtype]
+        fn = ("scvi_gather_rows_u8_raw" if self.compact_stage else
+              {torch.uint8: "scvi_gather_rows_u8", torch.uint16: "scvi_gather_rows_u16",
+               torch.float32: "scvi_gather_rows"}[self.dtype])
         with torch.cuda.stream(self.copy_stream):
             st = C.c_void_p(self.copy_stream.cuda_stream)
             idx = self._dev_idx[lo : lo + n]

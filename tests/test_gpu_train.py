@@ -260,3 +260,34 @@ def test_adam_graph_counter_advances_without_extra_kernel():
         torch.cuda.synchronize()
         assert counter.tolist() == [step + 1, 0]
     assert rel_err(p.cpu(), ref.detach().cpu()) < 1e-6
+
+
+@pytest.mark.parametrize("device_gather", [True, False], ids=["device-gather", "host-gather"])
+def test_streamed_uint8_stage_trains_like_resident_counts(device_gather):
+    """`HostStreamedCounts(compact_stage=True)`: uint8 host counts land unexpanded in uint8 staging rows (rows gathered
+    by the GPU straight from the pinned host matrix, or by the host threads) and the tcgen05 kernels read them as
+    they are -- identical weights to training on the HBM-resident matrix, ragged last minibatch included."""
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.data import DeviceResidentCounts, HostStreamedCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+
+    X, batch = O.synthetic_iid(700, 200, 3, seed=2)  # 200 % 16 != 0: padded staging rows
+    out = []
+    for streamed in (False, True):
+        torch.manual_seed(0)
+        m = S.VAE(n_input=200, n_batch=3, n_hidden=128, precision=1).train()
+        if streamed:
+            host = HostStreamedCounts(X, batch=batch, batch_size=256, device="cuda:0", compact_stage=True,
+                                      device_gather=device_gather)
+            assert host.dtype == torch.uint8 and host.stage.X.dtype == torch.uint8 and host.stage.X.stride(0) % 16 == 0
+            assert host.device_gather == device_gather
+            plan = FusedTrainingPlan(m, host.stage, batch_size=256, seed=3)
+            hist = plan.fit_streamed(host, max_epochs=2)
+        else:
+            plan = FusedTrainingPlan(m, DeviceResidentCounts(X, batch=batch, device="cuda:0"), batch_size=256, seed=3)
+            hist = plan.fit(max_epochs=2)
+        assert hist[-1]["n_cells"] == X.shape[0]
+        out.append(({k: v.detach().clone() for k, v in m.state_dict().items()}, hist))
+    for k in out[0][0]:
+        assert torch.equal(out[0][0][k], out[1][0][k]), k
+    assert out[0][1][-1]["train_loss"] == out[1][1][-1]["train_loss"]
