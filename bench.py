@@ -272,23 +272,26 @@ class ClockSampler(threading.Thread):
                 "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
-def algorithmic_bytes(a, B, n_arena):
-    """SURVEY.md section 8(d) / DESIGN.md section 4: algorithmic HBM bytes per launch of the main kernels (fp32
-    operands, every input read once, every output written once), keyed by the launch label."""
+def algorithmic_bytes(a, B, n_arena, xbytes=4):
+    """SURVEY.md section 8(d) / DESIGN.md section 4: algorithmic HBM bytes per launch of the main kernels (every input
+    read once, every output written once), keyed by the launch label.  `xbytes` = bytes per count: 4 is SURVEY's
+    figure (fp32 operands, what `roofline.achieved` is defined on); 1 is what the kernels move with uint8-resident
+    counts (reported beside it)."""
     G, H = a.genes, N_HIDDEN
     heads = 2 if a.likelihood == "zinb" else 1
     W = heads * 4 * G * H  # head weights, fp32
+    xb = xbytes
     return {
         # K2: x rows + h + (lse, library) in; dh + (reconst, S) out; head weights + 5 per-gene constants in
-        "scvi_decoder_nll_fwd(tc nll+dh)": B * (4 * G + 4 * H + 16) + B * (4 * H + 8) + W + 20 * G,
+        "scvi_decoder_nll_fwd(tc nll+dh)": B * (xb * G + 4 * H + 16) + B * (4 * H + 8) + W + 20 * G,
         # K1: h + scale-head weights + bias in; (max, sumexp) out
         "scvi_decoder_nll_fwd(tc lse)": B * (4 * H) + 4 * G * H + 4 * G + 8 * B,
         # K3: x rows + h + 4 row constants in; head weights in; dW, db, dpx_r out
-        "scvi_decoder_nll_bwd(tc dW)": B * (4 * G + 4 * H + 16) + W + 20 * G + W + heads * 4 * G + 4 * G,
+        "scvi_decoder_nll_bwd(tc dW)": B * (xb * G + 4 * H + 16) + W + 20 * G + W + heads * 4 * G + 4 * G,
         # E1: x rows + W in; y + library out
-        "scvi_linear_fwd(tc)": B * (4 * G + 8) + 4 * G * H + B * (4 * H + 4),
+        "scvi_linear_fwd(tc)": B * (xb * G + 8) + 4 * G * H + B * (4 * H + 4),
         # E2: x rows + dy in; dW out
-        "scvi_linear_bwd(tc dW)": B * (4 * G + 8 + 4 * H) + 4 * G * H,
+        "scvi_linear_bwd(tc dW)": B * (xb * G + 8 + 4 * H) + 4 * G * H,
         "scvi_gather_rows": 2 * 4 * B * G + 8 * B,
         "scvi_adam_step_graph": 28 * n_arena,
     }
@@ -655,11 +658,15 @@ def run_b200_arm(a):
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
         ab = algorithmic_bytes(a, B, plan.n_arena)
+        ab1 = algorithmic_bytes(a, B, plan.n_arena, xbytes=1) if compress else None
         for k, v in kern.items():
             v["algorithmic_bytes"] = ab.get(k)
             if ab.get(k):
                 v["GBps"] = ab[k] / v["ms"] / 1e6
                 v["frac_of_hbm_peak"] = v["GBps"] / peak
+                if ab1:  # what the kernel actually has to move with uint8-resident counts
+                    v["bytes_uint8_counts"] = ab1[k]
+                    v["GBps_uint8_counts"] = ab1[k] / v["ms"] / 1e6
         step_kernels = {k: v for k, v in kern.items() if k != "scvi_gather_rows"}
         dom = max(step_kernels, key=lambda k: step_kernels[k]["ms"] * step_kernels[k]["launches_per_step"])
         eager_ms = sum(v["ms"] * v["launches_per_step"] for v in step_kernels.values())
@@ -667,16 +674,22 @@ def run_b200_arm(a):
         try:  # DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` capture
             tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
             ent = tr.get(dom)
-            if ent and ent["batch_size"] == B and ent["genes"] == a.genes and ent["likelihood"] == a.likelihood:
+            if (ent and ent["batch_size"] == B and ent["genes"] == a.genes and ent["likelihood"] == a.likelihood
+                    and ent.get("resident_counts", "float32") == ("uint8" if compress else "float32")):
                 traffic = ent["dram_bytes_per_launch"]
         except Exception:
             pass
         roof = {"bound": "hbm", "kernel": dom, "achieved": kern[dom].get("GBps"), "peak": peak, "unit": "GB/s",
                 "frac": (kern[dom]["GBps"] / peak) if kern[dom].get("GBps") else None, "traffic": traffic,
                 "algorithmic_bytes": kern[dom]["algorithmic_bytes"], "kernel_ms": kern[dom]["ms"],
+                "algorithmic_bytes_uint8_counts": kern[dom].get("bytes_uint8_counts"),
+                "achieved_uint8_counts": kern[dom].get("GBps_uint8_counts"),
                 "peak_source": peak_src, "share_of_step": kern[dom]["ms"] * kern[dom]["launches_per_step"] / eager_ms,
                 "note": "HBM is the nearest roofline of the step's streaming kernels; the dominant kernel is limited "
-                        "by the issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4)"}
+                        "by the issue rate of the per-element likelihood math, not by bytes (DESIGN.md section 4). "
+                        "`achieved` / `frac` are on SURVEY 8(d)'s algorithmic bytes (fp32 counts, 4 B each); with the "
+                        "uint8-resident counts this run uses the kernel moves `algorithmic_bytes_uint8_counts` "
+                        "(`achieved_uint8_counts` GB/s) and `traffic` is the ncu DRAM figure of that uint8 kernel"}
     # ---- the other workloads SURVEY 8(d) asks for, as extra keys of the same line (every rank runs them: the
     # plans are data-parallel); each is W' warm-up steps + the median of 3 blocks of K steps
     if not a.no_extras:
