@@ -67,6 +67,9 @@ def parse():
     ap.add_argument("--e2e-dtype", default="auto", choices=["auto", "u16", "f32"],
                     help="host count type of the e2e leg: auto = narrowest lossless (uint8 / uint16 / float32)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--hybrid-fraction", type=float, default=0.45,
+                    help="e2e hybrid route: fraction of every minibatch the GPU pulls from the pinned host matrix "
+                         "itself while the host threads gather the rest (0 = skip the route)")
     ap.add_argument("--resident", default="auto", choices=["auto", "u8", "f32"],
                     help="type of the HBM-resident count matrix: uint8 when every count is < 256 (auto), or fp32")
     ap.add_argument("--value-only", action="store_true",
@@ -613,9 +616,12 @@ def run_b200_arm(a):
     legs = {}
     # uint8 host counts + tcgen05 kernels: the H2D copy lands in the uint8 rows the step reads (no expansion kernel)
     compact = hdt == torch.uint8 and a.precision == "tc" and a.resident != "f32"
-    for name, devg in (("device_gather", True), ("host_gather", False)):
+    for name, devg, frac in (("device_gather", True, 0.0), ("host_gather", False, 0.0),
+                             ("hybrid_gather", True, a.hybrid_fraction)):
+        if name == "hybrid_gather" and frac <= 0.0:
+            continue
         feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg,
-                                    compact_stage=compact)
+                                    compact_stage=compact, hybrid_fraction=frac)
         if devg and not feeder.device_gather:
             continue
         med, allb = run_e2e(feeder, lambda slot, i, f=feeder: f.submit(slot, rows=rows_of(i)))
@@ -635,7 +641,8 @@ def run_b200_arm(a):
            "host_dtype": str(hdt).replace("torch.", ""), "losses_read_on_host": len(losses), "route": best,
            "routes": legs, "host_matrix_rows": n_host_rows,
            "how": "whole count matrix in pinned host memory (narrowest lossless count type); per step: random row ids "
-                  "-> rows over PCIe (device_gather: a gather kernel reads the mapped host pages; host_gather: "
+                  "-> rows over PCIe (device_gather: a gather kernel reads the mapped host pages; hybrid_gather: the GPU "
+                  "pulls a fraction of the rows that way WHILE the host threads gather the rest; host_gather: "
                   "index_select on the host threads + cudaMemcpyAsync; uint8 counts land in the uint8 staging rows the "
                   "tcgen05 kernels read), fused step, "
                   "loss D2H each step read on the host one step behind the launch; preformed_minibatches = the "

@@ -99,6 +99,11 @@ int scvi_gather_i64(const int64_t* src, int64_t n_rows, const int64_t* idx, int6
  * integer-typed `adata.X`).  idx == NULL means the identity (expand rows 0..B-1 in place order). */
 int scvi_gather_rows_u16(const uint16_t* X, int64_t n_rows, int64_t G, int64_t ldx,
                          const int64_t* idx, int64_t B, float* out, int64_t ldo, void* stream);
+/* HOST code (no CUDA call): out[b, :] = X[idx[b], :] for a matrix in host memory, rows of `row_bytes` bytes, on a
+ * persistent pool of `n_threads` host threads (0 = all hardware threads) -- the per-minibatch `data[indexes]` of
+ * src/scvi/data/_anntorchdataset.py:143-152 ahead of the H2D copy.  Blocking; idx is checked against n_rows. */
+int scvi_host_gather_rows(const void* X, int64_t n_rows, int64_t row_bytes, int64_t ldx_bytes, const int64_t* idx,
+                          int64_t B, void* out, int64_t ldo_bytes, int n_threads);
 /* uint8 rows copied unexpanded (for the kernels that read uint8 counts, SCVI_X_U8): out[b, :] = X[idx[b], :] */
 int scvi_gather_rows_u8_raw(const uint8_t* X, int64_t n_rows, int64_t G, int64_t ldx, const int64_t* idx, int64_t B,
                             uint8_t* out, int64_t ldo, void* stream);

@@ -79,11 +79,18 @@ class HostStreamedCounts:
     """
 
     def __init__(self, X, batch=None, batch_size: int = 128, device="cuda", dtype: torch.dtype | None = None,
-                 device_gather: bool = True, compact_stage: bool = False):
+                 device_gather: bool = True, compact_stage: bool = False, host_threads: int = 0,
+                 hybrid_fraction: float = 0.0):
         """`compact_stage`: keep the staging rows in uint8 (host matrix of uint8 counts only) -- the tensor-core
         training kernels read uint8 counts directly (SCVI_X_U8 / SCVI_LIN_X_U8), so the H2D copy lands in the rows
         the step reads and nothing is expanded."""
         self.dev = torch.device(device)
+        self.host_threads = int(host_threads)  # threads of the host-side row gather (0 = all hardware threads)
+        # > 0: that fraction of every minibatch is pulled by the GPU straight from the mapped pinned matrix (no host
+        # core involved, ~25 GB/s of PCIe reads) WHILE the host threads gather the rest for a copy-engine H2D: the two
+        # routes add up when the host gather is the bottleneck
+        self.hybrid_fraction = float(hybrid_fraction)
+        self._gather_stream = None
         X = torch.as_tensor(np.asarray(X.toarray()) if hasattr(X, "toarray") else X)
         self.dtype = narrowest_count_dtype(X) if dtype is None else dtype
         self.host = X.to(self.dtype).contiguous().pin_memory()
@@ -142,13 +149,20 @@ class HostStreamedCounts:
         """Enqueue the copy of one minibatch into staging slot `slot` (0 / 1): either rows `rows` (host int64
         indices) of the host matrix -- gathered into a pinned buffer first -- or an already formed pinned
         minibatch (`host_x` in this object's dtype, `host_b`).  Returns the number of cells."""
+        if host_x is None and self.device_gather and self.hybrid_fraction > 0.0:
+            return self._submit_hybrid(slot, torch.as_tensor(rows, dtype=torch.int64))
         if host_x is None and self.device_gather:
             return self._submit_device_gather(slot, torch.as_tensor(rows, dtype=torch.int64))
         if host_x is None:
             rows = torch.as_tensor(rows, dtype=torch.int64)
             n = rows.numel()
             self.freed[slot].synchronize()  # the pinned buffer of this slot is reused
-            torch.index_select(self.host, 0, rows, out=self._pin[slot][:n])
+            # the library's host thread pool (rows are 1-4 KB and random: latency-bound, prefetched per thread)
+            pin = self._pin[slot]
+            call("scvi_host_gather_rows", C.c_void_p(self.host.data_ptr()), self.n_obs,
+                 self.n_vars * self.host.element_size(), self.host.stride(0) * self.host.element_size(),
+                 C.c_void_p(rows.data_ptr()), n, C.c_void_p(pin.data_ptr()), pin.stride(0) * pin.element_size(),
+                 self.host_threads)
             torch.index_select(self.host_batch, 0, rows, out=self._pin_b[slot][:n])
             host_x, host_b = self._pin[slot][:n], self._pin_b[slot][:n]
         n = host_x.shape[0]
@@ -166,24 +180,68 @@ class HostStreamedCounts:
             self.ready[slot].record(self.copy_stream)
         return n
 
-    def _submit_device_gather(self, slot: int, rows: torch.Tensor) -> int:
+    def _enqueue_device_gather(self, slot: int, rows: torch.Tensor, lo: int, st_obj) -> None:
+        """Device-side gather of `rows` (host int64) into staging rows lo .. lo + len(rows) on stream `st_obj`."""
         n = rows.numel()
-        lo = slot * self.B
         G = self.n_vars
-        self.freed[slot].synchronize()  # the pinned index buffer of this slot is reused
-        self._pin_idx[slot][:n].copy_(rows)
+        off = lo - slot * self.B
+        self._pin_idx[slot][off : off + n].copy_(rows)
         fn = ("scvi_gather_rows_u8_raw" if self.compact_stage else
               {torch.uint8: "scvi_gather_rows_u8", torch.uint16: "scvi_gather_rows_u16",
                torch.float32: "scvi_gather_rows"}[self.dtype])
-        with torch.cuda.stream(self.copy_stream):
-            st = C.c_void_p(self.copy_stream.cuda_stream)
+        with torch.cuda.stream(st_obj):
+            st = C.c_void_p(st_obj.cuda_stream)
             idx = self._dev_idx[lo : lo + n]
-            idx.copy_(self._pin_idx[slot][:n], non_blocking=True)
+            idx.copy_(self._pin_idx[slot][off : off + n], non_blocking=True)
             out = self.stage.X[lo : lo + n]
             call(fn, C.c_void_p(self._dev_x), self.n_obs, G, self.host.stride(0), C.c_void_p(idx.data_ptr()), n,
                  C.c_void_p(out.data_ptr()), out.stride(0), st)
             call("scvi_gather_i64", C.c_void_p(self._dev_b), self.n_obs, C.c_void_p(idx.data_ptr()), n,
                  C.c_void_p(self.stage.batch[lo : lo + n].data_ptr()), st)
+
+    def _submit_device_gather(self, slot: int, rows: torch.Tensor) -> int:
+        n = rows.numel()
+        lo = slot * self.B
+        self.freed[slot].synchronize()  # the pinned index buffer of this slot is reused
+        self.copy_stream.wait_event(self.freed[slot])
+        self._enqueue_device_gather(slot, rows, lo, self.copy_stream)
+        with torch.cuda.stream(self.copy_stream):
+            if self.on_batch is not None:
+                self.on_batch(lo, n)
+            self.ready[slot].record(self.copy_stream)
+        return n
+
+    def _submit_hybrid(self, slot: int, rows: torch.Tensor) -> int:
+        """First `hybrid_fraction` of the rows by the GPU over PCIe (zero-copy reads of the mapped matrix), the rest by
+        the host thread pool + a copy-engine H2D; the two proceed concurrently."""
+        n = rows.numel()
+        lo = slot * self.B
+        nd = max(0, min(n, int(round(n * self.hybrid_fraction)) // 16 * 16))
+        if self._gather_stream is None:
+            self._gather_stream = torch.cuda.Stream(device=self.dev)
+        gs = self._gather_stream
+        self.freed[slot].synchronize()  # pinned buffers of this slot are reused
+        gs.wait_event(self.freed[slot])
+        if nd > 0:
+            self._enqueue_device_gather(slot, rows[:nd], lo, gs)  # asynchronous: runs during the host gather below
+        nh = n - nd
+        if nh > 0:
+            pin = self._pin[slot]
+            hrows = rows[nd:].contiguous()
+            call("scvi_host_gather_rows", C.c_void_p(self.host.data_ptr()), self.n_obs,
+                 self.n_vars * self.host.element_size(), self.host.stride(0) * self.host.element_size(),
+                 C.c_void_p(hrows.data_ptr()), nh, C.c_void_p(pin.data_ptr()), pin.stride(0) * pin.element_size(),
+                 self.host_threads)
+            torch.index_select(self.host_batch, 0, hrows, out=self._pin_b[slot][:nh])
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.freed[slot])
+            if nh > 0:
+                dst = self.stage.X[lo + nd : lo + n] if self._compact is None else self._compact[lo + nd : lo + n]
+                dst.copy_(self._pin[slot][:nh], non_blocking=True)
+                if self._compact is not None:
+                    ops.gather_rows(self._compact[lo + nd : lo + n], None, out=self.stage.X[lo + nd : lo + n])
+                self.stage.batch[lo + nd : lo + n].copy_(self._pin_b[slot][:nh], non_blocking=True)
+            self.copy_stream.wait_stream(gs)
             if self.on_batch is not None:
                 self.on_batch(lo, n)
             self.ready[slot].record(self.copy_stream)

@@ -291,3 +291,30 @@ def test_streamed_uint8_stage_trains_like_resident_counts(device_gather):
     for k in out[0][0]:
         assert torch.equal(out[0][0][k], out[1][0][k]), k
     assert out[0][1][-1]["train_loss"] == out[1][1][-1]["train_loss"]
+
+
+def test_streamed_hybrid_gather_trains_like_resident_counts():
+    """`HostStreamedCounts(hybrid_fraction=0.4)`: part of every minibatch pulled by the GPU from the mapped pinned
+    matrix, the rest gathered by the host thread pool and copied -- same rows, same order, identical weights."""
+    import scvi_tools_b200 as S
+    from scvi_tools_b200.data import DeviceResidentCounts, HostStreamedCounts
+    from scvi_tools_b200.train import FusedTrainingPlan
+
+    X, batch = O.synthetic_iid(700, 208, 3, seed=2)
+    out = []
+    for streamed in (False, True):
+        torch.manual_seed(0)
+        m = S.VAE(n_input=208, n_batch=3, n_hidden=128, precision=1).train()
+        if streamed:
+            host = HostStreamedCounts(X, batch=batch, batch_size=256, device="cuda:0", compact_stage=True,
+                                      hybrid_fraction=0.4)
+            if not host.device_gather:
+                pytest.skip("pinned host memory is not mapped into the device address space")
+            plan = FusedTrainingPlan(m, host.stage, batch_size=256, seed=3)
+            hist = plan.fit_streamed(host, max_epochs=2)
+        else:
+            plan = FusedTrainingPlan(m, DeviceResidentCounts(X, batch=batch, device="cuda:0"), batch_size=256, seed=3)
+            hist = plan.fit(max_epochs=2)
+        out.append(({k: v.detach().clone() for k, v in m.state_dict().items()}, hist))
+    for k in out[0][0]:
+        assert torch.equal(out[0][0][k], out[1][0][k]), k
