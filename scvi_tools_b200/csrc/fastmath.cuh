@@ -18,6 +18,8 @@
 #define SCVI_FM static inline
 #endif
 
+#include <string.h>
+
 namespace scvi {
 namespace fm {
 
@@ -47,6 +49,37 @@ SCVI_FM float ex2(float x) { return exp2f(x); }
 SCVI_FM float lg2(float x) { return log2f(x); }
 SCVI_FM float rcp(float x) { return 1.0f / x; }
 #endif
+
+// 2^x for x <= 0 on the FMA / ALU pipes only (no SFU op): round-to-nearest split x = i + f with the 1.5 * 2^23 trick,
+// degree-5 minimax polynomial of 2^f on [-0.5, 0.5] (relative error 2.2e-7 in fp32 Horner form: the accuracy of
+// ex2.approx), exponent patched in with an integer add.  The fused likelihood kernels are bound by the SFU pipe
+// inside their element math (9 MUFU per ZINB element = 72 of ~118 issue cycles per warp and element) while the FMA
+// pipe idles at 19 %.  MEASURED (r02): using this for the two exp(-|.|) of the zero-inflation terms (ZINB: 9 -> 7 MUFU
+// per element, +22 FMA / ALU instructions) made K2 119.8 us (118.6) and K3 104.3 us (99.6): the element math is bound
+// by issue slots and dependent latency as much as by the SFU pipe, so trading 1 MUFU for 11 other instructions loses.
+// Kept (with its accuracy test) for kernels whose SFU pipe is the sole bound; not used by the fused kernels.
+SCVI_FM float ex2_fma(float x) {
+  x = fmaxf(x, -125.f);
+  const float t = x + 12582912.f;
+  const float f = x - (t - 12582912.f);
+  float p = 0.0013266970386324052f;
+  p = fmaf(p, f, 0.009675459745517628f);
+  p = fmaf(p, f, 0.05550742616002558f);
+  p = fmaf(p, f, 0.24022121753561645f);
+  p = fmaf(p, f, 0.6931469491610631f);
+  p = fmaf(p, f, 1.0000000710296983f);
+#if defined(__CUDA_ARCH__)
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+#else
+  int pb, tb;
+  memcpy(&pb, &p, 4);
+  memcpy(&tb, &t, 4);
+  pb += (int)((unsigned)tb << 23);
+  float r;
+  memcpy(&r, &pb, 4);
+  return r;
+#endif
+}
 
 SCVI_FM float fexp(float x) { return ex2(x * LOG2E); }
 SCVI_FM float flog(float x) { return lg2(x) * LN2; }

@@ -23,6 +23,10 @@ static GeneK make_gene(float theta, float eps) {
 }
 
 extern "C" {
+void fm_ex2_fma(int n, const float* x, float* y) {
+  for (int i = 0; i < n; ++i) y[i] = scvi::fm::ex2_fma(x[i]);
+}
+
 // out[n][4] = ll, g1, dpi, mu
 void fm_elem_fwd(int zinb, int n, const float* x, const float* s, const float* pi, const float* krow,
                  const float* theta, float eps, float* out) {

@@ -137,3 +137,15 @@ def test_lgamma_digamma_series(lib):
     lib.fm_digamma(z.size, _p(z), _p(out))
     ref = digamma(z.astype(np.float64))
     assert np.max(np.abs(out - ref) / (1.0 + np.abs(ref))) < 2e-6
+
+
+def test_ex2_on_the_fma_pipe(lib):
+    """`ex2_fma` (2^x for x <= 0 without an SFU op): relative error below 3e-7 (ex2.approx's own accuracy) over the
+    whole range the likelihood uses, exact 1 at 0, flushes to (nearly) zero below -125."""
+    x = np.concatenate([-np.linspace(0.0, 130.0, 200001), -np.logspace(-8, 2, 20001)]).astype(np.float32)
+    y = np.empty_like(x)
+    lib.fm_ex2_fma(len(x), x.ctypes.data_as(C.POINTER(C.c_float)), y.ctypes.data_as(C.POINTER(C.c_float)))
+    ref = np.exp2(np.maximum(x.astype(np.float64), -125.0))
+    assert np.max(np.abs(y / ref - 1.0)) < 3e-7
+    assert y[0] == 1.0 or abs(y[0] - 1.0) < 1.2e-7
+    assert np.all(y > 0) and np.all(np.isfinite(y))
