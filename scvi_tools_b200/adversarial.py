@@ -24,7 +24,7 @@ import torch
 import torch.nn.functional as F
 
 from .graphed import WholeStepGraph
-from .optim import ArenaAdam
+from .optim import ArenaAdam, broadcast_module_state
 from .scanvi import Classifier
 from .train import compute_kl_weight
 
@@ -56,7 +56,7 @@ class AdversarialTrainingPlan:
                  lr_threshold: float = 0.0, lr_scheduler_metric: str = "elbo_validation", lr_min: float = 0.0,
                  adversarial_classifier: bool | Classifier = False, scale_adversarial_loss: float | str = "auto",
                  max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, n_batch: int | None = None,
-                 use_cuda_graph: bool = False, **loss_kwargs):
+                 use_cuda_graph: bool = False, process_group=None, **loss_kwargs):
         self.module = module
         self.n_steps_kl_warmup, self.n_epochs_kl_warmup = n_steps_kl_warmup, n_epochs_kl_warmup
         self.max_kl_weight, self.min_kl_weight = max_kl_weight, min_kl_weight
@@ -78,11 +78,16 @@ class AdversarialTrainingPlan:
             self.adversarial_classifier = adversarial_classifier
             if adversarial_classifier is not False:
                 self.n_output_classifier = n_batch
-        self.opt1 = ArenaAdam(module.named_parameters, lr=lr, eps=eps, weight_decay=weight_decay, capturable=use_cuda_graph)
+        self.process_group = process_group
+        broadcast_module_state(module, process_group)
+        if self.adversarial_classifier is not False:
+            broadcast_module_state(self.adversarial_classifier, process_group)
+        self.opt1 = ArenaAdam(module.named_parameters, lr=lr, eps=eps, weight_decay=weight_decay, capturable=use_cuda_graph,
+                              process_group=process_group)
         self.opt2 = None
         if self.adversarial_classifier is not False:
             self.opt2 = ArenaAdam(self.adversarial_classifier.named_parameters, lr=1e-3, eps=0.01,
-                                  weight_decay=weight_decay, capturable=use_cuda_graph)
+                                  weight_decay=weight_decay, capturable=use_cuda_graph, process_group=process_group)
         # whole step (both backward passes, both optimizers) as one CUDA graph per minibatch shape: graphed.py
         self._graph = WholeStepGraph(self._step) if use_cuda_graph else None
         self._klw = None
@@ -146,6 +151,20 @@ class AdversarialTrainingPlan:
         return lo
 
     @torch.no_grad()
+    def sync_buffers(self):
+        """Rank 0's BatchNorm buffers to every rank (torch DDP's `broadcast_buffers`; statistics are per-rank during
+        the step, as under the reference's DDP)."""
+        if self.process_group is None:
+            return
+        import torch.distributed as dist
+
+        src = dist.get_global_rank(self.process_group, 0)
+        mods = [self.module] + ([self.adversarial_classifier] if self.adversarial_classifier is not False else [])
+        for mod in mods:
+            for b in mod.buffers():
+                dist.broadcast(b, src=src, group=self.process_group)
+
+    @torch.no_grad()
     def validation_step(self, batch):
         self.module.eval()
         _, _, lo = self.module(batch, loss_kwargs=dict(self.loss_kwargs))
@@ -186,6 +205,7 @@ class AdversarialTrainingPlan:
                 self.scheduler.step(rec[self.lr_scheduler_metric])
                 if self._graph is not None and self.opt1.lr != lr_before:
                     self._graph.invalidate()  # the rate is a launch argument of the captured Adam
+            self.sync_buffers()
             history.append(rec)
         self.current_epoch = first + max_epochs
         return history

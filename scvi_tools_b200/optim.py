@@ -17,14 +17,35 @@ import torch
 from ._lib import call
 
 
+def broadcast_module_state(module, process_group):
+    """Rank 0's parameters and buffers to every rank, once, at plan construction (what torch DDP does when it wraps
+    a module: replicas must start equal for the gradient mean to keep them equal)."""
+    if process_group is None:
+        return
+    import torch.distributed as dist
+
+    src = dist.get_global_rank(process_group, 0)
+    with torch.no_grad():
+        for t in list(module.parameters()) + list(module.buffers()):
+            dist.broadcast(t.data, src=src, group=process_group)
+
+
 class ArenaAdam:
     def __init__(self, named_parameters, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 0.01,
-                 weight_decay: float = 1e-6, capturable: bool = False):
+                 weight_decay: float = 1e-6, capturable: bool = False, process_group=None):
         """`named_parameters`: a callable returning (name, parameter) pairs, e.g. `module.named_parameters`.
         `capturable`: keep the step count on the device (`scvi_adam_step_graph`), so that `step()` can be captured
         into a CUDA graph; a learning-rate change then needs a re-capture (the rate is a launch argument)."""
         self._named = named_parameters
         self.capturable = capturable
+        # data parallelism (torch DDP's contract, reference `Trainer(strategy="ddp")`): parameters start as rank 0's,
+        # every step applies the MEAN of the ranks' gradients -- one all-reduce of the flat gradient arena
+        self.pg = process_group
+        self.world = 1
+        if process_group is not None:
+            import torch.distributed as dist
+
+            self.world = dist.get_world_size(process_group)
         self.lr, self.betas, self.eps, self.wd = lr, betas, eps, weight_decay
         self.arena = None
         self.names: list[str] = []
@@ -81,15 +102,21 @@ class ArenaAdam:
                 view.copy_(p.grad.reshape(-1))
                 p.grad = view.view(p.shape)
         a["step"] += 1
+        scale = 1.0
+        if self.world > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(a["g"], group=self.pg)  # captured with the step when the plan runs as a CUDA graph
+            scale = 1.0 / self.world
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         if self.capturable:
             call("scvi_adam_step_graph", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
                  C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(),
-                 C.c_void_p(a["counter"].data_ptr()), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, 1.0, st)
+                 C.c_void_p(a["counter"].data_ptr()), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, scale, st)
             return
         call("scvi_adam_step", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
              C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(), a["step"], self.lr,
-             self.betas[0], self.betas[1], self.eps, self.wd, 1.0, st)
+             self.betas[0], self.betas[1], self.eps, self.wd, scale, st)
 
     @property
     def n_steps(self) -> int:

@@ -29,7 +29,7 @@ import torch
 
 from .data import DeviceResidentCounts
 from .graphed import WholeStepGraph
-from .optim import ArenaAdam
+from .optim import ArenaAdam, broadcast_module_state
 from .train import compute_kl_weight
 
 
@@ -204,7 +204,8 @@ class SemiSupervisedTrainingPlan:
     def __init__(self, module, n_classes: int, *, classification_ratio: float = 50, lr: float = 1e-3,
                  weight_decay: float = 1e-6, eps: float = 0.01, betas=(0.9, 0.999),
                  n_steps_kl_warmup: int | None = None, n_epochs_kl_warmup: int | None = 400,
-                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, use_cuda_graph: bool = False, **loss_kwargs):
+                 max_kl_weight: float = 1.0, min_kl_weight: float = 0.0, use_cuda_graph: bool = False,
+                 process_group=None, **loss_kwargs):
         self.module = module
         self.n_classes = n_classes
         # whole step (zero_grad, forward, backward, Adam) as one CUDA graph per minibatch shape: graphed.py
@@ -217,8 +218,9 @@ class SemiSupervisedTrainingPlan:
         self.loss_kwargs["classification_ratio"] = classification_ratio
         self.current_epoch = 0
         self.global_step = 0
+        broadcast_module_state(module, process_group)
         self.optimizer = ArenaAdam(module.named_parameters, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
-                                   capturable=use_cuda_graph)
+                                   capturable=use_cuda_graph, process_group=process_group)
 
     @property
     def kl_weight(self):

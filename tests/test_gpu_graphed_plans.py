@@ -25,8 +25,13 @@ def fixed_rng(monkeypatch):
         n = int(np.prod(shape))
         return torch.sin(torch.arange(n, device=device, dtype=torch.float32) * 0.37).view(shape)
 
+    import scvi_tools_b200.module as M_
+    import scvi_tools_b200.totalvi as T_
+
     monkeypatch.setattr(N, "_next_mask", mask)
     monkeypatch.setattr(N, "_next_noise", noise)
+    monkeypatch.setattr(M_, "_next_noise", noise)  # bound by name at import
+    monkeypatch.setattr(T_, "_next_noise", noise)
 
 
 def _close(a, b, what):

@@ -145,3 +145,140 @@ def test_two_rank_step_matches_single_process_arithmetic():
     res = dict(q.get() for _ in range(2))
     for r in range(2):
         assert res[r] == "ok", f"rank {r}:\n{res[r]}"
+
+
+def _adv_worker(rank, world, port, q):
+    """Data-parallel `AdversarialTrainingPlan` (one all-reduce of each optimizer's flat gradient arena per step):
+    replicas built from different seeds start from rank 0's weights; after one step the parameters equal Adam applied
+    to the mean of the two single-process gradients, bit for bit; replicas stay identical over further steps, with
+    and without the whole-step CUDA graph."""
+    try:
+        import ctypes as C
+
+        import numpy as np
+        import torch.distributed as dist
+
+        import scvi_tools_b200 as S
+        from scvi_tools_b200 import nn as N
+        from scvi_tools_b200._lib import call
+        from scvi_tools_b200.adversarial import AdversarialTrainingPlan
+        from scvi_tools_b200.totalvi import TOTALVAE
+
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        pg = dist.group.WORLD
+
+        def mask(shape, p, device):  # fixed, capture-safe stand-ins for the random draws
+            n = int(np.prod(shape))
+            return ((torch.arange(n, device=device) * 7919) % 10 != 0).to(torch.uint8).view(shape)
+
+        def noise(shape, device):
+            n = int(np.prod(shape))
+            return torch.sin(torch.arange(n, device=device, dtype=torch.float32) * 0.37).view(shape)
+
+        import scvi_tools_b200.module as M_
+        import scvi_tools_b200.totalvi as T_
+
+        N._next_mask, N._next_noise = mask, noise
+        M_._next_noise = T_._next_noise = noise  # the modules bound the draw function by name at import
+        rng = np.random.default_rng(1)
+        n, G, P, nb, B = 1024, 80, 10, 3, 64
+        X = torch.from_numpy(rng.poisson(3.0, size=(n, G)).astype(np.float32)).to(dev)
+        Y = torch.from_numpy(rng.poisson(30.0, size=(n, P)).astype(np.float32)).to(dev)
+        bat = torch.from_numpy(rng.integers(0, nb, size=(n, 1))).to(dev)
+        lab = torch.zeros(n, 1, dtype=torch.long, device=dev)
+
+        def mb(r, t):
+            s = slice((2 * t + r) * B, (2 * t + r + 1) * B)
+            return {"X": X[s], "proteins": Y[s], "batch": bat[s], "labels": lab[s]}
+
+        def build(seed, group, graph=False):
+            torch.manual_seed(seed)
+            m = TOTALVAE(n_input_genes=G, n_input_proteins=P, n_batch=nb, n_panel=nb, n_hidden=64).to(dev)
+            plan = AdversarialTrainingPlan(m, lr=4e-3, adversarial_classifier=True, n_epochs_kl_warmup=16,
+                                           use_cuda_graph=graph, process_group=group)
+            plan.current_epoch = 3
+            return plan
+
+        ddp = build(11 * rank + 5, pg)  # different initial weights per rank before the broadcast
+        sd0 = {k: v.detach().clone() for k, v in ddp.module.state_dict().items()}
+        cd0 = {k: v.detach().clone() for k, v in ddp.adversarial_classifier.state_dict().items()}
+        both = [torch.empty_like(sd0["px_r"]) for _ in range(world)]
+        dist.all_gather(both, sd0["px_r"].contiguous())
+        assert torch.equal(both[0], both[1]), "replicas differ after construction"
+        ddp.training_step(mb(rank, 0))
+        torch.cuda.synchronize()
+        # expectation: single-process plans from the same state on each rank's minibatch -> mean gradient -> Adam
+        exp = []
+        for r in range(world):
+            sp = build(0, None)
+            sp.module.load_state_dict(sd0)
+            sp.adversarial_classifier.load_state_dict(cd0)
+            sp.training_step(mb(r, 0))
+            torch.cuda.synchronize()
+            exp.append(sp)
+        assert exp[0].opt1.names == ddp.opt1.names
+        for which in ("opt1", "opt2"):
+            g = sum(getattr(e, which).arena["g"] for e in exp)
+            ref = build(0, None)
+            ref.module.load_state_dict(sd0)
+            ref.adversarial_classifier.load_state_dict(cd0)
+            ref.training_step(mb(0, 0))  # lays the arenas out (values overwritten below)
+            a = getattr(ref, which).arena
+            named = dict((ref.module if which == "opt1" else ref.adversarial_classifier).named_parameters())
+            src = sd0 if which == "opt1" else cd0
+            for k, off in zip(getattr(ref, which).names, a["offs"], strict=True):
+                a["p"][off : off + named[k].numel()].copy_(src[k].reshape(-1))
+            a["m"].zero_()
+            a["v"].zero_()
+            o = getattr(ref, which)
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            call("scvi_adam_step", C.c_void_p(a["p"].data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(a["m"].data_ptr()),
+                 C.c_void_p(a["v"].data_ptr()), a["p"].numel(), 1, o.lr, o.betas[0], o.betas[1], o.eps, o.wd, 1.0 / world, st)
+            torch.cuda.synchronize()
+            got = getattr(ddp, which).arena["p"]
+            assert torch.equal(got, a["p"]), (which, float((got - a["p"]).abs().max()))
+        # replicas stay identical, eager and as a whole-step graph (NCCL all-reduce captured with the step)
+        for graph in (False, True):
+            plan = build(3, pg, graph)
+            for t in range(6):
+                plan.current_epoch = t
+                plan.training_step(mb(rank, t))
+            torch.cuda.synchronize()
+            if graph:
+                assert plan._graph.n_replays == 3
+            p = plan.opt1.arena["p"]
+            both = [torch.empty_like(p) for _ in range(world)]
+            dist.all_gather(both, p)
+            assert torch.equal(both[0], both[1]) and torch.isfinite(p).all(), f"replicas diverged (graph={graph})"
+        dist.barrier()
+        q.put((rank, "ok"))
+    except Exception:  # noqa: BLE001
+        q.put((rank, traceback.format_exc()))
+    finally:
+        os._exit(0)
+
+
+@pytest.mark.timeout(900)
+def test_two_rank_adversarial_plan_matches_single_process_arithmetic():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = 29800 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_adv_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=800)
+        if p.is_alive():
+            p.kill()
+            pytest.fail("data-parallel worker hung")
+    res = dict(q.get() for _ in range(2))
+    for r in range(2):
+        assert res[r] == "ok", f"rank {r}:\n{res[r]}"

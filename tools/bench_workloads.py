@@ -26,21 +26,38 @@ def counts(n, g, dev, seed=0, chunk=65536):
     return X
 
 
+WORLD = int(os.environ.get("WORLD_SIZE", "1"))
+RANK = int(os.environ.get("RANK", "0"))
+PG = None
+
+
+def barrier():
+    if WORLD > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+
+
 def timed(step, K, R, W):
     for i in range(W):
         step(i)
-    torch.cuda.synchronize()
+    barrier()
     out = []
     n = W
     for _ in range(R):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
         e0.record()
         for _i in range(K):
             step(n)
             n += 1
         e1.record()
-        torch.cuda.synchronize()
-        out.append(e0.elapsed_time(e1))
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if WORLD > 1:  # max over ranks
+            t = torch.tensor([ms], device="cuda")
+            torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+            ms = float(t)
+        out.append(ms)
     return float(np.median(out)), out
 
 
@@ -56,12 +73,12 @@ def scanvi(a, dev):
     data = DeviceResidentCounts(X, batch=torch.arange(a.cells) * 4 // a.cells, labels=labels, device=dev)
     torch.manual_seed(0)
     m = SCANVAE(n_input=a.genes, n_batch=4, n_labels=a.labels, gene_likelihood="zinb").to(dev)
-    plan = SemiSupervisedTrainingPlan(m, n_classes=a.labels, use_cuda_graph=not a.eager)
+    plan = SemiSupervisedTrainingPlan(m, n_classes=a.labels, use_cuda_graph=not a.eager, process_group=PG)
     B = a.batch_size
     lab_idx = torch.nonzero(labels != a.labels).view(-1).to(dev)
 
     def step(i):
-        gi = torch.Generator(device=dev).manual_seed(i)
+        gi = torch.Generator(device=dev).manual_seed(1000 * RANK + i)
         f = torch.randint(0, a.cells, (B,), device=dev, generator=gi)
         l = lab_idx[torch.randint(0, lab_idx.numel(), (B,), device=dev, generator=gi)]
         plan.training_step((data.minibatch(f), data.minibatch(l)))
@@ -69,7 +86,7 @@ def scanvi(a, dev):
     ms, blocks = timed(step, a.steps, 3, 5)
     return {"workload": f"SCANVI zinb semi-supervised step, synthetic {a.cells} cells x {a.genes} genes, {a.labels} labels, "
                         f"full + labelled minibatch of {B} cells each, classification_ratio 50",
-            "metric": "SCANVI train cells/sec (full-minibatch cells)", "value": a.steps * B / (ms / 1e3), "unit": "cells/s",
+            "metric": "SCANVI train cells/sec (full-minibatch cells)", "value": WORLD * a.steps * B / (ms / 1e3), "unit": "cells/s",
             "ms_per_step": ms / a.steps, "steps": a.steps, "blocks_ms": blocks, "path": "autograd over the library's kernels "
             "(SCANVAE.forward) + multi-tensor Adam; the [B,G] side is the fused decoder + likelihood kernel"}
 
@@ -84,18 +101,19 @@ def totalvi(a, dev):
     batch = (torch.arange(a.cells, device=dev) * nb // a.cells).view(-1, 1)
     torch.manual_seed(0)
     m = TOTALVAE(n_input_genes=a.genes, n_input_proteins=a.proteins, n_batch=nb).to(dev)
-    plan = AdversarialTrainingPlan(m, lr=4e-3, adversarial_classifier=True, n_batch=nb, use_cuda_graph=not a.eager)
+    plan = AdversarialTrainingPlan(m, lr=4e-3, adversarial_classifier=True, n_batch=nb, use_cuda_graph=not a.eager,
+                                   process_group=PG)
     B = a.batch_size
 
     def step(i):
-        gi = torch.Generator(device=dev).manual_seed(i)
+        gi = torch.Generator(device=dev).manual_seed(1000 * RANK + i)
         f = torch.randint(0, a.cells, (B,), device=dev, generator=gi)
         t = {"X": X[f], "proteins": Y[f], "batch": batch[f], "labels": torch.zeros(B, 1, dtype=torch.long, device=dev)}
         plan.training_step(t)
 
     ms, blocks = timed(step, a.steps, 3, 5)
     return {"workload": f"TOTALVI step (adversarial plan), synthetic {a.cells} cells x {a.genes} genes + {a.proteins} proteins, "
-                        f"batch_size {B}", "metric": "TOTALVI train cells/sec", "value": a.steps * B / (ms / 1e3),
+                        f"batch_size {B}", "metric": "TOTALVI train cells/sec", "value": WORLD * a.steps * B / (ms / 1e3),
             "unit": "cells/s", "ms_per_step": ms / a.steps, "steps": a.steps, "blocks_ms": blocks}
 
 
@@ -110,12 +128,22 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--eager", action="store_true", help="no whole-step CUDA graph")
     a = ap.parse_args()
-    dev = torch.device("cuda:0")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if WORLD > 1:
+        torch.distributed.init_process_group("nccl", device_id=dev)
+        PG = torch.distributed.group.WORLD
     if a.which == "scanvi":
         a.cells, a.genes, a.batch_size = a.cells or 500_000, a.genes or 2000, a.batch_size or 1024
         line = scanvi(a, dev)
     else:
         a.cells, a.genes, a.batch_size = a.cells or 200_000, a.genes or 4000, a.batch_size or 256
         line = totalvi(a, dev)
-    line.update({"n_gpus": 1, "data": "synthetic", "dtype": "f32", "whole_step_cuda_graph": not a.eager})
-    print(json.dumps(line))
+    line.update({"n_gpus": WORLD, "data": "synthetic", "dtype": "f32", "whole_step_cuda_graph": not a.eager,
+                 "scaling": "weak", "parallelism": f"dp{WORLD}: one all-reduce of the flat gradient arena per optimizer"})
+    if RANK == 0:
+        print(json.dumps(line))
+    if WORLD > 1:
+        torch.distributed.barrier()
+        os._exit(0)
