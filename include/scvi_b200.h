@@ -60,14 +60,10 @@ extern "C" {
 #define SCVI_X_U8 0x400
 /* SCVI_PREC_AOPS (with SCVI_PREC_TC and an integer count kind, OR-ed into `precision` of scvi_decoder_nll_fwd_ws_bytes,
  * scvi_decoder_nll_fwd with dh, and the matching scvi_decoder_nll_bwd with fwd_ws): the fused likelihood kernel keeps
- * its per-element derivative operands (fp16 hi/lo, in the forward workspace) and the weight-gradient kernel becomes a
- * pure tensor-core GEMM over them instead of recomputing every element. */
+ * its staged MMA operands (fp16 hi/lo, in the forward workspace) and the weight-gradient kernel becomes a tensor-core
+ * GEMM over them instead of recomputing the logits and every element (measured slower than the recompute kernel on
+ * B200: opt-in, see experiments/README.md). */
 #define SCVI_PREC_AOPS 0x800
-/* The count-only part of the dispersion gradient under SCVI_PREC_AOPS: sum_b u_b [psi(x_bg + theta_g) - psi(theta_g)]
- * into the forward workspace (u = g_reconst, 1 if NULL).  Needs only the counts, px_r and the loss weights: run it on a
- * side stream beside the forward; scvi_decoder_nll_bwd(SCVI_PREC_AOPS) reads the result from fwd_ws. */
-int scvi_decoder_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
-                           const float* g_reconst, int likelihood, int precision, void* fwd_ws, void* stream);
 #define SCVI_LIN_X_U8 SCVI_X_U8 /* scvi_linear_fwd / _bwd with SCVI_LIN_TC: `x` points to uint8 counts, ldx in bytes,
                                    rows 16-byte aligned; the converters look log1p(count) up in a 256-entry table
                                    built from the fp32 path's own arithmetic (results bit-identical to fp32 counts) */

@@ -31,7 +31,6 @@ SIGNATURES = {
     "scvi_gather_rows_u8": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
     "scvi_host_gather_rows": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, C.c_int]),
     "scvi_gather_rows_u8_raw": (C.c_int, [P, I64, I64, I64, P, I64, P, I64, P]),
-    "scvi_decoder_dpsi_sums": (C.c_int, [P, I64, P, I64, I64, P, P, C.c_int, C.c_int, P, P]),
     "scvi_gather_rows_csr": (C.c_int, [P, P, C.c_int, P, C.c_int, I64, I64, P, I64, P, I64, P, P]),
     "scvi_nb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),
     "scvi_zinb_logprob_fwd": (C.c_int, [P, I64, P, I64, P, I64, P, I64, I64, I64, F32, P, I64, P, P]),

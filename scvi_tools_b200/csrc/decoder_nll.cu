@@ -648,9 +648,6 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
                           const int64_t* row_idx, const float* row_stats, const float* g_reconst, int likelihood,
                           float* dWs, float* dbs, float* dWp, float* dbp, float* dpx_r, void* ws, const void* fwd_ws,
                           int xkind, const float* library, cudaStream_t st);
-void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops);
-int tc_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
-                 const float* g_reconst, int xkind, float* slab, cudaStream_t st);
 // count-operand kind carried in the `precision` argument (scvi_b200.h: SCVI_X_INTEGER / SCVI_X_U8)
 // bit 4 of the result: SCVI_PREC_AOPS (staged operands kept by the forward / consumed by the backward)
 static inline int take_xkind(int& precision) {
@@ -667,21 +664,6 @@ int64_t scvi_decoder_nll_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likel
   const int xk = scvi::take_xkind(precision);
   if (precision == SCVI_PREC_TC) return scvi::tc_decoder_fwd_ws_bytes(B, H, G, likelihood, (xk & 16) != 0);
   return 0;
-}
-
-int scvi_decoder_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
-                           const float* g_reconst, int likelihood, int precision, void* fwd_ws, void* stream) {
-  using namespace scvi;
-  const int xk = take_xkind(precision);
-  SCVI_REQUIRE(x && px_r && fwd_ws && B > 0 && G > 0 && ldx >= G, "scvi_decoder_dpsi_sums: bad argument");
-  if (!(xk & 16) || precision != SCVI_PREC_TC) {
-    set_error("scvi_decoder_dpsi_sums: needs SCVI_PREC_TC | SCVI_PREC_AOPS and an integer count kind");
-    return SCVI_EUNSUPPORTED;
-  }
-  size_t off_fmax, off_psi, off_aops;
-  tc_decoder_fwd_ws_aops(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1, &off_fmax, &off_psi, &off_aops);
-  return tc_dpsi_sums(x, ldx, row_idx, B, G, px_r, g_reconst, xk & 15, (float*)((uint8_t*)fwd_ws + off_psi),
-                      (cudaStream_t)stream);
 }
 
 int scvi_decoder_nll_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, int64_t G, const float* Ws,

@@ -417,10 +417,9 @@ struct TcPlan {
   int64_t nT, rowtiles;
   int nsplit, tiles_per_split;    // LSE / NLL-only kernels: 128-gene tiles
   int nsplit2, tiles_per_split2;  // fused NLL + dh kernel: 32-gene tiles
-  size_t off_packed, off_gconst, off_lse, off_out, off_packed32, off_dh, off_fmax, off_psi, off_aops, total;
+  size_t off_packed, off_gconst, off_lse, off_out, off_packed32, off_dh, off_fmax, off_aops, total;
 };
 size_t tc_aops_bytes(int64_t B, int64_t G, bool zinb);  // decoder_tc_train.cu
-size_t tc_dpsi_bytes(int64_t B, int64_t G);                // decoder_tc_dw2.cu
 
 static TcPlan tc_plan(int64_t B, int64_t G, int nheads, bool aops = false) {
   TcPlan p;
@@ -445,8 +444,7 @@ static TcPlan tc_plan(int64_t B, int64_t G, int nheads, bool aops = false) {
   // SCVI_PREC_AOPS: per-block maxima of the GEMM's row factors + the kept operands, behind everything else (the
   // offsets above do not depend on the flag)
   p.off_fmax = al(p.off_dh + (size_t)p.nsplit2 * 2 * B * TC_H * sizeof(float));
-  p.off_psi = al(p.off_fmax + (size_t)cdiv(B, 8) * 3 * sizeof(float));
-  p.off_aops = al(p.off_psi + tc_dpsi_bytes(B, G));
+  p.off_aops = al(p.off_fmax + (size_t)cdiv(B, 8) * 3 * sizeof(float));
   p.total = aops ? al(p.off_aops + tc_aops_bytes(B, G, nheads == 2)) : p.off_fmax;
   return p;
 }
@@ -464,10 +462,9 @@ int64_t tc_decoder_fwd_ws_bytes(int64_t B, int64_t H, int64_t G, int likelihood,
   return (int64_t)tc_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1, aops).total;
 }
 // where the forward workspace keeps the operands / factor maxima of SCVI_PREC_AOPS (read by the backward)
-void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops) {
+void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_aops) {
   const TcPlan p = tc_plan(B, G, nheads, true);
   *off_fmax = p.off_fmax;
-  *off_psi = p.off_psi;
   *off_aops = p.off_aops;
 }
 

@@ -6,15 +6,16 @@
 // and the gradients become
 //     dWs = (g1 s1)^T (u/s1 . h)  +  (p 2^P)^T (-u S 2^-P . h)          dbs = the same products with a ones column
 //     dWp = (-dpi 2^D)^T (u 2^-D . h)                                    dbp likewise
-//     dpx_r = -theta ( (dth')^T u  +  sum_b u_b [psi(x_bg + theta_g) - psi(theta_g)] )
+//     dpx_r = -theta sum_b u_b d(ll)/d(theta)_bg
 // (u = loss weight of the row, S = the row's sum of g1, s1 / 2^P / 2^D = K2's operand scales; the row factors live in
-// the B operand because rows are the reduction index here; dth' = d(ll)/d(theta) without its digamma term, which
-// depends on the count and theta only and is summed by tc_dpsi_colsum_kernel beside K2).
+// the B operand because rows are the reduction index here).  d(ll)/d(theta) is re-derived per element from the kept
+// g1 and p (-> mu), the count and theta by eight otherwise idle warps of the GEMM kernel while the stage they read is
+// being multiplied: 3 SFU ops per element, hidden under the kernel's HBM time.
 // Replaces, as tc_dw_kernel does, the autograd backward of the decoder heads + likelihood w.r.t. the head weights
 // (reference src/scvi/nn/_base_components.py:386-441, src/scvi/distributions/_negative_binomial.py:36-135).
 //
-// Roofline: the GEMM streams the kept operands once -- 8 parts x B x G x 2 B (ZINB; 264 MB at B = 8192, G = 2000)
-// -- so it is HBM-bound (~45 us at 6 TB/s); the tensor work (28 GFLOP in 3-MMA split form) hides under it.
+// Roofline: the GEMM streams the kept operands once -- 6 parts x B x G x 2 B (ZINB; 198 MB at B = 8192, G = 2000)
+// -- so it is HBM-bound (~35 us at 6 TB/s); the tensor work (28 GFLOP in 3-MMA split form) hides under it.
 #include "fastmath.cuh"
 #include "tc_layout.cuh"
 
@@ -27,18 +28,18 @@ __host__ __device__ inline size_t dw2_part_bytes(int64_t B, int64_t G) {
 }
 
 // ---- B operands: per 16-row piece {B1, B2, B3} x {hi, lo} x [18 chunks of 8 columns][16 rows][16 B] (columns 0..127 =
-// h, column 128 = 1, the rest 0; each scaled by the piece rows' factors) + Bf {hi, lo} x [2 chunks][16 rows][16 B]
-// (column 0 = u 2^k4) ------------------------------------------------------------------------------------------------
+// h, column 128 = 1, the rest 0; each scaled by the piece rows' factors) + a row table [16 rows][8 floats]:
+// {1/s1, 2^-P exp(library), u, valid, row id (int64 bits), -, -} for the d(ll)/d(theta) warps ----------------------
 constexpr uint32_t DW2_BV = 18 * 256;                 // one variant part
-constexpr uint32_t DW2_BF = 2 * 256;
-constexpr uint32_t DW2_BSTAGE = 6 * DW2_BV + 2 * DW2_BF;  // 28,672 B
+constexpr uint32_t DW2_RT = 16 * 32;                  // row table
+constexpr uint32_t DW2_BSTAGE = 6 * DW2_BV + DW2_RT;  // 28,160 B
 
-// scal[0..2] = 2^k12, 2^k3, 2^k4 (so that the largest row factor of each operand maps into (0.5, 1])
+// scal[0..1] = 2^k12, 2^k3 (so that the largest row factor of each operand maps into (0.5, 1])
 __global__ void __launch_bounds__(512)
     tc_pack_b16_kernel(const float* __restrict__ h, int64_t ldh, int64_t B, const float* __restrict__ row_stats,
                        const float* __restrict__ library, const float* __restrict__ g_reconst,
-                       const float* __restrict__ fmax_part, int n_fmax, uint8_t* __restrict__ bpack,
-                       float* __restrict__ scal) {
+                       const int64_t* __restrict__ row_idx, const float* __restrict__ fmax_part, int n_fmax,
+                       uint8_t* __restrict__ bpack, float* __restrict__ scal) {
   __shared__ float s_m[3];
   __shared__ float s_f[TC_M][4];
   const int tid = threadIdx.x;
@@ -53,43 +54,37 @@ __global__ void __launch_bounds__(512)
   auto k_of = [](float m) { return -max(-100, min(100, (int)ceilf(log2f(fmaxf(m, 1e-30f))))); };
   const int k12 = k_of(fmaxf(s_m[0], s_m[1]));
   const int k3 = k_of(s_m[2] * tc::pow2i(-TC_DP_SCALE_LOG2));
-  const int k4 = k_of(s_m[2]);
   if (blockIdx.x == 0 && tid == 0) {
     scal[0] = tc::pow2i(k12);
     scal[1] = tc::pow2i(k3);
-    scal[2] = tc::pow2i(k4);
   }
   const int64_t r0 = (int64_t)blockIdx.x * TC_M;
   if (tid < TC_M) {
     const int64_t b = r0 + tid;
-    float f1 = 0.f, f2 = 0.f, f3 = 0.f, f4 = 0.f;
+    float f1 = 0.f, f2 = 0.f, f3 = 0.f;
+    float4 t0 = make_float4(0.f, 0.f, 0.f, 0.f), t1 = t0;
     if (b < B) {
       const float u = g_reconst ? g_reconst[b] : 1.f;
       const float S = row_stats[b * 4 + 3];
-      const int e = max(-100, min(100, (int)ceilf(library[b] * fm::LOG2E)));  // K2's operand scale s1 = 2^(14 - e)
+      const float lib = library[b];
+      const int e = max(-100, min(100, (int)ceilf(lib * fm::LOG2E)));  // K2's operand scale s1 = 2^(14 - e)
       f1 = u * tc::pow2i(e - 14) * tc::pow2i(k12);
       f2 = -u * S * tc::pow2i(-TC_P_SCALE_LOG2) * tc::pow2i(k12);
       f3 = u * tc::pow2i(-TC_DP_SCALE_LOG2) * tc::pow2i(k3);
-      f4 = u * tc::pow2i(k4);
+      const int64_t rid = row_idx ? row_idx[b] : b;
+      t0 = make_float4(tc::pow2i(e - 14), expf(lib) * tc::pow2i(-TC_P_SCALE_LOG2), u, 1.f);
+      t1 = make_float4(__uint_as_float((uint32_t)(rid & 0xffffffffu)), __uint_as_float((uint32_t)((uint64_t)rid >> 32)), 0.f, 0.f);
     }
-    s_f[tid][0] = f1; s_f[tid][1] = f2; s_f[tid][2] = f3; s_f[tid][3] = f4;
+    s_f[tid][0] = f1; s_f[tid][1] = f2; s_f[tid][2] = f3; s_f[tid][3] = 0.f;
+    float* rt = reinterpret_cast<float*>(bpack + ((int64_t)blockIdx.x * 8 + (tid >> 4)) * DW2_BSTAGE + 6 * DW2_BV) + (tid & 15) * 8;
+    *reinterpret_cast<float4*>(rt) = t0;
+    *reinterpret_cast<float4*>(rt + 4) = t1;
   }
   __syncthreads();
-  for (int it = tid; it < TC_M * 19; it += 512) {
-    const int r = it % TC_M, c = it / TC_M;  // c < 18: chunk of the B variants; c == 18: the Bf chunks
+  for (int it = tid; it < TC_M * 18; it += 512) {
+    const int r = it % TC_M, c = it / TC_M;  // chunk of the B variants
     const int64_t b = r0 + r;
     uint8_t* piece = bpack + ((int64_t)blockIdx.x * 8 + (r >> 4)) * DW2_BSTAGE + (r & 15) * 16;
-    if (c == 18) {
-      float v[8] = {s_f[r][3], 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      uint4 hi, lo;
-      tc::split8(v, hi, lo);
-      uint8_t* o = piece + 6 * DW2_BV;
-      *reinterpret_cast<uint4*>(o) = hi;
-      *reinterpret_cast<uint4*>(o + 256) = make_uint4(0u, 0u, 0u, 0u);
-      *reinterpret_cast<uint4*>(o + DW2_BF) = lo;
-      *reinterpret_cast<uint4*>(o + DW2_BF + 256) = make_uint4(0u, 0u, 0u, 0u);
-      continue;
-    }
     float hs[8];
     if (c < 16 && b < B) {
       const float4 a = *reinterpret_cast<const float4*>(h + b * ldh + 8 * c);
@@ -116,25 +111,31 @@ __global__ void __launch_bounds__(512)
 }
 
 // ---- the GEMM --------------------------------------------------------------------------------------------------
-constexpr int DW2_NS = 3;       // stages
-constexpr int DW2_THREADS = 256;
+constexpr int DW2_NS = 3;        // stages
+constexpr int DW2_DTW = 16;      // d(ll)/d(theta) warps: warps 4..19 (thread = gene, four quarters of the stage's 16 rows)
+constexpr int DW2_RPW = 16 / (DW2_DTW / 4);  // rows of a stage per warp group
+constexpr int DW2_THREADS = 32 * (4 + DW2_DTW);
+constexpr int DW2_T = 32;        // digamma-difference table length per gene
 template <bool ZINB>
 struct Dw2Smem {
-  static constexpr int NP = ZINB ? 8 : 6;
+  static constexpr int NP = ZINB ? 6 : 4;
   static constexpr uint32_t A_BYTES = NP * 4096;
   static constexpr uint32_t STAGE = A_BYTES + DW2_BSTAGE;
   static constexpr uint32_t BARS = DW2_NS * STAGE;
   static constexpr uint32_t TMEM_PTR = BARS + 16 * 8;
-  static constexpr uint32_t TOTAL = TMEM_PTR + 16;
+  static constexpr uint32_t DGT = TMEM_PTR + 16;                  // [DW2_T][128 genes] psi(k + theta) - psi(theta)
+  static constexpr uint32_t RED = DGT + DW2_T * TC_M * 4;          // [3][128] partial sums of the other row quarters
+  static constexpr uint32_t TOTAL = RED + 3 * TC_M * 4;
 };
 static_assert(Dw2Smem<true>::TOTAL + 128 <= 232448, "dW GEMM shared memory");
 
-// CTA = (128-gene block gb, split of the 16-row pieces).  TMEM: D12 [128 genes x 144] at 0, D3 at 144, D4 [x 16] at 288.
-template <bool ZINB>
+// CTA = (128-gene block gb, split of the 16-row pieces).  TMEM: D12 [128 genes x 144] at 0, D3 at 144.
+template <bool ZINB, int XK>
 __global__ void __launch_bounds__(DW2_THREADS, 1)
     tc_dw_gemm_kernel(int64_t B, int64_t G, const uint8_t* __restrict__ aops, const uint8_t* __restrict__ bpack,
-                      const float* __restrict__ scal, int pieces_per_split, float* __restrict__ slabW /*[splits][NH][G][H]*/,
-                      float* __restrict__ slabv /*[splits][3][G]*/) {
+                      const float* __restrict__ scal, const void* __restrict__ xv, int64_t ldx,
+                      const float* __restrict__ px_r, float eps, int pieces_per_split,
+                      float* __restrict__ slabW /*[splits][NH][G][H]*/, float* __restrict__ slabv /*[splits][3][G]*/) {
   using L = Dw2Smem<ZINB>;
   constexpr int NH = ZINB ? 2 : 1;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -142,6 +143,8 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *full = bars, *empty = bars + DW2_NS, *accfull = bars + 2 * DW2_NS;
   uint32_t* s_tmem = reinterpret_cast<uint32_t*>(smem + L::TMEM_PTR);
+  float* s_dgt = reinterpret_cast<float*>(smem + L::DGT);
+  float* s_red = reinterpret_cast<float*>(smem + L::RED);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t gb = blockIdx.x;
   const int64_t nP = ((B + TC_M - 1) / TC_M) * 8;  // 16-row pieces
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < DW2_NS; ++i) {
       tc::mbar_init(&full[i], 1);
-      tc::mbar_init(&empty[i], 1);
+      tc::mbar_init(&empty[i], 1 + DW2_DTW);  // the MMA commit + the d(ll)/d(theta) warps that read the stage
     }
     tc::mbar_init(accfull, 1);
     tc::fence_mbar_init();
@@ -160,8 +163,9 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
   __syncthreads();
   tc::fence_after_sync();
   const uint32_t tmem_base = *s_tmem;
+  float dth_sum = 0.f;  // (d(ll)/d(theta) warps) sum_b u_b d(ll)/d(theta) of this thread's gene over its rows
   if (warp == 0) {
-    // ===== producer: the piece's operand blocks (one 4 KB bulk copy per part) + its 28 KB B block
+    // ===== producer: the piece's operand blocks (one 4 KB bulk copy per part) + its B block
     if (lane == 0) {
       const size_t ps = dw2_part_bytes(B, G);
       const int64_t nT4 = dw2_nT4(G);
@@ -179,7 +183,6 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
   } else if (warp == 1) {
     if (n > 0) {  // warp-uniform issue loop, one elected lane issues (tc.cuh)
       constexpr uint32_t idW = tc::idesc_f16_f32(TC_M, 144, 1, 1);
-      constexpr uint32_t idF = tc::idesc_f16_f32(TC_M, 16, 1, 1);
       const uint32_t leader = tc::elect_one();
       const uint32_t s0 = tc::smem_u32(smem);
       // MN-major blocks [chunk of 8][16 rows][16 B]: LBO (next 8 reduction rows) = 128, SBO (next chunk) = 256
@@ -195,9 +198,7 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
           const uint32_t base = s0 + s * L::STAGE;
           tc::mma3<1>(tmem_base, opA(base, 0), opB(base, 0), idW, i > 0);
           tc::mma3<1>(tmem_base, opA(base, 2), opB(base, 1), idW, true);
-          if (ZINB) tc::mma3<1>(tmem_base + 144, opA(base, 6), opB(base, 2), idW, i > 0);
-          const tc::Oper bf = tc::make_oper(base + L::A_BYTES + 6 * DW2_BV, base + L::A_BYTES + 6 * DW2_BV + DW2_BF, 128, 256, 0);
-          tc::mma3<1>(tmem_base + 288, opA(base, 4), bf, idF, i > 0);
+          if (ZINB) tc::mma3<1>(tmem_base + 144, opA(base, 4), opB(base, 2), idW, i > 0);
           tc::mma_commit(&empty[s]);
         }
         __syncwarp();
@@ -206,49 +207,138 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
       __syncwarp();
     }
   } else if (warp >= 4) {
-    // ===== epilogue: thread = gene 32 * (warp % 4) + lane of the block
-    const int gl = 32 * (warp & 3) + lane;
+    // ===== d(ll)/d(theta): thread = gene gl of the block, warp group q = (warp - 4) / 4 takes rows 4q..4q+3 of a stage
+    const int gl = 32 * (warp & 3) + lane, half = (warp - 4) >> 2;
     const int64_t g = gb * TC_M + gl;
     const bool gvalid = g < G;
-    if (n > 0) {
-      tc::mbar_wait(accfull, 0);
-      tc::fence_after_sync();
-    }
-    const uint32_t lane_sel = (uint32_t)(32 * (warp & 3)) << 16;
-    const float kW = 1.f / (scal[0] * TC_SCALE_H), kP = 1.f / (scal[1] * TC_SCALE_H), kT = 1.f / scal[2];
-#pragma unroll 1
-    for (int hd = 0; hd < NH; ++hd) {
-      float* o = slabW + (((int64_t)blockIdx.y * NH + hd) * G + g) * TC_H;
-      const float kk = hd == 0 ? kW : kP;
-#pragma unroll 1
-      for (int c = 0; c < 17; ++c) {  // 16 chunks of weights + the ones-column chunk
-        float v[8];
-        if (n > 0) {
-          tc::tmem_ld8(tmem_base + lane_sel + hd * 144 + 8 * c, v);
-          tc::tmem_ld_wait();
-        } else {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = 0.f;
-        }
-        if (!gvalid) continue;
-        if (c < 16) {
-          *reinterpret_cast<float4*>(o + 8 * c) = make_float4(v[0] * kk, v[1] * kk, v[2] * kk, v[3] * kk);
-          *reinterpret_cast<float4*>(o + 8 * c + 4) = make_float4(v[4] * kk, v[5] * kk, v[6] * kk, v[7] * kk);
-        } else {
-          slabv[((int64_t)blockIdx.y * 3 + hd) * G + g] = v[0] * kk;  // dbs / dbp
-        }
+    const int64_t gx = min(g, G - 1);  // a valid column to read for the threads past G
+    const float theta = expf(px_r[gx]);
+    const float rth = 1.f / (theta + eps);
+    if (half == 0) {  // psi(k + theta) - psi(theta) = sum_{i < k} 1 / (theta + i)
+      float d = 0.f;
+      for (int k = 0; k < DW2_T; ++k) {
+        s_dgt[k * TC_M + gl] = d;
+        d += __frcp_rn(theta + (float)k);
       }
     }
-    float v[8];
-    if (n > 0) {
-      tc::tmem_ld8(tmem_base + lane_sel + 288, v);
-      tc::tmem_ld_wait();
-    } else {
-      v[0] = 0.f;
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * DW2_DTW) : "memory");
+    const uint32_t eoff = (uint32_t)(gl >> 3) * 256 + (gl & 7) * 2 + half * (DW2_RPW * 16);  // (chunk, first row of the half, element)
+    // counts of this thread's 8 (row, gene) elements, software-pipelined two deep: the row ids of piece i + 2 and the
+    // counts of piece i + 1 are loaded (from the B block's row table in global memory / the count matrix) while
+    // piece i is processed, so neither global latency sits between `full` and the math
+    auto rid_ptr = [&](int i, int r) {
+      return reinterpret_cast<const int64_t*>(bpack + (size_t)(p0 + i) * DW2_BSTAGE + 6 * DW2_BV + (half * DW2_RPW + r) * 32 + 16);
+    };
+    auto load_x = [&](int64_t rid) -> int {
+      if (XK == XK_U8) return (int)reinterpret_cast<const uint8_t*>(xv)[rid * ldx + gx];
+      return (int)reinterpret_cast<const float*>(xv)[rid * ldx + gx];
+    };
+    int64_t rid_n[DW2_RPW];
+    int xa[DW2_RPW], xb[DW2_RPW];
+#pragma unroll
+    for (int r = 0; r < DW2_RPW; ++r) {
+      xa[r] = n > 0 ? load_x(*rid_ptr(0, r)) : 0;
+      rid_n[r] = n > 1 ? *rid_ptr(1, r) : 0;
+      xb[r] = 0;
     }
-    if (gvalid) {
-      if (!ZINB) slabv[((int64_t)blockIdx.y * 3 + 1) * G + g] = 0.f;
-      slabv[((int64_t)blockIdx.y * 3 + 2) * G + g] = v[0] * kT;  // sum_b u dth'
+    // one stage: this thread's DW2_RPW elements with the counts `xs`
+    auto stage_math = [&](int i, const int (&xs)[DW2_RPW]) {
+      const int s = i % DW2_NS;
+      tc::mbar_wait(&full[s], (i / DW2_NS) & 1);
+      const uint8_t* st = smem + s * L::STAGE;
+      const float* rt = reinterpret_cast<const float*>(st + L::A_BYTES + 6 * DW2_BV) + half * DW2_RPW * 8;
+#pragma unroll
+      for (int r = 0; r < DW2_RPW; ++r) {
+        const float4 t0 = *reinterpret_cast<const float4*>(rt + r * 8);  // 1/s1, 2^-P exp(library), u, valid
+        const uint8_t* e = st + eoff + r * 16;
+        const float a1 = __half2float(*reinterpret_cast<const __half*>(e)) + __half2float(*reinterpret_cast<const __half*>(e + 4096));
+        const float a2 = __half2float(*reinterpret_cast<const __half*>(e + 2 * 4096)) +
+                         __half2float(*reinterpret_cast<const __half*>(e + 3 * 4096));
+        const float g1 = a1 * t0.x, mu = a2 * t0.y;
+        const int xi = xs[r];
+        const float x = (float)xi;
+        const float rT = fm::rcp(theta + mu + eps);
+        const float d_log = -fm::LN2 * fm::lg2(fmaf(mu, rth, 1.f));  // log(theta+eps) - log(theta+mu+eps)
+        const float da = fmaf(theta, rth - rT, d_log);
+        float dgd;
+        if (xi < DW2_T) {
+          dgd = s_dgt[xi * TC_M + gl];
+        } else {
+          dgd = s_dgt[(DW2_T - 1) * TC_M + gl];
+          for (int k = DW2_T - 1; k < xi; ++k) dgd += __frcp_rn(theta + (float)k);
+        }
+        float dth = fmaf(-x, rT, da) + dgd;
+        if (ZINB && xi == 0) {  // zero-inflated zero: weight sigmoid(a) = g1 / (theta mu / (theta + mu + eps))
+          const float base = theta * mu * rT;
+          const float sa = base > 1e-30f ? fminf(fmaxf(g1 * fm::rcp(base), 0.f), 1.f) : 0.f;
+          dth = sa * da;
+        }
+        dth_sum = fmaf(t0.z * t0.w, dth, dth_sum);
+      }
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&empty[s]);
+    };
+    // two stages per trip so the count registers alternate without moves (a move would wait for the loads in flight)
+    for (int i = 0; i < n; i += 2) {
+      if (i + 1 < n) {
+#pragma unroll
+        for (int r = 0; r < DW2_RPW; ++r) xb[r] = load_x(rid_n[r]);
+      }
+      if (i + 2 < n) {
+#pragma unroll
+        for (int r = 0; r < DW2_RPW; ++r) rid_n[r] = *rid_ptr(i + 2, r);
+      }
+      stage_math(i, xa);
+      if (i + 1 < n) {
+        if (i + 2 < n) {
+#pragma unroll
+          for (int r = 0; r < DW2_RPW; ++r) xa[r] = load_x(rid_n[r]);
+        }
+        if (i + 3 < n) {
+#pragma unroll
+          for (int r = 0; r < DW2_RPW; ++r) rid_n[r] = *rid_ptr(i + 3, r);
+        }
+        stage_math(i + 1, xb);
+      }
+    }
+    if (half > 0) s_red[(half - 1) * TC_M + gl] = dth_sum;
+    asm volatile("bar.sync 1, %0;" ::"n"(32 * DW2_DTW) : "memory");
+    if (half == 0) {
+      dth_sum += (s_red[gl] + s_red[TC_M + gl]) + s_red[2 * TC_M + gl];
+      // ===== epilogue (warps 4..7): thread = gene; TMEM lane = gene
+      if (n > 0) {
+        tc::mbar_wait(accfull, 0);
+        tc::fence_after_sync();
+      }
+      const uint32_t lane_sel = (uint32_t)(32 * (warp & 3)) << 16;
+      const float kW = 1.f / (scal[0] * TC_SCALE_H), kP = 1.f / (scal[1] * TC_SCALE_H);
+#pragma unroll 1
+      for (int hd = 0; hd < NH; ++hd) {
+        float* o = slabW + (((int64_t)blockIdx.y * NH + hd) * G + g) * TC_H;
+        const float kk = hd == 0 ? kW : kP;
+#pragma unroll 1
+        for (int c = 0; c < 17; ++c) {  // 16 chunks of weights + the ones-column chunk
+          float v[8];
+          if (n > 0) {
+            tc::tmem_ld8(tmem_base + lane_sel + hd * 144 + 8 * c, v);
+            tc::tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+          }
+          if (!gvalid) continue;
+          if (c < 16) {
+            *reinterpret_cast<float4*>(o + 8 * c) = make_float4(v[0] * kk, v[1] * kk, v[2] * kk, v[3] * kk);
+            *reinterpret_cast<float4*>(o + 8 * c + 4) = make_float4(v[4] * kk, v[5] * kk, v[6] * kk, v[7] * kk);
+          } else {
+            slabv[((int64_t)blockIdx.y * 3 + hd) * G + g] = v[0] * kk;  // dbs / dbp
+          }
+        }
+      }
+      if (gvalid) {
+        if (!ZINB) slabv[((int64_t)blockIdx.y * 3 + 1) * G + g] = 0.f;
+        slabv[((int64_t)blockIdx.y * 3 + 2) * G + g] = dth_sum;  // sum_b u_b d(ll)/d(theta)
+      }
     }
   }
   tc::fence_before_sync();
@@ -256,74 +346,9 @@ __global__ void __launch_bounds__(DW2_THREADS, 1)
   if (warp == 2) tc::tmem_dealloc(tmem_base, 512);
 }
 
-// ---- sum_b u_b [psi(x_bg + theta_g) - psi(theta_g)] per gene: thread = gene, rows of one split in order.
-// psi(x + theta) - psi(theta) = sum_{i < x} 1 / (theta + i) for an integer count x: a 32-entry table per gene in shared
-// memory ([count][gene]: conflict-free), the rare larger counts by the series / asymptotic digamma.  Depends on the
-// counts, theta and the loss weights only: the training plan runs it on its side stream beside the forward.
-constexpr int DPSI_T = 32;
-template <int XK>
-__global__ void __launch_bounds__(128)
-    tc_dpsi_colsum_kernel(const void* __restrict__ xv, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
-                          int64_t G, const float* __restrict__ px_r, const float* __restrict__ g_reconst,
-                          int rows_per_split, float* __restrict__ slab /*[splits][G]*/) {
-  __shared__ float s_T[DPSI_T * 128];
-  __shared__ int64_t s_row[64];
-  __shared__ float s_u[64];
-  const int64_t g = (int64_t)blockIdx.x * 128 + threadIdx.x;
-  const int64_t b0 = (int64_t)blockIdx.y * rows_per_split, b1 = min(B, b0 + rows_per_split);
-  const float theta = g < G ? expf(px_r[g]) : 1.f;
-  {
-    float d = 0.f;
-    for (int k = 0; k < DPSI_T; ++k) {
-      s_T[k * 128 + threadIdx.x] = d;
-      d += __frcp_rn(theta + (float)k);
-    }
-  }
-  const int64_t gc = min(g, G - 1);  // threads past G read a valid column and drop the result
-  float acc = 0.f;
-  for (int64_t bb = b0; bb < b1; bb += 64) {
-    __syncthreads();
-    if (threadIdx.x < 64 && bb + threadIdx.x < b1) {
-      const int64_t b = bb + threadIdx.x;
-      s_row[threadIdx.x] = row_idx ? row_idx[b] : b;
-      s_u[threadIdx.x] = g_reconst ? g_reconst[b] : 1.f;
-    }
-    __syncthreads();
-    const int nrow = (int)min((int64_t)64, b1 - bb);
-    for (int rb = 0; rb < nrow; rb += 16) {
-      int xs[16];  // the 16 loads are issued together (no branch between them), then consumed
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const int r = min(rb + k, nrow - 1);
-        if (XK == XK_U8) xs[k] = (int)reinterpret_cast<const uint8_t*>(xv)[s_row[r] * ldx + gc];
-        else xs[k] = (int)reinterpret_cast<const float*>(xv)[s_row[r] * ldx + gc];
-      }
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        if (rb + k >= nrow) break;
-        const int xi = xs[k];
-        float d;
-        if (xi < DPSI_T) {
-          d = s_T[xi * 128 + threadIdx.x];
-        } else {
-          d = s_T[(DPSI_T - 1) * 128 + threadIdx.x];
-          if (xi < 256) {
-            for (int i = DPSI_T - 1; i < xi; ++i) d += __frcp_rn(theta + (float)i);
-          } else {
-            d = fm::digamma_pos_fast((float)xi + theta) - fm::digamma_pos_fast(theta);
-          }
-        }
-        acc = fmaf(s_u[rb + k], d, acc);
-      }
-    }
-  }
-  if (g < G) slab[(int64_t)blockIdx.y * G + g] = acc;
-}
-
 // ---- fixed-order sums of the split slabs -> gradients -----------------------------------------------------------
 static __global__ void tc_dw2_reduce_kernel(const float* __restrict__ slabW, const float* __restrict__ slabv,
-                                            const float* __restrict__ slabpsi, int64_t splits, int64_t splits_psi,
-                                            int nheads, int64_t GH, int64_t G, const float* __restrict__ px_r,
+                                            int64_t splits, int nheads, int64_t GH, int64_t G, const float* __restrict__ px_r,
                                             float* __restrict__ dWs, float* __restrict__ dWp, float* __restrict__ dbs,
                                             float* __restrict__ dbp, float* __restrict__ dpx_r) {
   const int64_t e = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -343,17 +368,16 @@ static __global__ void tc_dw2_reduce_kernel(const float* __restrict__ slabW, con
   }
   const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (g < G) {
-    float a = 0.f, b = 0.f, c = 0.f, d = 0.f;
+    float a = 0.f, b = 0.f, c = 0.f;
 #pragma unroll 4
     for (int64_t t = 0; t < splits; ++t) {
       a += slabv[(t * 3 + 0) * G + g];
       b += slabv[(t * 3 + 1) * G + g];
       c += slabv[(t * 3 + 2) * G + g];
     }
-    for (int64_t t = 0; t < splits_psi; ++t) d += slabpsi[t * G + g];
     if (dbs) dbs[g] = a;
     if (nheads == 2 && dbp) dbp[g] = b;
-    if (dpx_r) dpx_r[g] = -expf(px_r[g]) * (c + d);
+    if (dpx_r) dpx_r[g] = -expf(px_r[g]) * c;
   }
 }
 
@@ -382,28 +406,11 @@ int64_t tc_decoder_bwd2_ws_bytes(int64_t B, int64_t G, int likelihood) {
   return (int64_t)dw2_plan(B, G, likelihood == SCVI_LIK_ZINB ? 2 : 1).total;
 }
 
-// The count-only digamma sums (SCVI_PREC_AOPS): [dpsi_splits(B)][G] floats at `slab`
-int dpsi_splits(int64_t B) { return (int)cdiv(B, cdiv(B, std::max<int64_t>(1, std::min<int64_t>(32, B / 256)))); }
-size_t tc_dpsi_bytes(int64_t B, int64_t G) { return (size_t)dpsi_splits(B) * G * sizeof(float); }
-int tc_dpsi_sums(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t G, const float* px_r,
-                 const float* g_reconst, int xkind, float* slab, cudaStream_t st) {
-  const int splits = dpsi_splits(B);
-  const int rows_per_split = (int)cdiv(B, splits);
-  dim3 grid((unsigned)cdiv(G, 128), (unsigned)splits);
-  if (xkind == XK_U8)
-    tc_dpsi_colsum_kernel<XK_U8><<<grid, 128, 0, st>>>(x, ldx, row_idx, B, G, px_r, g_reconst, rows_per_split, slab);
-  else
-    tc_dpsi_colsum_kernel<XK_F32_INT><<<grid, 128, 0, st>>>(x, ldx, row_idx, B, G, px_r, g_reconst, rows_per_split, slab);
-  SCVI_LAUNCH_CHECK("scvi_decoder_dpsi_sums");
-  return SCVI_OK;
-}
-
 int tc_decoder_nll_bwd_dw2(const float* h, int64_t ldh, int64_t B, int64_t G, const float* px_r, const void* x,
                            int64_t ldx, const int64_t* row_idx, const float* library, const float* row_stats,
                            const float* g_reconst, int likelihood, float* dWs, float* dbs, float* dWp, float* dbp,
-                           float* dpx_r, void* ws, const uint8_t* aops, const float* fmax_part, const float* slabpsi,
+                           float* dpx_r, void* ws, const uint8_t* aops, const float* fmax_part, int xkind,
                            cudaStream_t st) {
-  (void)x; (void)ldx; (void)row_idx;
   const bool zinb = likelihood == SCVI_LIK_ZINB;
   const int nheads = zinb ? 2 : 1;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_AOPS): ws must be 256-byte aligned");
@@ -415,27 +422,31 @@ int tc_decoder_nll_bwd_dw2(const float* h, int64_t ldh, int64_t B, int64_t G, co
   float* scal = (float*)(w8 + p.off_scal);
   float* slabW = (float*)(w8 + p.off_slabW);
   float* slabv = (float*)(w8 + p.off_slabv);
-  tc_pack_b16_kernel<<<(unsigned)cdiv(B, TC_M), 512, 0, st>>>(h, ldh, B, row_stats, library, g_reconst, fmax_part,
+  tc_pack_b16_kernel<<<(unsigned)cdiv(B, TC_M), 512, 0, st>>>(h, ldh, B, row_stats, library, g_reconst, row_idx, fmax_part,
                                                               (int)cdiv(B, 8), bpack, scal);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc pack B)");
   dim3 grid((unsigned)p.nGB, (unsigned)p.splits);
+#define SCVI_DW2(Z, K)                                                                                          \
+  do {                                                                                                          \
+    auto k = tc_dw_gemm_kernel<Z, K>;                                                                           \
+    constexpr int smem = (int)Dw2Smem<Z>::TOTAL + 128;                                                          \
+    static std::atomic<uint64_t> optin{0};                                                                      \
+    if (int rc = smem_optin((const void*)k, smem, optin, "tc_dw_gemm")) return rc;                              \
+    k<<<grid, DW2_THREADS, smem, st>>>(B, G, aops, bpack, scal, x, ldx, px_r, 1e-8f, p.pieces_per_split, slabW, \
+                                       slabv);                                                                  \
+  } while (0)
   if (zinb) {
-    auto k = tc_dw_gemm_kernel<true>;
-    constexpr int smem = (int)Dw2Smem<true>::TOTAL + 128;
-    static std::atomic<uint64_t> optin{0};
-    if (int rc = smem_optin((const void*)k, smem, optin, "tc_dw_gemm")) return rc;
-    k<<<grid, DW2_THREADS, smem, st>>>(B, G, aops, bpack, scal, p.pieces_per_split, slabW, slabv);
+    if (xkind == XK_U8) SCVI_DW2(true, XK_U8);
+    else SCVI_DW2(true, XK_F32_INT);
   } else {
-    auto k = tc_dw_gemm_kernel<false>;
-    constexpr int smem = (int)Dw2Smem<false>::TOTAL + 128;
-    static std::atomic<uint64_t> optin{0};
-    if (int rc = smem_optin((const void*)k, smem, optin, "tc_dw_gemm")) return rc;
-    k<<<grid, DW2_THREADS, smem, st>>>(B, G, aops, bpack, scal, p.pieces_per_split, slabW, slabv);
+    if (xkind == XK_U8) SCVI_DW2(false, XK_U8);
+    else SCVI_DW2(false, XK_F32_INT);
   }
+#undef SCVI_DW2
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc dW gemm)");
   const int64_t GH = G * TC_H;
   tc_dw2_reduce_kernel<<<(unsigned)cdiv(std::max<int64_t>(GH / 4, G), 256), 256, 0, st>>>(
-      slabW, slabv, slabpsi, p.splits, dpsi_splits(B), nheads, GH, G, px_r, dWs, dWp, dbs, dbp, dpx_r);
+      slabW, slabv, p.splits, nheads, GH, G, px_r, dWs, dWp, dbs, dbp, dpx_r);
   SCVI_LAUNCH_CHECK("scvi_decoder_nll_bwd(tc reduce)");
   return SCVI_OK;
 }

@@ -138,11 +138,12 @@ __device__ long long g_k2_trace[3 * 64 * 8];
 // =======================================================================================
 // K2: fused NLL + dh
 // =======================================================================================
-template <bool ZINB>
+template <bool ZINB, bool AOPS = false>
 struct K2Smem {
   static constexpr int NH = ZINB ? 2 : 1;
   static constexpr uint32_t WSTAGE = tc_w32_stage_bytes(NH);
-  static constexpr int NSTG = ZINB ? 3 : 2;  // staged operands: g1, p, (dp)
+  static constexpr int NMMA = ZINB ? 3 : 2;          // staged operands of the dh GEMMs: g1, p, (dp)
+  static constexpr int NSTG = NMMA;  // (AOPS: the same blocks are also copied to global memory for the dW GEMM)
   static constexpr uint32_t H_HI = 0;
   static constexpr uint32_t H_LO = TC_OPER_BYTES;
   static constexpr uint32_t W0 = 2 * TC_OPER_BYTES;
@@ -190,12 +191,12 @@ __device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi
 // 32-gene tile t, 8-gene chunk cg) = 16 rows x 16 B at
 //   aops + p * tt_aops_part_bytes + ((((rt * 8 + o) * nT4 + t) * 4 + cg) * 256,    nT4 = tiles padded to whole 128-gene blocks
 // i.e. the 4 KB block [16 gene chunks][16 rows][16 B] of (row piece, 128-gene block) is contiguous: an MN-major A
-// operand of the GEMM, one bulk copy.  Parts: 0/1 = g1 s1 hi/lo, 2/3 = p 2^P hi/lo, 4/5 = dth' hi/lo, 6/7 = -dpi 2^D hi/lo.
+// operand of the GEMM, one bulk copy.  Parts: 0/1 = g1 s1 hi/lo, 2/3 = p 2^P hi/lo, 4/5 = -dpi 2^D hi/lo (ZINB).
 __host__ __device__ inline int64_t tt_nT4(int64_t G) { return ((G + TC_M - 1) / TC_M) * 4; }
 __host__ __device__ inline size_t tt_aops_part_bytes(int64_t B, int64_t G) {
   return (size_t)((B + TC_M - 1) / TC_M) * 8 * tt_nT4(G) * 4 * 256;
 }
-__host__ __device__ inline int tt_aops_parts(bool zinb) { return zinb ? 8 : 6; }
+__host__ __device__ inline int tt_aops_parts(bool zinb) { return zinb ? 6 : 4; }
 size_t tc_aops_bytes(int64_t B, int64_t G, bool zinb) { return tt_aops_part_bytes(B, G) * tt_aops_parts(zinb); }
 
 template <bool ZINB, int XK, bool AOPS>
@@ -206,8 +207,9 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
                      const float* __restrict__ lse_part /*[nsplit_lse][B][2]*/, int nsplit_lse, int tiles_per_split,
                      float eps, int xvec, float* __restrict__ out_part /*[nsplit][B][2] = (nll, S)*/,
                      float* __restrict__ dh_part /*[nsplit][2][B][H]*/, uint8_t* __restrict__ aops /*nullable*/) {
-  using L = K2Smem<ZINB>;
-  constexpr bool DTH = AOPS && XK != XK_F32;  // integer counts: the operands are kept for the dW GEMM
+  using L = K2Smem<ZINB, AOPS>;
+  constexpr bool KEEP = AOPS && XK != XK_F32;  // integer counts: the staged operands are kept for the dW GEMM
+  constexpr bool DTH = false;
   constexpr int NH = L::NH;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
@@ -234,7 +236,7 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::mbar_init(&tempty[i], TT_EPI_WARPS);
     }
     tc::mbar_init(sfull, TT_EPI_WARPS);
-    tc::mbar_init(sempty, 1);
+    tc::mbar_init(sempty, KEEP ? 3 : 1);  // + the two copier warps when the operands are kept
     tc::mbar_init(accfull, 1);
     tc::fence_mbar_init();
   }
@@ -323,6 +325,41 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       if (leader) tc::mma_commit(accfull);
       __syncwarp();
     }
+  } else if ((warp == 2 || warp == 3) && KEEP) {
+    // ===== copier (SCVI_PREC_AOPS): the staged operand blocks of every tile go to global memory in the layout the dW
+    // GEMM loads (tt_aops_part_bytes).  A whole warp that does nothing else: the epilogue warps pay nothing for it
+    // (issuing the 16-byte stores from the epilogue threads cost the kernel 19 %).  Two warps on two different
+    // schedulers share the blocks; the staging buffers are released (sempty) by the MMA commit AND by both.
+    if (aops) {
+      const size_t ps = tt_aops_part_bytes(B, G);
+      const int64_t nT4 = tt_nT4(G);
+      const uint8_t* stg = smem + L::STG;
+      for (int j = 0; j < ntiles; ++j) {
+        tc::mbar_wait(sfull, j & 1);
+        uint8_t* base = aops + (((size_t)blockIdx.x * 8) * nT4 + (t0 + j)) * 4 * 256;
+#pragma unroll
+        for (int k = warp - 2; k < 2 * L::NSTG; k += 2) {  // warp 2: the hi blocks, warp 3: the lo blocks
+          const int part = k;  // 0/1 = g1 s1 hi/lo, 2/3 = p 2^P hi/lo, 4/5 = -dpi 2^D hi/lo
+          uint4 v[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = *reinterpret_cast<const uint4*>(stg + k * TT_ABLK + (lane + 32 * i) * 16);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int c = lane + 32 * i, cgc = c >> 7, rr = c & 127;  // chunk c of the block = (column group, row)
+            // streaming store (evict-first): 264 MB per launch must not push the weight tiles and h out of L2
+            __stcs(reinterpret_cast<uint4*>(base + part * ps + ((size_t)(rr >> 4) * nT4 * 4 + cgc) * 256 + (rr & 15) * 16), v[i]);
+          }
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(sempty);
+      }
+    } else {
+      for (int j = 0; j < ntiles; ++j) {
+        tc::mbar_wait(sfull, j & 1);
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(sempty);
+      }
+    }
   } else if (warp >= 4) {
     // ===== epilogue: thread = (row r = 32*(warp%4) + lane, column group cg of 8 genes)
     const int q = warp & 3, cg = (warp - 4) >> 2;
@@ -406,22 +443,6 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       tc::split8(a1, hi1, lo1);
       tc::split8(a2, hi2, lo2);
       if (ZINB) tc::split8(a3, hi3, lo3);
-      if (DTH && aops) {  // keep the operands for the dW GEMM (a warp writes two 256-byte pieces per part)
-        uint4 hi4, lo4;
-        tc::split8(a4, hi4, lo4);
-        const size_t ps = tt_aops_part_bytes(B, G);
-        uint8_t* o = aops + ((((size_t)blockIdx.x * 8 + (r >> 4)) * tt_nT4(G) + (t0 + j)) * 4 + cg) * 256 + (r & 15) * 16;
-        *reinterpret_cast<uint4*>(o + 0 * ps) = hi1;
-        *reinterpret_cast<uint4*>(o + 1 * ps) = lo1;
-        *reinterpret_cast<uint4*>(o + 2 * ps) = hi2;
-        *reinterpret_cast<uint4*>(o + 3 * ps) = lo2;
-        *reinterpret_cast<uint4*>(o + 4 * ps) = hi4;
-        *reinterpret_cast<uint4*>(o + 5 * ps) = lo4;
-        if (ZINB) {
-          *reinterpret_cast<uint4*>(o + 6 * ps) = hi3;
-          *reinterpret_cast<uint4*>(o + 7 * ps) = lo3;
-        }
-      }
 #ifdef SCVI_K2_TRACE
       asm volatile("" ::"r"(hi1.x), "r"(lo2.w), "r"(hi3.y) : "memory");  // the math is done before the stamp
 #endif
@@ -581,7 +602,7 @@ static int tt_launch_k2(const float* h, int64_t ldh, int64_t B, int64_t G, const
                         int nsplit, int tiles_per_split, int xvec, float* out_part, float* dh_part, uint8_t* aops,
                         cudaStream_t st) {
   auto k = tc_nll_dh_kernel<ZINB, XK, AOPS>;
-  constexpr int smem = (int)K2Smem<ZINB>::TOTAL + 128;
+  constexpr int smem = (int)K2Smem<ZINB, AOPS>::TOTAL + 128;
   static std::atomic<uint64_t> optin{0};
   if (int rc = smem_optin((const void*)k, smem, optin, "tc_nll_dh")) return rc;
   dim3 grid((unsigned)cdiv(B, TC_M), (unsigned)nsplit);
@@ -1018,12 +1039,12 @@ __global__ void tc_pack_heads_kernel(const float* __restrict__ Ws, const float* 
                                      float* __restrict__ gconst);
 
 void tc_decoder_fwd_ws_offsets(int64_t B, int64_t G, int nheads, size_t* off_packed, size_t* off_gconst);
-void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_psi, size_t* off_aops);
+void tc_decoder_fwd_ws_aops(int64_t B, int64_t G, int nheads, size_t* off_fmax, size_t* off_aops);
 int64_t tc_decoder_bwd2_ws_bytes(int64_t B, int64_t G, int likelihood);  // decoder_tc_dw2.cu
 int tc_decoder_nll_bwd_dw2(const float* h, int64_t ldh, int64_t B, int64_t G, const float* px_r, const void* x,
                            int64_t ldx, const int64_t* row_idx, const float* library, const float* row_stats,
                            const float* g_reconst, int likelihood, float* dWs, float* dbs, float* dWp, float* dbp,
-                           float* dpx_r, void* ws, const uint8_t* aops, const float* fmax_part, const float* slabpsi,
+                           float* dpx_r, void* ws, const uint8_t* aops, const float* fmax_part, int xkind,
                            cudaStream_t st);
 
 struct TtBwdPlan {
@@ -1078,12 +1099,11 @@ int tc_decoder_nll_bwd_dw(const float* h, int64_t ldh, int64_t B, int64_t G, con
   const int nheads = zinb ? 2 : 1;
   if (xkind & 16) {  // SCVI_PREC_AOPS: the matching forward kept its operands in fwd_ws -> pure GEMM
     SCVI_REQUIRE(fwd_ws != nullptr, "scvi_decoder_nll_bwd(SCVI_PREC_AOPS): needs the forward workspace");
-    size_t off_fmax, off_psi, off_aops;
-    tc_decoder_fwd_ws_aops(B, G, nheads, &off_fmax, &off_psi, &off_aops);
+    size_t off_fmax, off_aops;
+    tc_decoder_fwd_ws_aops(B, G, nheads, &off_fmax, &off_aops);
     const uint8_t* f8 = (const uint8_t*)fwd_ws;
     return tc_decoder_nll_bwd_dw2(h, ldh, B, G, px_r, x, ldx, row_idx, library, row_stats, g_reconst, likelihood, dWs, dbs,
-                                  dWp, dbp, dpx_r, ws, f8 + off_aops, (const float*)(f8 + off_fmax),
-                                  (const float*)(f8 + off_psi), st);
+                                  dWp, dbp, dpx_r, ws, f8 + off_aops, (const float*)(f8 + off_fmax), xkind & 15, st);
   }
   xkind &= 15;
   SCVI_REQUIRE(ws != nullptr && ((uintptr_t)ws % 256 == 0), "scvi_decoder_nll_bwd(SCVI_PREC_TC): ws must be 256-byte aligned");

@@ -282,9 +282,9 @@ class FusedTrainingPlan:
         self.dy1_amax = f(int(query("scvi_mid_n_tiles", B)))  # max |dy1| per row tile (mid_bwd -> encoder dW)
         # SCVI_AOPS=1 (integer counts + tcgen05 kernels): the fused likelihood kernel keeps its per-element operands in
         # the forward workspace and the head-weight gradients are a pure tensor-core GEMM over them (SCVI_PREC_AOPS).
-        # Opt-in: parity-green, the GEMM takes 54 us where the recompute kernel takes 99 us, but keeping the operands
-        # costs the fused kernel ~35 us (it is bound by its instruction count), so the step does not get faster
-        # 
+        # Opt-in: parity-green, but keeping the operands costs the fused kernel ~15 us and the dispersion derivative
+        # has to be re-derived per element inside the GEMM kernel: 0.427 ms per step against 0.379 ms (DESIGN.md
+        # section 9, experiments/README.md)
         self._aops = (_lib.PREC_AOPS if (self.module.precision == _lib.PREC_TC and H == 128 and self._x_integer
                                          and os.environ.get("SCVI_AOPS", "0") == "1") else 0)
         nf = query("scvi_decoder_nll_fwd_ws_bytes", B, H, G, lik,
@@ -339,9 +339,6 @@ class FusedTrainingPlan:
                 if self._ev_prologue is None:
                     self._ev_prologue = torch.cuda.Event()
                 self._ev_prologue.record(side)
-            if aops:  # count-only part of the dispersion gradient: needs the counts and the loss weights only
-                call("scvi_decoder_dpsi_sums", _p(X), ldx, _p(self.idx), B, G, _p(P["px_r"]), _p(self.g_rec), lik,
-                     prec | xkind | aops, _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
             call("scvi_decoder_nll_prepack", B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), lik, prec, 1,
                  _p(self.ws_fwd), C.c_void_p(side.cuda_stream))
         if prologue is not None and not overlap:
@@ -383,9 +380,6 @@ class FusedTrainingPlan:
         else:
             call("scvi_elbo_reduce", _p(self.reconst), _p(self.kl), B, 0.0, _p(self.klw), _p(self.out3), st)
         # ---- backward
-        if aops and not overlap:
-            call("scvi_decoder_dpsi_sums", _p(X), ldx, _p(self.idx), B, G, _p(P["px_r"]), _p(self.g_rec), lik,
-                 prec | xkind | aops, _p(self.ws_fwd), st)
         call("scvi_decoder_nll_bwd", _p(self.h), H, B, H, G, _p(Ws), _p(bs), _p(Wp), _p(bp), _p(P["px_r"]), _p(X), ldx,
              _p(self.idx), _p(self.library), _p(self.stats), _p(self.g_rec), lik, prec | xkind | aops, None, H,
              _p(Gd["decoder.px_scale_decoder.0.weight"]), _p(Gd["decoder.px_scale_decoder.0.bias"]),
