@@ -158,12 +158,12 @@ struct K2Smem {
 // the 8 elements of one thread for one tile.  Padded genes (beyond G) carry constants that make every output an
 // exact zero (scale bias -1e30 => mu = 0, dropout bias 0, theta 1, count 0), so nothing is masked here; rows
 // beyond B produce values that are never stored.
-template <bool ZINB, bool LEAN, bool DTH>
+template <bool ZINB, bool LEAN>
 __device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi)[8], const float (&sv)[8],
                                             const float (&pv)[8], const float* __restrict__ gc,
                                             const float* __restrict__ tab, const float* __restrict__ s_lgx1, float krow,
                                             float eps, float s1, float kP, float kD, float& nll, float& S,
-                                            float (&a1)[8], float (&a2)[8], float (&a3)[8], float (&a4)[8]) {
+                                            float (&a1)[8], float (&a2)[8], float (&a3)[8]) {
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const float4 k0 = *reinterpret_cast<const float4*>(gc + i * TC_GC);
@@ -172,18 +172,16 @@ __device__ __forceinline__ void tt_k2_elems(const float (&xq)[8], const int (&xi
     gk.theta = k0.x; gk.log_theta = k0.y; gk.lg_theta = k0.z; gk.rth = k1.y; gk.dg_theta = k1.z;
     const float sl = fmaf(sv[i], TC_RESCALE, k0.w);
     const float pl = ZINB ? fmaf(pv[i], TC_RESCALE, k1.x) : 0.f;
-    float ll, g1, dpi, mu, dthp = 0.f;
+    float ll, g1, dpi, mu;
     if (LEAN)
-      fm::elem_fwd_lean<ZINB, DTH>(xq[i], tab[i * fm::LGT + xi[i]], sl, pl, krow, gk, eps, ll, g1, dpi, mu, &dthp);
+      fm::elem_fwd_lean<ZINB>(xq[i], tab[i * fm::LGT + xi[i]], sl, pl, krow, gk, eps, ll, g1, dpi, mu);
     else
-      fm::elem_fwd_tab<ZINB, DTH>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu, &dthp);
+      fm::elem_fwd_tab<ZINB>(xq[i], sl, pl, krow, gk, eps, tab + i * fm::LGT, s_lgx1, ll, g1, dpi, mu);
     nll -= ll;
     S += g1;
     a1[i] = g1 * s1;
     a2[i] = mu * kP;
     a3[i] = dpi * kD;
-    // d(ll)/d(theta) without its digamma term (K3 as a pure GEMM: DESIGN section 4.3); padded genes give an exact 0
-    if (DTH) a4[i] = fmaxf(dthp, -60000.f);  // dth' <= 0 (log(1 + y) >= y / (1 + y)): one-sided clamp
   }
 }
 
@@ -209,7 +207,6 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
                      float* __restrict__ dh_part /*[nsplit][2][B][H]*/, uint8_t* __restrict__ aops /*nullable*/) {
   using L = K2Smem<ZINB, AOPS>;
   constexpr bool KEEP = AOPS && XK != XK_F32;  // integer counts: the staged operands are kept for the dW GEMM
-  constexpr bool DTH = false;
   constexpr int NH = L::NH;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((128u - (tc::smem_u32(smem_raw) & 127u)) & 127u);
@@ -434,11 +431,11 @@ __global__ void __launch_bounds__(TT_THREADS, 1)
       const float* gc = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32) + 8 * cg * TC_GC;
       const float* tab = reinterpret_cast<const float*>(smem + L::W0 + s * L::WSTAGE + NH * 2 * TC_BLK32 + TC_GC32_BYTES) +
                          8 * cg * fm::LGT;
-      float a1[8], a2[8], a3[8], a4[8];
+      float a1[8], a2[8], a3[8];
       if (XK != XK_F32 && lean)
-        tt_k2_elems<ZINB, true, DTH>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3, a4);
+        tt_k2_elems<ZINB, true>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
       else
-        tt_k2_elems<ZINB, false, DTH>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3, a4);
+        tt_k2_elems<ZINB, false>(xq, xi, sv, pv, gc, tab, s_lgx1, krow, eps, s1, kP, kD, nll, S, a1, a2, a3);
       uint4 hi1, lo1, hi2, lo2, hi3, lo3;
       tc::split8(a1, hi1, lo1);
       tc::split8(a2, hi2, lo2);

@@ -187,13 +187,10 @@ SCVI_FM void elem_fwd(float x, float s, float pi, float krow, const GeneK& g, fl
 // 9 SFU ops per element (ZINB), 5 (NB).
 constexpr int LGT = 64;
 
-// DTH: also return *dthp = d(ll)/d(theta) WITHOUT its digamma term psi(x + theta) - psi(theta) (a function of the
-// count and theta only, summed over the minibatch by a separate pass): theta (1/(theta+eps) - 1/(theta+mu+eps))
-// + log(theta+eps) - log(theta+mu+eps) - x/(theta+mu+eps), weighted by sigmoid(a) in the zero-inflated zero case.
-template <bool ZINB, bool DTH = false>
+template <bool ZINB>
 SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g, float eps,
                           const float* __restrict__ tab /*[LGT] of this gene*/, const float* __restrict__ lgx1,
-                          float& ll, float& g1, float& dpi, float& mu, float* dthp = nullptr) {
+                          float& ll, float& g1, float& dpi, float& mu) {
   mu = ex2(fmaf(s, LOG2E, krow));
   const float me = mu + eps;
   const float rT = rcp(g.theta + mu + eps);
@@ -219,15 +216,10 @@ SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g
     g1 = base * (zero ? sa : fmaf(-x, r1, 1.f));   // r1 - rT = theta / (me T)
     const float e_rp = ep * rp;
     dpi = zero ? (pi >= 0.f ? e_rp : rp) - sa : -(pi >= 0.f ? rp : e_rp);
-    if (DTH) {
-      const float da_dth = fmaf(g.theta, g.rth - rT, d_log);
-      *dthp = zero ? sa * da_dth : fmaf(-x, rT, da_dth);
-    }
   } else {
     ll = fmaf(g.theta, d_log, fmaf(x, flog(me * rT), lgd));
     g1 = base * fmaf(-x, rcp(me), 1.f);
     dpi = 0.f;
-    if (DTH) *dthp = fmaf(-x, rT, fmaf(g.theta, g.rth - rT, d_log));
   }
 }
 
@@ -238,9 +230,9 @@ SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g
 // by side interleave freely, which is what hides the SFU latency.  log(theta+mu+eps) is formed as
 // log(theta+eps) + log(1 + mu/(theta+eps)) from the one lg2 the NB term needs anyway.
 // SFU ops: ZINB 9 (ex2 x3, lg2 x3, rcp x3), NB 5.
-template <bool ZINB, bool DTH = false>
+template <bool ZINB>
 SCVI_FM void elem_fwd_lean(float x, float lgd, float s, float pi, float krow, const GeneK& g, float eps, float& ll,
-                           float& g1, float& dpi, float& mu, float* dthp = nullptr) {
+                           float& g1, float& dpi, float& mu) {
   mu = ex2(fmaf(s, LOG2E, krow));
   const float me = mu + eps;
   const float rT = rcp(g.theta + me);
@@ -267,16 +259,11 @@ SCVI_FM void elem_fwd_lean(float x, float lgd, float s, float pi, float krow, co
     const float sp = pi >= 0.f ? e_rp : rp;          // sigmoid(-pi)
     const float sn = pi >= 0.f ? rp : e_rp;          // sigmoid(pi)
     dpi = zero ? sp - sa : -sn;
-    if (DTH) {
-      const float da_dth = fmaf(g.theta, g.rth - rT, -LN2 * lu);
-      *dthp = zero ? sa * da_dth : fmaf(-x, rT, da_dth);
-    }
   } else {
     const float l2 = lg2(me);
     ll = fmaf(thl, lu, fmaf(x, fmaf(LN2, l2 - lu, -g.log_theta), lgd));
     g1 = base * fmaf(-x, rcp(me), 1.f);
     dpi = 0.f;
-    if (DTH) *dthp = fmaf(-x, rT, fmaf(g.theta, g.rth - rT, -LN2 * lu));
   }
 }
 
