@@ -125,3 +125,109 @@ def test_fused_step_vs_eager_pytorch_on_the_same_gpu(B):
         with open(os.path.join("gpurun_out", f"same_gpu_comparator_B{B}.json"), "w") as f:
             f.write(json.dumps(line) + "\n")
     assert fused < eager_dev, line
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The same eager arm under data parallelism (SURVEY 8d "Reference timed beside it"): what torch
+# DDP does for the reference's `Trainer(strategy="ddp")` -- every rank runs the eager step on its own minibatch, the
+# gradients are mean-all-reduced over NCCL (DDP's single 25 MB bucket: one flattened all-reduce; the arena is 3 MB),
+# every rank applies Adam.  Weak scaling, 8192 cells per rank and step, counts resident on each device.
+# ---------------------------------------------------------------------------------------------------------------
+def _ddp_eager_worker(rank, world, port, q):
+    try:
+        import torch.distributed as dist
+
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(port)
+        torch.cuda.set_device(rank)
+        dev = torch.device("cuda", rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+        B = 8192
+        X, batch = _counts()
+        import scvi_tools_b200 as S
+
+        torch.manual_seed(0)
+        m = S.VAE(n_input=G, n_batch=NB, gene_likelihood="zinb", n_hidden=H, n_latent=L, precision=1)
+        P = {k: v.detach().clone().to(dev) for k, v in m.state_dict().items()}
+        keys = O.trained_keys("zinb")
+        M = {k: torch.zeros_like(P[k]) for k in keys}
+        V = {k: torch.zeros_like(P[k]) for k in keys}
+        X_dev = torch.from_numpy(X).to(dev)
+        b_dev = torch.from_numpy(batch).to(dev)
+        gen = torch.Generator(device=dev).manual_seed(100 + rank)
+        t = [0]
+
+        def step():
+            ii = torch.randint(0, N_CELLS, (B,), device=dev, generator=gen)
+            mask = torch.rand(B, H, device=dev, generator=gen) >= 0.1
+            noise = torch.randn(B, L, device=dev, generator=gen)
+            out, grads = O.loss_and_grads(P, X_dev[ii], b_dev[ii].view(-1, 1), n_batch=NB, gene_likelihood="zinb",
+                                          kl_weight=0.0, drop_mask=mask, noise=noise)
+            flat = torch.cat([grads[k].reshape(-1) for k in keys])
+            dist.all_reduce(flat)
+            flat /= world
+            t[0] += 1
+            off = 0
+            for k in keys:
+                n = P[k].numel()
+                P[k], M[k], V[k] = O.adam_step(P[k], flat[off : off + n].view_as(P[k]), M[k], V[k], t[0])
+                off += n
+            P.update(out["bn_buffers"])
+
+        for _ in range(5):
+            step()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        steps = 20
+        e0.record()
+        for _ in range(steps):
+            step()
+        e1.record()
+        dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        chk = torch.stack([P[k].double().sum() for k in keys]).sum().view(1)
+        both = [torch.empty_like(chk) for _ in range(world)]
+        dist.all_gather(both, chk)
+        same = all(torch.equal(both[0], b) for b in both)
+        q.put((rank, "ok", float(ms), same))
+    except Exception:  # noqa: BLE001
+        import traceback
+
+        q.put((rank, traceback.format_exc(), 0.0, False))
+    finally:
+        os._exit(0)
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_eager_ddp_comparator_weak_scaling(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs >= {world} GPUs")
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = 29900 + (os.getpid() % 1000) + world
+    procs = [ctx.Process(target=_ddp_eager_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=600)
+        if p.is_alive():
+            p.kill()
+            pytest.fail("eager DDP worker hung")
+    res = [q.get() for _ in range(world)]
+    for r in res:
+        assert r[1] == "ok", r[1]
+    ms = max(r[2] for r in res)
+    assert all(r[3] for r in res), "replicas diverged"
+    line = {"what": "reference algorithm as eager PyTorch fp32 + gradient mean all-reduce (DDP semantics), weak scaling",
+            "n_gpus": world, "batch_size_per_gpu": 8192, "genes": G, "ms_per_step": ms,
+            "cells_per_s": world * 8192 / ms * 1e3, "replicas_identical": True}
+    print("\nEAGER_DDP_COMPARATOR " + json.dumps(line))
+    if os.path.isdir("gpurun_out"):
+        with open(os.path.join("gpurun_out", f"eager_ddp_comparator_n{world}.json"), "w") as f:
+            f.write(json.dumps(line) + "\n")
