@@ -621,7 +621,8 @@ def run_b200_arm(a):
         if name == "hybrid_gather" and frac <= 0.0:
             continue
         feeder = HostStreamedCounts(host_mat, batch=host_batch, batch_size=B, device=dev, dtype=hdt, device_gather=devg,
-                                    compact_stage=compact, hybrid_fraction=frac)
+                                    compact_stage=compact, hybrid_fraction=frac,
+                                    host_threads=max(1, (os.cpu_count() or 1) // world))  # the ranks share the host cores
         if devg and not feeder.device_gather:
             continue
         med, allb = run_e2e(feeder, lambda slot, i, f=feeder: f.submit(slot, rows=rows_of(i)))
