@@ -344,6 +344,23 @@ int scvi_decoder_params_fwd(const float* h, int64_t ldh, int64_t B, int64_t H, i
                             const float* bs, const float* Wp, const float* bp, const float* library,
                             float* px_scale, float* px_rate, float* px_dropout, int64_t ldo, void* stream);
 
+/* ---- f1 / f2: per-row reductions of the semi-supervised and multi-modal losses ---------
+ * out[r] = sum_d Normal(loc, scale).log_prob(value)[r, d] (torch.distributions.Normal.log_prob: -(v-m)^2 / (2 var)
+ * - log(scale) - log(sqrt(2 pi))), as SCANVAE.loss uses it for the z1 terms (src/scvi/module/_scanvae.py:178-278).
+ * `second` is the scale, or the variance when is_var != 0.  value / loc / second: contiguous [R, D]. */
+int scvi_normal_logprob_sum_fwd(const float* value, const float* loc, const float* second, int64_t R, int64_t D,
+                                int is_var, float* out, void* stream);
+/* gradients times gout[r]; dvalue / dloc / dsecond [R, D] are each nullable. */
+int scvi_normal_logprob_sum_bwd(const float* value, const float* loc, const float* second, const float* gout,
+                                int64_t R, int64_t D, int is_var, float* dvalue, float* dloc, float* dsecond,
+                                void* stream);
+/* kl[r] = KL(Categorical(probs=p[r]) || Categorical(probs=q[r])) exactly as torch builds it (row-normalised probs,
+ * logits = log(clamp(probs, eps, 1-eps)), inf where q == 0, 0 where p == 0): the label-prior term of SCANVAE.loss.
+ * q: [R, C] (ldq = C) or one row shared by all (ldq = 0).  dp (nullable, [R, C]) = gout[r] * d kl[r] / d p[r, :];
+ * kl may be NULL when only the gradient is wanted. */
+int scvi_categorical_kl(const float* p, const float* q, int64_t ldq, int64_t R, int64_t C, const float* gout,
+                        float* kl, float* dp, void* stream);
+
 /* ---- a12: multi-tensor Adam over one flat arena ---------------------------------------
  * replaces torch.optim.Adam(lr=1e-3, eps=0.01, weight_decay=1e-6) built by
  * TrainingPlan.configure_optimizers (src/scvi/train/_trainingplans.py:475-482,497-519):
@@ -358,6 +375,12 @@ int scvi_adam_step(float* p, const float* g, float* m, float* v, int64_t n, int6
 int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, int64_t* step_counter,
                          float lr, float beta1, float beta2, float eps, float weight_decay,
                          float grad_scale, void* stream);
+/* Gradient tensors -> the flat gradient arena of scvi_adam_step, one launch per 64 tensors: dst[offs[i] : offs[i]
+ * + ns[i]] = src[i][0 : ns[i]] (fp32, contiguous; src[i] == NULL zero-fills the slot).  src / offs / ns are HOST
+ * arrays; the table is passed by value to the kernel, so the call can be captured into a CUDA graph.  Stands where
+ * torch's AccumulateGrad would add every gradient into a pre-zeroed `.grad` (one launch per parameter). */
+int scvi_gather_segments(const void* const* src, const int64_t* offs, const int64_t* ns, int count, float* dst,
+                         void* stream);
 /* loss pieces of VAE.loss (src/scvi/module/_vae.py:573-580):
  * out[0] = mean_b(reconst + kl_weight * kl), out[1] = sum reconst, out[2] = sum kl.
  * kl_weight_dev (nullable, device float[1]) overrides `kl_weight` (graph replay: the KL warm-up

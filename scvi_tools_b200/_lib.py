@@ -73,6 +73,10 @@ SIGNATURES = {
     ),
     "scvi_decoder_params_fwd": (C.c_int, [P, I64, I64, I64, I64, P, P, P, P, P, P, P, P, I64, P]),
     "scvi_adam_step": (C.c_int, [P, P, P, P, I64, I64, F32, F32, F32, F32, F32, F32, P]),
+    "scvi_normal_logprob_sum_fwd": (C.c_int, [P, P, P, I64, I64, I32, P, P]),
+    "scvi_normal_logprob_sum_bwd": (C.c_int, [P, P, P, P, I64, I64, I32, P, P, P, P]),
+    "scvi_categorical_kl": (C.c_int, [P, P, I64, I64, I64, P, P, P, P]),
+    "scvi_gather_segments": (C.c_int, [P, P, P, I32, P, P]),
     "scvi_adam_step_graph": (C.c_int, [P, P, P, P, I64, P, F32, F32, F32, F32, F32, F32, P]),
     "scvi_host_device_pointer": (C.c_int, [P, C.POINTER(C.c_void_p)]),
     "scvi_comm_ctrl_bytes": (I64, []),

@@ -107,6 +107,35 @@ __global__ void elbo_seed_kernel(int64_t B, float klw_host, const float* __restr
   }
 }
 
+// Gradient tensors scattered over the allocator -> the flat gradient arena, one launch for up to GS_MAX tensors
+// (the table travels by value in the launch parameters: captured into a CUDA graph with the step, no device-side
+// pointer table to keep alive).  A NULL source zero-fills its slot (a parameter that received no gradient).
+constexpr int GS_MAX = 64;
+struct GatherSegs {
+  const float* src[GS_MAX];
+  int64_t off[GS_MAX];
+  int64_t n[GS_MAX];
+};
+__global__ void gather_segments_kernel(const GatherSegs s, float* __restrict__ dst) {
+  const int seg = blockIdx.y;
+  const float* __restrict__ src = s.src[seg];
+  float* __restrict__ d = dst + s.off[seg];
+  const int64_t n = s.n[seg];
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (src == nullptr) {
+    for (int64_t i = t0; i < n; i += stride) d[i] = 0.f;
+    return;
+  }
+  if ((((uintptr_t)src | (uintptr_t)d) & 15) == 0) {
+    const int64_t n4 = n >> 2;
+    for (int64_t i = t0; i < n4; i += stride) reinterpret_cast<float4*>(d)[i] = reinterpret_cast<const float4*>(src)[i];
+    for (int64_t i = 4 * n4 + t0; i < n; i += stride) d[i] = src[i];
+  } else {
+    for (int64_t i = t0; i < n; i += stride) d[i] = src[i];
+  }
+}
+
 static int adam_launch(float* p, const float* g, float* m, float* v, int64_t n, int64_t* counter, int64_t step,
                        float lr, float beta1, float beta2, float eps, float wd, float grad_scale, void* stream,
                        const char* name) {
@@ -129,6 +158,29 @@ extern "C" {
 int scvi_adam_step(float* p, const float* g, float* m, float* v, int64_t n, int64_t step, float lr, float beta1,
                    float beta2, float eps, float weight_decay, float grad_scale, void* stream) {
   return scvi::adam_launch(p, g, m, v, n, nullptr, step, lr, beta1, beta2, eps, weight_decay, grad_scale, stream, "scvi_adam_step");
+}
+
+int scvi_gather_segments(const void* const* src, const int64_t* offs, const int64_t* ns, int count, float* dst,
+                         void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(count >= 0 && (count == 0 || (src && offs && ns && dst)), "scvi_gather_segments: bad argument");
+  for (int c0 = 0; c0 < count; c0 += GS_MAX) {
+    const int c = std::min(GS_MAX, count - c0);
+    GatherSegs s;
+    int64_t nmax = 0;
+    for (int i = 0; i < c; ++i) {
+      SCVI_REQUIRE(offs[c0 + i] >= 0 && ns[c0 + i] >= 0, "scvi_gather_segments: negative offset or length");
+      s.src[i] = (const float*)src[c0 + i];
+      s.off[i] = offs[c0 + i];
+      s.n[i] = ns[c0 + i];
+      nmax = std::max(nmax, ns[c0 + i]);
+    }
+    if (nmax == 0) continue;
+    dim3 grid((unsigned)std::min<int64_t>(cdiv(cdiv(nmax, 4), 256), 32), (unsigned)c);
+    gather_segments_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(s, dst);
+    SCVI_LAUNCH_CHECK("scvi_gather_segments");
+  }
+  return SCVI_OK;
 }
 
 int scvi_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, int64_t* step_counter, float lr,

@@ -113,15 +113,30 @@ __global__ void bn_bwd_reduce_kernel(const float* __restrict__ da, int64_t ldda,
   const float mu = mean[n], rs = rstd[n];
   const float g = gamma ? gamma[n] : 1.f, bt = beta ? beta[n] : 0.f;
   float s1 = 0.f, s2 = 0.f;
-  for (int r = 0; r < cnt; ++r) {
-    const int64_t b = r0 + r;
-    const float xhat = (y[b * ldy + n] - mu) * rs;
-    const float u = xhat * g + bt;
-    float d = da[b * ldda + n];
-    if (mask) d = mask[b * N + n] ? d * drop_scale : 0.f;
-    if (relu && !(u > 0.f)) d = 0.f;
-    s1 += d;
-    s2 = fmaf(d, xhat, s2);
+  // rows in groups of 8: all loads of a group are issued before the (strictly ordered) accumulation, so the few
+  // warps of a small-batch launch wait for one memory round trip per group instead of one per row
+  for (int rg = 0; rg < cnt; rg += 8) {
+    float yv[8], dv[8];
+    uint8_t mv[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const bool ok = rg + i < cnt;
+      const int64_t b = r0 + rg + (ok ? i : 0);
+      yv[i] = y[b * ldy + n];
+      dv[i] = da[b * ldda + n];
+      mv[i] = mask ? mask[b * N + n] : (uint8_t)1;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (rg + i >= cnt) break;
+      const float xhat = (yv[i] - mu) * rs;
+      const float u = xhat * g + bt;
+      float d = dv[i];
+      if (mask) d = mv[i] ? d * drop_scale : 0.f;
+      if (relu && !(u > 0.f)) d = 0.f;
+      s1 += d;
+      s2 = fmaf(d, xhat, s2);
+    }
   }
   part[((int64_t)blockIdx.x * 2 + 0) * N + n] = s1;
   part[((int64_t)blockIdx.x * 2 + 1) * N + n] = s2;

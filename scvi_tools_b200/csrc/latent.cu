@@ -115,6 +115,94 @@ __global__ void __launch_bounds__(LATB_THREADS)
   }
 }
 
+// ---- small per-row reductions of the semi-supervised / multi-modal losses ---------------------------------
+// out[r] = sum_d log N(value[r,d]; loc[r,d], scale[r,d])   (torch.distributions.Normal.log_prob(value).sum(-1);
+// `second` is the variance instead of the scale when is_var).  One thread per row, fixed summation order.
+__global__ void normal_logprob_sum_fwd_kernel(const float* __restrict__ value, const float* __restrict__ loc,
+                                              const float* __restrict__ second, int64_t R, int D, int is_var,
+                                              float* __restrict__ out) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  const float c = 0.9189385332046727f;  // log(sqrt(2 pi))
+  float acc = 0.f;
+  for (int d = 0; d < D; ++d) {
+    const float v = value[r * D + d], m = loc[r * D + d], s2 = second[r * D + d];
+    const float var = is_var ? s2 : s2 * s2;
+    const float log_scale = is_var ? 0.5f * logf(s2) : logf(s2);
+    const float df = v - m;
+    acc += -(df * df) / (2.f * var) - log_scale - c;
+  }
+  out[r] = acc;
+}
+
+// gradients of the above times gout[r]; any output may be NULL
+__global__ void normal_logprob_sum_bwd_kernel(const float* __restrict__ value, const float* __restrict__ loc,
+                                              const float* __restrict__ second, const float* __restrict__ gout,
+                                              int64_t R, int D, int is_var, float* __restrict__ dvalue,
+                                              float* __restrict__ dloc, float* __restrict__ dsecond) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= R * D) return;
+  const float g = gout[e / D];
+  const float v = value[e], m = loc[e], s2 = second[e];
+  const float df = v - m;
+  const float var = is_var ? s2 : s2 * s2;
+  const float dv = -g * df / var;
+  if (dvalue) dvalue[e] = dv;
+  if (dloc) dloc[e] = -dv;
+  if (dsecond) {
+    if (is_var)
+      dsecond[e] = g * (df * df / (2.f * var * var) - 0.5f / var);
+    else
+      dsecond[e] = g * (df * df / (var * s2) - 1.f / s2);
+  }
+}
+
+// KL(Categorical(probs = p) || Categorical(probs = q)) per row, torch's construction: both arguments are
+// normalised by their row sum, logits = log(clamp(probs, eps, 1 - eps)), t = p (log p - log q), t = inf where
+// q == 0, then t = 0 where p == 0, summed over the classes.  q: [R, C] (ldq = C) or one row for all (ldq = 0).
+// With dp != NULL the same pass writes gout[r] * d(kl[r]) / d(p[r, :]) (q carries no gradient).
+__global__ void categorical_kl_kernel(const float* __restrict__ p, const float* __restrict__ q, int64_t ldq,
+                                      int64_t R, int C, const float* __restrict__ gout, float* __restrict__ kl,
+                                      float* __restrict__ dp) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= R) return;
+  const float eps = 1.1920928955078125e-07f;  // torch.finfo(float32).eps
+  const float* pr = p + r * C;
+  const float* qr = q + r * ldq;
+  float sp = 0.f, sq = 0.f;
+  for (int c = 0; c < C; ++c) {
+    sp += pr[c];
+    sq += qr[c];
+  }
+  float acc = 0.f, dot = 0.f;
+  for (int c = 0; c < C; ++c) {
+    const float pn = pr[c] / sp, qn = qr[c] / sq;
+    const float lp = logf(fminf(fmaxf(pn, eps), 1.f - eps));
+    const float lq = logf(fminf(fmaxf(qn, eps), 1.f - eps));
+    float t = pn * (lp - lq);
+    if (qn == 0.f) t = INFINITY;
+    if (pn == 0.f) t = 0.f;
+    acc += t;
+    if (dp) {
+      float dpn = 0.f;
+      if (qn != 0.f && pn != 0.f) dpn = (lp - lq) + ((pn >= eps && pn <= 1.f - eps) ? 1.f : 0.f);
+      dot += dpn * pn;
+    }
+  }
+  if (kl) kl[r] = acc;
+  if (dp) {
+    const float g = gout[r] / sp;
+    for (int c = 0; c < C; ++c) {
+      const float pn = pr[c] / sp, qn = qr[c] / sq;
+      const float lp = logf(fminf(fmaxf(pn, eps), 1.f - eps));
+      const float lq = logf(fminf(fmaxf(qn, eps), 1.f - eps));
+      float dpn = 0.f;
+      if (qn != 0.f && pn != 0.f) dpn = (lp - lq) + ((pn >= eps && pn <= 1.f - eps) ? 1.f : 0.f);
+      dp[r * C + c] = g * (dpn - dot);
+    }
+  }
+}
+
 }  // namespace scvi
 
 extern "C" {
@@ -170,6 +258,40 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
     rc = launch_colsum(partb, ctas, 2 * L, 2 * L, segs, st, "scvi_latent_bwd(reduce b)");
     if (rc) return rc;
   }
+  return SCVI_OK;
+}
+
+int scvi_normal_logprob_sum_fwd(const float* value, const float* loc, const float* second, int64_t R, int64_t D,
+                                int is_var, float* out, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(R >= 0 && D > 0 && D <= 4096, "scvi_normal_logprob_sum_fwd: bad shape");
+  if (R == 0) return SCVI_OK;
+  SCVI_REQUIRE(value && loc && second && out, "scvi_normal_logprob_sum_fwd: NULL pointer");
+  normal_logprob_sum_fwd_kernel<<<(unsigned)cdiv(R, 128), 128, 0, (cudaStream_t)stream>>>(value, loc, second, R, (int)D, is_var, out);
+  SCVI_LAUNCH_CHECK("scvi_normal_logprob_sum_fwd");
+  return SCVI_OK;
+}
+
+int scvi_normal_logprob_sum_bwd(const float* value, const float* loc, const float* second, const float* gout,
+                                int64_t R, int64_t D, int is_var, float* dvalue, float* dloc, float* dsecond,
+                                void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(R >= 0 && D > 0 && D <= 4096, "scvi_normal_logprob_sum_bwd: bad shape");
+  if (R == 0) return SCVI_OK;
+  SCVI_REQUIRE(value && loc && second && gout, "scvi_normal_logprob_sum_bwd: NULL pointer");
+  normal_logprob_sum_bwd_kernel<<<(unsigned)cdiv(R * D, 256), 256, 0, (cudaStream_t)stream>>>(value, loc, second, gout, R, (int)D, is_var, dvalue, dloc, dsecond);
+  SCVI_LAUNCH_CHECK("scvi_normal_logprob_sum_bwd");
+  return SCVI_OK;
+}
+
+int scvi_categorical_kl(const float* p, const float* q, int64_t ldq, int64_t R, int64_t C, const float* gout,
+                        float* kl, float* dp, void* stream) {
+  using namespace scvi;
+  SCVI_REQUIRE(R >= 0 && C > 0 && C <= 65536 && (ldq == 0 || ldq >= C), "scvi_categorical_kl: bad shape");
+  if (R == 0) return SCVI_OK;
+  SCVI_REQUIRE(p && q && (kl || dp) && (!dp || gout), "scvi_categorical_kl: NULL pointer");
+  categorical_kl_kernel<<<(unsigned)cdiv(R, 128), 128, 0, (cudaStream_t)stream>>>(p, q, ldq, R, (int)C, gout, kl, dp);
+  SCVI_LAUNCH_CHECK("scvi_categorical_kl");
   return SCVI_OK;
 }
 }

@@ -266,12 +266,21 @@ __global__ void linear_dcov_kernel(const float* __restrict__ dy, int64_t lddy, i
   const int64_t b0 = (int64_t)blockIdx.x * COV_ROWS;
   const int64_t b1 = min(B, b0 + COV_ROWS);
   if (n < N) {
-    for (int64_t b = b0; b < b1; ++b) {
-      const float d = dy[b * lddy + n];
-      accs[n_extra * blockDim.x + n_local] += d;
-      for (int c = 0; c < n_cov; ++c) {
-        const int col = cov_cols[b * n_cov + c] - (int)K;
-        accs[col * blockDim.x + n_local] += d;
+    // rows in groups of 8, loads first (same accumulation order): one memory round trip per group
+    for (int64_t bg = b0; bg < b1; bg += 8) {
+      float dv[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dv[i] = dy[min(bg + i, b1 - 1) * lddy + n];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int64_t b = bg + i;
+        if (b >= b1) break;
+        const float d = dv[i];
+        accs[n_extra * blockDim.x + n_local] += d;
+        for (int c = 0; c < n_cov; ++c) {
+          const int col = cov_cols[b * n_cov + c] - (int)K;
+          accs[col * blockDim.x + n_local] += d;
+        }
       }
     }
     for (int c = 0; c <= n_extra; ++c)

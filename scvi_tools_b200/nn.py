@@ -44,7 +44,8 @@ def _next_mask(shape, p, device):
     if _FEED["drop_masks"]:
         m = _FEED["drop_masks"].pop(0)
         return m.to(device=device, dtype=torch.uint8)
-    return (torch.rand(shape, device=device) >= p).to(torch.uint8)
+    # keep with probability 1 - p: one Philox launch (graph-safe), no uniform -> compare -> cast chain
+    return torch.empty(shape, dtype=torch.uint8, device=device).bernoulli_(1.0 - p)
 
 
 def _next_noise(shape, device):

@@ -515,6 +515,89 @@ class DecoderNLL(torch.autograd.Function):
         return dh, dWs, dbs, dWp, dbp, dr, None, dlib, None, None, None
 
 
+# --------------------------------------------------------------------------------------
+# f1 / f2: per-row reductions of the semi-supervised / multi-modal losses
+# --------------------------------------------------------------------------------------
+class _NormalLogProbSum(torch.autograd.Function):
+    """Normal(loc, scale).log_prob(value).sum(-1) (`second` = scale, or the variance when is_var): one forward and
+    one backward launch where torch.distributions runs ~10 + ~20 element-wise kernels."""
+
+    @staticmethod
+    def forward(ctx, value, loc, second, is_var):
+        D = value.shape[-1]
+        lead = value.shape[:-1]
+        v = _check(value, "value").reshape(-1, D).contiguous()
+        m = _check(loc, "loc").reshape(-1, D).contiguous()
+        s2 = _check(second, "scale").reshape(-1, D).contiguous()
+        R = v.shape[0]
+        out = torch.empty(R, dtype=torch.float32, device=v.device)
+        call("scvi_normal_logprob_sum_fwd", _ptr(v), _ptr(m), _ptr(s2), R, D, int(is_var), _ptr(out), _stream())
+        ctx.save_for_backward(v, m, s2)
+        ctx.meta = (tuple(value.shape), bool(is_var))
+        return out.view(lead)
+
+    @staticmethod
+    def backward(ctx, g):
+        v, m, s2 = ctx.saved_tensors
+        shape, is_var = ctx.meta
+        R, D = v.shape
+        g = g.reshape(-1).contiguous().float()
+        nv, nm, ns = ctx.needs_input_grad[:3]
+        dv = torch.empty_like(v) if nv else None
+        dm = torch.empty_like(v) if nm else None
+        ds = torch.empty_like(v) if ns else None
+        if nv or nm or ns:
+            call("scvi_normal_logprob_sum_bwd", _ptr(v), _ptr(m), _ptr(s2), _ptr(g), R, D, int(is_var), _ptr(dv), _ptr(dm),
+                 _ptr(ds), _stream())
+        rs = lambda t: None if t is None else t.view(shape)  # noqa: E731
+        return rs(dv), rs(dm), rs(ds), None
+
+
+def normal_log_prob_sum(value, loc, scale=None, var=None):
+    """sum over the last axis of Normal(loc, scale or sqrt(var)).log_prob(value) (arguments broadcast together)."""
+    second, is_var = (var, True) if var is not None else (scale, False)
+    if not (value.shape == loc.shape == second.shape):
+        value, loc, second = torch.broadcast_tensors(value, loc, second)
+    return _NormalLogProbSum.apply(value, loc, second, is_var)
+
+
+class _CategoricalKL(torch.autograd.Function):
+    """kl_divergence(Categorical(probs=p), Categorical(probs=q)) over the last axis, q without gradient; the
+    gradient is produced by a second launch of the same kernel."""
+
+    @staticmethod
+    def forward(ctx, p, q):
+        C_ = p.shape[-1]
+        pe = _check(p, "probs").reshape(-1, C_).contiguous()
+        q = _check(q, "prior")
+        shared = q.numel() == C_
+        qe = q.reshape(-1).contiguous() if shared else q.expand(p.shape).reshape(-1, C_).contiguous()
+        R = pe.shape[0]
+        kl = torch.empty(R, dtype=torch.float32, device=pe.device)
+        call("scvi_categorical_kl", _ptr(pe), _ptr(qe), 0 if shared else C_, R, C_, None, _ptr(kl), None, _stream())
+        ctx.save_for_backward(pe, qe)
+        ctx.meta = (tuple(p.shape), shared)
+        return kl.view(p.shape[:-1])
+
+    @staticmethod
+    def backward(ctx, g):
+        pe, qe = ctx.saved_tensors
+        shape, shared = ctx.meta
+        R, C_ = pe.shape
+        if not ctx.needs_input_grad[0]:
+            return None, None
+        g = g.reshape(-1).contiguous().float()
+        dp = torch.empty_like(pe)
+        call("scvi_categorical_kl", _ptr(pe), _ptr(qe), 0 if shared else C_, R, C_, _ptr(g), None, _ptr(dp), _stream())
+        return dp.view(shape), None
+
+
+def categorical_kl(probs, prior_probs):
+    """KL(Categorical(probs) || Categorical(prior_probs)) per row, torch's construction (see scvi_categorical_kl);
+    `prior_probs`: one row of class probabilities or the shape of `probs`; it receives no gradient."""
+    return _CategoricalKL.apply(probs, prior_probs.detach())
+
+
 def decoder_params(h, Ws, bs, Wp, bp, library, want_scale=True, want_rate=True, want_dropout=True):
     """Materialise px_scale / px_rate / px_dropout for inference-time getters (no autograd)."""
     h = _rowmajor(h, "h")

@@ -4,8 +4,12 @@ multi-tensor Adam (`scvi_adam_step`) over a flat parameter / gradient / moment a
 
 The arena is laid out at the first `step()` over the parameters that hold a gradient by then (torch's Adam skips
 parameters whose `.grad` is None; so does this one -- and it refuses, loudly, a parameter that starts receiving
-gradient later, because its moments would have no slot).  Parameters and their `.grad` become views of the arena:
-autograd accumulates straight into it, `zero_grad()` is one memset.
+gradient later, because its moments would have no slot).  Parameters become views of the parameter arena.
+
+Gradients: `zero_grad()` sets every `.grad` to None, so autograd's first accumulation into a parameter KEEPS the
+tensor the backward kernel wrote (no `grad += new` launch per parameter, no arena memset); `step()` moves all of
+them into the flat gradient arena with ONE launch (`scvi_gather_segments`, pointer table by value in the launch
+parameters -- capturable), which is also the buffer the data-parallel all-reduce runs on.
 """
 
 from __future__ import annotations
@@ -67,21 +71,19 @@ class ArenaAdam:
         for (_, p), o in zip(params, offs, strict=True):
             n = p.numel()
             P[o : o + n].copy_(p.data.reshape(-1))
-            G[o : o + n].copy_(p.grad.reshape(-1))
             p.data = P[o : o + n].view(p.shape)
-            p.grad = G[o : o + n].view(p.shape)
         self.arena = {"p": P, "g": G, "m": torch.zeros_like(P), "v": torch.zeros_like(P), "step": 0, "offs": offs,
                       "counter": torch.zeros(2, dtype=torch.int64, device=dev)}
         self.names = [k for k, _ in params]
         taken = set(self.names)
         self._frozen = [k for k, p in self._named() if p.requires_grad and k not in taken]
+        n = len(params)
+        self._offs_c = (C.c_int64 * n)(*offs)
+        self._ns_c = (C.c_int64 * n)(*[p.numel() for _, p in params])
 
     def zero_grad(self):
-        if self.arena is not None:
-            self.arena["g"].zero_()
-        else:
-            for _, p in self._named():
-                p.grad = None
+        for _, p in self._named():
+            p.grad = None
 
     def step(self):
         if self.arena is None:
@@ -91,16 +93,20 @@ class ArenaAdam:
         for k in self._frozen:
             if named[k].grad is not None:
                 raise RuntimeError(f"parameter {k} received a gradient after the optimizer arena was laid out")
-        # autograd accumulates into the arena views in place; should it have swapped a `.grad` tensor, fold it back
-        for k, off in zip(self.names, a["offs"], strict=True):
-            p = named[k]
-            n = p.numel()
-            view = a["g"][off : off + n]
-            if p.grad is None:
-                view.zero_()
-            elif p.grad.data_ptr() != view.data_ptr():
-                view.copy_(p.grad.reshape(-1))
-                p.grad = view.view(p.shape)
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        # every gradient tensor -> its slot of the flat arena, one launch (a parameter without gradient: zeros)
+        n = len(self.names)
+        srcs = (C.c_void_p * n)()
+        keep = []
+        for i, k in enumerate(self.names):
+            g = named[k].grad
+            if g is None:
+                continue
+            if g.dtype != torch.float32 or not g.is_contiguous():
+                g = g.float().contiguous()
+                keep.append(g)
+            srcs[i] = g.data_ptr()
+        call("scvi_gather_segments", srcs, self._offs_c, self._ns_c, n, C.c_void_p(a["g"].data_ptr()), st)
         a["step"] += 1
         scale = 1.0
         if self.world > 1:
@@ -108,7 +114,6 @@ class ArenaAdam:
 
             dist.all_reduce(a["g"], group=self.pg)  # captured with the step when the plan runs as a CUDA graph
             scale = 1.0 / self.world
-        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         if self.capturable:
             call("scvi_adam_step_graph", C.c_void_p(a["p"].data_ptr()), C.c_void_p(a["g"].data_ptr()),
                  C.c_void_p(a["m"].data_ptr()), C.c_void_p(a["v"].data_ptr()), a["p"].numel(),

@@ -23,7 +23,7 @@ from typing import Literal
 import numpy as np
 import torch
 from torch import nn
-from torch.distributions import Categorical, Normal
+from torch.distributions import Normal
 from torch.distributions import kl_divergence as kl
 from torch.nn import functional as F
 
@@ -203,8 +203,9 @@ class SCANVAE(VAE):
         kl_divergence_z2 = getattr(qz2, "_b200_kl", None)  # KL(q || N(0, I)) from the latent-head kernel
         if kl_divergence_z2 is None:
             kl_divergence_z2 = kl(qz2, Normal(torch.zeros_like(qz2.loc), torch.ones_like(qz2.scale))).sum(dim=-1)
-        loss_z1_unweight = -Normal(pz1_m, torch.sqrt(pz1_v)).log_prob(z1s).sum(dim=-1)
-        loss_z1_weight = qz1.log_prob(z1).sum(dim=-1)
+        # Normal(.).log_prob(.).sum(-1): one launch each way instead of torch.distributions' element-wise chain
+        loss_z1_unweight = -ops.normal_log_prob_sum(z1s, pz1_m, var=pz1_v)
+        loss_z1_weight = ops.normal_log_prob_sum(z1, qz1.loc, scale=qz1.scale)
 
         probs = self.classifier(z1)
         if self.classifier.logits:
@@ -218,9 +219,8 @@ class SCANVAE(VAE):
             kl_divergence_z2_ = torch.transpose(kl_divergence_z2.view(z1.shape[0], self.n_labels, -1), -1, -2)
         reconst_loss = reconst_loss + loss_z1_weight + (loss_z1_unweight_ * probs).sum(dim=-1)
         kl_divergence = (kl_divergence_z2_ * probs).sum(dim=-1)
-        prior = (self.y_prior.repeat(probs.size(0), probs.size(1), 1) if probs.dim() == 3
-                 else self.y_prior.repeat(probs.size(0), 1))
-        kl_divergence = kl_divergence + kl(Categorical(probs=probs), Categorical(probs=prior))
+        # kl(Categorical(probs), Categorical(y_prior repeated over the cells)), torch's construction, fused
+        kl_divergence = kl_divergence + ops.categorical_kl(probs, self.y_prior)
 
         if not self.use_observed_lib_size:
             ql = inference_outputs[MODULE_KEYS.QL_KEY]
