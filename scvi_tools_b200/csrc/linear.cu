@@ -15,13 +15,70 @@ constexpr int LTHREADS = 256;
 // ---------------------------------------------------------------------------------------
 // forward
 // ---------------------------------------------------------------------------------------
-template <bool VEC>
+// epilogue of one 64 x 64 output tile held as acc[4][4] per thread (rows ty + 16 i, columns tx + 16 j):
+// bias + covariate columns (the one-hot GEMM as a column gather), store, per-tile BatchNorm statistics.
+// `smem`: at least LT * (LT + 1) floats, free to overwrite.
+__device__ __forceinline__ void linear_fwd_epilogue(float (&acc)[4][4], float* smem, int tid, int64_t r0, int64_t n0,
+                                                    int64_t B, int64_t N, const float* __restrict__ W, int64_t ldw,
+                                                    const float* __restrict__ bias,
+                                                    const int32_t* __restrict__ cov_cols, int n_cov,
+                                                    float* __restrict__ y, int64_t ldy,
+                                                    float* __restrict__ bn_partials) {
+  const int tx = tid & 15, ty = tid >> 4;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int64_t r = r0 + ty + 16 * i;
+    if (r >= B) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int64_t n = n0 + tx + 16 * j;
+      if (n >= N) continue;
+      float v = acc[i][j];
+      for (int c = 0; c < n_cov; ++c) v += W[n * ldw + cov_cols[r * n_cov + c]];
+      if (bias) v += bias[n];
+      acc[i][j] = v;
+      y[r * ldy + n] = v;
+    }
+  }
+  // per-tile BatchNorm statistics (mean, M2) over the valid rows of this tile
+  if (bn_partials != nullptr) {
+    float* ts = smem;  // [LT][LT+1] staging
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) ts[(ty + 16 * i) * (LT + 1) + tx + 16 * j] = acc[i][j];
+    __syncthreads();
+    if (tid < LT) {
+      const int64_t n = n0 + tid;
+      const int cnt = (int)min((int64_t)LT, B - r0);
+      if (n < N) {
+        float s = 0.f;
+        for (int r = 0; r < cnt; ++r) s += ts[r * (LT + 1) + tid];
+        const float mean = s / (float)cnt;
+        float m2 = 0.f;
+        for (int r = 0; r < cnt; ++r) {
+          const float d = ts[r * (LT + 1) + tid] - mean;
+          m2 = fmaf(d, d, m2);
+        }
+        bn_partials[((int64_t)blockIdx.x * 2 + 0) * N + n] = mean;
+        bn_partials[((int64_t)blockIdx.x * 2 + 1) * N + n] = m2;
+      }
+    }
+  }
+}
+
+// SPLIT: blockIdx.z owns the reduction range [z * k_per_split, +k_per_split) and leaves its raw partial tile in
+// part[z][B][N] (no epilogue); linear_fwd_finish_kernel sums the partials in z order and runs the epilogue.  For
+// few-cell minibatches with a long reduction (TOTALVI's encoder: 256 cells x 4100 inputs -> 256) the 64 x 64 tiles
+// alone would occupy a tenth of the SMs.
+template <bool VEC, bool SPLIT>
 __global__ void __launch_bounds__(LTHREADS)
     linear_fwd_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
                       int64_t K, int64_t N, const float* __restrict__ W, int64_t ldw,
                       const float* __restrict__ bias, const int32_t* __restrict__ cov_cols, int n_cov,
                       int flags, float* __restrict__ y, int64_t ldy, float* __restrict__ library,
-                      float* __restrict__ bn_partials) {
+                      float* __restrict__ bn_partials, int64_t k_per_split, float* __restrict__ part) {
   __shared__ __align__(16) float smem[2 * LT * LPAD + LT];
   float* xs = smem;              // [LT][LPAD]
   float* ws = smem + LT * LPAD;  // [LT][LPAD]
@@ -47,7 +104,9 @@ __global__ void __launch_bounds__(LTHREADS)
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
   float lib_part[2] = {0.f, 0.f};
 
-  for (int64_t k0 = 0; k0 < K; k0 += LK) {
+  const int64_t k_begin = SPLIT ? (int64_t)blockIdx.z * k_per_split : 0;
+  const int64_t k_end = SPLIT ? min(K, k_begin + k_per_split) : K;
+  for (int64_t k0 = k_begin; k0 < k_end; k0 += LK) {
     if (VEC) {
       // 64 rows x 8 float4 per operand; thread -> (row = tid/8 + 32*it, kq = tid%8)
       const int kq = tid & 7;
@@ -109,6 +168,21 @@ __global__ void __launch_bounds__(LTHREADS)
     __syncthreads();
   }
 
+  if (SPLIT) {
+    float* pz = part + (int64_t)blockIdx.z * B * N;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t r = r0 + ty + 16 * i;
+      if (r >= B) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int64_t n = n0 + tx + 16 * j;
+        if (n < N) pz[r * N + n] = acc[i][j];
+      }
+    }
+    return;
+  }
+
   // library = log(sum_g x)   (reference _vae.py:372)
   if (want_lib) {
     if (VEC) {
@@ -126,49 +200,32 @@ __global__ void __launch_bounds__(LTHREADS)
     }
   }
 
-  // epilogue: bias + covariate columns (the one-hot GEMM as a column gather)
+  linear_fwd_epilogue(acc, smem, tid, r0, n0, B, N, W, ldw, bias, cov_cols, n_cov, y, ldy, bn_partials);
+}
+
+// sums the split-K partial tiles in split order, then the common epilogue
+__global__ void __launch_bounds__(LTHREADS)
+    linear_fwd_finish_kernel(const float* __restrict__ part, int n_split, int64_t B, int64_t N,
+                             const float* __restrict__ W, int64_t ldw, const float* __restrict__ bias,
+                             const int32_t* __restrict__ cov_cols, int n_cov, float* __restrict__ y, int64_t ldy,
+                             float* __restrict__ bn_partials) {
+  __shared__ __align__(16) float smem[LT * (LT + 1)];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int64_t r0 = (int64_t)blockIdx.x * LT;
+  const int64_t n0 = (int64_t)blockIdx.y * LT;
+  float acc[4][4];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int64_t r = r0 + ty + 16 * i;
-    if (r >= B) continue;
+  for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int64_t n = n0 + tx + 16 * j;
-      if (n >= N) continue;
-      float v = acc[i][j];
-      for (int c = 0; c < n_cov; ++c) v += W[n * ldw + cov_cols[r * n_cov + c]];
-      if (bias) v += bias[n];
+      const int64_t r = r0 + ty + 16 * i, n = n0 + tx + 16 * j;
+      float v = 0.f;
+      if (r < B && n < N)
+        for (int z = 0; z < n_split; ++z) v += part[((int64_t)z * B + r) * N + n];
       acc[i][j] = v;
-      y[r * ldy + n] = v;
     }
-  }
-
-  // per-tile BatchNorm statistics (mean, M2) over the valid rows of this tile
-  if (bn_partials != nullptr) {
-    float* ts = smem;  // [LT][LT+1] staging, reuses xs/ws (>= 64*65 floats)
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-#pragma unroll
-      for (int j = 0; j < 4; ++j) ts[(ty + 16 * i) * (LT + 1) + tx + 16 * j] = acc[i][j];
-    __syncthreads();
-    if (tid < LT) {
-      const int64_t n = n0 + tid;
-      const int cnt = (int)min((int64_t)LT, B - r0);
-      if (n < N) {
-        float s = 0.f;
-        for (int r = 0; r < cnt; ++r) s += ts[r * (LT + 1) + tid];
-        const float mean = s / (float)cnt;
-        float m2 = 0.f;
-        for (int r = 0; r < cnt; ++r) {
-          const float d = ts[r * (LT + 1) + tid] - mean;
-          m2 = fmaf(d, d, m2);
-        }
-        bn_partials[((int64_t)blockIdx.x * 2 + 0) * N + n] = mean;
-        bn_partials[((int64_t)blockIdx.x * 2 + 1) * N + n] = m2;
-      }
-    }
-  }
+  linear_fwd_epilogue(acc, smem, tid, r0, n0, B, N, W, ldw, bias, cov_cols, n_cov, y, ldy, bn_partials);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -309,10 +366,12 @@ __global__ void linear_dw_scatter_kernel(const float* __restrict__ tot, int64_t 
   dW[(e / K) * ldw + e % K] = tot[e];
 }
 
-// dx[b, k] = sum_n dy[b, n] * W[n, k]   (k < K)
+// dx[b, k] = sum_n dy[b, n] * W[n, k]   (k < K).  gridDim.z > 1: blockIdx.z reduces over its own range of
+// n_per_split outputs into slab z of `dx` (slab stride B * lddx); the caller sums the slabs in order.
 __global__ void __launch_bounds__(LTHREADS)
     linear_dx_kernel(const float* __restrict__ dy, int64_t lddy, int64_t B, int64_t K, int64_t N,
-                     const float* __restrict__ W, int64_t ldw, float* __restrict__ dx, int64_t lddx) {
+                     const float* __restrict__ W, int64_t ldw, float* __restrict__ dx, int64_t lddx,
+                     int64_t n_per_split) {
   __shared__ float dys[LT][LK + 1];  // [b][n]
   __shared__ float wsm[LK][LT + 1];  // [n][k]
   const int tid = threadIdx.x;
@@ -324,7 +383,10 @@ __global__ void __launch_bounds__(LTHREADS)
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  for (int64_t nn0 = 0; nn0 < N; nn0 += LK) {
+  const int64_t n_begin = (int64_t)blockIdx.z * n_per_split;
+  const int64_t n_end = min(N, n_begin + n_per_split);
+  dx += (int64_t)blockIdx.z * B * lddx;
+  for (int64_t nn0 = n_begin; nn0 < n_end; nn0 += LK) {
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int e = tid + LTHREADS * it;  // 0..2047
@@ -366,6 +428,33 @@ __global__ void __launch_bounds__(LTHREADS)
   }
 }
 
+// split-K plan of the forward GEMM: only when the 64 x 64 tiles alone would leave most SMs idle and the reduction
+// is long enough to share out.  Returns the number of splits (1 = none) and the (LK-aligned) range per split.
+static int64_t fwd_splits(int64_t B, int64_t K, int64_t N, int flags, int64_t* k_per_split) {
+  const int64_t tiles = cdiv(B, LT) * cdiv(N, LT);
+  const int64_t chunks = cdiv(K, LK);
+  *k_per_split = K;
+  if ((flags & SCVI_LIN_LIBRARY) || tiles >= 74 || chunks < 16) return 1;
+  int64_t s = std::min<int64_t>(std::min<int64_t>(cdiv(2 * 148, tiles), chunks / 4), 32);
+  if (s <= 1) return 1;
+  const int64_t kps = cdiv(chunks, s) * LK;
+  *k_per_split = kps;
+  return cdiv(K, kps);
+}
+
+// the same for dx = dy W (reduction over the N outputs)
+static int64_t dx_splits(int64_t B, int64_t K, int64_t N, int64_t* n_per_split) {
+  const int64_t tiles = cdiv(B, LT) * cdiv(K, LT);
+  const int64_t chunks = cdiv(N, LK);
+  *n_per_split = N;
+  if (tiles >= 74 || chunks < 16) return 1;
+  int64_t s = std::min<int64_t>(std::min<int64_t>(cdiv(2 * 148, tiles), chunks / 4), 32);
+  if (s <= 1) return 1;
+  const int64_t nps = cdiv(chunks, s) * LK;
+  *n_per_split = nps;
+  return cdiv(N, nps);
+}
+
 static int64_t dw_splits(int64_t B, int64_t K, int64_t N) {
   const int64_t tiles = cdiv(K, LT) * cdiv(N, LT);
   int64_t s = cdiv(4 * 148, tiles);                  // aim for ~4 CTAs per SM
@@ -385,7 +474,10 @@ int tc_enc_dw(const void* x, int64_t ldx, const int64_t* row_idx, int64_t B, int
 extern "C" {
 
 int64_t scvi_linear_fwd_ws_bytes(int64_t B, int64_t K, int64_t N, int flags) {
-  return ((flags & SCVI_LIN_TC) && N == 128) ? scvi::tc_enc_fwd_ws_bytes(B, K) : 0;
+  int64_t kps;
+  const int64_t S = scvi::fwd_splits(B, K, N, flags, &kps);
+  const int64_t split = S > 1 ? 4 * S * B * N : 0;
+  return std::max<int64_t>(((flags & SCVI_LIN_TC) && N == 128) ? scvi::tc_enc_fwd_ws_bytes(B, K) : 0, split);
 }
 
 int scvi_linear_fwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
@@ -421,21 +513,44 @@ int scvi_linear_fwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t
   const bool vec = (K % 4 == 0) && (ldx % 4 == 0) && (ldw % 4 == 0) && ((uintptr_t)x % 16 == 0) &&
                    ((uintptr_t)W % 16 == 0);
   dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(N, LT));
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t kps;
+  const int64_t S = ws ? fwd_splits(B, K, N, flags, &kps) : 1;  // no workspace (a caller that did not ask): no split
+  if (S > 1) {
+    float* part = (float*)ws;
+    dim3 sgrid(grid.x, grid.y, (unsigned)S);
+    if (vec)
+      linear_fwd_kernel<true, true><<<sgrid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials, kps, part);
+    else
+      linear_fwd_kernel<false, true><<<sgrid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials, kps, part);
+    SCVI_LAUNCH_CHECK("scvi_linear_fwd(split)");
+    linear_fwd_finish_kernel<<<grid, LTHREADS, 0, st>>>(part, (int)S, B, N, W, ldw, bias, cov_cols, n_cov, y, ldy, bn_partials);
+    SCVI_LAUNCH_CHECK("scvi_linear_fwd(finish)");
+    return SCVI_OK;
+  }
   if (vec)
-    linear_fwd_kernel<true><<<grid, LTHREADS, 0, (cudaStream_t)stream>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials);
+    linear_fwd_kernel<true, false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials, K, nullptr);
   else
-    linear_fwd_kernel<false><<<grid, LTHREADS, 0, (cudaStream_t)stream>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials);
+    linear_fwd_kernel<false, false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, W, ldw, bias, cov_cols, n_cov, flags, y, ldy, library, bn_partials, K, nullptr);
   SCVI_LAUNCH_CHECK("scvi_linear_fwd");
   return SCVI_OK;
 }
 
-int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols) {
+// everything but the dx slabs, which sit behind it
+static int64_t linear_bwd_base_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols) {
   using namespace scvi;
   const int64_t S = dw_splits(B, K, N);
   const int64_t n_extra = n_w_cols - K;
   const int64_t cov = 4 * (cdiv(B, COV_ROWS) + 1) * (n_extra + 1) * N + 256;
   const int64_t ffma = 4 * (S * N * K + N * K) + cov;
-  return N == 128 ? std::max<int64_t>(ffma, tc_enc_dw_ws_bytes(B, K) + cov) : ffma;
+  const int64_t base = N == 128 ? std::max<int64_t>(ffma, tc_enc_dw_ws_bytes(B, K) + cov) : ffma;
+  return (base + 255) / 256 * 256;
+}
+
+int64_t scvi_linear_bwd_ws_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols) {
+  int64_t nps;
+  const int64_t Sx = scvi::dx_splits(B, K, N, &nps);
+  return linear_bwd_base_bytes(B, K, N, n_w_cols) + (Sx > 1 ? 4 * Sx * B * K : 0);
 }
 
 int scvi_linear_bwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t B, int64_t K, int64_t N,
@@ -511,8 +626,19 @@ int scvi_linear_bwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t
   }
   if (dx) {
     dim3 grid((unsigned)cdiv(B, LT), (unsigned)cdiv(K, LT));
-    linear_dx_kernel<<<grid, LTHREADS, 0, st>>>(dy, lddy, B, K, N, W, ldw, dx, lddx);
-    SCVI_LAUNCH_CHECK("scvi_linear_bwd(dx)");
+    int64_t nps;
+    const int64_t Sx = (lddx == K) ? dx_splits(B, K, N, &nps) : 1;  // the slab reduction writes a contiguous dx
+    if (Sx > 1) {
+      float* xslabs = (float*)((uint8_t*)ws + linear_bwd_base_bytes(B, K, N, n_w_cols));
+      grid.z = (unsigned)Sx;
+      linear_dx_kernel<<<grid, LTHREADS, 0, st>>>(dy, lddy, B, K, N, W, ldw, xslabs, K, nps);
+      SCVI_LAUNCH_CHECK("scvi_linear_bwd(dx split)");
+      int rc = launch_colsum(xslabs, Sx, B * K, B * K, colsum_seg1(dx, B * K), st, "scvi_linear_bwd(dx reduce)");
+      if (rc) return rc;
+    } else {
+      linear_dx_kernel<<<grid, LTHREADS, 0, st>>>(dy, lddy, B, K, N, W, ldw, dx, lddx, N);
+      SCVI_LAUNCH_CHECK("scvi_linear_bwd(dx)");
+    }
   }
   return SCVI_OK;
 }

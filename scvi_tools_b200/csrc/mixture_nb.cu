@@ -14,6 +14,7 @@
 namespace scvi {
 
 constexpr int MX_THREADS = 128;
+constexpr int MX_RG = 8;  // row groups per 64-row tile in the backward kernel (blockDim.y)
 
 struct MixTerms {
   float l1, l2;  // component log-likelihoods
@@ -39,10 +40,10 @@ __global__ void __launch_bounds__(MX_THREADS)
     mixture_fwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu1, int64_t ld1,
                        const float* __restrict__ mu2, int64_t ld2, const float* __restrict__ theta, int64_t theta_ld,
                        const float* __restrict__ pi, int64_t ldpi, int64_t B, int64_t P, float eps,
-                       float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support) {
+                       float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support, int row_tile) {
   const int64_t g = (int64_t)blockIdx.x * MX_THREADS + threadIdx.x;
-  const int64_t r0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
-  const int64_t r1 = min(r0 + (int64_t)SCVI_BN_TILE, B);
+  const int64_t r0 = (int64_t)blockIdx.y * row_tile;
+  const int64_t r1 = min(r0 + (int64_t)row_tile, B);
   if (g >= P) return;
   GeneConst c;
   if (THETA_PER_COL) c = make_gene_const(theta[g], eps);
@@ -59,20 +60,24 @@ __global__ void __launch_bounds__(MX_THREADS)
 }
 
 template <bool THETA_PER_COL>
-__global__ void __launch_bounds__(MX_THREADS)
+__global__ void __launch_bounds__(MX_THREADS * MX_RG)
     mixture_bwd_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu1, int64_t ld1,
                        const float* __restrict__ mu2, int64_t ld2, const float* __restrict__ theta, int64_t theta_ld,
                        const float* __restrict__ pi, int64_t ldpi, const float* __restrict__ gout, int64_t ldg,
                        int64_t B, int64_t P, float eps, float* __restrict__ dmu1, float* __restrict__ dmu2,
                        float* __restrict__ dtheta, float* __restrict__ dpi) {
+  // blockDim = (MX_THREADS, MX_RG): row group ty owns SCVI_BN_TILE / MX_RG consecutive rows of the tile; the
+  // per-tile dtheta partial is the sum of the groups' partials in group order (fixed)
+  __shared__ float dth_sh[MX_RG][MX_THREADS];
   const int64_t g = (int64_t)blockIdx.x * MX_THREADS + threadIdx.x;
-  const int64_t r0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
-  const int64_t r1 = min(r0 + (int64_t)SCVI_BN_TILE, B);
-  if (g >= P) return;
+  const int64_t t0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
+  const int64_t r0 = min(t0 + (int64_t)threadIdx.y * (SCVI_BN_TILE / MX_RG), B);
+  const int64_t r1 = min(r0 + (int64_t)(SCVI_BN_TILE / MX_RG), B);
+  const bool col_ok = g < P;
   GeneConst c;
-  if (THETA_PER_COL) c = make_gene_const(theta[g], eps);
+  if (THETA_PER_COL && col_ok) c = make_gene_const(theta[g], eps);
   float dth_acc = 0.f;
-  for (int64_t r = r0; r < r1; ++r) {
+  for (int64_t r = r0; col_ok && r < r1; ++r) {
     const float xv = x[r * ldx + g];
     const float m1 = mu1[r * ld1 + g], m2 = mu2[r * ld2 + g];
     if (!THETA_PER_COL) c = make_gene_const(theta[r * theta_ld + g], eps);
@@ -96,7 +101,16 @@ __global__ void __launch_bounds__(MX_THREADS)
         dtheta[r * P + g] = v;
     }
   }
-  if (THETA_PER_COL && dtheta) dtheta[(int64_t)blockIdx.y * P + g] = dth_acc;  // per-row-tile partial
+  if (THETA_PER_COL && dtheta) {  // per-row-tile partial
+    dth_sh[threadIdx.y][threadIdx.x] = dth_acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && col_ok) {
+      float t = 0.f;
+#pragma unroll
+      for (int q = 0; q < MX_RG; ++q) t += dth_sh[q][threadIdx.x];
+      dtheta[(int64_t)blockIdx.y * P + g] = t;
+    }
+  }
 }
 
 }  // namespace scvi
@@ -113,12 +127,17 @@ int scvi_mixture_nb_logprob_fwd(const float* x, int64_t ldx, const float* mu1, i
                    (theta_ld == 0 || theta_ld >= P),
                "scvi_mixture_nb_logprob_fwd: bad shape");
   if (B == 0 || P == 0) return SCVI_OK;
-  dim3 grid((unsigned)cdiv(P, MX_THREADS), (unsigned)cdiv(B, SCVI_BN_TILE));
+  // a thread walks `row_tile` rows of its column: short tiles when 64-row tiles would leave most SMs without work
+  // (totalVI: 256 cells x ~100 proteins)
+  const int gx = (int)cdiv(P, MX_THREADS);
+  const int row_tile = (gx * cdiv(B, SCVI_BN_TILE) >= 148) ? SCVI_BN_TILE : 4;
+  dim3 grid((unsigned)gx, (unsigned)cdiv(B, row_tile));
+  SCVI_REQUIRE(grid.y <= 65535, "scvi_mixture_nb_logprob_fwd: B too large for one launch");
   cudaStream_t st = (cudaStream_t)stream;
   if (theta_ld == 0)
-    mixture_fwd_kernel<true><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, 0, pi, ldpi, B, P, eps, out, ldo, bad_support);
+    mixture_fwd_kernel<true><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, 0, pi, ldpi, B, P, eps, out, ldo, bad_support, row_tile);
   else
-    mixture_fwd_kernel<false><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, theta_ld, pi, ldpi, B, P, eps, out, ldo, bad_support);
+    mixture_fwd_kernel<false><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, theta_ld, pi, ldpi, B, P, eps, out, ldo, bad_support, row_tile);
   SCVI_LAUNCH_CHECK("scvi_mixture_nb_logprob_fwd");
   return SCVI_OK;
 }
@@ -135,10 +154,11 @@ int scvi_mixture_nb_logprob_bwd(const float* x, int64_t ldx, const float* mu1, i
   if (B == 0 || P == 0) return SCVI_OK;
   dim3 grid((unsigned)cdiv(P, MX_THREADS), (unsigned)cdiv(B, SCVI_BN_TILE));
   cudaStream_t st = (cudaStream_t)stream;
+  const dim3 block(MX_THREADS, MX_RG);
   if (theta_ld == 0)
-    mixture_bwd_kernel<true><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, 0, pi, ldpi, gout, ldg, B, P, eps, dmu1, dmu2, dtheta, dpi);
+    mixture_bwd_kernel<true><<<grid, block, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, 0, pi, ldpi, gout, ldg, B, P, eps, dmu1, dmu2, dtheta, dpi);
   else
-    mixture_bwd_kernel<false><<<grid, MX_THREADS, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, theta_ld, pi, ldpi, gout, ldg, B, P, eps, dmu1, dmu2, dtheta, dpi);
+    mixture_bwd_kernel<false><<<grid, block, 0, st>>>(x, ldx, mu1, ldmu1, mu2, ldmu2, theta, theta_ld, pi, ldpi, gout, ldg, B, P, eps, dmu1, dmu2, dtheta, dpi);
   SCVI_LAUNCH_CHECK("scvi_mixture_nb_logprob_bwd");
   return SCVI_OK;
 }

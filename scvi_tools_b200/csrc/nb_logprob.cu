@@ -98,13 +98,14 @@ template <bool ZINB>
 __global__ void __launch_bounds__(LP4_THREADS, 8)
     logprob_fwd4_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
                         const float* __restrict__ theta, const float* __restrict__ pi, int64_t ldpi, int64_t B,
-                        int64_t G, float eps, float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support) {
+                        int64_t G, float eps, float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support,
+                        int row_tile) {
   __shared__ float s_lgx1[fm::LGX1_TABLE];
   for (int i = threadIdx.x; i < fm::LGX1_TABLE; i += LP4_THREADS) s_lgx1[i] = lgammaf((float)i + 1.f);
   __syncthreads();
   const int64_t g = ((int64_t)blockIdx.x * LP4_THREADS + threadIdx.x) * 4;
-  const int64_t r0 = (int64_t)blockIdx.y * SCVI_BN_TILE;
-  const int64_t r1 = min(r0 + (int64_t)SCVI_BN_TILE, B);
+  const int64_t r0 = (int64_t)blockIdx.y * row_tile;
+  const int64_t r1 = min(r0 + (int64_t)row_tile, B);
   if (g >= G) return;  // G % 4 == 0 on this path
   const float4 th = *reinterpret_cast<const float4*>(theta + g);
   const fm::GeneK k0 = lp_gene_k(th.x, eps), k1 = lp_gene_k(th.y, eps), k2 = lp_gene_k(th.z, eps), k3 = lp_gene_k(th.w, eps);
@@ -186,7 +187,10 @@ static int launch_fwd(const float* x, int64_t ldx, const float* mu, int64_t ldmu
   if (theta_ld == 0 && G % 4 == 0 && ldx % 4 == 0 && ldmu % 4 == 0 && ldo % 4 == 0 && (!ZINB || ldpi % 4 == 0) && lp_al16(x) &&
       lp_al16(mu) && lp_al16(theta) && lp_al16(out) && lp_al16(pi)) {
     grid.x = (unsigned)cdiv(G / 4, LP4_THREADS);
-    logprob_fwd4_kernel<ZINB><<<grid, LP4_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, pi, ldpi, B, G, eps, out, ldo, bad);
+    // few cells (totalVI / SCANVI minibatches): 16-row tiles, so that the launch still covers the SMs
+    const int row_tile = ((int64_t)grid.x * grid.y >= 2 * 148) ? SCVI_BN_TILE : 16;
+    grid.y = (unsigned)cdiv(B, row_tile);
+    logprob_fwd4_kernel<ZINB><<<grid, LP4_THREADS, 0, (cudaStream_t)stream>>>(x, ldx, mu, ldmu, theta, pi, ldpi, B, G, eps, out, ldo, bad, row_tile);
     SCVI_LAUNCH_CHECK(name);
     return SCVI_OK;
   }

@@ -127,3 +127,78 @@ def test_arena_adam_matches_torch_adam():
     opt.step()
     o = offs[2]
     assert float(opt.arena["g"][o : o + net[2].weight.numel()].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("B,K,N,ncov", [(256, 4100, 256, 0), (256, 276, 4000, 3), (100, 2049, 130, 2), (64, 7, 5, 1)])
+def test_fused_linear_few_cells_long_reduction(B, K, N, ncov):
+    """FusedLinear against torch on shapes whose 64 x 64 tiles alone would not fill the GPU: the forward splits the
+    K reduction (partial tiles + finish kernel), dx splits the N reduction (slabs + ordered sum).  BatchNorm tile
+    statistics, covariate columns and all three gradients included."""
+    from scvi_tools_b200 import _lib, ops
+
+    g = torch.Generator(device="cuda").manual_seed(B + K)
+    x = torch.randn(B, K, device="cuda", generator=g).requires_grad_()
+    W = (torch.randn(N, K + ncov, device="cuda", generator=g) / K**0.5).requires_grad_()
+    b = torch.randn(N, device="cuda", generator=g).requires_grad_()
+    cov = torch.randint(0, max(ncov, 1), (B, 1), device="cuda", generator=g)
+    cols = (K + cov).to(torch.int32) if ncov else None
+    w = torch.randn(B, N, device="cuda", generator=g)
+    y, part, _ = ops.FusedLinear.apply(x, W, b, cols, K, 0, None, True)
+    gx, gW, gb = torch.autograd.grad((y * w).sum(), [x, W, b])
+    x64, W64 = x.detach().double(), W.detach().double()
+    ref = x64 @ W64[:, :K].t() + b.detach().double()
+    if ncov:
+        ref = ref + W64[:, K:].t()[cov.view(-1)]
+    scale = float(ref.abs().max())
+    assert float((y.double() - ref).abs().max()) <= 2e-6 * scale * K**0.5
+    w64 = w.double()
+    rx = w64 @ W64[:, :K]
+    assert float((gx.double() - rx).abs().max()) <= 2e-6 * float(rx.abs().max()) * N**0.5
+    rW = torch.zeros_like(W64)
+    rW[:, :K] = w64.t() @ x64
+    if ncov:
+        oh = torch.nn.functional.one_hot(cov.view(-1), ncov).double()
+        rW[:, K:] = w64.t() @ oh
+    assert float((gW.double() - rW).abs().max()) <= 2e-6 * float(rW.abs().max()) * B**0.5
+    assert float((gb.double() - w64.sum(0)).abs().max()) <= 2e-6 * float(w64.sum(0).abs().max()) * B**0.5
+    # tile statistics of the (summed) output: mean and M2 per 64-row tile
+    T = (B + _lib.BN_TILE - 1) // _lib.BN_TILE
+    assert part.shape == (T, 2, N)
+    for t in range(T):
+        rows = y[t * _lib.BN_TILE : (t + 1) * _lib.BN_TILE].double()
+        m = rows.mean(0)
+        assert torch.allclose(part[t, 0].double(), m, rtol=1e-5, atol=1e-5 * scale)
+        assert torch.allclose(part[t, 1].double(), ((rows - m) ** 2).sum(0), rtol=1e-4, atol=1e-5 * scale**2)
+
+
+@pytest.mark.parametrize("B,P", [(256, 100), (70, 130), (1, 3)])
+def test_small_batch_likelihood_tiles(B, P):
+    """The few-cell launch geometry of the stand-alone likelihood kernels (short row tiles in the forward, row groups
+    in the mixture backward) against torch.distributions-style float64 formulas via the existing wide-batch path:
+    the same op evaluated on the rows repeated to a large batch must agree bit for bit in the forward, and the
+    per-column dispersion gradient to rounding."""
+    from scvi_tools_b200 import ops
+
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.poisson(3 * torch.rand(B, P, device="cuda", generator=g))
+    m1 = (torch.rand(B, P, device="cuda", generator=g) * 5 + 0.1).requires_grad_()
+    m2 = (torch.rand(B, P, device="cuda", generator=g) * 50 + 1).requires_grad_()
+    th = (torch.rand(P, device="cuda", generator=g) * 3 + 0.2).requires_grad_()
+    pi = torch.randn(B, P, device="cuda", generator=g).requires_grad_()
+    rep = 20000 // B + 1  # tall enough for the 64-row tiles
+
+    def run(fn, args, reps):
+        big = [a.repeat(reps, 1) if a.dim() == 2 else a for a in args]
+        return fn(*big)
+
+    for fn, args in ((ops.mixture_nb_log_prob, (x, m1, m2, th, pi)), (ops.nb_log_prob, (x, m1, th)),
+                     (ops.zinb_log_prob, (x, m1, th, pi))):
+        if fn is not ops.mixture_nb_log_prob and P % 4:
+            continue  # the vectorised kernels need 16-byte rows; the scalar path has one geometry
+        small = fn(*args)
+        tall = run(fn, args, rep)
+        assert torch.equal(tall[:B], small), fn.__name__
+        gs = torch.autograd.grad(small.sum(), [a for a in args if a.requires_grad])
+        gt = torch.autograd.grad(tall[:B].sum(), [a for a in args if a.requires_grad])
+        for a, b_ in zip(gs, gt, strict=True):
+            assert torch.allclose(a, b_, rtol=1e-5, atol=1e-6), fn.__name__
