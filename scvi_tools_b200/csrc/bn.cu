@@ -101,45 +101,61 @@ __global__ void bn_act_drop_fwd_kernel(const float* __restrict__ y, int64_t ldy,
 
 // ---- backward ------------------------------------------------------------------------------
 // du = da * keep*scale * 1[u>0];  partial column sums of du and du*xhat per row tile
-__global__ void bn_bwd_reduce_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y,
-                                     int64_t ldy, int64_t B, int64_t N, const float* __restrict__ mean,
-                                     const float* __restrict__ rstd, const float* __restrict__ gamma,
-                                     const float* __restrict__ beta, int relu, const uint8_t* __restrict__ mask,
-                                     float drop_scale, float* __restrict__ part /*[T][2][N]*/) {
-  const int64_t n = (int64_t)blockIdx.y * blockDim.x + threadIdx.x;
-  const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE;
-  const int cnt = (int)min((int64_t)SCVI_BN_TILE, B - r0);
-  if (n >= N) return;
-  const float mu = mean[n], rs = rstd[n];
-  const float g = gamma ? gamma[n] : 1.f, bt = beta ? beta[n] : 0.f;
+constexpr int BNR_RG = 4;  // row groups per 64-row tile (blockDim.y)
+__global__ void __launch_bounds__(64 * BNR_RG)
+    bn_bwd_reduce_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y, int64_t ldy,
+                         int64_t B, int64_t N, const float* __restrict__ mean, const float* __restrict__ rstd,
+                         const float* __restrict__ gamma, const float* __restrict__ beta, int relu,
+                         const uint8_t* __restrict__ mask, float drop_scale, float* __restrict__ part /*[T][2][N]*/) {
+  // blockDim = (64 columns, BNR_RG row groups): group ty walks rows ty * 16 .. + 16 of the tile, eight rows per
+  // memory round trip; the tile's partial is the sum of the groups' partials in group order (fixed).  Few-cell
+  // minibatches launch a handful of these CTAs, so the per-thread serial chain is what sets the kernel's duration.
+  __shared__ float sh[BNR_RG][2][64];
+  constexpr int RPG = SCVI_BN_TILE / BNR_RG;
+  const int64_t n = (int64_t)blockIdx.y * 64 + threadIdx.x;
+  const int64_t r0 = (int64_t)blockIdx.x * SCVI_BN_TILE + (int64_t)threadIdx.y * RPG;
+  const int cnt = (int)max((int64_t)0, min((int64_t)RPG, B - r0));
+  const bool col_ok = n < N;
   float s1 = 0.f, s2 = 0.f;
-  // rows in groups of 8: all loads of a group are issued before the (strictly ordered) accumulation, so the few
-  // warps of a small-batch launch wait for one memory round trip per group instead of one per row
-  for (int rg = 0; rg < cnt; rg += 8) {
-    float yv[8], dv[8];
-    uint8_t mv[8];
+  if (col_ok && cnt > 0) {
+    const float mu = mean[n], rs = rstd[n];
+    const float g = gamma ? gamma[n] : 1.f, bt = beta ? beta[n] : 0.f;
+    for (int rg = 0; rg < cnt; rg += 8) {
+      float yv[8], dv[8];
+      uint8_t mv[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const bool ok = rg + i < cnt;
-      const int64_t b = r0 + rg + (ok ? i : 0);
-      yv[i] = y[b * ldy + n];
-      dv[i] = da[b * ldda + n];
-      mv[i] = mask ? mask[b * N + n] : (uint8_t)1;
-    }
+      for (int i = 0; i < 8; ++i) {
+        const int64_t b = r0 + min(rg + i, cnt - 1);
+        yv[i] = y[b * ldy + n];
+        dv[i] = da[b * ldda + n];
+        mv[i] = mask ? mask[b * N + n] : (uint8_t)1;
+      }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      if (rg + i >= cnt) break;
-      const float xhat = (yv[i] - mu) * rs;
-      const float u = xhat * g + bt;
-      float d = dv[i];
-      if (mask) d = mv[i] ? d * drop_scale : 0.f;
-      if (relu && !(u > 0.f)) d = 0.f;
-      s1 += d;
-      s2 = fmaf(d, xhat, s2);
+      for (int i = 0; i < 8; ++i) {  // straight-line: a row past the group contributes an exact zero
+        const float xhat = (yv[i] - mu) * rs;
+        const float u = xhat * g + bt;
+        float d = dv[i];
+        if (mask) d = mv[i] ? d * drop_scale : 0.f;
+        if (relu && !(u > 0.f)) d = 0.f;
+        if (rg + i >= cnt) d = 0.f;
+        s1 += d;
+        s2 = fmaf(d, xhat, s2);
+      }
     }
   }
-  part[((int64_t)blockIdx.x * 2 + 0) * N + n] = s1;
-  part[((int64_t)blockIdx.x * 2 + 1) * N + n] = s2;
+  sh[threadIdx.y][0][threadIdx.x] = s1;
+  sh[threadIdx.y][1][threadIdx.x] = s2;
+  __syncthreads();
+  if (threadIdx.y == 0 && col_ok) {
+    float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+    for (int q = 0; q < BNR_RG; ++q) {
+      t1 += sh[q][0][threadIdx.x];
+      t2 += sh[q][1][threadIdx.x];
+    }
+    part[((int64_t)blockIdx.x * 2 + 0) * N + n] = t1;
+    part[((int64_t)blockIdx.x * 2 + 1) * N + n] = t2;
+  }
 }
 
 __global__ void bn_bwd_apply_kernel(const float* __restrict__ da, int64_t ldda, const float* __restrict__ y,
@@ -265,7 +281,7 @@ int scvi_bn_act_drop_bwd(const float* da, int64_t ldda, const float* y, int64_t 
   float* sums = part + T * 2 * N;
   if (mean) {
     dim3 grid((unsigned)T, (unsigned)cdiv(N, 64));
-    bn_bwd_reduce_kernel<<<grid, 64, 0, st>>>(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask,
+    bn_bwd_reduce_kernel<<<grid, dim3(64, BNR_RG), 0, st>>>(da, ldda, y, ldy, B, N, mean, rstd, gamma, beta, relu, drop_mask,
                                               drop_scale, part);
     SCVI_LAUNCH_CHECK("scvi_bn_act_drop_bwd(reduce)");
     // sums[0..N) = sum_t du, sums[N..2N) = sum_t du * xhat; the same rows are dbeta / dgamma

@@ -327,11 +327,13 @@ __global__ void linear_dcov_kernel(const float* __restrict__ dy, int64_t lddy, i
     for (int64_t bg = b0; bg < b1; bg += 8) {
       float dv[8];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) dv[i] = dy[min(bg + i, b1 - 1) * lddy + n];
-#pragma unroll
       for (int i = 0; i < 8; ++i) {
         const int64_t b = bg + i;
-        if (b >= b1) break;
+        dv[i] = (b < b1) ? dy[b * lddy + n] : 0.f;  // a row past the chunk adds an exact zero
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int64_t b = min(bg + i, b1 - 1);
         const float d = dv[i];
         accs[n_extra * blockDim.x + n_local] += d;
         for (int c = 0; c < n_cov; ++c) {
