@@ -8,8 +8,10 @@
 namespace scvi {
 
 constexpr int LAT_WARPS = 4;
+constexpr int LAT_RPW = 4;  // rows a warp carries through the head GEMV together (4 independent FMA chains per lane)
 
-// one warp per row; weights staged in smem as Wt[k][2L] (k-major => lane j reads Wt[k][j])
+// one warp per LAT_RPW rows; weights staged in smem as Wt[k][2L] (k-major => lane j reads Wt[k][j]), the rows'
+// activations as arT[k][LAT_RPW] so that one broadcast float4 feeds the four chains
 __global__ void __launch_bounds__(LAT_WARPS * 32)
     latent_fwd_kernel(const float* __restrict__ a, int64_t lda, int64_t B, int H, int L,
                       const float* __restrict__ Wm, const float* __restrict__ bm, const float* __restrict__ Wv,
@@ -18,38 +20,57 @@ __global__ void __launch_bounds__(LAT_WARPS * 32)
                       float* __restrict__ kl) {
   extern __shared__ float sm[];
   const int L2 = 2 * L;
-  float* Wt = sm;                          // [H][L2]
-  float* arow = Wt + (size_t)H * L2;       // [LAT_WARPS][H]
-  float* res = arow + LAT_WARPS * H;       // [LAT_WARPS][L2]
+  float* Wt = sm;                                                  // [H][L2]
+  float* arT = sm + (((size_t)H * L2 + 3) & ~(size_t)3);           // [LAT_WARPS][H][LAT_RPW], 16-byte aligned
+  float* res = arT + (size_t)LAT_WARPS * H * LAT_RPW;              // [LAT_WARPS][LAT_RPW][L2]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int e = tid; e < H * L2; e += blockDim.x) {
-    const int k = e / L2, j = e % L2;
-    Wt[e] = (j < L) ? Wm[j * H + k] : Wv[(j - L) * H + k];
+  for (int j = 0; j < L2; ++j) {
+    const float* src = (j < L) ? Wm + (size_t)j * H : Wv + (size_t)(j - L) * H;
+    for (int k = tid; k < H; k += blockDim.x) Wt[k * L2 + j] = src[k];
   }
   __syncthreads();
-  for (int64_t r = (int64_t)blockIdx.x * LAT_WARPS + warp; r < B; r += (int64_t)gridDim.x * LAT_WARPS) {
-    for (int k = lane; k < H; k += 32) arow[warp * H + k] = a[r * lda + k];
+  float* art = arT + (size_t)warp * H * LAT_RPW;
+  float* rs = res + (size_t)warp * LAT_RPW * L2;
+  for (int64_t rb = ((int64_t)blockIdx.x * LAT_WARPS + warp) * LAT_RPW; rb < B;
+       rb += (int64_t)gridDim.x * LAT_WARPS * LAT_RPW) {
+#pragma unroll
+    for (int rr = 0; rr < LAT_RPW; ++rr)
+      for (int k = lane; k < H; k += 32) art[k * LAT_RPW + rr] = (rb + rr < B) ? a[(rb + rr) * lda + k] : 0.f;
     __syncwarp();
     for (int j = lane; j < L2; j += 32) {
-      float s = (j < L) ? bm[j] : bv[j - L];
-      const float* ar = arow + warp * H;
-      for (int k = 0; k < H; ++k) s = fmaf(ar[k], Wt[k * L2 + j], s);
-      res[warp * L2 + j] = s;
+      const float b0 = (j < L) ? bm[j] : bv[j - L];
+      float s0 = b0, s1 = b0, s2 = b0, s3 = b0;
+      for (int k = 0; k < H; ++k) {
+        const float4 av = *reinterpret_cast<const float4*>(art + k * LAT_RPW);
+        const float w = Wt[k * L2 + j];
+        s0 = fmaf(av.x, w, s0);
+        s1 = fmaf(av.y, w, s1);
+        s2 = fmaf(av.z, w, s2);
+        s3 = fmaf(av.w, w, s3);
+      }
+      rs[0 * L2 + j] = s0;
+      rs[1 * L2 + j] = s1;
+      rs[2 * L2 + j] = s2;
+      rs[3 * L2 + j] = s3;
     }
     __syncwarp();
-    float klp = 0.f;
-    for (int l = lane; l < L; l += 32) {
-      const float m = res[warp * L2 + l];
-      const float v = expf(res[warp * L2 + L + l]) + var_eps;
-      const float s = sqrtf(v);
-      const float s2 = s * s;
-      q_m[r * L + l] = m;
-      q_v[r * L + l] = v;
-      z[r * L + l] = fmaf(s, noise[r * L + l], m);
-      klp += 0.5f * (s2 + m * m - 1.f - logf(s2));
+    for (int rr = 0; rr < LAT_RPW; ++rr) {
+      const int64_t r = rb + rr;
+      if (r >= B) break;  // warp-uniform
+      float klp = 0.f;
+      for (int l = lane; l < L; l += 32) {
+        const float m = rs[rr * L2 + l];
+        const float v = expf(rs[rr * L2 + L + l]) + var_eps;
+        const float s = sqrtf(v);
+        const float s2 = s * s;
+        q_m[r * L + l] = m;
+        q_v[r * L + l] = v;
+        z[r * L + l] = fmaf(s, noise[r * L + l], m);
+        klp += 0.5f * (s2 + m * m - 1.f - logf(s2));
+      }
+      klp = warp_sum(klp);
+      if (lane == 0) kl[r] = klp;
     }
-    klp = warp_sum(klp);
-    if (lane == 0) kl[r] = klp;
     __syncwarp();
   }
 }
@@ -68,15 +89,13 @@ __global__ void __launch_bounds__(LATB_THREADS)
   const int L2 = 2 * L;
   float* Wn = sm;                            // [L2][H]   rows 0..L-1 = Wm, L..2L-1 = Wv
   float* as = Wn + (size_t)L2 * H;           // [LATB_ROWS][H]
-  float* dq = as + (size_t)LATB_ROWS * H;    // [LATB_ROWS][L2]  (dq_m | dt)
+  float* dqT = sm + (((size_t)L2 * H + (size_t)LATB_ROWS * H + 3) & ~(size_t)3);  // [L2][LATB_ROWS]  (dq_m | dt), 16-byte aligned
   const int tid = threadIdx.x;
   const int64_t r0 = (int64_t)blockIdx.x * LATB_ROWS;
   const int cnt = (int)min((int64_t)LATB_ROWS, B - r0);
   for (int e = tid; e < L2 * H; e += blockDim.x) Wn[e] = (e < L * H) ? Wm[e] : Wv[e - L * H];
-  for (int e = tid; e < LATB_ROWS * H; e += blockDim.x) {
-    const int r = e / H, k = e % H;
-    as[e] = (r < cnt) ? a[(r0 + r) * lda + k] : 0.f;
-  }
+  for (int r = 0; r < LATB_ROWS; ++r)
+    for (int k = tid; k < H; k += blockDim.x) as[r * H + k] = (r < cnt) ? a[(r0 + r) * lda + k] : 0.f;
   for (int e = tid; e < LATB_ROWS * L; e += blockDim.x) {
     const int r = e / L, l = e % L;
     float dm = 0.f, dt = 0.f;
@@ -90,28 +109,54 @@ __global__ void __launch_bounds__(LATB_THREADS)
       float dv = (g_qv ? g_qv[i] : 0.f) + gz * noise[i] / (2.f * s) + gk * 0.5f * (1.f - 1.f / v);
       dt = dv * (v - var_eps);  // d exp(t) = exp(t) = q_v - var_eps
     }
-    dq[r * L2 + l] = dm;
-    dq[r * L2 + L + l] = dt;
+    dqT[l * LATB_ROWS + r] = dm;  // rows past the batch hold zeros: the loops below run over all LATB_ROWS
+    dqT[(L + l) * LATB_ROWS + r] = dt;
   }
   __syncthreads();
+  static_assert(LATB_ROWS == 16, "the register blocking below is written for 16 rows");
   for (int k = tid; k < H; k += blockDim.x) {
-    // da[r][k] = sum_j dq[r][j] * Wn[j][k]
-    for (int r = 0; r < cnt; ++r) {
-      float s = 0.f;
-      for (int j = 0; j < L2; ++j) s = fmaf(dq[r * L2 + j], Wn[j * H + k], s);
-      da[(r0 + r) * ldda + k] = s;
-    }
-    // dW[j][k] partial = sum_r dq[r][j] * a[r][k]
+    // da[r][k] = sum_j dq[r][j] * Wn[j][k]: one W value and four broadcast float4 of dq^T per j, 16 running sums
+    float s[LATB_ROWS];
+#pragma unroll
+    for (int r = 0; r < LATB_ROWS; ++r) s[r] = 0.f;
     for (int j = 0; j < L2; ++j) {
-      float s = 0.f;
-      for (int r = 0; r < cnt; ++r) s = fmaf(dq[r * L2 + j], as[r * H + k], s);
-      partW[((int64_t)blockIdx.x * L2 + j) * H + k] = s;
+      const float w = Wn[j * H + k];
+      const float4* q4 = reinterpret_cast<const float4*>(dqT + j * LATB_ROWS);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 d = q4[q];
+        s[4 * q + 0] = fmaf(d.x, w, s[4 * q + 0]);
+        s[4 * q + 1] = fmaf(d.y, w, s[4 * q + 1]);
+        s[4 * q + 2] = fmaf(d.z, w, s[4 * q + 2]);
+        s[4 * q + 3] = fmaf(d.w, w, s[4 * q + 3]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < LATB_ROWS; ++r)
+      if (r < cnt) da[(r0 + r) * ldda + k] = s[r];
+    // dW[j][k] partial = sum_r dq[r][j] * a[r][k]: the 16 activations of column k stay in registers
+    float av[LATB_ROWS];
+#pragma unroll
+    for (int r = 0; r < LATB_ROWS; ++r) av[r] = as[r * H + k];
+#pragma unroll 2
+    for (int j = 0; j < L2; ++j) {
+      const float4* q4 = reinterpret_cast<const float4*>(dqT + j * LATB_ROWS);
+      float t = 0.f;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float4 d = q4[q];
+        t = fmaf(d.x, av[4 * q + 0], t);
+        t = fmaf(d.y, av[4 * q + 1], t);
+        t = fmaf(d.z, av[4 * q + 2], t);
+        t = fmaf(d.w, av[4 * q + 3], t);
+      }
+      partW[((int64_t)blockIdx.x * L2 + j) * H + k] = t;
     }
   }
   for (int j = tid; j < L2; j += blockDim.x) {
-    float s = 0.f;
-    for (int r = 0; r < cnt; ++r) s += dq[r * L2 + j];
-    partb[(int64_t)blockIdx.x * L2 + j] = s;
+    float t = 0.f;
+    for (int r = 0; r < cnt; ++r) t += dqT[j * LATB_ROWS + r];
+    partb[(int64_t)blockIdx.x * L2 + j] = t;
   }
 }
 
@@ -214,9 +259,13 @@ int scvi_latent_fwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   SCVI_REQUIRE(a && Wm && bm && Wv && bv && noise && q_m && q_v && z && kl, "scvi_latent_fwd: NULL pointer");
   SCVI_REQUIRE(B >= 0 && H > 0 && L > 0 && L <= 32 && lda >= H, "scvi_latent_fwd: bad shape (L <= 32)");
   if (B == 0) return SCVI_OK;
-  const size_t smem = sizeof(float) * ((size_t)H * 2 * L + LAT_WARPS * H + LAT_WARPS * 2 * L);
-  SCVI_REQUIRE(smem <= 48 * 1024, "scvi_latent_fwd: H*L too large for shared memory");
-  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(B, LAT_WARPS), 148 * 4);
+  const size_t smem = sizeof(float) * ((size_t)H * 2 * L + 4 + (size_t)LAT_WARPS * LAT_RPW * (H + 2 * L));
+  static std::atomic<uint64_t> optin{0};
+  if (smem > 48 * 1024) {
+    SCVI_REQUIRE(smem <= 200 * 1024, "scvi_latent_fwd: H*L too large for shared memory");
+    if (int rc = smem_optin((const void*)latent_fwd_kernel, 200 * 1024, optin, "scvi_latent_fwd")) return rc;
+  }
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(B, LAT_WARPS * LAT_RPW), 148 * 4);
   latent_fwd_kernel<<<blocks, LAT_WARPS * 32, smem, (cudaStream_t)stream>>>(a, lda, B, (int)H, (int)L, Wm, bm, Wv, bv, noise, var_eps, q_m, q_v, z, kl);
   SCVI_LAUNCH_CHECK("scvi_latent_fwd");
   return SCVI_OK;
@@ -234,7 +283,7 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   using namespace scvi;
   SCVI_REQUIRE(a && Wm && Wv && noise && q_m && q_v && da && ws, "scvi_latent_bwd: NULL pointer");
   SCVI_REQUIRE(B > 0 && H > 0 && L > 0 && L <= 32 && lda >= H && ldda >= H, "scvi_latent_bwd: bad shape");
-  const size_t smem = sizeof(float) * ((size_t)2 * L * H + (size_t)LATB_ROWS * H + (size_t)LATB_ROWS * 2 * L);
+  const size_t smem = sizeof(float) * ((size_t)2 * L * H + (size_t)LATB_ROWS * H + (size_t)LATB_ROWS * 2 * L + 4);
   static std::atomic<uint64_t> optin{0};
   if (smem > 48 * 1024) {
     SCVI_REQUIRE(smem <= 200 * 1024, "scvi_latent_bwd: H*L too large for shared memory");

@@ -148,8 +148,7 @@ __global__ void __launch_bounds__(LTHREADS)
       }
     }
     __syncthreads();
-#pragma unroll
-    for (int k = 0; k < LK; k += 4) {
+    auto kstep = [&](int k) {
       float4 a[4], b[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(&xs[(ty + 16 * i) * LPAD + k]);
@@ -164,6 +163,14 @@ __global__ void __launch_bounds__(LTHREADS)
           acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
           acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
         }
+    };
+    if (k_end - k0 >= LK) {
+#pragma unroll
+      for (int k = 0; k < LK; k += 4) kstep(k);
+    } else {
+      // short tail chunk (the whole reduction for the 10-wide latent inputs): the staged zeros beyond it add nothing
+      const int kt = (int)(k_end - k0);
+      for (int k = 0; k < kt; k += 4) kstep(k);
     }
     __syncthreads();
   }
