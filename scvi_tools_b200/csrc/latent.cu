@@ -8,10 +8,14 @@
 namespace scvi {
 
 constexpr int LAT_WARPS = 4;
-constexpr int LAT_RPW = 4;  // rows a warp carries through the head GEMV together (4 independent FMA chains per lane)
+constexpr int LAT_RPW_MAX = 4;  // rows a warp carries through the head GEMV together when the batch is large
 
 // one warp per LAT_RPW rows; weights staged in smem as Wt[k][2L] (k-major => lane j reads Wt[k][j]), the rows'
-// activations as arT[k][LAT_RPW] so that one broadcast float4 feeds the four chains
+// activations as arT[k][LAT_RPW] so that one broadcast float4 feeds four independent FMA chains per lane.
+// LAT_RPW = 4 for tall inputs (SCANVI's label-enumerated 20 x B rows); 1 for few-cell minibatches, where the
+// number of warps in flight matters more than the instruction count (measured: B = 1024, 64 CTAs of 4 rows per
+// warp 18 us, 256 CTAs of 1 row per warp 11.5 us).
+template <int LAT_RPW>
 __global__ void __launch_bounds__(LAT_WARPS * 32)
     latent_fwd_kernel(const float* __restrict__ a, int64_t lda, int64_t B, int H, int L,
                       const float* __restrict__ Wm, const float* __restrict__ bm, const float* __restrict__ Wv,
@@ -21,6 +25,7 @@ __global__ void __launch_bounds__(LAT_WARPS * 32)
   extern __shared__ float sm[];
   const int L2 = 2 * L;
   float* Wt = sm;                                                  // [H][L2]
+  static_assert(LAT_RPW == 1 || LAT_RPW == 4, "rows per warp: 1 or 4");
   float* arT = sm + (((size_t)H * L2 + 3) & ~(size_t)3);           // [LAT_WARPS][H][LAT_RPW], 16-byte aligned
   float* res = arT + (size_t)LAT_WARPS * H * LAT_RPW;              // [LAT_WARPS][LAT_RPW][L2]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -41,17 +46,23 @@ __global__ void __launch_bounds__(LAT_WARPS * 32)
       const float b0 = (j < L) ? bm[j] : bv[j - L];
       float s0 = b0, s1 = b0, s2 = b0, s3 = b0;
       for (int k = 0; k < H; ++k) {
-        const float4 av = *reinterpret_cast<const float4*>(art + k * LAT_RPW);
         const float w = Wt[k * L2 + j];
-        s0 = fmaf(av.x, w, s0);
-        s1 = fmaf(av.y, w, s1);
-        s2 = fmaf(av.z, w, s2);
-        s3 = fmaf(av.w, w, s3);
+        if (LAT_RPW == 4) {
+          const float4 av = *reinterpret_cast<const float4*>(art + k * LAT_RPW);
+          s0 = fmaf(av.x, w, s0);
+          s1 = fmaf(av.y, w, s1);
+          s2 = fmaf(av.z, w, s2);
+          s3 = fmaf(av.w, w, s3);
+        } else {
+          s0 = fmaf(art[k], w, s0);
+        }
       }
       rs[0 * L2 + j] = s0;
-      rs[1 * L2 + j] = s1;
-      rs[2 * L2 + j] = s2;
-      rs[3 * L2 + j] = s3;
+      if (LAT_RPW == 4) {
+        rs[1 * L2 + j] = s1;
+        rs[2 * L2 + j] = s2;
+        rs[3 * L2 + j] = s3;
+      }
     }
     __syncwarp();
     for (int rr = 0; rr < LAT_RPW; ++rr) {
@@ -76,7 +87,7 @@ __global__ void __launch_bounds__(LAT_WARPS * 32)
 }
 
 constexpr int LATB_ROWS = 16;
-constexpr int LATB_THREADS = 128;
+constexpr int LATB_THREADS = 256;  // launch bound; 128 threads when H <= 128 (one hidden column per thread)
 
 __global__ void __launch_bounds__(LATB_THREADS)
     latent_bwd_kernel(const float* __restrict__ a, int64_t lda, int64_t B, int H, int L,
@@ -259,14 +270,20 @@ int scvi_latent_fwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   SCVI_REQUIRE(a && Wm && bm && Wv && bv && noise && q_m && q_v && z && kl, "scvi_latent_fwd: NULL pointer");
   SCVI_REQUIRE(B >= 0 && H > 0 && L > 0 && L <= 32 && lda >= H, "scvi_latent_fwd: bad shape (L <= 32)");
   if (B == 0) return SCVI_OK;
-  const size_t smem = sizeof(float) * ((size_t)H * 2 * L + 4 + (size_t)LAT_WARPS * LAT_RPW * (H + 2 * L));
-  static std::atomic<uint64_t> optin{0};
+  const int rpw = (cdiv(B, LAT_WARPS * LAT_RPW_MAX) >= 2 * 148) ? LAT_RPW_MAX : 1;
+  const size_t smem = sizeof(float) * ((size_t)H * 2 * L + 4 + (size_t)LAT_WARPS * rpw * (H + 2 * L));
+  static std::atomic<uint64_t> optin1{0}, optin4{0};
   if (smem > 48 * 1024) {
     SCVI_REQUIRE(smem <= 200 * 1024, "scvi_latent_fwd: H*L too large for shared memory");
-    if (int rc = smem_optin((const void*)latent_fwd_kernel, 200 * 1024, optin, "scvi_latent_fwd")) return rc;
+    if (int rc = rpw == 1 ? smem_optin((const void*)latent_fwd_kernel<1>, 200 * 1024, optin1, "scvi_latent_fwd")
+                          : smem_optin((const void*)latent_fwd_kernel<LAT_RPW_MAX>, 200 * 1024, optin4, "scvi_latent_fwd"))
+      return rc;
   }
-  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(B, LAT_WARPS * LAT_RPW), 148 * 4);
-  latent_fwd_kernel<<<blocks, LAT_WARPS * 32, smem, (cudaStream_t)stream>>>(a, lda, B, (int)H, (int)L, Wm, bm, Wv, bv, noise, var_eps, q_m, q_v, z, kl);
+  const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(B, LAT_WARPS * rpw), 148 * 4);
+  if (rpw == 1)
+    latent_fwd_kernel<1><<<blocks, LAT_WARPS * 32, smem, (cudaStream_t)stream>>>(a, lda, B, (int)H, (int)L, Wm, bm, Wv, bv, noise, var_eps, q_m, q_v, z, kl);
+  else
+    latent_fwd_kernel<LAT_RPW_MAX><<<blocks, LAT_WARPS * 32, smem, (cudaStream_t)stream>>>(a, lda, B, (int)H, (int)L, Wm, bm, Wv, bv, noise, var_eps, q_m, q_v, z, kl);
   SCVI_LAUNCH_CHECK("scvi_latent_fwd");
   return SCVI_OK;
 }
@@ -293,7 +310,7 @@ int scvi_latent_bwd(const float* a, int64_t lda, int64_t B, int64_t H, int64_t L
   float* partW = (float*)ws;
   float* partb = partW + ctas * 2 * L * H;
   cudaStream_t st = (cudaStream_t)stream;
-  latent_bwd_kernel<<<(unsigned)ctas, LATB_THREADS, smem, st>>>(a, lda, B, (int)H, (int)L, Wm, Wv, noise, var_eps, q_m, q_v, g_qm, g_qv, g_z, g_kl, da, ldda, partW, partb);
+  latent_bwd_kernel<<<(unsigned)ctas, H > 128 ? LATB_THREADS : 128, smem, st>>>(a, lda, B, (int)H, (int)L, Wm, Wv, noise, var_eps, q_m, q_v, g_qm, g_qv, g_z, g_kl, da, ldda, partW, partb);
   SCVI_LAUNCH_CHECK("scvi_latent_bwd");
   {
     ColsumSegs segs{};
