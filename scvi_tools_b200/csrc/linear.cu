@@ -106,24 +106,32 @@ __global__ void __launch_bounds__(LTHREADS)
 
   const int64_t k_begin = SPLIT ? (int64_t)blockIdx.z * k_per_split : 0;
   const int64_t k_end = SPLIT ? min(K, k_begin + k_per_split) : K;
+  // vector path, software-pipelined: the global loads of chunk i + 1 are in flight while chunk i is multiplied out of
+  // shared memory (64 rows x 8 float4 per operand; thread -> (row = tid/8 + 32*it, kq = tid%8))
+  float4 xv[2], wv[2];
+  const int kq = tid & 7;
+  auto gload = [&](int64_t k0) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int rr = (tid >> 3) + 32 * it;
+      const int64_t k = k0 + 4 * kq;
+      const int64_t src = rows[rr];
+      const int64_t n = n0 + rr;
+      xv[it] = (src >= 0 && k < K) ? ld_stream4(x + src * ldx + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+      wv[it] = (n < N && k < K) ? *reinterpret_cast<const float4*>(W + n * ldw + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  if (VEC && k_begin < k_end) gload(k_begin);
   for (int64_t k0 = k_begin; k0 < k_end; k0 += LK) {
     if (VEC) {
-      // 64 rows x 8 float4 per operand; thread -> (row = tid/8 + 32*it, kq = tid%8)
-      const int kq = tid & 7;
 #pragma unroll
       for (int it = 0; it < 2; ++it) {
         const int rr = (tid >> 3) + 32 * it;
-        const int64_t k = k0 + 4 * kq;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int64_t src = rows[rr];
-        if (src >= 0 && k < K) v = ld_stream4(x + src * ldx + k);
+        float4 v = xv[it];
         lib_part[it] += (v.x + v.y) + (v.z + v.w);
         if (log1p_in) v = make_float4(log1pf(v.x), log1pf(v.y), log1pf(v.z), log1pf(v.w));
         *reinterpret_cast<float4*>(&xs[rr * LPAD + 4 * kq]) = v;
-        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int64_t n = n0 + rr;
-        if (n < N && k < K) w = *reinterpret_cast<const float4*>(W + n * ldw + k);
-        *reinterpret_cast<float4*>(&ws[rr * LPAD + 4 * kq]) = w;
+        *reinterpret_cast<float4*>(&ws[rr * LPAD + 4 * kq]) = wv[it];
       }
     } else {
       // scalar path: thread -> (row = tid/32 + 8*it, k = tid%32)
@@ -148,6 +156,7 @@ __global__ void __launch_bounds__(LTHREADS)
       }
     }
     __syncthreads();
+    if (VEC && k0 + LK < k_end) gload(k0 + LK);
     auto kstep = [&](int k) {
       float4 a[4], b[4];
 #pragma unroll
@@ -260,7 +269,9 @@ __global__ void __launch_bounds__(LTHREADS)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
-  for (int64_t b0 = b_begin; b0 < b_end; b0 += BB) {
+  // software-pipelined: the loads of the next 32-row chunk are in flight while this one is multiplied
+  float4 dreg[2], vreg[2];
+  auto gload = [&](int64_t b0) {
     // 32 rows x 64 cols per operand = 512 float4 -> 2 per thread
 #pragma unroll
     for (int it = 0; it < 2; ++it) {
@@ -286,10 +297,20 @@ __global__ void __launch_bounds__(LTHREADS)
         }
         if (log1p_in) v = make_float4(log1pf(v.x), log1pf(v.y), log1pf(v.z), log1pf(v.w));
       }
-      *reinterpret_cast<float4*>(&dys[rr][c4]) = d;
-      *reinterpret_cast<float4*>(&xs[rr][c4]) = v;
+      dreg[it] = d;
+      vreg[it] = v;
+    }
+  };
+  if (b_begin < b_end) gload(b_begin);
+  for (int64_t b0 = b_begin; b0 < b_end; b0 += BB) {
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+      const int e = tid + LTHREADS * it;
+      *reinterpret_cast<float4*>(&dys[e >> 4][(e & 15) * 4]) = dreg[it];
+      *reinterpret_cast<float4*>(&xs[e >> 4][(e & 15) * 4]) = vreg[it];
     }
     __syncthreads();
+    if (b0 + BB < b_end) gload(b0 + BB);
 #pragma unroll 8
     for (int r = 0; r < BB; ++r) {
       const float4 a = *reinterpret_cast<const float4*>(&dys[r][4 * ty]);
@@ -395,22 +416,34 @@ __global__ void __launch_bounds__(LTHREADS)
   const int64_t n_begin = (int64_t)blockIdx.z * n_per_split;
   const int64_t n_end = min(N, n_begin + n_per_split);
   dx += (int64_t)blockIdx.z * B * lddx;
-  for (int64_t nn0 = n_begin; nn0 < n_end; nn0 += LK) {
+  // software-pipelined: the loads of the next 32-output chunk are in flight while this one is multiplied
+  float dyr[8], wr[8];
+  auto gload = [&](int64_t nn0) {
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int e = tid + LTHREADS * it;  // 0..2047
       {  // dy tile: [64 b][32 n]
         const int rr = e >> 5, nn = e & 31;
         const int64_t b = r0 + rr, n = nn0 + nn;
-        dys[rr][nn] = (b < B && n < N) ? dy[b * lddy + n] : 0.f;
+        dyr[it] = (b < B && n < n_end) ? dy[b * lddy + n] : 0.f;
       }
       {  // W tile: [32 n][64 k]
         const int nn = e >> 6, kk = e & 63;
         const int64_t n = nn0 + nn, k = k0 + kk;
-        wsm[nn][kk] = (n < N && k < K) ? W[n * ldw + k] : 0.f;
+        wr[it] = (n < n_end && k < K) ? W[n * ldw + k] : 0.f;
       }
     }
+  };
+  if (n_begin < n_end) gload(n_begin);
+  for (int64_t nn0 = n_begin; nn0 < n_end; nn0 += LK) {
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int e = tid + LTHREADS * it;
+      dys[e >> 5][e & 31] = dyr[it];
+      wsm[e >> 6][e & 63] = wr[it];
+    }
     __syncthreads();
+    if (nn0 + LK < n_end) gload(nn0 + LK);
 #pragma unroll 8
     for (int nn = 0; nn < LK; ++nn) {
       float a[4], b[4];
