@@ -249,11 +249,17 @@ __global__ void __launch_bounds__(LTHREADS)
 // ---------------------------------------------------------------------------------------
 constexpr int BB = 32;  // rows per reduction chunk
 
+// The covariate columns and the bias ride along as extra columns of the x operand: column k in [K, n_w_cols) is the
+// one-hot indicator "some cov_cols[b, .] == k", column n_w_cols (when k_ext > n_w_cols) is all ones, so that
+// dW[:, K:] (the one-hot part of the weight) and db come out of the same GEMM instead of three more launches.
+// db_direct (non-NULL only for an unsplit launch writing straight into dW) receives the ones-column.
 template <bool VEC>
 __global__ void __launch_bounds__(LTHREADS)
     linear_dw_kernel(const float* __restrict__ x, int64_t ldx, const int64_t* __restrict__ row_idx, int64_t B,
                      int64_t K, int64_t N, const float* __restrict__ dy, int64_t lddy, int log1p_in,
-                     int64_t rows_per_split, float* __restrict__ out, int64_t ldo, int64_t slab_stride) {
+                     int64_t rows_per_split, float* __restrict__ out, int64_t ldo, int64_t slab_stride,
+                     const int32_t* __restrict__ cov_cols, int n_cov, int64_t n_w_cols, int64_t k_ext,
+                     float* __restrict__ db_direct) {
   __shared__ __align__(16) float dys[BB][LT];  // [b][n]
   __shared__ __align__(16) float xs[BB][LT];   // [b][k]
   const int tid = threadIdx.x;
@@ -296,6 +302,21 @@ __global__ void __launch_bounds__(LTHREADS)
           }
         }
         if (log1p_in) v = make_float4(log1pf(v.x), log1pf(v.y), log1pf(v.z), log1pf(v.w));
+        if (k0 + c4 + 3 >= K && k_ext > K) {  // this piece reaches into the one-hot / ones columns
+          float* vp = &v.x;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int64_t k = k0 + c4 + q;
+            if (k < K || k >= k_ext) continue;
+            float e = 0.f;
+            if (k < n_w_cols) {
+              for (int c = 0; c < n_cov; ++c) e = (cov_cols[b * n_cov + c] == (int32_t)k) ? 1.f : e;
+            } else {
+              e = 1.f;
+            }
+            vp[q] = e;
+          }
+        }
       }
       dreg[it] = d;
       vreg[it] = v;
@@ -332,9 +353,28 @@ __global__ void __launch_bounds__(LTHREADS)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int64_t k = k0 + 4 * tx + j;
-      if (k < K) o[n * ldo + k] = acc[i][j];
+      if (k >= k_ext) continue;
+      if (db_direct != nullptr && k == n_w_cols)
+        db_direct[n] = acc[i][j];
+      else
+        o[n * ldo + k] = acc[i][j];
     }
   }
+}
+
+// sum of the dW slabs in split order; columns [0, n_w_cols) -> dW (row stride ldw), column n_w_cols -> db
+__global__ void linear_dw_finish_kernel(const float* __restrict__ slabs, int n_split, int64_t N, int64_t k_ext,
+                                        int64_t n_w_cols, int64_t ldw, float* __restrict__ dW,
+                                        float* __restrict__ db) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= N * k_ext) return;
+  float t = 0.f;
+  for (int z = 0; z < n_split; ++z) t += slabs[(int64_t)z * N * k_ext + e];
+  const int64_t n = e / k_ext, k = e % k_ext;
+  if (k < n_w_cols)
+    dW[n * ldw + k] = t;
+  else if (db)
+    db[n] = t;
 }
 
 // covariate columns + bias: per row-chunk partial of
@@ -581,10 +621,11 @@ int scvi_linear_fwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t
 // everything but the dx slabs, which sit behind it
 static int64_t linear_bwd_base_bytes(int64_t B, int64_t K, int64_t N, int64_t n_w_cols) {
   using namespace scvi;
-  const int64_t S = dw_splits(B, K, N);
+  const int64_t KX = n_w_cols + 1;  // x columns + one-hot covariate columns + the ones column of the bias
+  const int64_t S = dw_splits(B, KX, N);
   const int64_t n_extra = n_w_cols - K;
   const int64_t cov = 4 * (cdiv(B, COV_ROWS) + 1) * (n_extra + 1) * N + 256;
-  const int64_t ffma = 4 * (S * N * K + N * K) + cov;
+  const int64_t ffma = 4 * (S * N * KX + N * KX) + cov;
   const int64_t base = N == 128 ? std::max<int64_t>(ffma, tc_enc_dw_ws_bytes(B, K) + cov) : ffma;
   return (base + 255) / 256 * 256;
 }
@@ -609,7 +650,8 @@ int scvi_linear_bwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t
   cudaStream_t st = (cudaStream_t)stream;
   const int n_extra = (int)(n_w_cols - K);
   float* slabs = (float*)ws;
-  const int64_t S = dw_splits(B, K, N);
+  const int64_t KX = n_w_cols + 1;
+  const int64_t S = dw_splits(B, KX, N);
   bool tc = (flags & SCVI_LIN_TC) != 0;
   if (tc && (N != 128 || n_extra != 0 || ldw != K || !(flags & SCVI_LIN_LOG1P))) {
     set_error("scvi_linear_bwd(SCVI_LIN_TC): needs N == 128, SCVI_LIN_LOG1P, no covariates, contiguous dW");
@@ -621,36 +663,33 @@ int scvi_linear_bwd(const void* xv, int64_t ldx, const int64_t* row_idx, int64_t
     return SCVI_EUNSUPPORTED;
   }
   tc = tc && (u8 || ((K % 4 == 0) && (ldx % 4 == 0))) && ((uintptr_t)x % 16 == 0) && (lddy % 4 == 0) && ((uintptr_t)dy % 16 == 0);
-  float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * K + N * K;
+  float* part = tc ? (float*)((uint8_t*)ws + tc_enc_dw_ws_bytes(B, K)) : slabs + S * N * KX + N * KX;
+  bool cov_done = false;  // covariate columns and bias already produced by the dW GEMM
   if (dW && tc) {
     int rc = tc_enc_dw(xv, ldx, row_idx, B, K, dy, lddy, flags, dW, dy_absmax_part, n_absmax_part, ws, st);
     if (rc) return rc;
   } else if (dW) {
     const bool vec = (K % 4 == 0) && (N % 4 == 0) && (ldx % 4 == 0) && (lddy % 4 == 0) &&
                      ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0);
+    SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_bwd: cov_cols is NULL");
+    const int64_t k_ext = n_w_cols + (db ? 1 : 0);
     const int64_t rps = cdiv(cdiv(B, S), BB) * BB;
-    dim3 grid((unsigned)cdiv(K, LT), (unsigned)cdiv(N, LT), (unsigned)S);
+    dim3 grid((unsigned)cdiv(k_ext, LT), (unsigned)cdiv(N, LT), (unsigned)S);
     float* out = (S == 1) ? dW : slabs;
-    const int64_t ldo = (S == 1) ? ldw : K;
+    const int64_t ldo = (S == 1) ? ldw : k_ext;
+    float* dbd = (S == 1) ? db : nullptr;
     if (vec)
-      linear_dw_kernel<true><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * K);
+      linear_dw_kernel<true><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * k_ext, cov_cols, n_cov, n_w_cols, k_ext, dbd);
     else
-      linear_dw_kernel<false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * K);
+      linear_dw_kernel<false><<<grid, LTHREADS, 0, st>>>(x, ldx, row_idx, B, K, N, dy, lddy, flags & SCVI_LIN_LOG1P, rps, out, ldo, N * k_ext, cov_cols, n_cov, n_w_cols, k_ext, dbd);
     SCVI_LAUNCH_CHECK("scvi_linear_bwd(dW)");
     if (S > 1) {
-      if (ldw == K) {
-        int rc = launch_colsum(slabs, S, N * K, N * K, colsum_seg1(dW, N * K), st, "scvi_linear_bwd(reduce)");
-        if (rc) return rc;
-      } else {
-        float* tot = slabs + S * N * K;
-        int rc = launch_colsum(slabs, S, N * K, N * K, colsum_seg1(tot, N * K), st, "scvi_linear_bwd(reduce)");
-        if (rc) return rc;
-        linear_dw_scatter_kernel<<<(unsigned)cdiv(N * K, 256), 256, 0, st>>>(tot, N, K, ldw, dW);
-        SCVI_LAUNCH_CHECK("scvi_linear_bwd(scatter)");
-      }
+      linear_dw_finish_kernel<<<(unsigned)cdiv(N * k_ext, 256), 256, 0, st>>>(slabs, (int)S, N, k_ext, n_w_cols, ldw, dW, db);
+      SCVI_LAUNCH_CHECK("scvi_linear_bwd(dW finish)");
     }
+    cov_done = true;
   }
-  if ((dW && n_extra > 0) || db) {
+  if (!cov_done && ((dW && n_extra > 0) || db)) {
     SCVI_REQUIRE(n_cov == 0 || cov_cols, "scvi_linear_bwd: cov_cols is NULL");
     const int64_t chunks = cdiv(B, COV_ROWS);
     const int bt = 128;
