@@ -81,6 +81,31 @@ SCVI_FM float ex2_fma(float x) {
 #endif
 }
 
+SCVI_FM int fbits(float x) {
+#if defined(__CUDA_ARCH__)
+  return __float_as_int(x);
+#else
+  int b;
+  memcpy(&b, &x, 4);
+  return b;
+#endif
+}
+
+// Is x a non-negative integer below `limit` (<= 2^22)?  If so idx = x.  No float<->int conversion instruction:
+// F2I / I2F / FRND issue on the same quarter-rate pipe as the transcendentals, which bounds these kernels; x + 2^23
+// carries round(x) in its low mantissa bits and (x + 2^23) - 2^23 == x exactly when x is an integer below 2^23.
+SCVI_FM bool count_index(float x, int limit, int& idx) {
+  const float t = x + 8388608.f;
+  idx = fbits(t) & 0x7fffff;
+  return (t - 8388608.f == x) & (x >= 0.f) & (x < (float)limit);
+}
+
+// support check of the count distributions: negative, NaN or non-integer (floats from 2^23 up are all integers)
+SCVI_FM bool bad_count(float x) {
+  const float t = x + 8388608.f;
+  return !(x >= 0.f) | ((x < 8388608.f) & (t - 8388608.f != x));
+}
+
 SCVI_FM float fexp(float x) { return ex2(x * LOG2E); }
 SCVI_FM float flog(float x) { return lg2(x) * LN2; }
 
@@ -112,8 +137,8 @@ SCVI_FM float digamma_pos_fast(float z) {
 
 // lgamma(x + 1) for a count x >= 0: table for integer x < LGX1_TABLE, series otherwise
 SCVI_FM float lgamma_x1(float x, const float* __restrict__ table) {
-  const int xi = (int)x;
-  if (x < (float)LGX1_TABLE && (float)xi == x) return table[xi];
+  int xi;
+  if (count_index(x, LGX1_TABLE, xi)) return table[xi];
   return lgamma_pos(x + 1.f);
 }
 
@@ -195,9 +220,9 @@ SCVI_FM void elem_fwd_tab(float x, float s, float pi, float krow, const GeneK& g
   const float me = mu + eps;
   const float rT = rcp(g.theta + mu + eps);
   const float d_log = -flog(fmaf(mu, g.rth, 1.f));  // log(theta+eps) - log(theta+mu+eps)
-  const int xi = (int)x;
+  int xi;
   float lgd;
-  if (x < (float)LGT && (float)xi == x) lgd = tab[xi];
+  if (count_index(x, LGT, xi)) lgd = tab[xi];
   else lgd = lgamma_pos(x + g.theta) - g.lg_theta - lgamma_x1(x, lgx1);  // rare
   const float base = g.theta * mu * rT;
   if (ZINB) {
@@ -301,7 +326,45 @@ SCVI_FM void elem_bwd_lean(float x, float dgd, float s, float pi, float krow, co
 // ---- the same likelihoods with mu given (standalone log_prob kernels) -------------------------------------
 // lgamma(x + theta) - lgamma(theta) - lgamma(x + 1); exactly 0 at x == 0 as in the reference
 SCVI_FM float lgd_series(float x, const GeneK& g, const float* __restrict__ lgx1) {
-  return x == 0.f ? 0.f : lgamma_pos(x + g.theta) - g.lg_theta - lgamma_x1(x, lgx1);
+  // evaluated for x == 0 too and then discarded: no divergent branch around the three SFU ops (a warp of 128 elements
+  // is never all-zero in practice, so the branch saved nothing and kept the elements from interleaving)
+  const float v = lgamma_pos(x + g.theta) - g.lg_theta - lgamma_x1(x, lgx1);
+  return x == 0.f ? 0.f : v;
+}
+
+// The same value as ll_mu below for a count that passed count_index(x, LGX1_TABLE): the lgamma(x + 1) table is read
+// unconditionally, so the function is straight-line code -- several of them unrolled side by side interleave their
+// SFU chains freely (a per-element fallback branch pins every element between two convergence barriers).
+template <bool ZINB>
+SCVI_FM float ll_mu_count(float x, float mu, float pi, const GeneK& g, float eps, const float* __restrict__ lgx1) {
+  const float me = mu + eps;
+  const float rT = rcp(g.theta + mu + eps);
+  const float d_log = -flog(fmaf(mu, g.rth, 1.f));  // log(theta+eps) - log(theta+mu+eps)
+  const float lx1 = lgx1[fbits(x + 8388608.f) & 0x7fffff];
+  const float v = lgamma_pos(x + g.theta) - g.lg_theta - lx1;
+  const float lgd = x == 0.f ? 0.f : v;
+  if (!ZINB) return fmaf(g.theta, d_log, fmaf(x, flog(me * rT), lgd));
+  const bool zero = x < eps;
+  const float a = fmaf(g.theta, d_log, -pi);
+  const float spn = fmaxf(-pi, 0.f) + flog(1.f + ex2(-fabsf(pi) * LOG2E));  // softplus(-pi)
+  const float oa = 1.f + ex2(-fabsf(a) * LOG2E);
+  const float lsel = flog(zero ? oa : me * rT);
+  const float ll = (zero ? fmaxf(a, 0.f) : a) - spn + (zero ? 1.f : x) * lsel + lgd;
+  return x == eps ? 0.f : ll;  // x == eps: both reference masks are 0
+}
+
+// all four counts of a 16-byte piece are integers in [0, LGX1_TABLE): the precondition of ll_mu_count
+SCVI_FM bool counts_in_table4(float x0, float x1, float x2, float x3) {
+  const float h = 0.5f * (float)(LGX1_TABLE - 1);
+  bool ok = (x0 + 8388608.f) - 8388608.f == x0;
+  ok &= (x1 + 8388608.f) - 8388608.f == x1;
+  ok &= (x2 + 8388608.f) - 8388608.f == x2;
+  ok &= (x3 + 8388608.f) - 8388608.f == x3;
+  ok &= fabsf(x0 - h) <= h;
+  ok &= fabsf(x1 - h) <= h;
+  ok &= fabsf(x2 - h) <= h;
+  ok &= fabsf(x3 - h) <= h;
+  return ok;
 }
 
 template <bool ZINB>
@@ -402,9 +465,9 @@ SCVI_FM void elem_bwd_tab(float x, float s, float pi, float krow, const GeneK& g
   const float rT = rcp(g.theta + mu + eps);
   const float d_log = -flog(fmaf(mu, g.rth, 1.f));
   const float da_dth = d_log + g.theta * (g.rth - rT);
-  const int xi = (int)x;
+  int xi;
   float dgd;
-  if (x < (float)DGT && (float)xi == x) dgd = tab[xi];
+  if (count_index(x, DGT, xi)) dgd = tab[xi];
   else dgd = digamma_pos_fast(x + g.theta) - g.dg_theta;  // rare
   const float base = g.theta * mu * rT;
   const float nz_dth = da_dth - x * rT + dgd;

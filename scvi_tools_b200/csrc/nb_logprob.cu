@@ -83,6 +83,12 @@ __global__ void __launch_bounds__(LP_THREADS)
 // genes live in registers; hand-written SFU math (fastmath.cuh) keeps the kernels on the HBM roofline:
 // NB forward 6 SFU ops per element, ZINB 9.
 constexpr int LP4_THREADS = 128;
+// rows per straight-line block of the forward kernel (two blocks live in registers): NB reads two operands per
+// element, ZINB three -- the same bytes in flight per thread either way
+template <bool ZINB>
+struct Lp4Rb {
+  static constexpr int value = ZINB ? 3 : 4;
+};
 
 __device__ __forceinline__ fm::GeneK lp_gene_k(float theta, float eps) {
   fm::GeneK k;
@@ -95,11 +101,12 @@ __device__ __forceinline__ fm::GeneK lp_gene_k(float theta, float eps) {
 }
 
 template <bool ZINB>
-__global__ void __launch_bounds__(LP4_THREADS, 8)
+__global__ void __launch_bounds__(LP4_THREADS, 4)
     logprob_fwd4_kernel(const float* __restrict__ x, int64_t ldx, const float* __restrict__ mu, int64_t ldmu,
                         const float* __restrict__ theta, const float* __restrict__ pi, int64_t ldpi, int64_t B,
                         int64_t G, float eps, float* __restrict__ out, int64_t ldo, int32_t* __restrict__ bad_support,
                         int row_tile) {
+  constexpr int LP4_RB = Lp4Rb<ZINB>::value;
   __shared__ float s_lgx1[fm::LGX1_TABLE];
   for (int i = threadIdx.x; i < fm::LGX1_TABLE; i += LP4_THREADS) s_lgx1[i] = lgammaf((float)i + 1.f);
   __syncthreads();
@@ -110,8 +117,54 @@ __global__ void __launch_bounds__(LP4_THREADS, 8)
   const float4 th = *reinterpret_cast<const float4*>(theta + g);
   const fm::GeneK k0 = lp_gene_k(th.x, eps), k1 = lp_gene_k(th.y, eps), k2 = lp_gene_k(th.z, eps), k3 = lp_gene_k(th.w, eps);
   bool bad = false;
-#pragma unroll 8
-  for (int64_t r = r0; r < r1; ++r) {
+  // Blocks of LP4_RB rows, register double-buffered: the loads of block i + 1 are issued BEFORE block i is evaluated,
+  // so a warp always has a block in flight (the kernel was waiting on memory: long-scoreboard stalls 5.3 per issue).
+  // Per block ONE test that every count indexes the lgamma(x + 1) table, then LP4_RB x 4 straight-line elements
+  // (their SFU chains interleave); a block holding anything else -- a count >= 256, a non-integer, a negative --
+  // hands the rest of the tile to the generic per-element loop below, which also raises the support flag.
+  auto load_block = [&](float4 (&xv)[LP4_RB], float4 (&m)[LP4_RB], float4 (&p)[LP4_RB], int64_t r) {
+#pragma unroll
+    for (int i = 0; i < LP4_RB; ++i) {
+      xv[i] = ld_stream4(x + (r + i) * ldx + g);
+      m[i] = ld_stream4(mu + (r + i) * ldmu + g);
+      p[i] = ZINB ? ld_stream4(pi + (r + i) * ldpi + g) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  };
+  auto eval_block = [&](const float4 (&xv)[LP4_RB], const float4 (&m)[LP4_RB], const float4 (&p)[LP4_RB], int64_t r) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < LP4_RB; ++i) ok &= fm::counts_in_table4(xv[i].x, xv[i].y, xv[i].z, xv[i].w);
+    if (!ok) return false;
+#pragma unroll
+    for (int i = 0; i < LP4_RB; ++i) {
+      float4 o;
+      o.x = fm::ll_mu_count<ZINB>(xv[i].x, m[i].x, p[i].x, k0, eps, s_lgx1);
+      o.y = fm::ll_mu_count<ZINB>(xv[i].y, m[i].y, p[i].y, k1, eps, s_lgx1);
+      o.z = fm::ll_mu_count<ZINB>(xv[i].z, m[i].z, p[i].z, k2, eps, s_lgx1);
+      o.w = fm::ll_mu_count<ZINB>(xv[i].w, m[i].w, p[i].w, k3, eps, s_lgx1);
+      *reinterpret_cast<float4*>(out + (r + i) * ldo + g) = o;
+    }
+    return true;
+  };
+  int64_t r = r0;
+  if (r + LP4_RB <= r1) {
+    float4 xA[LP4_RB], mA[LP4_RB], pA[LP4_RB], xB[LP4_RB], mB[LP4_RB], pB[LP4_RB];
+    load_block(xA, mA, pA, r);
+    while (true) {
+      const bool moreB = r + 2 * LP4_RB <= r1;
+      if (moreB) load_block(xB, mB, pB, r + LP4_RB);
+      if (!eval_block(xA, mA, pA, r)) break;
+      r += LP4_RB;
+      if (!moreB) break;
+      const bool moreA = r + 2 * LP4_RB <= r1;
+      if (moreA) load_block(xA, mA, pA, r + LP4_RB);
+      if (!eval_block(xB, mB, pB, r)) break;
+      r += LP4_RB;
+      if (!moreA) break;
+    }
+  }
+  for (; r < r1; ++r) {  // generic per-element path: the rest of a tile after a block that failed the test, and the
+                         // rows left over when the tile is not a multiple of the block
     const float4 xv = ld_stream4(x + r * ldx + g);
     const float4 m = ld_stream4(mu + r * ldmu + g);
     float4 p = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -121,8 +174,7 @@ __global__ void __launch_bounds__(LP4_THREADS, 8)
     o.y = fm::ll_mu<ZINB>(xv.y, m.y, p.y, k1, eps, s_lgx1);
     o.z = fm::ll_mu<ZINB>(xv.z, m.z, p.z, k2, eps, s_lgx1);
     o.w = fm::ll_mu<ZINB>(xv.w, m.w, p.w, k3, eps, s_lgx1);
-    bad |= (xv.x < 0.f) || (xv.x != floorf(xv.x)) || (xv.y < 0.f) || (xv.y != floorf(xv.y)) || (xv.z < 0.f) ||
-           (xv.z != floorf(xv.z)) || (xv.w < 0.f) || (xv.w != floorf(xv.w));
+    bad |= fm::bad_count(xv.x) | fm::bad_count(xv.y) | fm::bad_count(xv.z) | fm::bad_count(xv.w);
     *reinterpret_cast<float4*>(out + r * ldo + g) = o;
   }
   if (bad_support != nullptr && bad) *bad_support = 1;
