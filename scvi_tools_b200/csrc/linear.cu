@@ -1,4 +1,5 @@
-// FCLayers linear layer: y = f(x) W[:, :K]^T + sum_c W[:, cov_col_c] + b, fp32 FFMA tiles.
+// FCLayers linear layer: y = f(x) W[:, :K]^T + sum_c W[:, cov_col_c] + b, fp32 FFMA tiles (software-pipelined;
+// split reductions for few-cell minibatches; covariate-column and bias gradients inside the dW GEMM).
 // Replaces `torch.cat((x, one_hot(cat)))` + nn.Linear of FCLayers
 // (reference src/scvi/nn/_base_components.py:148-188,198-215) and the encoder pre-ops
 // log1p / library (src/scvi/module/_vae.py:370-374).  The one-hot concat is a weight-column
@@ -428,14 +429,6 @@ __global__ void linear_dcov_scatter_kernel(const float* __restrict__ tot, int n_
     db[n] = tot[e];
   }
 }
-// dW[n, k] (row stride ldw) = tot[n * K + k]
-__global__ void linear_dw_scatter_kernel(const float* __restrict__ tot, int64_t N, int64_t K, int64_t ldw,
-                                         float* __restrict__ dW) {
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= N * K) return;
-  dW[(e / K) * ldw + e % K] = tot[e];
-}
-
 // dx[b, k] = sum_n dy[b, n] * W[n, k]   (k < K).  gridDim.z > 1: blockIdx.z reduces over its own range of
 // n_per_split outputs into slab z of `dx` (slab stride B * lddx); the caller sums the slabs in order.
 __global__ void __launch_bounds__(LTHREADS)
