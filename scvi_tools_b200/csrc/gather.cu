@@ -5,23 +5,37 @@
 
 namespace scvi {
 
-// one warp-group of threads per row segment; 16-byte vector copies when alignment allows
+// GR_ROWS rows per CTA pass: the row ids are read first, then every thread issues the 16-byte loads of its column
+// piece for all of them before the first store -- 64 bytes in flight per thread and iteration instead of 16 (measured
+// alone, 8192 random rows of 2000 floats: 37.3 us with one row per pass, 36.7 with two, 34.9 with four).
+constexpr int GR_ROWS = 4;
 template <bool VEC4>
 __global__ void gather_rows_kernel(const float* __restrict__ X, int64_t ldx, const int64_t* __restrict__ idx,
                                    int64_t B, int64_t G, float* __restrict__ out, int64_t ldo) {
-  // grid.y strides over rows, grid.x * blockDim.x covers the row
-  for (int64_t b = blockIdx.y; b < B; b += gridDim.y) {
-    const float* src = X + idx[b] * ldx;
-    float* dst = out + b * ldo;
+  // grid.y strides over groups of GR_ROWS rows, grid.x * blockDim.x covers the row
+  for (int64_t b0 = (int64_t)blockIdx.y * GR_ROWS; b0 < B; b0 += (int64_t)gridDim.y * GR_ROWS) {
+    const float* src[GR_ROWS];
+#pragma unroll
+    for (int j = 0; j < GR_ROWS; ++j) src[j] = X + idx[min(b0 + j, B - 1)] * ldx;  // past the end: a duplicate read
     if (VEC4) {
       const int64_t n4 = G >> 2;
       for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
-        float4 v = ld_stream4(src + 4 * i);
-        *reinterpret_cast<float4*>(dst + 4 * i) = v;
+        float4 v[GR_ROWS];
+#pragma unroll
+        for (int j = 0; j < GR_ROWS; ++j) v[j] = ld_stream4(src[j] + 4 * i);
+#pragma unroll
+        for (int j = 0; j < GR_ROWS; ++j)
+          if (b0 + j < B) *reinterpret_cast<float4*>(out + (b0 + j) * ldo + 4 * i) = v[j];
       }
     } else {
-      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x)
-        dst[i] = ld_stream(src + i);
+      for (int64_t i = blockIdx.x * blockDim.x + threadIdx.x; i < G; i += (int64_t)gridDim.x * blockDim.x) {
+        float v[GR_ROWS];
+#pragma unroll
+        for (int j = 0; j < GR_ROWS; ++j) v[j] = ld_stream(src[j] + i);
+#pragma unroll
+        for (int j = 0; j < GR_ROWS; ++j)
+          if (b0 + j < B) out[(b0 + j) * ldo + i] = v[j];
+      }
     }
   }
 }
@@ -158,8 +172,9 @@ int scvi_gather_rows(const float* X, int64_t n_rows, int64_t G, int64_t ldx, con
                    ((uintptr_t)out % 16 == 0);
   const int threads = 256;
   const int64_t per_row = vec ? G / 4 : G;
-  // one CTA per row (2 x 16 B in flight per thread at G=2000); very long rows split over grid.x
-  dim3 grid((unsigned)std::min<int64_t>(cdiv(per_row, 16 * threads), 64), (unsigned)std::min<int64_t>(B, 65535));
+  // one CTA per GR_ROWS rows (2 x 4 x 16 B in flight per thread at G=2000); very long rows split over grid.x
+  dim3 grid((unsigned)std::min<int64_t>(cdiv(per_row, 16 * threads), 64),
+            (unsigned)std::min<int64_t>(cdiv(B, GR_ROWS), 65535));
   if (vec)
     gather_rows_kernel<true><<<grid, threads, 0, (cudaStream_t)stream>>>(X, ldx, idx, B, G, out, ldo);
   else
