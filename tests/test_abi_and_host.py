@@ -44,6 +44,30 @@ def test_workspace_queries_are_pure_host_functions():
     assert _lib.query("scvi_decoder_nll_bwd_ws_bytes", 8192, 128, 2000, 1) >= 4 * 2 * 2000 * 128
 
 
+def test_linear_workspace_covers_the_split_reductions():
+    """The FFMA linear layer splits its reduction for few-cell minibatches (csrc/linear.cu): the workspace queries
+    must hand out room for the partial tiles / slabs exactly when a split can happen, and the dW slabs must cover the
+    covariate and bias columns that ride along in the GEMM."""
+    from scvi_tools_b200 import _lib
+
+    q = _lib.query
+    # forward: totalVI's encoder input layer, 256 cells x 4100 inputs -> 256 (16 tiles, 129 chunks): split-K partials
+    ws = q("scvi_linear_fwd_ws_bytes", 256, 4100, 256, 0)
+    assert ws >= 4 * 2 * 256 * 256 and ws % (4 * 256 * 256) == 0
+    # a minibatch that fills the SMs with tiles, a short reduction, or the library row-sum flag: no split, no workspace
+    assert q("scvi_linear_fwd_ws_bytes", 8192, 4100, 256, 0) == 0
+    assert q("scvi_linear_fwd_ws_bytes", 256, 128, 256, 0) == 0
+    assert q("scvi_linear_fwd_ws_bytes", 256, 4100, 256, _lib.LIN_LIBRARY) == 0
+    # backward: dx slabs on top of the dW slabs when the N reduction is long and the output small
+    base = q("scvi_linear_bwd_ws_bytes", 8192, 276, 4000, 276)
+    few = q("scvi_linear_bwd_ws_bytes", 256, 276, 4000, 276)
+    assert few > 0 and base > 0
+    # dW slabs hold K + covariate columns + the ones column of the bias
+    assert q("scvi_linear_bwd_ws_bytes", 1024, 10, 128, 30) >= 4 * 128 * 31
+    # monotone in the number of weight columns
+    assert q("scvi_linear_bwd_ws_bytes", 1024, 10, 128, 30) >= q("scvi_linear_bwd_ws_bytes", 1024, 10, 128, 10)
+
+
 def test_state_dict_layout_matches_reference_golden():
     """Every parameter / buffer recorded from the reference module exists with the same shape."""
     import scvi_tools_b200 as S
